@@ -1,0 +1,374 @@
+/*
+ * vspg.h -- C ABI of the B200-native render pass of GuidedVolPathVSPGIntegrator.
+ *
+ * This is the drop-in boundary.  Every entry point below
+ * replaces a piece of the reference's seam
+ *     Integrator::Create(name, params, camera, sampler, aggregate, lights, ...)   src/pbrt/cpu/integrators.cpp:3711-3768
+ *     GuidedVolPathVSPGIntegrator::GuidedVolPathVSPGIntegrator(...)              src/pbrt/cpu/guidedvolpathvspgintegrator.cpp:61-198
+ *     Integrator::Render()  (ImageTileIntegrator::Render)                        src/pbrt/cpu/integrators.cpp:75-269
+ *     Film::AddSample / GetPixelRGB / WriteImage                                 src/pbrt/film.h:251-290
+ * and of the OpenPGL C API the integrator consumes (pglFieldLoadFromFile,
+ * pglFieldInit{Surface,Volume}SamplingDistribution, ...; openpgl/api/api.cpp:81-945).
+ *
+ * Plain C: pointers + sizes, int return codes (0 = ok, negative = error; the
+ * message is available through vspg_last_error).  Nothing here throws, exits or
+ * exposes torch / CUDA types (the stream is passed as void*).
+ * All host arrays are borrowed for the duration of the call only; the context
+ * copies what it needs into HBM and owns that device memory.
+ */
+#ifndef VSPG_H
+#define VSPG_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define VSPG_OK 0
+#define VSPG_ERR_INVALID (-1)   /* bad argument / inconsistent description          */
+#define VSPG_ERR_CUDA (-2)      /* CUDA runtime failure (message has the detail)      */
+#define VSPG_ERR_IO (-3)        /* file missing / malformed                           */
+#define VSPG_ERR_UNSUPPORTED (-4) /* scene feature outside the hot-path scope */
+#define VSPG_ERR_STATE (-5)     /* call order (e.g. render before set_scene)          */
+
+/* ------------------------------------------------------------------ scene POD */
+
+/* Row-major 4x4 and its inverse, as pbrt::Transform stores them (util/transform.h). */
+typedef struct vspg_transform {
+    float m[4][4];
+    float mInv[4][4];
+} vspg_transform;
+
+/* cameras.cpp:410 PerspectiveCamera::GenerateRay.  camera_from_raster and
+ * render_from_camera are built by the front end exactly as pbrt does
+ * (cameras.h ProjectiveCamera ctor; CameraTransform with the default
+ * "cameraworld" render space: render = world translated by -cameraPosition). */
+typedef struct vspg_camera {
+    vspg_transform camera_from_raster;
+    vspg_transform render_from_camera;
+    float lens_radius;
+    float focal_distance;
+    int medium;              /* medium the camera sits in, -1 = vacuum */
+    int width, height;       /* full film resolution                    */
+    float filter_radius[2];  /* box filter radius (filters.h BoxFilter) */
+    int filter_type;         /* 0 = box, 1 = gaussian                    */
+    float filter_sigma;      /* gaussian only                            */
+    float imaging_ratio;     /* film.cpp:233 exposureTime*ISO/100        */
+    float max_component_value; /* film.h:257 clamp; +inf = none         */
+} vspg_camera;
+
+enum { VSPG_MEDIUM_HOMOGENEOUS = 0, VSPG_MEDIUM_GRID = 1, VSPG_MEDIUM_RGBGRID = 2 };
+
+/* media.h:221-467.  sigma_a/sigma_s are the RGB spectra ALREADY multiplied by
+ * the medium's "scale" for homogeneous/uniformgrid (their ctors call
+ * sigma_*_spec.Scale(sigmaScale), media.h:240-242 / media.cpp:249-250); for
+ * rgbgrid sigma_scale is applied at lookup time (media.h:427-432). */
+typedef struct vspg_medium {
+    int type;
+    float bounds_min[3], bounds_max[3];
+    vspg_transform render_from_medium;
+    float sigma_a[3], sigma_s[3];
+    float sigma_scale;
+    float g;
+    int nx, ny, nz;
+    const float *density;      /* uniformgrid: nx*ny*nz, x fastest (containers.h:833)   */
+    const float *sigma_a_rgb;  /* rgbgrid: nx*ny*nz*3 or NULL (=> 1)                     */
+    const float *sigma_s_rgb;  /* rgbgrid: nx*ny*nz*3 or NULL (=> 1)                     */
+    int maj_res[3];            /* 16,16,16 for grid/rgbgrid (media.cpp:246,382)          */
+    const float *majorant;     /* maj_res product floats; NULL => built by set_scene     */
+} vspg_medium;
+
+/* One bilinear patch (shapes.h:1350) in render space; vertex order p00,p10,p01,p11. */
+typedef struct vspg_quad {
+    float p00[3], p10[3], p01[3], p11[3];
+    int material;        /* index into materials; -1 = "interface" (null BSDF)            */
+    int area_light;      /* index into lights (type DIFFUSE_AREA) or -1                    */
+    int medium_inside;   /* MediumInterface (interaction.h:117-121); -1 = vacuum           */
+    int medium_outside;
+    int has_interface;   /* 0: primitive has no MediumInterface => ray keeps its medium    */
+    int flip_normal;     /* reverseOrientation ^ transformSwapsHandedness                 */
+} vspg_quad;
+
+/* One triangle (shapes.h:833) in render space. */
+typedef struct vspg_triangle {
+    float p0[3], p1[3], p2[3];
+    int material, area_light, medium_inside, medium_outside, has_interface, flip_normal;
+} vspg_triangle;
+
+/* One sphere (shapes.h:107), full sphere only, object space = translate(center). */
+typedef struct vspg_sphere {
+    float center[3];
+    float radius;
+    int material, area_light, medium_inside, medium_outside, has_interface, flip_normal;
+} vspg_sphere;
+
+enum { VSPG_MATERIAL_DIFFUSE = 0 };
+typedef struct vspg_material {
+    int type;
+    float reflectance[3]; /* DiffuseBxDF R (bxdfs.h:31-82) */
+} vspg_material;
+
+enum {
+    VSPG_LIGHT_DIFFUSE_AREA = 0, /* lights.h:458 */
+    VSPG_LIGHT_POINT = 1,
+    VSPG_LIGHT_DISTANT = 2,
+    VSPG_LIGHT_UNIFORM_INFINITE = 3
+};
+typedef struct vspg_light {
+    int type;
+    float L[3];        /* emitted radiance / intensity, already times "scale" (RGB mode) */
+    float pos[3];      /* point: position (render space); distant: direction TO the light */
+    int shape_kind;    /* area: 0 quad, 1 triangle, 2 sphere                             */
+    int shape_index;   /* area: index into that shape array                              */
+    int two_sided;     /* area                                                           */
+    int medium;        /* point: medium the light sits in; -1 vacuum                     */
+} vspg_light;
+
+enum { VSPG_LIGHTSAMPLER_UNIFORM = 0, VSPG_LIGHTSAMPLER_POWER = 1, VSPG_LIGHTSAMPLER_BVH = 2 };
+
+typedef struct vspg_scene_desc {
+    vspg_camera camera;
+    int n_media;      const vspg_medium *media;
+    int n_quads;      const vspg_quad *quads;
+    int n_triangles;  const vspg_triangle *triangles;
+    int n_spheres;    const vspg_sphere *spheres;
+    int n_materials;  const vspg_material *materials;
+    int n_lights;     const vspg_light *lights;
+} vspg_scene_desc;
+
+/* ------------------------------------------------------------ guiding inputs */
+
+/* openpgl KDNode (spatial/kdtree/KDTree.h:20-178): splitDim in the top 2 bits
+ * (3 = leaf), child / data index in the low 30. */
+typedef struct vspg_kdnode {
+    float split;
+    uint32_t dim_idx;
+} vspg_kdnode;
+
+#define VSPG_MAX_LOBES 32
+/* One region's ParallaxAwareVonMisesFisherMixture<4,32,true>
+ * (directional/vmm/ParallaxAwareVonMisesFisherMixture.h:64-81) flattened in the
+ * lobe order of the file (vector k, lane j => lobe 4k+j). */
+typedef struct vspg_mixture {
+    float weight[VSPG_MAX_LOBES];
+    float kappa[VSPG_MAX_LOBES];
+    float mu_x[VSPG_MAX_LOBES], mu_y[VSPG_MAX_LOBES], mu_z[VSPG_MAX_LOBES];
+    float norm[VSPG_MAX_LOBES];
+    float e_minus_2k[VSPG_MAX_LOBES];
+    float mean_cos[VSPG_MAX_LOBES];
+    float distance[VSPG_MAX_LOBES];
+    float vsp_weight[VSPG_MAX_LOBES];
+    float pivot[3];
+    int num_components;
+    int valid;             /* IRegion::valid (spatial/Region.h:80) */
+    int pad_[3];
+} vspg_mixture;
+
+/* RegionNeighbours<4> (spatial/KNN.h:66-124), rebuilt at load time like
+ * Field::deserialize does (field/Field.h:345-348). */
+typedef struct vspg_neighbours {
+    uint32_t ids[8];       /* ~0u = empty slot */
+    float px[8], py[8], pz[8];
+    uint32_t size;
+    uint32_t pad_[7];
+} vspg_neighbours;
+
+typedef struct vspg_field {
+    int usable;            /* m_iteration > 0 (field/Field.h:116)                    */
+    float bounds_min[3], bounds_max[3]; /* KDTree::m_bounds                          */
+    int n_nodes;           const vspg_kdnode *nodes;
+    int n_regions;         const vspg_mixture *regions;
+    const vspg_neighbours *neighbours;  /* n_regions, or NULL if !stochastic_nn      */
+    int stochastic_nn;     /* m_useStochasticNNLookUp                                */
+    int is_nn;             /* m_useISNNLookUp (unsupported if set)                   */
+} vspg_field;
+
+typedef struct vspg_guiding_desc {
+    const vspg_field *surface;  /* NULL = no cache (guiding disabled)                */
+    const vspg_field *volume;
+    const float *isg_vsp;       /* width*height VSP estimate (layer VSP.Y) or NULL   */
+    int isg_width, isg_height;
+    const float *tr_rgb;        /* width*height*3 transmittance buffer or NULL       */
+    int tr_width, tr_height;
+} vspg_guiding_desc;
+
+/* guidedvolpathvspgintegrator.cpp:1260-1322 (same names, same defaults). */
+typedef struct vspg_integrator_params {
+    int max_depth;              /* maxdepth 5              */
+    int min_rr_depth;           /* minrrdepth 1            */
+    int use_nee;                /* usenee true             */
+    int surface_guiding;        /* surfaceguiding true     */
+    int volume_guiding;         /* volumeguiding true      */
+    int surface_guiding_ris;    /* surfaceguidingtype "ris" => 1, "mis" => 0 */
+    int volume_guiding_ris;     /* volumeguidingtype  "mis" => 0             */
+    int vsp_guiding;            /* vspguiding true         */
+    int vsp_primary_guiding;    /* vspprimaryguiding true  */
+    int vsp_secondary_guiding;  /* vspsecondaryguiding true*/
+    float vsp_mis_ratio;        /* vspmisratio 0.5         */
+    int vsp_criterion_variance; /* vspcriterion "variance" => 1 (only tags the cache) */
+    int vsp_sampling_nds;       /* vspsamplingmethod "resampling" => 0, "nds" => 1    */
+    int collision_probability_bias; /* collisionProbabilityBias false (NDS+)          */
+    int light_sampler;          /* lightsampler "bvh"      */
+    int regularize;             /* regularize false (no effect on diffuse/interface)  */
+} vspg_integrator_params;
+
+typedef struct vspg_counters {
+    unsigned long long paths;             /* P: camera samples finished                */
+    unsigned long long density_queries;   /* Q: Medium::SamplePoint calls              */
+    unsigned long long dda_steps;         /* S: DDAMajorantIterator::Next calls        */
+    unsigned long long cache_lookups;     /* C: pgl sampling-distribution inits        */
+    unsigned long long bvh_nodes;         /* B: BVH nodes visited                      */
+    unsigned long long shadow_rays;
+    unsigned long long kernel_launches;   /* our kernels launched since create/reset   */
+    unsigned long long wave_iterations;
+} vspg_counters;
+
+typedef struct vspg_ctx vspg_ctx;
+
+/* ------------------------------------------------------------------ lifecycle */
+int vspg_create(vspg_ctx **out, int device_ordinal);
+void vspg_destroy(vspg_ctx *ctx);
+const char *vspg_last_error(const vspg_ctx *ctx); /* ctx may be NULL: last create error */
+const char *vspg_version(void);
+
+void vspg_integrator_defaults(vspg_integrator_params *p);
+
+/* replaces RenderCPU's object construction (cpu/render.cpp:24-160) */
+int vspg_set_scene(vspg_ctx *ctx, const vspg_scene_desc *scene);
+/* replaces the loadGuidingCache / loadISGBuffer / loadTrBuffer branches (vspg.cpp:117-193) */
+int vspg_set_guiding(vspg_ctx *ctx, const vspg_guiding_desc *guiding);
+/* replaces GuidedVolPathVSPGIntegrator::Create (vspg.cpp:1260-1322) */
+int vspg_set_integrator(vspg_ctx *ctx, const vspg_integrator_params *params);
+
+/* Maximum number of paths resident in HBM at once (wavefront capacity). 0 = default. */
+int vspg_set_capacity(vspg_ctx *ctx, int max_paths_in_flight);
+
+/* ------------------------------------------------------------------ rendering */
+/* replaces ImageTileIntegrator::Render's wave loop (cpu/integrators.cpp:75-269):
+ * renders sample indices [spp_begin, spp_end) with stride spp_stride (sample-pass
+ * sharding across ranks: rank r uses spp_begin=r, stride=N) over the pixel window
+ * [x0,x1) x [y0,y1), accumulating into the ctx-owned film.  Asynchronous on
+ * `cuda_stream` (a cudaStream_t, NULL = default stream) except for the bounded
+ * polling of the device-side path counter.  seed = Options->seed. */
+int vspg_render(vspg_ctx *ctx, int spp_begin, int spp_end, int spp_stride, int x0, int y0, int x1,
+                int y1, int seed, void *cuda_stream);
+
+/* Film (film.h:251-290): 4 doubles per pixel {rgbSum[3], weightSum}. */
+int vspg_film_clear(vspg_ctx *ctx);
+int vspg_film_device_ptr(vspg_ctx *ctx, double **rgbw, size_t *n_doubles);
+int vspg_film_download(vspg_ctx *ctx, double *host_rgbw);           /* H*W*4 doubles     */
+int vspg_film_resolve(vspg_ctx *ctx, float *host_rgb);              /* H*W*3 rgb/weight  */
+int vspg_counters_get(vspg_ctx *ctx, vspg_counters *out);
+int vspg_counters_reset(vspg_ctx *ctx);
+/* average device time (ms) and launch count of the medium-tracking kernel since reset */
+int vspg_kernel_times(vspg_ctx *ctx, int enable, float *ms_medium, float *ms_total,
+                      unsigned long long *launches_medium);
+
+/* -------------------------------------------------- host front end (C++ side) */
+/* Scene handle produced by the .pbrt front end (parser.cpp / scene.cpp subset).
+ * The handle owns every array the descs point at. */
+typedef struct vspg_host_scene vspg_host_scene;
+int vspg_host_scene_parse(const char *pbrt_path, vspg_host_scene **out, char *err, size_t err_len);
+int vspg_host_scene_parse_string(const char *pbrt_text, const char *base_dir, vspg_host_scene **out,
+                                 char *err, size_t err_len);
+void vspg_host_scene_free(vspg_host_scene *s);
+const vspg_scene_desc *vspg_host_scene_desc(const vspg_host_scene *s);
+const vspg_guiding_desc *vspg_host_scene_guiding(const vspg_host_scene *s);
+const vspg_integrator_params *vspg_host_scene_integrator(const vspg_host_scene *s);
+int vspg_host_scene_spp(const vspg_host_scene *s);        /* Sampler "pixelsamples"        */
+int vspg_host_scene_seed(const vspg_host_scene *s);       /* Sampler "seed" / Options seed */
+const char *vspg_host_scene_outfile(const vspg_host_scene *s); /* Film "filename"           */
+
+/* loaders, usable on their own (replace pglFieldLoadFromFile, ISGB/Tr EXR readers) */
+typedef struct vspg_host_field vspg_host_field;
+int vspg_host_field_load(const char *pgl_path, vspg_host_field **out, char *err, size_t err_len);
+void vspg_host_field_free(vspg_host_field *f);
+const vspg_field *vspg_host_field_surface(const vspg_host_field *f);
+const vspg_field *vspg_host_field_volume(const vspg_host_field *f);
+
+/* Minimal EXR I/O (util/image.cpp subset: scanline, NONE/ZIP/ZIPS, HALF/FLOAT). */
+int vspg_exr_read_channel(const char *path, const char *channel, float **out, int *w, int *h,
+                          char *err, size_t err_len); /* free with vspg_free */
+int vspg_exr_write_rgb(const char *path, const float *rgb, int w, int h, int as_half);
+void vspg_free(void *p);
+
+/* 16^3 majorant grid exactly as GridMedium / RGBGridMedium ctors build it
+ * (media.cpp:218-270, 370-409).  out has maj_res product floats. */
+int vspg_build_majorant_grid(const vspg_medium *m, float *out);
+
+/* -------------------------------------------- per-kernel parity hooks (GPU) */
+typedef struct vspg_segment {
+    float t_min, t_max;
+    float sigma_maj[3];
+} vspg_segment;
+
+/* DDAMajorantIterator (media.h:140-218) over medium `medium`: for ray i writes up to
+ * max_segments segments to out[i*max_segments..] and the count to out_count[i].
+ * rays: n*(ox,oy,oz,dx,dy,dz,tMax) floats; tMax is the value AFTER normalisation. */
+int vspg_debug_majorant_segments(vspg_ctx *ctx, int medium, int n, const float *rays7,
+                                 int max_segments, vspg_segment *out, int *out_count);
+
+/* One SampleDistance call (vspg.cpp:637-1096) up to and including the
+ * scatter / pass-through decision, on explicit inputs. */
+typedef struct vspg_sd_input {
+    float o[3], d[3];
+    float t_max;            /* si->tHit */
+    int medium;
+    int pixel_x, pixel_y;
+    int depth;
+    int channel;            /* hero channel                                          */
+    float vsp;              /* secondary VSP as returned by the guided distribution; ignored at depth 0 */
+    float beta[3], r_u[3], r_l[3];
+    uint64_t rng_state, rng_inc; /* path sampler (PCG32) state before the call      */
+} vspg_sd_input;
+
+typedef struct vspg_sd_output {
+    int scattered;          /* a real-scatter vertex was chosen (before phase sampling) */
+    int terminated;
+    int depth;              /* after the call                                         */
+    float p[3];             /* scatter position                                       */
+    float sigma_a[3], sigma_s[3]; /* medium properties at p                           */
+    float beta[3], r_u[3], r_l[3];
+    uint64_t rng_state;     /* path sampler state after the call                      */
+    int density_queries;
+    int dda_steps;
+} vspg_sd_output;
+int vspg_debug_sample_distance(vspg_ctx *ctx, int n, const vspg_sd_input *in, vspg_sd_output *out);
+
+/* Field::getRegion (field/Field.h:114-150): leaf id, selected region id, u after draw(). */
+int vspg_debug_cache_lookup(vspg_ctx *ctx, int is_surface, int n, const float *pos3, const float *u,
+                            int *out_leaf, int *out_region, float *out_u);
+
+/* GuidedPhaseFunction / GuidedBSDF (cpu/guiding.h:57-638) on explicit inputs. */
+typedef struct vspg_gs_input {
+    float p[3];
+    float wo[3];            /* = -ray.d                                              */
+    float n[3];             /* surface: shading normal (unused for volume)           */
+    float g;                /* volume: HG g; surface: unused                         */
+    float reflectance[3];   /* surface: diffuse R                                    */
+    float v;                /* cache-lookup sample                                   */
+    float u1;               /* surface: Get1D for Sample_f                           */
+    float u2[2];            /* Get2D                                                 */
+    float wq[3];            /* extra direction at which pdf / VSP are evaluated      */
+    uint64_t rng_state, rng_inc; /* sampler, for the extra RIS draws                  */
+} vspg_gs_input;
+typedef struct vspg_gs_output {
+    int ok;                 /* cache init succeeded                                  */
+    int region;
+    int valid;              /* a sample was produced                                 */
+    float wi[3];
+    float f[3];             /* surface: f; volume: f[0] = p                          */
+    float pdf, scatter_pdf, mis_pdf;
+    float pdf_wq;           /* Guided{BSDF,PhaseFunction}::PDF(wo, wq)               */
+    float vsp_wq;           /* VolumeScatterProbability(wq)                          */
+    uint64_t rng_state;
+} vspg_gs_output;
+int vspg_debug_guided_sample(vspg_ctx *ctx, int is_surface, int n, const vspg_gs_input *in,
+                             vspg_gs_output *out);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* VSPG_H */

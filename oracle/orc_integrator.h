@@ -1,0 +1,966 @@
+// TEST INFRASTRUCTURE -- NOT PRODUCT CODE.  (see orc_math.h header)
+// CPU restatement of GuidedVolPathVSPGIntegrator's render pass: camera sample, Li, SampleDistance,
+// SampleLd, guided BSDF / phase sampling, film.  Paths relative to /root/reference/src/pbrt/;
+// "vspg.cpp" = cpu/guidedvolpathvspgintegrator.cpp.
+#pragma once
+#include <atomic>
+#include <cmath>
+#include <thread>
+#include <vector>
+
+#include "orc_guiding.h"
+#include "orc_media.h"
+
+namespace orc {
+
+struct Hit {
+    bool valid = false;
+    float t = Infinity;
+    int kind = 0, index = -1;  // 0 quad, 1 triangle, 2 sphere
+    float u = 0, v = 0;
+};
+
+// Surface interaction data the integrator consumes (interaction.h SurfaceInteraction subset)
+struct SurfaceIntr {
+    V3 p, pError, n, ns, dpdu, wo;
+    float uv[2];
+    int material = -1, areaLight = -1;
+    bool hasInterface = false;
+    int mediumInside = -1, mediumOutside = -1;
+    int rayMedium = -1;
+    int GetMedium(V3 w) const {  // interaction.h:117-121
+        if (hasInterface) return Dot(w, n) > 0 ? mediumOutside : mediumInside;
+        return rayMedium;
+    }
+};
+
+// ray.h:75-92
+inline V3 OffsetRayOrigin(V3 p, V3 pError, V3 n, V3 w) {
+    float d = Dot(Abs(n), pError);
+    V3 offset = d * n;
+    if (Dot(w, n) < 0) offset = -offset;
+    V3 po = p + offset;
+    for (int i = 0; i < 3; ++i) {
+        if (offset[i] > 0) po[i] = NextFloatUp(po[i]);
+        else if (offset[i] < 0) po[i] = NextFloatDown(po[i]);
+    }
+    return po;
+}
+
+// util/math.h:613-636
+inline bool Quadratic(float a, float b, float c, float *t0, float *t1) {
+    if (a == 0) {
+        if (b == 0) return false;
+        *t0 = *t1 = -c / b;
+        return true;
+    }
+    float discrim = DifferenceOfProducts(b, b, 4 * a, c);
+    if (discrim < 0) return false;
+    float rootDiscrim = std::sqrt(discrim);
+    float q = -0.5f * (b + std::copysign(rootDiscrim, b));
+    *t0 = q / a; *t1 = c / q;
+    if (*t0 > *t1) std::swap(*t0, *t1);
+    return true;
+}
+// util/math.h SquareMatrix<3> Determinant: m00*DoP(m11,m22,m12,m21) - m01*DoP(m10,m22,m12,m20) + m02*DoP(m10,m21,m11,m20)
+inline float Det3(float m00, float m01, float m02, float m10, float m11, float m12, float m20, float m21, float m22) {
+    float minor12 = DifferenceOfProducts(m11, m22, m12, m21);
+    float minor02 = DifferenceOfProducts(m10, m22, m12, m20);
+    float minor01 = DifferenceOfProducts(m10, m21, m11, m20);
+    return FMA(m02, minor01, DifferenceOfProducts(m00, minor12, m01, minor02));
+}
+// shapes.h:1279-1345 IntersectBilinearPatch
+inline bool IntersectBilinearPatch(V3 ro, V3 rd, float tMax, V3 p00, V3 p10, V3 p01, V3 p11, float *uo, float *vo, float *to) {
+    float a = Dot(Cross(p10 - p00, p01 - p11), rd);
+    float c = Dot(Cross(p00 - ro, rd), p01 - p00);
+    float b = Dot(Cross(p10 - ro, rd), p11 - p10) - (a + c);
+    float u1, u2;
+    if (!Quadratic(a, b, c, &u1, &u2)) return false;
+    float eps = gamma_(30) * (MaxComponentValue(Abs(ro)) + MaxComponentValue(Abs(rd)) + MaxComponentValue(Abs(p00)) +
+                              MaxComponentValue(Abs(p10)) + MaxComponentValue(Abs(p01)) + MaxComponentValue(Abs(p11)));
+    float t = tMax, u = 0, v = 0;
+    if (0 <= u1 && u1 <= 1) {
+        V3 uo_ = LerpV(u1, p00, p10);
+        V3 ud = LerpV(u1, p01, p11) - uo_;
+        V3 deltao = uo_ - ro;
+        V3 perp = Cross(rd, ud);
+        float p2 = LengthSquared(perp);
+        float v1 = Det3(deltao.x, rd.x, perp.x, deltao.y, rd.y, perp.y, deltao.z, rd.z, perp.z);
+        float t1 = Det3(deltao.x, ud.x, perp.x, deltao.y, ud.y, perp.y, deltao.z, ud.z, perp.z);
+        if (t1 > p2 * eps && 0 <= v1 && v1 <= p2) { u = u1; v = v1 / p2; t = t1 / p2; }
+    }
+    if (0 <= u2 && u2 <= 1 && u2 != u1) {
+        V3 uo_ = LerpV(u2, p00, p10);
+        V3 ud = LerpV(u2, p01, p11) - uo_;
+        V3 deltao = uo_ - ro;
+        V3 perp = Cross(rd, ud);
+        float p2 = LengthSquared(perp);
+        float v2 = Det3(deltao.x, rd.x, perp.x, deltao.y, rd.y, perp.y, deltao.z, rd.z, perp.z);
+        float t2 = Det3(deltao.x, ud.x, perp.x, deltao.y, ud.y, perp.y, deltao.z, ud.z, perp.z);
+        t2 /= p2;
+        if (0 <= v2 && v2 <= p2 && t > t2 && t2 > eps) { t = t2; u = u2; v = v2 / p2; }
+    }
+    if (t >= tMax) return false;
+    *uo = u; *vo = v; *to = t;
+    return true;
+}
+
+struct LightSampleCtx { V3 p, pError, n, ns; };
+
+struct Scene {
+    const vspg_scene_desc *d = nullptr;
+    const vspg_guiding_desc *g = nullptr;
+    vspg_integrator_params ip;
+    std::vector<Medium> media;
+    std::vector<float> quadArea;
+    std::vector<float> lightCdf;  // power sampler pmf
+    V3 sceneCenter; float sceneRadius = 0;
+    int seed = 0;
+    bool ownMajorant = false;
+
+    void init(const vspg_scene_desc *desc, const vspg_guiding_desc *gd, const vspg_integrator_params *p, bool ownMaj) {
+        d = desc; g = gd; ip = *p; ownMajorant = ownMaj;
+        media.resize(d->n_media);
+        for (int i = 0; i < d->n_media; i++) media[i].init(&d->media[i], ownMaj);
+        quadArea.resize(d->n_quads);
+        V3 bmin(Infinity, Infinity, Infinity), bmax(-Infinity, -Infinity, -Infinity);
+        for (int i = 0; i < d->n_quads; i++) {
+            const vspg_quad &q = d->quads[i];
+            V3 p00(q.p00), p10(q.p10), p01(q.p01), p11(q.p11);
+            quadArea[i] = QuadArea(p00, p10, p01, p11);
+            for (V3 p : {p00, p10, p01, p11})
+                for (int a = 0; a < 3; a++) { bmin[a] = std::min(bmin[a], p[a]); bmax[a] = std::max(bmax[a], p[a]); }
+        }
+        // Bounds3::BoundingSphere: center = (pMin+pMax)/2, radius = Inside(center) ? Distance(center, pMax) : 0
+        sceneCenter = (bmin + bmax) / 2;
+        sceneRadius = d->n_quads ? Distance(sceneCenter, bmax) : 0;
+        // PowerLightSampler pmf (lightsamplers.cpp:76-96): phi averaged over RGB
+        lightCdf.assign(d->n_lights, 0.f);
+        float sum = 0;
+        for (int i = 0; i < d->n_lights; i++) { lightCdf[i] = LightPower(i); sum += lightCdf[i]; }
+        if (sum == 0) for (auto &v : lightCdf) v = 1.f, sum += 1.f;
+        for (auto &v : lightCdf) v /= sum;
+    }
+    static bool IsRectangle(V3 p00, V3 p10, V3 p01, V3 p11) {  // shapes.h BilinearPatch::IsRectangle
+        if (p00 == p01 || p01 == p11 || p11 == p10 || p10 == p00) return false;
+        V3 n = Normalize(Cross(p10 - p00, p01 - p00));
+        if (AbsDot(Normalize(p11 - p00), n) > 1e-5f) return false;
+        V3 pCenter = (p00 + p01 + p10 + p11) / 4;
+        float d2[4] = {DistanceSquared(p00, pCenter), DistanceSquared(p01, pCenter), DistanceSquared(p10, pCenter), DistanceSquared(p11, pCenter)};
+        for (int i = 1; i < 4; ++i)
+            if (std::abs(d2[i] - d2[0]) / d2[0] > 1e-4f) return false;
+        return true;
+    }
+    static float QuadArea(V3 p00, V3 p10, V3 p01, V3 p11) {  // shapes.cpp:1038-1068
+        if (IsRectangle(p00, p10, p01, p11)) return Distance(p00, p01) * Distance(p00, p10);
+        constexpr int na = 3;
+        V3 p[na + 1][na + 1];
+        for (int i = 0; i <= na; ++i) {
+            float u = float(i) / float(na);
+            for (int j = 0; j <= na; ++j) {
+                float v = float(j) / float(na);
+                p[i][j] = LerpV(u, LerpV(v, p00, p01), LerpV(v, p10, p11));
+            }
+        }
+        float area = 0;
+        for (int i = 0; i < na; ++i)
+            for (int j = 0; j < na; ++j) area += 0.5f * Length(Cross(p[i + 1][j + 1] - p[i][j], p[i + 1][j] - p[i][j + 1]));
+        return area;
+    }
+    float LightPower(int i) const {  // lights.cpp Phi() for each type, averaged over RGB
+        const vspg_light &l = d->lights[i];
+        S3 L(l.L);
+        switch (l.type) {
+        case VSPG_LIGHT_DIFFUSE_AREA: return (L * (Pi * (l.two_sided ? 2.f : 1.f) * quadArea[l.shape_index])).Average();
+        case VSPG_LIGHT_POINT: return (L * (4 * Pi)).Average();
+        case VSPG_LIGHT_DISTANT: return (L * (Pi * Sqr(sceneRadius))).Average();
+        default: return (L * (4 * Pi * Pi * Sqr(sceneRadius))).Average();
+        }
+    }
+
+    // Closest hit by brute force over all primitives with the reference's intersection arithmetic
+    // (the product walks its own BVH; the closest hit is the same hit).
+    Hit Intersect(V3 ro, V3 rd, float tMax) const {
+        Hit h;
+        float best = tMax;
+        for (int i = 0; i < d->n_quads; i++) {
+            const vspg_quad &q = d->quads[i];
+            float u, v, t;
+            if (IntersectBilinearPatch(ro, rd, best, V3(q.p00), V3(q.p10), V3(q.p01), V3(q.p11), &u, &v, &t)) {
+                best = t; h.valid = true; h.t = t; h.kind = 0; h.index = i; h.u = u; h.v = v;
+            }
+        }
+        return h;
+    }
+    // shapes.h:1398-1500 BilinearPatch::InteractionFromIntersection (no mesh uv / normals) + primitive.cpp
+    // GeometricPrimitive::Intersect -> SetIntersectionProperties (interaction.h:218-229)
+    SurfaceIntr MakeIntr(const Hit &h, V3 rayD, int rayMedium) const {
+        SurfaceIntr s;
+        const vspg_quad &q = d->quads[h.index];
+        V3 p00(q.p00), p10(q.p10), p01(q.p01), p11(q.p11);
+        s.p = LerpV(h.u, LerpV(h.v, p00, p01), LerpV(h.v, p10, p11));
+        V3 dpdu = LerpV(h.v, p10, p11) - LerpV(h.v, p00, p01);
+        V3 dpdv = LerpV(h.u, p01, p11) - LerpV(h.u, p00, p10);
+        V3 pAbsSum = Abs(p00) + Abs(p01) + Abs(p10) + Abs(p11);
+        s.pError = gamma_(6) * pAbsSum;
+        s.n = Normalize(Cross(dpdu, dpdv));
+        if (q.flip_normal) s.n = -s.n;
+        s.ns = s.n; s.dpdu = dpdu;
+        s.wo = Normalize(-rayD);
+        s.uv[0] = h.u; s.uv[1] = h.v;
+        s.material = q.material; s.areaLight = q.area_light;
+        s.hasInterface = q.has_interface && (q.medium_inside != q.medium_outside);
+        s.mediumInside = q.medium_inside; s.mediumOutside = q.medium_outside; s.rayMedium = rayMedium;
+        return s;
+    }
+    // lights.h:492-515 DiffuseAreaLight::L
+    S3 AreaL(int light, V3 n, V3 w) const {
+        const vspg_light &l = d->lights[light];
+        if (!l.two_sided && Dot(n, w) < 0) return S3(0.f);
+        return S3(l.L);
+    }
+};
+
+// cpu/guiding.h:57-358 GuidedBSDF for the DiffuseBxDF
+struct GuidedBSDF {
+    const Scene *sc; Sampler *sampler;
+    bool enableGuiding, enableScatterGuiding, ris;
+    float guidingProbability = 0.5f;
+    bool useGuiding = false, useScatterGuiding = false;
+    SamplingDistribution dist;
+    Frame frame; S3 R; bool hasR = false;
+    int lookups = 0;
+    void setBSDF(V3 ns, V3 dpdus, S3 refl) { frame = Frame::FromXZ(Normalize(dpdus), ns); R = refl; hasR = (bool)R; }
+    bool IsNonSpecular() const { return hasR; }  // DiffuseReflection flag only when R != 0 (bxdfs.h:82-84)
+    S3 f(V3 woR, V3 wiR) const {  // bsdf.h:41-47 + bxdfs.h:39-43
+        V3 wi = frame.ToLocal(wiR), wo = frame.ToLocal(woR);
+        if (wo.z == 0) return S3(0.f);
+        if (!(wo.z * wi.z > 0)) return S3(0.f);
+        return R * InvPi;
+    }
+    float bsdfPDF(V3 woR, V3 wiR) const {
+        V3 wo = frame.ToLocal(woR), wi = frame.ToLocal(wiR);
+        if (wo.z == 0) return 0;
+        if (!(wo.z * wi.z > 0)) return 0;
+        return CosineHemispherePDF(std::abs(wi.z));
+    }
+    struct Sample { bool valid = false; S3 f; V3 wi; float pdf = 0, bsdfPdf = 0, misPdf = 0; };
+    Sample bsdfSample(V3 woR, const float *u2) const {  // bsdf.h:58-80 + bxdfs.h:46-59
+        Sample s;
+        V3 wo = frame.ToLocal(woR);
+        if (wo.z == 0 || !hasR) return s;
+        V3 wi = SampleCosineHemisphere(u2);
+        if (wo.z < 0) wi.z *= -1;
+        float pdf = CosineHemispherePDF(std::abs(wi.z));
+        S3 fv = R * InvPi;
+        if (!fv || pdf == 0 || wi.z == 0) return s;
+        s.valid = true; s.f = fv; s.wi = frame.FromLocal(wi); s.pdf = s.bsdfPdf = s.misPdf = pdf;
+        return s;
+    }
+    // guiding.h:83-109
+    bool init(V3 p, V3 rayD, V3 ns, float &rand) {
+        bool success = false;
+        if (IsNonSpecular() && sc->g && sc->g->surface) {
+            int leaf;
+            int r = field_get_region(sc->g->surface, p, &rand, &leaf);
+            if (leaf >= 0) lookups++;
+            if (r >= 0 && sc->g->surface->regions[r].valid) {
+                dist.init(&sc->g->surface->regions[r], p);
+                dist.region = r;
+                V3 n = ns;
+                if (Dot(-rayD, ns) < 0.f) n = -n;
+                dist.applyCosineProduct(n);
+                success = true;
+            }
+        }
+        useGuiding = enableGuiding ? success : false;
+        useScatterGuiding = enableScatterGuiding ? success : false;
+        return success;
+    }
+    float PDF(V3 wo, V3 wi) const {  // guiding.h:271-289
+        float b = bsdfPDF(wo, wi);
+        if (useGuiding) {
+            float gp = dist.pdf(wi);
+            if (!ris) return ((1.0f - guidingProbability) * b) + (guidingProbability * gp);
+            return (0.5f * b) + (0.5f * gp);
+        }
+        return b;
+    }
+    float VolumeScatterProbability(V3 wi) const { return useScatterGuiding ? dist.vsp(wi) : -1.f; }  // :295-305
+    Sample Sample_f(V3 wo, float u, const float *u2) {  // :120-269
+        if (!ris) {
+            Sample bs; bool sampleBSDF = true;
+            if (useGuiding) {
+                if (guidingProbability > u) { u /= guidingProbability; sampleBSDF = false; }
+                else { u -= guidingProbability; u /= (1.0f - guidingProbability); sampleBSDF = true; }
+            }
+            if (sampleBSDF) {
+                bs = bsdfSample(wo, u2);
+                if (bs.valid && useGuiding) {
+                    float gp = dist.pdf(bs.wi);
+                    bs.bsdfPdf = bs.pdf;
+                    bs.pdf = ((1.0f - guidingProbability) * bs.pdf) + (guidingProbability * gp);
+                    bs.misPdf = bs.pdf;
+                }
+            } else {
+                V3 wi; float gp = dist.samplePdf(u2[0], u2[1], &wi);
+                S3 fv = f(wo, wi); float bp = bsdfPDF(wo, wi);
+                if (bp > 0.f) {
+                    float pdf = ((1.0f - guidingProbability) * bp) + (guidingProbability * gp);
+                    bs.valid = true; bs.f = fv; bs.wi = wi; bs.pdf = pdf; bs.bsdfPdf = bp; bs.misPdf = pdf;
+                }
+            }
+            return bs;
+        }
+        if (!useGuiding) return bsdfSample(wo, u2);
+        const float uniformIncomingRadiancePDF = ((1.0f / (4.0f * M_PI)));
+        struct R_ { float bsdfPDF = 0, guidingPDF = 0, misPDF = 0, liPDF = 0; S3 f; V3 wi; float w = 0; } rs[2];
+        Sample bs0 = bsdfSample(wo, u2);
+        if (bs0.valid) {
+            rs[0].f = bs0.f; rs[0].bsdfPDF = bs0.pdf; rs[0].wi = bs0.wi;
+            rs[0].guidingPDF = dist.pdf(bs0.wi); rs[0].liPDF = dist.pdfLi(bs0.wi);
+            rs[0].misPDF = 0.5f * (rs[0].bsdfPDF + rs[0].guidingPDF);
+        }
+        float s2[2]; sampler->Get2D(s2);
+        V3 wi1; rs[1].guidingPDF = dist.samplePdf(s2[0], s2[1], &wi1);
+        rs[1].liPDF = dist.pdfLi(wi1);
+        rs[1].f = f(wo, wi1); rs[1].bsdfPDF = bsdfPDF(wo, wi1); rs[1].wi = wi1;
+        rs[1].misPDF = 0.5f * (rs[1].bsdfPDF + rs[1].guidingPDF);
+        float sumW = 0.f; int nS = 0;
+        for (int i = 0; i < 2; i++)
+            if (rs[i].bsdfPDF > 0.f) {
+                rs[i].w = (rs[i].bsdfPDF * ((1.0f - guidingProbability) * uniformIncomingRadiancePDF + guidingProbability * rs[i].liPDF));
+                rs[i].w /= rs[i].misPDF;
+                sumW += rs[i].w; nS++;
+            }
+        Sample bs;
+        if (nS == 0 || sumW <= 0.f) return bs;
+        int idx = 0;
+        float s1 = sumW * sampler->Get1D();
+        float sumRis = 0.f;
+        for (int i = 0; i < 2; i++) { sumRis += rs[i].w; if (s1 <= sumRis) { idx = i; break; } }
+        float pdf = (rs[idx].w * rs[idx].misPDF) * (float(2) / sumW);
+        bs.valid = true; bs.f = rs[idx].f; bs.wi = rs[idx].wi; bs.pdf = pdf; bs.bsdfPdf = rs[idx].bsdfPDF; bs.misPdf = rs[idx].misPDF;
+        return bs;
+    }
+};
+
+// cpu/guiding.h:360-638 GuidedPhaseFunction over HGPhaseFunction (media.h:44-74)
+struct GuidedPhase {
+    const Scene *sc; Sampler *sampler;
+    bool enableGuiding, enableScatterGuiding, ris;
+    float guidingProbability = 0.5f;
+    bool useGuiding = false, useScatterGuiding = false;
+    SamplingDistribution dist;
+    float g = 0;
+    int lookups = 0;
+    float p(V3 wo, V3 wi) const { return HenyeyGreenstein(Dot(wo, wi), g); }
+    struct Sample { bool valid = false; float p = 0; V3 wi; float pdf = 0, phasePdf = 0, misPdf = 0; };
+    Sample phaseSample(V3 wo, const float *u) const {
+        Sample s; float pdf;
+        s.wi = SampleHenyeyGreenstein(wo, g, u, &pdf);
+        s.valid = true; s.p = pdf; s.pdf = s.phasePdf = s.misPdf = pdf;
+        return s;
+    }
+    bool init(float g_, V3 pos, V3 wo, float &rand) {  // :383-398 (wo argument = ray.d, vspg.cpp:810)
+        g = g_;
+        bool success = false;
+        if (sc->g && sc->g->volume) {
+            int leaf;
+            int r = field_get_region(sc->g->volume, pos, &rand, &leaf);
+            if (leaf >= 0) lookups++;
+            if (r >= 0 && sc->g->volume->regions[r].valid) {
+                dist.init(&sc->g->volume->regions[r], pos);
+                dist.region = r;
+                dist.applyHGProduct(wo, g);
+                success = true;
+            }
+        }
+        useGuiding = enableGuiding ? success : false;
+        useScatterGuiding = enableScatterGuiding ? success : false;
+        return success;
+    }
+    float PDF(V3 wo, V3 wi) const {
+        float ph = p(wo, wi);
+        if (useGuiding) {
+            float gp = dist.pdf(wi);
+            if (!ris) return ((1.0f - guidingProbability) * ph) + (guidingProbability * gp);
+            return (0.5f * ph) + (0.5f * gp);
+        }
+        return ph;
+    }
+    float VolumeScatterProbability(V3 wi) const { return useScatterGuiding ? dist.vsp(wi) : -1.f; }
+    Sample Sample_p(V3 wo, const float *uin) {
+        float u[2] = {uin[0], uin[1]};
+        if (!ris) {
+            Sample ps; bool samplePhase = true;
+            if (useGuiding) {
+                if (guidingProbability > u[0]) { u[0] /= guidingProbability; samplePhase = false; }
+                else { u[0] -= guidingProbability; u[0] /= (1.0f - guidingProbability); samplePhase = true; }
+            }
+            if (samplePhase) {
+                ps = phaseSample(wo, u);
+                if (ps.valid && useGuiding) {
+                    float gp = dist.pdf(ps.wi);
+                    ps.phasePdf = ps.pdf;
+                    ps.pdf = ((1.0f - guidingProbability) * ps.pdf) + (guidingProbability * gp);
+                    ps.misPdf = ps.pdf;
+                }
+            } else {
+                V3 wi; float gp = dist.samplePdf(u[0], u[1], &wi);
+                float pv = p(wo, wi); float ph = pv;
+                if (ph > 0.f) {
+                    float pdf = ((1.0f - guidingProbability) * ph) + (guidingProbability * gp);
+                    ps.valid = true; ps.p = pv; ps.wi = wi; ps.pdf = pdf; ps.phasePdf = ph; ps.misPdf = pdf;
+                }
+            }
+            return ps;
+        }
+        if (!useGuiding) return phaseSample(wo, u);
+        const float uniformIncomingRadiancePDF = ((1.0f / (4.0f * M_PI)));
+        struct R_ { float phasePDF = 0, guidingPDF = 0, misPDF = 0, liPDF = 0, p = 0; V3 wi; float w = 0; } rs[2];
+        Sample ps0 = phaseSample(wo, u);
+        rs[0].p = ps0.p; rs[0].phasePDF = ps0.pdf; rs[0].wi = ps0.wi;
+        rs[0].guidingPDF = dist.pdf(ps0.wi); rs[0].liPDF = dist.pdfLi(ps0.wi);
+        rs[0].misPDF = 0.5f * (rs[0].phasePDF + rs[0].guidingPDF);
+        float s2[2]; sampler->Get2D(s2);
+        V3 wi1; rs[1].guidingPDF = dist.samplePdf(s2[0], s2[1], &wi1);
+        rs[1].liPDF = dist.pdfLi(wi1);
+        rs[1].p = p(wo, wi1); rs[1].phasePDF = rs[1].p; rs[1].wi = wi1;
+        rs[1].misPDF = 0.5f * (rs[1].phasePDF + rs[1].guidingPDF);
+        float sumW = 0.f; int nS = 0;
+        for (int i = 0; i < 2; i++)
+            if (rs[i].phasePDF > 0.f) {
+                rs[i].w = (rs[i].phasePDF * ((1.0f - guidingProbability) * uniformIncomingRadiancePDF + guidingProbability * rs[i].liPDF));
+                rs[i].w /= rs[i].misPDF;
+                sumW += rs[i].w; nS++;
+            }
+        Sample ps;
+        if (nS == 0 || sumW <= 0.f) return ps;
+        int idx = 0;
+        float s1 = sumW * sampler->Get1D();
+        float sumRis = 0.f;
+        for (int i = 0; i < 2; i++) { sumRis += rs[i].w; if (s1 <= sumRis) { idx = i; break; } }
+        float pdf = (rs[idx].w * rs[idx].misPDF) * (float(2) / sumW);
+        ps.valid = true; ps.p = rs[idx].p; ps.wi = rs[idx].wi; ps.pdf = pdf; ps.phasePdf = rs[idx].phasePDF; ps.misPdf = rs[idx].misPDF;
+        return ps;
+    }
+};
+
+struct Counters { long paths = 0, queries = 0, dda = 0, lookups = 0, shadow = 0; };
+
+struct Integrator {
+    const Scene *sc;
+    Counters cnt;
+
+    // ---------------------------------------------------------------- light sampling
+    int SampleLight(float u, float *pmf) const {  // lightsamplers.h:33-38 (uniform) / power pmf via CDF walk
+        int n = sc->d->n_lights;
+        if (n == 0) return -1;
+        if (sc->ip.light_sampler == VSPG_LIGHTSAMPLER_UNIFORM) {
+            int li = std::min<int>((int)(u * n), n - 1);
+            *pmf = 1.f / n;
+            return li;
+        }
+        float c = 0;
+        for (int i = 0; i < n; i++) { c += sc->lightCdf[i]; if (u < c || i == n - 1) { *pmf = sc->lightCdf[i]; return i; } }
+        return -1;
+    }
+    float LightPMF(int light) const {
+        int n = sc->d->n_lights;
+        if (n == 0) return 0;
+        if (sc->ip.light_sampler == VSPG_LIGHTSAMPLER_UNIFORM) return 1.f / n;
+        return sc->lightCdf[light];
+    }
+    struct LiSample { bool valid = false; S3 L; V3 wi; float pdf = 0; V3 pLight, pLightErr, nLight; bool delta = false; };
+    // shapes.cpp:1155-1214 Sample(u) (area sampling) + :1254-1280 conversion to solid angle; lights.cpp:796-818
+    LiSample SampleLi(int light, const LightSampleCtx &ctx, const float *u) const {
+        LiSample ls;
+        const vspg_light &l = sc->d->lights[light];
+        if (l.type == VSPG_LIGHT_POINT) {  // lights.h:243-250
+            V3 p(l.pos);
+            ls.wi = Normalize(p - ctx.p);
+            ls.L = S3(l.L) / DistanceSquared(p, ctx.p);
+            ls.pdf = 1; ls.pLight = p; ls.delta = true; ls.valid = true;
+            return ls;
+        }
+        if (l.type == VSPG_LIGHT_DISTANT) {  // lights.h:316-323
+            V3 wi = Normalize(V3(l.pos));
+            ls.wi = wi; ls.L = S3(l.L); ls.pdf = 1; ls.delta = true; ls.valid = true;
+            ls.pLight = ctx.p + wi * (2 * sc->sceneRadius);
+            return ls;
+        }
+        if (l.type == VSPG_LIGHT_UNIFORM_INFINITE) return ls;  // allowIncompletePDF = true (lights.cpp:1022-1023)
+        const vspg_quad &q = sc->d->quads[l.shape_index];
+        V3 p00(q.p00), p10(q.p10), p01(q.p01), p11(q.p11);
+        float pdf = 1; float uv[2];
+        if (!Scene::IsRectangle(p00, p10, p01, p11)) {
+            float w[4] = {Length(Cross(p10 - p00, p01 - p00)), Length(Cross(p10 - p00, p11 - p10)),
+                          Length(Cross(p01 - p00, p11 - p01)), Length(Cross(p11 - p10, p11 - p01))};
+            SampleBilinear(u, w, uv);
+            pdf = BilinearPDF(uv, w);
+        } else { uv[0] = u[0]; uv[1] = u[1]; }
+        V3 pu0 = LerpV(uv[1], p00, p01), pu1 = LerpV(uv[1], p10, p11);
+        V3 p = LerpV(uv[0], pu0, pu1);
+        V3 dpdu = pu1 - pu0;
+        V3 dpdv = LerpV(uv[0], p01, p11) - LerpV(uv[0], p00, p10);
+        if (LengthSquared(dpdu) == 0 || LengthSquared(dpdv) == 0) return ls;
+        V3 n = Normalize(Cross(dpdu, dpdv));
+        if (q.flip_normal) n = -n;
+        V3 pError = gamma_(6) * (Abs(p00) + Abs(p01) + Abs(p10) + Abs(p11));
+        float pdfA = pdf / Length(Cross(dpdu, dpdv));
+        V3 wi = p - ctx.p;
+        if (LengthSquared(wi) == 0) return ls;
+        wi = Normalize(wi);
+        float pdfW = pdfA / (AbsDot(n, -wi) / DistanceSquared(ctx.p, p));
+        if (std::isinf(pdfW)) return ls;
+        if (pdfW == 0) return ls;
+        S3 Le = sc->AreaL(light, n, -wi);
+        if (!Le) return ls;
+        ls.valid = true; ls.L = Le; ls.wi = wi; ls.pdf = pdfW; ls.pLight = p; ls.pLightErr = pError; ls.nLight = n;
+        return ls;
+    }
+    // lights.cpp:820-824 -> shapes.cpp:1329-1347 (area-sampling branch), evaluated at the actual hit
+    float AreaPDF_Li(int light, const LightSampleCtx &ctx, V3 wi, const SurfaceIntr &hit) const {
+        const vspg_light &l = sc->d->lights[light];
+        const vspg_quad &q = sc->d->quads[l.shape_index];
+        V3 p00(q.p00), p10(q.p10), p01(q.p01), p11(q.p11);
+        float pdf = 1;
+        if (!Scene::IsRectangle(p00, p10, p01, p11)) {
+            float w[4] = {Length(Cross(p10 - p00, p01 - p00)), Length(Cross(p10 - p00, p11 - p10)),
+                          Length(Cross(p01 - p00, p11 - p01)), Length(Cross(p11 - p10, p11 - p01))};
+            pdf = BilinearPDF(hit.uv, w);
+        }
+        V3 pu0 = LerpV(hit.uv[1], p00, p01), pu1 = LerpV(hit.uv[1], p10, p11);
+        V3 dpdu = pu1 - pu0;
+        V3 dpdv = LerpV(hit.uv[0], p01, p11) - LerpV(hit.uv[0], p00, p10);
+        float pdfA = pdf / Length(Cross(dpdu, dpdv));
+        float r = pdfA * (DistanceSquared(ctx.p, hit.p) / AbsDot(hit.n, -wi));
+        return std::isinf(r) ? 0 : r;
+    }
+
+    // ---------------------------------------------------------------- SampleLd  vspg.cpp:1136-1252
+    S3 SampleLd(bool surface, const SurfaceIntr *si, V3 pMed, V3 woMed, int medium, GuidedBSDF *gb, GuidedPhase *gp, Sampler &sampler,
+                S3 r_p, int ch) {
+        LightSampleCtx ctx;
+        V3 p, pErr, n, wo;
+        if (surface) {
+            ctx.p = si->p; ctx.pError = si->pError; ctx.n = si->n; ctx.ns = si->ns;
+            // reflective-only BSDF: ctx.pi = intr.OffsetRayOrigin(intr.wo)  (vspg.cpp:1147-1149)
+            ctx.p = OffsetRayOrigin(si->p, si->pError, si->n, si->wo); ctx.pError = V3();
+            p = si->p; pErr = si->pError; n = si->n; wo = si->wo;
+        } else {
+            ctx.p = pMed; p = pMed; wo = woMed;
+        }
+        float u = sampler.Get1D();
+        float pmf = 0;
+        int light = SampleLight(u, &pmf);
+        float uLight[2]; sampler.Get2D(uLight);
+        if (light < 0) return S3(0.f);
+        LiSample ls = SampleLi(light, ctx, uLight);
+        if (!ls.valid || !ls.L || ls.pdf == 0) return S3(0.f);
+        float p_l = pmf * ls.pdf;
+        float scatterPDF; S3 f_hat;
+        V3 wi = ls.wi;
+        if (surface) { f_hat = gb->f(wo, wi) * AbsDot(wi, si->ns); scatterPDF = 1.0f * gb->PDF(wo, wi); }
+        else { f_hat = S3(gp->p(wo, wi)); scatterPDF = 1.0f * gp->PDF(wo, wi); }
+        if (!f_hat) return S3(0.f);
+        // Ray lightRay = intr.SpawnRayTo(ls->pLight)   (interaction.h:105-109 -> ray.h:104-109, both ends offset)
+        auto spawnTo = [&](V3 pf_, V3 pfErr, V3 nf, int curMediumIfNoIface, const SurfaceIntr *from, Ray *out) {
+            V3 pf = OffsetRayOrigin(pf_, pfErr, nf, ls.pLight - pf_);
+            V3 pt = OffsetRayOrigin(ls.pLight, ls.pLightErr, ls.nLight, pf - ls.pLight);
+            out->o = pf; out->d = pt - pf;
+            out->medium = from ? from->GetMedium(out->d) : curMediumIfNoIface;
+        };
+        Ray lightRay;
+        spawnTo(p, pErr, n, medium, surface ? si : nullptr, &lightRay);
+        S3 T_ray(1.f), r_l(1.f), r_u(1.f);
+        RNG rng(HashV3(lightRay.o), HashV3(lightRay.d));
+        cnt.shadow++;
+        while (lightRay.d != V3(0, 0, 0)) {
+            Hit h = sc->Intersect(lightRay.o, lightRay.d, 1 - ShadowEpsilon);
+            if (h.valid && sc->d->quads[h.index].material >= 0) return S3(0.f);
+            if (lightRay.medium >= 0) {
+                float tMax = h.valid ? h.t : (1 - ShadowEpsilon);
+                float uu = rng.Uniform();
+                TrackStats st;
+                S3 T_maj = SampleT_maj(sc->media[lightRay.medium], lightRay, tMax, uu, rng, ch, &st,
+                                       [&](V3, const MediumProps &mp, S3 sigma_maj, S3 T_maj) {
+                                           S3 sigma_n = ClampZero(sigma_maj - mp.sigma_a - mp.sigma_s);
+                                           float pdf = T_maj[ch] * sigma_maj[ch];
+                                           T_ray *= T_maj * sigma_n / pdf;
+                                           r_l *= T_maj * sigma_maj / pdf;
+                                           r_u *= T_maj * sigma_n / pdf;
+                                           S3 Tr = T_ray / (r_l + r_u).Average();
+                                           if (Tr.MaxComponentValue() < 0.05f) {
+                                               float q = 0.75f;
+                                               if (rng.Uniform() < q) T_ray = S3(0.f);
+                                               else T_ray /= 1 - q;
+                                           }
+                                           if (!T_ray) return false;
+                                           return true;
+                                       });
+                cnt.queries += st.queries; cnt.dda += st.dda;
+                T_ray *= T_maj / T_maj[ch];
+                r_l *= T_maj / T_maj[ch];
+                r_u *= T_maj / T_maj[ch];
+            }
+            if (!T_ray) return S3(0.f);
+            if (!h.valid) break;
+            SurfaceIntr hs = sc->MakeIntr(h, lightRay.d, lightRay.medium);
+            spawnTo(hs.p, hs.pError, hs.n, lightRay.medium, &hs, &lightRay);
+        }
+        r_l *= r_p * p_l;
+        r_u *= r_p * scatterPDF;
+        if (ls.delta) return f_hat * T_ray * ls.L / r_l.Average();
+        else return f_hat * T_ray * ls.L / (r_l + r_u).Average();
+    }
+
+    struct PathState {
+        S3 L{0.f}, beta{1.f}, r_u{1.f}, r_l{1.f};
+        bool specularBounce = false, anyNonSpecularBounces = false, lastVertexVolume = false;
+        int depth = 0;
+        float etaScale = 1, rr_correction = 1;
+        LightSampleCtx prevCtx;
+        Ray ray;
+    };
+
+    // One distance-sampling decision (vspg.cpp:637-800 up to the chosen event).  Returns through `ev`.
+    struct DistanceEvent { bool scattered = false, terminated = false; V3 p; MediumProps mp; int queries = 0, dda = 0; };
+
+    // vspg.cpp:804-875 / 988-1058: the scatter-vertex part shared by both routines
+    void ScatterVertex(PathState &ps, int px, int py, V3 p, const MediumProps &mp, Sampler &sampler, GuidedPhase &gphase, int ch,
+                       bool &scattered, bool &terminated) {
+        if (ps.beta && ps.r_u) {
+            float v = sampler.Get1D();
+            int before = gphase.lookups;
+            gphase.init(mp.g, p, ps.ray.d, v);
+            cnt.lookups += gphase.lookups - before;
+            float survivalProb = 1.0f;
+            if (ps.depth > sc->ip.min_rr_depth) {
+                S3 rrw = (ps.beta / ps.r_u.Average()) * ps.rr_correction;
+                survivalProb = ps.specularBounce ? 0.95f : std::max(0.f, std::min(1.f, rrw.MaxComponentValue()));
+            }
+            if (sc->ip.use_nee) {
+                S3 Ld = SampleLd(false, nullptr, p, -ps.ray.d, ps.ray.medium, nullptr, &gphase, sampler, ps.r_u, ch);
+                ps.L += ps.beta * Ld;
+            }
+            if (survivalProb < 1 && ps.depth > sc->ip.min_rr_depth) {
+                float q = std::max<float>(0, 1 - survivalProb);
+                if (sampler.Get1D() < q) { terminated = true; return; }
+                ps.beta /= 1 - q;
+            }
+            float u[2]; sampler.Get2D(u);
+            GuidedPhase::Sample s = gphase.Sample_p(-ps.ray.d, u);
+            if (!s.valid || s.pdf == 0) { terminated = true; return; }
+            float phaseFunctionWeight = s.p / s.pdf;
+            ps.beta *= phaseFunctionWeight;
+            ps.r_l = ps.r_u / s.pdf;
+            ps.prevCtx = LightSampleCtx{p, V3(), V3(), V3()};
+            scattered = true;
+            ps.ray.o = p; ps.ray.d = s.wi;
+            ps.specularBounce = false; ps.anyNonSpecularBounces = true;
+            ps.lastVertexVolume = true;
+        }
+    }
+
+    // vspg.cpp:637-1096.  `probe`: stop right after the event decision (used by the per-kernel parity hook).
+    void SampleDistance(PathState &ps, int px, int py, float tMax, Sampler &sampler, RNG &rng, int ch, GuidedBSDF &gbsdf,
+                        GuidedPhase &gphase, bool &scattered, bool &terminated, bool probe, const float *vspOverride,
+                        DistanceEvent *ev) {
+        const vspg_integrator_params &ip = sc->ip;
+        const Medium &med = sc->media[ps.ray.medium];
+        bool guideScatterDecision = false;
+        float vsp = -1.f;
+        auto validate = [&](float v) { guideScatterDecision = !(std::isnan(v) || v < 0.f || v > 1.f); return v; };
+        if (ps.depth == 0) {
+            if (ip.vsp_guiding && ip.vsp_primary_guiding) {  // vspg.cpp:1098-1112
+                if (sc->g && sc->g->isg_vsp) vsp = sc->g->isg_vsp[(size_t)py * sc->g->isg_width + px];
+                else vsp = 0.5f;
+                validate(vsp);
+            }
+        } else if (ip.vsp_guiding && ip.vsp_secondary_guiding) {
+            if (vspOverride) vsp = *vspOverride;
+            else vsp = ps.lastVertexVolume ? gphase.VolumeScatterProbability(ps.ray.d) : gbsdf.VolumeScatterProbability(ps.ray.d);
+            validate(vsp);
+        }
+        if (guideScatterDecision) vsp = std::max(std::min(vsp, 0.999f), 0.001f);
+        TrackStats st;
+        bool use_resampling = !ip.vsp_sampling_nds && !med.IsHomogeneous();
+        if (use_resampling) {
+            float volumeRatioCompensated = 0, majorantScale = 1;
+            float weightSum = 0;
+            S3 trRatioEst(1.f), beta_rs(1.f), r_u_rs(1.f);
+            struct Cand { V3 p; MediumProps mp; float wi = 0, sigmaTTrEst = 0; S3 num{0.f}, den{0.f}; } sel;
+            S3 T_maj = SampleT_maj_Resampling(
+                med, ps.ray, tMax, sampler.Get1D(), rng, ch, guideScatterDecision, vsp, volumeRatioCompensated, majorantScale, &st,
+                [&](V3 p, const MediumProps &mp, S3 sigma_maj, S3 T_maj) {
+                    S3 sigma_t = mp.sigma_s + mp.sigma_a;
+                    S3 sigma_n = ClampZero(sigma_maj - sigma_t);
+                    float wi = (sigma_t / sigma_maj * trRatioEst)[ch];
+                    if (wi > 0) {
+                        weightSum += wi;
+                        if (sampler.Get1D() < wi / weightSum) {
+                            float pdf = T_maj[ch] * sigma_t[ch];
+                            sel.p = p; sel.mp = mp; sel.wi = wi; sel.sigmaTTrEst = wi;
+                            sel.num = beta_rs * T_maj * mp.sigma_s / pdf;
+                            sel.den = r_u_rs * T_maj * sigma_t / pdf;
+                        }
+                    }
+                    float pdf = T_maj[ch] * sigma_n[ch];
+                    beta_rs *= T_maj * sigma_n / pdf;
+                    r_u_rs *= T_maj * sigma_n / pdf;
+                    trRatioEst *= sigma_n / sigma_maj;
+                    return true;
+                });
+            beta_rs *= T_maj / T_maj[ch];
+            r_u_rs *= T_maj / T_maj[ch];
+            cnt.queries += st.queries; cnt.dda += st.dda;
+            if (ev) { ev->queries = (int)st.queries; ev->dda = (int)st.dda; }
+            float trS = trRatioEst[ch];
+            Cand surf; surf.p = ps.ray.at(tMax); surf.wi = trS; surf.sigmaTTrEst = trS; surf.num = beta_rs; surf.den = r_u_rs;
+            if (guideScatterDecision && trS < 1 && trS > 0 && weightSum > 0) {
+                float volRatio = volumeRatioCompensated * ip.vsp_mis_ratio + (1 - trS) * (1 - ip.vsp_mis_ratio);
+                float surfRatio = 1 - volRatio;
+                surf.wi = surfRatio / volRatio * weightSum;
+            }
+            weightSum += surf.wi;
+            bool selectSurface = false;
+            if (weightSum == 0) return;
+            else if (sampler.Get1D() < surf.wi / weightSum) { sel = surf; selectSurface = true; }
+            float rf = weightSum * sel.sigmaTTrEst / sel.wi;
+            if (selectSurface) {
+                ps.beta *= sel.num * rf;
+                ps.r_u *= sel.den;
+                if (ps.beta.HasNaNs() || ps.r_u.HasNaNs() || YIsInf(ps.beta) || YIsInf(ps.r_u)) { terminated = true; return; }
+            } else {
+                if (ps.depth++ >= ip.max_depth) { terminated = true; return; }
+                ps.beta *= sel.num * rf;
+                ps.r_u *= sel.den;
+                if (ps.beta.HasNaNs() || ps.r_u.HasNaNs() || YIsInf(ps.beta) || YIsInf(ps.r_u)) { terminated = true; return; }
+                if (ev) { ev->scattered = true; ev->p = sel.p; ev->mp = sel.mp; }
+                if (probe) { scattered = true; return; }
+                ScatterVertex(ps, px, py, sel.p, sel.mp, sampler, gphase, ch, scattered, terminated);
+            }
+        } else {
+            S3 beta_factor(1.f), r_u_factor(1.f);
+            bool trLoaded = sc->g && sc->g->tr_rgb;
+            S3 T_maj = SampleT_maj_OpticalDepthSpace(
+                med, ps.ray, tMax, sampler.Get1D(), rng, ch, guideScatterDecision, vsp, ip.vsp_mis_ratio, ip.vsp_sampling_nds != 0,
+                beta_factor, r_u_factor, &st, [&](V3 p, const MediumProps &mp, S3 sigma_maj, S3 T_maj, bool activateNDS) {
+                    if (!ps.beta) { terminated = true; return false; }
+                    S3 sigma_t = mp.sigma_s + mp.sigma_a;
+                    float pScatter = sigma_t[ch] / sigma_maj[ch];
+                    bool NDS_plus = false;
+                    if (ps.depth == 0 && ip.vsp_sampling_nds && ip.collision_probability_bias && trLoaded && activateNDS) {
+                        NDS_plus = true;
+                        float trEstCache = sc->g->tr_rgb[3 * ((size_t)py * sc->g->tr_width + px) + ch];
+                        float gamma = 1 + trEstCache;
+                        pScatter = std::pow(pScatter, 1 / gamma);
+                    }
+                    float pNull = std::max<float>(0, 1 - pScatter);
+                    float um = rng.Uniform();
+                    // SampleDiscrete({pScatter, pNull}, um)  util/sampling.h:79-112
+                    int mode;
+                    {
+                        float w[2] = {pScatter, pNull};
+                        float sumW = w[0] + w[1];
+                        float up = um * sumW;
+                        if (up == sumW) up = NextFloatDown(up);
+                        int offset = 0; float sum = 0;
+                        while (sum + w[offset] <= up) { sum += w[offset++]; if (offset > 1) { offset = 1; break; } }
+                        mode = offset;
+                    }
+                    if (mode == 0) {
+                        if (ps.depth++ >= ip.max_depth) { terminated = true; return false; }
+                        float pdf = T_maj[ch] * sigma_t[ch];
+                        ps.beta *= T_maj * mp.sigma_s / pdf;
+                        ps.r_u *= T_maj * sigma_t / pdf;
+                        if (NDS_plus) ps.r_u *= sigma_maj * pScatter / sigma_t;
+                        ps.beta *= beta_factor;
+                        ps.r_u *= r_u_factor;
+                        if (ev) { ev->scattered = true; ev->p = p; ev->mp = mp; }
+                        if (probe) { scattered = true; return false; }
+                        ScatterVertex(ps, px, py, p, mp, sampler, gphase, ch, scattered, terminated);
+                        return false;
+                    } else {
+                        S3 sigma_n = ClampZero(sigma_maj - mp.sigma_a - mp.sigma_s);
+                        float pdf = T_maj[ch] * sigma_n[ch];
+                        ps.beta *= T_maj * sigma_n / pdf;
+                        if (pdf == 0) ps.beta = S3(0.f);
+                        ps.r_u *= T_maj * sigma_n / pdf;
+                        if (NDS_plus) ps.r_u *= sigma_maj * (1 - pScatter) / sigma_n;
+                        ps.r_l *= T_maj * sigma_maj / pdf;
+                        return (bool)ps.beta && (bool)ps.r_u;
+                    }
+                });
+            bool multiply_T_maj = !(scattered || terminated || !ps.beta || !ps.r_u);
+            if (probe && ev && ev->scattered) multiply_T_maj = false;
+            if (multiply_T_maj) {
+                ps.beta *= T_maj / T_maj[ch];
+                ps.r_u *= T_maj / T_maj[ch];
+                ps.r_l *= T_maj / T_maj[ch];
+                ps.beta *= beta_factor;
+                ps.r_u *= r_u_factor;
+                ps.r_l *= r_u_factor;
+            }
+            cnt.queries += st.queries; cnt.dda += st.dda;
+            if (ev) { ev->queries = (int)st.queries; ev->dda = (int)st.dda; }
+        }
+    }
+
+    // vspg.cpp:262-635
+    S3 Li(int px, int py, Ray ray, Sampler &sampler, int ch) {
+        const vspg_integrator_params &ip = sc->ip;
+        GuidedBSDF gbsdf; gbsdf.sc = sc; gbsdf.sampler = &sampler; gbsdf.enableGuiding = ip.surface_guiding;
+        gbsdf.enableScatterGuiding = ip.vsp_secondary_guiding; gbsdf.ris = ip.surface_guiding_ris;
+        GuidedPhase gphase; gphase.sc = sc; gphase.sampler = &sampler; gphase.enableGuiding = ip.volume_guiding;
+        gphase.enableScatterGuiding = ip.vsp_secondary_guiding; gphase.ris = ip.volume_guiding_ris;
+        PathState ps; ps.ray = ray;
+        while (true) {
+            Hit h = sc->Intersect(ps.ray.o, ps.ray.d, Infinity);
+            float tMax = h.valid ? h.t : Infinity;
+            if (ps.ray.medium >= 0 && !std::isinf(tMax)) {
+                bool scattered = false, terminated = false;
+                uint64_t hash0 = HashFloat1(sampler.Get1D());
+                uint64_t hash1 = HashFloat1(sampler.Get1D());
+                RNG rng(hash0, hash1);
+                SampleDistance(ps, px, py, tMax, sampler, rng, ch, gbsdf, gphase, scattered, terminated, false, nullptr, nullptr);
+                if (terminated || !ps.beta || !ps.r_u) break;
+                if (scattered) continue;
+            }
+            if (!h.valid) {
+                for (int i = 0; i < sc->d->n_lights; i++) {
+                    const vspg_light &l = sc->d->lights[i];
+                    if (l.type != VSPG_LIGHT_UNIFORM_INFINITE) continue;  // infiniteLights: only LightType::Infinite
+                    S3 Le(l.L);
+                    if (ps.depth == 0 || ps.specularBounce) ps.L += ps.beta * Le / ps.r_u.Average();
+                    else {
+                        float lightPDF = LightPMF(i) * 0.f;  // PDF_Li(..., allowIncompletePDF=true) = 0 (lights.cpp:1031-1036)
+                        ps.r_l *= lightPDF;
+                        float w_b = ip.use_nee ? 1.0f / (ps.r_u + ps.r_l).Average() : 1.f;
+                        ps.L += ps.beta * w_b * Le;
+                    }
+                }
+                break;
+            }
+            SurfaceIntr isect = sc->MakeIntr(h, ps.ray.d, ps.ray.medium);
+            if (isect.areaLight >= 0) {
+                S3 Le = sc->AreaL(isect.areaLight, isect.n, -ps.ray.d);
+                if (Le) {
+                    if (ps.depth == 0 || ps.specularBounce) ps.L += ps.beta * Le / ps.r_u.Average();
+                    else {
+                        float lightPDF = LightPMF(isect.areaLight) * AreaPDF_Li(isect.areaLight, ps.prevCtx, ps.ray.d, isect);
+                        ps.r_l *= lightPDF;
+                        float w_l = ip.use_nee ? 1.0f / (ps.r_u + ps.r_l).Average() : 1.0f;
+                        ps.L += ps.beta * w_l * Le;
+                    }
+                }
+            }
+            if (isect.material < 0) {  // interface: SkipIntersection (interaction.cpp:91-97)
+                V3 d = ps.ray.d;
+                ps.ray.o = OffsetRayOrigin(isect.p, isect.pError, isect.n, d);
+                ps.ray.medium = isect.GetMedium(d);
+                continue;
+            }
+            if (ps.depth++ >= ip.max_depth) break;
+            const vspg_material &mat = sc->d->materials[isect.material];
+            gbsdf.setBSDF(isect.ns, isect.dpdu, S3(mat.reflectance));
+            float v = sampler.Get1D();
+            int before = gbsdf.lookups;
+            gbsdf.init(ps.ray.o + h.t * ps.ray.d, ps.ray.d, isect.ns, v);
+            cnt.lookups += gbsdf.lookups - before;
+            if (ip.use_nee && gbsdf.IsNonSpecular()) {
+                S3 Ld = SampleLd(true, &isect, V3(), V3(), ps.ray.medium, &gbsdf, nullptr, sampler, ps.r_u, ch);
+                ps.L += ps.beta * Ld;
+            }
+            ps.prevCtx = LightSampleCtx{isect.p, isect.pError, isect.n, isect.ns};
+            V3 wo = -ps.ray.d;
+            float u = sampler.Get1D();
+            float u2[2]; sampler.Get2D(u2);
+            GuidedBSDF::Sample bs = gbsdf.Sample_f(wo, u, u2);
+            if (!bs.valid) break;
+            ps.lastVertexVolume = false;
+            ps.rr_correction *= bs.pdf / bs.bsdfPdf;
+            S3 bsdfWeight = bs.f * AbsDot(bs.wi, isect.ns) / bs.pdf;
+            ps.beta *= bsdfWeight;
+            ps.r_l = ps.r_u / bs.misPdf;
+            ps.specularBounce = false; ps.anyNonSpecularBounces = true;
+            ps.ray.o = OffsetRayOrigin(isect.p, isect.pError, isect.n, bs.wi);
+            ps.ray.d = bs.wi;
+            ps.ray.medium = isect.GetMedium(bs.wi);
+            if (!ps.beta) break;
+            float survivalProb = 1.f;
+            if (ps.depth > ip.min_rr_depth) {
+                S3 rrw = (ps.beta / ps.r_u.Average()) * ps.rr_correction * ps.etaScale;
+                survivalProb = ps.specularBounce ? 0.95f : std::max(0.f, std::min(1.f, rrw.MaxComponentValue()));
+            }
+            if (survivalProb < 1 && ps.depth > ip.min_rr_depth) {
+                float q = std::max<float>(0, 1 - survivalProb);
+                if (sampler.Get1D() < q) break;
+                ps.beta /= 1 - q;
+            }
+        }
+        return ps.L;
+    }
+
+    // cpu/integrators.cpp:272-334 + samplers.h:797-814 + cameras.cpp:410-437
+    bool CameraRay(int px, int py, Sampler &sampler, Ray *ray, int *ch, float *filterWeight) const {
+        const vspg_camera &c = sc->d->camera;
+        float lu = sampler.Get1D();
+        *ch = std::min<int>((int)std::floor(lu * 3), 2);  // util/spectrum.h:335-339
+        float uf[2]; sampler.Get2D(uf);
+        // BoxFilter::Sample (filters.h): p = Lerp(u, -radius, radius), weight 1
+        float fx = Lerp(uf[0], -c.filter_radius[0], c.filter_radius[0]), fy = Lerp(uf[1], -c.filter_radius[1], c.filter_radius[1]);
+        *filterWeight = 1.f;
+        float pFilmX = px + fx + 0.5f, pFilmY = py + fy + 0.5f;
+        (void)sampler.Get1D();  // time
+        float ul[2]; sampler.Get2D(ul);
+        // cameraFromRaster(pFilm): util/transform.h operator()(Point3) with w divide
+        const float(*m)[4] = c.camera_from_raster.m;
+        float x = pFilmX, y = pFilmY, z = 0;
+        float xp = m[0][0] * x + m[0][1] * y + m[0][2] * z + m[0][3];
+        float yp = m[1][0] * x + m[1][1] * y + m[1][2] * z + m[1][3];
+        float zp = m[2][0] * x + m[2][1] * y + m[2][2] * z + m[2][3];
+        float wp = m[3][0] * x + m[3][1] * y + m[3][2] * z + m[3][3];
+        V3 pCamera = (wp == 1) ? V3(xp, yp, zp) : V3(xp, yp, zp) / wp;
+        V3 o(0, 0, 0), d = Normalize(pCamera);
+        if (c.lens_radius > 0) {
+            float pl[2]; SampleUniformDiskConcentric(ul, pl);
+            pl[0] *= c.lens_radius; pl[1] *= c.lens_radius;
+            float ft = c.focal_distance / d.z;
+            V3 pFocus = o + d * ft;
+            o = V3(pl[0], pl[1], 0);
+            d = Normalize(pFocus - o);
+        }
+        // CameraTransform::RenderFromCamera(ray): point and vector transforms (no error offsetting: Transform::operator()(Ray)
+        // does offset the origin by its error bound; the camera origin (0,0,0) maps with zero error for pinhole cameras)
+        const float(*r)[4] = c.render_from_camera.m;
+        V3 ro((r[0][0] * o.x + r[0][1] * o.y) + (r[0][2] * o.z + r[0][3]), (r[1][0] * o.x + r[1][1] * o.y) + (r[1][2] * o.z + r[1][3]),
+              (r[2][0] * o.x + r[2][1] * o.y) + (r[2][2] * o.z + r[2][3]));
+        V3 rd(r[0][0] * d.x + r[0][1] * d.y + r[0][2] * d.z, r[1][0] * d.x + r[1][1] * d.y + r[1][2] * d.z,
+              r[2][0] * d.x + r[2][1] * d.y + r[2][2] * d.z);
+        ray->o = ro; ray->d = rd; ray->medium = c.medium;
+        return true;
+    }
+
+    void RenderPixelSample(int px, int py, int sampleIndex, double *film) {
+        Sampler sampler;
+        sampler.StartPixelSample(px, py, sc->seed, sampleIndex);
+        Ray ray; int ch; float fw;
+        CameraRay(px, py, sampler, &ray, &ch, &fw);
+        S3 L = Li(px, py, ray, sampler, ch);
+        if (L.HasNaNs() || YIsInf(L)) L = S3(0.f);
+        cnt.paths++;
+        // film.h:251-267 RGBFilm::AddSample
+        const vspg_camera &c = sc->d->camera;
+        float rgb[3] = {c.imaging_ratio * L[0], c.imaging_ratio * L[1], c.imaging_ratio * L[2]};
+        float m = std::max({rgb[0], rgb[1], rgb[2]});
+        if (m > c.max_component_value) for (float &v : rgb) v *= c.max_component_value / m;
+        double *pix = film + 4 * ((size_t)py * c.width + px);
+        for (int k = 0; k < 3; k++) pix[k] += fw * rgb[k];
+        pix[3] += fw;
+    }
+};
+
+}  // namespace orc

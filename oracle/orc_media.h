@@ -1,0 +1,513 @@
+// TEST INFRASTRUCTURE -- NOT PRODUCT CODE.  (see orc_math.h header)
+// CPU restatement of the reference's media: majorant grid construction, DDA majorant iterator,
+// trilinear density lookup and the three SampleT_maj variants of the fork.
+// Paths are relative to /root/reference/src/pbrt/.
+#pragma once
+#include <vector>
+
+#include "../include/vspg.h"
+#include "orc_math.h"
+
+namespace orc {
+
+struct Ray {
+    V3 o, d;
+    int medium = -1;
+    V3 at(float t) const { return o + d * t; }  // ray.h operator()
+};
+
+struct Bounds3 {
+    V3 pMin, pMax;
+    V3 Offset(V3 p) const {  // util/vecmath.h Bounds3::Offset
+        V3 o = p - pMin;
+        if (pMax.x > pMin.x) o.x /= pMax.x - pMin.x;
+        if (pMax.y > pMin.y) o.y /= pMax.y - pMin.y;
+        if (pMax.z > pMin.z) o.z /= pMax.z - pMin.z;
+        return o;
+    }
+    V3 Diagonal() const { return pMax - pMin; }
+    // util/vecmath.h:1547-1571
+    bool IntersectP(V3 o, V3 d, float tMax, float *hitt0, float *hitt1) const {
+        float t0 = 0, t1 = tMax;
+        for (int i = 0; i < 3; ++i) {
+            float invRayDir = 1 / d[i];
+            float tNear = (pMin[i] - o[i]) * invRayDir;
+            float tFar = (pMax[i] - o[i]) * invRayDir;
+            if (tNear > tFar) std::swap(tNear, tFar);
+            tFar *= 1 + 2 * gamma_(3);
+            t0 = tNear > t0 ? tNear : t0;
+            t1 = tFar < t1 ? tFar : t1;
+            if (t0 > t1) return false;
+        }
+        if (hitt0) *hitt0 = t0;
+        if (hitt1) *hitt1 = t1;
+        return true;
+    }
+};
+
+// util/transform.cpp:263-303 + util/transform.h:416-429  Transform::ApplyInverse(const Ray&, Float *tMax)
+inline void ApplyInverseRay(const vspg_transform &T, V3 ro, V3 rd, float *tMax, V3 *oOut, V3 *dOut) {
+    const float(*mInv)[4] = T.mInv;
+    float x = ro.x, y = ro.y, z = ro.z;
+    float xp = (mInv[0][0] * x + mInv[0][1] * y) + (mInv[0][2] * z + mInv[0][3]);
+    float yp = (mInv[1][0] * x + mInv[1][1] * y) + (mInv[1][2] * z + mInv[1][3]);
+    float zp = (mInv[2][0] * x + mInv[2][1] * y) + (mInv[2][2] * z + mInv[2][3]);
+    float wp = (mInv[3][0] * x + mInv[3][1] * y) + (mInv[3][2] * z + mInv[3][3]);
+    V3 err;
+    err.x = gamma_(3) * (std::abs(mInv[0][0] * x) + std::abs(mInv[0][1] * y) + std::abs(mInv[0][2] * z));
+    err.y = gamma_(3) * (std::abs(mInv[1][0] * x) + std::abs(mInv[1][1] * y) + std::abs(mInv[1][2] * z));
+    err.z = gamma_(3) * (std::abs(mInv[2][0] * x) + std::abs(mInv[2][1] * y) + std::abs(mInv[2][2] * z));
+    // Point3fi(p, e) stores [SubRoundDown(p,e), AddRoundUp(p,e)]; Width()/2 of that interval (util/math.h Interval):
+    auto halfWidth = [](float v, float e) {
+        float lo, hi;
+        if (e == 0) { lo = hi = v; }
+        else { lo = NextFloatDown(v - e); hi = NextFloatUp(v + e); }
+        return (hi - lo) / 2;
+    };
+    auto mid = [](float v, float e) {
+        if (e == 0) return v;
+        float lo = NextFloatDown(v - e), hi = NextFloatUp(v + e);
+        return (lo + hi) / 2;
+    };
+    V3 o(xp, yp, zp);
+    if (wp != 1) { /* affine transforms only (wp == 1); projective medium transforms are out of scope */ }
+    // Vector: util/transform.h:401-406
+    V3 d(mInv[0][0] * rd.x + mInv[0][1] * rd.y + mInv[0][2] * rd.z, mInv[1][0] * rd.x + mInv[1][1] * rd.y + mInv[1][2] * rd.z,
+         mInv[2][0] * rd.x + mInv[2][1] * rd.y + mInv[2][2] * rd.z);
+    float lengthSquared = LengthSquared(d);
+    V3 om(mid(o.x, err.x), mid(o.y, err.y), mid(o.z, err.z));
+    if (lengthSquared > 0) {
+        V3 oError(halfWidth(o.x, err.x), halfWidth(o.y, err.y), halfWidth(o.z, err.z));
+        float dt = Dot(Abs(d), oError) / lengthSquared;
+        // o += d * dt on the interval, then Point3f(o) takes interval midpoints.  Interval + exact value keeps
+        // the same half width up to rounding; we follow the midpoint arithmetic.
+        V3 lo(NextFloatDown(o.x - err.x), NextFloatDown(o.y - err.y), NextFloatDown(o.z - err.z));
+        V3 hi(NextFloatUp(o.x + err.x), NextFloatUp(o.y + err.y), NextFloatUp(o.z + err.z));
+        if (err.x == 0) lo.x = hi.x = o.x;
+        if (err.y == 0) lo.y = hi.y = o.y;
+        if (err.z == 0) lo.z = hi.z = o.z;
+        V3 a = d * dt;
+        // Interval operator+(Interval, Interval{exact}) = {SubRoundDown? no: AddRoundDown(lo, a), AddRoundUp(hi, a)}
+        for (int i = 0; i < 3; i++) {
+            float l = lo[i] + a[i], h = hi[i] + a[i];
+            l = NextFloatDown(l); h = NextFloatUp(h);
+            om[i] = (l + h) / 2;
+        }
+        if (tMax) *tMax -= dt;
+    }
+    *oOut = om;
+    *dOut = d;
+}
+inline V3 ApplyInversePoint(const vspg_transform &T, V3 p) {  // util/transform.h Transform::ApplyInverse(Point3<T>)
+    const float(*mInv)[4] = T.mInv;
+    float x = p.x, y = p.y, z = p.z;
+    float xp = (mInv[0][0] * x + mInv[0][1] * y) + (mInv[0][2] * z + mInv[0][3]);
+    float yp = (mInv[1][0] * x + mInv[1][1] * y) + (mInv[1][2] * z + mInv[1][3]);
+    float zp = (mInv[2][0] * x + mInv[2][1] * y) + (mInv[2][2] * z + mInv[2][3]);
+    float wp = (mInv[3][0] * x + mInv[3][1] * y) + (mInv[3][2] * z + mInv[3][3]);
+    if (wp == 1) return {xp, yp, zp};
+    return V3(xp, yp, zp) / wp;
+}
+
+struct MediumProps { S3 sigma_a, sigma_s; float g; };
+struct Segment { float tMin, tMax; S3 sigma_maj; };
+
+struct Medium {
+    const vspg_medium *m = nullptr;
+    std::vector<float> ownMaj;
+    const float *maj = nullptr;
+    Bounds3 bounds;
+    bool IsHomogeneous() const { return m->type == VSPG_MEDIUM_HOMOGENEOUS; }
+
+    float gridAt(int x, int y, int z) const {  // util/containers.h:826-831 Lookup(Point3i)
+        if (x < 0 || y < 0 || z < 0 || x >= m->nx || y >= m->ny || z >= m->nz) return 0.f;
+        return m->density[(size_t)(z * m->ny + y) * m->nx + x];
+    }
+    S3 rgbAt(const float *g, int x, int y, int z) const {
+        if (x < 0 || y < 0 || z < 0 || x >= m->nx || y >= m->ny || z >= m->nz) return S3(0.f);
+        return S3(g + 3 * ((size_t)(z * m->ny + y) * m->nx + x));
+    }
+    // util/containers.h:804-818 SampledGrid<Float>::Lookup(Point3f)
+    float densityLookup(V3 p) const {
+        V3 ps(p.x * m->nx - .5f, p.y * m->ny - .5f, p.z * m->nz - .5f);
+        int ix = (int)std::floor(ps.x), iy = (int)std::floor(ps.y), iz = (int)std::floor(ps.z);
+        V3 d(ps.x - (float)ix, ps.y - (float)iy, ps.z - (float)iz);
+        float d00 = Lerp(d.x, gridAt(ix, iy, iz), gridAt(ix + 1, iy, iz));
+        float d10 = Lerp(d.x, gridAt(ix, iy + 1, iz), gridAt(ix + 1, iy + 1, iz));
+        float d01 = Lerp(d.x, gridAt(ix, iy, iz + 1), gridAt(ix + 1, iy, iz + 1));
+        float d11 = Lerp(d.x, gridAt(ix, iy + 1, iz + 1), gridAt(ix + 1, iy + 1, iz + 1));
+        return Lerp(d.z, Lerp(d.y, d00, d10), Lerp(d.y, d01, d11));
+    }
+    S3 rgbLookup(const float *g, V3 p) const {  // containers.h:785-801 with convert = Sample(lambda) = rgb
+        V3 ps(p.x * m->nx - .5f, p.y * m->ny - .5f, p.z * m->nz - .5f);
+        int ix = (int)std::floor(ps.x), iy = (int)std::floor(ps.y), iz = (int)std::floor(ps.z);
+        V3 d(ps.x - (float)ix, ps.y - (float)iy, ps.z - (float)iz);
+        auto L = [](float t, S3 a, S3 b) { return (1 - t) * a + t * b; };
+        S3 d00 = L(d.x, rgbAt(g, ix, iy, iz), rgbAt(g, ix + 1, iy, iz));
+        S3 d10 = L(d.x, rgbAt(g, ix, iy + 1, iz), rgbAt(g, ix + 1, iy + 1, iz));
+        S3 d01 = L(d.x, rgbAt(g, ix, iy, iz + 1), rgbAt(g, ix + 1, iy, iz + 1));
+        S3 d11 = L(d.x, rgbAt(g, ix, iy + 1, iz + 1), rgbAt(g, ix + 1, iy + 1, iz + 1));
+        return L(d.z, L(d.y, d00, d10), L(d.y, d01, d11));
+    }
+    // media.h:256-261, 316-348, 417-441 SamplePoint (emission branches out of scope: configs have none)
+    MediumProps SamplePoint(V3 p) const {
+        MediumProps mp; mp.g = m->g;
+        if (m->type == VSPG_MEDIUM_HOMOGENEOUS) { mp.sigma_a = S3(m->sigma_a); mp.sigma_s = S3(m->sigma_s); return mp; }
+        p = ApplyInversePoint(m->render_from_medium, p);
+        p = bounds.Offset(p);
+        if (m->type == VSPG_MEDIUM_GRID) {
+            float d = densityLookup(p);
+            mp.sigma_a = S3(m->sigma_a) * d; mp.sigma_s = S3(m->sigma_s) * d;
+        } else {
+            mp.sigma_a = m->sigma_scale * (m->sigma_a_rgb ? rgbLookup(m->sigma_a_rgb, p) : S3(1.f));
+            mp.sigma_s = m->sigma_scale * (m->sigma_s_rgb ? rgbLookup(m->sigma_s_rgb, p) : S3(1.f));
+        }
+        return mp;
+    }
+    // containers.h:838-855 SampledGrid::MaxValue(bounds, convert)
+    template <typename F>
+    float MaxValue(V3 bmin, V3 bmax, F at) const {
+        V3 ps0(bmin.x * m->nx - .5f, bmin.y * m->ny - .5f, bmin.z * m->nz - .5f);
+        V3 ps1(bmax.x * m->nx - .5f, bmax.y * m->ny - .5f, bmax.z * m->nz - .5f);
+        int lo[3] = {std::max((int)std::floor(ps0.x), 0), std::max((int)std::floor(ps0.y), 0), std::max((int)std::floor(ps0.z), 0)};
+        int hi[3] = {std::min((int)std::floor(ps1.x) + 1, m->nx - 1), std::min((int)std::floor(ps1.y) + 1, m->ny - 1),
+                     std::min((int)std::floor(ps1.z) + 1, m->nz - 1)};
+        float maxValue = at(lo[0], lo[1], lo[2]);
+        for (int z = lo[2]; z <= hi[2]; ++z)
+            for (int y = lo[1]; y <= hi[1]; ++y)
+                for (int x = lo[0]; x <= hi[0]; ++x) maxValue = std::max(maxValue, at(x, y, z));
+        return maxValue;
+    }
+    // media.cpp:256-269 (GridMedium) and media.cpp:393-408 (RGBGridMedium)
+    void BuildMajorant(float *out) const {
+        int rx = m->maj_res[0], ry = m->maj_res[1], rz = m->maj_res[2];
+        for (int z = 0; z < rz; ++z)
+            for (int y = 0; y < ry; ++y)
+                for (int x = 0; x < rx; ++x) {
+                    V3 p0(float(x) / rx, float(y) / ry, float(z) / rz);          // media.h:126-130 VoxelBounds
+                    V3 p1(float(x + 1) / rx, float(y + 1) / ry, float(z + 1) / rz);
+                    float v;
+                    if (m->type == VSPG_MEDIUM_GRID) v = MaxValue(p0, p1, [&](int a, int b, int c) { return gridAt(a, b, c); });
+                    else {
+                        float ma = m->sigma_a_rgb ? MaxValue(p0, p1, [&](int a, int b, int c) { return rgbAt(m->sigma_a_rgb, a, b, c).MaxComponentValue(); }) : 1;
+                        float ms = m->sigma_s_rgb ? MaxValue(p0, p1, [&](int a, int b, int c) { return rgbAt(m->sigma_s_rgb, a, b, c).MaxComponentValue(); }) : 1;
+                        v = m->sigma_scale * (ma + ms);
+                    }
+                    out[x + rx * (y + ry * z)] = v;
+                }
+    }
+    void init(const vspg_medium *mm, bool ownMajorant) {
+        m = mm;
+        bounds.pMin = V3(m->bounds_min); bounds.pMax = V3(m->bounds_max);
+        maj = m->majorant;
+        if (m->type != VSPG_MEDIUM_HOMOGENEOUS && (ownMajorant || !maj)) {
+            ownMaj.resize((size_t)m->maj_res[0] * m->maj_res[1] * m->maj_res[2]);
+            BuildMajorant(ownMaj.data());
+            maj = ownMaj.data();
+        }
+    }
+};
+
+// media.h:140-218 DDAMajorantIterator and media.h:76-107 HomogeneousMajorantIterator
+struct MajorantIterator {
+    bool homogeneous = false, called = false;
+    Segment hseg;
+    S3 sigma_t;
+    float tMin = Infinity, tMax = -Infinity;
+    const float *grid = nullptr;
+    int res[3] = {0, 0, 0};
+    float nextCrossingT[3], deltaT[3];
+    int step[3], voxelLimit[3], voxel[3];
+    long steps = 0;
+
+    void initDDA(V3 ro, V3 rd, float tMin_, float tMax_, const Medium &med, S3 sigma_t_) {
+        tMin = tMin_; tMax = tMax_; grid = med.maj; sigma_t = sigma_t_;
+        for (int i = 0; i < 3; i++) res[i] = med.m->maj_res[i];
+        V3 diag = med.bounds.Diagonal();
+        V3 go = med.bounds.Offset(ro);
+        V3 gd(rd.x / diag.x, rd.y / diag.y, rd.z / diag.z);
+        V3 gridIntersect = go + gd * tMin;
+        for (int axis = 0; axis < 3; ++axis) {
+            voxel[axis] = Clamp((int)(gridIntersect[axis] * res[axis]), 0, res[axis] - 1);
+            deltaT[axis] = 1 / (std::abs(gd[axis]) * res[axis]);
+            if (gd[axis] == -0.f) gd[axis] = 0.f;
+            if (gd[axis] >= 0) {
+                float nextVoxelPos = float(voxel[axis] + 1) / res[axis];
+                nextCrossingT[axis] = tMin + (nextVoxelPos - gridIntersect[axis]) / gd[axis];
+                step[axis] = 1; voxelLimit[axis] = res[axis];
+            } else {
+                float nextVoxelPos = float(voxel[axis]) / res[axis];
+                nextCrossingT[axis] = tMin + (nextVoxelPos - gridIntersect[axis]) / gd[axis];
+                step[axis] = -1; voxelLimit[axis] = -1;
+            }
+        }
+    }
+    bool Next(Segment *seg) {
+        steps++;
+        if (homogeneous) {
+            if (called) return false;
+            called = true; *seg = hseg; return true;
+        }
+        if (tMin >= tMax) return false;
+        int bits = ((nextCrossingT[0] < nextCrossingT[1]) << 2) + ((nextCrossingT[0] < nextCrossingT[2]) << 1) +
+                   ((nextCrossingT[1] < nextCrossingT[2]));
+        const int cmpToAxis[8] = {2, 1, 2, 1, 2, 2, 0, 0};
+        int stepAxis = cmpToAxis[bits];
+        float tVoxelExit = std::min(tMax, nextCrossingT[stepAxis]);
+        S3 sigma_maj = sigma_t * grid[voxel[0] + res[0] * (voxel[1] + res[1] * voxel[2])];
+        *seg = Segment{tMin, tVoxelExit, sigma_maj};
+        tMin = tVoxelExit;
+        if (nextCrossingT[stepAxis] > tMax) tMin = tMax;
+        voxel[stepAxis] += step[stepAxis];
+        if (voxel[stepAxis] == voxelLimit[stepAxis]) tMin = tMax;
+        nextCrossingT[stepAxis] += deltaT[stepAxis];
+        return true;
+    }
+};
+
+// media.h:264-269, 351-366, 444-455  Medium::SampleRay
+inline MajorantIterator SampleRay(const Medium &med, Ray ray, float raytMax) {
+    MajorantIterator it;
+    const vspg_medium *m = med.m;
+    if (m->type == VSPG_MEDIUM_HOMOGENEOUS) {
+        it.homogeneous = true;
+        it.hseg = Segment{0.f, raytMax, S3(m->sigma_a) + S3(m->sigma_s)};
+        return it;
+    }
+    V3 o, d;
+    ApplyInverseRay(m->render_from_medium, ray.o, ray.d, &raytMax, &o, &d);
+    float tMin, tMax;
+    if (!med.bounds.IntersectP(o, d, raytMax, &tMin, &tMax)) return it;  // default iterator: tMin=inf >= tMax=-inf
+    S3 sigma_t = (m->type == VSPG_MEDIUM_GRID) ? (S3(m->sigma_a) + S3(m->sigma_s)) : S3(1.f);
+    it.initDDA(o, d, tMin, tMax, med, sigma_t);
+    return it;
+}
+
+struct TrackStats { long queries = 0, dda = 0; };
+
+// media_sampleTMaj.h:49-117.  callback(p, mp, sigma_maj, T_maj) -> bool
+template <typename F>
+S3 SampleT_maj(const Medium &med, Ray ray, float tMax, float u, RNG &rng, int ch, TrackStats *st, F callback) {
+    tMax *= Length(ray.d);
+    ray.d = Normalize(ray.d);
+    MajorantIterator iter = SampleRay(med, ray, tMax);
+    S3 T_maj(1.f);
+    bool done = false;
+    Segment seg;
+    while (!done) {
+        if (!iter.Next(&seg)) { if (st) st->dda += iter.steps; return T_maj; }
+        if (seg.sigma_maj[ch] == 0) {
+            float dt = seg.tMax - seg.tMin;
+            if (std::isinf(dt)) dt = std::numeric_limits<float>::max();
+            T_maj *= FastExp(-dt * seg.sigma_maj);
+            continue;
+        }
+        float tMin = seg.tMin;
+        while (true) {
+            float t = tMin + SampleExponential(u, seg.sigma_maj[ch]);
+            u = rng.Uniform();
+            if (t < seg.tMax) {
+                T_maj *= FastExp(-(t - tMin) * seg.sigma_maj);
+                MediumProps mp = med.SamplePoint(ray.at(t));
+                if (st) st->queries++;
+                if (!callback(ray.at(t), mp, seg.sigma_maj, T_maj)) { done = true; break; }
+                T_maj = S3(1.f);
+                tMin = t;
+            } else {
+                float dt = seg.tMax - tMin;
+                if (std::isinf(dt)) dt = std::numeric_limits<float>::max();
+                T_maj *= FastExp(-dt * seg.sigma_maj);
+                break;
+            }
+        }
+    }
+    if (st) st->dda += iter.steps;
+    return S3(1.f);
+}
+
+// media_sampleTMaj.h:136-248
+template <typename F>
+S3 SampleT_maj_Resampling(const Medium &med, Ray ray, float tMax, float u, RNG &rng, int ch, bool guideScatterDecision,
+                          float volScatterProb, float &volumeRatioZeroCandidateCompensation, float &majorantScale,
+                          TrackStats *st, F callback) {
+    tMax *= Length(ray.d);
+    ray.d = Normalize(ray.d);
+    MajorantIterator iter = SampleRay(med, ray, tMax);
+    MajorantIterator pre = iter;
+    float totalLength = 0.f;
+    Segment seg;
+    while (true) {
+        if (!pre.Next(&seg)) break;
+        if (seg.sigma_maj[ch] == 0) continue;
+        totalLength += seg.sigma_maj[ch] * (seg.tMax - seg.tMin);
+    }
+    if (st) st->dda += pre.steps;
+    if (totalLength == 0.f) return S3(1.f);
+    majorantScale = 1.0f;
+    volumeRatioZeroCandidateCompensation = volScatterProb;
+    if (guideScatterDecision) {
+        float minTotalLength = -std::log(1 - volScatterProb);
+        if (minTotalLength > totalLength) {
+            majorantScale = minTotalLength / totalLength;
+            totalLength = minTotalLength;
+        }
+        float expNegTotalLength = FastExp(-totalLength);
+        volumeRatioZeroCandidateCompensation = volScatterProb / (1 - expNegTotalLength);
+    }
+    S3 T_maj(1.f);
+    bool done = false;
+    int count = 0;
+    iter.steps = 0;
+    while (!done) {
+        if (!iter.Next(&seg)) { if (st) st->dda += iter.steps; return T_maj; }
+        seg.sigma_maj *= majorantScale;
+        if (seg.sigma_maj[ch] == 0) {
+            float dt = seg.tMax - seg.tMin;
+            if (std::isinf(dt)) dt = std::numeric_limits<float>::max();
+            T_maj *= FastExp(-dt * seg.sigma_maj);
+            continue;
+        }
+        float tMin = seg.tMin;
+        while (true) {
+            count++;
+            float t = tMin + SampleExponential(u, seg.sigma_maj[ch]);
+            u = rng.Uniform();
+            if (t < seg.tMax) {
+                if (count > 10000) break;
+                T_maj *= FastExp(-(t - tMin) * seg.sigma_maj);
+                MediumProps mp = med.SamplePoint(ray.at(t));
+                if (st) st->queries++;
+                if (!callback(ray.at(t), mp, seg.sigma_maj, T_maj)) { done = true; break; }
+                T_maj = S3(1.f);
+                tMin = t;
+            } else {
+                float dt = seg.tMax - tMin;
+                if (std::isinf(dt)) dt = std::numeric_limits<float>::max();
+                T_maj *= FastExp(-dt * seg.sigma_maj);
+                break;
+            }
+        }
+    }
+    if (st) st->dda += iter.steps;
+    return S3(1.f);
+}
+
+// media_sampleTMaj.h:269-491.  callback(p, mp, sigma_maj, T_maj, activateNDS) -> bool
+template <typename F>
+S3 SampleT_maj_OpticalDepthSpace(const Medium &med, Ray ray, float tMax, float u, RNG &rng, int ch, bool guideScatterDecision,
+                                 float vsp, float vspMISRatio, bool NDS, S3 &beta_factor, S3 &r_u_factor, TrackStats *st,
+                                 F callback) {
+    auto plain = [&](const V3 &p, const MediumProps &mp, const S3 &sm, const S3 &tm) { return callback(p, mp, sm, tm, false); };
+    if (!guideScatterDecision || vspMISRatio == 0.f) return SampleT_maj(med, ray, tMax, u, rng, ch, st, plain);
+    tMax *= Length(ray.d);
+    ray.d = Normalize(ray.d);
+    MajorantIterator iter = SampleRay(med, ray, tMax);
+    MajorantIterator pre = iter;
+    float t_v = 0.f;
+    Segment seg;
+    while (true) {
+        if (!pre.Next(&seg)) break;
+        if (std::isinf(seg.tMax)) { if (st) st->dda += pre.steps; return SampleT_maj(med, ray, tMax, u, rng, ch, st, plain); }
+        if (seg.sigma_maj[ch] == 0) continue;
+        t_v += seg.sigma_maj[ch] * (seg.tMax - seg.tMin);
+    }
+    if (st) st->dda += pre.steps;
+    if (t_v == 0.f) return S3(1.f);
+    float OneMinusENegTv = 1.f - FastExp(-t_v);
+    float t_n = -1.f, t_n_current = -1.f;
+    if (NDS) {
+        if (vsp < 1 - FastExp(-t_v)) return SampleT_maj(med, ray, tMax, u, rng, ch, st, plain);  // (already-normalised ray, as in the reference)
+        else {
+            t_n = (float)(-std::log(1.0 - OneMinusENegTv / vsp));  // double arithmetic as in the reference (1.0 literal)
+            t_n_current = t_n;
+        }
+    }
+    S3 T_maj(1.f), tpScaleFactor(1.f);
+    float t_v_current = t_v;
+    float remainingDist = 0;
+    bool deltaTracking = false;
+    if (u > vspMISRatio) { deltaTracking = true; u = (u - vspMISRatio) / (1 - vspMISRatio); }
+    else u /= vspMISRatio;
+    bool done = false;
+    int count = 0;
+    bool overTheEnd = false;
+    const float ScatterEpsilon = 1e-5;
+    iter.steps = 0;
+    while (!done) {
+        if (!iter.Next(&seg)) { if (st) st->dda += iter.steps; return T_maj; }
+        if (seg.sigma_maj[ch] == 0 || overTheEnd) {
+            float dt = seg.tMax - seg.tMin;
+            if (std::isinf(dt)) dt = std::numeric_limits<float>::max();
+            T_maj *= FastExp(-dt * seg.sigma_maj);
+            continue;
+        }
+        float tMin = seg.tMin;
+        S3 normalizedMaj = seg.sigma_maj / seg.sigma_maj[ch];
+        if (remainingDist > 0) {
+            tMin += remainingDist / seg.sigma_maj[ch];
+            if (tMin > seg.tMax + ScatterEpsilon) {
+                float dist = (seg.tMax - seg.tMin) * seg.sigma_maj[ch];
+                t_v_current -= dist; t_n_current -= dist; remainingDist -= dist;
+                T_maj *= FastExp(-(seg.tMax - seg.tMin) * seg.sigma_maj);
+                continue;
+            }
+            t_v_current -= remainingDist; t_n_current -= remainingDist; remainingDist = 0;
+            T_maj *= FastExp(-(tMin - seg.tMin) * seg.sigma_maj);
+            MediumProps mp = med.SamplePoint(ray.at(tMin));
+            if (st) st->queries++;
+            r_u_factor = S3(vspMISRatio) / tpScaleFactor + S3(1 - vspMISRatio);
+            if (!callback(ray.at(tMin), mp, seg.sigma_maj, T_maj, true)) break;
+            T_maj = S3(1.f);
+        }
+        while (true) {
+            count++;
+            float dist = std::numeric_limits<float>::max();
+            S3 tpSingle;
+            if (NDS) {
+                tpSingle = S3(1.0f) - FastExp(-t_n_current * normalizedMaj);
+                if (!deltaTracking) dist = (float)(-std::log(1.0 - u * tpSingle[ch]));
+            } else {
+                tpSingle = (S3(1.0f) - FastExp(-t_v_current * normalizedMaj)) / vsp;
+                if (!deltaTracking) {
+                    if (u < vsp) dist = (float)(-std::log(1.0 - u * tpSingle[ch]));
+                }
+            }
+            if (deltaTracking) dist = (float)(-std::log(1.0 - u));
+            bool passThrough = t_v_current - dist < ScatterEpsilon || dist == 0;
+            if (NDS || !passThrough) tpScaleFactor *= tpSingle;
+            if (passThrough) {
+                if (NDS) tpScaleFactor /= 1.0f - FastExp(-t_n + t_v);
+                else tpScaleFactor *= FastExp(-t_v_current * normalizedMaj) / (1 - vsp);
+                r_u_factor = S3(vspMISRatio) / tpScaleFactor + S3(1 - vspMISRatio);
+                overTheEnd = true;
+                T_maj *= FastExp(-(seg.tMax - tMin) * seg.sigma_maj);
+                break;
+            }
+            float t = tMin + dist / seg.sigma_maj[ch];
+            u = rng.Uniform();
+            if (t <= seg.tMax + ScatterEpsilon) {
+                if (count > 10000) break;
+                t_v_current -= dist; t_n_current -= dist; remainingDist = 0;
+                T_maj *= FastExp(-(t - tMin) * seg.sigma_maj);
+                MediumProps mp = med.SamplePoint(ray.at(t));
+                if (st) st->queries++;
+                r_u_factor = S3(vspMISRatio) / tpScaleFactor + S3(1 - vspMISRatio);
+                if (!callback(ray.at(t), mp, seg.sigma_maj, T_maj, true)) { done = true; break; }
+                T_maj = S3(1.f);
+                tMin = t;
+            } else {
+                float dt = seg.tMax - tMin;
+                if (std::isinf(dt)) dt = std::numeric_limits<float>::max();
+                T_maj *= FastExp(-dt * seg.sigma_maj);
+                float distWithinThisSeg = dt * seg.sigma_maj[ch];
+                remainingDist = dist - distWithinThisSeg;
+                t_v_current -= distWithinThisSeg; t_n_current -= distWithinThisSeg;
+                break;
+            }
+        }
+    }
+    if (st) st->dda += iter.steps;
+    return S3(1.f);
+}
+
+}  // namespace orc
