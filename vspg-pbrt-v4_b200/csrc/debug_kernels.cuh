@@ -1,0 +1,122 @@
+// Layout-conversion kernel and the per-kernel parity hooks (include/vspg.h, "per-kernel parity hooks").
+#pragma once
+#include "kernels2.cuh"
+
+namespace vspg {
+
+// CELL8 layout: cell (cx,cy,cz), cx in [0,nx], holds the corners of interpolation cell ix = cx-1 .. (see dscene.cuh)
+__global__ void k_build_cells(const float *density, int nx, int ny, int nz, float4 *cells) {
+    size_t ncell = (size_t)(nx + 1) * (ny + 1) * (nz + 1);
+    for (size_t c = (size_t)blockIdx.x * blockDim.x + threadIdx.x; c < ncell; c += (size_t)gridDim.x * blockDim.x) {
+        int cx = (int)(c % (nx + 1)), cy = (int)((c / (nx + 1)) % (ny + 1)), cz = (int)(c / ((size_t)(nx + 1) * (ny + 1)));
+        int ix = cx - 1, iy = cy - 1, iz = cz - 1;
+        auto at = [&](int x, int y, int z) -> float {
+            if (x < 0 || y < 0 || z < 0 || x >= nx || y >= ny || z >= nz) return 0.f;
+            return density[(size_t)(z * ny + y) * nx + x];
+        };
+        cells[2 * c] = make_float4(at(ix, iy, iz), at(ix + 1, iy, iz), at(ix, iy + 1, iz), at(ix + 1, iy + 1, iz));
+        cells[2 * c + 1] = make_float4(at(ix, iy, iz + 1), at(ix + 1, iy, iz + 1), at(ix, iy + 1, iz + 1), at(ix + 1, iy + 1, iz + 1));
+    }
+}
+
+// DDAMajorantIterator segments for explicit rays (already normalised d, tMax given)
+__global__ void k_debug_segments(const DScene sc, int medium, int n, const float *rays7, int maxSeg, vspg_segment *out, int *outCount) {
+    for (int i = gtid(); i < n; i += gstride()) {
+        const float *r = rays7 + 7 * i;
+        Ray ray; ray.o = V3(r[0], r[1], r[2]); ray.d = V3(r[3], r[4], r[5]); ray.medium = medium;
+        MajorantIterator it = sample_ray(sc.media[medium], ray, r[6]);
+        Segment s; int c = 0;
+        while (it.next(&s)) {
+            if (c < maxSeg) {
+                vspg_segment &o = out[(size_t)i * maxSeg + c];
+                o.t_min = s.tMin; o.t_max = s.tMax; o.sigma_maj[0] = s.sigma_maj.x; o.sigma_maj[1] = s.sigma_maj.y; o.sigma_maj[2] = s.sigma_maj.z;
+            }
+            c++;
+        }
+        outCount[i] = c;
+    }
+}
+
+__global__ void k_debug_density(const DScene sc, int medium, int n, const float *pos3, float *out7) {
+    for (int i = gtid(); i < n; i += gstride()) {
+        MediumProps mp = sample_point(sc.media[medium], V3(pos3[3 * i], pos3[3 * i + 1], pos3[3 * i + 2]));
+        float *o = out7 + 7 * i;
+        o[0] = mp.sigma_a.x; o[1] = mp.sigma_a.y; o[2] = mp.sigma_a.z; o[3] = mp.sigma_s.x; o[4] = mp.sigma_s.y; o[5] = mp.sigma_s.z; o[6] = mp.g;
+    }
+}
+
+__global__ void k_debug_sample_distance(const DScene sc, int n, const vspg_sd_input *in, vspg_sd_output *out) {
+    for (int i = gtid(); i < n; i += gstride()) {
+        const vspg_sd_input &I = in[i];
+        vspg_sd_output &O = out[i];
+        PathRegs ps;
+        ps.ray.o = V3(I.o[0], I.o[1], I.o[2]); ps.ray.d = V3(I.d[0], I.d[1], I.d[2]); ps.ray.medium = I.medium;
+        ps.beta = V3(I.beta[0], I.beta[1], I.beta[2]); ps.r_u = V3(I.r_u[0], I.r_u[1], I.r_u[2]); ps.r_l = V3(I.r_l[0], I.r_l[1], I.r_l[2]);
+        ps.L = V3();
+        ps.rng.state = I.rng_state; ps.rng.inc = I.rng_inc;
+        ps.fl.depth = I.depth; ps.fl.channel = I.channel; ps.fl.specular = false; ps.fl.anyNonSpecular = false; ps.fl.lastVertexVolume = false;
+        ps.rr_correction = 1.f; ps.vsp_next = I.vsp; ps.prevP = V3();
+        ps.pixel = I.pixel_y * sc.cam.width + I.pixel_x; ps.sampleIndex = 0;
+        TrackCounters tc; tc.queries = 0; tc.dda = 0;
+        DistanceResult res; res.p = V3(); res.mp.sigma_a = V3(); res.mp.sigma_s = V3(); res.mp.g = 0;
+        sample_distance(sc, ps, I.t_max, tc, res);
+        O.scattered = res.scattered; O.terminated = res.terminated; O.depth = ps.fl.depth;
+        V3 p = res.scattered ? res.p : V3();
+        O.p[0] = p.x; O.p[1] = p.y; O.p[2] = p.z;
+        V3 sa = res.scattered ? res.mp.sigma_a : V3(), ss = res.scattered ? res.mp.sigma_s : V3();
+        O.sigma_a[0] = sa.x; O.sigma_a[1] = sa.y; O.sigma_a[2] = sa.z; O.sigma_s[0] = ss.x; O.sigma_s[1] = ss.y; O.sigma_s[2] = ss.z;
+        O.beta[0] = ps.beta.x; O.beta[1] = ps.beta.y; O.beta[2] = ps.beta.z;
+        O.r_u[0] = ps.r_u.x; O.r_u[1] = ps.r_u.y; O.r_u[2] = ps.r_u.z;
+        O.r_l[0] = ps.r_l.x; O.r_l[1] = ps.r_l.y; O.r_l[2] = ps.r_l.z;
+        O.rng_state = ps.rng.state; O.density_queries = (int)tc.queries; O.dda_steps = (int)tc.dda;
+    }
+}
+
+__global__ void k_debug_cache_lookup(const DScene sc, int isSurface, int n, const float *pos3, const float *u, int *outLeaf, int *outRegion, float *outU) {
+    for (int i = gtid(); i < n; i += gstride()) {
+        float s = u[i]; int leaf;
+        outRegion[i] = field_get_region(isSurface ? sc.surf : sc.vol, V3(pos3[3 * i], pos3[3 * i + 1], pos3[3 * i + 2]), &s, &leaf);
+        outLeaf[i] = leaf; outU[i] = s;
+    }
+}
+
+// GuidedBSDF / GuidedPhaseFunction on explicit inputs: one warp per item.
+__global__ void __launch_bounds__(kBlock) k_debug_guided_sample(const DScene sc, int isSurface, int n, const vspg_gs_input *in, vspg_gs_output *out) {
+    const vspg_integrator_params &ip = sc.ip;
+    const bool leader = (threadIdx.x & 31) == 0;
+    for (int i = gtid() >> 5; i < n; i += gstride() >> 5) {
+        const vspg_gs_input &I = in[i];
+        vspg_gs_output O; memset(&O, 0, sizeof O);
+        Rng sampler; sampler.state = I.rng_state; sampler.inc = I.rng_inc;
+        float v = I.v;
+        V3 wo(I.wo[0], I.wo[1], I.wo[2]), p(I.p[0], I.p[1], I.p[2]), wq(I.wq[0], I.wq[1], I.wq[2]);
+        unsigned lookups = 0;
+        ScatterSample s;
+        if (isSurface) {
+            GuidedBSDF<true> gb;
+            gb.enableGuiding = ip.surface_guiding; gb.enableScatterGuiding = ip.vsp_secondary_guiding; gb.ris = ip.surface_guiding_ris;
+            V3 ns(I.n[0], I.n[1], I.n[2]);
+            V3 dpdu, t2; coordinate_system(ns, &dpdu, &t2);
+            gb.set_bsdf(ns, dpdu, V3(I.reflectance[0], I.reflectance[1], I.reflectance[2]));
+            O.ok = gb.init(sc, p, -wo, ns, v, lookups);
+            O.region = O.ok ? gb.region : -1;
+            s = gb.sample_f(wo, I.u1, I.u2[0], I.u2[1], sampler);
+            O.pdf_wq = gb.pdf(wo, wq); O.vsp_wq = gb.vsp(wq);
+            if (s.valid) { O.f[0] = s.f.x; O.f[1] = s.f.y; O.f[2] = s.f.z; }
+        } else {
+            GuidedPhase<true> gp;
+            gp.enableGuiding = ip.volume_guiding; gp.enableScatterGuiding = ip.vsp_secondary_guiding; gp.ris = ip.volume_guiding_ris;
+            O.ok = gp.init(sc, I.g, p, -wo, v, lookups);
+            O.region = O.ok ? gp.region : -1;
+            s = gp.sample_p(wo, I.u2[0], I.u2[1], sampler);
+            O.pdf_wq = gp.pdf(wo, wq); O.vsp_wq = gp.vsp(wq);
+            if (s.valid) O.f[0] = s.f.x;
+        }
+        O.valid = s.valid;
+        if (s.valid) { O.wi[0] = s.wi.x; O.wi[1] = s.wi.y; O.wi[2] = s.wi.z; O.pdf = s.pdf; O.scatter_pdf = s.scatPdf; O.mis_pdf = s.misPdf; }
+        O.rng_state = sampler.state;
+        if (leader) out[i] = O;
+    }
+}
+
+}  // namespace vspg

@@ -1,0 +1,150 @@
+// Device-resident scene, guiding inputs and wavefront state (all pointers are HBM addresses).
+#pragma once
+#include "../../include/vspg.h"
+#include "dmath.cuh"
+
+namespace vspg {
+
+// Density-grid layouts in HBM.
+//  LINEAR   : the reference's SampledGrid order (x fastest), 8 scalar gathers per trilinear query.
+//  CELL8    : one 32-byte record per interpolation cell holding its 8 corner densities
+//             {d000,d100,d010,d110,d001,d101,d011,d111}; cells cover ix in [-1,nx-1] (zero padded), so
+//             a query is exactly one aligned 32-byte sector = the algorithmic 32 B of SURVEY 8(d).
+enum { GRID_LINEAR = 0, GRID_CELL8 = 1 };
+
+struct DMedium {
+    int type;
+    float bmin[3], bmax[3];
+    float mInv[4][4];     // render_from_medium inverse (util/transform.h ApplyInverse)
+    int identity;         // mInv == I (skips nothing arithmetically; informational)
+    float sigma_a[3], sigma_s[3];
+    float sigma_scale, g;
+    int nx, ny, nz;
+    const float *density;      // LINEAR
+    const float4 *cells;       // CELL8: 2 x float4 per cell, (nx+1)*(ny+1)*(nz+1) cells
+    const float *sa_rgb, *ss_rgb;
+    int mres[3];
+    const float *majorant;
+    int layout;
+};
+
+struct DQuad {
+    float p00[3], p10[3], p01[3], p11[3];
+    int material, area_light, medium_inside, medium_outside, has_interface, flip_normal;
+    int is_rect;          // BilinearPatch::IsRectangle (shapes.h), precomputed on the host
+    float area;
+};
+
+// Threaded (stackless) BVH node: DFS order, `skip` = next node when this subtree is done/missed.
+struct DBvhNode {
+    float bmin[3]; int skip;
+    float bmax[3]; int prim_begin;   // leaf: first index into prim_ids; interior: -1
+    int prim_count; int pad[3];
+};
+
+struct DLight {
+    int type;
+    float L[3];
+    float pos[3];
+    int shape_index, two_sided, medium;
+    float pmf;            // light sampler probability (uniform / power)
+};
+
+struct DField {
+    int present, usable;
+    float bmin[3], bmax[3];
+    int n_nodes, n_regions;
+    const vspg_kdnode *nodes;
+    const vspg_mixture *regions;
+    const vspg_neighbours *neigh;
+    int stochastic_nn;
+};
+
+struct DHGRow { int K; float g; float w[4], mc[4], kappa[4], norm[4]; };
+
+struct DScene {
+    vspg_camera cam;
+    int n_media; const DMedium *media;
+    int n_quads; const DQuad *quads;
+    int n_bvh; const DBvhNode *bvh; const int *prim_ids;
+    int n_materials; const vspg_material *materials;
+    int n_lights; const DLight *lights;
+    int n_inf_lights; const int *inf_lights;
+    float scene_center[3]; float scene_radius;
+    DField surf, vol;
+    const DHGRow *hg_table;   // 128 rows
+    const float *isg_vsp; int isg_w, isg_h;
+    const float *tr_rgb; int tr_w, tr_h;
+    vspg_integrator_params ip;
+    int seed;
+};
+
+// ------------------------------------------------------------------ wavefront state (SoA, one slot per path in flight)
+struct PathSoA {
+    float4 *o_dx;        // ray.o xyz, d.x
+    float4 *d_med;       // d.y d.z, medium(int), packed flags(int)
+    float4 *beta_ru;     // beta xyz, r_u.x
+    float4 *ru_rl;       // r_u.y r_u.z r_l.x r_l.y
+    float4 *rl_L;        // r_l.z, L xyz
+    ulonglong2 *rng;     // sampler PCG32 state, inc
+    float4 *misc;        // rr_correction, vsp_next, prevCtx.p.x, prevCtx.p.y
+    float4 *misc2;       // prevCtx.p.z, pixel(int), sampleIndex(int), unused
+    float4 *hit;         // t, u, v, prim(int)  (prim < 0: no hit)
+    float4 *ev;          // medium scatter event: p xyz, g
+    // shadow-ray record emitted by the scatter kernels
+    float4 *sh_o;        // o xyz, d.x
+    float4 *sh_d;        // d.y d.z, medium(int), flags(int: bit0 delta light, bits 8.. channel)
+    float4 *sh_c;        // contribution  beta*f_hat*L  xyz, unused
+    float4 *sh_rl;       // r_p*p_l xyz, unused
+    float4 *sh_ru;       // r_p*scatterPDF xyz, unused
+    float4 *sh_pl;       // pLight xyz, nLight.x
+    float4 *sh_ple;      // pLightErr xyz, nLight.y
+    float *sh_nz;        // nLight.z
+};
+
+// packed flags in d_med.w : bits 0-7 depth, 8-9 channel, 10 specularBounce, 11 anyNonSpecular, 12 lastVertexVolume
+struct PathFlags {
+    int depth, channel; bool specular, anyNonSpecular, lastVertexVolume;
+    VD int pack() const { return (depth & 0xff) | (channel << 8) | (specular << 10) | (anyNonSpecular << 11) | (lastVertexVolume << 12); }
+    VD static PathFlags unpack(int v) {
+        PathFlags f; f.depth = v & 0xff; f.channel = (v >> 8) & 3; f.specular = (v >> 10) & 1; f.anyNonSpecular = (v >> 11) & 1;
+        f.lastVertexVolume = (v >> 12) & 1; return f;
+    }
+};
+
+struct Queue { int *items; int *count; };
+
+struct Wavefront {
+    PathSoA P;
+    int capacity;
+    Queue active, next, medium, surface, shade, volscatter, shadow, done;
+    unsigned long long *next_sample;   // regeneration cursor
+    unsigned long long total_samples;
+    int x0, y0, x1, y1, spp_begin, spp_stride, n_spp;
+    double *film;                      // H*W*4
+    unsigned long long *counters;      // vspg_counters layout (8 x u64)
+    int *cursors;                      // per-kernel dynamic work cursors
+};
+
+enum { CNT_PATHS = 0, CNT_QUERIES = 1, CNT_DDA = 2, CNT_LOOKUPS = 3, CNT_BVH = 4, CNT_SHADOW = 5 };
+
+// ------------------------------------------------------------------ warp-aggregated queue push (ballot + popc prefix)
+VD void queue_push(const Queue &q, bool pred, int value) {
+    unsigned mask = __ballot_sync(__activemask(), pred);
+    if (!pred) return;
+    int lane = threadIdx.x & 31;
+    int leader = __ffs(mask) - 1;
+    int base = 0;
+    if (lane == leader) base = atomicAdd(q.count, __popc(mask));
+    base = __shfl_sync(mask, base, leader);
+    q.items[base + __popc(mask & ((1u << lane) - 1))] = value;
+}
+
+VD void counter_add(unsigned long long *counters, int which, unsigned v) {
+    // warp-reduce (REDUX) then one atomic per warp
+    unsigned mask = __activemask();
+    unsigned s = __reduce_add_sync(mask, v);
+    if ((threadIdx.x & 31) == (__ffs(mask) - 1) && s) atomicAdd(&counters[which], (unsigned long long)s);
+}
+
+}  // namespace vspg

@@ -1,0 +1,170 @@
+// Surfaces on the device: bilinear-patch intersection with the reference's arithmetic, a stackless
+// (threaded, skip-link) BVH walk, surface interaction construction and ray spawning.
+#pragma once
+#include "dmedia.cuh"
+
+namespace vspg {
+
+struct Hit { float t, u, v; int prim; };   // prim < 0: miss
+
+struct SurfaceIntr {
+    V3 p, pError, n, ns, dpdu, wo;
+    float u, v;
+    int material, areaLight;
+    bool hasInterface;
+    int mediumInside, mediumOutside, rayMedium;
+    VD int get_medium(V3 w) const {  // interaction.h:117-121
+        if (hasInterface) return dot(w, n) > 0 ? mediumOutside : mediumInside;
+        return rayMedium;
+    }
+};
+
+// ray.h:75-92
+VD V3 offset_ray_origin(V3 p, V3 pError, V3 n, V3 w) {
+    float d = dot(vabs(n), pError);
+    V3 offset = d * n;
+    if (dot(w, n) < 0) offset = -offset;
+    V3 po = p + offset;
+    if (offset.x > 0) po.x = next_up(po.x); else if (offset.x < 0) po.x = next_down(po.x);
+    if (offset.y > 0) po.y = next_up(po.y); else if (offset.y < 0) po.y = next_down(po.y);
+    if (offset.z > 0) po.z = next_up(po.z); else if (offset.z < 0) po.z = next_down(po.z);
+    return po;
+}
+
+// util/math.h:613-636
+VD bool quadratic(float a, float b, float c, float *t0, float *t1) {
+    if (a == 0) {
+        if (b == 0) return false;
+        *t0 = *t1 = -c / b;
+        return true;
+    }
+    float discrim = diff_of_products(b, b, 4 * a, c);
+    if (discrim < 0) return false;
+    float rootDiscrim = sqrtf(discrim);
+    float q = -0.5f * (b + copysignf(rootDiscrim, b));
+    *t0 = q / a; *t1 = c / q;
+    if (*t0 > *t1) { float t = *t0; *t0 = *t1; *t1 = t; }
+    return true;
+}
+// util/math.h SquareMatrix<3> Determinant
+VD float det3(float m00, float m01, float m02, float m10, float m11, float m12, float m20, float m21, float m22) {
+    float minor12 = diff_of_products(m11, m22, m12, m21);
+    float minor02 = diff_of_products(m10, m22, m12, m20);
+    float minor01 = diff_of_products(m10, m21, m11, m20);
+    return fmaf(m02, minor01, diff_of_products(m00, minor12, m01, minor02));
+}
+// shapes.h:1279-1345 IntersectBilinearPatch.  The candidate (t,u,v) does not depend on tMax except for the final
+// accept test, so the caller does the `t < tMax` comparison (this lets the BVH order break ties by primitive id).
+VD bool intersect_bilinear_patch(V3 ro, V3 rd, V3 p00, V3 p10, V3 p01, V3 p11, float *uo, float *vo, float *to) {
+    float a = dot(cross(p10 - p00, p01 - p11), rd);
+    float c = dot(cross(p00 - ro, rd), p01 - p00);
+    float b = dot(cross(p10 - ro, rd), p11 - p10) - (a + c);
+    float u1, u2;
+    if (!quadratic(a, b, c, &u1, &u2)) return false;
+    float eps = gammaN(30) * (max_comp(vabs(ro)) + max_comp(vabs(rd)) + max_comp(vabs(p00)) + max_comp(vabs(p10)) +
+                              max_comp(vabs(p01)) + max_comp(vabs(p11)));
+    float t = inff(), u = 0, v = 0;
+    bool found = false;
+    if (0 <= u1 && u1 <= 1) {
+        V3 uo_ = lerpv(u1, p00, p10);
+        V3 ud = lerpv(u1, p01, p11) - uo_;
+        V3 deltao = uo_ - ro;
+        V3 perp = cross(rd, ud);
+        float p2 = length_sq(perp);
+        float v1 = det3(deltao.x, rd.x, perp.x, deltao.y, rd.y, perp.y, deltao.z, rd.z, perp.z);
+        float t1 = det3(deltao.x, ud.x, perp.x, deltao.y, ud.y, perp.y, deltao.z, ud.z, perp.z);
+        if (t1 > p2 * eps && 0 <= v1 && v1 <= p2) { u = u1; v = v1 / p2; t = t1 / p2; found = true; }
+    }
+    if (0 <= u2 && u2 <= 1 && u2 != u1) {
+        V3 uo_ = lerpv(u2, p00, p10);
+        V3 ud = lerpv(u2, p01, p11) - uo_;
+        V3 deltao = uo_ - ro;
+        V3 perp = cross(rd, ud);
+        float p2 = length_sq(perp);
+        float v2 = det3(deltao.x, rd.x, perp.x, deltao.y, rd.y, perp.y, deltao.z, rd.z, perp.z);
+        float t2 = det3(deltao.x, ud.x, perp.x, deltao.y, ud.y, perp.y, deltao.z, ud.z, perp.z);
+        t2 /= p2;
+        if (0 <= v2 && v2 <= p2 && t > t2 && t2 > eps) { t = t2; u = u2; v = v2 / p2; found = true; }
+    }
+    if (!found) return false;
+    *uo = u; *vo = v; *to = t;
+    return true;
+}
+
+// Closest hit: stackless walk over the DFS-ordered threaded BVH.  Box test is the conservative slab test of
+// util/vecmath.h:1574 (tFar widened by 1+2*gamma(3)) so no hit of the brute-force reference order is lost;
+// ties in t go to the lower primitive index (= first primitive in scene order, as a linear scan would keep).
+VD Hit scene_intersect(const DScene &sc, V3 ro, V3 rd, float tMax, unsigned &nodesVisited) {
+    Hit h; h.t = tMax; h.prim = -1; h.u = h.v = 0;
+    V3 inv(1 / rd.x, 1 / rd.y, 1 / rd.z);
+    int node = 0;
+    const int n = sc.n_bvh;
+    while (node < n) {
+        const float4 *np = reinterpret_cast<const float4 *>(&sc.bvh[node]);
+        float4 a = __ldg(np), b = __ldg(np + 1);
+        int4 c = __ldg(reinterpret_cast<const int4 *>(np + 2));
+        nodesVisited++;
+        float t0 = 0, t1 = h.t;
+        bool hitBox = true;
+        {
+            float tn = (a.x - ro.x) * inv.x, tf = (b.x - ro.x) * inv.x;
+            if (tn > tf) { float t = tn; tn = tf; tf = t; }
+            tf *= 1 + 2 * gammaN(3);
+            t0 = tn > t0 ? tn : t0; t1 = tf < t1 ? tf : t1;
+            if (t0 > t1) hitBox = false;
+            tn = (a.y - ro.y) * inv.y; tf = (b.y - ro.y) * inv.y;
+            if (tn > tf) { float t = tn; tn = tf; tf = t; }
+            tf *= 1 + 2 * gammaN(3);
+            t0 = tn > t0 ? tn : t0; t1 = tf < t1 ? tf : t1;
+            if (t0 > t1) hitBox = false;
+            tn = (a.z - ro.z) * inv.z; tf = (b.z - ro.z) * inv.z;
+            if (tn > tf) { float t = tn; tn = tf; tf = t; }
+            tf *= 1 + 2 * gammaN(3);
+            t0 = tn > t0 ? tn : t0; t1 = tf < t1 ? tf : t1;
+            if (t0 > t1) hitBox = false;
+        }
+        int skip = __float_as_int(a.w), primBegin = __float_as_int(b.w), primCount = c.x;
+        if (!hitBox) { node = skip; continue; }
+        if (primBegin >= 0) {
+            for (int i = 0; i < primCount; i++) {
+                int q = __ldg(&sc.prim_ids[primBegin + i]);
+                const DQuad &Q = sc.quads[q];
+                float u, v, t;
+                if (intersect_bilinear_patch(ro, rd, ld3(Q.p00), ld3(Q.p10), ld3(Q.p01), ld3(Q.p11), &u, &v, &t)) {
+                    if (t < h.t || (t == h.t && h.prim >= 0 && q < h.prim)) { h.t = t; h.u = u; h.v = v; h.prim = q; }
+                }
+            }
+            node = skip;
+        } else node = node + 1;
+    }
+    return h;
+}
+
+// shapes.h:1398-1500 BilinearPatch::InteractionFromIntersection (no mesh uv / normals) + interaction.h:218-229
+VD SurfaceIntr make_intr(const DScene &sc, const Hit &h, V3 rayD, int rayMedium) {
+    SurfaceIntr s;
+    const DQuad &q = sc.quads[h.prim];
+    V3 p00 = ld3(q.p00), p10 = ld3(q.p10), p01 = ld3(q.p01), p11 = ld3(q.p11);
+    s.p = lerpv(h.u, lerpv(h.v, p00, p01), lerpv(h.v, p10, p11));
+    V3 dpdu = lerpv(h.v, p10, p11) - lerpv(h.v, p00, p01);
+    V3 dpdv = lerpv(h.u, p01, p11) - lerpv(h.u, p00, p10);
+    V3 pAbsSum = vabs(p00) + vabs(p01) + vabs(p10) + vabs(p11);
+    s.pError = gammaN(6) * pAbsSum;
+    s.n = normalize(cross(dpdu, dpdv));
+    if (q.flip_normal) s.n = -s.n;
+    s.ns = s.n; s.dpdu = dpdu;
+    s.wo = normalize(-rayD);
+    s.u = h.u; s.v = h.v;
+    s.material = q.material; s.areaLight = q.area_light;
+    s.hasInterface = q.has_interface && (q.medium_inside != q.medium_outside);
+    s.mediumInside = q.medium_inside; s.mediumOutside = q.medium_outside; s.rayMedium = rayMedium;
+    return s;
+}
+
+// lights.h:492-515 DiffuseAreaLight::L
+VD V3 area_L(const DLight &l, V3 n, V3 w) {
+    if (!l.two_sided && dot(n, w) < 0) return V3();
+    return ld3(l.L);
+}
+
+}  // namespace vspg

@@ -1,0 +1,323 @@
+// Scatter-vertex work: light sampling (NEE set-up), GuidedPhaseFunction / GuidedBSDF (cpu/guiding.h:57-638) and the
+// shadow-ray record.  Templated on GUIDED: when a guiding field is loaded the caller runs one WARP per vertex (all
+// lanes execute this code on identical scalars, the vMF mixtures are spread over the lanes); without a field the
+// caller runs one THREAD per vertex and every mixture op is compiled out.
+#pragma once
+#include "dguiding.cuh"
+#include "dpath.cuh"
+
+namespace vspg {
+
+struct LightSampleCtx { V3 p; };
+
+struct LiSample { bool valid; V3 L, wi; float pdf; V3 pLight, pLightErr, nLight; bool delta; };
+
+// lightsamplers.h:33-38 UniformLightSampler / PowerLightSampler pmf (precomputed per light on the host)
+VD int sample_light(const DScene &sc, float u, float *pmf) {
+    int n = sc.n_lights;
+    if (n == 0) return -1;
+    if (sc.ip.light_sampler == VSPG_LIGHTSAMPLER_UNIFORM) {
+        int li = min((int)(u * n), n - 1);
+        *pmf = 1.f / n;
+        return li;
+    }
+    float c = 0;
+    for (int i = 0; i < n; i++) {
+        float p = sc.lights[i].pmf;
+        c += p;
+        if (u < c || i == n - 1) { *pmf = p; return i; }
+    }
+    return -1;
+}
+VD float light_pmf(const DScene &sc, int light) {
+    if (sc.n_lights == 0) return 0;
+    if (sc.ip.light_sampler == VSPG_LIGHTSAMPLER_UNIFORM) return 1.f / sc.n_lights;
+    return sc.lights[light].pmf;
+}
+
+// lights.cpp:796-818 DiffuseAreaLight::SampleLi -> shapes.cpp:1155-1214, 1254-1280 (area-sampling branch);
+// lights.h:243-250 (point), 316-323 (distant); uniform infinite: allowIncompletePDF (lights.cpp:1022-1023)
+VD LiSample sample_li(const DScene &sc, int light, V3 ctxP, float u0, float u1) {
+    LiSample ls; ls.valid = false; ls.delta = false; ls.pdf = 0;
+    const DLight &l = sc.lights[light];
+    if (l.type == VSPG_LIGHT_POINT) {
+        V3 p = ld3(l.pos);
+        ls.wi = normalize(p - ctxP);
+        ls.L = ld3(l.L) / dist_sq(p, ctxP);
+        ls.pdf = 1; ls.pLight = p; ls.delta = true; ls.valid = true;
+        return ls;
+    }
+    if (l.type == VSPG_LIGHT_DISTANT) {
+        V3 wi = normalize(ld3(l.pos));
+        ls.wi = wi; ls.L = ld3(l.L); ls.pdf = 1; ls.delta = true; ls.valid = true;
+        ls.pLight = ctxP + wi * (2 * sc.scene_radius);
+        return ls;
+    }
+    if (l.type == VSPG_LIGHT_UNIFORM_INFINITE) return ls;
+    const DQuad &q = sc.quads[l.shape_index];
+    V3 p00 = ld3(q.p00), p10 = ld3(q.p10), p01 = ld3(q.p01), p11 = ld3(q.p11);
+    float pdf = 1, uvx, uvy;
+    if (!q.is_rect) {
+        float w[4] = {length(cross(p10 - p00, p01 - p00)), length(cross(p10 - p00, p11 - p10)),
+                      length(cross(p01 - p00, p11 - p01)), length(cross(p11 - p10, p11 - p01))};
+        sample_bilinear(u0, u1, w, &uvx, &uvy);
+        pdf = bilinear_pdf(uvx, uvy, w);
+    } else { uvx = u0; uvy = u1; }
+    V3 pu0 = lerpv(uvy, p00, p01), pu1 = lerpv(uvy, p10, p11);
+    V3 p = lerpv(uvx, pu0, pu1);
+    V3 dpdu = pu1 - pu0;
+    V3 dpdv = lerpv(uvx, p01, p11) - lerpv(uvx, p00, p10);
+    if (length_sq(dpdu) == 0 || length_sq(dpdv) == 0) return ls;
+    V3 n = normalize(cross(dpdu, dpdv));
+    if (q.flip_normal) n = -n;
+    V3 pError = gammaN(6) * (vabs(p00) + vabs(p01) + vabs(p10) + vabs(p11));
+    float pdfA = pdf / length(cross(dpdu, dpdv));
+    V3 wi = p - ctxP;
+    if (length_sq(wi) == 0) return ls;
+    wi = normalize(wi);
+    float pdfW = pdfA / (absdot(n, -wi) / dist_sq(ctxP, p));
+    if (isinf(pdfW)) return ls;
+    if (pdfW == 0) return ls;
+    V3 Le = area_L(l, n, -wi);
+    if (!nonzero(Le)) return ls;
+    ls.valid = true; ls.L = Le; ls.wi = wi; ls.pdf = pdfW; ls.pLight = p; ls.pLightErr = pError; ls.nLight = n;
+    return ls;
+}
+// lights.cpp:820-824 -> shapes.cpp:1329-1347 (area-sampling branch) evaluated at the actual hit
+VD float area_pdf_li(const DScene &sc, int light, V3 ctxP, V3 wi, const SurfaceIntr &hit) {
+    const DQuad &q = sc.quads[sc.lights[light].shape_index];
+    V3 p00 = ld3(q.p00), p10 = ld3(q.p10), p01 = ld3(q.p01), p11 = ld3(q.p11);
+    float pdf = 1;
+    if (!q.is_rect) {
+        float w[4] = {length(cross(p10 - p00, p01 - p00)), length(cross(p10 - p00, p11 - p10)),
+                      length(cross(p01 - p00, p11 - p01)), length(cross(p11 - p10, p11 - p01))};
+        pdf = bilinear_pdf(hit.u, hit.v, w);
+    }
+    V3 pu0 = lerpv(hit.v, p00, p01), pu1 = lerpv(hit.v, p10, p11);
+    V3 dpdu = pu1 - pu0;
+    V3 dpdv = lerpv(hit.u, p01, p11) - lerpv(hit.u, p00, p10);
+    float pdfA = pdf / length(cross(dpdu, dpdv));
+    float r = pdfA * (dist_sq(ctxP, hit.p) / absdot(hit.n, -wi));
+    return isinf(r) ? 0 : r;
+}
+
+struct ScatterSample { bool valid; V3 f; V3 wi; float pdf, scatPdf, misPdf; };  // surface: f; volume: f.x = p
+
+// ------------------------------------------------------------------ GuidedPhaseFunction (cpu/guiding.h:360-638)
+template <bool GUIDED>
+struct GuidedPhase {
+    bool enableGuiding, enableScatterGuiding, ris;
+    bool useGuiding, useScatterGuiding;
+    SamplingDist dist;
+    float g;
+    int region;
+
+    VD float p(V3 wo, V3 wi) const { return henyey_greenstein(dot(wo, wi), g); }
+    VD ScatterSample phase_sample(V3 wo, float u0, float u1) const {
+        ScatterSample s; float pdf;
+        s.wi = sample_henyey_greenstein(wo, g, u0, u1, &pdf);
+        s.valid = true; s.f = V3(pdf, 0, 0); s.pdf = s.scatPdf = s.misPdf = pdf;
+        return s;
+    }
+    // :383-398; `wo` is ray.d at the call site (vspg.cpp:810)
+    VD bool init(const DScene &sc, float g_, V3 pos, V3 wo, float &rnd, unsigned &lookups) {
+        g = g_; region = -1;
+        bool success = false;
+        if (GUIDED) {
+            int leaf;
+            int r = field_get_region(sc.vol, pos, &rnd, &leaf);
+            if (leaf >= 0) lookups++;
+            if (r >= 0 && __ldg(&sc.vol.regions[r].valid)) {
+                dist.init(&sc.vol.regions[r], pos);
+                region = r;
+                dist.apply_hg_product(sc.hg_table, wo, g);
+                success = true;
+            }
+        }
+        useGuiding = enableGuiding ? success : false;
+        useScatterGuiding = enableScatterGuiding ? success : false;
+        return success;
+    }
+    VD float pdf(V3 wo, V3 wi) const {  // :542-558
+        float ph = p(wo, wi);
+        if (GUIDED && useGuiding) {
+            float gp = dist.pdf(wi);
+            return (0.5f * ph) + (0.5f * gp);  // guidingProbability = 0.5 in both the MIS and the RIS branch
+        }
+        return ph;
+    }
+    VD float vsp(V3 wi) const { if (GUIDED && useScatterGuiding) return dist.vsp(wi); return -1.f; }  // :564-574
+    // :404-530.  RIS pulls Get2D + Get1D from the path sampler (:472, 509)
+    VD ScatterSample sample_p(V3 wo, float u0, float u1, Rng &sampler) const {
+        const float gp_ = 0.5f;
+        if (!ris) {
+            ScatterSample ps; ps.valid = false; bool samplePhase = true;
+            if (GUIDED && useGuiding) {
+                if (gp_ > u0) { u0 /= gp_; samplePhase = false; }
+                else { u0 -= gp_; u0 /= (1.0f - gp_); samplePhase = true; }
+            }
+            if (samplePhase) {
+                ps = phase_sample(wo, u0, u1);
+                if (GUIDED && ps.valid && useGuiding) {
+                    float gp = dist.pdf(ps.wi);
+                    ps.scatPdf = ps.pdf;
+                    ps.pdf = ((1.0f - gp_) * ps.pdf) + (gp_ * gp);
+                    ps.misPdf = ps.pdf;
+                }
+            } else if (GUIDED) {
+                V3 wi; float gp = dist.sample_pdf(u0, u1, &wi);
+                float pv = p(wo, wi);
+                if (pv > 0.f) {
+                    float pdf = ((1.0f - gp_) * pv) + (gp_ * gp);
+                    ps.valid = true; ps.f = V3(pv, 0, 0); ps.wi = wi; ps.pdf = pdf; ps.scatPdf = pv; ps.misPdf = pdf;
+                }
+            }
+            return ps;
+        }
+        if (!(GUIDED && useGuiding)) return phase_sample(wo, u0, u1);
+        ScatterSample out; out.valid = false;
+        if (GUIDED) {
+            const float uniformLiPDF = (float)(1.0f / (4.0f * 3.14159265358979323846));
+            ScatterSample c0 = phase_sample(wo, u0, u1);
+            float p0 = c0.f.x, ph0 = c0.pdf, gd0 = dist.pdf(c0.wi), li0 = dist.pdf_li(c0.wi);
+            float mis0 = 0.5f * (ph0 + gd0);
+            float s2a = sampler.uniform(), s2b = sampler.uniform();
+            V3 wi1; float gd1 = dist.sample_pdf(s2a, s2b, &wi1);
+            float li1 = dist.pdf_li(wi1);
+            float p1 = p(wo, wi1), ph1 = p1;
+            float mis1 = 0.5f * (ph1 + gd1);
+            float w0 = 0, w1 = 0, sumW = 0; int nS = 0;
+            if (ph0 > 0.f) { w0 = (ph0 * ((1.0f - gp_) * uniformLiPDF + gp_ * li0)); w0 /= mis0; sumW += w0; nS++; }
+            if (ph1 > 0.f) { w1 = (ph1 * ((1.0f - gp_) * uniformLiPDF + gp_ * li1)); w1 /= mis1; sumW += w1; nS++; }
+            if (nS == 0 || sumW <= 0.f) return out;
+            float s1 = sumW * sampler.uniform();
+            int idx = 0; float sumRis = 0.f;
+            sumRis += w0;
+            if (!(s1 <= sumRis)) { sumRis += w1; if (s1 <= sumRis) idx = 1; }
+            float wS = idx ? w1 : w0, misS = idx ? mis1 : mis0;
+            out.valid = true; out.f = V3(idx ? p1 : p0, 0, 0); out.wi = idx ? wi1 : c0.wi;
+            out.pdf = (wS * misS) * (float(2) / sumW); out.scatPdf = idx ? ph1 : ph0; out.misPdf = misS;
+        }
+        return out;
+    }
+};
+
+// ------------------------------------------------------------------ GuidedBSDF over DiffuseBxDF (cpu/guiding.h:57-358)
+template <bool GUIDED>
+struct GuidedBSDF {
+    bool enableGuiding, enableScatterGuiding, ris;
+    bool useGuiding, useScatterGuiding;
+    SamplingDist dist;
+    Frame frame; V3 R; bool hasR;
+    int region;
+
+    VD void set_bsdf(V3 ns, V3 dpdus, V3 refl) { frame = Frame::from_xz(normalize(dpdus), ns); R = refl; hasR = nonzero(R); }
+    VD bool non_specular() const { return hasR; }
+    VD V3 f(V3 woR, V3 wiR) const {  // bsdf.h:41-47 + bxdfs.h:39-43
+        V3 wi = frame.to_local(wiR), wo = frame.to_local(woR);
+        if (wo.z == 0) return V3();
+        if (!(wo.z * wi.z > 0)) return V3();
+        return R * kInvPi;
+    }
+    VD float bsdf_pdf(V3 woR, V3 wiR) const {
+        V3 wo = frame.to_local(woR), wi = frame.to_local(wiR);
+        if (wo.z == 0) return 0;
+        if (!(wo.z * wi.z > 0)) return 0;
+        return fabsf(wi.z) * kInvPi;
+    }
+    VD ScatterSample bsdf_sample(V3 woR, float u0, float u1) const {  // bsdf.h:58-80 + bxdfs.h:46-59
+        ScatterSample s; s.valid = false;
+        V3 wo = frame.to_local(woR);
+        if (wo.z == 0 || !hasR) return s;
+        V3 wi = sample_cosine_hemisphere(u0, u1);
+        if (wo.z < 0) wi.z *= -1;
+        float pdf = fabsf(wi.z) * kInvPi;
+        V3 fv = R * kInvPi;
+        if (!nonzero(fv) || pdf == 0 || wi.z == 0) return s;
+        s.valid = true; s.f = fv; s.wi = frame.from_local(wi); s.pdf = s.scatPdf = s.misPdf = pdf;
+        return s;
+    }
+    VD bool init(const DScene &sc, V3 p, V3 rayD, V3 ns, float &rnd, unsigned &lookups) {  // :83-109
+        bool success = false; region = -1;
+        if (GUIDED && non_specular()) {
+            int leaf;
+            int r = field_get_region(sc.surf, p, &rnd, &leaf);
+            if (leaf >= 0) lookups++;
+            if (r >= 0 && __ldg(&sc.surf.regions[r].valid)) {
+                dist.init(&sc.surf.regions[r], p);
+                region = r;
+                V3 n = ns;
+                if (dot(-rayD, ns) < 0.f) n = -n;
+                dist.apply_cosine_product(n);
+                success = true;
+            }
+        }
+        useGuiding = enableGuiding ? success : false;
+        useScatterGuiding = enableScatterGuiding ? success : false;
+        return success;
+    }
+    VD float pdf(V3 wo, V3 wi) const {  // :271-289
+        float b = bsdf_pdf(wo, wi);
+        if (GUIDED && useGuiding) {
+            float gp = dist.pdf(wi);
+            return (0.5f * b) + (0.5f * gp);
+        }
+        return b;
+    }
+    VD float vsp(V3 wi) const { if (GUIDED && useScatterGuiding) return dist.vsp(wi); return -1.f; }
+    VD ScatterSample sample_f(V3 wo, float u, float u0, float u1, Rng &sampler) const {  // :120-269
+        const float gp_ = 0.5f;
+        if (!ris) {
+            ScatterSample bs; bs.valid = false; bool sampleBSDF = true;
+            if (GUIDED && useGuiding) {
+                if (gp_ > u) { u /= gp_; sampleBSDF = false; }
+                else { u -= gp_; u /= (1.0f - gp_); sampleBSDF = true; }
+            }
+            if (sampleBSDF) {
+                bs = bsdf_sample(wo, u0, u1);
+                if (GUIDED && bs.valid && useGuiding) {
+                    float gp = dist.pdf(bs.wi);
+                    bs.scatPdf = bs.pdf;
+                    bs.pdf = ((1.0f - gp_) * bs.pdf) + (gp_ * gp);
+                    bs.misPdf = bs.pdf;
+                }
+            } else if (GUIDED) {
+                V3 wi; float gp = dist.sample_pdf(u0, u1, &wi);
+                V3 fv = f(wo, wi); float bp = bsdf_pdf(wo, wi);
+                if (bp > 0.f) {
+                    float pdf = ((1.0f - gp_) * bp) + (gp_ * gp);
+                    bs.valid = true; bs.f = fv; bs.wi = wi; bs.pdf = pdf; bs.scatPdf = bp; bs.misPdf = pdf;
+                }
+            }
+            return bs;
+        }
+        if (!(GUIDED && useGuiding)) return bsdf_sample(wo, u0, u1);
+        ScatterSample out; out.valid = false;
+        if (GUIDED) {
+            const float uniformLiPDF = (float)(1.0f / (4.0f * 3.14159265358979323846));
+            ScatterSample c0 = bsdf_sample(wo, u0, u1);
+            float b0 = 0, gd0 = 0, li0 = 0, mis0 = 0;
+            if (c0.valid) { b0 = c0.pdf; gd0 = dist.pdf(c0.wi); li0 = dist.pdf_li(c0.wi); mis0 = 0.5f * (b0 + gd0); }
+            else { c0.f = V3(); c0.wi = V3(); }
+            float s2a = sampler.uniform(), s2b = sampler.uniform();
+            V3 wi1; float gd1 = dist.sample_pdf(s2a, s2b, &wi1);
+            float li1 = dist.pdf_li(wi1);
+            V3 f1 = f(wo, wi1); float b1 = bsdf_pdf(wo, wi1);
+            float mis1 = 0.5f * (b1 + gd1);
+            float w0 = 0, w1 = 0, sumW = 0; int nS = 0;
+            if (b0 > 0.f) { w0 = (b0 * ((1.0f - gp_) * uniformLiPDF + gp_ * li0)); w0 /= mis0; sumW += w0; nS++; }
+            if (b1 > 0.f) { w1 = (b1 * ((1.0f - gp_) * uniformLiPDF + gp_ * li1)); w1 /= mis1; sumW += w1; nS++; }
+            if (nS == 0 || sumW <= 0.f) return out;
+            float s1 = sumW * sampler.uniform();
+            int idx = 0; float sumRis = 0.f;
+            sumRis += w0;
+            if (!(s1 <= sumRis)) { sumRis += w1; if (s1 <= sumRis) idx = 1; }
+            float wS = idx ? w1 : w0, misS = idx ? mis1 : mis0;
+            out.valid = true; out.f = idx ? f1 : c0.f; out.wi = idx ? wi1 : c0.wi;
+            out.pdf = (wS * misS) * (float(2) / sumW); out.scatPdf = idx ? b1 : b0; out.misPdf = misS;
+        }
+        return out;
+    }
+};
+
+}  // namespace vspg

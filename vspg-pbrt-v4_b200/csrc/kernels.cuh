@@ -1,0 +1,186 @@
+// Wavefront stage kernels of the GuidedVolPathVSPGIntegrator render pass (Li, vspg.cpp:262-635, re-expressed as
+// queues of path slots).  One iteration = intersect -> medium -> volume-scatter | surface -> shade -> shadow -> finish.
+#pragma once
+#include "dsampledistance.cuh"
+#include "dvertex.cuh"
+
+namespace vspg {
+
+constexpr int kBlock = 128;
+
+VD int gtid() { return blockIdx.x * blockDim.x + threadIdx.x; }
+VD int gstride() { return gridDim.x * blockDim.x; }
+
+// ------------------------------------------------------------------ regenerate: new camera samples into free slots
+VD bool regenerate(const DScene &sc, const Wavefront &W, int slot, PathRegs &r) {
+    // warp-aggregated fetch of the next sample id
+    unsigned mask = __activemask();
+    int lane = threadIdx.x & 31, leader = __ffs(mask) - 1;
+    unsigned long long base = 0;
+    if (lane == leader) base = atomicAdd(W.next_sample, (unsigned long long)__popc(mask));
+    base = __shfl_sync(mask, base, leader);
+    unsigned long long id = base + __popc(mask & ((1u << lane) - 1));
+    if (id >= W.total_samples) return false;
+    const int w = W.x1 - W.x0, npix = w * (W.y1 - W.y0);
+    int s = (int)(id / (unsigned long long)npix), pix = (int)(id % (unsigned long long)npix);
+    int px = W.x0 + pix % w, py = W.y0 + pix / w;
+    generate_camera_path(sc, px, py, W.spp_begin + s * W.spp_stride, r);
+    path_store(W.P, slot, r);
+    return true;
+}
+
+__global__ void __launch_bounds__(kBlock) k_generate(const DScene sc, const Wavefront W, int nslots) {
+    for (int slot = gtid(); slot < nslots; slot += gstride()) {
+        PathRegs r;
+        bool ok = regenerate(sc, W, slot, r);
+        queue_push(W.active, ok, slot);
+    }
+}
+
+// ------------------------------------------------------------------ closest hit (vspg.cpp:314)
+__global__ void __launch_bounds__(kBlock) k_intersect(const DScene sc, const Wavefront W) {
+    const int n = *W.active.count;
+    unsigned nodes = 0;
+    for (int i = gtid(); i < n; i += gstride()) {
+        int slot = W.active.items[i];
+        float4 a = W.P.o_dx[slot], b = W.P.d_med[slot];
+        V3 o(a.x, a.y, a.z), d(a.w, b.x, b.y);
+        int medium = __float_as_int(b.z);
+        Hit h = scene_intersect(sc, o, d, inff(), nodes);
+        W.P.hit[slot] = make_float4(h.t, h.u, h.v, __int_as_float(h.prim));
+        bool toMedium = medium >= 0 && h.prim >= 0;  // vspg.cpp:318: rays escaping to infinity skip the medium
+        queue_push(W.medium, toMedium, slot);
+        queue_push(W.surface, !toMedium, slot);
+    }
+    counter_add(W.counters, CNT_BVH, nodes);
+}
+
+// ------------------------------------------------------------------ SampleDistance (vspg.cpp:318-351, 637-1096)
+__global__ void __launch_bounds__(kBlock) k_medium(const DScene sc, const Wavefront W) {
+    const int n = *W.medium.count;
+    TrackCounters tc; tc.queries = 0; tc.dda = 0;
+    for (int i = gtid(); i < n; i += gstride()) {
+        int slot = W.medium.items[i];
+        PathRegs ps; path_load(W.P, slot, ps);
+        float tHit = W.P.hit[slot].x;
+        DistanceResult res;
+        sample_distance(sc, ps, tHit, tc, res);
+        path_store(W.P, slot, ps);
+        bool dead = res.terminated || !nonzero(ps.beta) || !nonzero(ps.r_u);
+        bool scat = !dead && res.scattered;
+        if (scat) W.P.ev[slot] = make_float4(res.p.x, res.p.y, res.p.z, res.mp.g);
+        queue_push(W.done, dead, slot);
+        queue_push(W.volscatter, scat, slot);
+        queue_push(W.surface, !dead && !scat, slot);
+    }
+    counter_add(W.counters, CNT_QUERIES, tc.queries);
+    counter_add(W.counters, CNT_DDA, tc.dda);
+}
+
+// ------------------------------------------------------------------ shadow-ray record (SampleLd front half, vspg.cpp:1136-1192)
+struct ShadowRec { V3 o, d; int medium; V3 contrib, rl, ru; V3 pLight, pLightErr, nLight; bool delta; int channel; };
+VD void shadow_store(const PathSoA &P, int s, const ShadowRec &r) {
+    P.sh_o[s] = make_float4(r.o.x, r.o.y, r.o.z, r.d.x);
+    P.sh_d[s] = make_float4(r.d.y, r.d.z, __int_as_float(r.medium), __int_as_float((r.delta ? 1 : 0) | (r.channel << 8)));
+    P.sh_c[s] = make_float4(r.contrib.x, r.contrib.y, r.contrib.z, 0);
+    P.sh_rl[s] = make_float4(r.rl.x, r.rl.y, r.rl.z, 0);
+    P.sh_ru[s] = make_float4(r.ru.x, r.ru.y, r.ru.z, 0);
+    P.sh_pl[s] = make_float4(r.pLight.x, r.pLight.y, r.pLight.z, r.nLight.x);
+    P.sh_ple[s] = make_float4(r.pLightErr.x, r.pLightErr.y, r.pLightErr.z, r.nLight.y);
+    P.sh_nz[s] = r.nLight.z;
+}
+VD void shadow_load(const PathSoA &P, int s, ShadowRec &r) {
+    float4 a = P.sh_o[s], b = P.sh_d[s], c = P.sh_c[s], d = P.sh_rl[s], e = P.sh_ru[s], f = P.sh_pl[s], g = P.sh_ple[s];
+    r.o = V3(a.x, a.y, a.z); r.d = V3(a.w, b.x, b.y); r.medium = __float_as_int(b.z);
+    int fl = __float_as_int(b.w); r.delta = fl & 1; r.channel = (fl >> 8) & 3;
+    r.contrib = V3(c.x, c.y, c.z); r.rl = V3(d.x, d.y, d.z); r.ru = V3(e.x, e.y, e.z);
+    r.pLight = V3(f.x, f.y, f.z); r.pLightErr = V3(g.x, g.y, g.z); r.nLight = V3(f.w, g.w, P.sh_nz[s]);
+}
+// interaction.h:105-109 SpawnRayTo(pFrom, pTo): both ends offset (ray.h:104-109)
+VD void spawn_ray_to(V3 pf_, V3 pfErr, V3 nf, V3 pLight, V3 pLightErr, V3 nLight, V3 *o, V3 *d) {
+    V3 pf = offset_ray_origin(pf_, pfErr, nf, pLight - pf_);
+    V3 pt = offset_ray_origin(pLight, pLightErr, nLight, pf - pLight);
+    *o = pf; *d = pt - pf;
+}
+
+// ------------------------------------------------------------------ volume scatter vertex (vspg.cpp:804-875 / 988-1058)
+template <bool GUIDED>
+__global__ void __launch_bounds__(kBlock) k_volscatter(const DScene sc, const Wavefront W) {
+    const int n = *W.volscatter.count;
+    const int first = GUIDED ? (gtid() >> 5) : gtid(), step = GUIDED ? (gstride() >> 5) : gstride();
+    const bool leader = GUIDED ? ((threadIdx.x & 31) == 0) : true;
+    unsigned lookups = 0, shadows = 0;
+    for (int i = first; i < n; i += step) {
+        int slot = W.volscatter.items[i];
+        PathRegs ps; path_load(W.P, slot, ps);
+        float4 e = W.P.ev[slot];
+        V3 p(e.x, e.y, e.z);
+        const vspg_integrator_params &ip = sc.ip;
+        GuidedPhase<GUIDED> gphase;
+        gphase.enableGuiding = ip.volume_guiding; gphase.enableScatterGuiding = ip.vsp_secondary_guiding; gphase.ris = ip.volume_guiding_ris;
+        float v = ps.rng.uniform();
+        gphase.init(sc, e.w, p, ps.ray.d, v, lookups);
+        float survivalProb = 1.0f;
+        if (ps.fl.depth > ip.min_rr_depth) {
+            V3 rrw = (ps.beta / avg3(ps.r_u)) * ps.rr_correction;   // openpgl/cpp/RussianRoulette.h:32-35
+            survivalProb = ps.fl.specular ? 0.95f : fmaxf(0.f, fminf(1.f, max_comp(rrw)));
+        }
+        bool emitShadow = false;
+        if (ip.use_nee) {
+            V3 wo = -ps.ray.d;
+            float u = ps.rng.uniform();
+            float pmf = 0;
+            int light = sample_light(sc, u, &pmf);
+            float ul0 = ps.rng.uniform(), ul1 = ps.rng.uniform();
+            if (light >= 0) {
+                LiSample ls = sample_li(sc, light, p, ul0, ul1);
+                if (ls.valid && nonzero(ls.L) && ls.pdf != 0) {
+                    float p_l = pmf * ls.pdf;
+                    float ph = gphase.p(wo, ls.wi);
+                    float scatterPDF = 1.0f * gphase.pdf(wo, ls.wi);
+                    if (ph != 0) {
+                        ShadowRec sr;
+                        spawn_ray_to(p, V3(), V3(), ls.pLight, ls.pLightErr, ls.nLight, &sr.o, &sr.d);
+                        sr.medium = ps.ray.medium;
+                        sr.contrib = ps.beta * (splat(ph) * ls.L);
+                        sr.rl = ps.r_u * p_l; sr.ru = ps.r_u * scatterPDF;
+                        sr.pLight = ls.pLight; sr.pLightErr = ls.pLightErr; sr.nLight = ls.nLight;
+                        sr.delta = ls.delta; sr.channel = ps.fl.channel;
+                        if (leader) shadow_store(W.P, slot, sr);
+                        emitShadow = true;
+                    }
+                }
+            }
+        }
+        bool alive = true;
+        if (survivalProb < 1 && ps.fl.depth > ip.min_rr_depth) {
+            float q = fmaxf(0.f, 1 - survivalProb);
+            if (ps.rng.uniform() < q) alive = false;
+            else ps.beta = ps.beta / (1 - q);
+        }
+        if (alive) {
+            float u0 = ps.rng.uniform(), u1 = ps.rng.uniform();
+            ScatterSample s = gphase.sample_p(-ps.ray.d, u0, u1, ps.rng);
+            if (!s.valid || s.pdf == 0) alive = false;
+            else {
+                float phaseFunctionWeight = s.f.x / s.pdf;
+                ps.beta = ps.beta * phaseFunctionWeight;
+                ps.r_l = ps.r_u / s.pdf;
+                ps.prevP = p;
+                ps.ray.o = p; ps.ray.d = s.wi;
+                ps.fl.specular = false; ps.fl.anyNonSpecular = true; ps.fl.lastVertexVolume = true;
+                ps.vsp_next = gphase.vsp(s.wi);
+            }
+        }
+        if (leader) {
+            path_store(W.P, slot, ps);
+            if (emitShadow) shadows++;
+        }
+        queue_push(W.shadow, leader && emitShadow, slot);
+        queue_push(W.next, leader && alive, slot);
+        queue_push(W.done, leader && !alive, slot);
+    }
+    if (leader) { counter_add(W.counters, CNT_LOOKUPS, lookups); counter_add(W.counters, CNT_SHADOW, shadows); }
+}
+
+}  // namespace vspg

@@ -1,0 +1,233 @@
+// Wavefront stage kernels, part 2: surface hit handling, BSDF shading, shadow rays, film.
+#pragma once
+#include "kernels.cuh"
+
+namespace vspg {
+
+// ------------------------------------------------------------------ escape / emission / interface (vspg.cpp:353-446)
+__global__ void __launch_bounds__(kBlock) k_surface(const DScene sc, const Wavefront W) {
+    const int n = *W.surface.count;
+    const vspg_integrator_params &ip = sc.ip;
+    for (int i = gtid(); i < n; i += gstride()) {
+        int slot = W.surface.items[i];
+        PathRegs ps; path_load(W.P, slot, ps);
+        float4 hr = W.P.hit[slot];
+        Hit h; h.t = hr.x; h.u = hr.y; h.v = hr.z; h.prim = __float_as_int(hr.w);
+        bool toDone = false, toNext = false, toShade = false;
+        if (h.prim < 0) {
+            // infinite lights (only LightType::Infinite); PDF_Li(..., allowIncompletePDF = true) = 0 for the uniform one
+            for (int k = 0; k < sc.n_inf_lights; k++) {
+                int li = sc.inf_lights[k];
+                V3 Le = ld3(sc.lights[li].L);
+                if (ps.fl.depth == 0 || ps.fl.specular) ps.L = ps.L + ps.beta * Le / avg3(ps.r_u);
+                else {
+                    float lightPDF = light_pmf(sc, li) * 0.f;
+                    ps.r_l = ps.r_l * lightPDF;
+                    float w_b = ip.use_nee ? 1.0f / avg3(ps.r_u + ps.r_l) : 1.f;
+                    ps.L = ps.L + ps.beta * w_b * Le;
+                }
+            }
+            toDone = true;
+        } else {
+            SurfaceIntr isect = make_intr(sc, h, ps.ray.d, ps.ray.medium);
+            if (isect.areaLight >= 0) {
+                V3 Le = area_L(sc.lights[isect.areaLight], isect.n, -ps.ray.d);
+                if (nonzero(Le)) {
+                    if (ps.fl.depth == 0 || ps.fl.specular) ps.L = ps.L + ps.beta * Le / avg3(ps.r_u);
+                    else {
+                        float lightPDF = light_pmf(sc, isect.areaLight) * area_pdf_li(sc, isect.areaLight, ps.prevP, ps.ray.d, isect);
+                        ps.r_l = ps.r_l * lightPDF;
+                        float w_l = ip.use_nee ? 1.0f / avg3(ps.r_u + ps.r_l) : 1.0f;
+                        ps.L = ps.L + ps.beta * w_l * Le;
+                    }
+                }
+            }
+            if (isect.material < 0) {  // interface material: SkipIntersection (interaction.cpp:91-97)
+                V3 d = ps.ray.d;
+                ps.ray.o = offset_ray_origin(isect.p, isect.pError, isect.n, d);
+                ps.ray.medium = isect.get_medium(d);
+                toNext = true;
+            } else if (ps.fl.depth++ >= ip.max_depth) toDone = true;
+            else toShade = true;
+        }
+        path_store(W.P, slot, ps);
+        queue_push(W.done, toDone, slot);
+        queue_push(W.next, toNext, slot);
+        queue_push(W.shade, toShade, slot);
+    }
+}
+
+// ------------------------------------------------------------------ surface scatter vertex (vspg.cpp:448-607)
+template <bool GUIDED>
+__global__ void __launch_bounds__(kBlock) k_shade(const DScene sc, const Wavefront W) {
+    const int n = *W.shade.count;
+    const int first = GUIDED ? (gtid() >> 5) : gtid(), step = GUIDED ? (gstride() >> 5) : gstride();
+    const bool leader = GUIDED ? ((threadIdx.x & 31) == 0) : true;
+    const vspg_integrator_params &ip = sc.ip;
+    unsigned lookups = 0, shadows = 0;
+    for (int i = first; i < n; i += step) {
+        int slot = W.shade.items[i];
+        PathRegs ps; path_load(W.P, slot, ps);
+        float4 hr = W.P.hit[slot];
+        Hit h; h.t = hr.x; h.u = hr.y; h.v = hr.z; h.prim = __float_as_int(hr.w);
+        SurfaceIntr isect = make_intr(sc, h, ps.ray.d, ps.ray.medium);
+        GuidedBSDF<GUIDED> gbsdf;
+        gbsdf.enableGuiding = ip.surface_guiding; gbsdf.enableScatterGuiding = ip.vsp_secondary_guiding; gbsdf.ris = ip.surface_guiding_ris;
+        gbsdf.set_bsdf(isect.ns, isect.dpdu, ld3(sc.materials[isect.material].reflectance));
+        float v = ps.rng.uniform();
+        gbsdf.init(sc, ps.ray.o + h.t * ps.ray.d, ps.ray.d, isect.ns, v, lookups);
+        bool emitShadow = false;
+        if (ip.use_nee && gbsdf.non_specular()) {
+            V3 ctxP = offset_ray_origin(isect.p, isect.pError, isect.n, isect.wo);  // reflective-only BSDF (vspg.cpp:1147-1149)
+            V3 wo = isect.wo;
+            float u = ps.rng.uniform();
+            float pmf = 0;
+            int light = sample_light(sc, u, &pmf);
+            float ul0 = ps.rng.uniform(), ul1 = ps.rng.uniform();
+            if (light >= 0) {
+                LiSample ls = sample_li(sc, light, ctxP, ul0, ul1);
+                if (ls.valid && nonzero(ls.L) && ls.pdf != 0) {
+                    float p_l = pmf * ls.pdf;
+                    V3 f_hat = gbsdf.f(wo, ls.wi) * absdot(ls.wi, isect.ns);
+                    float scatterPDF = 1.0f * gbsdf.pdf(wo, ls.wi);
+                    if (nonzero(f_hat)) {
+                        ShadowRec sr;
+                        spawn_ray_to(isect.p, isect.pError, isect.n, ls.pLight, ls.pLightErr, ls.nLight, &sr.o, &sr.d);
+                        sr.medium = isect.get_medium(sr.d);
+                        sr.contrib = ps.beta * (f_hat * ls.L);
+                        sr.rl = ps.r_u * p_l; sr.ru = ps.r_u * scatterPDF;
+                        sr.pLight = ls.pLight; sr.pLightErr = ls.pLightErr; sr.nLight = ls.nLight;
+                        sr.delta = ls.delta; sr.channel = ps.fl.channel;
+                        if (leader) shadow_store(W.P, slot, sr);
+                        emitShadow = true;
+                    }
+                }
+            }
+        }
+        ps.prevP = isect.p;
+        V3 wo = -ps.ray.d;
+        float u = ps.rng.uniform();
+        float u0 = ps.rng.uniform(), u1 = ps.rng.uniform();
+        ScatterSample bs = gbsdf.sample_f(wo, u, u0, u1, ps.rng);
+        bool alive = bs.valid;
+        if (alive) {
+            ps.fl.lastVertexVolume = false;
+            ps.rr_correction *= bs.pdf / bs.scatPdf;
+            V3 bsdfWeight = bs.f * absdot(bs.wi, isect.ns) / bs.pdf;
+            ps.beta = ps.beta * bsdfWeight;
+            ps.r_l = ps.r_u / bs.misPdf;
+            ps.fl.specular = false; ps.fl.anyNonSpecular = true;
+            ps.ray.o = offset_ray_origin(isect.p, isect.pError, isect.n, bs.wi);
+            ps.ray.d = bs.wi;
+            ps.ray.medium = isect.get_medium(bs.wi);
+            ps.vsp_next = gbsdf.vsp(bs.wi);
+            if (!nonzero(ps.beta)) alive = false;
+        }
+        if (alive) {
+            float survivalProb = 1.f;
+            if (ps.fl.depth > ip.min_rr_depth) {
+                const float etaScale = 1.f;  // no transmissive BxDFs on this path
+                V3 rrw = (ps.beta / avg3(ps.r_u)) * ps.rr_correction * etaScale;
+                survivalProb = ps.fl.specular ? 0.95f : fmaxf(0.f, fminf(1.f, max_comp(rrw)));
+            }
+            if (survivalProb < 1 && ps.fl.depth > ip.min_rr_depth) {
+                float q = fmaxf(0.f, 1 - survivalProb);
+                if (ps.rng.uniform() < q) alive = false;
+                else ps.beta = ps.beta / (1 - q);
+            }
+        }
+        if (leader) {
+            path_store(W.P, slot, ps);
+            if (emitShadow) shadows++;
+        }
+        queue_push(W.shadow, leader && emitShadow, slot);
+        queue_push(W.next, leader && alive, slot);
+        queue_push(W.done, leader && !alive, slot);
+    }
+    if (leader) { counter_add(W.counters, CNT_LOOKUPS, lookups); counter_add(W.counters, CNT_SHADOW, shadows); }
+}
+
+// ------------------------------------------------------------------ shadow rays (SampleLd back half, vspg.cpp:1193-1252)
+__global__ void __launch_bounds__(kBlock) k_shadow(const DScene sc, const Wavefront W) {
+    const int n = *W.shadow.count;
+    TrackCounters tc; tc.queries = 0; tc.dda = 0;
+    unsigned nodes = 0;
+    for (int i = gtid(); i < n; i += gstride()) {
+        int slot = W.shadow.items[i];
+        ShadowRec sr; shadow_load(W.P, slot, sr);
+        const int ch = sr.channel;
+        Ray lightRay; lightRay.o = sr.o; lightRay.d = sr.d; lightRay.medium = sr.medium;
+        V3 T_ray = splat(1.f), r_l = splat(1.f), r_u = splat(1.f);
+        Rng rng; rng.set_sequence(hash_v3(lightRay.o), hash_v3(lightRay.d));
+        bool blocked = false;
+        while (!(lightRay.d == V3(0, 0, 0))) {
+            Hit h = scene_intersect(sc, lightRay.o, lightRay.d, 1 - kShadowEpsilon, nodes);
+            if (h.prim >= 0 && sc.quads[h.prim].material >= 0) { blocked = true; break; }
+            if (lightRay.medium >= 0) {
+                float tMax = h.prim >= 0 ? h.t : (1 - kShadowEpsilon);
+                float uu = rng.uniform();
+                Ray tr = lightRay;
+                tMax *= length(tr.d);
+                tr.d = normalize(tr.d);
+                V3 T_maj = track_T_maj(sc.media[lightRay.medium], tr, tMax, uu, rng, ch, tc,
+                                       [&](V3, const MediumProps &mp, V3 sigma_maj, V3 T_maj) {
+                                           V3 sigma_n = clamp_zero(sigma_maj - mp.sigma_a - mp.sigma_s);
+                                           float pdf = T_maj[ch] * sigma_maj[ch];
+                                           T_ray = T_ray * (T_maj * sigma_n / pdf);
+                                           r_l = r_l * (T_maj * sigma_maj / pdf);
+                                           r_u = r_u * (T_maj * sigma_n / pdf);
+                                           V3 Tr = T_ray / avg3(r_l + r_u);
+                                           if (max_comp(Tr) < 0.05f) {
+                                               float q = 0.75f;
+                                               if (rng.uniform() < q) T_ray = V3();
+                                               else T_ray = T_ray / (1 - q);
+                                           }
+                                           return nonzero(T_ray);
+                                       });
+                T_ray = T_ray * (T_maj / T_maj[ch]);
+                r_l = r_l * (T_maj / T_maj[ch]);
+                r_u = r_u * (T_maj / T_maj[ch]);
+            }
+            if (!nonzero(T_ray)) { blocked = true; break; }
+            if (h.prim < 0) break;
+            SurfaceIntr hs = make_intr(sc, h, lightRay.d, lightRay.medium);
+            spawn_ray_to(hs.p, hs.pError, hs.n, sr.pLight, sr.pLightErr, sr.nLight, &lightRay.o, &lightRay.d);
+            lightRay.medium = hs.get_medium(lightRay.d);
+        }
+        if (!blocked) {
+            r_l = r_l * sr.rl;
+            r_u = r_u * sr.ru;
+            V3 Ld = sr.delta ? sr.contrib * T_ray / avg3(r_l) : sr.contrib * T_ray / avg3(r_l + r_u);
+            float4 e = W.P.rl_L[slot];
+            e.y += Ld.x; e.z += Ld.y; e.w += Ld.z;
+            W.P.rl_L[slot] = e;
+        }
+    }
+    counter_add(W.counters, CNT_QUERIES, tc.queries);
+    counter_add(W.counters, CNT_DDA, tc.dda);
+    counter_add(W.counters, CNT_BVH, nodes);
+}
+
+// ------------------------------------------------------------------ film + regeneration (integrators.cpp:308-334)
+__global__ void __launch_bounds__(kBlock) k_finish(const DScene sc, const Wavefront W) {
+    const int n = *W.done.count;
+    unsigned paths = 0;
+    for (int i = gtid(); i < n; i += gstride()) {
+        int slot = W.done.items[i];
+        float4 e = W.P.rl_L[slot];
+        int pixel = __float_as_int(W.P.misc2[slot].y);
+        film_add(sc, W.film, pixel, V3(e.y, e.z, e.w));
+        paths++;
+        PathRegs r;
+        bool ok = regenerate(sc, W, slot, r);
+        queue_push(W.next, ok, slot);
+    }
+    counter_add(W.counters, CNT_PATHS, paths);
+}
+
+__global__ void k_reset_counts(int *counts, int n, int keep) {
+    int i = threadIdx.x;
+    if (i < n && i != keep) counts[i] = 0;
+}
+
+}  // namespace vspg

@@ -1,0 +1,257 @@
+// C-ABI implementation (include/vspg.h): context, HBM staging of the scene / guiding inputs, the wavefront
+// render loop, film and counters, and the per-kernel parity hooks.  No CPU fallback: every compute entry point
+// launches CUDA kernels and returns VSPG_ERR_CUDA if the device is unavailable.
+#include <cuda_runtime.h>
+
+#include <cstdarg>
+#include <cstdio>
+#include <cstdlib>
+#include <string>
+#include <vector>
+
+#include "host_util.h"
+#include "kernels2.cuh"
+#include "debug_kernels.cuh"
+
+using namespace vspg;
+using namespace vspg_host;
+
+extern "C" const float vspg_hg_vmm_table[128 * 18];  // hg_table_data.cpp
+
+struct vspg_ctx {
+    int device = 0;
+    int sm_count = 148;
+    std::string err;
+    std::vector<void *> scene_allocs, guide_allocs, wf_allocs;
+    DScene sc{};
+    bool have_scene = false;
+    Wavefront W{};
+    int capacity = 0, requested_capacity = 0;
+    int *qcounts = nullptr;       // device: 8 queue counters
+    int *h_pinned = nullptr;      // pinned readback
+    double *film = nullptr;
+    unsigned long long *counters = nullptr;
+    unsigned long long launches = 0, iterations = 0;
+    int film_w = 0, film_h = 0;
+    int grid_layout = GRID_CELL8;
+    // timing
+    bool timing = false;
+    cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+    double ms_medium = 0, ms_total = 0;
+    unsigned long long launches_medium = 0;
+};
+
+static std::string g_create_error;
+
+static int fail(vspg_ctx *c, int code, const char *fmt, ...) {
+    char buf[1024];
+    va_list ap; va_start(ap, fmt); vsnprintf(buf, sizeof buf, fmt, ap); va_end(ap);
+    if (c) c->err = buf; else g_create_error = buf;
+    return code;
+}
+#define CK(call)                                                                                         \
+    do {                                                                                                 \
+        cudaError_t e_ = (call);                                                                         \
+        if (e_ != cudaSuccess) return fail(ctx, VSPG_ERR_CUDA, "%s failed: %s", #call, cudaGetErrorString(e_)); \
+    } while (0)
+
+template <typename T>
+static cudaError_t upload(std::vector<void *> &owner, const T *host, size_t n, const T **dev) {
+    *dev = nullptr;
+    if (n == 0) return cudaSuccess;
+    void *p = nullptr;
+    cudaError_t e = cudaMalloc(&p, n * sizeof(T));
+    if (e != cudaSuccess) return e;
+    owner.push_back(p);
+    e = cudaMemcpy(p, host, n * sizeof(T), cudaMemcpyHostToDevice);
+    *dev = (const T *)p;
+    return e;
+}
+static void free_all(std::vector<void *> &v) { for (void *p : v) cudaFree(p); v.clear(); }
+
+extern "C" {
+
+const char *vspg_version(void) { return "vspg-b200 0.1 (sm_100a)"; }
+
+const char *vspg_last_error(const vspg_ctx *ctx) { return ctx ? ctx->err.c_str() : g_create_error.c_str(); }
+
+void vspg_integrator_defaults(vspg_integrator_params *p) {  // vspg.cpp:1263-1319
+    p->max_depth = 5; p->min_rr_depth = 1; p->use_nee = 1; p->surface_guiding = 1; p->volume_guiding = 1;
+    p->surface_guiding_ris = 1; p->volume_guiding_ris = 0; p->vsp_guiding = 1; p->vsp_primary_guiding = 1;
+    p->vsp_secondary_guiding = 1; p->vsp_mis_ratio = 0.5f; p->vsp_criterion_variance = 1; p->vsp_sampling_nds = 0;
+    p->collision_probability_bias = 0; p->light_sampler = VSPG_LIGHTSAMPLER_BVH; p->regularize = 0;
+}
+
+int vspg_create(vspg_ctx **out, int device_ordinal) {
+    if (!out) return fail(nullptr, VSPG_ERR_INVALID, "vspg_create: out is NULL");
+    *out = nullptr;
+    int n = 0;
+    cudaError_t e = cudaGetDeviceCount(&n);
+    if (e != cudaSuccess || n == 0)
+        return fail(nullptr, VSPG_ERR_CUDA, "vspg_create: no CUDA device (%s); this library has no CPU fallback",
+                    e == cudaSuccess ? "device count 0" : cudaGetErrorString(e));
+    if (device_ordinal < 0 || device_ordinal >= n) return fail(nullptr, VSPG_ERR_INVALID, "vspg_create: device %d out of range [0,%d)", device_ordinal, n);
+    vspg_ctx *ctx = new vspg_ctx();
+    ctx->device = device_ordinal;
+    if ((e = cudaSetDevice(device_ordinal)) != cudaSuccess) { delete ctx; return fail(nullptr, VSPG_ERR_CUDA, "cudaSetDevice: %s", cudaGetErrorString(e)); }
+    cudaDeviceProp prop;
+    if (cudaGetDeviceProperties(&prop, device_ordinal) == cudaSuccess) ctx->sm_count = prop.multiProcessorCount;
+    vspg_integrator_defaults(&ctx->sc.ip);
+    ctx->sc.ip.light_sampler = VSPG_LIGHTSAMPLER_UNIFORM;
+    const char *lay = getenv("VSPG_GRID_LAYOUT");
+    if (lay && std::string(lay) == "linear") ctx->grid_layout = GRID_LINEAR;
+    *out = ctx;
+    return VSPG_OK;
+}
+
+void vspg_destroy(vspg_ctx *ctx) {
+    if (!ctx) return;
+    cudaSetDevice(ctx->device);
+    free_all(ctx->scene_allocs); free_all(ctx->guide_allocs); free_all(ctx->wf_allocs);
+    if (ctx->h_pinned) cudaFreeHost(ctx->h_pinned);
+    if (ctx->ev0) cudaEventDestroy(ctx->ev0);
+    if (ctx->ev1) cudaEventDestroy(ctx->ev1);
+    delete ctx;
+}
+
+int vspg_build_majorant_grid(const vspg_medium *m, float *out) {
+    if (!m || !out || m->type == VSPG_MEDIUM_HOMOGENEOUS) return VSPG_ERR_INVALID;
+    build_majorant_grid(m, out);
+    return VSPG_OK;
+}
+
+int vspg_set_scene(vspg_ctx *ctx, const vspg_scene_desc *s) {
+    if (!ctx || !s) return VSPG_ERR_INVALID;
+    CK(cudaSetDevice(ctx->device));
+    if (s->n_triangles > 0 || s->n_spheres > 0)
+        return fail(ctx, VSPG_ERR_UNSUPPORTED, "set_scene: triangles/spheres are not on the supported path yet (quads only)");
+    if (s->camera.filter_type != 0) return fail(ctx, VSPG_ERR_UNSUPPORTED, "set_scene: only the box filter is supported");
+    if (s->camera.width <= 0 || s->camera.height <= 0) return fail(ctx, VSPG_ERR_INVALID, "set_scene: bad film resolution");
+    free_all(ctx->scene_allocs);
+    ctx->have_scene = false;
+    DScene &sc = ctx->sc;
+    sc.cam = s->camera;
+    // ---- media
+    std::vector<DMedium> media(s->n_media);
+    for (int i = 0; i < s->n_media; i++) {
+        const vspg_medium &m = s->media[i];
+        DMedium &d = media[i];
+        memset(&d, 0, sizeof d);
+        d.type = m.type;
+        for (int a = 0; a < 3; a++) { d.bmin[a] = m.bounds_min[a]; d.bmax[a] = m.bounds_max[a]; d.sigma_a[a] = m.sigma_a[a]; d.sigma_s[a] = m.sigma_s[a]; d.mres[a] = m.maj_res[a]; }
+        memcpy(d.mInv, m.render_from_medium.mInv, sizeof d.mInv);
+        d.sigma_scale = m.sigma_scale; d.g = m.g; d.nx = m.nx; d.ny = m.ny; d.nz = m.nz;
+        d.layout = GRID_LINEAR;
+        if (m.type == VSPG_MEDIUM_HOMOGENEOUS) continue;
+        if (m.type != VSPG_MEDIUM_GRID && m.type != VSPG_MEDIUM_RGBGRID) return fail(ctx, VSPG_ERR_UNSUPPORTED, "set_scene: medium %d has unsupported type %d", i, m.type);
+        size_t nvox = (size_t)m.nx * m.ny * m.nz;
+        if (nvox == 0 || m.maj_res[0] <= 0 || m.maj_res[1] <= 0 || m.maj_res[2] <= 0) return fail(ctx, VSPG_ERR_INVALID, "set_scene: medium %d has empty grid", i);
+        if (m.type == VSPG_MEDIUM_GRID) {
+            if (!m.density) return fail(ctx, VSPG_ERR_INVALID, "set_scene: medium %d has no density grid", i);
+            CK(upload(ctx->scene_allocs, m.density, nvox, &d.density));
+        } else {
+            if (m.sigma_a_rgb) CK(upload(ctx->scene_allocs, m.sigma_a_rgb, nvox * 3, &d.sa_rgb));
+            if (m.sigma_s_rgb) CK(upload(ctx->scene_allocs, m.sigma_s_rgb, nvox * 3, &d.ss_rgb));
+        }
+        size_t nmaj = (size_t)m.maj_res[0] * m.maj_res[1] * m.maj_res[2];
+        if (m.majorant) CK(upload(ctx->scene_allocs, m.majorant, nmaj, &d.majorant));
+        else {
+            std::vector<float> maj(nmaj);
+            build_majorant_grid(&m, maj.data());
+            CK(upload(ctx->scene_allocs, maj.data(), nmaj, &d.majorant));
+        }
+        if (m.type == VSPG_MEDIUM_GRID && ctx->grid_layout == GRID_CELL8) {
+            size_t ncell = (size_t)(m.nx + 1) * (m.ny + 1) * (m.nz + 1);
+            void *cells = nullptr;
+            CK(cudaMalloc(&cells, ncell * 32));
+            ctx->scene_allocs.push_back(cells);
+            int blocks = (int)std::min<size_t>((ncell + 255) / 256, 148 * 32);
+            k_build_cells<<<blocks, 256>>>(d.density, m.nx, m.ny, m.nz, (float4 *)cells);
+            CK(cudaGetLastError());
+            d.cells = (const float4 *)cells; d.layout = GRID_CELL8;
+        }
+    }
+    CK(upload(ctx->scene_allocs, media.data(), media.size(), &sc.media));
+    sc.n_media = s->n_media;
+    // ---- quads + BVH
+    std::vector<DQuad> quads(s->n_quads);
+    float bmin[3] = {INFINITY, INFINITY, INFINITY}, bmax[3] = {-INFINITY, -INFINITY, -INFINITY};
+    for (int i = 0; i < s->n_quads; i++) {
+        const vspg_quad &q = s->quads[i];
+        DQuad &d = quads[i];
+        memcpy(d.p00, q.p00, 12); memcpy(d.p10, q.p10, 12); memcpy(d.p01, q.p01, 12); memcpy(d.p11, q.p11, 12);
+        d.material = q.material; d.area_light = q.area_light; d.medium_inside = q.medium_inside; d.medium_outside = q.medium_outside;
+        d.has_interface = q.has_interface; d.flip_normal = q.flip_normal;
+        if (q.material >= s->n_materials || q.area_light >= s->n_lights || q.medium_inside >= s->n_media || q.medium_outside >= s->n_media)
+            return fail(ctx, VSPG_ERR_INVALID, "set_scene: quad %d references an out-of-range material/light/medium", i);
+        H3 p00(q.p00), p10(q.p10), p01(q.p01), p11(q.p11);
+        d.is_rect = quad_is_rectangle(p00, p10, p01, p11) ? 1 : 0;
+        d.area = quad_area(p00, p10, p01, p11);
+        const float *P[4] = {q.p00, q.p10, q.p01, q.p11};
+        for (int k = 0; k < 4; k++)
+            for (int a = 0; a < 3; a++) { bmin[a] = std::min(bmin[a], P[k][a]); bmax[a] = std::max(bmax[a], P[k][a]); }
+    }
+    CK(upload(ctx->scene_allocs, quads.data(), quads.size(), &sc.quads));
+    sc.n_quads = s->n_quads;
+    HostBvh bvh = build_bvh(s->quads, s->n_quads);
+    static_assert(sizeof(HostBvhNode) == sizeof(DBvhNode) && sizeof(DBvhNode) == 48, "BVH node layout");
+    CK(upload(ctx->scene_allocs, (const DBvhNode *)bvh.nodes.data(), bvh.nodes.size(), &sc.bvh));
+    CK(upload(ctx->scene_allocs, bvh.prim_ids.data(), bvh.prim_ids.size(), &sc.prim_ids));
+    sc.n_bvh = (int)bvh.nodes.size();
+    // Bounds3::BoundingSphere of the aggregate bounds (lights' Preprocess)
+    if (s->n_quads) {
+        H3 c((bmin[0] + bmax[0]) / 2, (bmin[1] + bmax[1]) / 2, (bmin[2] + bmax[2]) / 2);
+        sc.scene_center[0] = c.x; sc.scene_center[1] = c.y; sc.scene_center[2] = c.z;
+        sc.scene_radius = hdist(c, H3(bmax[0], bmax[1], bmax[2]));
+    } else { sc.scene_center[0] = sc.scene_center[1] = sc.scene_center[2] = 0; sc.scene_radius = 0; }
+    // ---- materials, lights
+    for (int i = 0; i < s->n_materials; i++)
+        if (s->materials[i].type != VSPG_MATERIAL_DIFFUSE) return fail(ctx, VSPG_ERR_UNSUPPORTED, "set_scene: material %d: only diffuse is supported", i);
+    CK(upload(ctx->scene_allocs, s->materials, (size_t)s->n_materials, &sc.materials));
+    sc.n_materials = s->n_materials;
+    std::vector<DLight> lights(s->n_lights);
+    std::vector<int> inf;
+    std::vector<float> power(s->n_lights);
+    float sum = 0;
+    for (int i = 0; i < s->n_lights; i++) {
+        const vspg_light &l = s->lights[i];
+        DLight &d = lights[i];
+        d.type = l.type; memcpy(d.L, l.L, 12); memcpy(d.pos, l.pos, 12);
+        d.shape_index = l.shape_index; d.two_sided = l.two_sided; d.medium = l.medium; d.pmf = 0;
+        const float Pi = 3.14159265358979323846f;
+        auto avgScaled = [&](float c) { float v = l.L[0] * c; v += l.L[1] * c; v += l.L[2] * c; return v / 3; };  // (L * c).Average()
+        switch (l.type) {  // lights.cpp Phi(), averaged over RGB
+        case VSPG_LIGHT_DIFFUSE_AREA:
+            if (l.shape_kind != 0 || l.shape_index < 0 || l.shape_index >= s->n_quads) return fail(ctx, VSPG_ERR_UNSUPPORTED, "set_scene: light %d: area lights must reference a quad", i);
+            power[i] = avgScaled(Pi * (l.two_sided ? 2.f : 1.f) * quads[l.shape_index].area); break;
+        case VSPG_LIGHT_POINT: power[i] = avgScaled(4 * Pi); break;
+        case VSPG_LIGHT_DISTANT: power[i] = avgScaled(Pi * (sc.scene_radius * sc.scene_radius)); break;
+        case VSPG_LIGHT_UNIFORM_INFINITE: power[i] = avgScaled(4 * Pi * Pi * (sc.scene_radius * sc.scene_radius)); inf.push_back(i); break;
+        default: return fail(ctx, VSPG_ERR_UNSUPPORTED, "set_scene: light %d has unsupported type %d", i, l.type);
+        }
+        sum += power[i];
+    }
+    if (sum == 0) { for (auto &p : power) p = 1.f; sum = (float)s->n_lights; }
+    for (int i = 0; i < s->n_lights; i++) lights[i].pmf = power[i] / sum;
+    CK(upload(ctx->scene_allocs, lights.data(), lights.size(), &sc.lights));
+    CK(upload(ctx->scene_allocs, inf.data(), inf.size(), &sc.inf_lights));
+    sc.n_lights = s->n_lights; sc.n_inf_lights = (int)inf.size();
+    // ---- film
+    if (ctx->film_w != s->camera.width || ctx->film_h != s->camera.height || !ctx->film) {
+        if (ctx->film) cudaFree(ctx->film);
+        ctx->film = nullptr;
+        ctx->film_w = s->camera.width; ctx->film_h = s->camera.height;
+        CK(cudaMalloc((void **)&ctx->film, (size_t)ctx->film_w * ctx->film_h * 4 * sizeof(double)));
+    }
+    CK(cudaMemset(ctx->film, 0, (size_t)ctx->film_w * ctx->film_h * 4 * sizeof(double)));
+    if (!ctx->counters) { CK(cudaMalloc((void **)&ctx->counters, 8 * sizeof(unsigned long long))); CK(cudaMemset(ctx->counters, 0, 64)); }
+    CK(cudaDeviceSynchronize());
+    ctx->have_scene = true;
+    return VSPG_OK;
+}
+
+}  // extern "C"
+
+#include "vspg_ctx_guiding.inl"
+#include "vspg_ctx_render.inl"
+#include "vspg_ctx_debug.inl"

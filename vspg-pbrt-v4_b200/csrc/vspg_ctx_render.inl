@@ -1,0 +1,168 @@
+// Wavefront allocation, the render loop (ImageTileIntegrator::Render re-expressed), film and counters.
+// (included by vspg_ctx.cu)
+
+enum { Q_A = 0, Q_B = 1, Q_MEDIUM = 2, Q_SURFACE = 3, Q_SHADE = 4, Q_VOLSCATTER = 5, Q_SHADOW = 6, Q_DONE = 7, Q_COUNT = 8 };
+
+static int ensure_wavefront(vspg_ctx *ctx, unsigned long long total) {
+    int want = ctx->requested_capacity > 0 ? ctx->requested_capacity : (1 << 21);
+    if ((unsigned long long)want > total) want = (int)total;
+    want = std::max(want, 1024);
+    if (ctx->capacity >= want && ctx->capacity <= 4 * want) return VSPG_OK;
+    free_all(ctx->wf_allocs);
+    ctx->capacity = 0;
+    const size_t n = (size_t)want;
+    auto alloc = [&](void **p, size_t bytes) -> cudaError_t {
+        cudaError_t e = cudaMalloc(p, bytes);
+        if (e == cudaSuccess) ctx->wf_allocs.push_back(*p);
+        return e;
+    };
+    PathSoA &P = ctx->W.P;
+    float4 **f4[] = {&P.o_dx, &P.d_med, &P.beta_ru, &P.ru_rl, &P.rl_L, &P.misc, &P.misc2, &P.hit, &P.ev,
+                     &P.sh_o, &P.sh_d, &P.sh_c, &P.sh_rl, &P.sh_ru, &P.sh_pl, &P.sh_ple};
+    for (auto pp : f4) CK(alloc((void **)pp, n * sizeof(float4)));
+    CK(alloc((void **)&P.rng, n * sizeof(ulonglong2)));
+    CK(alloc((void **)&P.sh_nz, n * sizeof(float)));
+    CK(alloc((void **)&ctx->qcounts, Q_COUNT * sizeof(int)));
+    int *items = nullptr;
+    CK(alloc((void **)&items, Q_COUNT * n * sizeof(int)));
+    Queue *qs[Q_COUNT] = {&ctx->W.active, &ctx->W.next, &ctx->W.medium, &ctx->W.surface, &ctx->W.shade, &ctx->W.volscatter, &ctx->W.shadow, &ctx->W.done};
+    for (int i = 0; i < Q_COUNT; i++) { qs[i]->items = items + (size_t)i * n; qs[i]->count = ctx->qcounts + i; }
+    CK(alloc((void **)&ctx->W.next_sample, sizeof(unsigned long long)));
+    if (!ctx->h_pinned) CK(cudaMallocHost((void **)&ctx->h_pinned, 64));
+    ctx->capacity = want;
+    ctx->W.capacity = want;
+    return VSPG_OK;
+}
+
+extern "C" {
+
+int vspg_render(vspg_ctx *ctx, int spp_begin, int spp_end, int spp_stride, int x0, int y0, int x1, int y1, int seed, void *cuda_stream) {
+    if (!ctx) return VSPG_ERR_INVALID;
+    if (!ctx->have_scene) return fail(ctx, VSPG_ERR_STATE, "render: set_scene has not been called");
+    CK(cudaSetDevice(ctx->device));
+    if (spp_stride < 1) spp_stride = 1;
+    if (x0 < 0 || y0 < 0 || x1 > ctx->film_w || y1 > ctx->film_h || x0 >= x1 || y0 >= y1) return fail(ctx, VSPG_ERR_INVALID, "render: bad pixel window");
+    if (spp_begin < 0 || spp_end < spp_begin) return fail(ctx, VSPG_ERR_INVALID, "render: bad sample range");
+    const DScene &scRef = ctx->sc;
+    if ((scRef.ip.volume_guiding_ris == 0 || true) && scRef.ip.vsp_sampling_nds && scRef.ip.collision_probability_bias && !scRef.tr_rgb) {
+        // the reference falls back to *training* a Tr buffer here; this build has no training pass
+        return fail(ctx, VSPG_ERR_STATE, "render: collisionProbabilityBias needs a loaded transmittance buffer (loadTrBuffer)");
+    }
+    int nspp = (spp_end - spp_begin + spp_stride - 1) / spp_stride;
+    unsigned long long npix = (unsigned long long)(x1 - x0) * (y1 - y0);
+    unsigned long long total = npix * (unsigned long long)nspp;
+    if (total == 0) return VSPG_OK;
+    int rc = ensure_wavefront(ctx, total);
+    if (rc != VSPG_OK) return rc;
+    cudaStream_t st = (cudaStream_t)cuda_stream;
+    Wavefront &W = ctx->W;
+    W.total_samples = total; W.x0 = x0; W.y0 = y0; W.x1 = x1; W.y1 = y1; W.spp_begin = spp_begin; W.spp_stride = spp_stride; W.n_spp = nspp;
+    W.film = ctx->film; W.counters = ctx->counters;
+    ctx->sc.seed = seed;
+    const DScene sc = ctx->sc;
+    Queue *phys[2] = {nullptr, nullptr};
+    Queue qa = W.active, qb = W.next;   // physical queues 0 and 1; roles swap each iteration
+    (void)phys;
+    CK(cudaMemsetAsync(ctx->qcounts, 0, Q_COUNT * sizeof(int), st));
+    CK(cudaMemsetAsync(W.next_sample, 0, sizeof(unsigned long long), st));
+    const int grid = ctx->sm_count * 8;
+    const bool guidedVol = sc.vol.present, guidedSurf = sc.surf.present;
+    int nslots = (int)std::min<unsigned long long>((unsigned long long)ctx->capacity, total);
+    W.active = qa; W.next = qb;
+    k_generate<<<grid, kBlock, 0, st>>>(sc, W, nslots);
+    ctx->launches++;
+    int cur = 0;  // physical index of the active queue
+    const bool timing = ctx->timing;
+    if (timing && !ctx->ev0) { CK(cudaEventCreate(&ctx->ev0)); CK(cudaEventCreate(&ctx->ev1)); }
+    cudaEvent_t evStart = nullptr, evStop = nullptr;
+    if (timing) { CK(cudaEventCreate(&evStart)); CK(cudaEventCreate(&evStop)); CK(cudaEventRecord(evStart, st)); }
+    float msMedium = 0;
+    while (true) {
+        k_intersect<<<grid, kBlock, 0, st>>>(sc, W);
+        if (timing) CK(cudaEventRecord(ctx->ev0, st));
+        k_medium<<<grid, kBlock, 0, st>>>(sc, W);
+        if (timing) CK(cudaEventRecord(ctx->ev1, st));
+        if (guidedVol) k_volscatter<true><<<grid, kBlock, 0, st>>>(sc, W); else k_volscatter<false><<<grid, kBlock, 0, st>>>(sc, W);
+        k_surface<<<grid, kBlock, 0, st>>>(sc, W);
+        if (guidedSurf) k_shade<true><<<grid, kBlock, 0, st>>>(sc, W); else k_shade<false><<<grid, kBlock, 0, st>>>(sc, W);
+        k_shadow<<<grid, kBlock, 0, st>>>(sc, W);
+        k_finish<<<grid, kBlock, 0, st>>>(sc, W);
+        ctx->launches += 7; ctx->iterations++; ctx->launches_medium++;
+        // swap roles: next becomes active; clear every other counter
+        cur ^= 1;
+        Queue t = W.active; W.active = W.next; W.next = t;
+        CK(cudaMemcpyAsync(ctx->h_pinned, W.active.count, sizeof(int), cudaMemcpyDeviceToHost, st));
+        k_reset_counts<<<1, 32, 0, st>>>(ctx->qcounts, Q_COUNT, cur);
+        ctx->launches++;
+        CK(cudaStreamSynchronize(st));
+        if (timing) { float ms = 0; CK(cudaEventElapsedTime(&ms, ctx->ev0, ctx->ev1)); msMedium += ms; }
+        if (ctx->h_pinned[0] == 0) break;
+    }
+    if (timing) {
+        CK(cudaEventRecord(evStop, st)); CK(cudaEventSynchronize(evStop));
+        float ms = 0; CK(cudaEventElapsedTime(&ms, evStart, evStop));
+        ctx->ms_total += ms; ctx->ms_medium += msMedium;
+        cudaEventDestroy(evStart); cudaEventDestroy(evStop);
+    }
+    CK(cudaGetLastError());
+    return VSPG_OK;
+}
+
+int vspg_film_clear(vspg_ctx *ctx) {
+    if (!ctx || !ctx->film) return VSPG_ERR_STATE;
+    CK(cudaSetDevice(ctx->device));
+    CK(cudaMemset(ctx->film, 0, (size_t)ctx->film_w * ctx->film_h * 4 * sizeof(double)));
+    return VSPG_OK;
+}
+int vspg_film_device_ptr(vspg_ctx *ctx, double **rgbw, size_t *n_doubles) {
+    if (!ctx || !ctx->film || !rgbw) return VSPG_ERR_STATE;
+    *rgbw = ctx->film;
+    if (n_doubles) *n_doubles = (size_t)ctx->film_w * ctx->film_h * 4;
+    return VSPG_OK;
+}
+int vspg_film_download(vspg_ctx *ctx, double *host_rgbw) {
+    if (!ctx || !ctx->film || !host_rgbw) return VSPG_ERR_STATE;
+    CK(cudaSetDevice(ctx->device));
+    CK(cudaMemcpy(host_rgbw, ctx->film, (size_t)ctx->film_w * ctx->film_h * 4 * sizeof(double), cudaMemcpyDeviceToHost));
+    return VSPG_OK;
+}
+int vspg_film_resolve(vspg_ctx *ctx, float *host_rgb) {  // film.h:269-290 GetPixelRGB: rgbSum / weightSum
+    if (!ctx || !ctx->film || !host_rgb) return VSPG_ERR_STATE;
+    size_t n = (size_t)ctx->film_w * ctx->film_h;
+    std::vector<double> tmp(n * 4);
+    int rc = vspg_film_download(ctx, tmp.data());
+    if (rc != VSPG_OK) return rc;
+    for (size_t i = 0; i < n; i++) {
+        double w = tmp[4 * i + 3];
+        for (int k = 0; k < 3; k++) host_rgb[3 * i + k] = w != 0 ? (float)(tmp[4 * i + k] / w) : 0.f;
+    }
+    return VSPG_OK;
+}
+int vspg_counters_get(vspg_ctx *ctx, vspg_counters *out) {
+    if (!ctx || !out) return VSPG_ERR_INVALID;
+    memset(out, 0, sizeof *out);
+    if (!ctx->counters) return VSPG_OK;
+    CK(cudaSetDevice(ctx->device));
+    unsigned long long h[8];
+    CK(cudaMemcpy(h, ctx->counters, sizeof h, cudaMemcpyDeviceToHost));
+    out->paths = h[CNT_PATHS]; out->density_queries = h[CNT_QUERIES]; out->dda_steps = h[CNT_DDA]; out->cache_lookups = h[CNT_LOOKUPS];
+    out->bvh_nodes = h[CNT_BVH]; out->shadow_rays = h[CNT_SHADOW]; out->kernel_launches = ctx->launches; out->wave_iterations = ctx->iterations;
+    return VSPG_OK;
+}
+int vspg_counters_reset(vspg_ctx *ctx) {
+    if (!ctx) return VSPG_ERR_INVALID;
+    CK(cudaSetDevice(ctx->device));
+    if (ctx->counters) CK(cudaMemset(ctx->counters, 0, 64));
+    ctx->launches = 0; ctx->iterations = 0; ctx->ms_medium = 0; ctx->ms_total = 0; ctx->launches_medium = 0;
+    return VSPG_OK;
+}
+int vspg_kernel_times(vspg_ctx *ctx, int enable, float *ms_medium, float *ms_total, unsigned long long *launches_medium) {
+    if (!ctx) return VSPG_ERR_INVALID;
+    if (ms_medium) *ms_medium = (float)ctx->ms_medium;
+    if (ms_total) *ms_total = (float)ctx->ms_total;
+    if (launches_medium) *launches_medium = ctx->launches_medium;
+    ctx->timing = enable != 0;
+    return VSPG_OK;
+}
+
+}  // extern "C"
