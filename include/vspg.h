@@ -310,6 +310,10 @@ typedef struct vspg_segment {
 int vspg_debug_majorant_segments(vspg_ctx *ctx, int medium, int n, const float *rays7,
                                  int max_segments, vspg_segment *out, int *out_count);
 
+/* Medium::SamplePoint (media.h:256-261, 316-348, 417-441) at n render-space points:
+ * out7[i] = sigma_a RGB, sigma_s RGB, g. */
+int vspg_debug_density(vspg_ctx *ctx, int medium, int n, const float *pos3, float *out7);
+
 /* One SampleDistance call (vspg.cpp:637-1096) up to and including the
  * scatter / pass-through decision, on explicit inputs. */
 typedef struct vspg_sd_input {

@@ -1,0 +1,264 @@
+"""GPU parity tests: the CUDA path, called through the C ABI (libvspg.so), against the CPU oracle on the same seeded
+inputs.  Bars (BASELINE.json north_star): majorant segments, density fetches and cache-node selection bit-exact;
+sampled distances / pdfs / weights within 1e-5 relative; full renders statistically identical on fixed streams.
+"""
+import ctypes as C
+
+import numpy as np
+import pytest
+
+from pyvspg import _abi as A
+from pyvspg import api
+
+import helpers as H
+
+pytestmark = pytest.mark.gpu
+
+REL_TOL = 1e-5  # north_star: "sampled distances, PDFs and weights match within 1e-5 relative"
+
+
+def _setup(ctx, cfg):
+    ctx.set_scene(cfg.scene)
+    ctx.set_guiding(cfg.guiding)
+    ctx.set_integrator(cfg.ip)
+
+
+@pytest.mark.parametrize("name", ["C2", "C5"])
+def test_majorant_segments_bit_exact(ctx, orc, name):
+    cfg = H.small(name)
+    _setup(ctx, cfg)
+    rng = np.random.default_rng(11)
+    rays = H.random_rays(rng, 4096, cfg.scene.eye)
+    med = cfg.scene.desc.media[0]
+    seg_g, cnt_g = ctx.debug_majorant_segments(0, rays, 64)
+    seg_o, cnt_o = orc.majorant_segments(med, rays, 64)
+    assert np.array_equal(cnt_g, cnt_o)
+    assert cnt_o.max() > 8 and (cnt_o == 0).any()          # both long walks and misses are covered
+    for i in range(len(cnt_o)):
+        c = min(int(cnt_o[i]), 64)
+        assert np.array_equal(seg_g[i, :c].view(np.uint32), seg_o[i, :c].view(np.uint32)), f"ray {i}"
+
+
+def test_majorant_grid_host_builder_matches_oracle(orc):
+    cfg = H.small("C2")
+    med = cfg.scene.desc.media[0]
+    assert np.array_equal(api.build_majorant_grid(med).view(np.uint32), orc.build_majorant_grid(med).view(np.uint32))
+    cfg5 = H.small("C5")
+    med5 = cfg5.scene.desc.media[0]
+    assert np.array_equal(api.build_majorant_grid(med5).view(np.uint32), orc.build_majorant_grid(med5).view(np.uint32))
+
+
+@pytest.mark.parametrize("name", ["C1", "C2", "C5"])
+def test_density_fetch_bit_exact(ctx, orc, name):
+    cfg = H.small(name)
+    _setup(ctx, cfg)
+    rng = np.random.default_rng(5)
+    pts = (rng.uniform(-0.1, 1.1, size=(2000, 3)) - cfg.scene.eye).astype(np.float32)
+    got = ctx.debug_density(0, pts)
+    med = cfg.scene.desc.media[0]
+    want = np.array([orc.density_lookup(med, p) for p in pts], dtype=np.float32)  # sigma_a[0] + sigma_s[0]
+    assert np.array_equal((got[:, 0] + got[:, 3]).view(np.uint32), want.view(np.uint32))
+
+
+@pytest.mark.parametrize("which", ["surface", "volume"])
+def test_cache_lookup_bit_exact(ctx, orc, which):
+    cfg = H.small("C2", vol_leaves=512, surf_leaves=512)
+    _setup(ctx, cfg)
+    f = cfg.guiding.fields[which]
+    rng = np.random.default_rng(3)
+    lo, hi = np.array(list(f.bounds_min)), np.array(list(f.bounds_max))
+    pts = rng.uniform(lo - 0.05, hi + 0.05, size=(20000, 3)).astype(np.float32)
+    u = rng.random(20000).astype(np.float32)
+    u[:50] = -1.0                                          # negative sample => deterministic leaf (Field.h:136)
+    lg, rg, ug = ctx.debug_cache_lookup(which == "surface", pts, u)
+    lo_, ro, uo = orc.cache_lookup(f, pts, u)
+    assert np.array_equal(lg, lo_) and np.array_equal(rg, ro)
+    assert np.array_equal(ug.view(np.uint32), uo.view(np.uint32))
+    assert (rg != lg).any() and (rg == -1).any()           # stochastic neighbour picks and out-of-bounds both seen
+
+
+def _sd_inputs(cfg, rng, n, depth_mix=True):
+    arr = (A.SdInput * n)()
+    eye = cfg.scene.eye
+    rays = H.random_rays(rng, n, eye, tmax_range=(0.3, 3.0))
+    w, h = cfg.width, cfg.height
+    for i in range(n):
+        I = arr[i]
+        scale_ = 1.0 if i % 4 else float(rng.uniform(0.3, 2.5))   # unnormalised directions too (media_sampleTMaj.h:55-56)
+        I.o[:] = [float(x) for x in rays[i, :3]]
+        I.d[:] = [float(np.float32(x * scale_)) for x in rays[i, 3:6]]
+        I.t_max = float(rays[i, 6] / scale_)
+        I.medium = 0
+        I.pixel_x, I.pixel_y = int(rng.integers(0, w)), int(rng.integers(0, h))
+        I.depth = int(rng.integers(0, 4)) if depth_mix else 0
+        I.channel = int(rng.integers(0, 3))
+        r = rng.random()
+        I.vsp = float(rng.uniform(0.0, 1.0)) if r < 0.8 else (-1.0 if r < 0.9 else float("nan"))
+        I.beta[:] = [float(x) for x in rng.uniform(0.2, 1.5, 3)]
+        I.r_u[:] = [float(x) for x in rng.uniform(0.5, 1.5, 3)]
+        I.r_l[:] = [float(x) for x in rng.uniform(0.5, 1.5, 3)]
+        I.rng_state, I.rng_inc = H.pcg_state(rng)
+    return arr
+
+
+SD_CASES = [
+    ("C1", {}),                                                                     # homogeneous, unguided delta tracking
+    ("C1", dict(vsp_guiding=1)),                                                    # homogeneous analytic VSP (optical-depth space)
+    ("C2", {}),                                                                     # resampling
+    ("C2", dict(vsp_guiding=0)),                                                    # resampling routine, unguided weights
+    ("C2", dict(vsp_mis_ratio=1.0)),
+    ("C3", {}),                                                                     # NDS+ with Tr buffer
+    ("C3", dict(collision_probability_bias=0)),                                     # NDS
+    ("C3", dict(vsp_mis_ratio=0.0)),                                                # falls back to plain SampleT_maj
+    ("C5", {}),                                                                     # rgbgrid resampling (chromatic majorants)
+    ("C5", dict(vsp_sampling_nds=1)),
+]
+
+
+@pytest.mark.parametrize("name,over", SD_CASES)
+def test_sample_distance_parity(ctx, orc, name, over):
+    cfg = H.small(name)
+    for k, v in over.items():
+        setattr(cfg.ip, k, v)
+    _setup(ctx, cfg)
+    rng = np.random.default_rng(17)
+    n = 3000
+    inp = _sd_inputs(cfg, rng, n)
+    got = ctx.debug_sample_distance(inp)
+    want = orc.sample_distance(cfg.scene, cfg.guiding, cfg.ip, inp)
+    f = lambda a, k: H.struct_array_to_np(a, k)
+    # discrete decisions: identical except where a 1-ulp libm difference flips a comparison (must be very rare)
+    same = (f(got, "scattered") == f(want, "scattered")) & (f(got, "terminated") == f(want, "terminated")) & \
+           (f(got, "depth") == f(want, "depth")) & (f(got, "rng_state") == f(want, "rng_state")) & \
+           (f(got, "density_queries") == f(want, "density_queries")) & (f(got, "dda_steps") == f(want, "dda_steps"))
+    assert same.mean() >= 0.995, f"decision mismatch fraction {1 - same.mean():.4f}"
+    assert f(want, "scattered").sum() > n * 0.05 and (f(want, "scattered") == 0).sum() > n * 0.05
+    for k in ("p", "sigma_a", "sigma_s", "beta", "r_u", "r_l"):
+        a, b = f(got, k)[same], f(want, k)[same]
+        fin = np.isfinite(b).all(axis=1)
+        assert np.array_equal(np.isfinite(a).all(axis=1), fin)
+        err = H.rel_err(a[fin], b[fin], floor=1e-12)
+        assert err.max() <= REL_TOL, f"{k}: max rel err {err.max():.3e}"
+
+
+@pytest.mark.parametrize("surface,ris", [(1, 1), (1, 0), (0, 0), (0, 1)])
+def test_guided_sample_parity(ctx, orc, surface, ris):
+    cfg = H.small("C2", vol_leaves=256, surf_leaves=256)
+    cfg.ip.surface_guiding_ris = ris
+    cfg.ip.volume_guiding_ris = ris
+    _setup(ctx, cfg)
+    f = cfg.guiding.fields["surface" if surface else "volume"]
+    rng = np.random.default_rng(23)
+    n = 4000
+    lo, hi = np.array(list(f.bounds_min)), np.array(list(f.bounds_max))
+    arr = (A.GsInput * n)()
+
+    def unit():
+        v = rng.normal(size=3)
+        return v / np.linalg.norm(v)
+
+    for i in range(n):
+        I = arr[i]
+        I.p[:] = [float(x) for x in rng.uniform(lo, hi)]
+        nrm = unit()
+        wo = unit()
+        if surface and i % 3:                       # mostly front-facing wo
+            wo = wo if np.dot(wo, nrm) > 0 else -wo
+        I.wo[:] = [float(np.float32(x)) for x in wo]
+        I.n[:] = [float(np.float32(x)) for x in nrm]
+        I.g = float(rng.choice([0.0, 0.3, 0.6, 0.85, -0.4, 0.995]))
+        I.reflectance[:] = [float(x) for x in rng.uniform(0.1, 0.9, 3)]
+        I.v, I.u1 = float(rng.random()), float(rng.random())
+        I.u2[:] = [float(rng.random()), float(rng.random())]
+        I.wq[:] = [float(np.float32(x)) for x in unit()]
+        I.rng_state, I.rng_inc = H.pcg_state(rng)
+    got = ctx.debug_guided_sample(surface, arr)
+    want = orc.guided_sample(cfg.scene, cfg.guiding, cfg.ip, surface, arr)
+    g = lambda a, k: H.struct_array_to_np(a, k)
+    assert np.array_equal(g(got, "ok"), g(want, "ok"))
+    assert np.array_equal(g(got, "region"), g(want, "region"))           # cache-node selection: bit-exact
+    same = (g(got, "valid") == g(want, "valid")) & (g(got, "rng_state") == g(want, "rng_state"))
+    assert same.mean() >= 0.999
+    v = same & (g(want, "valid") == 1)
+    assert v.sum() > n * 0.5
+    # direction: compare by angle (components near zero have no relative meaning)
+    wi_g, wi_o = g(got, "wi")[v], g(want, "wi")[v]
+    cosang = np.clip((wi_g * wi_o).sum(1) / np.linalg.norm(wi_g, axis=1) / np.linalg.norm(wi_o, axis=1), -1, 1)
+    close = np.arccos(cosang) < 1e-3
+    assert close.mean() >= 0.998, f"direction mismatch fraction {1 - close.mean():.4f}"  # lobe picks flip only at CDF ties
+    idx = np.where(v)[0][close]
+    for k in ("pdf", "scatter_pdf", "mis_pdf", "f"):
+        a, b = g(got, k)[idx], g(want, k)[idx]
+        err = H.rel_err(a, b, floor=1e-7)
+        # the sampled direction itself carries ~1e-7 relative error; a kappa<=200 lobe amplifies it by <= kappa
+        assert np.quantile(err, 0.99) <= 2e-4 and err.max() <= 5e-3, f"{k}: q99 {np.quantile(err, 0.99):.2e} max {err.max():.2e}"
+    for k in ("pdf_wq", "vsp_wq"):                  # evaluated at an input direction: pure arithmetic parity
+        a, b = g(got, k), g(want, k)
+        err = H.rel_err(a, b, floor=1e-12)
+        assert err.max() <= REL_TOL, f"{k}: max rel err {err.max():.3e}"
+
+
+RENDER_CASES = [("C1", {}), ("C1", dict(vsp_guiding=1)), ("C2", {}), ("C3", {}), ("C4", {}), ("C5", {}),
+                ("C2", dict(use_nee=0)), ("C2", dict(max_depth=1)), ("C3", dict(volume_guiding_ris=1, surface_guiding_ris=0))]
+
+
+@pytest.mark.parametrize("name,over", RENDER_CASES)
+def test_render_matches_oracle_on_fixed_streams(ctx, orc, name, over):
+    """Every (pixel, sampleIndex) draws the same PCG32 stream on both sides, so whole films agree path by path except
+    where a last-ulp libm difference flips one stochastic decision; those paths are few and their effect is bounded."""
+    cfg = H.small(name)
+    for k, v in over.items():
+        setattr(cfg.ip, k, v)
+    _setup(ctx, cfg)
+    ctx.set_capacity(1500)          # smaller than the path count: exercises regeneration into free slots
+    ctx.film_clear()
+    ctx.counters_reset()
+    ctx.render(0, cfg.spp, seed=7)
+    film_g = ctx.film_download()
+    cnt_g = ctx.counters()
+    film_o, cnt_o = orc.render(cfg.scene, cfg.guiding, cfg.ip, 0, cfg.spp, seed=7, nthreads=8)
+    assert np.array_equal(film_g[..., 3], film_o[..., 3])                  # weight sums: exact
+    assert cnt_g["paths"] == cnt_o["paths"] == cfg.width * cfg.height * cfg.spp
+    a, b = film_g[..., :3], film_o[..., :3]
+    assert np.isfinite(a).all()
+    err = H.rel_err(a, b, floor=1e-3)
+    frac_close = (err.max(axis=2) < 1e-3).mean()
+    assert frac_close >= 0.97, f"only {frac_close:.4f} of pixels agree"
+    assert abs(a.mean() - b.mean()) <= 0.01 * b.mean() + 1e-6
+    for k in ("density_queries", "dda_steps", "cache_lookups", "shadow_rays"):
+        assert abs(cnt_g[k] - cnt_o[k]) <= 0.01 * max(1, cnt_o[k]), (k, cnt_g[k], cnt_o[k])
+
+
+def test_render_window_and_sample_stride_compose(ctx):
+    """Sharding invariants used by the multi-GPU path: disjoint windows / interleaved sample passes sum to the whole."""
+    cfg = H.small("C2")
+    _setup(ctx, cfg)
+    ctx.film_clear()
+    ctx.render(0, 4, seed=3)
+    whole = ctx.film_download()
+    ctx.film_clear()
+    w, h = cfg.width, cfg.height
+    ctx.render(0, 4, window=(0, 0, w // 2, h), seed=3)
+    ctx.render(0, 4, window=(w // 2, 0, w, h), seed=3)
+    assert np.allclose(ctx.film_download(), whole, rtol=1e-12, atol=0)
+    ctx.film_clear()
+    ctx.render(0, 4, spp_stride=2, seed=3)
+    ctx.render(1, 4, spp_stride=2, seed=3)
+    assert np.allclose(ctx.film_download(), whole, rtol=1e-12, atol=0)
+
+
+def test_errors_are_reported_not_fatal(ctx):
+    cfg = H.small("C3")
+    ctx.set_scene(cfg.scene)
+    ctx.set_guiding(None)
+    ctx.set_integrator(cfg.ip)
+    with pytest.raises(api.VspgError) as e:     # NDS+ without a transmittance buffer: the reference would start training
+        ctx.render(0, 1)
+    assert "transmittance" in str(e.value)
+    with pytest.raises(api.VspgError):
+        ctx.render(0, 1, window=(0, 0, cfg.width + 1, cfg.height))
+    ip = api.integrator_defaults(light_sampler=A.LIGHTSAMPLER_BVH)
+    with pytest.raises(api.VspgError):
+        ctx.set_integrator(ip)
+    with pytest.raises(KeyError):
+        api.integrator_defaults(no_such_parameter=1)

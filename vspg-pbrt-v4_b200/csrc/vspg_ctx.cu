@@ -16,7 +16,7 @@
 using namespace vspg;
 using namespace vspg_host;
 
-extern "C" const float vspg_hg_vmm_table[128 * 18];  // hg_table_data.cpp
+extern "C" const uint32_t vspg_hg_vmm_table_bits[128 * 18];  // hg_table_data.cpp (generated data)
 
 struct vspg_ctx {
     int device = 0;

@@ -1,0 +1,121 @@
+// Per-kernel parity hooks of the C ABI (include/vspg.h, "per-kernel parity hooks").  Each one stages the explicit
+// inputs in HBM, launches the same device functions the wavefront kernels call, and copies the results back.
+// (included by vspg_ctx.cu)
+
+namespace {
+struct DevBuf {
+    void *p = nullptr;
+    ~DevBuf() { if (p) cudaFree(p); }
+    cudaError_t alloc(size_t bytes) { return cudaMalloc(&p, bytes ? bytes : 1); }
+    template <typename T> T *as() { return (T *)p; }
+};
+}  // namespace
+
+#define CK_STATE(cond, msg) do { if (!(cond)) return fail(ctx, VSPG_ERR_STATE, msg); } while (0)
+
+extern "C" {
+
+int vspg_debug_majorant_segments(vspg_ctx *ctx, int medium, int n, const float *rays7, int max_segments, vspg_segment *out, int *out_count) {
+    if (!ctx || n < 0 || !rays7 || !out || !out_count || max_segments <= 0) return VSPG_ERR_INVALID;
+    CK_STATE(ctx->have_scene, "debug_majorant_segments: set_scene has not been called");
+    if (medium < 0 || medium >= ctx->sc.n_media) return fail(ctx, VSPG_ERR_INVALID, "debug_majorant_segments: medium %d out of range", medium);
+    if (n == 0) return VSPG_OK;
+    CK(cudaSetDevice(ctx->device));
+    DevBuf dr, dout, dcnt;
+    CK(dr.alloc((size_t)n * 7 * sizeof(float)));
+    CK(dout.alloc((size_t)n * max_segments * sizeof(vspg_segment)));
+    CK(dcnt.alloc((size_t)n * sizeof(int)));
+    CK(cudaMemcpy(dr.p, rays7, (size_t)n * 7 * sizeof(float), cudaMemcpyHostToDevice));
+    CK(cudaMemset(dout.p, 0, (size_t)n * max_segments * sizeof(vspg_segment)));
+    int blocks = std::min((n + kBlock - 1) / kBlock, ctx->sm_count * 8);
+    k_debug_segments<<<blocks, kBlock>>>(ctx->sc, medium, n, dr.as<float>(), max_segments, dout.as<vspg_segment>(), dcnt.as<int>());
+    ctx->launches++;
+    CK(cudaGetLastError());
+    CK(cudaMemcpy(out, dout.p, (size_t)n * max_segments * sizeof(vspg_segment), cudaMemcpyDeviceToHost));
+    CK(cudaMemcpy(out_count, dcnt.p, (size_t)n * sizeof(int), cudaMemcpyDeviceToHost));
+    return VSPG_OK;
+}
+
+int vspg_debug_density(vspg_ctx *ctx, int medium, int n, const float *pos3, float *out7) {
+    if (!ctx || n < 0 || !pos3 || !out7) return VSPG_ERR_INVALID;
+    CK_STATE(ctx->have_scene, "debug_density: set_scene has not been called");
+    if (medium < 0 || medium >= ctx->sc.n_media) return fail(ctx, VSPG_ERR_INVALID, "debug_density: medium %d out of range", medium);
+    if (n == 0) return VSPG_OK;
+    CK(cudaSetDevice(ctx->device));
+    DevBuf dp, dout;
+    CK(dp.alloc((size_t)n * 3 * sizeof(float)));
+    CK(dout.alloc((size_t)n * 7 * sizeof(float)));
+    CK(cudaMemcpy(dp.p, pos3, (size_t)n * 3 * sizeof(float), cudaMemcpyHostToDevice));
+    int blocks = std::min((n + kBlock - 1) / kBlock, ctx->sm_count * 8);
+    k_debug_density<<<blocks, kBlock>>>(ctx->sc, medium, n, dp.as<float>(), dout.as<float>());
+    ctx->launches++;
+    CK(cudaGetLastError());
+    CK(cudaMemcpy(out7, dout.p, (size_t)n * 7 * sizeof(float), cudaMemcpyDeviceToHost));
+    return VSPG_OK;
+}
+
+int vspg_debug_sample_distance(vspg_ctx *ctx, int n, const vspg_sd_input *in, vspg_sd_output *out) {
+    if (!ctx || n < 0 || !in || !out) return VSPG_ERR_INVALID;
+    CK_STATE(ctx->have_scene, "debug_sample_distance: set_scene has not been called");
+    for (int i = 0; i < n; i++) {
+        if (in[i].medium < 0 || in[i].medium >= ctx->sc.n_media) return fail(ctx, VSPG_ERR_INVALID, "debug_sample_distance: item %d: medium out of range", i);
+        if (in[i].channel < 0 || in[i].channel > 2) return fail(ctx, VSPG_ERR_INVALID, "debug_sample_distance: item %d: channel out of range", i);
+        if (in[i].pixel_x < 0 || in[i].pixel_x >= ctx->film_w || in[i].pixel_y < 0 || in[i].pixel_y >= ctx->film_h)
+            return fail(ctx, VSPG_ERR_INVALID, "debug_sample_distance: item %d: pixel outside the film", i);
+    }
+    if (n == 0) return VSPG_OK;
+    CK(cudaSetDevice(ctx->device));
+    DevBuf di, dout;
+    CK(di.alloc((size_t)n * sizeof(vspg_sd_input)));
+    CK(dout.alloc((size_t)n * sizeof(vspg_sd_output)));
+    CK(cudaMemcpy(di.p, in, (size_t)n * sizeof(vspg_sd_input), cudaMemcpyHostToDevice));
+    CK(cudaMemset(dout.p, 0, (size_t)n * sizeof(vspg_sd_output)));
+    int blocks = std::min((n + kBlock - 1) / kBlock, ctx->sm_count * 8);
+    k_debug_sample_distance<<<blocks, kBlock>>>(ctx->sc, n, di.as<vspg_sd_input>(), dout.as<vspg_sd_output>());
+    ctx->launches++;
+    CK(cudaGetLastError());
+    CK(cudaMemcpy(out, dout.p, (size_t)n * sizeof(vspg_sd_output), cudaMemcpyDeviceToHost));
+    return VSPG_OK;
+}
+
+int vspg_debug_cache_lookup(vspg_ctx *ctx, int is_surface, int n, const float *pos3, const float *u, int *out_leaf, int *out_region, float *out_u) {
+    if (!ctx || n < 0 || !pos3 || !u || !out_leaf || !out_region || !out_u) return VSPG_ERR_INVALID;
+    const DField &f = is_surface ? ctx->sc.surf : ctx->sc.vol;
+    CK_STATE(f.present, "debug_cache_lookup: no guiding field loaded (set_guiding)");
+    if (n == 0) return VSPG_OK;
+    CK(cudaSetDevice(ctx->device));
+    DevBuf dp, du, dl, dr, dou;
+    CK(dp.alloc((size_t)n * 12)); CK(du.alloc((size_t)n * 4)); CK(dl.alloc((size_t)n * 4)); CK(dr.alloc((size_t)n * 4)); CK(dou.alloc((size_t)n * 4));
+    CK(cudaMemcpy(dp.p, pos3, (size_t)n * 12, cudaMemcpyHostToDevice));
+    CK(cudaMemcpy(du.p, u, (size_t)n * 4, cudaMemcpyHostToDevice));
+    int blocks = std::min((n + kBlock - 1) / kBlock, ctx->sm_count * 8);
+    k_debug_cache_lookup<<<blocks, kBlock>>>(ctx->sc, is_surface, n, dp.as<float>(), du.as<float>(), dl.as<int>(), dr.as<int>(), dou.as<float>());
+    ctx->launches++;
+    CK(cudaGetLastError());
+    CK(cudaMemcpy(out_leaf, dl.p, (size_t)n * 4, cudaMemcpyDeviceToHost));
+    CK(cudaMemcpy(out_region, dr.p, (size_t)n * 4, cudaMemcpyDeviceToHost));
+    CK(cudaMemcpy(out_u, dou.p, (size_t)n * 4, cudaMemcpyDeviceToHost));
+    return VSPG_OK;
+}
+
+int vspg_debug_guided_sample(vspg_ctx *ctx, int is_surface, int n, const vspg_gs_input *in, vspg_gs_output *out) {
+    if (!ctx || n < 0 || !in || !out) return VSPG_ERR_INVALID;
+    const DField &f = is_surface ? ctx->sc.surf : ctx->sc.vol;
+    CK_STATE(f.present, "debug_guided_sample: no guiding field loaded (set_guiding)");
+    if (n == 0) return VSPG_OK;
+    CK(cudaSetDevice(ctx->device));
+    DevBuf di, dout;
+    CK(di.alloc((size_t)n * sizeof(vspg_gs_input)));
+    CK(dout.alloc((size_t)n * sizeof(vspg_gs_output)));
+    CK(cudaMemcpy(di.p, in, (size_t)n * sizeof(vspg_gs_input), cudaMemcpyHostToDevice));
+    CK(cudaMemset(dout.p, 0, (size_t)n * sizeof(vspg_gs_output)));
+    long long threads = (long long)n * 32;
+    int blocks = (int)std::min<long long>((threads + kBlock - 1) / kBlock, (long long)ctx->sm_count * 8);
+    k_debug_guided_sample<<<blocks, kBlock>>>(ctx->sc, is_surface, n, di.as<vspg_gs_input>(), dout.as<vspg_gs_output>());
+    ctx->launches++;
+    CK(cudaGetLastError());
+    CK(cudaMemcpy(out, dout.p, (size_t)n * sizeof(vspg_gs_output), cudaMemcpyDeviceToHost));
+    return VSPG_OK;
+}
+
+}  // extern "C"

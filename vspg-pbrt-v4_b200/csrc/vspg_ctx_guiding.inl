@@ -44,7 +44,7 @@ int vspg_set_guiding(vspg_ctx *ctx, const vspg_guiding_desc *g) {
         // directional/vmm/VMMPhaseFunctions.cpp: 128 single-lobe-HG -> vMF-mixture fits (data table)
         std::vector<DHGRow> rows(128);
         for (int i = 0; i < 128; i++) {
-            const float *r = vspg_hg_vmm_table + 18 * i;
+            float r[18]; memcpy(r, vspg_hg_vmm_table_bits + 18 * i, sizeof r);
             rows[i].K = (int)r[0]; rows[i].g = r[1];
             for (int j = 0; j < 4; j++) { rows[i].w[j] = r[2 + j]; rows[i].mc[j] = r[6 + j]; rows[i].kappa[j] = r[10 + j]; rows[i].norm[j] = r[14 + j]; }
             if (rows[i].K < 0 || rows[i].K > 3) return fail(ctx, VSPG_ERR_INVALID, "HG table row %d has K=%d", i, rows[i].K);

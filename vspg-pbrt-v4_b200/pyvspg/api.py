@@ -1,0 +1,167 @@
+"""Python harness over the C ABI of libvspg.so (include/vspg.h): the call a user of the reference's
+`Integrator::Create(...)->Render()` seam makes (cpu/integrators.cpp:3711-3768, cpu/render.cpp:163), as a context
+object.  Host arrays are numpy; device memory is owned by the context.  No CPU fallback exists.
+"""
+import ctypes as C
+
+import numpy as np
+
+from . import _abi as A
+
+_lib = None
+
+
+def lib():
+    global _lib
+    if _lib is None:
+        _lib = A.load_library()
+    return _lib
+
+
+class VspgError(RuntimeError):
+    def __init__(self, code, msg):
+        super().__init__(f"vspg error {A.ERR_NAMES.get(code, code)}: {msg}")
+        self.code = code
+
+
+def integrator_defaults(**over):
+    """guidedvolpathvspgintegrator.cpp:1260-1322 defaults, overridable by keyword (field names of vspg_integrator_params)."""
+    ip = A.IntegratorParams()
+    lib().vspg_integrator_defaults(C.byref(ip))
+    for k, v in over.items():
+        if not hasattr(ip, k):
+            raise KeyError(f"unknown integrator parameter {k!r}")  # the reference ErrorExits on unused parameters
+        setattr(ip, k, v)
+    return ip
+
+
+def _fp(a):
+    return a.ctypes.data_as(A.PF)
+
+
+class Context:
+    """One vspg_ctx (= one GPU).  Thread-compatible, not thread-safe."""
+
+    def __init__(self, device=0):
+        self._h = A.P()
+        rc = lib().vspg_create(C.byref(self._h), int(device))
+        if rc != 0:
+            raise VspgError(rc, lib().vspg_last_error(None).decode())
+        self.width = self.height = 0
+
+    def close(self):
+        if self._h:
+            lib().vspg_destroy(self._h)
+            self._h = A.P()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def _ck(self, rc):
+        if rc != 0:
+            raise VspgError(rc, lib().vspg_last_error(self._h).decode())
+
+    # ---- inputs
+    def set_scene(self, scene):
+        """scene: pyvspg.scenes.Scene (holds the vspg_scene_desc and keeps its arrays alive)."""
+        self._ck(lib().vspg_set_scene(self._h, C.byref(scene.desc)))
+        self.width, self.height = scene.desc.camera.width, scene.desc.camera.height
+
+    def set_guiding(self, guiding):
+        self._ck(lib().vspg_set_guiding(self._h, C.byref(guiding.desc) if guiding is not None else None))
+
+    def set_integrator(self, ip):
+        self._ck(lib().vspg_set_integrator(self._h, C.byref(ip)))
+
+    def set_capacity(self, n):
+        self._ck(lib().vspg_set_capacity(self._h, int(n)))
+
+    # ---- rendering
+    def render(self, spp_begin, spp_end, spp_stride=1, window=None, seed=0, stream=None):
+        x0, y0, x1, y1 = window if window is not None else (0, 0, self.width, self.height)
+        self._ck(lib().vspg_render(self._h, spp_begin, spp_end, spp_stride, x0, y0, x1, y1, int(seed), stream))
+
+    def film_clear(self):
+        self._ck(lib().vspg_film_clear(self._h))
+
+    def film_device_ptr(self):
+        p, n = A.P(), C.c_size_t()
+        self._ck(lib().vspg_film_device_ptr(self._h, C.byref(p), C.byref(n)))
+        return p.value, n.value
+
+    def film_download(self, out=None):
+        if out is None:
+            out = np.empty((self.height, self.width, 4), dtype=np.float64)
+        self._ck(lib().vspg_film_download(self._h, out.ctypes.data_as(A.P)))
+        return out
+
+    def film_download_to(self, host_ptr):
+        """Download into a caller-owned (e.g. pinned) host buffer given by address."""
+        self._ck(lib().vspg_film_download(self._h, A.P(host_ptr)))
+
+    def film_resolve(self):
+        out = np.empty((self.height, self.width, 3), dtype=np.float32)
+        self._ck(lib().vspg_film_resolve(self._h, out.ctypes.data_as(A.P)))
+        return out
+
+    def counters(self):
+        c = A.Counters()
+        self._ck(lib().vspg_counters_get(self._h, C.byref(c)))
+        return {k: int(getattr(c, k)) for k, _ in A.Counters._fields_}
+
+    def counters_reset(self):
+        self._ck(lib().vspg_counters_reset(self._h))
+
+    def kernel_times(self, enable=True):
+        a, b, n = A.f32(), A.f32(), C.c_ulonglong()
+        self._ck(lib().vspg_kernel_times(self._h, int(enable), C.byref(a), C.byref(b), C.byref(n)))
+        return {"ms_medium": a.value, "ms_total": b.value, "launches_medium": n.value}
+
+    # ---- per-kernel parity hooks
+    def debug_majorant_segments(self, medium, rays7, max_segments=64):
+        rays7 = np.ascontiguousarray(rays7, dtype=np.float32).reshape(-1, 7)
+        n = rays7.shape[0]
+        seg = (A.Segment * (n * max_segments))()
+        cnt = np.zeros(n, dtype=np.int32)
+        self._ck(lib().vspg_debug_majorant_segments(self._h, medium, n, _fp(rays7), max_segments, seg, cnt.ctypes.data_as(C.POINTER(A.i32))))
+        arr = np.frombuffer(seg, dtype=np.float32).reshape(n, max_segments, 5).copy()
+        return arr, cnt
+
+    def debug_density(self, medium, pos3):
+        pos3 = np.ascontiguousarray(pos3, dtype=np.float32).reshape(-1, 3)
+        out = np.zeros((pos3.shape[0], 7), dtype=np.float32)
+        self._ck(lib().vspg_debug_density(self._h, medium, pos3.shape[0], _fp(pos3), _fp(out)))
+        return out
+
+    def debug_sample_distance(self, inputs):
+        n = len(inputs)
+        out = (A.SdOutput * n)()
+        self._ck(lib().vspg_debug_sample_distance(self._h, n, inputs, out))
+        return out
+
+    def debug_cache_lookup(self, is_surface, pos3, u):
+        pos3 = np.ascontiguousarray(pos3, dtype=np.float32).reshape(-1, 3)
+        u = np.ascontiguousarray(u, dtype=np.float32)
+        n = pos3.shape[0]
+        leaf, region, uo = np.zeros(n, np.int32), np.zeros(n, np.int32), np.zeros(n, np.float32)
+        self._ck(lib().vspg_debug_cache_lookup(self._h, int(is_surface), n, _fp(pos3), _fp(u), leaf.ctypes.data_as(C.POINTER(A.i32)),
+                                               region.ctypes.data_as(C.POINTER(A.i32)), _fp(uo)))
+        return leaf, region, uo
+
+    def debug_guided_sample(self, is_surface, inputs):
+        n = len(inputs)
+        out = (A.GsOutput * n)()
+        self._ck(lib().vspg_debug_guided_sample(self._h, int(is_surface), n, inputs, out))
+        return out
+
+
+def build_majorant_grid(medium):
+    n = medium.maj_res[0] * medium.maj_res[1] * medium.maj_res[2]
+    out = np.zeros(n, dtype=np.float32)
+    rc = lib().vspg_build_majorant_grid(C.byref(medium), _fp(out))
+    if rc != 0:
+        raise VspgError(rc, "build_majorant_grid")
+    return out
