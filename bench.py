@@ -1,0 +1,351 @@
+#!/usr/bin/env python
+"""bench.py -- paths/sec of the guidedvolpath(VSPG) render pass on B200 (BASELINE.json metric).
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--workload C2] [--impl reference]
+
+A *step* is one render of the whole workload (every (pixel, sampleIndex) of the configuration) on each rank.
+Workload = BASELINE.json configs[1] (C2: fBm 128^3 grid medium, VSPG resampling, loaded cache + ISG buffer,
+512x512, 64 spp) unless --workload says otherwise.  N > 1 (launched by torchrun, one rank per GPU): sample-pass
+sharding -- rank r renders sample indices r, r+N, ... of an N*spp render (per-GPU work fixed => "weak"), and the fp64
+film buffers are combined with one NCCL reduce over NVLink inside the timed region.
+
+JSON line keys (see DESIGN.md "Measurement"):
+  value     whole-job paths/s, inputs already resident in HBM (CUDA events, max over ranks)
+  e2e       same metric through the C ABI from HOST buffers: set_scene + set_guiding (H2D of grids / cache / buffers),
+            render, film download (D2H) inside the timed region
+  roofline  the dominant kernel's algorithmic grid bytes (Q*b_q + S*4) / its CUDA-event time vs the
+            measured HBM copy peak (MEASURED_PEAKS.json)
+  cpu_baseline  the CPU oracle port of the reference integrator on this box's host cores, bounded sample
+--impl reference: the reference's CPU algorithm (oracle port; the full pbrt binary is unbuildable here, see
+DESIGN.md) timed on the host cores, same metric/config.
+"""
+import argparse
+import json
+import os
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, os.path.join(ROOT, "vspg-pbrt-v4_b200"))
+
+WORKLOADS = {
+    # name: (builder key, kwargs, b_q bytes per density query)
+    "C1": ("C1", {}, 0),
+    "C2": ("C2", {}, 32),
+    "C3": ("C3", {}, 32),
+    "C4": ("C4", {}, 32),
+    "C5": ("C5", {}, 192),
+}
+
+
+def parse_args():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--workload", default="C2", choices=sorted(WORKLOADS))
+    ap.add_argument("--spp", type=int, default=0, help="override samples per pixel (reported in config)")
+    ap.add_argument("--res-scale", type=float, default=1.0, help="scale film resolution (reported in config)")
+    ap.add_argument("--capacity", type=int, default=0, help="paths in flight (0 = library default)")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--cpu-spp", type=int, default=0, help="spp of the CPU sample (0 = auto, ~10-30 s)")
+    return ap.parse_args()
+
+
+def build_config(args):
+    from pyvspg import configs
+    key, kw, bq = WORKLOADS[args.workload]
+    kw = dict(kw)
+    b = configs.BUILDERS[key]
+    if args.spp:
+        kw["spp"] = args.spp
+    if args.res_scale != 1.0:
+        import inspect
+        sig = inspect.signature(b).parameters
+        if "res" in sig:
+            kw["res"] = int(sig["res"].default * args.res_scale)
+        else:
+            kw["width"] = int(sig["width"].default * args.res_scale)
+            kw["height"] = int(sig["height"].default * args.res_scale)
+    return b(**kw), bq
+
+
+def config_dict(cfg, args, world):
+    med = cfg.scene.desc.media[0]
+    return {
+        "workload": cfg.name, "description": cfg.description, "width": cfg.width, "height": cfg.height, "spp_per_gpu": cfg.spp,
+        "spp_total": cfg.spp * world, "grid": [med.nx, med.ny, med.nz] if med.type != 0 else "homogeneous",
+        "sampler": "independent", "maxdepth": cfg.ip.max_depth,
+        "parallelism": f"sample-pass sharding x{world}" + (" + NCCL film reduce" if world > 1 else ""),
+        "l2": "path-state working set (2M paths x ~330 B = 0.7 GB) exceeds the 126 MB L2 each wave iteration; density grid "
+              "itself is L2-resident for 128^3 (8 MiB), HBM-resident for 512^3",
+    }
+
+
+class ClockSampler:
+    """Samples SM clock and throttle reasons through NVML while the timed region runs (B200_PROFILING.md)."""
+
+    def __init__(self, index):
+        self.samples, self.reasons, self.max_mhz, self._stop = [], set(), None, threading.Event()
+        self._t = None
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            self.nv = pynvml
+            self.h = pynvml.nvmlDeviceGetHandleByIndex(index)
+            self.max_mhz = pynvml.nvmlDeviceGetMaxClockInfo(self.h, pynvml.NVML_CLOCK_SM)
+        except Exception as e:  # NVML missing: record that, do not fail the bench
+            self.nv = None
+            self.err = str(e)
+
+    def _run(self):
+        nv = self.nv
+        names = {"hw_slowdown": nv.nvmlClocksThrottleReasonHwSlowdown, "hw_thermal_slowdown": nv.nvmlClocksThrottleReasonHwThermalSlowdown,
+                 "sw_thermal_slowdown": nv.nvmlClocksThrottleReasonSwThermalSlowdown, "sw_power_cap": nv.nvmlClocksThrottleReasonSwPowerCap}
+        while not self._stop.is_set():
+            try:
+                self.samples.append(nv.nvmlDeviceGetClockInfo(self.h, nv.NVML_CLOCK_SM))
+                r = nv.nvmlDeviceGetCurrentClocksThrottleReasons(self.h)
+                for k, bit in names.items():
+                    if r & bit:
+                        self.reasons.add(k)
+            except Exception:
+                pass
+            self._stop.wait(0.1)
+
+    def start(self):
+        if self.nv:
+            self._t = threading.Thread(target=self._run, daemon=True)
+            self._t.start()
+
+    def stop(self):
+        self._stop.set()
+        if self._t:
+            self._t.join()
+        if not self.nv:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": [], "note": "NVML unavailable: " + getattr(self, "err", "")}
+        s = sorted(self.samples)
+        return {"sm_mhz": s[len(s) // 2] if s else None, "sm_max_mhz": self.max_mhz, "reasons": sorted(self.reasons),
+                "samples": len(s)}
+
+
+def cpu_oracle_paths_per_s(cfg, spp, seed=0):
+    """Times the CPU oracle port (oracle/liboracle.so) of the reference integrator on all host cores.
+    Checker/baseline use only: nothing on the product path calls this."""
+    sys.path.insert(0, os.path.join(ROOT, "oracle"))
+    import orc
+    orc.lib()
+    cores = os.cpu_count() or 1
+    t0 = time.perf_counter()
+    _, cnt = orc.render(cfg.scene, cfg.guiding, cfg.ip, 0, spp, seed=seed, nthreads=cores)
+    dt = time.perf_counter() - t0
+    return cnt["paths"] / dt, cores, dt, cnt["paths"]
+
+
+def run_reference(args):
+    """--impl reference: the reference's CPU algorithm on the host cores (oracle port; kind = "port")."""
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    cfg, _ = build_config(args)
+    # bounded sample per step: calibrate with 1 spp, then size each step to ~8 s
+    v1, cores, dt1, _ = cpu_oracle_paths_per_s(cfg, 1)
+    spp_step = args.cpu_spp or max(1, min(cfg.spp, int(8.0 / max(dt1, 1e-3))))
+    for _ in range(max(0, args.warmup - 1)):
+        cpu_oracle_paths_per_s(cfg, 1)
+    tot_paths, tot_t = 0, 0.0
+    for s in range(args.steps):
+        v, cores, dt, n = cpu_oracle_paths_per_s(cfg, spp_step, seed=s)
+        tot_paths += n
+        tot_t += dt
+    val = tot_paths / tot_t
+    sample = f"{cfg.width}x{cfg.height} x {spp_step} spp per step of the {cfg.spp}-spp workload (waves are independent)"
+    print(json.dumps({
+        "impl": "reference", "metric": "paths/sec (guidedvolpathvspg render pass)", "value": val, "unit": "paths/s", "n_gpus": args.gpus,
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * tot_t / max(1, args.steps), "higher_is_better": True,
+        "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic", "config": config_dict(cfg, args, 1),
+        "cpu_baseline": {"value": val, "unit": "paths/s", "cores": cores, "kind": "port", "sample": sample},
+        "e2e": {"value": val, "unit": "paths/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }))
+
+
+class _DevArray:
+    """Zero-copy view of ctx-owned device memory for torch (NCCL reduce operates on the film buffer in place)."""
+
+    def __init__(self, ptr, n, typestr="<f8"):
+        self.__cuda_array_interface__ = {"shape": (n,), "typestr": typestr, "data": (ptr, False), "version": 2}
+
+
+def input_bytes(cfg):
+    """Host->device bytes of one vspg_set_scene + vspg_set_guiding (what the e2e timed region copies)."""
+    import ctypes as C
+    from pyvspg import _abi as A
+    n = 0
+    d = cfg.scene.desc
+    for i in range(d.n_media):
+        m = d.media[i]
+        nv = m.nx * m.ny * m.nz
+        if m.type == A.MEDIUM_GRID:
+            n += nv * 4 + 16 ** 3 * 4
+        elif m.type == A.MEDIUM_RGBGRID:
+            n += nv * 24 + 16 ** 3 * 4
+    n += d.n_quads * C.sizeof(A.Quad) + d.n_lights * C.sizeof(A.Light) + d.n_materials * C.sizeof(A.Material)
+    g = cfg.guiding
+    if g is not None:
+        for f in g.fields.values():
+            n += f.n_regions * (C.sizeof(A.Mixture) + C.sizeof(A.Neighbours)) + f.n_nodes * C.sizeof(A.KdNode)
+        if getattr(g, "isg", None) is not None:
+            n += g.isg.nbytes
+        if getattr(g, "tr", None) is not None:
+            n += g.tr.nbytes
+    return n
+
+
+def run_b200(args):
+    import numpy as np
+    import torch
+    import torch.distributed as dist
+    from pyvspg import api
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise RuntimeError("bench.py: no CUDA device; the render pass has no CPU fallback (use --impl reference for the CPU arm)")
+    torch.cuda.set_device(local)
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    cfg, b_q = build_config(args)
+    ctx = api.Context(local)
+    if args.capacity:
+        ctx.set_capacity(args.capacity)
+    ctx.set_scene(cfg.scene)
+    ctx.set_guiding(cfg.guiding)
+    ctx.set_integrator(cfg.ip)
+    stream = torch.cuda.current_stream().cuda_stream
+    fptr, fn = ctx.film_device_ptr()
+    film_t = torch.as_tensor(_DevArray(fptr, fn), device=f"cuda:{local}")
+    W, Hh, spp = cfg.width, cfg.height, cfg.spp
+    paths_per_step = W * Hh * spp * world
+
+    def step(seed):
+        # rank r renders sample indices r, r+world, ... of a (spp*world)-spp render; film reduced onto rank 0
+        ctx.film_clear()
+        ctx.render(rank, spp * world, spp_stride=world, seed=seed, stream=stream)
+        if world > 1:
+            dist.reduce(film_t, dst=0, op=dist.ReduceOp.SUM)
+
+    for i in range(args.warmup):
+        step(i)
+    barrier()
+    ctx.counters_reset()
+    ctx.kernel_stats(enable_timing=True)
+    clocks = ClockSampler(local)
+    clocks.start()
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    barrier()
+    ev0.record()
+    for i in range(args.steps):
+        step(100 + i)
+    ev1.record()
+    barrier()
+    clk = clocks.stop()
+    ms = torch.tensor([ev0.elapsed_time(ev1)], device=f"cuda:{local}", dtype=torch.float64)
+    if world > 1:
+        dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+    ms_total = float(ms.item())
+    cnt = ctx.counters()
+    ks = ctx.kernel_stats(enable_timing=False)
+    value = paths_per_step * args.steps / (ms_total * 1e-3)
+
+    # ---- e2e: host buffers -> C ABI -> host film, copies inside the timed region
+    h2d = input_bytes(cfg)
+    film_host = torch.empty((Hh, W, 4), dtype=torch.float64).pin_memory()
+    d2h = film_host.numel() * 8
+    e2e_steps = max(1, min(args.steps, 3))
+
+    def e2e_step(seed):
+        ctx.set_scene(cfg.scene)          # H2D: density grid(s), majorant grid, shapes, lights
+        ctx.set_guiding(cfg.guiding)      # H2D: guiding cache (KD nodes, mixtures, neighbour tables), ISG / Tr buffers
+        ctx.set_integrator(cfg.ip)
+        ctx.render(rank, spp * world, spp_stride=world, seed=seed, stream=stream)
+        if world > 1:
+            dist.reduce(film_t, dst=0, op=dist.ReduceOp.SUM)
+        ctx.film_download_to(film_host.data_ptr())   # D2H: fp64 film
+
+    e2e_step(7)
+    barrier()
+    t0 = time.perf_counter()
+    for i in range(e2e_steps):
+        e2e_step(200 + i)
+    barrier()
+    dt = torch.tensor([time.perf_counter() - t0], device=f"cuda:{local}", dtype=torch.float64)
+    if world > 1:
+        dist.all_reduce(dt, op=dist.ReduceOp.MAX)
+    e2e_value = paths_per_step * e2e_steps / float(dt.item())
+
+    if rank == 0:
+        # ---- roofline of the dominant kernel (by summed CUDA-event time)
+        names = [k for k in ks if k != "ms_total"]
+        dom = max(names, key=lambda k: ks[k]["ms"])
+        tracked = dom if ks[dom]["density_queries"] else max(("medium", "shadow"), key=lambda k: ks[k]["ms"])
+        kk = ks[tracked]
+        alg_bytes = kk["density_queries"] * b_q + kk["dda_steps"] * 4
+        peaks_path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+        if os.path.exists(peaks_path):
+            peak, peak_src = json.load(open(peaks_path))["hbm_gbs"], "measured (MEASURED_PEAKS.json hbm_gbs, burst copy)"
+        else:
+            peak, peak_src = 6650.0, "fallback (B200_PROFILING.md)"
+        achieved = alg_bytes / max(kk["ms"] * 1e-3, 1e-12) / 1e9 if kk["launches"] else 0.0
+        per_launch_ms = kk["ms"] / max(1, kk["launches"])
+        roofline = {
+            "bound": "hbm", "kernel": "k_" + tracked, "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
+            "traffic": None, "peak_source": peak_src,
+            "algorithmic_bytes_per_launch": alg_bytes / max(1, kk["launches"]), "avg_launch_ms": per_launch_ms,
+            "bytes_per_query": b_q, "queries": kk["density_queries"], "dda_steps": kk["dda_steps"],
+            "kernel_ms_share": {k: round(ks[k]["ms"] / max(1e-9, sum(ks[n]["ms"] for n in names)), 4) for k in names},
+            "kernel_ms_sum": sum(ks[n]["ms"] for n in names), "timed_region_ms": ms_total,
+        }
+        cpu = None
+        if not args.no_cpu_baseline and world == 1:
+            v1, cores, dt1, _ = cpu_oracle_paths_per_s(cfg, 1)
+            cspp = args.cpu_spp or max(1, min(spp, int(15.0 / max(dt1, 1e-3))))
+            v, cores, dtc, n = cpu_oracle_paths_per_s(cfg, cspp, seed=1)
+            cpu = {"value": v, "unit": "paths/s", "cores": cores, "kind": "port",
+                   "sample": f"{W}x{Hh} x {cspp} spp of the {spp}-spp workload ({n} paths, {dtc:.1f} s); oracle/liboracle.so "
+                             "(CPU restatement of the reference integrator), all host threads"}
+        out = {
+            "metric": "paths/sec (guidedvolpathvspg render pass)", "value": value, "unit": "paths/s", "n_gpus": world, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": ms_total / args.steps, "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "f32", "data": "synthetic", "config": config_dict(cfg, args, world),
+            "e2e": {"value": e2e_value, "unit": "paths/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h, "steps": e2e_steps},
+            "gpu_launches": cnt["kernel_launches"], "clocks": clk, "roofline": roofline, "cpu_baseline": cpu,
+            "counters": {k: cnt[k] for k in ("paths", "density_queries", "dda_steps", "cache_lookups", "bvh_nodes", "shadow_rays", "wave_iterations")},
+            "mean_radiance": float(film_host[..., :3].sum() / max(1.0, float(film_host[..., 3].sum()))),
+        }
+        print(json.dumps(out))
+    ctx.close()
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def main():
+    args = parse_args()
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_b200(args)
+
+
+if __name__ == "__main__":
+    main()

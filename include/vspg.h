@@ -262,9 +262,21 @@ int vspg_film_download(vspg_ctx *ctx, double *host_rgbw);           /* H*W*4 dou
 int vspg_film_resolve(vspg_ctx *ctx, float *host_rgb);              /* H*W*3 rgb/weight  */
 int vspg_counters_get(vspg_ctx *ctx, vspg_counters *out);
 int vspg_counters_reset(vspg_ctx *ctx);
-/* average device time (ms) and launch count of the medium-tracking kernel since reset */
-int vspg_kernel_times(vspg_ctx *ctx, int enable, float *ms_medium, float *ms_total,
-                      unsigned long long *launches_medium);
+/* Per-kernel device time (CUDA events on the render stream), launch counts and the grid traffic counters of the
+ * two tracking kernels, accumulated since the last vspg_counters_reset.  Timing is recorded only while enabled
+ * (`enable_timing` sets the mode for subsequent vspg_render calls and returns what has been gathered so far). */
+enum {
+    VSPG_K_GENERATE = 0, VSPG_K_INTERSECT = 1, VSPG_K_MEDIUM = 2, VSPG_K_VOLSCATTER = 3, VSPG_K_SURFACE = 4,
+    VSPG_K_SHADE = 5, VSPG_K_SHADOW = 6, VSPG_K_FINISH = 7, VSPG_K_COUNT = 8
+};
+typedef struct vspg_kernel_stats {
+    float ms[VSPG_K_COUNT];                          /* summed device time per kernel                    */
+    unsigned long long launches[VSPG_K_COUNT];
+    unsigned long long density_queries[VSPG_K_COUNT]; /* Q issued by that kernel (MEDIUM and SHADOW only) */
+    unsigned long long dda_steps[VSPG_K_COUNT];       /* S issued by that kernel (MEDIUM and SHADOW only) */
+    float ms_total;                                  /* first launch to last kernel end, summed over renders */
+} vspg_kernel_stats;
+int vspg_kernel_stats_get(vspg_ctx *ctx, int enable_timing, vspg_kernel_stats *out);
 
 /* -------------------------------------------------- host front end (C++ side) */
 /* Scene handle produced by the .pbrt front end (parser.cpp / scene.cpp subset).

@@ -126,7 +126,8 @@ struct Wavefront {
     int *cursors;                      // per-kernel dynamic work cursors
 };
 
-enum { CNT_PATHS = 0, CNT_QUERIES = 1, CNT_DDA = 2, CNT_LOOKUPS = 3, CNT_BVH = 4, CNT_SHADOW = 5 };
+// CNT_QUERIES / CNT_DDA: issued by the SampleDistance kernel; *_SH: issued by the shadow-ray kernel
+enum { CNT_PATHS = 0, CNT_QUERIES = 1, CNT_DDA = 2, CNT_LOOKUPS = 3, CNT_BVH = 4, CNT_SHADOW = 5, CNT_QUERIES_SH = 6, CNT_DDA_SH = 7, CNT_COUNT = 8 };
 
 // ------------------------------------------------------------------ warp-aggregated queue push (ballot + popc prefix)
 VD void queue_push(const Queue &q, bool pred, int value) {

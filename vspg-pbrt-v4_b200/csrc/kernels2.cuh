@@ -203,8 +203,8 @@ __global__ void __launch_bounds__(kBlock) k_shadow(const DScene sc, const Wavefr
             W.P.rl_L[slot] = e;
         }
     }
-    counter_add(W.counters, CNT_QUERIES, tc.queries);
-    counter_add(W.counters, CNT_DDA, tc.dda);
+    counter_add(W.counters, CNT_QUERIES_SH, tc.queries);
+    counter_add(W.counters, CNT_DDA_SH, tc.dda);
     counter_add(W.counters, CNT_BVH, nodes);
 }
 

@@ -26,6 +26,7 @@ struct vspg_ctx {
     DScene sc{};
     bool have_scene = false;
     Wavefront W{};
+    Queue phys_q[2]{};            // the two ping-pong path queues (roles swap each wave iteration)
     int capacity = 0, requested_capacity = 0;
     int *qcounts = nullptr;       // device: 8 queue counters
     int *h_pinned = nullptr;      // pinned readback
@@ -34,11 +35,12 @@ struct vspg_ctx {
     unsigned long long launches = 0, iterations = 0;
     int film_w = 0, film_h = 0;
     int grid_layout = GRID_CELL8;
-    // timing
+    // timing (vspg_kernel_stats_get)
     bool timing = false;
-    cudaEvent_t ev0 = nullptr, ev1 = nullptr;
-    double ms_medium = 0, ms_total = 0;
-    unsigned long long launches_medium = 0;
+    cudaEvent_t ev[VSPG_K_COUNT + 1] = {};
+    double ms_kernel[VSPG_K_COUNT] = {};
+    unsigned long long launches_kernel[VSPG_K_COUNT] = {};
+    double ms_total = 0;
 };
 
 static std::string g_create_error;
@@ -109,8 +111,7 @@ void vspg_destroy(vspg_ctx *ctx) {
     cudaSetDevice(ctx->device);
     free_all(ctx->scene_allocs); free_all(ctx->guide_allocs); free_all(ctx->wf_allocs);
     if (ctx->h_pinned) cudaFreeHost(ctx->h_pinned);
-    if (ctx->ev0) cudaEventDestroy(ctx->ev0);
-    if (ctx->ev1) cudaEventDestroy(ctx->ev1);
+    for (auto e : ctx->ev) if (e) cudaEventDestroy(e);
     delete ctx;
 }
 

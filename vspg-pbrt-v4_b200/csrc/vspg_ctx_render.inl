@@ -27,6 +27,7 @@ static int ensure_wavefront(vspg_ctx *ctx, unsigned long long total) {
     CK(alloc((void **)&items, Q_COUNT * n * sizeof(int)));
     Queue *qs[Q_COUNT] = {&ctx->W.active, &ctx->W.next, &ctx->W.medium, &ctx->W.surface, &ctx->W.shade, &ctx->W.volscatter, &ctx->W.shadow, &ctx->W.done};
     for (int i = 0; i < Q_COUNT; i++) { qs[i]->items = items + (size_t)i * n; qs[i]->count = ctx->qcounts + i; }
+    ctx->phys_q[0] = ctx->W.active; ctx->phys_q[1] = ctx->W.next;
     CK(alloc((void **)&ctx->W.next_sample, sizeof(unsigned long long)));
     if (!ctx->h_pinned) CK(cudaMallocHost((void **)&ctx->h_pinned, 64));
     ctx->capacity = want;
@@ -60,34 +61,38 @@ int vspg_render(vspg_ctx *ctx, int spp_begin, int spp_end, int spp_stride, int x
     W.film = ctx->film; W.counters = ctx->counters;
     ctx->sc.seed = seed;
     const DScene sc = ctx->sc;
-    Queue *phys[2] = {nullptr, nullptr};
-    Queue qa = W.active, qb = W.next;   // physical queues 0 and 1; roles swap each iteration
-    (void)phys;
+    Queue qa = ctx->phys_q[0], qb = ctx->phys_q[1];   // physical queues 0 and 1; roles swap each iteration
     CK(cudaMemsetAsync(ctx->qcounts, 0, Q_COUNT * sizeof(int), st));
     CK(cudaMemsetAsync(W.next_sample, 0, sizeof(unsigned long long), st));
     const int grid = ctx->sm_count * 8;
     const bool guidedVol = sc.vol.present, guidedSurf = sc.surf.present;
     int nslots = (int)std::min<unsigned long long>((unsigned long long)ctx->capacity, total);
     W.active = qa; W.next = qb;
-    k_generate<<<grid, kBlock, 0, st>>>(sc, W, nslots);
-    ctx->launches++;
-    int cur = 0;  // physical index of the active queue
     const bool timing = ctx->timing;
-    if (timing && !ctx->ev0) { CK(cudaEventCreate(&ctx->ev0)); CK(cudaEventCreate(&ctx->ev1)); }
+    if (timing && !ctx->ev[0])
+        for (auto &e : ctx->ev) CK(cudaEventCreate(&e));
     cudaEvent_t evStart = nullptr, evStop = nullptr;
     if (timing) { CK(cudaEventCreate(&evStart)); CK(cudaEventCreate(&evStop)); CK(cudaEventRecord(evStart, st)); }
-    float msMedium = 0;
+    k_generate<<<grid, kBlock, 0, st>>>(sc, W, nslots);
+    ctx->launches++; ctx->launches_kernel[VSPG_K_GENERATE]++;
+    if (timing) {
+        CK(cudaEventRecord(ctx->ev[0], st)); CK(cudaEventSynchronize(ctx->ev[0]));
+        float ms = 0; CK(cudaEventElapsedTime(&ms, evStart, ctx->ev[0])); ctx->ms_kernel[VSPG_K_GENERATE] += ms;
+    }
+    int cur = 0;  // physical index of the active queue
+#define VSPG_STAGE(K, launch) do { launch; ctx->launches_kernel[K]++; if (timing) CK(cudaEventRecord(ctx->ev[K], st)); } while (0)
     while (true) {
-        k_intersect<<<grid, kBlock, 0, st>>>(sc, W);
-        if (timing) CK(cudaEventRecord(ctx->ev0, st));
-        k_medium<<<grid, kBlock, 0, st>>>(sc, W);
-        if (timing) CK(cudaEventRecord(ctx->ev1, st));
-        if (guidedVol) k_volscatter<true><<<grid, kBlock, 0, st>>>(sc, W); else k_volscatter<false><<<grid, kBlock, 0, st>>>(sc, W);
-        k_surface<<<grid, kBlock, 0, st>>>(sc, W);
-        if (guidedSurf) k_shade<true><<<grid, kBlock, 0, st>>>(sc, W); else k_shade<false><<<grid, kBlock, 0, st>>>(sc, W);
-        k_shadow<<<grid, kBlock, 0, st>>>(sc, W);
-        k_finish<<<grid, kBlock, 0, st>>>(sc, W);
-        ctx->launches += 7; ctx->iterations++; ctx->launches_medium++;
+        if (timing) CK(cudaEventRecord(ctx->ev[0], st));
+        VSPG_STAGE(VSPG_K_INTERSECT, (k_intersect<<<grid, kBlock, 0, st>>>(sc, W)));
+        VSPG_STAGE(VSPG_K_MEDIUM, (k_medium<<<grid, kBlock, 0, st>>>(sc, W)));
+        if (guidedVol) VSPG_STAGE(VSPG_K_VOLSCATTER, (k_volscatter<true><<<grid, kBlock, 0, st>>>(sc, W)));
+        else VSPG_STAGE(VSPG_K_VOLSCATTER, (k_volscatter<false><<<grid, kBlock, 0, st>>>(sc, W)));
+        VSPG_STAGE(VSPG_K_SURFACE, (k_surface<<<grid, kBlock, 0, st>>>(sc, W)));
+        if (guidedSurf) VSPG_STAGE(VSPG_K_SHADE, (k_shade<true><<<grid, kBlock, 0, st>>>(sc, W)));
+        else VSPG_STAGE(VSPG_K_SHADE, (k_shade<false><<<grid, kBlock, 0, st>>>(sc, W)));
+        VSPG_STAGE(VSPG_K_SHADOW, (k_shadow<<<grid, kBlock, 0, st>>>(sc, W)));
+        VSPG_STAGE(VSPG_K_FINISH, (k_finish<<<grid, kBlock, 0, st>>>(sc, W)));
+        ctx->launches += 7; ctx->iterations++;
         // swap roles: next becomes active; clear every other counter
         cur ^= 1;
         Queue t = W.active; W.active = W.next; W.next = t;
@@ -95,13 +100,18 @@ int vspg_render(vspg_ctx *ctx, int spp_begin, int spp_end, int spp_stride, int x
         k_reset_counts<<<1, 32, 0, st>>>(ctx->qcounts, Q_COUNT, cur);
         ctx->launches++;
         CK(cudaStreamSynchronize(st));
-        if (timing) { float ms = 0; CK(cudaEventElapsedTime(&ms, ctx->ev0, ctx->ev1)); msMedium += ms; }
+        if (timing)
+            for (int k = VSPG_K_INTERSECT; k < VSPG_K_COUNT; k++) {
+                float ms = 0; CK(cudaEventElapsedTime(&ms, ctx->ev[k == VSPG_K_INTERSECT ? 0 : k - 1], ctx->ev[k]));
+                ctx->ms_kernel[k] += ms;
+            }
         if (ctx->h_pinned[0] == 0) break;
     }
+#undef VSPG_STAGE
     if (timing) {
         CK(cudaEventRecord(evStop, st)); CK(cudaEventSynchronize(evStop));
         float ms = 0; CK(cudaEventElapsedTime(&ms, evStart, evStop));
-        ctx->ms_total += ms; ctx->ms_medium += msMedium;
+        ctx->ms_total += ms;
         cudaEventDestroy(evStart); cudaEventDestroy(evStop);
     }
     CK(cudaGetLastError());
@@ -143,9 +153,9 @@ int vspg_counters_get(vspg_ctx *ctx, vspg_counters *out) {
     memset(out, 0, sizeof *out);
     if (!ctx->counters) return VSPG_OK;
     CK(cudaSetDevice(ctx->device));
-    unsigned long long h[8];
+    unsigned long long h[CNT_COUNT];
     CK(cudaMemcpy(h, ctx->counters, sizeof h, cudaMemcpyDeviceToHost));
-    out->paths = h[CNT_PATHS]; out->density_queries = h[CNT_QUERIES]; out->dda_steps = h[CNT_DDA]; out->cache_lookups = h[CNT_LOOKUPS];
+    out->paths = h[CNT_PATHS]; out->density_queries = h[CNT_QUERIES] + h[CNT_QUERIES_SH]; out->dda_steps = h[CNT_DDA] + h[CNT_DDA_SH]; out->cache_lookups = h[CNT_LOOKUPS];
     out->bvh_nodes = h[CNT_BVH]; out->shadow_rays = h[CNT_SHADOW]; out->kernel_launches = ctx->launches; out->wave_iterations = ctx->iterations;
     return VSPG_OK;
 }
@@ -153,15 +163,24 @@ int vspg_counters_reset(vspg_ctx *ctx) {
     if (!ctx) return VSPG_ERR_INVALID;
     CK(cudaSetDevice(ctx->device));
     if (ctx->counters) CK(cudaMemset(ctx->counters, 0, 64));
-    ctx->launches = 0; ctx->iterations = 0; ctx->ms_medium = 0; ctx->ms_total = 0; ctx->launches_medium = 0;
+    ctx->launches = 0; ctx->iterations = 0; ctx->ms_total = 0;
+    for (int k = 0; k < VSPG_K_COUNT; k++) { ctx->ms_kernel[k] = 0; ctx->launches_kernel[k] = 0; }
     return VSPG_OK;
 }
-int vspg_kernel_times(vspg_ctx *ctx, int enable, float *ms_medium, float *ms_total, unsigned long long *launches_medium) {
+int vspg_kernel_stats_get(vspg_ctx *ctx, int enable_timing, vspg_kernel_stats *out) {
     if (!ctx) return VSPG_ERR_INVALID;
-    if (ms_medium) *ms_medium = (float)ctx->ms_medium;
-    if (ms_total) *ms_total = (float)ctx->ms_total;
-    if (launches_medium) *launches_medium = ctx->launches_medium;
-    ctx->timing = enable != 0;
+    ctx->timing = enable_timing != 0;
+    if (!out) return VSPG_OK;
+    memset(out, 0, sizeof *out);
+    for (int k = 0; k < VSPG_K_COUNT; k++) { out->ms[k] = (float)ctx->ms_kernel[k]; out->launches[k] = ctx->launches_kernel[k]; }
+    out->ms_total = (float)ctx->ms_total;
+    if (ctx->counters) {
+        CK(cudaSetDevice(ctx->device));
+        unsigned long long h[CNT_COUNT];
+        CK(cudaMemcpy(h, ctx->counters, sizeof h, cudaMemcpyDeviceToHost));
+        out->density_queries[VSPG_K_MEDIUM] = h[CNT_QUERIES]; out->dda_steps[VSPG_K_MEDIUM] = h[CNT_DDA];
+        out->density_queries[VSPG_K_SHADOW] = h[CNT_QUERIES_SH]; out->dda_steps[VSPG_K_SHADOW] = h[CNT_DDA_SH];
+    }
     return VSPG_OK;
 }
 

@@ -111,6 +111,14 @@ class Counters(C.Structure):
                 ("kernel_launches", C.c_ulonglong), ("wave_iterations", C.c_ulonglong)]
 
 
+class KernelStats(C.Structure):
+    _fields_ = [("ms", f32 * 8), ("launches", C.c_ulonglong * 8), ("density_queries", C.c_ulonglong * 8),
+                ("dda_steps", C.c_ulonglong * 8), ("ms_total", f32)]
+
+
+KERNEL_NAMES = ("generate", "intersect", "medium", "volscatter", "surface", "shade", "shadow", "finish")
+
+
 class Segment(C.Structure):
     _fields_ = [("t_min", f32), ("t_max", f32), ("sigma_maj", F3)]
 
@@ -154,7 +162,7 @@ SYMBOLS = {
     "vspg_film_resolve": (i32, [P, P]),
     "vspg_counters_get": (i32, [P, C.POINTER(Counters)]),
     "vspg_counters_reset": (i32, [P]),
-    "vspg_kernel_times": (i32, [P, i32, PF, PF, C.POINTER(C.c_ulonglong)]),
+    "vspg_kernel_stats_get": (i32, [P, i32, C.POINTER(KernelStats)]),
     "vspg_host_scene_parse": (i32, [C.c_char_p, C.POINTER(P), C.c_char_p, C.c_size_t]),
     "vspg_host_scene_parse_string": (i32, [C.c_char_p, C.c_char_p, C.POINTER(P), C.c_char_p, C.c_size_t]),
     "vspg_host_scene_free": (None, [P]),

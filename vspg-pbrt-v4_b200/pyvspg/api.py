@@ -115,10 +115,15 @@ class Context:
     def counters_reset(self):
         self._ck(lib().vspg_counters_reset(self._h))
 
-    def kernel_times(self, enable=True):
-        a, b, n = A.f32(), A.f32(), C.c_ulonglong()
-        self._ck(lib().vspg_kernel_times(self._h, int(enable), C.byref(a), C.byref(b), C.byref(n)))
-        return {"ms_medium": a.value, "ms_total": b.value, "launches_medium": n.value}
+    def kernel_stats(self, enable_timing=True):
+        """Per-kernel device ms / launches / grid-traffic counters since the last counters_reset()."""
+        st = A.KernelStats()
+        self._ck(lib().vspg_kernel_stats_get(self._h, int(enable_timing), C.byref(st)))
+        out = {"ms_total": st.ms_total}
+        for i, k in enumerate(A.KERNEL_NAMES):
+            out[k] = {"ms": st.ms[i], "launches": int(st.launches[i]), "density_queries": int(st.density_queries[i]),
+                      "dda_steps": int(st.dda_steps[i])}
+        return out
 
     # ---- per-kernel parity hooks
     def debug_majorant_segments(self, medium, rays7, max_segments=64):
