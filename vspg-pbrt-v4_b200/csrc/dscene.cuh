@@ -100,6 +100,7 @@ struct PathSoA {
     float4 *sh_pl;       // pLight xyz, nLight.x
     float4 *sh_ple;      // pLightErr xyz, nLight.y
     float *sh_nz;        // nLight.z
+    float2 *rs_pre;      // resampling pre-pass (media_sampleTMaj.h:153-164): sum of sigma_maj[ch]*dt, DDA steps(int)
 };
 
 // packed flags in d_med.w : bits 0-7 depth, 8-9 channel, 10 specularBounce, 11 anyNonSpecular, 12 lastVertexVolume
@@ -117,7 +118,7 @@ struct Queue { int *items; int *count; };
 struct Wavefront {
     PathSoA P;
     int capacity;
-    Queue active, next, medium, surface, shade, volscatter, shadow, done;
+    Queue active, next, medium, surface, shade, volscatter, shadow, done, medium_rs;
     unsigned long long *next_sample;   // regeneration cursor
     unsigned long long total_samples;
     int x0, y0, x1, y1, spp_begin, spp_stride, n_spp;

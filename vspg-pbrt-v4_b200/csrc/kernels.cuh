@@ -49,7 +49,26 @@ __global__ void __launch_bounds__(kBlock) k_intersect(const DScene sc, const Wav
         Hit h = scene_intersect(sc, o, d, inff(), nodes);
         W.P.hit[slot] = make_float4(h.t, h.u, h.v, __int_as_float(h.prim));
         bool toMedium = medium >= 0 && h.prim >= 0;  // vspg.cpp:318: rays escaping to infinity skip the medium
-        queue_push(W.medium, toMedium, slot);
+        // vspg.cpp:679 use_resampling: the persistent-lane kernel takes those, the generic kernel the rest
+        bool rs = toMedium && !sc.ip.vsp_sampling_nds && sc.media[medium].type != VSPG_MEDIUM_HOMOGENEOUS;
+        if (rs) {
+            // pre-pass of SampleT_maj_Resampling (media_sampleTMaj.h:153-164): total majorant optical depth of the
+            // hero channel along [0, tHit]; done here, one thread per ray, so the persistent walk kernel starts sampling
+            const int ch = PathFlags::unpack(__float_as_int(b.w)).channel;
+            Ray ray; ray.o = o; ray.medium = medium;
+            float tMax = h.t * length(d);
+            ray.d = normalize(d);
+            MajorantIterator pre = sample_ray(sc.media[medium], ray, tMax);
+            float totalLength = 0.f;
+            Segment seg;
+            while (pre.next(&seg)) {
+                if (seg.sigma_maj[ch] == 0) continue;
+                totalLength += seg.sigma_maj[ch] * (seg.tMax - seg.tMin);
+            }
+            W.P.rs_pre[slot] = make_float2(totalLength, __int_as_float((int)pre.steps));
+        }
+        queue_push(W.medium_rs, rs, slot);
+        queue_push(W.medium, toMedium && !rs, slot);
         queue_push(W.surface, !toMedium, slot);
     }
     counter_add(W.counters, CNT_BVH, nodes);

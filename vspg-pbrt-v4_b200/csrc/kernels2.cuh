@@ -1,6 +1,7 @@
 // Wavefront stage kernels, part 2: surface hit handling, BSDF shading, shadow rays, film.
 #pragma once
 #include "kernels.cuh"
+#include "kmedium_rs.cuh"
 
 namespace vspg {
 

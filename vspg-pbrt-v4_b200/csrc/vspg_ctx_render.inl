@@ -1,7 +1,8 @@
 // Wavefront allocation, the render loop (ImageTileIntegrator::Render re-expressed), film and counters.
 // (included by vspg_ctx.cu)
 
-enum { Q_A = 0, Q_B = 1, Q_MEDIUM = 2, Q_SURFACE = 3, Q_SHADE = 4, Q_VOLSCATTER = 5, Q_SHADOW = 6, Q_DONE = 7, Q_COUNT = 8 };
+enum { Q_A = 0, Q_B = 1, Q_MEDIUM = 2, Q_SURFACE = 3, Q_SHADE = 4, Q_VOLSCATTER = 5, Q_SHADOW = 6, Q_DONE = 7, Q_MEDIUM_RS = 8, Q_COUNT = 9,
+       Q_CURSORS = 4, Q_INTS = Q_COUNT + Q_CURSORS };  // + per-kernel dynamic work cursors
 
 static int ensure_wavefront(vspg_ctx *ctx, unsigned long long total) {
     int want = ctx->requested_capacity > 0 ? ctx->requested_capacity : (1 << 21);
@@ -22,10 +23,11 @@ static int ensure_wavefront(vspg_ctx *ctx, unsigned long long total) {
     for (auto pp : f4) CK(alloc((void **)pp, n * sizeof(float4)));
     CK(alloc((void **)&P.rng, n * sizeof(ulonglong2)));
     CK(alloc((void **)&P.sh_nz, n * sizeof(float)));
-    CK(alloc((void **)&ctx->qcounts, Q_COUNT * sizeof(int)));
+    CK(alloc((void **)&P.rs_pre, n * sizeof(float2)));
+    CK(alloc((void **)&ctx->qcounts, Q_INTS * sizeof(int)));
     int *items = nullptr;
     CK(alloc((void **)&items, Q_COUNT * n * sizeof(int)));
-    Queue *qs[Q_COUNT] = {&ctx->W.active, &ctx->W.next, &ctx->W.medium, &ctx->W.surface, &ctx->W.shade, &ctx->W.volscatter, &ctx->W.shadow, &ctx->W.done};
+    Queue *qs[Q_COUNT] = {&ctx->W.active, &ctx->W.next, &ctx->W.medium, &ctx->W.surface, &ctx->W.shade, &ctx->W.volscatter, &ctx->W.shadow, &ctx->W.done, &ctx->W.medium_rs};
     for (int i = 0; i < Q_COUNT; i++) { qs[i]->items = items + (size_t)i * n; qs[i]->count = ctx->qcounts + i; }
     ctx->phys_q[0] = ctx->W.active; ctx->phys_q[1] = ctx->W.next;
     CK(alloc((void **)&ctx->W.next_sample, sizeof(unsigned long long)));
@@ -62,7 +64,7 @@ int vspg_render(vspg_ctx *ctx, int spp_begin, int spp_end, int spp_stride, int x
     ctx->sc.seed = seed;
     const DScene sc = ctx->sc;
     Queue qa = ctx->phys_q[0], qb = ctx->phys_q[1];   // physical queues 0 and 1; roles swap each iteration
-    CK(cudaMemsetAsync(ctx->qcounts, 0, Q_COUNT * sizeof(int), st));
+    CK(cudaMemsetAsync(ctx->qcounts, 0, Q_INTS * sizeof(int), st));
     CK(cudaMemsetAsync(W.next_sample, 0, sizeof(unsigned long long), st));
     const int grid = ctx->sm_count * 8;
     const bool guidedVol = sc.vol.present, guidedSurf = sc.surf.present;
@@ -84,6 +86,7 @@ int vspg_render(vspg_ctx *ctx, int spp_begin, int spp_end, int spp_stride, int x
     while (true) {
         if (timing) CK(cudaEventRecord(ctx->ev[0], st));
         VSPG_STAGE(VSPG_K_INTERSECT, (k_intersect<<<grid, kBlock, 0, st>>>(sc, W)));
+        k_medium_rs<<<ctx->sm_count * 4, kBlock, 0, st>>>(sc, W, ctx->qcounts + Q_COUNT);
         VSPG_STAGE(VSPG_K_MEDIUM, (k_medium<<<grid, kBlock, 0, st>>>(sc, W)));
         if (guidedVol) VSPG_STAGE(VSPG_K_VOLSCATTER, (k_volscatter<true><<<grid, kBlock, 0, st>>>(sc, W)));
         else VSPG_STAGE(VSPG_K_VOLSCATTER, (k_volscatter<false><<<grid, kBlock, 0, st>>>(sc, W)));
@@ -92,12 +95,12 @@ int vspg_render(vspg_ctx *ctx, int spp_begin, int spp_end, int spp_stride, int x
         else VSPG_STAGE(VSPG_K_SHADE, (k_shade<false><<<grid, kBlock, 0, st>>>(sc, W)));
         VSPG_STAGE(VSPG_K_SHADOW, (k_shadow<<<grid, kBlock, 0, st>>>(sc, W)));
         VSPG_STAGE(VSPG_K_FINISH, (k_finish<<<grid, kBlock, 0, st>>>(sc, W)));
-        ctx->launches += 7; ctx->iterations++;
+        ctx->launches += 8; ctx->iterations++;
         // swap roles: next becomes active; clear every other counter
         cur ^= 1;
         Queue t = W.active; W.active = W.next; W.next = t;
         CK(cudaMemcpyAsync(ctx->h_pinned, W.active.count, sizeof(int), cudaMemcpyDeviceToHost, st));
-        k_reset_counts<<<1, 32, 0, st>>>(ctx->qcounts, Q_COUNT, cur);
+        k_reset_counts<<<1, 32, 0, st>>>(ctx->qcounts, Q_INTS, cur);
         ctx->launches++;
         CK(cudaStreamSynchronize(st));
         if (timing)
