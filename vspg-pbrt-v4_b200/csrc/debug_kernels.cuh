@@ -93,7 +93,7 @@ __global__ void __launch_bounds__(kBlock) k_debug_guided_sample(const DScene sc,
         unsigned lookups = 0;
         ScatterSample s;
         if (isSurface) {
-            GuidedBSDF<true> gb;
+            GuidedBSDF<32> gb;
             gb.enableGuiding = ip.surface_guiding; gb.enableScatterGuiding = ip.vsp_secondary_guiding; gb.ris = ip.surface_guiding_ris;
             V3 ns(I.n[0], I.n[1], I.n[2]);
             V3 dpdu, t2; coordinate_system(ns, &dpdu, &t2);
@@ -104,7 +104,7 @@ __global__ void __launch_bounds__(kBlock) k_debug_guided_sample(const DScene sc,
             O.pdf_wq = gb.pdf(wo, wq); O.vsp_wq = gb.vsp(wq);
             if (s.valid) { O.f[0] = s.f.x; O.f[1] = s.f.y; O.f[2] = s.f.z; }
         } else {
-            GuidedPhase<true> gp;
+            GuidedPhase<32> gp;
             gp.enableGuiding = ip.volume_guiding; gp.enableScatterGuiding = ip.vsp_secondary_guiding; gp.ris = ip.volume_guiding_ris;
             O.ok = gp.init(sc, I.g, p, -wo, v, lookups);
             O.region = O.ok ? gp.region : -1;

@@ -1,9 +1,10 @@
 // OpenPGL 0.7.0 (VSP branch) query side on the device: KD-tree walk, stochastic nearest-region pick and the
-// parallax-aware vMF mixture operations.  A mixture (<= 32 lobes) is spread over the 32 lanes of a warp: lane i
-// holds lobe i (the reference's SSE vector i/4, lane i%4), so every mixture op is one pass of lane-parallel math
-// plus a shuffle reduction that keeps the reference's summation order (per-SSE-lane accumulators over vectors,
-// then (l0+l1)+(l2+l3)).  All functions below must be called by a fully converged warp; scalar arguments and
-// results are warp-uniform.  Citations relative to /root/reference/src/ext/openpgl/openpgl unless noted.
+// parallax-aware vMF mixture operations.  A mixture (<= 32 lobes) is spread over the G lanes of a lane GROUP
+// (G = 8, 16 or 32, chosen per vertex from the region's lobe count so that 4*ceil(n/4) <= G; a warp serves 32/G
+// vertices at once): lane i of the group holds lobe i (the reference's SSE vector i/4, lane i%4), so every mixture
+// op is one pass of lane-parallel math plus a shuffle reduction that keeps the reference's summation order
+// (per-SSE-lane accumulators over vectors, then (l0+l1)+(l2+l3)).  The functions below must be called by all G
+// lanes of a group together; scalar arguments and results are group-uniform.  Citations relative to /root/reference/src/ext/openpgl/openpgl unless noted.
 #pragma once
 #include "dscene.cuh"
 
@@ -11,6 +12,14 @@ namespace vspg {
 
 constexpr unsigned kFull = 0xffffffffu;
 constexpr float kFltEps = 1.1920928955078125e-7f;
+
+template <int G> VD unsigned grp_mask() {
+    if (G == 32) return kFull;
+    return ((1u << (G & 31)) - 1u) << ((threadIdx.x & 31) & ~(G - 1));
+}
+template <int G> VD int grp_lane() { return threadIdx.x & (G - 1); }
+template <int G> VD float gshfl(float v, int src) { return __shfl_sync(grp_mask<G>(), v, src, G); }
+template <int G> VD float gshfl_xor(float v, int m) { return __shfl_xor_sync(grp_mask<G>(), v, m, G); }
 
 // third-party/embreeSrc/common/math/transcendental.h:333-384
 VD float pgl_exp(float v) {
@@ -116,18 +125,17 @@ struct Lobe { float w, k, mx, my, mz, nrm, e2k; };
 struct LiLobe : Lobe { float mc, dist, vspw; };
 
 // Sum over lobes in the reference's association.  `val` must be 0 on lanes >= 4*cnt.
-VD float mix_reduce(float val) {
+template <int G> VD float mix_reduce(float val, int cnt) {
     int l = threadIdx.x & 3;
-    float acc = __shfl_sync(kFull, val, l);
-#pragma unroll
-    for (int v = 1; v < 8; v++) acc += __shfl_sync(kFull, val, 4 * v + l);
-    float s = acc + __shfl_xor_sync(kFull, acc, 1);
-    return s + __shfl_xor_sync(kFull, s, 2);
+    float acc = gshfl<G>(val, l);
+    for (int v = 1; v < cnt; v++) acc += gshfl<G>(val, 4 * v + l);   // vectors >= cnt hold exact zeros
+    float s = acc + gshfl_xor<G>(acc, 1);
+    return s + gshfl_xor<G>(s, 2);
 }
 VD float dot_e(float ax, float ay, float az, float bx, float by, float bz) { return ax * bx + (ay * by + az * bz); }  // embree madd chain
 
-VD void mix_load(const vspg_mixture *m, LiLobe &L, int &n, V3 &pivot) {
-    int i = threadIdx.x & 31;
+template <int G> VD void mix_load(const vspg_mixture *m, LiLobe &L, int &n, V3 &pivot) {
+    int i = grp_lane<G>();
     L.w = __ldg(&m->weight[i]); L.k = __ldg(&m->kappa[i]);
     L.mx = __ldg(&m->mu_x[i]); L.my = __ldg(&m->mu_y[i]); L.mz = __ldg(&m->mu_z[i]);
     L.nrm = __ldg(&m->norm[i]); L.e2k = __ldg(&m->e_minus_2k[i]); L.mc = __ldg(&m->mean_cos[i]);
@@ -136,8 +144,8 @@ VD void mix_load(const vspg_mixture *m, LiLobe &L, int &n, V3 &pivot) {
     pivot = V3(__ldg(&m->pivot[0]), __ldg(&m->pivot[1]), __ldg(&m->pivot[2]));
 }
 // directional/vmm/ParallaxAwareVonMisesFisherMixture.h:1132-1155
-VD void mix_parallax_shift(LiLobe &L, int cnt, V3 s) {
-    int i = threadIdx.x & 31;
+template <int G> VD void mix_parallax_shift(LiLobe &L, int cnt, V3 s) {
+    int i = grp_lane<G>();
     if (i < 4 * cnt) {
         float px = L.mx * L.dist + s.x, py = L.my * L.dist + s.y, pz = L.mz * L.dist + s.z;
         float len = sqrtf(dot_e(px, py, pz, px, py, pz));
@@ -148,8 +156,9 @@ VD void mix_parallax_shift(LiLobe &L, int cnt, V3 s) {
     }
 }
 // :861-880
-VD float mix_pdf(const Lobe &L, int cnt, V3 d) {
-    int i = threadIdx.x & 31;
+// by value + noinline: 17 call sites per scatter kernel; inlining them blew the kernels past the instruction cache
+template <int G> __device__ __noinline__ float mix_pdf(Lobe L, int cnt, V3 d) {
+    int i = grp_lane<G>();
     float val = 0.f;
     if (i < 4 * cnt) {
         float cosTheta = dot_e(d.x, d.y, d.z, L.mx, L.my, L.mz);
@@ -157,11 +166,11 @@ VD float mix_pdf(const Lobe &L, int cnt, V3 d) {
         float eval = L.nrm * pgl_exp(L.k * cm1);
         val = L.w * eval;
     }
-    return mix_reduce(val);
+    return mix_reduce<G>(val, cnt);
 }
 // :1237-1258
-VD float mix_vsp(const LiLobe &L, int cnt, V3 d) {
-    int i = threadIdx.x & 31;
+template <int G> __device__ __noinline__ float mix_vsp(LiLobe L, int cnt, V3 d) {
+    int i = grp_lane<G>();
     float e = 0.f, ev = 0.f;
     if (i < 4 * cnt) {
         float cosTheta = dot_e(d.x, d.y, d.z, L.mx, L.my, L.mz);
@@ -169,12 +178,12 @@ VD float mix_vsp(const LiLobe &L, int cnt, V3 d) {
         e = L.w * L.nrm * pgl_exp(L.k * cm1);
         ev = L.vspw * e;
     }
-    float sv = mix_reduce(ev), sp = mix_reduce(e);
+    float sv = mix_reduce<G>(ev, cnt), sp = mix_reduce<G>(e, cnt);
     return sv / sp;
 }
 // :776-858 product(weight, meanDirection, kappa, normalization); returns the product integral
-VD float mix_product(Lobe &L, int n, int cnt, float _w, V3 md, float _k, float _n) {
-    int i = threadIdx.x & 31;
+template <int G> VD float mix_product(Lobe &L, int n, int cnt, float _w, V3 md, float _k, float _n) {
+    int i = grp_lane<G>();
     const float twoPi = 2.0f * kPi;
     float wv = 0.f;
     if (i < 4 * cnt) {
@@ -195,17 +204,17 @@ VD float mix_product(Lobe &L, int n, int cnt, float _w, V3 md, float _k, float _
         L.w = scale; L.k = nk; L.mx = nx; L.my = ny; L.mz = nz; L.nrm = nn; L.e2k = ne2k;
         wv = L.w;
     }
-    float integral = mix_reduce(wv);
+    float integral = mix_reduce<G>(wv, cnt);
     if (i < 4 * cnt) L.w /= integral;
     int rem = n % 4;
     if (rem > 0 && i >= 4 * (cnt - 1) + rem && i < 4 * cnt) { L.mx = 0; L.my = 0; L.mz = 1; L.k = 0; L.nrm = kInv4Pi; L.e2k = 1; }
     return integral;
 }
 // :970-1031 selectComponentSIMD + :1086-1129 sample.  s0 drives cos(theta), s1 picks the lobe and becomes phi.
-VD V3 mix_sample(const Lobe &L, int n, float s0, float s1) {
-    int lane = threadIdx.x & 31, l = lane & 3, base = lane & ~3;
-    float v0 = __shfl_sync(kFull, L.w, base), v1 = __shfl_sync(kFull, L.w, base + 1);
-    float v2 = __shfl_sync(kFull, L.w, base + 2), v3 = __shfl_sync(kFull, L.w, base + 3);
+template <int G> __device__ __noinline__ V3 mix_sample(Lobe L, int n, float s0, float s1) {
+    int lane = grp_lane<G>(), l = lane & 3, base = lane & ~3;
+    float v0 = gshfl<G>(L.w, base), v1 = gshfl<G>(L.w, base + 1);
+    float v2 = gshfl<G>(L.w, base + 2), v3 = gshfl<G>(L.w, base + 3);
     // openpgl_common.h:164-170 prefix sum inside one SSE vector
     float cdl = l == 0 ? v0 : (l == 1 ? v0 + v1 : (l == 2 ? (v1 + v2) + v0 : (v2 + v3) + (v0 + v1)));
     const float searched = s1;
@@ -213,14 +222,14 @@ VD V3 mix_sample(const Lobe &L, int n, float s0, float s1) {
     int quot = (n - 1) / 4, rem = (n - 1) % 4;
     int sv = 0;
     for (sv = 0; sv < 8; sv++) {
-        float cdf = __shfl_sync(kFull, cdl, 4 * sv + 3);
+        float cdf = gshfl<G>(cdl, 4 * sv + 3);
         if (sumWeights + cdf >= searched || sv >= quot) break;
         sumWeights += cdf;
     }
     if (sv > 7) sv = 7;
     const int maxSel = sv == quot ? rem + 1 : 4;
-    float cd0 = __shfl_sync(kFull, cdl, 4 * sv) + sumWeights, cd1 = __shfl_sync(kFull, cdl, 4 * sv + 1) + sumWeights;
-    float cd2 = __shfl_sync(kFull, cdl, 4 * sv + 2) + sumWeights, cd3 = __shfl_sync(kFull, cdl, 4 * sv + 3) + sumWeights;
+    float cd0 = gshfl<G>(cdl, 4 * sv) + sumWeights, cd1 = gshfl<G>(cdl, 4 * sv + 1) + sumWeights;
+    float cd2 = gshfl<G>(cdl, 4 * sv + 2) + sumWeights, cd3 = gshfl<G>(cdl, 4 * sv + 3) + sumWeights;
     // embree select_min(valid, v): lowest lane holding the minimum among valid lanes
     int sc = -1; float best = inff();
     if (cd0 >= searched && cd0 < best) { best = cd0; sc = 0; }
@@ -234,21 +243,21 @@ VD V3 mix_sample(const Lobe &L, int n, float s0, float s1) {
     float prev = sc == 1 ? cd0 : (sc == 2 ? cd1 : cd2);
     sumWeights = sc > 0 ? prev : sumWeights;
     int sel = 4 * sv + sc;
-    float cdfw = fmaxf(kFltEps, __shfl_sync(kFull, L.w, sel));
+    float cdfw = fmaxf(kFltEps, gshfl<G>(L.w, sel));
     s1 = fminf(1 - kFltEps, (searched - sumWeights) / cdfw);
-    float sK = __shfl_sync(kFull, L.k, sel), sE = __shfl_sync(kFull, L.e2k, sel);
-    V3 mu(__shfl_sync(kFull, L.mx, sel), __shfl_sync(kFull, L.my, sel), __shfl_sync(kFull, L.mz, sel));
+    float sK = gshfl<G>(L.k, sel), sE = gshfl<G>(L.e2k, sel);
+    V3 mu(gshfl<G>(L.mx, sel), gshfl<G>(L.my, sel), gshfl<G>(L.mz, sel));
     V3 dir(0, 0, 1);
     if (sK == 0.0f) {  // openpgl_common.h:330 squareToUniformSphere
         float z = 1.0f - 2.0f * s1;
         float r = sqrtf(fmaxf(0.f, (1.0f - z * z)));
-        float sp, cp; sincosf(2.0f * kPi * s0, &sp, &cp);
+        float sp, cp; sincospif(2.0f * s0, &sp, &cp);   // sincosf(2*pi*s0) up to the rounding of the product
         dir = V3(r * cp, r * sp, z);
     } else {
         float cosTheta = 1.f + (pgl_log(1.0f + ((sE - 1.f) * s0))) / sK;
         cosTheta = fminf(1.0f, fmaxf(cosTheta, -1.f));
         float sinTheta = sqrtf(1.f - cosTheta * cosTheta);
-        float sp, cp; sincosf(2.f * kPi * s1, &sp, &cp);
+        float sp, cp; sincospif(2.f * s1, &sp, &cp);    // sincosf(2*pi*s1) up to the rounding of the product
         dir = V3(sinTheta * cp, sinTheta * sp, cosTheta);
     }
     // embree::frame(N), linearspace3.h:117-124 (the CPU's rsqrtss+Newton normalise is replaced by an exact one)
@@ -263,6 +272,7 @@ VD V3 mix_sample(const Lobe &L, int n, float s0, float s1) {
 }
 
 // VMMSurfaceSamplingDistribution.h:37-101 / VMMVolumeSamplingDistribution.h:35-117,199-204
+template <int G>
 struct SamplingDist {
     LiLobe li;
     Lobe d0, d1, d2;
@@ -270,16 +280,16 @@ struct SamplingDist {
     int numDist, n, cnt;
 
     VD void init(const vspg_mixture *m, V3 samplePos) {
-        V3 pivot; mix_load(m, li, n, pivot);
+        V3 pivot; mix_load<G>(m, li, n, pivot);
         cnt = (n + 3) / 4;
-        mix_parallax_shift(li, cnt, pivot - samplePos);
+        mix_parallax_shift<G>(li, cnt, pivot - samplePos);
         d0 = li; w0 = 1.f; w1 = w2 = 0.f; numDist = 1;
     }
     VD void apply_cosine_product(V3 normal) {
         const float cosine_kappa = 2.18853f;
         // VMMSurfaceSamplingDistribution.h:55: 2.18853f/(2*pi*(1-exp(-2*2.18853f))) as the CPU evaluates it in float
         const float cosine_normalization = 0x1.69366ap-2f;
-        mix_product(d0, n, cnt, 1.0f, normal, cosine_kappa, cosine_normalization);
+        mix_product<G>(d0, n, cnt, 1.0f, normal, cosine_kappa, cosine_normalization);
     }
     VD void apply_hg_product(const DHGRow *table, V3 dir, float meanCosine) {
         const float stepSize = (0.99f - 0.f) / float(128);
@@ -287,9 +297,9 @@ struct SamplingDist {
         const DHGRow &pf = table[idx];
         float sumWeights = 0.f;
         int K = pf.K;
-        if (K > 0) { d0 = li; V3 od = meanCosine * pf.mc[0] > 0.f ? dir : -dir; w0 = mix_product(d0, n, cnt, pf.w[0], od, pf.kappa[0], pf.norm[0]); sumWeights += w0; }
-        if (K > 1) { d1 = li; V3 od = meanCosine * pf.mc[1] > 0.f ? dir : -dir; w1 = mix_product(d1, n, cnt, pf.w[1], od, pf.kappa[1], pf.norm[1]); sumWeights += w1; }
-        if (K > 2) { d2 = li; V3 od = meanCosine * pf.mc[2] > 0.f ? dir : -dir; w2 = mix_product(d2, n, cnt, pf.w[2], od, pf.kappa[2], pf.norm[2]); sumWeights += w2; }
+        if (K > 0) { d0 = li; V3 od = meanCosine * pf.mc[0] > 0.f ? dir : -dir; w0 = mix_product<G>(d0, n, cnt, pf.w[0], od, pf.kappa[0], pf.norm[0]); sumWeights += w0; }
+        if (K > 1) { d1 = li; V3 od = meanCosine * pf.mc[1] > 0.f ? dir : -dir; w1 = mix_product<G>(d1, n, cnt, pf.w[1], od, pf.kappa[1], pf.norm[1]); sumWeights += w1; }
+        if (K > 2) { d2 = li; V3 od = meanCosine * pf.mc[2] > 0.f ? dir : -dir; w2 = mix_product<G>(d2, n, cnt, pf.w[2], od, pf.kappa[2], pf.norm[2]); sumWeights += w2; }
         if (K > 0) w0 /= sumWeights;
         if (K > 1) w1 /= sumWeights;
         if (K > 2) w2 /= sumWeights;
@@ -297,9 +307,9 @@ struct SamplingDist {
     }
     VD float pdf(V3 d) const {
         float p = 0.f;
-        if (numDist > 0) p += w0 * mix_pdf(d0, cnt, d);
-        if (numDist > 1) p += w1 * mix_pdf(d1, cnt, d);
-        if (numDist > 2) p += w2 * mix_pdf(d2, cnt, d);
+        if (numDist > 0) p += w0 * mix_pdf<G>(d0, cnt, d);
+        if (numDist > 1) p += w1 * mix_pdf<G>(d1, cnt, d);
+        if (numDist > 2) p += w2 * mix_pdf<G>(d2, cnt, d);
         return p;
     }
     VD V3 sample(float sx, float sy) const {
@@ -312,13 +322,12 @@ struct SamplingDist {
         }
         float wsel = i == 0 ? w0 : (i == 1 ? w1 : w2);
         float s0 = (sx - weight) / wsel;
-        if (i == 0) return mix_sample(d0, n, s0, sy);
-        if (i == 1) return mix_sample(d1, n, s0, sy);
-        return mix_sample(d2, n, s0, sy);
+        Lobe L = i == 0 ? d0 : (i == 1 ? d1 : d2);
+        return mix_sample<G>(L, n, s0, sy);
     }
     VD float sample_pdf(float sx, float sy, V3 *dir) const { *dir = sample(sx, sy); return pdf(*dir); }
-    VD float pdf_li(V3 d) const { return mix_pdf(li, cnt, d); }
-    VD float vsp(V3 d) const { return mix_vsp(li, cnt, d); }
+    VD float pdf_li(V3 d) const { return mix_pdf<G>(li, cnt, d); }
+    VD float vsp(V3 d) const { return mix_vsp<G>(li, cnt, d); }
 };
 
 }  // namespace vspg

@@ -114,8 +114,12 @@ struct Frame {
     VD V3 to_local(V3 v) const { return V3(dot(v, x), dot(v, y), dot(v, z)); }
     VD V3 from_local(V3 v) const { return v.x * x + v.y * y + v.z * z; }
 };
-VD V3 spherical_direction(float sinTheta, float cosTheta, float phi) {
-    return V3(clampf(sinTheta, -1, 1) * cosf(phi), clampf(sinTheta, -1, 1) * sinf(phi), clampf(cosTheta, -1, 1));
+// util/vecmath.h SphericalDirection with phi = 2*pi*u.  sin/cos are taken as sincospi(2u): the same angle up to the
+// float rounding of the product 2*pi*u (<= 4e-7 rad), without dragging libdevice's large-argument reduction into
+// every scatter kernel (it was 470 SASS instructions per call site).
+VD V3 spherical_direction_2pi(float sinTheta, float cosTheta, float u) {
+    float sp, cp; sincospif(2.f * u, &sp, &cp);
+    return V3(clampf(sinTheta, -1, 1) * cp, clampf(sinTheta, -1, 1) * sp, clampf(cosTheta, -1, 1));
 }
 
 // ------------------------------------------------------------------ hashing / RNG (integer: bit-exact)
@@ -192,9 +196,8 @@ VD V3 sample_henyey_greenstein(V3 wo, float g, float u0, float u1, float *pdf) {
     if (fabsf(g) < 1e-3f) cosTheta = 1 - 2 * u0;
     else cosTheta = -1 / (2 * g) * (1 + sqr(g) - sqr((1 - sqr(g)) / (1 + g - 2 * g * u0)));
     float sinTheta = safe_sqrt(1 - sqr(cosTheta));
-    float phi = 2 * kPi * u1;
     Frame wFrame = Frame::from_z(wo);
-    V3 wi = wFrame.from_local(spherical_direction(sinTheta, cosTheta, phi));
+    V3 wi = wFrame.from_local(spherical_direction_2pi(sinTheta, cosTheta, u1));
     *pdf = henyey_greenstein(cosTheta, g);
     return wi;
 }

@@ -100,6 +100,7 @@ struct PathSoA {
     float4 *sh_pl;       // pLight xyz, nLight.x
     float4 *sh_ple;      // pLightErr xyz, nLight.y
     float *sh_nz;        // nLight.z
+    int *lk;             // guiding-cache region chosen by k_lookup for the pending scatter vertex (-1 = none)
     float2 *rs_pre;      // resampling pre-pass (media_sampleTMaj.h:153-164): sum of sigma_maj[ch]*dt, DDA steps(int)
 };
 
@@ -118,7 +119,7 @@ struct Queue { int *items; int *count; };
 struct Wavefront {
     PathSoA P;
     int capacity;
-    Queue active, next, medium, surface, shade, volscatter, shadow, done, medium_rs;
+    Queue active, next, medium, surface, shade, volscatter, shadow, done, medium_rs, vol8, vol16, vol32, sh8, sh16, sh32;
     unsigned long long *next_sample;   // regeneration cursor
     unsigned long long total_samples;
     int x0, y0, x1, y1, spp_begin, spp_stride, n_spp;

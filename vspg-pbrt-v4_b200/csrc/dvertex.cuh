@@ -1,7 +1,8 @@
 // Scatter-vertex work: light sampling (NEE set-up), GuidedPhaseFunction / GuidedBSDF (cpu/guiding.h:57-638) and the
-// shadow-ray record.  Templated on GUIDED: when a guiding field is loaded the caller runs one WARP per vertex (all
-// lanes execute this code on identical scalars, the vMF mixtures are spread over the lanes); without a field the
-// caller runs one THREAD per vertex and every mixture op is compiled out.
+// shadow-ray record.  Templated on the lane-group width G: G = 8/16/32 when a guiding field is loaded -- the caller
+// runs one lane GROUP per vertex (all lanes of the group execute this code on identical scalars, the vMF mixture is
+// spread over the group's lanes, see dguiding.cuh); G = 0 without a field -- one THREAD per vertex and every
+// mixture op compiled out.
 #pragma once
 #include "dguiding.cuh"
 #include "dpath.cuh"
@@ -104,11 +105,12 @@ VD float area_pdf_li(const DScene &sc, int light, V3 ctxP, V3 wi, const SurfaceI
 struct ScatterSample { bool valid; V3 f; V3 wi; float pdf, scatPdf, misPdf; };  // surface: f; volume: f.x = p
 
 // ------------------------------------------------------------------ GuidedPhaseFunction (cpu/guiding.h:360-638)
-template <bool GUIDED>
+template <int G>
 struct GuidedPhase {
+    static constexpr bool GUIDED = G > 0;
     bool enableGuiding, enableScatterGuiding, ris;
     bool useGuiding, useScatterGuiding;
-    SamplingDist dist;
+    SamplingDist<GUIDED ? G : 32> dist;
     float g;
     int region;
 
@@ -119,15 +121,12 @@ struct GuidedPhase {
         s.valid = true; s.f = V3(pdf, 0, 0); s.pdf = s.scatPdf = s.misPdf = pdf;
         return s;
     }
-    // :383-398; `wo` is ray.d at the call site (vspg.cpp:810)
-    VD bool init(const DScene &sc, float g_, V3 pos, V3 wo, float &rnd, unsigned &lookups) {
+    // :383-398; `wo` is ray.d at the call site (vspg.cpp:810).  `r` = region chosen by Field::getRegion (k_lookup), -1 = none
+    VD bool init_region(const DScene &sc, float g_, V3 pos, V3 wo, int r) {
         g = g_; region = -1;
         bool success = false;
         if (GUIDED) {
-            int leaf;
-            int r = field_get_region(sc.vol, pos, &rnd, &leaf);
-            if (leaf >= 0) lookups++;
-            if (r >= 0 && __ldg(&sc.vol.regions[r].valid)) {
+            if (r >= 0) {
                 dist.init(&sc.vol.regions[r], pos);
                 region = r;
                 dist.apply_hg_product(sc.hg_table, wo, g);
@@ -137,6 +136,16 @@ struct GuidedPhase {
         useGuiding = enableGuiding ? success : false;
         useScatterGuiding = enableScatterGuiding ? success : false;
         return success;
+    }
+    VD bool init(const DScene &sc, float g_, V3 pos, V3 wo, float &rnd, unsigned &lookups) {
+        int r = -1;
+        if (GUIDED) {
+            int leaf;
+            r = field_get_region(sc.vol, pos, &rnd, &leaf);
+            if (leaf >= 0) lookups++;
+            if (r >= 0 && !__ldg(&sc.vol.regions[r].valid)) r = -1;
+        }
+        return init_region(sc, g_, pos, wo, r);
     }
     VD float pdf(V3 wo, V3 wi) const {  // :542-558
         float ph = p(wo, wi);
@@ -203,11 +212,12 @@ struct GuidedPhase {
 };
 
 // ------------------------------------------------------------------ GuidedBSDF over DiffuseBxDF (cpu/guiding.h:57-358)
-template <bool GUIDED>
+template <int G>
 struct GuidedBSDF {
+    static constexpr bool GUIDED = G > 0;
     bool enableGuiding, enableScatterGuiding, ris;
     bool useGuiding, useScatterGuiding;
-    SamplingDist dist;
+    SamplingDist<GUIDED ? G : 32> dist;
     Frame frame; V3 R; bool hasR;
     int region;
 
@@ -237,13 +247,11 @@ struct GuidedBSDF {
         s.valid = true; s.f = fv; s.wi = frame.from_local(wi); s.pdf = s.scatPdf = s.misPdf = pdf;
         return s;
     }
-    VD bool init(const DScene &sc, V3 p, V3 rayD, V3 ns, float &rnd, unsigned &lookups) {  // :83-109
+    // :83-109.  `r` = region chosen by Field::getRegion (k_lookup), -1 = none / specular-only BSDF
+    VD bool init_region(const DScene &sc, V3 p, V3 rayD, V3 ns, int r) {
         bool success = false; region = -1;
         if (GUIDED && non_specular()) {
-            int leaf;
-            int r = field_get_region(sc.surf, p, &rnd, &leaf);
-            if (leaf >= 0) lookups++;
-            if (r >= 0 && __ldg(&sc.surf.regions[r].valid)) {
+            if (r >= 0) {
                 dist.init(&sc.surf.regions[r], p);
                 region = r;
                 V3 n = ns;
@@ -255,6 +263,16 @@ struct GuidedBSDF {
         useGuiding = enableGuiding ? success : false;
         useScatterGuiding = enableScatterGuiding ? success : false;
         return success;
+    }
+    VD bool init(const DScene &sc, V3 p, V3 rayD, V3 ns, float &rnd, unsigned &lookups) {
+        int r = -1;
+        if (GUIDED && non_specular()) {
+            int leaf;
+            r = field_get_region(sc.surf, p, &rnd, &leaf);
+            if (leaf >= 0) lookups++;
+            if (r >= 0 && !__ldg(&sc.surf.regions[r].valid)) r = -1;
+        }
+        return init_region(sc, p, rayD, ns, r);
     }
     VD float pdf(V3 wo, V3 wi) const {  // :271-289
         float b = bsdf_pdf(wo, wi);

@@ -123,22 +123,74 @@ VD void spawn_ray_to(V3 pf_, V3 pfErr, V3 nf, V3 pLight, V3 pLightErr, V3 nLight
 }
 
 // ------------------------------------------------------------------ volume scatter vertex (vspg.cpp:804-875 / 988-1058)
-template <bool GUIDED>
-__global__ void __launch_bounds__(kBlock) k_volscatter(const DScene sc, const Wavefront W) {
-    const int n = *W.volscatter.count;
-    const int first = GUIDED ? (gtid() >> 5) : gtid(), step = GUIDED ? (gstride() >> 5) : gstride();
-    const bool leader = GUIDED ? ((threadIdx.x & 31) == 0) : true;
+// Lane-group scheduling shared by the two scatter-vertex kernels: G = 0 -> one thread per vertex; G = 8/16/32 ->
+// one G-lane group per vertex (32/G vertices per warp).  The warp iterates uniformly; a group whose item index is
+// past the end re-runs the warp's first item with every side effect suppressed (`live` false) so that the
+// group-mask shuffles of the mixture code stay well-formed.
+template <int G> struct GroupIter {
+    static constexpr int W = G > 0 ? G : 1;        // lanes per vertex
+    int first, step, sub; bool leader;
+    VD GroupIter() {
+        if (G > 0) { first = (gtid() >> 5) * (32 / W); step = (gstride() >> 5) * (32 / W); sub = (threadIdx.x & 31) / W; leader = (threadIdx.x & (W - 1)) == 0; }
+        else { first = gtid(); step = gstride(); sub = 0; leader = true; }
+    }
+};
+
+// ------------------------------------------------------------------ Field::getRegion for a whole stage queue
+// (field/Field.h:114-150; guiding.h:83-109 / 383-398 front half).  One THREAD per vertex: draws the sampler's `v`,
+// walks the KD tree, picks the stochastic neighbour, and sorts the vertex into the queue of the lane-group width its
+// mixture needs (<= 8 lobes -> G8, <= 16 -> G16, else G32; vertices without a usable region go to G8).
+template <bool SURFACE>
+__global__ void __launch_bounds__(kBlock) k_lookup(const DScene sc, const Wavefront W, const Queue in, const Queue q8, const Queue q16, const Queue q32) {
+    const int n = *in.count;
+    unsigned lookups = 0;
+    for (int i = gtid(); i < n; i += gstride()) {
+        int slot = in.items[i];
+        ulonglong2 q = W.P.rng[slot];
+        Rng rng; rng.state = q.x; rng.inc = q.y;
+        float v = rng.uniform();
+        W.P.rng[slot] = make_ulonglong2(rng.state, rng.inc);
+        V3 p; bool want = true;
+        if (SURFACE) {
+            float4 a = W.P.o_dx[slot], b = W.P.d_med[slot], hr = W.P.hit[slot];
+            p = V3(a.x, a.y, a.z) + hr.x * V3(a.w, b.x, b.y);
+            const DQuad &Q = sc.quads[__float_as_int(hr.w)];
+            want = nonzero(ld3(sc.materials[Q.material].reflectance));   // GuidedBSDF::init only looks up for non-specular BSDFs
+        } else { float4 e = W.P.ev[slot]; p = V3(e.x, e.y, e.z); }
+        const DField &f = SURFACE ? sc.surf : sc.vol;
+        int r = -1, nl = 0;
+        if (want) {
+            int leaf;
+            r = field_get_region(f, p, &v, &leaf);
+            if (leaf >= 0) lookups++;
+            if (r >= 0) { if (__ldg(&f.regions[r].valid)) nl = __ldg(&f.regions[r].num_components); else r = -1; }
+        }
+        W.P.lk[slot] = r;
+        queue_push(q8, nl <= 8, slot);
+        queue_push(q16, nl > 8 && nl <= 16, slot);
+        queue_push(q32, nl > 16, slot);
+    }
+    counter_add(W.counters, CNT_LOOKUPS, lookups);
+}
+
+// ------------------------------------------------------------------ volume scatter vertex (vspg.cpp:804-875 / 988-1058)
+template <int G>
+__global__ void __launch_bounds__(kBlock) k_volscatter(const DScene sc, const Wavefront W, const Queue in) {
+    const int n = *in.count;
+    const GroupIter<G> gi;
+    const bool leader = gi.leader;
     unsigned lookups = 0, shadows = 0;
-    for (int i = first; i < n; i += step) {
-        int slot = W.volscatter.items[i];
+    for (int i0 = gi.first; i0 < n; i0 += gi.step) {
+        const bool live = i0 + gi.sub < n;
+        int slot = in.items[live ? i0 + gi.sub : i0];
         PathRegs ps; path_load(W.P, slot, ps);
         float4 e = W.P.ev[slot];
         V3 p(e.x, e.y, e.z);
         const vspg_integrator_params &ip = sc.ip;
-        GuidedPhase<GUIDED> gphase;
+        GuidedPhase<G> gphase;
         gphase.enableGuiding = ip.volume_guiding; gphase.enableScatterGuiding = ip.vsp_secondary_guiding; gphase.ris = ip.volume_guiding_ris;
-        float v = ps.rng.uniform();
-        gphase.init(sc, e.w, p, ps.ray.d, v, lookups);
+        if (G > 0) gphase.init_region(sc, e.w, p, ps.ray.d, W.P.lk[slot]);   // `v` was drawn by k_lookup
+        else { float v = ps.rng.uniform(); gphase.init(sc, e.w, p, ps.ray.d, v, lookups); }
         float survivalProb = 1.0f;
         if (ps.fl.depth > ip.min_rr_depth) {
             V3 rrw = (ps.beta / avg3(ps.r_u)) * ps.rr_correction;   // openpgl/cpp/RussianRoulette.h:32-35
@@ -165,7 +217,7 @@ __global__ void __launch_bounds__(kBlock) k_volscatter(const DScene sc, const Wa
                         sr.rl = ps.r_u * p_l; sr.ru = ps.r_u * scatterPDF;
                         sr.pLight = ls.pLight; sr.pLightErr = ls.pLightErr; sr.nLight = ls.nLight;
                         sr.delta = ls.delta; sr.channel = ps.fl.channel;
-                        if (leader) shadow_store(W.P, slot, sr);
+                        if (leader && live) shadow_store(W.P, slot, sr);
                         emitShadow = true;
                     }
                 }
@@ -191,13 +243,14 @@ __global__ void __launch_bounds__(kBlock) k_volscatter(const DScene sc, const Wa
                 ps.vsp_next = gphase.vsp(s.wi);
             }
         }
-        if (leader) {
+        const bool w = leader && live;
+        if (w) {
             path_store(W.P, slot, ps);
             if (emitShadow) shadows++;
         }
-        queue_push(W.shadow, leader && emitShadow, slot);
-        queue_push(W.next, leader && alive, slot);
-        queue_push(W.done, leader && !alive, slot);
+        queue_push(W.shadow, w && emitShadow, slot);
+        queue_push(W.next, w && alive, slot);
+        queue_push(W.done, w && !alive, slot);
     }
     if (leader) { counter_add(W.counters, CNT_LOOKUPS, lookups); counter_add(W.counters, CNT_SHADOW, shadows); }
 }

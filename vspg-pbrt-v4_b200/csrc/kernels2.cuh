@@ -59,24 +59,25 @@ __global__ void __launch_bounds__(kBlock) k_surface(const DScene sc, const Wavef
 }
 
 // ------------------------------------------------------------------ surface scatter vertex (vspg.cpp:448-607)
-template <bool GUIDED>
-__global__ void __launch_bounds__(kBlock) k_shade(const DScene sc, const Wavefront W) {
-    const int n = *W.shade.count;
-    const int first = GUIDED ? (gtid() >> 5) : gtid(), step = GUIDED ? (gstride() >> 5) : gstride();
-    const bool leader = GUIDED ? ((threadIdx.x & 31) == 0) : true;
+template <int G>
+__global__ void __launch_bounds__(kBlock) k_shade(const DScene sc, const Wavefront W, const Queue in) {
+    const int n = *in.count;
+    const GroupIter<G> gi;
+    const bool leader = gi.leader;
     const vspg_integrator_params &ip = sc.ip;
     unsigned lookups = 0, shadows = 0;
-    for (int i = first; i < n; i += step) {
-        int slot = W.shade.items[i];
+    for (int i0 = gi.first; i0 < n; i0 += gi.step) {
+        const bool live = i0 + gi.sub < n;
+        int slot = in.items[live ? i0 + gi.sub : i0];
         PathRegs ps; path_load(W.P, slot, ps);
         float4 hr = W.P.hit[slot];
         Hit h; h.t = hr.x; h.u = hr.y; h.v = hr.z; h.prim = __float_as_int(hr.w);
         SurfaceIntr isect = make_intr(sc, h, ps.ray.d, ps.ray.medium);
-        GuidedBSDF<GUIDED> gbsdf;
+        GuidedBSDF<G> gbsdf;
         gbsdf.enableGuiding = ip.surface_guiding; gbsdf.enableScatterGuiding = ip.vsp_secondary_guiding; gbsdf.ris = ip.surface_guiding_ris;
         gbsdf.set_bsdf(isect.ns, isect.dpdu, ld3(sc.materials[isect.material].reflectance));
-        float v = ps.rng.uniform();
-        gbsdf.init(sc, ps.ray.o + h.t * ps.ray.d, ps.ray.d, isect.ns, v, lookups);
+        if (G > 0) gbsdf.init_region(sc, ps.ray.o + h.t * ps.ray.d, ps.ray.d, isect.ns, W.P.lk[slot]);   // `v` was drawn by k_lookup
+        else { float v = ps.rng.uniform(); gbsdf.init(sc, ps.ray.o + h.t * ps.ray.d, ps.ray.d, isect.ns, v, lookups); }
         bool emitShadow = false;
         if (ip.use_nee && gbsdf.non_specular()) {
             V3 ctxP = offset_ray_origin(isect.p, isect.pError, isect.n, isect.wo);  // reflective-only BSDF (vspg.cpp:1147-1149)
@@ -99,7 +100,7 @@ __global__ void __launch_bounds__(kBlock) k_shade(const DScene sc, const Wavefro
                         sr.rl = ps.r_u * p_l; sr.ru = ps.r_u * scatterPDF;
                         sr.pLight = ls.pLight; sr.pLightErr = ls.pLightErr; sr.nLight = ls.nLight;
                         sr.delta = ls.delta; sr.channel = ps.fl.channel;
-                        if (leader) shadow_store(W.P, slot, sr);
+                        if (leader && live) shadow_store(W.P, slot, sr);
                         emitShadow = true;
                     }
                 }
@@ -137,13 +138,14 @@ __global__ void __launch_bounds__(kBlock) k_shade(const DScene sc, const Wavefro
                 else ps.beta = ps.beta / (1 - q);
             }
         }
-        if (leader) {
+        const bool w = leader && live;
+        if (w) {
             path_store(W.P, slot, ps);
             if (emitShadow) shadows++;
         }
-        queue_push(W.shadow, leader && emitShadow, slot);
-        queue_push(W.next, leader && alive, slot);
-        queue_push(W.done, leader && !alive, slot);
+        queue_push(W.shadow, w && emitShadow, slot);
+        queue_push(W.next, w && alive, slot);
+        queue_push(W.done, w && !alive, slot);
     }
     if (leader) { counter_add(W.counters, CNT_LOOKUPS, lookups); counter_add(W.counters, CNT_SHADOW, shadows); }
 }

@@ -1,7 +1,7 @@
 // Wavefront allocation, the render loop (ImageTileIntegrator::Render re-expressed), film and counters.
 // (included by vspg_ctx.cu)
 
-enum { Q_A = 0, Q_B = 1, Q_MEDIUM = 2, Q_SURFACE = 3, Q_SHADE = 4, Q_VOLSCATTER = 5, Q_SHADOW = 6, Q_DONE = 7, Q_MEDIUM_RS = 8, Q_COUNT = 9,
+enum { Q_A = 0, Q_B = 1, Q_MEDIUM = 2, Q_SURFACE = 3, Q_SHADE = 4, Q_VOLSCATTER = 5, Q_SHADOW = 6, Q_DONE = 7, Q_MEDIUM_RS = 8, Q_VOL8 = 9, Q_VOL16 = 10, Q_VOL32 = 11, Q_SH8 = 12, Q_SH16 = 13, Q_SH32 = 14, Q_COUNT = 15,
        Q_CURSORS = 4, Q_INTS = Q_COUNT + Q_CURSORS };  // + per-kernel dynamic work cursors
 
 static int ensure_wavefront(vspg_ctx *ctx, unsigned long long total) {
@@ -24,10 +24,12 @@ static int ensure_wavefront(vspg_ctx *ctx, unsigned long long total) {
     CK(alloc((void **)&P.rng, n * sizeof(ulonglong2)));
     CK(alloc((void **)&P.sh_nz, n * sizeof(float)));
     CK(alloc((void **)&P.rs_pre, n * sizeof(float2)));
+    CK(alloc((void **)&P.lk, n * sizeof(int)));
     CK(alloc((void **)&ctx->qcounts, Q_INTS * sizeof(int)));
     int *items = nullptr;
     CK(alloc((void **)&items, Q_COUNT * n * sizeof(int)));
-    Queue *qs[Q_COUNT] = {&ctx->W.active, &ctx->W.next, &ctx->W.medium, &ctx->W.surface, &ctx->W.shade, &ctx->W.volscatter, &ctx->W.shadow, &ctx->W.done, &ctx->W.medium_rs};
+    Queue *qs[Q_COUNT] = {&ctx->W.active, &ctx->W.next, &ctx->W.medium, &ctx->W.surface, &ctx->W.shade, &ctx->W.volscatter, &ctx->W.shadow, &ctx->W.done, &ctx->W.medium_rs,
+                          &ctx->W.vol8, &ctx->W.vol16, &ctx->W.vol32, &ctx->W.sh8, &ctx->W.sh16, &ctx->W.sh32};
     for (int i = 0; i < Q_COUNT; i++) { qs[i]->items = items + (size_t)i * n; qs[i]->count = ctx->qcounts + i; }
     ctx->phys_q[0] = ctx->W.active; ctx->phys_q[1] = ctx->W.next;
     CK(alloc((void **)&ctx->W.next_sample, sizeof(unsigned long long)));
@@ -88,11 +90,21 @@ int vspg_render(vspg_ctx *ctx, int spp_begin, int spp_end, int spp_stride, int x
         VSPG_STAGE(VSPG_K_INTERSECT, (k_intersect<<<grid, kBlock, 0, st>>>(sc, W)));
         k_medium_rs<<<ctx->sm_count * 4, kBlock, 0, st>>>(sc, W, ctx->qcounts + Q_COUNT);
         VSPG_STAGE(VSPG_K_MEDIUM, (k_medium<<<grid, kBlock, 0, st>>>(sc, W)));
-        if (guidedVol) VSPG_STAGE(VSPG_K_VOLSCATTER, (k_volscatter<true><<<grid, kBlock, 0, st>>>(sc, W)));
-        else VSPG_STAGE(VSPG_K_VOLSCATTER, (k_volscatter<false><<<grid, kBlock, 0, st>>>(sc, W)));
+        if (guidedVol) {
+            k_lookup<false><<<grid, kBlock, 0, st>>>(sc, W, W.volscatter, W.vol8, W.vol16, W.vol32);
+            k_volscatter<8><<<grid, kBlock, 0, st>>>(sc, W, W.vol8);
+            k_volscatter<16><<<grid, kBlock, 0, st>>>(sc, W, W.vol16);
+            VSPG_STAGE(VSPG_K_VOLSCATTER, (k_volscatter<32><<<grid, kBlock, 0, st>>>(sc, W, W.vol32)));
+            ctx->launches += 3;
+        } else VSPG_STAGE(VSPG_K_VOLSCATTER, (k_volscatter<0><<<grid, kBlock, 0, st>>>(sc, W, W.volscatter)));
         VSPG_STAGE(VSPG_K_SURFACE, (k_surface<<<grid, kBlock, 0, st>>>(sc, W)));
-        if (guidedSurf) VSPG_STAGE(VSPG_K_SHADE, (k_shade<true><<<grid, kBlock, 0, st>>>(sc, W)));
-        else VSPG_STAGE(VSPG_K_SHADE, (k_shade<false><<<grid, kBlock, 0, st>>>(sc, W)));
+        if (guidedSurf) {
+            k_lookup<true><<<grid, kBlock, 0, st>>>(sc, W, W.shade, W.sh8, W.sh16, W.sh32);
+            k_shade<8><<<grid, kBlock, 0, st>>>(sc, W, W.sh8);
+            k_shade<16><<<grid, kBlock, 0, st>>>(sc, W, W.sh16);
+            VSPG_STAGE(VSPG_K_SHADE, (k_shade<32><<<grid, kBlock, 0, st>>>(sc, W, W.sh32)));
+            ctx->launches += 3;
+        } else VSPG_STAGE(VSPG_K_SHADE, (k_shade<0><<<grid, kBlock, 0, st>>>(sc, W, W.shade)));
         VSPG_STAGE(VSPG_K_SHADOW, (k_shadow<<<grid, kBlock, 0, st>>>(sc, W)));
         VSPG_STAGE(VSPG_K_FINISH, (k_finish<<<grid, kBlock, 0, st>>>(sc, W)));
         ctx->launches += 8; ctx->iterations++;
