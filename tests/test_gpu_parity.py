@@ -39,15 +39,6 @@ def test_majorant_segments_bit_exact(ctx, orc, name):
         assert np.array_equal(seg_g[i, :c].view(np.uint32), seg_o[i, :c].view(np.uint32)), f"ray {i}"
 
 
-def test_majorant_grid_host_builder_matches_oracle(orc):
-    cfg = H.small("C2")
-    med = cfg.scene.desc.media[0]
-    assert np.array_equal(api.build_majorant_grid(med).view(np.uint32), orc.build_majorant_grid(med).view(np.uint32))
-    cfg5 = H.small("C5")
-    med5 = cfg5.scene.desc.media[0]
-    assert np.array_equal(api.build_majorant_grid(med5).view(np.uint32), orc.build_majorant_grid(med5).view(np.uint32))
-
-
 @pytest.mark.parametrize("name", ["C1", "C2", "C5"])
 def test_density_fetch_bit_exact(ctx, orc, name):
     cfg = H.small(name)
@@ -198,6 +189,63 @@ def test_guided_sample_parity(ctx, orc, surface, ris):
     for k in ("pdf_wq", "vsp_wq"):                  # evaluated at an input direction: pure arithmetic parity
         a, b = g(got, k), g(want, k)
         err = H.rel_err(a, b, floor=1e-12)
+        assert err.max() <= REL_TOL, f"{k}: max rel err {err.max():.3e}"
+
+
+def _real_field_guiding():
+    """The golden OpenPGL field (written by the reference, tests/golden/make_golden.py) through the product loader."""
+    import os
+    from pyvspg import synthetic as syn
+    lib = api.lib()
+    h, err = A.P(), C.create_string_buffer(512)
+    path = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "field_small.pgl")
+    assert lib.vspg_host_field_load(path.encode(), C.byref(h), err, 512) == 0, err.value
+    g = syn.Guiding()
+    g.set_field("surface", lib.vspg_host_field_surface(h).contents, h)
+    g.set_field("volume", lib.vspg_host_field_volume(h).contents, h)
+    return g
+
+
+@pytest.mark.parametrize("surface", [1, 0])
+def test_guided_sample_parity_on_a_reference_trained_field(ctx, orc, surface):
+    """Same comparison as above on a field trained and stored by the reference's OpenPGL (11-17 lobes per region, so the
+    16- and 32-lane mixture paths run); the oracle is pinned bit-exactly to the reference library on this field
+    (tests/test_cpu.py), so this ties the CUDA mixture code to the reference itself."""
+    cfg = H.small("C2")
+    g = _real_field_guiding()
+    ctx.set_scene(cfg.scene)
+    ctx.set_guiding(g)
+    ctx.set_integrator(cfg.ip)
+    f = g.fields["surface" if surface else "volume"]
+    rng = np.random.default_rng(29)
+    n = 3000
+    arr = (A.GsInput * n)()
+    for i in range(n):
+        I = arr[i]
+        p = rng.uniform(-1.0, 2.0, 3)
+        if surface:
+            p[1] = rng.uniform(-1.0, -0.9)
+        I.p[:] = [float(x) for x in p]
+        v = rng.normal(size=(3, 3))
+        v /= np.linalg.norm(v, axis=1, keepdims=True)
+        nrm, wo, wq = v
+        if surface and np.dot(wo, nrm) < 0:
+            wo = -wo
+        I.wo[:] = [float(np.float32(x)) for x in wo]
+        I.n[:] = [float(np.float32(x)) for x in nrm]
+        I.wq[:] = [float(np.float32(x)) for x in wq]
+        I.g = float(rng.choice([0.0, 0.6, 0.85, -0.4]))
+        I.reflectance[:] = [0.5, 0.5, 0.5]
+        I.v, I.u1 = float(rng.random()), float(rng.random())
+        I.u2[:] = [float(rng.random()), float(rng.random())]
+        I.rng_state, I.rng_inc = H.pcg_state(rng)
+    got = ctx.debug_guided_sample(surface, arr)
+    want = orc.guided_sample(cfg.scene, g, cfg.ip, surface, arr)
+    q = lambda a, k: H.struct_array_to_np(a, k)
+    assert np.array_equal(q(got, "ok"), q(want, "ok")) and q(want, "ok").sum() > n * 0.8
+    assert np.array_equal(q(got, "region"), q(want, "region"))
+    for k in ("pdf_wq", "vsp_wq"):
+        err = H.rel_err(q(got, k), q(want, k), floor=1e-12)
         assert err.max() <= REL_TOL, f"{k}: max rel err {err.max():.3e}"
 
 

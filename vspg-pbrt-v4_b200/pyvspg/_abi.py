@@ -10,6 +10,7 @@ PKG_DIR = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 LIB_PATH = os.path.join(PKG_DIR, "libvspg.so")
 
 VSPG_OK = 0
+ERR_INVALID, ERR_CUDA, ERR_IO, ERR_UNSUPPORTED, ERR_STATE = -1, -2, -3, -4, -5
 ERR_NAMES = {0: "OK", -1: "INVALID", -2: "CUDA", -3: "IO", -4: "UNSUPPORTED", -5: "STATE"}
 
 MEDIUM_HOMOGENEOUS, MEDIUM_GRID, MEDIUM_RGBGRID = 0, 1, 2
