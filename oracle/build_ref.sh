@@ -20,7 +20,9 @@ fi
 EXT="$REF/src/ext"; PGL="$EXT/openpgl"; TBB="$EXT/tbb"
 OUT="$HERE/_ref"; OBJ="$OUT/obj"; mkdir -p "$OBJ/tbb" "$OBJ/pgl"
 JOBS="${JOBS:-$(nproc)}"
-CXX="${CXX:-g++}"
+# /usr/bin/g++ links libstdc++ dynamically; the image's /opt/gcc wrapper links it statically, and one private copy of
+# libstdc++ per .so breaks iostream locale facets across the three libraries (seen as a crash in std::cout << bool).
+if [ -x /usr/bin/g++ ]; then CXX="${VSPG_REF_CXX:-/usr/bin/g++}"; else CXX="${VSPG_REF_CXX:-g++}"; fi
 # ---- oneTBB ------------------------------------------------------------------
 if [ ! -f "$OUT/libtbb_ref.so" ]; then
   ls "$TBB"/src/tbb/*.cpp | xargs -P "$JOBS" -I{} sh -c \

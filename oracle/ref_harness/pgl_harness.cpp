@@ -135,6 +135,39 @@ int ref_distribution_probe(void *h, int mode, int n, const float *pos3, const fl
     return 0;
 }
 
+// Image-space guiding buffer through the reference's public API: accumulate deterministic pixel samples, Update()
+// (OIDN is the identity stub here, so the stored estimate is the un-denoised one), Store() -> multi-layer EXR written
+// by the reference's tinyexr path (imagespace/ImageSpaceGuidingBuffer.h:360-630).  (Loading the file back with the
+// reference's own loader, :120-345, crashes in this trimmed build, so the in-memory estimate is what gets pinned.)
+int ref_isgb_make(const char *path, int w, int h, int spp, int seed, float *vsp_out) {
+    using pg::util::ImageSpaceGuidingBuffer;
+    ImageSpaceGuidingBuffer::Config cfg(pgl_point2i{w, h});
+    cfg.EnableContributionEstimate(true);
+    cfg.EnableVolumeScatterProbabilityEstimate(true);
+    ImageSpaceGuidingBuffer buf(cfg);
+    std::mt19937 rng(seed);
+    std::uniform_real_distribution<float> U(0.f, 1.f);
+    for (int s = 0; s < spp; s++)
+        for (int y = 0; y < h; y++)
+            for (int x = 0; x < w; x++) {
+                ImageSpaceGuidingBuffer::Sample smp;
+                float pv = 0.5f + 0.45f * std::sin(0.37f * x) * std::cos(0.23f * y);
+                bool vol = U(rng) < pv;
+                float c = (vol ? 0.8f : 0.3f) * (0.5f + U(rng));
+                smp.contribution = {c, 0.9f * c, 0.7f * c};
+                smp.albedo = {0.5f, 0.5f, 0.5f};
+                smp.normal = {0.f, 0.f, -1.f};
+                smp.SetSurfaceEvent(!vol);
+                buf.AddSample(pgl_point2i{x, y}, smp);
+            }
+    buf.Update();
+    buf.Store(std::string(path));
+    // the estimate the integrator reads at depth 0 (vspg.cpp:1098-1112 -> ImageSpaceGuidingBuffer.h:802-809), taken from
+    // the very buffer Store() has just written as layer "VSP"
+    for (int y = 0; y < h; y++)
+        for (int x = 0; x < w; x++) vsp_out[y * w + x] = buf.GetVolumeScatterProbabilityEstimate(pgl_point2i{x, y});
+    return buf.IsReady() ? 1 : 0;
+}
 float ref_standard_rr(float x, float y, float z) {
     pgl_vec3f t = {x, y, z};
     return openpgl::cpp::util::StandardThroughputBasedRussianRoulette(t);

@@ -3,6 +3,9 @@ oracle/build_ref.sh from /root/reference; this script only runs where /root/refe
 
   tests/golden/field_small.pgl    a real OpenPGL 0.7.0 field trained through the reference's public API
                                    (SampleStorage::AddSample + Field::Update) and stored with Field::Store
+  tests/golden/isg_small.exr      an image-space guiding buffer accumulated, updated and stored by the reference's
+                                   ImageSpaceGuidingBuffer (multi-layer float EXR via its tinyexr path)
+  tests/golden/isg_small_vsp.npy  GetVolumeScatterProbabilityEstimate() of that buffer for every pixel
   tests/golden/pgl_probe.npz      reference answers on seeded probes of that field: region id, u after draw(),
                                    PDF / VSP / IncomingRadiancePDF at a query direction, SamplePDF (direction + pdf)
                                    for surface (+cosine product) and volume (+HG product) distributions
@@ -30,6 +33,7 @@ def harness():
     L.ref_field_load.restype = C.c_void_p
     L.ref_field_free.argtypes = [C.c_void_p]
     L.ref_field_iteration.argtypes = [C.c_void_p]
+    L.ref_isgb_make.argtypes = [C.c_char_p, C.c_int, C.c_int, C.c_int, C.c_int, PF]
     L.ref_distribution_probe.argtypes = [C.c_void_p, C.c_int, C.c_int, PF, PF, PF, PF, PF, PF, PI, PF, PF, PF, PF, PF, PF]
     return L
 
@@ -78,6 +82,10 @@ def main():
             out[f"{name}_{k}"] = v
     L.ref_field_free(h)
     np.savez_compressed(os.path.join(HERE, "pgl_probe.npz"), **out)
+    w, hgt = 40, 24
+    vsp = np.zeros((hgt, w), np.float32)
+    assert L.ref_isgb_make(os.path.join(HERE, "isg_small.exr").encode(), w, hgt, 8, 5, fp(vsp)) == 1
+    np.save(os.path.join(HERE, "isg_small_vsp.npy"), vsp)
     print("wrote", path, os.path.getsize(path), "bytes;", {k: int((out[k] >= 0).sum()) for k in out if k.endswith("_id")})
 
 

@@ -202,6 +202,52 @@ def test_oracle_guiding_math_is_bit_exact_against_the_reference_library(orc, gol
     assert ((o["vsp"][ok] >= 0) & (o["vsp"][ok] <= 1)).all()
 
 
+# ------------------------------------------------------------------ EXR I/O (ISG buffer in, film out)
+def _read_channel(path, ch):
+    lib = api.lib()
+    out, w, h, err = A.PF(), C.c_int(), C.c_int(), C.create_string_buffer(256)
+    rc = lib.vspg_exr_read_channel(path.encode(), ch.encode(), C.byref(out), C.byref(w), C.byref(h), err, 256)
+    if rc != 0:
+        raise api.VspgError(rc, err.value.decode())
+    a = np.ctypeslib.as_array(out, shape=(h.value, w.value)).copy()
+    lib.vspg_free(out)
+    return a
+
+
+def test_isg_buffer_reader_matches_the_reference_estimate():
+    """isg_small.exr was stored by the reference's ImageSpaceGuidingBuffer; isg_small_vsp.npy is what its
+    GetVolumeScatterProbabilityEstimate returned per pixel (ImageSpaceGuidingBuffer.h:802-809).  Layer VSP, channel Y."""
+    got = _read_channel(os.path.join(GOLD, "isg_small.exr"), "VSP.Y")
+    want = np.load(os.path.join(GOLD, "isg_small_vsp.npy"))
+    assert got.shape == want.shape == (24, 40)
+    assert np.array_equal(got.view(np.uint32), want.view(np.uint32))
+    with pytest.raises(api.VspgError) as e:
+        _read_channel(os.path.join(GOLD, "isg_small.exr"), "Nope.Y")
+    assert "not found" in str(e.value)
+
+
+@pytest.mark.parametrize("half", [0, 1])
+def test_exr_film_writer_round_trip(tmp_path, half):
+    """R,G,B scanline ZIP file, HALF by default like film.cpp's WriteImage; half conversion rounds to nearest even
+    (util/float_test.cpp); cross-checked with the reference's tinyexr when oracle/_ref is present."""
+    rgb = (np.random.default_rng(0).random((37, 53, 3)) * 4).astype(np.float32)
+    rgb[0, 0] = [0.0, 1e-6, 70000.0]                     # zero, half-subnormal, half-overflow
+    path = str(tmp_path / "film.exr")
+    assert api.lib().vspg_exr_write_rgb(path.encode(), rgb.ctypes.data_as(A.PF), 53, 37, half) == 0
+    with np.errstate(over="ignore"):
+        want = rgb.astype(np.float16).astype(np.float32) if half else rgb
+    for i, ch in enumerate("RGB"):
+        assert np.array_equal(_read_channel(path, ch), want[..., i])
+    ref = os.path.join(ROOT, "oracle", "_ref", "libopenpgl_ref.so")
+    if os.path.exists(ref):
+        L = C.CDLL(ref)
+        L.LoadEXR.argtypes = [C.POINTER(A.PF), C.POINTER(C.c_int), C.POINTER(C.c_int), C.c_char_p, C.POINTER(C.c_char_p)]
+        out, w, h, err = A.PF(), C.c_int(), C.c_int(), C.c_char_p()
+        assert L.LoadEXR(C.byref(out), C.byref(w), C.byref(h), path.encode(), C.byref(err)) == 0
+        m = np.ctypeslib.as_array(out, shape=(37, 53, 4))
+        assert np.array_equal(m[..., :3], want)
+
+
 # ------------------------------------------------------------------ oracle invariants the reference's tests use (SURVEY 4)
 def test_sampler_stream_is_a_function_of_pixel_seed_and_sample_index(orc):
     """samplers.h:455-458: the stream depends only on (pixel, seed, sampleIndex) -- what makes sharding exact."""

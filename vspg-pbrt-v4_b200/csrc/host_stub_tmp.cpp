@@ -13,7 +13,4 @@ const vspg_integrator_params *vspg_host_scene_integrator(const vspg_host_scene *
 int vspg_host_scene_spp(const vspg_host_scene *) { return 0; }
 int vspg_host_scene_seed(const vspg_host_scene *) { return 0; }
 const char *vspg_host_scene_outfile(const vspg_host_scene *) { return ""; }
-int vspg_exr_read_channel(const char *, const char *, float **, int *, int *, char *err, size_t n) { return nyi(err, n); }
-int vspg_exr_write_rgb(const char *, const float *, int, int, int) { return VSPG_ERR_UNSUPPORTED; }
-void vspg_free(void *p) { free(p); }
 }
