@@ -163,6 +163,66 @@ class Context:
         return out
 
 
+class HostScene:
+    """A .pbrt scene parsed by the C++ front end (vspg_host_scene_parse): exposes .desc / .guiding / .ip with the
+    same attribute names Context.set_scene / set_guiding / set_integrator consume, plus spp / seed / outfile.
+    Raises VspgError with the front end's file:line message (the reference ErrorExits there)."""
+
+    def __init__(self, path=None, text=None, base_dir="."):
+        self._h = A.P()
+        err = C.create_string_buffer(1024)
+        if path is not None:
+            rc = lib().vspg_host_scene_parse(str(path).encode(), C.byref(self._h), err, len(err))
+        else:
+            rc = lib().vspg_host_scene_parse_string(text.encode(), str(base_dir).encode(), C.byref(self._h), err, len(err))
+        if rc != 0:
+            self._h = A.P()
+            raise VspgError(rc, err.value.decode())
+        self.desc = lib().vspg_host_scene_desc(self._h).contents
+        g = lib().vspg_host_scene_guiding(self._h)
+        self.guiding = _Holder(g.contents) if g else None
+        self.ip = lib().vspg_host_scene_integrator(self._h).contents
+        self.spp = lib().vspg_host_scene_spp(self._h)
+        self.seed = lib().vspg_host_scene_seed(self._h)
+        self.outfile = lib().vspg_host_scene_outfile(self._h).decode()
+
+    def close(self):
+        if self._h:
+            self.desc = self.guiding = self.ip = None
+            lib().vspg_host_scene_free(self._h)
+            self._h = A.P()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
+class _Holder:
+    def __init__(self, desc):
+        self.desc = desc
+
+
+def exr_read_channel(path, channel):
+    """vspg_exr_read_channel -> float32 [h, w]."""
+    out, w, h = A.PF(), A.i32(), A.i32()
+    err = C.create_string_buffer(512)
+    rc = lib().vspg_exr_read_channel(str(path).encode(), channel.encode(), C.byref(out), C.byref(w), C.byref(h), err, len(err))
+    if rc != 0:
+        raise VspgError(rc, err.value.decode())
+    a = np.ctypeslib.as_array(out, shape=(h.value, w.value)).copy()
+    lib().vspg_free(out)
+    return a
+
+
+def exr_write_rgb(path, rgb, as_half=False):
+    rgb = np.ascontiguousarray(rgb, dtype=np.float32)
+    rc = lib().vspg_exr_write_rgb(str(path).encode(), _fp(rgb), rgb.shape[1], rgb.shape[0], int(as_half))
+    if rc != 0:
+        raise VspgError(rc, f"cannot write {path}")
+
+
 def build_majorant_grid(medium):
     n = medium.maj_res[0] * medium.maj_res[1] * medium.maj_res[2]
     out = np.zeros(n, dtype=np.float32)

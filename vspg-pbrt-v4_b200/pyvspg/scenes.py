@@ -67,6 +67,8 @@ def perspective_camera(eye, look, up, fov_deg, width, height, lens_radius=0.0, f
     cam.filter_type, cam.filter_sigma = 0, 0.0
     cam.imaging_ratio = 1.0                      # film.cpp:233 exposureTime * ISO / 100 with the defaults
     cam.max_component_value = float("inf")
+    cam._params = dict(eye=eye.tolist(), look=look.tolist(), up=up.tolist(), fov=float(fov_deg), lens_radius=float(lens_radius),
+                       focal_distance=float(focal_distance))   # for pbrt_writer
     return cam, eye
 
 
@@ -79,8 +81,10 @@ class Scene:
         self.quads, self.materials, self.lights, self.media = [], [], [], []
         self._keep = []
         self.desc = None
+        self.log = []   # world-space record of every add_* call, in order (pbrt_writer turns it into a .pbrt file)
 
     def add_material(self, reflectance):
+        self.log.append(("material", dict(reflectance=[float(x) for x in reflectance], index=len(self.materials))))
         m = A.Material()
         m.type = 0
         m.reflectance[:] = [float(x) for x in reflectance]
@@ -93,6 +97,9 @@ class Scene:
         if corners is None:
             o, eu, ev = (np.asarray(v, dtype=np.float64) for v in (origin, eu, ev))
             corners = [o, o + eu, o + ev, o + eu + ev]
+        self.log.append(("quad", dict(corners=[[float(x) for x in np.asarray(p, dtype=np.float64)] for p in corners], material=material,
+                                      emission=None if emission is None else [float(x) for x in emission], two_sided=bool(two_sided),
+                                      medium_inside=medium_inside, medium_outside=medium_outside, has_interface=bool(has_interface))))
         q = A.Quad()
         for name, p in zip(("p00", "p10", "p01", "p11"), corners):
             getattr(q, name)[:] = [float(np.float32(x)) for x in (np.asarray(p, dtype=np.float64) - self.eye)]
@@ -123,6 +130,7 @@ class Scene:
         self.add_quad([a[0], a[1], b[2]], X, Y, **kw)      # +z
 
     def add_point_light(self, pos, intensity, medium=-1):
+        self.log.append(("point", dict(pos=[float(x) for x in pos], I=[float(x) for x in intensity], medium=medium)))
         l = A.Light()
         l.type = A.LIGHT_POINT
         l.L[:] = [float(x) for x in intensity]
@@ -131,6 +139,7 @@ class Scene:
         self.lights.append(l)
 
     def add_distant_light(self, to_light, radiance):
+        self.log.append(("distant", dict(to_light=[float(x) for x in to_light], L=[float(x) for x in radiance])))
         l = A.Light()
         l.type = A.LIGHT_DISTANT
         l.L[:] = [float(x) for x in radiance]
@@ -139,6 +148,7 @@ class Scene:
         self.lights.append(l)
 
     def add_uniform_infinite_light(self, radiance):
+        self.log.append(("infinite", dict(L=[float(x) for x in radiance])))
         l = A.Light()
         l.type = A.LIGHT_UNIFORM_INFINITE
         l.L[:] = [float(x) for x in radiance]
@@ -160,6 +170,8 @@ class Scene:
 
     def add_homogeneous_medium(self, sigma_a, sigma_s, scale_=1.0, g=0.0):
         # media.h:240-242: sigma_* spectra scaled by "scale" in the ctor
+        self.log.append(("medium", dict(type="homogeneous", sigma_a=[float(x) for x in sigma_a], sigma_s=[float(x) for x in sigma_s],
+                                        scale=float(scale_), g=float(g), index=len(self.media))))
         m = self._medium_common(A.MEDIUM_HOMOGENEOUS, (0, 0, 0), (1, 1, 1), np.float32(sigma_a) * np.float32(scale_),
                                 np.float32(sigma_s) * np.float32(scale_), 1.0, g, None)
         self.media.append(m)
@@ -169,6 +181,9 @@ class Scene:
         """uniformgrid (media.cpp:272-361): density[nz][ny][nx] float32, medium-space bounds lo..hi."""
         d = np.ascontiguousarray(density, dtype=np.float32)
         self._keep.append(d)
+        self.log.append(("medium", dict(type="uniformgrid", density=d, lo=[float(x) for x in lo], hi=[float(x) for x in hi],
+                                        sigma_a=[float(x) for x in sigma_a], sigma_s=[float(x) for x in sigma_s], scale=float(scale_), g=float(g),
+                                        world_from_medium=world_from_medium, index=len(self.media))))
         m = self._medium_common(A.MEDIUM_GRID, lo, hi, np.float32(sigma_a) * np.float32(scale_),
                                 np.float32(sigma_s) * np.float32(scale_), 1.0, g, world_from_medium)
         m.nz, m.ny, m.nx = d.shape
@@ -181,6 +196,8 @@ class Scene:
         sa = np.ascontiguousarray(sigma_a_rgb, dtype=np.float32)
         ss = np.ascontiguousarray(sigma_s_rgb, dtype=np.float32)
         self._keep += [sa, ss]
+        self.log.append(("medium", dict(type="rgbgrid", sigma_a_rgb=sa, sigma_s_rgb=ss, lo=[float(x) for x in lo], hi=[float(x) for x in hi],
+                                        scale=float(scale_), g=float(g), world_from_medium=world_from_medium, index=len(self.media))))
         m = self._medium_common(A.MEDIUM_RGBGRID, lo, hi, (1, 1, 1), (1, 1, 1), scale_, g, world_from_medium)
         m.nz, m.ny, m.nx = sa.shape[:3]
         m.sigma_a_rgb = sa.ctypes.data_as(A.PF)
