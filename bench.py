@@ -49,6 +49,7 @@ def parse_args():
     ap.add_argument("--spp", type=int, default=0, help="override samples per pixel (reported in config)")
     ap.add_argument("--res-scale", type=float, default=1.0, help="scale film resolution (reported in config)")
     ap.add_argument("--capacity", type=int, default=0, help="paths in flight (0 = library default)")
+    ap.add_argument("--shard", default="samples", choices=["samples", "bands"], help="multi-GPU partition (pyvspg.multi)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--cpu-spp", type=int, default=0, help="spp of the CPU sample (0 = auto, ~10-30 s)")
     return ap.parse_args()
@@ -78,7 +79,7 @@ def config_dict(cfg, args, world):
         "workload": cfg.name, "description": cfg.description, "width": cfg.width, "height": cfg.height, "spp_per_gpu": cfg.spp,
         "spp_total": cfg.spp * world, "grid": [med.nx, med.ny, med.nz] if med.type != 0 else "homogeneous",
         "sampler": "independent", "maxdepth": cfg.ip.max_depth,
-        "parallelism": f"sample-pass sharding x{world}" + (" + NCCL film reduce" if world > 1 else ""),
+        "parallelism": f"{'sample-pass' if args.shard == 'samples' else 'interleaved-band'} sharding x{world}" + (" + NCCL film reduce" if world > 1 else ""),
         "l2": "path-state working set (2M paths x ~330 B = 0.7 GB) exceeds the 126 MB L2 each wave iteration; density grid "
               "itself is L2-resident for 128^3 (8 MiB), HBM-resident for 512^3",
     }
@@ -208,7 +209,7 @@ def run_b200(args):
     import numpy as np
     import torch
     import torch.distributed as dist
-    from pyvspg import api
+    from pyvspg import api, multi
 
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
@@ -238,12 +239,15 @@ def run_b200(args):
     W, Hh, spp = cfg.width, cfg.height, cfg.spp
     paths_per_step = W * Hh * spp * world
 
+    def render(b, e, s, window, seed):
+        ctx.render(b, e, spp_stride=s, window=window, seed=seed, stream=stream)
+
     def step(seed):
-        # rank r renders sample indices r, r+world, ... of a (spp*world)-spp render; film reduced onto rank 0
+        # weak scaling: a (spp*world)-spp render of the image; rank r takes its shard (sample indices r, r+world, ...
+        # or its interleaved row bands), then the fp64 films are summed onto rank 0 (the one exchange step)
         ctx.film_clear()
-        ctx.render(rank, spp * world, spp_stride=world, seed=seed, stream=stream)
-        if world > 1:
-            dist.reduce(film_t, dst=0, op=dist.ReduceOp.SUM)
+        multi.render_shard(render, W, Hh, spp * world, rank, world, seed, mode=args.shard)
+        multi.combine_film(film_t, world, dst=0)
 
     for i in range(args.warmup):
         step(i)
@@ -278,9 +282,8 @@ def run_b200(args):
         ctx.set_scene(cfg.scene)          # H2D: density grid(s), majorant grid, shapes, lights
         ctx.set_guiding(cfg.guiding)      # H2D: guiding cache (KD nodes, mixtures, neighbour tables), ISG / Tr buffers
         ctx.set_integrator(cfg.ip)
-        ctx.render(rank, spp * world, spp_stride=world, seed=seed, stream=stream)
-        if world > 1:
-            dist.reduce(film_t, dst=0, op=dist.ReduceOp.SUM)
+        multi.render_shard(render, W, Hh, spp * world, rank, world, seed, mode=args.shard)
+        multi.combine_film(film_t, world, dst=0)
         ctx.film_download_to(film_host.data_ptr())   # D2H: fp64 film
 
     e2e_step(7)
