@@ -32,8 +32,61 @@ def _value_noise(x, y, z, seed):
     return out
 
 
-def fbm_grid(n, seed=1337, octaves=5, base_freq=4.0, gain=0.5, lacunarity=2.0, scale_=1.6, offset=-0.3, slab=16):
-    """density[nz][ny][nx] = clamp(fBm * scale + offset, 0, 1); generated slab by slab to bound memory."""
+def _fbm_torch(n, seed, octaves, base_freq, gain, lacunarity, scale_, offset, slab=32):
+    """The same arithmetic as the numpy path below, op for op, on torch tensors (CUDA when present): the 512^3 grids
+    of C4 take minutes in single-threaded numpy and about a second here."""
+    import torch
+    dev = torch.device("cuda") if torch.cuda.is_available() else torch.device("cpu")
+    f32, i64 = torch.float32, torch.int64
+
+    def u64(v):   # two's-complement int64 with the same bits as the uint64 constant
+        return v - (1 << 64) if v >= (1 << 63) else v
+
+    def lsr(h, k):   # logical shift right on int64
+        return (h >> k) & ((1 << (64 - k)) - 1)
+
+    def hash3(ix, iy, iz, sd):
+        h = (ix * u64(0x9E3779B185EBCA87)) ^ (iy * u64(0xC2B2AE3D27D4EB4F)) ^ (iz * u64(0x165667B19E3779F9)) ^ sd
+        h = h ^ lsr(h, 33)
+        h = h * u64(0xFF51AFD7ED558CCD)
+        h = h ^ lsr(h, 33)
+        return lsr(h, 40).to(f32) * (1.0 / (1 << 24))
+
+    def value_noise(x, y, z, sd):
+        fl = [torch.floor(v) for v in (x, y, z)]
+        ix, iy, iz = (v.to(i64) for v in fl)
+        fx, fy, fz = x - fl[0], y - fl[1], z - fl[2]
+        sx, sy, sz = fx * fx * (3 - 2 * fx), fy * fy * (3 - 2 * fy), fz * fz * (3 - 2 * fz)
+        out = torch.zeros_like(fx)
+        for dz in (0, 1):
+            for dy in (0, 1):
+                for dx in (0, 1):
+                    w = (sx if dx else 1 - sx) * (sy if dy else 1 - sy) * (sz if dz else 1 - sz)
+                    out += w * hash3(ix + dx, iy + dy, iz + dz, sd)
+        return out
+
+    out = np.empty((n, n, n), dtype=np.float32)
+    xs = (torch.arange(n, dtype=f32, device=dev) + 0.5) / n
+    norm = sum(gain ** o for o in range(octaves))
+    for z0 in range(0, n, slab):
+        zs = (torch.arange(z0, min(n, z0 + slab), dtype=f32, device=dev) + 0.5) / n
+        Z, Y, X = torch.meshgrid(zs, xs, xs, indexing="ij")
+        acc = torch.zeros_like(X)
+        amp, freq = 1.0, base_freq
+        for o in range(octaves):
+            acc += float(np.float32(amp)) * value_noise(X * freq, Y * freq, Z * freq, seed + 101 * o)
+            amp *= gain
+            freq *= lacunarity
+        d = torch.clamp(acc / float(np.float32(norm)) * float(np.float32(scale_)) + float(np.float32(offset)), 0, 1)
+        out[z0:z0 + len(zs)] = d.cpu().numpy()
+    return out
+
+
+def fbm_grid(n, seed=1337, octaves=5, base_freq=4.0, gain=0.5, lacunarity=2.0, scale_=1.6, offset=-0.3, slab=16, backend=None):
+    """density[nz][ny][nx] = clamp(fBm * scale + offset, 0, 1); generated slab by slab to bound memory.
+    backend: "numpy" | "torch" | None (= torch for n >= 192, where numpy takes minutes)."""
+    if backend == "torch" or (backend is None and n >= 192):
+        return _fbm_torch(n, seed, octaves, base_freq, gain, lacunarity, scale_, offset)
     nx = ny = nz = n
     out = np.empty((nz, ny, nx), dtype=np.float32)
     xs = (np.arange(nx, dtype=np.float32) + 0.5) / nx
