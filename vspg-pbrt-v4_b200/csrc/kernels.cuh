@@ -127,14 +127,24 @@ VD void spawn_ray_to(V3 pf_, V3 pfErr, V3 nf, V3 pLight, V3 pLightErr, V3 nLight
 // one G-lane group per vertex (32/G vertices per warp).  The warp iterates uniformly; a group whose item index is
 // past the end re-runs the warp's first item with every side effect suppressed (`live` false) so that the
 // group-mask shuffles of the mixture code stay well-formed.
+//
+// The scatter kernels are ~90 KB of mostly straight-line SASS; with the warps of an SM scattered over that much code
+// the top stall was instruction fetch (ncu r01c: no_instruction 3.8-5.9 per issue).  Trip counts are therefore
+// uniform over the whole CTA (`base` is a CTA quantity) and the loop body carries __syncthreads() between its
+// phases (scatter_phase_sync), so that the warps of a CTA walk the code together and share instruction-cache lines.
+constexpr int kScatterBlock = 512;        // launch bound; the default launch uses 256 (r01e A/B: 512 -> 116.5, 256 -> 118.0, 128 -> 109.4 Mpaths/s)
 template <int G> struct GroupIter {
     static constexpr int W = G > 0 ? G : 1;        // lanes per vertex
-    int first, step, sub; bool leader;
+    int first, step, warpOff, sub; bool leader;
     VD GroupIter() {
-        if (G > 0) { first = (gtid() >> 5) * (32 / W); step = (gstride() >> 5) * (32 / W); sub = (threadIdx.x & 31) / W; leader = (threadIdx.x & (W - 1)) == 0; }
-        else { first = gtid(); step = gstride(); sub = 0; leader = true; }
+        if (G > 0) {
+            const int perCta = (blockDim.x >> 5) * (32 / W);
+            first = blockIdx.x * perCta; step = gridDim.x * perCta;
+            warpOff = (threadIdx.x >> 5) * (32 / W); sub = (threadIdx.x & 31) / W; leader = (threadIdx.x & (W - 1)) == 0;
+        } else { first = blockIdx.x * blockDim.x; step = gstride(); warpOff = threadIdx.x; sub = 0; leader = true; }
     }
 };
+template <int G> VD void scatter_phase_sync() { if (G > 0) __syncthreads(); }
 
 // ------------------------------------------------------------------ Field::getRegion for a whole stage queue
 // (field/Field.h:114-150; guiding.h:83-109 / 383-398 front half).  One THREAD per vertex: draws the sampler's `v`,
@@ -175,14 +185,17 @@ __global__ void __launch_bounds__(kBlock) k_lookup(const DScene sc, const Wavefr
 
 // ------------------------------------------------------------------ volume scatter vertex (vspg.cpp:804-875 / 988-1058)
 template <int G>
-__global__ void __launch_bounds__(kBlock) k_volscatter(const DScene sc, const Wavefront W, const Queue in) {
+__global__ void __launch_bounds__(G > 0 ? kScatterBlock : kBlock) k_volscatter(const DScene sc, const Wavefront W, const Queue in) {
     const int n = *in.count;
     const GroupIter<G> gi;
     const bool leader = gi.leader;
     unsigned lookups = 0, shadows = 0;
-    for (int i0 = gi.first; i0 < n; i0 += gi.step) {
+    for (int base = gi.first; base < n; base += gi.step) {
+        const int i0 = base + gi.warpOff;
         const bool live = i0 + gi.sub < n;
-        int slot = in.items[live ? i0 + gi.sub : i0];
+        if (G == 0 && !live) continue;             // one thread per vertex: no group shuffles, no barriers
+        scatter_phase_sync<G>();
+        int slot = in.items[live ? i0 + gi.sub : base];
         PathRegs ps; path_load(W.P, slot, ps);
         float4 e = W.P.ev[slot];
         V3 p(e.x, e.y, e.z);
@@ -191,6 +204,7 @@ __global__ void __launch_bounds__(kBlock) k_volscatter(const DScene sc, const Wa
         gphase.enableGuiding = ip.volume_guiding; gphase.enableScatterGuiding = ip.vsp_secondary_guiding; gphase.ris = ip.volume_guiding_ris;
         if (G > 0) gphase.init_region(sc, e.w, p, ps.ray.d, W.P.lk[slot]);   // `v` was drawn by k_lookup
         else { float v = ps.rng.uniform(); gphase.init(sc, e.w, p, ps.ray.d, v, lookups); }
+        scatter_phase_sync<G>();
         float survivalProb = 1.0f;
         if (ps.fl.depth > ip.min_rr_depth) {
             V3 rrw = (ps.beta / avg3(ps.r_u)) * ps.rr_correction;   // openpgl/cpp/RussianRoulette.h:32-35
@@ -223,6 +237,7 @@ __global__ void __launch_bounds__(kBlock) k_volscatter(const DScene sc, const Wa
                 }
             }
         }
+        scatter_phase_sync<G>();
         bool alive = true;
         if (survivalProb < 1 && ps.fl.depth > ip.min_rr_depth) {
             float q = fmaxf(0.f, 1 - survivalProb);
@@ -243,6 +258,7 @@ __global__ void __launch_bounds__(kBlock) k_volscatter(const DScene sc, const Wa
                 ps.vsp_next = gphase.vsp(s.wi);
             }
         }
+        scatter_phase_sync<G>();
         const bool w = leader && live;
         if (w) {
             path_store(W.P, slot, ps);

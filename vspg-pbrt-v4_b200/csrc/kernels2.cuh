@@ -60,15 +60,18 @@ __global__ void __launch_bounds__(kBlock) k_surface(const DScene sc, const Wavef
 
 // ------------------------------------------------------------------ surface scatter vertex (vspg.cpp:448-607)
 template <int G>
-__global__ void __launch_bounds__(kBlock) k_shade(const DScene sc, const Wavefront W, const Queue in) {
+__global__ void __launch_bounds__(G > 0 ? kScatterBlock : kBlock) k_shade(const DScene sc, const Wavefront W, const Queue in) {
     const int n = *in.count;
     const GroupIter<G> gi;
     const bool leader = gi.leader;
     const vspg_integrator_params &ip = sc.ip;
     unsigned lookups = 0, shadows = 0;
-    for (int i0 = gi.first; i0 < n; i0 += gi.step) {
+    for (int base = gi.first; base < n; base += gi.step) {
+        const int i0 = base + gi.warpOff;
         const bool live = i0 + gi.sub < n;
-        int slot = in.items[live ? i0 + gi.sub : i0];
+        if (G == 0 && !live) continue;             // one thread per vertex: no group shuffles, no barriers
+        scatter_phase_sync<G>();
+        int slot = in.items[live ? i0 + gi.sub : base];
         PathRegs ps; path_load(W.P, slot, ps);
         float4 hr = W.P.hit[slot];
         Hit h; h.t = hr.x; h.u = hr.y; h.v = hr.z; h.prim = __float_as_int(hr.w);
@@ -78,6 +81,7 @@ __global__ void __launch_bounds__(kBlock) k_shade(const DScene sc, const Wavefro
         gbsdf.set_bsdf(isect.ns, isect.dpdu, ld3(sc.materials[isect.material].reflectance));
         if (G > 0) gbsdf.init_region(sc, ps.ray.o + h.t * ps.ray.d, ps.ray.d, isect.ns, W.P.lk[slot]);   // `v` was drawn by k_lookup
         else { float v = ps.rng.uniform(); gbsdf.init(sc, ps.ray.o + h.t * ps.ray.d, ps.ray.d, isect.ns, v, lookups); }
+        scatter_phase_sync<G>();
         bool emitShadow = false;
         if (ip.use_nee && gbsdf.non_specular()) {
             V3 ctxP = offset_ray_origin(isect.p, isect.pError, isect.n, isect.wo);  // reflective-only BSDF (vspg.cpp:1147-1149)
@@ -106,6 +110,7 @@ __global__ void __launch_bounds__(kBlock) k_shade(const DScene sc, const Wavefro
                 }
             }
         }
+        scatter_phase_sync<G>();
         ps.prevP = isect.p;
         V3 wo = -ps.ray.d;
         float u = ps.rng.uniform();
@@ -138,6 +143,7 @@ __global__ void __launch_bounds__(kBlock) k_shade(const DScene sc, const Wavefro
                 else ps.beta = ps.beta / (1 - q);
             }
         }
+        scatter_phase_sync<G>();
         const bool w = leader && live;
         if (w) {
             path_store(W.P, slot, ps);

@@ -12,23 +12,57 @@
 
 namespace vspg {
 
+// A medium whose sigma_a and sigma_s are equal across R, G and B ("gray": every BASELINE config except the rgbgrid of
+// C5) makes every spectral quantity of the reservoir walk -- sigma_maj, T_maj, trRatioEst, beta_rs, r_u_rs, the
+// selected candidate's numerator / denominator -- three copies of one float: each channel performs the identical
+// IEEE operation sequence.  G1 carries that one float; the GRAY kernel is bit-identical to the V3 kernel on such
+// scenes at a third of the arithmetic (16 -> 6 IEEE divisions, 9 -> 3 FastExp per collision) and ~20 fewer registers.
+struct G1 {
+    float v;
+    VD G1() : v(0) {}
+    VD explicit G1(float a) : v(a) {}
+    VD float operator[](int) const { return v; }
+};
+VD G1 operator*(G1 a, G1 b) { return G1(a.v * b.v); }
+VD G1 operator*(G1 a, float s) { return G1(a.v * s); }
+VD G1 operator*(float s, G1 a) { return G1(a.v * s); }
+VD G1 operator/(G1 a, G1 b) { return G1(a.v / b.v); }
+VD G1 operator/(G1 a, float s) { return G1(a.v / s); }
+VD G1 operator+(G1 a, G1 b) { return G1(a.v + b.v); }
+VD G1 operator-(G1 a, G1 b) { return G1(a.v - b.v); }
+VD G1 operator-(G1 a) { return G1(-a.v); }
+VD G1 clamp_zero(G1 a) { return G1(fmaxf(0.f, a.v)); }
+VD G1 fast_exp3(G1 a) { return G1(fast_exp(a.v)); }
+template <bool GRAY> struct SpecT { typedef V3 type; };
+template <> struct SpecT<true> { typedef G1 type; };
+template <bool GRAY> VD typename SpecT<GRAY>::type to_spec(V3 v);
+template <> VD V3 to_spec<false>(V3 v) { return v; }
+template <> VD G1 to_spec<true>(V3 v) { return G1(v.x); }
+VD V3 to_v3(V3 v) { return v; }
+VD V3 to_v3(G1 g) { return splat(g.v); }
+
 enum { RS_NEED_SEG = 1, RS_IN_SEG = 2, RS_DONE = 3 };
 
+template <bool GRAY>
 struct RsLane {
+    typedef typename SpecT<GRAY>::type Sp;
     int slot, phase;
     Ray ray;                             // normalised ray (media_sampleTMaj.h:55-56)
     MajorantIterator it;
     float majorantScale, volumeRatioComp;
     bool guide;
-    Segment seg; float tMin;
-    V3 T_maj; float u; Rng rng, prng;    // tracking RNG, path sampler
+    Sp segSigma; float segTMax, tMin;    // current majorant segment (sigma_maj already times majorantScale)
+    Sp T_maj; float u; Rng rng, prng;    // tracking RNG, path sampler
     int count, ch, medium;
     // reservoir (vspg.cpp:690-731)
     float weightSum, selWi, selG;
-    V3 trRatioEst, beta_rs, r_u_rs, selP, selNum, selDen;
+    Sp trRatioEst, beta_rs, r_u_rs, selNum, selDen;
+    V3 selP;
 };
 
-VD void rs_fetch(const DScene &sc, const Wavefront &W, int slot, RsLane &s, unsigned &ddaSteps) {
+template <bool GRAY>
+VD void rs_fetch(const DScene &sc, const Wavefront &W, int slot, RsLane<GRAY> &s, unsigned &ddaSteps) {
+    typedef typename SpecT<GRAY>::type Sp;
     const vspg_integrator_params &ip = sc.ip;
     float4 a = W.P.o_dx[slot], b = W.P.d_med[slot];
     ulonglong2 q = W.P.rng[slot];
@@ -61,9 +95,9 @@ VD void rs_fetch(const DScene &sc, const Wavefront &W, int slot, RsLane &s, unsi
     s.ray.d = normalize(s.ray.d);
     s.u = s.prng.uniform();
     s.weightSum = 0; s.selWi = 0; s.selG = 0;
-    s.trRatioEst = s.beta_rs = s.r_u_rs = splat(1.f);
-    s.selP = V3(); s.selNum = V3(); s.selDen = V3();
-    s.T_maj = splat(1.f);
+    s.trRatioEst = s.beta_rs = s.r_u_rs = to_spec<GRAY>(splat(1.f));
+    s.selP = V3(); s.selNum = Sp(); s.selDen = Sp();
+    s.T_maj = to_spec<GRAY>(splat(1.f));
     s.count = 0;
     ddaSteps += (unsigned)__float_as_int(pre.y);
     // media_sampleTMaj.h:166-181 with the pre-pass sum from k_intersect
@@ -85,10 +119,12 @@ VD void rs_fetch(const DScene &sc, const Wavefront &W, int slot, RsLane &s, unsi
 }
 
 // vspg.cpp:733-800: surface candidate, final pick, beta / r_u update; then hand-over to the next stage
-VD void rs_finalize(const DScene &sc, const Wavefront &W, RsLane &s) {
+template <bool GRAY>
+VD void rs_finalize(const DScene &sc, const Wavefront &W, RsLane<GRAY> &s) {
+    typedef typename SpecT<GRAY>::type Sp;
     const vspg_integrator_params &ip = sc.ip;
     const int ch = s.ch, slot = s.slot;
-    V3 T_maj = s.T_maj;
+    Sp T_maj = s.T_maj;
     s.beta_rs = s.beta_rs * (T_maj / T_maj[ch]);
     s.r_u_rs = s.r_u_rs * (T_maj / T_maj[ch]);
     float trS = s.trRatioEst[ch];
@@ -114,8 +150,8 @@ VD void rs_finalize(const DScene &sc, const Wavefront &W, RsLane &s) {
             else { b.w = __int_as_float(fl.pack()); W.P.d_med[slot] = b; }
         }
         if (!terminated) {
-            beta = beta * (s.selNum * rf);
-            r_u = r_u * s.selDen;
+            beta = beta * to_v3(s.selNum * rf);
+            r_u = r_u * to_v3(s.selDen);
             if (has_nan(beta) || has_nan(r_u) || y_is_inf(beta) || y_is_inf(r_u)) terminated = true;
             else scattered = !selectSurface;
         }
@@ -133,13 +169,52 @@ VD void rs_finalize(const DScene &sc, const Wavefront &W, RsLane &s) {
 
 constexpr int kRsRefillIdle = 8;    // fetch new rays once this many lanes of the warp are idle
 constexpr int kRsTripsPerCheck = 4; // collisions between two refill checks
+constexpr int kRsSearchMax = 4;     // search steps before the collision body runs for the lanes that are ready
 
-__global__ void __launch_bounds__(kBlock) k_medium_rs(const DScene sc, const Wavefront W, int *cursor) {
+// One search step of media_sampleTMaj.h:183-246 for one lane, straight-line: (A) if the lane needs a majorant segment,
+// pull the next one from the DDA; (B) if it is inside a segment, draw the next exponential step.  Returns with `hit`
+// set when a tentative collision at `t` lies inside the segment.
+template <bool GRAY>
+VD void rs_search_step(RsLane<GRAY> &s, float &t, bool &hit) {
+    const int ch = s.ch;
+    if (s.phase == RS_NEED_SEG) {
+        Segment seg;
+        if (!s.it.next(&seg)) s.phase = RS_DONE;                        // T_maj = residual transmittance
+        else {
+            typename SpecT<GRAY>::type sm = to_spec<GRAY>(seg.sigma_maj) * s.majorantScale;
+            if (sm[ch] == 0) {
+                float dt = seg_dt(seg.tMax, seg.tMin);
+                s.T_maj = s.T_maj * fast_exp3(-dt * sm);
+            } else { s.segSigma = sm; s.segTMax = seg.tMax; s.tMin = seg.tMin; s.phase = RS_IN_SEG; }
+        }
+    }
+    if (s.phase == RS_IN_SEG) {
+        s.count++;
+        t = s.tMin + sample_exponential(s.u, s.segSigma[ch]);
+        s.u = s.rng.uniform();
+        if (t < s.segTMax) {
+            if (s.count > 10000) s.phase = RS_NEED_SEG;                 // media_sampleTMaj.h:216-219 leaves the segment
+            else hit = true;
+        } else {
+            float dt = seg_dt(s.segTMax, s.tMin);
+            s.T_maj = s.T_maj * fast_exp3(-dt * s.segSigma);
+            s.phase = RS_NEED_SEG;
+        }
+    }
+}
+
+// The whole warp runs every loop below (idle lanes carry phase == RS_DONE and do nothing), so the votes are full-warp.
+// Per trip: up to kRsSearchMax search steps, leaving early as soon as at least half of the lanes still walking have a
+// collision ready; then the collision body, predicated on `hit`.  Bounding the search keeps both halves of the trip
+// above ~60 % lane utilisation (an unbounded search ran at 7 lanes of 32, profiles/r01c).
+template <bool GRAY>
+__global__ void __launch_bounds__(kBlock, GRAY ? 5 : 4) k_medium_rs(const DScene sc, const Wavefront W, int *cursor) {
+    typedef typename SpecT<GRAY>::type Sp;
     const int n = *W.medium_rs.count;
     const int lane = threadIdx.x & 31;
     TrackCounters tc; tc.queries = 0; tc.dda = 0;
-    RsLane s;
-    s.phase = RS_DONE; s.it.init_empty();
+    RsLane<GRAY> s;
+    s.phase = RS_DONE; s.it.init_empty(); s.medium = 0; s.ch = 0;
     bool busy = false, drained = false;
     while (true) {
         __syncwarp();
@@ -151,80 +226,61 @@ __global__ void __launch_bounds__(kBlock) k_medium_rs(const DScene sc, const Wav
             if (base + nIdle >= n) drained = true;
             if (!busy) {
                 int idx = base + __popc(idle & ((1u << lane) - 1));
-                if (idx < n) { rs_fetch(sc, W, W.medium_rs.items[idx], s, tc.dda); busy = true; }
+                if (idx < n) { rs_fetch<GRAY>(sc, W, W.medium_rs.items[idx], s, tc.dda); busy = true; }
             }
             __syncwarp();
             idle = __ballot_sync(kFull, !busy);
         }
         if (idle == kFull) { if (drained) break; else continue; }
-        if (busy) {
-            const DMedium &med = sc.media[s.medium];
-            const int ch = s.ch;
+        const int ch = s.ch;
 #pragma unroll 1
-            for (int trip = 0; trip < kRsTripsPerCheck; trip++) {
-                // ---- (1) light: advance to the next tentative collision inside the medium (or the end of the ray)
-                float t = 0;
-                bool hit = false;
+        for (int trip = 0; trip < kRsTripsPerCheck; trip++) {
+            // ---- (1) advance towards the next tentative collision inside the medium (or the end of the ray)
+            float t = 0;
+            bool hit = false;
 #pragma unroll 1
-                while (s.phase != RS_DONE && !hit) {
-                    if (s.phase == RS_NEED_SEG) {
-                        Segment seg;
-                        if (!s.it.next(&seg)) { s.phase = RS_DONE; break; }     // T_maj = residual transmittance
-                        seg.sigma_maj = seg.sigma_maj * s.majorantScale;
-                        if (seg.sigma_maj[ch] == 0) {
-                            float dt = seg_dt(seg.tMax, seg.tMin);
-                            s.T_maj = s.T_maj * fast_exp3(-dt * seg.sigma_maj);
-                            continue;
-                        }
-                        s.seg = seg; s.tMin = seg.tMin; s.phase = RS_IN_SEG;
-                    }
-                    s.count++;
-                    t = s.tMin + sample_exponential(s.u, s.seg.sigma_maj[ch]);
-                    s.u = s.rng.uniform();
-                    if (t < s.seg.tMax) {
-                        if (s.count > 10000) s.phase = RS_NEED_SEG;   // media_sampleTMaj.h:216-219 leaves the segment
-                        else hit = true;
-                    } else {
-                        float dt = seg_dt(s.seg.tMax, s.tMin);
-                        s.T_maj = s.T_maj * fast_exp3(-dt * s.seg.sigma_maj);
-                        s.phase = RS_NEED_SEG;
-                    }
-                }
-                // ---- (2) heavy, branch-free: density fetch + reservoir callback (vspg.cpp:690-731)
-                if (hit) {
-                    V3 T_maj = s.T_maj * fast_exp3(-(t - s.tMin) * s.seg.sigma_maj);
-                    V3 p = s.ray.at(t);
-                    MediumProps mp = sample_point(med, p);
-                    tc.queries++;
-                    V3 sigma_maj = s.seg.sigma_maj;
-                    V3 sigma_t = mp.sigma_s + mp.sigma_a;
-                    V3 sigma_n = clamp_zero(sigma_maj - sigma_t);
-                    float wi = (sigma_t / sigma_maj * s.trRatioEst)[ch];
-                    const bool cand = wi > 0;
-                    Rng pr = s.prng;                        // the reservoir draw happens only for wi > 0 (:699-702)
-                    float ur = pr.uniform();
-                    float ws = s.weightSum + wi;
-                    if (cand) { s.prng = pr; s.weightSum = ws; }
-                    const bool take = cand && (ur < wi / ws);
-                    float pdfT = T_maj[ch] * sigma_t[ch];
-                    V3 num = s.beta_rs * T_maj * mp.sigma_s / pdfT;
-                    V3 den = s.r_u_rs * T_maj * sigma_t / pdfT;
-                    if (take) { s.selP = p; s.selG = mp.g; s.selWi = wi; s.selNum = num; s.selDen = den; }
-                    float pdf = T_maj[ch] * sigma_n[ch];
-                    V3 f = T_maj * sigma_n / pdf;
-                    s.beta_rs = s.beta_rs * f;
-                    s.r_u_rs = s.r_u_rs * f;
-                    s.trRatioEst = s.trRatioEst * (sigma_n / sigma_maj);
-                    s.T_maj = splat(1.f);
-                    s.tMin = t;
-                }
-                if (s.phase == RS_DONE) break;
+            for (int j = 0; j < kRsSearchMax; j++) {
+                if (s.phase != RS_DONE && !hit) rs_search_step<GRAY>(s, t, hit);
+                unsigned hits = __ballot_sync(kFull, hit);
+                unsigned walking = __ballot_sync(kFull, s.phase != RS_DONE && !hit);
+                if (2 * __popc(hits) >= __popc(hits | walking)) break;
             }
-            if (s.phase == RS_DONE) {
-                tc.dda += s.it.steps;
-                rs_finalize(sc, W, s);
-                busy = false;
+            // ---- (2) density fetch + reservoir callback (vspg.cpp:690-731)
+            if (hit) {
+                const DMedium &med = sc.media[s.medium];
+                Sp T_maj = s.T_maj * fast_exp3(-(t - s.tMin) * s.segSigma);
+                V3 p = s.ray.at(t);
+                MediumProps mp = sample_point(med, p);
+                tc.queries++;
+                Sp sigma_maj = s.segSigma;
+                Sp sigma_s = to_spec<GRAY>(mp.sigma_s);
+                Sp sigma_t = sigma_s + to_spec<GRAY>(mp.sigma_a);
+                Sp sigma_n = clamp_zero(sigma_maj - sigma_t);
+                float wi = (sigma_t / sigma_maj * s.trRatioEst)[ch];
+                const bool cand = wi > 0;
+                Rng pr = s.prng;                        // the reservoir draw happens only for wi > 0 (:699-702)
+                float ur = pr.uniform();
+                float ws = s.weightSum + wi;
+                if (cand) { s.prng = pr; s.weightSum = ws; }
+                const bool take = cand && (ur < wi / ws);
+                float pdfT = T_maj[ch] * sigma_t[ch];
+                Sp num = s.beta_rs * T_maj * sigma_s / pdfT;
+                Sp den = s.r_u_rs * T_maj * sigma_t / pdfT;
+                if (take) { s.selP = p; s.selG = mp.g; s.selWi = wi; s.selNum = num; s.selDen = den; }
+                float pdf = T_maj[ch] * sigma_n[ch];
+                Sp f = T_maj * sigma_n / pdf;
+                s.beta_rs = s.beta_rs * f;
+                s.r_u_rs = s.r_u_rs * f;
+                s.trRatioEst = s.trRatioEst * (sigma_n / sigma_maj);
+                s.T_maj = to_spec<GRAY>(splat(1.f));
+                s.tMin = t;
             }
+            if (__any_sync(kFull, busy && s.phase == RS_DONE)) break;
+        }
+        if (busy && s.phase == RS_DONE) {
+            tc.dda += s.it.steps;
+            rs_finalize<GRAY>(sc, W, s);
+            busy = false;
         }
     }
     counter_add(W.counters, CNT_QUERIES, tc.queries);

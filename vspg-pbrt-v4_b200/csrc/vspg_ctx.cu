@@ -35,6 +35,8 @@ struct vspg_ctx {
     unsigned long long launches = 0, iterations = 0;
     int film_w = 0, film_h = 0;
     int grid_layout = GRID_CELL8;
+    int scatter_block = 256;   // VSPG_SCATTER_BLOCK overrides (A/B runs)
+    bool all_gray = false;        // every medium has sigma_a / sigma_s equal across RGB => scalar tracking kernels (kmedium_rs.cuh)
     // timing (vspg_kernel_stats_get)
     bool timing = false;
     cudaEvent_t ev[VSPG_K_COUNT + 1] = {};
@@ -100,6 +102,7 @@ int vspg_create(vspg_ctx **out, int device_ordinal) {
     if (cudaGetDeviceProperties(&prop, device_ordinal) == cudaSuccess) ctx->sm_count = prop.multiProcessorCount;
     vspg_integrator_defaults(&ctx->sc.ip);
     ctx->sc.ip.light_sampler = VSPG_LIGHTSAMPLER_UNIFORM;
+    if (const char *sb = getenv("VSPG_SCATTER_BLOCK")) { int v = atoi(sb); if (v >= 32 && v <= kScatterBlock && v % 32 == 0) ctx->scatter_block = v; }
     const char *lay = getenv("VSPG_GRID_LAYOUT");
     if (lay && std::string(lay) == "linear") ctx->grid_layout = GRID_LINEAR;
     *out = ctx;
@@ -174,6 +177,10 @@ int vspg_set_scene(vspg_ctx *ctx, const vspg_scene_desc *s) {
     }
     CK(upload(ctx->scene_allocs, media.data(), media.size(), &sc.media));
     sc.n_media = s->n_media;
+    ctx->all_gray = !getenv("VSPG_NO_GRAY");
+    for (const DMedium &d : media)
+        if (d.type == VSPG_MEDIUM_RGBGRID || d.sigma_a[0] != d.sigma_a[1] || d.sigma_a[0] != d.sigma_a[2] || d.sigma_s[0] != d.sigma_s[1] || d.sigma_s[0] != d.sigma_s[2])
+            ctx->all_gray = false;
     // ---- quads + BVH
     std::vector<DQuad> quads(s->n_quads);
     float bmin[3] = {INFINITY, INFINITY, INFINITY}, bmax[3] = {-INFINITY, -INFINITY, -INFINITY};

@@ -69,6 +69,7 @@ int vspg_render(vspg_ctx *ctx, int spp_begin, int spp_end, int spp_stride, int x
     CK(cudaMemsetAsync(ctx->qcounts, 0, Q_INTS * sizeof(int), st));
     CK(cudaMemsetAsync(W.next_sample, 0, sizeof(unsigned long long), st));
     const int grid = ctx->sm_count * 8;
+    const int sblock = ctx->scatter_block, sgrid = ctx->sm_count * std::max(1, 512 / sblock);   // lane-group scatter kernels (kernels.cuh GroupIter)
     const bool guidedVol = sc.vol.present, guidedSurf = sc.surf.present;
     int nslots = (int)std::min<unsigned long long>((unsigned long long)ctx->capacity, total);
     W.active = qa; W.next = qb;
@@ -88,21 +89,22 @@ int vspg_render(vspg_ctx *ctx, int spp_begin, int spp_end, int spp_stride, int x
     while (true) {
         if (timing) CK(cudaEventRecord(ctx->ev[0], st));
         VSPG_STAGE(VSPG_K_INTERSECT, (k_intersect<<<grid, kBlock, 0, st>>>(sc, W)));
-        k_medium_rs<<<ctx->sm_count * 4, kBlock, 0, st>>>(sc, W, ctx->qcounts + Q_COUNT);
+        if (ctx->all_gray) k_medium_rs<true><<<ctx->sm_count * 5, kBlock, 0, st>>>(sc, W, ctx->qcounts + Q_COUNT);
+        else k_medium_rs<false><<<ctx->sm_count * 4, kBlock, 0, st>>>(sc, W, ctx->qcounts + Q_COUNT);
         VSPG_STAGE(VSPG_K_MEDIUM, (k_medium<<<grid, kBlock, 0, st>>>(sc, W)));
         if (guidedVol) {
             k_lookup<false><<<grid, kBlock, 0, st>>>(sc, W, W.volscatter, W.vol8, W.vol16, W.vol32);
-            k_volscatter<8><<<grid, kBlock, 0, st>>>(sc, W, W.vol8);
-            k_volscatter<16><<<grid, kBlock, 0, st>>>(sc, W, W.vol16);
-            VSPG_STAGE(VSPG_K_VOLSCATTER, (k_volscatter<32><<<grid, kBlock, 0, st>>>(sc, W, W.vol32)));
+            k_volscatter<8><<<sgrid, sblock, 0, st>>>(sc, W, W.vol8);
+            k_volscatter<16><<<sgrid, sblock, 0, st>>>(sc, W, W.vol16);
+            VSPG_STAGE(VSPG_K_VOLSCATTER, (k_volscatter<32><<<sgrid, sblock, 0, st>>>(sc, W, W.vol32)));
             ctx->launches += 3;
         } else VSPG_STAGE(VSPG_K_VOLSCATTER, (k_volscatter<0><<<grid, kBlock, 0, st>>>(sc, W, W.volscatter)));
         VSPG_STAGE(VSPG_K_SURFACE, (k_surface<<<grid, kBlock, 0, st>>>(sc, W)));
         if (guidedSurf) {
             k_lookup<true><<<grid, kBlock, 0, st>>>(sc, W, W.shade, W.sh8, W.sh16, W.sh32);
-            k_shade<8><<<grid, kBlock, 0, st>>>(sc, W, W.sh8);
-            k_shade<16><<<grid, kBlock, 0, st>>>(sc, W, W.sh16);
-            VSPG_STAGE(VSPG_K_SHADE, (k_shade<32><<<grid, kBlock, 0, st>>>(sc, W, W.sh32)));
+            k_shade<8><<<sgrid, sblock, 0, st>>>(sc, W, W.sh8);
+            k_shade<16><<<sgrid, sblock, 0, st>>>(sc, W, W.sh16);
+            VSPG_STAGE(VSPG_K_SHADE, (k_shade<32><<<sgrid, sblock, 0, st>>>(sc, W, W.sh32)));
             ctx->launches += 3;
         } else VSPG_STAGE(VSPG_K_SHADE, (k_shade<0><<<grid, kBlock, 0, st>>>(sc, W, W.shade)));
         VSPG_STAGE(VSPG_K_SHADOW, (k_shadow<<<grid, kBlock, 0, st>>>(sc, W)));
