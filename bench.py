@@ -219,6 +219,7 @@ def run_b200(args):
     torch.cuda.set_device(local)
     if world > 1:
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")   # keep stdout to the one JSON line ("NCCL version ..." goes to stderr)
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
 
     def barrier():
