@@ -18,6 +18,7 @@ struct Hit {
     float t = Infinity;
     int kind = 0, index = -1;  // 0 quad, 1 triangle, 2 sphere
     float u = 0, v = 0;
+    float b[3] = {0, 0, 0};  // triangle barycentrics (TriangleIntersection)
 };
 
 // Surface interaction data the integrator consumes (interaction.h SurfaceInteraction subset)
@@ -105,6 +106,55 @@ inline bool IntersectBilinearPatch(V3 ro, V3 rd, float tMax, V3 p00, V3 p10, V3 
     return true;
 }
 
+// shapes.cpp:168-263 IntersectTriangle
+inline bool IntersectTriangle(V3 ro, V3 rd, float tMax, V3 p0, V3 p1, V3 p2, float *b, float *to) {
+    if (LengthSquared(Cross(p2 - p0, p1 - p0)) == 0) return false;
+    V3 p0t = p0 - ro, p1t = p1 - ro, p2t = p2 - ro;
+    V3 ad = Abs(rd);
+    int kz = (ad.x > ad.y) ? ((ad.x > ad.z) ? 0 : 2) : ((ad.y > ad.z) ? 1 : 2);
+    int kx = kz + 1; if (kx == 3) kx = 0;
+    int ky = kx + 1; if (ky == 3) ky = 0;
+    V3 d(rd[kx], rd[ky], rd[kz]);
+    p0t = V3(p0t[kx], p0t[ky], p0t[kz]); p1t = V3(p1t[kx], p1t[ky], p1t[kz]); p2t = V3(p2t[kx], p2t[ky], p2t[kz]);
+    float Sx = -d.x / d.z, Sy = -d.y / d.z, Sz = 1 / d.z;
+    p0t.x += Sx * p0t.z; p0t.y += Sy * p0t.z;
+    p1t.x += Sx * p1t.z; p1t.y += Sy * p1t.z;
+    p2t.x += Sx * p2t.z; p2t.y += Sy * p2t.z;
+    float e0 = DifferenceOfProducts(p1t.x, p2t.y, p1t.y, p2t.x);
+    float e1 = DifferenceOfProducts(p2t.x, p0t.y, p2t.y, p0t.x);
+    float e2 = DifferenceOfProducts(p0t.x, p1t.y, p0t.y, p1t.x);
+    if (e0 == 0.0f || e1 == 0.0f || e2 == 0.0f) {
+        double p2txp1ty = (double)p2t.x * (double)p1t.y, p2typ1tx = (double)p2t.y * (double)p1t.x;
+        e0 = (float)(p2typ1tx - p2txp1ty);
+        double p0txp2ty = (double)p0t.x * (double)p2t.y, p0typ2tx = (double)p0t.y * (double)p2t.x;
+        e1 = (float)(p0typ2tx - p0txp2ty);
+        double p1txp0ty = (double)p1t.x * (double)p0t.y, p1typ0tx = (double)p1t.y * (double)p0t.x;
+        e2 = (float)(p1typ0tx - p1txp0ty);
+    }
+    if ((e0 < 0 || e1 < 0 || e2 < 0) && (e0 > 0 || e1 > 0 || e2 > 0)) return false;
+    float det = e0 + e1 + e2;
+    if (det == 0) return false;
+    p0t.z *= Sz; p1t.z *= Sz; p2t.z *= Sz;
+    float tScaled = e0 * p0t.z + e1 * p1t.z + e2 * p2t.z;
+    if (det < 0 && (tScaled >= 0 || tScaled < tMax * det)) return false;
+    else if (det > 0 && (tScaled <= 0 || tScaled > tMax * det)) return false;
+    float invDet = 1 / det;
+    float b0 = e0 * invDet, b1 = e1 * invDet, b2 = e2 * invDet;
+    float t = tScaled * invDet;
+    float maxZt = MaxComponentValue(Abs(V3(p0t.z, p1t.z, p2t.z)));
+    float deltaZ = gamma_(3) * maxZt;
+    float maxXt = MaxComponentValue(Abs(V3(p0t.x, p1t.x, p2t.x)));
+    float maxYt = MaxComponentValue(Abs(V3(p0t.y, p1t.y, p2t.y)));
+    float deltaX = gamma_(5) * (maxXt + maxZt);
+    float deltaY = gamma_(5) * (maxYt + maxZt);
+    float deltaE = 2 * (gamma_(2) * maxXt * maxYt + deltaY * maxXt + deltaX * maxYt);
+    float maxE = MaxComponentValue(Abs(V3(e0, e1, e2)));
+    float deltaT = 3 * (gamma_(3) * maxE * maxZt + deltaE * maxZt + deltaZ * maxE) * std::abs(invDet);
+    if (t <= deltaT) return false;
+    b[0] = b0; b[1] = b1; b[2] = b2; *to = t;
+    return true;
+}
+
 struct LightSampleCtx { V3 p, pError, n, ns; };
 
 struct Scene {
@@ -131,9 +181,14 @@ struct Scene {
             for (V3 p : {p00, p10, p01, p11})
                 for (int a = 0; a < 3; a++) { bmin[a] = std::min(bmin[a], p[a]); bmax[a] = std::max(bmax[a], p[a]); }
         }
+        for (int i = 0; i < d->n_triangles; i++) {
+            const vspg_triangle &t = d->triangles[i];
+            for (V3 p : {V3(t.p0), V3(t.p1), V3(t.p2)})
+                for (int a = 0; a < 3; a++) { bmin[a] = std::min(bmin[a], p[a]); bmax[a] = std::max(bmax[a], p[a]); }
+        }
         // Bounds3::BoundingSphere: center = (pMin+pMax)/2, radius = Inside(center) ? Distance(center, pMax) : 0
         sceneCenter = (bmin + bmax) / 2;
-        sceneRadius = d->n_quads ? Distance(sceneCenter, bmax) : 0;
+        sceneRadius = (d->n_quads + d->n_triangles) ? Distance(sceneCenter, bmax) : 0;
         // PowerLightSampler pmf (lightsamplers.cpp:76-96): phi averaged over RGB
         lightCdf.assign(d->n_lights, 0.f);
         float sum = 0;
@@ -190,12 +245,50 @@ struct Scene {
                 best = t; h.valid = true; h.t = t; h.kind = 0; h.index = i; h.u = u; h.v = v;
             }
         }
+        // triangles: tested against the ray's own tMax, then compared with the closest hit so far (closest-hit
+        // semantics of the aggregate; the product's BVH does the same)
+        for (int i = 0; i < d->n_triangles; i++) {
+            const vspg_triangle &q = d->triangles[i];
+            float b[3], t;
+            if (IntersectTriangle(ro, rd, tMax, V3(q.p0), V3(q.p1), V3(q.p2), b, &t) && t < best) {
+                best = t; h.valid = true; h.t = t; h.kind = 1; h.index = i; h.u = b[0]; h.v = b[1];
+                h.b[0] = b[0]; h.b[1] = b[1]; h.b[2] = b[2];
+            }
+        }
         return h;
     }
     // shapes.h:1398-1500 BilinearPatch::InteractionFromIntersection (no mesh uv / normals) + primitive.cpp
     // GeometricPrimitive::Intersect -> SetIntersectionProperties (interaction.h:218-229)
+    int HitMaterial(const Hit &h) const { return h.kind == 1 ? d->triangles[h.index].material : d->quads[h.index].material; }
     SurfaceIntr MakeIntr(const Hit &h, V3 rayD, int rayMedium) const {
         SurfaceIntr s;
+        if (h.kind == 1) {  // shapes.h:884-945 Triangle::InteractionFromIntersection, default uvs, no mesh normals
+            const vspg_triangle &q = d->triangles[h.index];
+            V3 p0(q.p0), p1(q.p1), p2(q.p2);
+            V3 dp02 = p0 - p2, dp12 = p1 - p2;
+            const float duv02[2] = {-1, -1}, duv12[2] = {0, -1};
+            float determinant = DifferenceOfProducts(duv02[0], duv12[1], duv02[1], duv12[0]);
+            float invdet = 1 / determinant;
+            V3 dpdu = V3(DifferenceOfProducts(duv12[1], dp02.x, duv02[1], dp12.x), DifferenceOfProducts(duv12[1], dp02.y, duv02[1], dp12.y),
+                         DifferenceOfProducts(duv12[1], dp02.z, duv02[1], dp12.z)) * invdet;
+            V3 dpdv = V3(DifferenceOfProducts(duv02[0], dp12.x, duv12[0], dp02.x), DifferenceOfProducts(duv02[0], dp12.y, duv12[0], dp02.y),
+                         DifferenceOfProducts(duv02[0], dp12.z, duv12[0], dp02.z)) * invdet;
+            if (LengthSquared(Cross(dpdu, dpdv)) == 0) {
+                V3 ng = Cross(p2 - p0, p1 - p0);
+                CoordinateSystem(Normalize(ng), &dpdu, &dpdv);
+            }
+            s.p = h.b[0] * p0 + h.b[1] * p1 + h.b[2] * p2;
+            s.pError = gamma_(7) * (Abs(h.b[0] * p0) + Abs(h.b[1] * p1) + Abs(h.b[2] * p2));
+            s.n = Normalize(Cross(dp02, dp12));
+            if (q.flip_normal) s.n = -s.n;
+            s.ns = s.n; s.dpdu = dpdu;
+            s.wo = Normalize(-rayD);
+            s.uv[0] = h.b[1] + h.b[2]; s.uv[1] = h.b[2];
+            s.material = q.material; s.areaLight = q.area_light;
+            s.hasInterface = q.has_interface && (q.medium_inside != q.medium_outside);
+            s.mediumInside = q.medium_inside; s.mediumOutside = q.medium_outside; s.rayMedium = rayMedium;
+            return s;
+        }
         const vspg_quad &q = d->quads[h.index];
         V3 p00(q.p00), p10(q.p10), p01(q.p01), p11(q.p11);
         s.p = LerpV(h.u, LerpV(h.v, p00, p01), LerpV(h.v, p10, p11));
@@ -579,7 +672,7 @@ struct Integrator {
         cnt.shadow++;
         while (lightRay.d != V3(0, 0, 0)) {
             Hit h = sc->Intersect(lightRay.o, lightRay.d, 1 - ShadowEpsilon);
-            if (h.valid && sc->d->quads[h.index].material >= 0) return S3(0.f);
+            if (h.valid && sc->HitMaterial(h) >= 0) return S3(0.f);
             if (lightRay.medium >= 0) {
                 float tMax = h.valid ? h.t : (1 - ShadowEpsilon);
                 float uu = rng.Uniform();

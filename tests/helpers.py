@@ -11,6 +11,8 @@ def small(name, **kw):
     """The BASELINE configs at sizes the CPU oracle finishes in seconds."""
     if name == "C1":
         return configs.config1(res=kw.get("res", 48), spp=kw.get("spp", 4))
+    if name == "C1T":
+        return configs.config1_triangles(res=kw.get("res", 48), spp=kw.get("spp", 4))
     common = dict(grid_n=kw.get("grid_n", 32), vol_leaves=kw.get("vol_leaves", 256), surf_leaves=kw.get("surf_leaves", 128))
     if name == "C2":
         return configs.config2(res=kw.get("res", 48), spp=kw.get("spp", 4), **common)

@@ -40,6 +40,8 @@ def assert_descs_equal(d, e):
             assert x == y, n
     for i in range(d.n_quads):
         assert raw(d.quads[i]) == raw(e.quads[i]), f"quad {i}"
+    for i in range(d.n_triangles):
+        assert raw(d.triangles[i]) == raw(e.triangles[i]), f"triangle {i}"
     for i in range(d.n_materials):
         assert raw(d.materials[i]) == raw(e.materials[i]), f"material {i}"
     for i in range(d.n_lights):
@@ -90,11 +92,11 @@ def write_exr(path, channels):
 
 
 # ------------------------------------------------------------------ descs
-@pytest.mark.parametrize("name", ["C1", "C2-unguided", "C5-unguided"])
+@pytest.mark.parametrize("name", ["C1", "C1T", "C2-unguided", "C5-unguided"])
 def test_front_end_reproduces_the_harness_descs(name, tmp_path):
     base = name.split("-")[0]
     cfg = H.small(base, grid_n=8)
-    if base != "C1":   # guiding inputs come from files in the scene language: covered by the next test
+    if not base.startswith("C1"):   # guiding inputs come from files in the scene language: covered by the next test
         cfg.ip.surface_guiding = cfg.ip.volume_guiding = cfg.ip.vsp_guiding = 0
     path = pbrt_writer.write_scene(cfg, str(tmp_path / "scene.pbrt"), seed=3, raw_density=(base == "C2"))
     hs = api.HostScene(path=path)

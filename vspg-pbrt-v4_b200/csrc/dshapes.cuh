@@ -91,11 +91,63 @@ VD bool intersect_bilinear_patch(V3 ro, V3 rd, V3 p00, V3 p10, V3 p01, V3 p11, f
     return true;
 }
 
+
+// shapes.cpp:168-263 IntersectTriangle (watertight: permute, shear, edge functions with the double-precision
+// fallback at edges, conservative t > deltaT).  Returns barycentrics and t; the caller compares t with its closest hit.
+VD bool intersect_triangle(V3 ro, V3 rd, float tMax, V3 p0, V3 p1, V3 p2, float *b0o, float *b1o, float *b2o, float *to) {
+    if (length_sq(cross(p2 - p0, p1 - p0)) == 0) return false;
+    V3 p0t = p0 - ro, p1t = p1 - ro, p2t = p2 - ro;
+    V3 ad = vabs(rd);
+    int kz = (ad.x > ad.y) ? ((ad.x > ad.z) ? 0 : 2) : ((ad.y > ad.z) ? 1 : 2);   // util/vecmath.h MaxComponentIndex
+    int kx = kz + 1; if (kx == 3) kx = 0;
+    int ky = kx + 1; if (ky == 3) ky = 0;
+    V3 d(rd[kx], rd[ky], rd[kz]);
+    p0t = V3(p0t[kx], p0t[ky], p0t[kz]); p1t = V3(p1t[kx], p1t[ky], p1t[kz]); p2t = V3(p2t[kx], p2t[ky], p2t[kz]);
+    float Sx = -d.x / d.z, Sy = -d.y / d.z, Sz = 1 / d.z;
+    p0t.x += Sx * p0t.z; p0t.y += Sy * p0t.z;
+    p1t.x += Sx * p1t.z; p1t.y += Sy * p1t.z;
+    p2t.x += Sx * p2t.z; p2t.y += Sy * p2t.z;
+    float e0 = diff_of_products(p1t.x, p2t.y, p1t.y, p2t.x);
+    float e1 = diff_of_products(p2t.x, p0t.y, p2t.y, p0t.x);
+    float e2 = diff_of_products(p0t.x, p1t.y, p0t.y, p1t.x);
+    if (e0 == 0.0f || e1 == 0.0f || e2 == 0.0f) {
+        double p2txp1ty = (double)p2t.x * (double)p1t.y, p2typ1tx = (double)p2t.y * (double)p1t.x;
+        e0 = (float)(p2typ1tx - p2txp1ty);
+        double p0txp2ty = (double)p0t.x * (double)p2t.y, p0typ2tx = (double)p0t.y * (double)p2t.x;
+        e1 = (float)(p0typ2tx - p0txp2ty);
+        double p1txp0ty = (double)p1t.x * (double)p0t.y, p1typ0tx = (double)p1t.y * (double)p0t.x;
+        e2 = (float)(p1typ0tx - p1txp0ty);
+    }
+    if ((e0 < 0 || e1 < 0 || e2 < 0) && (e0 > 0 || e1 > 0 || e2 > 0)) return false;
+    float det = e0 + e1 + e2;
+    if (det == 0) return false;
+    p0t.z *= Sz; p1t.z *= Sz; p2t.z *= Sz;
+    float tScaled = e0 * p0t.z + e1 * p1t.z + e2 * p2t.z;
+    if (det < 0 && (tScaled >= 0 || tScaled < tMax * det)) return false;
+    else if (det > 0 && (tScaled <= 0 || tScaled > tMax * det)) return false;
+    float invDet = 1 / det;
+    float b0 = e0 * invDet, b1 = e1 * invDet, b2 = e2 * invDet;
+    float t = tScaled * invDet;
+    float maxZt = max_comp(vabs(V3(p0t.z, p1t.z, p2t.z)));
+    float deltaZ = gammaN(3) * maxZt;
+    float maxXt = max_comp(vabs(V3(p0t.x, p1t.x, p2t.x)));
+    float maxYt = max_comp(vabs(V3(p0t.y, p1t.y, p2t.y)));
+    float deltaX = gammaN(5) * (maxXt + maxZt);
+    float deltaY = gammaN(5) * (maxYt + maxZt);
+    float deltaE = 2 * (gammaN(2) * maxXt * maxYt + deltaY * maxXt + deltaX * maxYt);
+    float maxE = max_comp(vabs(V3(e0, e1, e2)));
+    float deltaT = 3 * (gammaN(3) * maxE * maxZt + deltaE * maxZt + deltaZ * maxE) * fabsf(invDet);
+    if (t <= deltaT) return false;
+    *b0o = b0; *b1o = b1; *b2o = b2; *to = t;
+    return true;
+}
+
 // Closest hit: stackless walk over the DFS-ordered threaded BVH.  Box test is the conservative slab test of
 // util/vecmath.h:1574 (tFar widened by 1+2*gamma(3)) so no hit of the brute-force reference order is lost;
 // ties in t go to the lower primitive index (= first primitive in scene order, as a linear scan would keep).
 VD Hit scene_intersect(const DScene &sc, V3 ro, V3 rd, float tMax, unsigned &nodesVisited) {
     Hit h; h.t = tMax; h.prim = -1; h.u = h.v = 0;
+    const float rayTMax = tMax;
     V3 inv(1 / rd.x, 1 / rd.y, 1 / rd.z);
     int node = 0;
     const int n = sc.n_bvh;
@@ -129,10 +181,10 @@ VD Hit scene_intersect(const DScene &sc, V3 ro, V3 rd, float tMax, unsigned &nod
             for (int i = 0; i < primCount; i++) {
                 int q = __ldg(&sc.prim_ids[primBegin + i]);
                 const DQuad &Q = sc.quads[q];
-                float u, v, t;
-                if (intersect_bilinear_patch(ro, rd, ld3(Q.p00), ld3(Q.p10), ld3(Q.p01), ld3(Q.p11), &u, &v, &t)) {
-                    if (t < h.t || (t == h.t && h.prim >= 0 && q < h.prim)) { h.t = t; h.u = u; h.v = v; h.prim = q; }
-                }
+                float u, v, t, b2;
+                bool got = Q.kind == PRIM_TRIANGLE ? intersect_triangle(ro, rd, rayTMax, ld3(Q.p00), ld3(Q.p10), ld3(Q.p01), &u, &v, &b2, &t)
+                                                   : intersect_bilinear_patch(ro, rd, ld3(Q.p00), ld3(Q.p10), ld3(Q.p01), ld3(Q.p11), &u, &v, &t);
+                if (got && (t < h.t || (t == h.t && h.prim >= 0 && q < h.prim))) { h.t = t; h.u = u; h.v = v; h.prim = q; }
             }
             node = skip;
         } else node = node + 1;
@@ -141,10 +193,36 @@ VD Hit scene_intersect(const DScene &sc, V3 ro, V3 rd, float tMax, unsigned &nod
 }
 
 // shapes.h:1398-1500 BilinearPatch::InteractionFromIntersection (no mesh uv / normals) + interaction.h:218-229
-VD SurfaceIntr make_intr(const DScene &sc, const Hit &h, V3 rayD, int rayMedium) {
+// Triangles: shapes.h:884-945 Triangle::InteractionFromIntersection with the default (0,0),(1,0),(1,1) uvs and no
+// mesh normals; the barycentrics are recomputed from the ray (the hit record carries t, b0, b1 only).
+VD SurfaceIntr make_intr(const DScene &sc, const Hit &h, V3 rayO, V3 rayD, int rayMedium) {
     SurfaceIntr s;
     const DQuad &q = sc.quads[h.prim];
     V3 p00 = ld3(q.p00), p10 = ld3(q.p10), p01 = ld3(q.p01), p11 = ld3(q.p11);
+    if (q.kind == PRIM_TRIANGLE) {
+        V3 p0 = p00, p1 = p10, p2 = p01;
+        float b0 = h.u, b1 = h.v, b2 = 0, t;
+        intersect_triangle(rayO, rayD, inff(), p0, p1, p2, &b0, &b1, &b2, &t);
+        V3 dp02 = p0 - p2, dp12 = p1 - p2;
+        // duv02 = (-1,-1), duv12 = (0,-1), determinant 1: DifferenceOfProducts collapses to one rounding per component
+        V3 dpdu(fmaf(-1.f, dp02.x, dp12.x), fmaf(-1.f, dp02.y, dp12.y), fmaf(-1.f, dp02.z, dp12.z));
+        V3 dpdv = -dp12;
+        if (length_sq(cross(dpdu, dpdv)) == 0) {
+            V3 ng = cross(p2 - p0, p1 - p0);
+            coordinate_system(normalize(ng), &dpdu, &dpdv);
+        }
+        s.p = b0 * p0 + b1 * p1 + b2 * p2;
+        s.pError = gammaN(7) * (vabs(b0 * p0) + vabs(b1 * p1) + vabs(b2 * p2));
+        s.n = normalize(cross(dp02, dp12));
+        if (q.flip_normal) s.n = -s.n;
+        s.ns = s.n; s.dpdu = dpdu;
+        s.wo = normalize(-rayD);
+        s.u = b0 * 0.f + b1 * 1.f + b2 * 1.f; s.v = b0 * 0.f + b1 * 0.f + b2 * 1.f;
+        s.material = q.material; s.areaLight = q.area_light;
+        s.hasInterface = q.has_interface && (q.medium_inside != q.medium_outside);
+        s.mediumInside = q.medium_inside; s.mediumOutside = q.medium_outside; s.rayMedium = rayMedium;
+        return s;
+    }
     s.p = lerpv(h.u, lerpv(h.v, p00, p01), lerpv(h.v, p10, p11));
     V3 dpdu = lerpv(h.v, p10, p11) - lerpv(h.v, p00, p01);
     V3 dpdv = lerpv(h.u, p01, p11) - lerpv(h.u, p00, p10);

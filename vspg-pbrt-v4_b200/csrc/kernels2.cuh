@@ -30,7 +30,7 @@ __global__ void __launch_bounds__(kBlock) k_surface(const DScene sc, const Wavef
             }
             toDone = true;
         } else {
-            SurfaceIntr isect = make_intr(sc, h, ps.ray.d, ps.ray.medium);
+            SurfaceIntr isect = make_intr(sc, h, ps.ray.o, ps.ray.d, ps.ray.medium);
             if (isect.areaLight >= 0) {
                 V3 Le = area_L(sc.lights[isect.areaLight], isect.n, -ps.ray.d);
                 if (nonzero(Le)) {
@@ -75,7 +75,7 @@ __global__ void __launch_bounds__(G > 0 ? kScatterBlock : kBlock) k_shade(const 
         PathRegs ps; path_load(W.P, slot, ps);
         float4 hr = W.P.hit[slot];
         Hit h; h.t = hr.x; h.u = hr.y; h.v = hr.z; h.prim = __float_as_int(hr.w);
-        SurfaceIntr isect = make_intr(sc, h, ps.ray.d, ps.ray.medium);
+        SurfaceIntr isect = make_intr(sc, h, ps.ray.o, ps.ray.d, ps.ray.medium);
         GuidedBSDF<G> gbsdf;
         gbsdf.enableGuiding = ip.surface_guiding; gbsdf.enableScatterGuiding = ip.vsp_secondary_guiding; gbsdf.ris = ip.surface_guiding_ris;
         gbsdf.set_bsdf(isect.ns, isect.dpdu, ld3(sc.materials[isect.material].reflectance));
@@ -199,7 +199,7 @@ __global__ void __launch_bounds__(kBlock) k_shadow(const DScene sc, const Wavefr
             }
             if (!nonzero(T_ray)) { blocked = true; break; }
             if (h.prim < 0) break;
-            SurfaceIntr hs = make_intr(sc, h, lightRay.d, lightRay.medium);
+            SurfaceIntr hs = make_intr(sc, h, lightRay.o, lightRay.d, lightRay.medium);
             spawn_ray_to(hs.p, hs.pError, hs.n, sr.pLight, sr.pLightErr, sr.nLight, &lightRay.o, &lightRay.d);
             lightRay.medium = hs.get_medium(lightRay.d);
         }

@@ -127,8 +127,8 @@ int vspg_build_majorant_grid(const vspg_medium *m, float *out) {
 int vspg_set_scene(vspg_ctx *ctx, const vspg_scene_desc *s) {
     if (!ctx || !s) return VSPG_ERR_INVALID;
     CK(cudaSetDevice(ctx->device));
-    if (s->n_triangles > 0 || s->n_spheres > 0)
-        return fail(ctx, VSPG_ERR_UNSUPPORTED, "set_scene: triangles/spheres are not on the supported path yet (quads only)");
+    if (s->n_spheres > 0)
+        return fail(ctx, VSPG_ERR_UNSUPPORTED, "set_scene: spheres are not on the supported path yet (bilinear patches and triangles are)");
     if (s->camera.filter_type != 0) return fail(ctx, VSPG_ERR_UNSUPPORTED, "set_scene: only the box filter is supported");
     if (s->camera.width <= 0 || s->camera.height <= 0) return fail(ctx, VSPG_ERR_INVALID, "set_scene: bad film resolution");
     free_all(ctx->scene_allocs);
@@ -182,32 +182,45 @@ int vspg_set_scene(vspg_ctx *ctx, const vspg_scene_desc *s) {
         if (d.type == VSPG_MEDIUM_RGBGRID || d.sigma_a[0] != d.sigma_a[1] || d.sigma_a[0] != d.sigma_a[2] || d.sigma_s[0] != d.sigma_s[1] || d.sigma_s[0] != d.sigma_s[2])
             ctx->all_gray = false;
     // ---- quads + BVH
-    std::vector<DQuad> quads(s->n_quads);
+    // prims = quads, then triangles stored in the same record (p0,p1,p2 in p00,p10,p01; kind = PRIM_TRIANGLE)
+    const int nPrims = s->n_quads + s->n_triangles;
+    std::vector<vspg_quad> hostPrims(nPrims);
+    std::vector<DQuad> quads(nPrims);
+    for (int i = 0; i < s->n_triangles; i++) {
+        const vspg_triangle &t = s->triangles[i];
+        vspg_quad &q = hostPrims[s->n_quads + i];
+        memcpy(q.p00, t.p0, 12); memcpy(q.p10, t.p1, 12); memcpy(q.p01, t.p2, 12); memcpy(q.p11, t.p2, 12);
+        q.material = t.material; q.area_light = t.area_light; q.medium_inside = t.medium_inside; q.medium_outside = t.medium_outside;
+        q.has_interface = t.has_interface; q.flip_normal = t.flip_normal;
+        if (t.area_light >= 0) return fail(ctx, VSPG_ERR_UNSUPPORTED, "set_scene: triangle %d: area lights must be bilinear patches (emissive triangles are not built yet)", i);
+    }
     float bmin[3] = {INFINITY, INFINITY, INFINITY}, bmax[3] = {-INFINITY, -INFINITY, -INFINITY};
-    for (int i = 0; i < s->n_quads; i++) {
-        const vspg_quad &q = s->quads[i];
+    for (int i = 0; i < s->n_quads; i++) hostPrims[i] = s->quads[i];
+    for (int i = 0; i < nPrims; i++) {
+        const vspg_quad &q = hostPrims[i];
         DQuad &d = quads[i];
+        d.kind = i < s->n_quads ? PRIM_QUAD : PRIM_TRIANGLE;
         memcpy(d.p00, q.p00, 12); memcpy(d.p10, q.p10, 12); memcpy(d.p01, q.p01, 12); memcpy(d.p11, q.p11, 12);
         d.material = q.material; d.area_light = q.area_light; d.medium_inside = q.medium_inside; d.medium_outside = q.medium_outside;
         d.has_interface = q.has_interface; d.flip_normal = q.flip_normal;
         if (q.material >= s->n_materials || q.area_light >= s->n_lights || q.medium_inside >= s->n_media || q.medium_outside >= s->n_media)
-            return fail(ctx, VSPG_ERR_INVALID, "set_scene: quad %d references an out-of-range material/light/medium", i);
+            return fail(ctx, VSPG_ERR_INVALID, "set_scene: primitive %d references an out-of-range material/light/medium", i);
         H3 p00(q.p00), p10(q.p10), p01(q.p01), p11(q.p11);
-        d.is_rect = quad_is_rectangle(p00, p10, p01, p11) ? 1 : 0;
-        d.area = quad_area(p00, p10, p01, p11);
+        if (d.kind == PRIM_QUAD) { d.is_rect = quad_is_rectangle(p00, p10, p01, p11) ? 1 : 0; d.area = quad_area(p00, p10, p01, p11); }
+        else { d.is_rect = 0; d.area = 0.5f * hlen(hcross(p10 - p00, p01 - p00)); }   // shapes.h Triangle::Area
         const float *P[4] = {q.p00, q.p10, q.p01, q.p11};
         for (int k = 0; k < 4; k++)
             for (int a = 0; a < 3; a++) { bmin[a] = std::min(bmin[a], P[k][a]); bmax[a] = std::max(bmax[a], P[k][a]); }
     }
     CK(upload(ctx->scene_allocs, quads.data(), quads.size(), &sc.quads));
-    sc.n_quads = s->n_quads;
-    HostBvh bvh = build_bvh(s->quads, s->n_quads);
+    sc.n_quads = nPrims;
+    HostBvh bvh = build_bvh(hostPrims.data(), nPrims);
     static_assert(sizeof(HostBvhNode) == sizeof(DBvhNode) && sizeof(DBvhNode) == 48, "BVH node layout");
     CK(upload(ctx->scene_allocs, (const DBvhNode *)bvh.nodes.data(), bvh.nodes.size(), &sc.bvh));
     CK(upload(ctx->scene_allocs, bvh.prim_ids.data(), bvh.prim_ids.size(), &sc.prim_ids));
     sc.n_bvh = (int)bvh.nodes.size();
     // Bounds3::BoundingSphere of the aggregate bounds (lights' Preprocess)
-    if (s->n_quads) {
+    if (nPrims) {
         H3 c((bmin[0] + bmax[0]) / 2, (bmin[1] + bmax[1]) / 2, (bmin[2] + bmax[2]) / 2);
         sc.scene_center[0] = c.x; sc.scene_center[1] = c.y; sc.scene_center[2] = c.z;
         sc.scene_radius = hdist(c, H3(bmax[0], bmax[1], bmax[2]));

@@ -99,6 +99,15 @@ def scene_text(cfg, out_dir=None, outfile="out.exr", seed=0, integrator_name="gu
                 L.append(f'  AreaLightSource "diffuse" "rgb L" [{_v(e["emission"])}] "bool twosided" {_b(e["two_sided"])}')
             L.append('  Shape "bilinearmesh" "point3 P" [' + "  ".join(_v(p) for p in e["corners"]) + "]")
             L.append("AttributeEnd")
+        elif kind == "trimesh":
+            L.append("AttributeBegin")
+            if e["has_interface"]:
+                name = lambda i: f"medium{i}" if i >= 0 else ""
+                L.append(f'  MediumInterface "{name(e["medium_inside"])}" "{name(e["medium_outside"])}"')
+            L.append(f'  NamedMaterial "mat{e["material"]}"' if e["material"] >= 0 else '  Material "interface"')
+            L.append('  Shape "trianglemesh" "point3 P" [' + "  ".join(_v(p) for p in e["points"]) + '] "integer indices" ['
+                     + "  ".join(" ".join(str(i) for i in t) for t in e["indices"]) + "]")
+            L.append("AttributeEnd")
         elif kind == "point":
             L.append(f'LightSource "point" "rgb I" [{_v(e["I"])}] "point3 from" [{_v(e["pos"])}]')
         elif kind == "distant":

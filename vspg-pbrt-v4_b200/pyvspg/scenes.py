@@ -78,7 +78,7 @@ class Scene:
 
     def __init__(self, camera, eye):
         self.camera, self.eye = camera, np.asarray(eye, dtype=np.float64)
-        self.quads, self.materials, self.lights, self.media = [], [], [], []
+        self.quads, self.triangles, self.materials, self.lights, self.media = [], [], [], [], []
         self._keep = []
         self.desc = None
         self.log = []   # world-space record of every add_* call, in order (pbrt_writer turns it into a .pbrt file)
@@ -115,6 +115,31 @@ class Scene:
             self.lights.append(l)
             q.area_light = len(self.lights) - 1
         return qi
+
+    def add_triangles(self, points, indices, material=-1, medium_inside=-1, medium_outside=-1, has_interface=False):
+        """Shape "trianglemesh": points [n][3] (world space), indices [m][3]."""
+        pts = np.asarray(points, dtype=np.float64).reshape(-1, 3)
+        idx = np.asarray(indices, dtype=np.int64).reshape(-1, 3)
+        self.log.append(("trimesh", dict(points=pts.tolist(), indices=idx.tolist(), material=material, medium_inside=medium_inside,
+                                         medium_outside=medium_outside, has_interface=bool(has_interface))))
+        for tri in idx:
+            t = A.Triangle()
+            for name, vi in zip(("p0", "p1", "p2"), tri):
+                getattr(t, name)[:] = [float(np.float32(x)) for x in (pts[vi] - self.eye)]
+            t.material, t.area_light = material, -1
+            t.medium_inside, t.medium_outside, t.has_interface, t.flip_normal = medium_inside, medium_outside, int(has_interface), 0
+            self.triangles.append(t)
+
+    def add_triangle_box(self, lo, hi, **kw):
+        """Axis-aligned box as 12 outward-facing triangles (n = normalize(cross(p0 - p2, p1 - p2)))."""
+        a, b = np.asarray(lo, dtype=np.float64), np.asarray(hi, dtype=np.float64)
+        P = [[a[0], a[1], a[2]], [b[0], a[1], a[2]], [b[0], b[1], a[2]], [a[0], b[1], a[2]],
+             [a[0], a[1], b[2]], [b[0], a[1], b[2]], [b[0], b[1], b[2]], [a[0], b[1], b[2]]]
+        quads = [(0, 3, 2, 1), (4, 5, 6, 7), (0, 1, 5, 4), (3, 7, 6, 2), (0, 4, 7, 3), (1, 2, 6, 5)]   # outward (counter-clockwise from outside)
+        idx = []
+        for q in quads:
+            idx += [(q[0], q[1], q[2]), (q[0], q[2], q[3])]
+        self.add_triangles(P, idx, **kw)
 
     def add_box(self, lo, hi, material=-1, medium_inside=-1, medium_outside=-1, has_interface=False):
         """Axis-aligned box with outward-facing normals."""
@@ -209,13 +234,13 @@ class Scene:
         d = A.SceneDesc()
         d.camera = self.camera
         arrs = {}
-        for name, items, T in (("media", self.media, A.Medium), ("quads", self.quads, A.Quad),
+        for name, items, T in (("media", self.media, A.Medium), ("quads", self.quads, A.Quad), ("triangles", self.triangles, A.Triangle),
                                ("materials", self.materials, A.Material), ("lights", self.lights, A.Light)):
             arr = (T * max(1, len(items)))(*items)
             arrs[name] = arr
             setattr(d, "n_" + name, len(items))
             setattr(d, name, arr)
-        d.n_triangles = d.n_spheres = 0
+        d.n_spheres = 0
         self._arrs = arrs
         self.desc = d
         return self
