@@ -357,6 +357,12 @@ int vspg_debug_sample_distance(vspg_ctx *ctx, int n, const vspg_sd_input *in, vs
 int vspg_debug_cache_lookup(vspg_ctx *ctx, int is_surface, int n, const float *pos3, const float *u,
                             int *out_leaf, int *out_region, float *out_u);
 
+/* LightSampler::Sample(ctx, u) and ::PMF(ctx, light) (lightsamplers.h:33-38, 266-359) with the sampler chosen by
+ * set_integrator, at n contexts: pos3 = ctx.p(), ns3 = ctx.ns (zero in a medium).  out_light[i] = sampled light or
+ * -1, out_pmf[i] its pmf, out_pmf_of[i] = PMF(ctx, light_of[i]). */
+int vspg_debug_light_sample(vspg_ctx *ctx, int n, const float *pos3, const float *ns3, const float *u, const int *light_of,
+                            int *out_light, float *out_pmf, float *out_pmf_of);
+
 /* GuidedPhaseFunction / GuidedBSDF (cpu/guiding.h:57-638) on explicit inputs. */
 typedef struct vspg_gs_input {
     float p[3];

@@ -115,6 +115,19 @@ def distribution_probe(field, mode, pos3, u, aux3, g, s2, wq3):
     return dict(region=region, pdf=pdf, vsp=vsp, li_pdf=lipdf, sampled=sampled, sampled_pdf=spdf)
 
 
+def light_sample(scene, ip, pos3, ns3, u, light_of):
+    pos3 = np.ascontiguousarray(pos3, dtype=np.float32).reshape(-1, 3)
+    ns3 = np.ascontiguousarray(ns3, dtype=np.float32).reshape(-1, 3)
+    u = np.ascontiguousarray(u, dtype=np.float32)
+    light_of = np.ascontiguousarray(light_of, dtype=np.int32)
+    n = pos3.shape[0]
+    light, pmf, pmf_of = np.zeros(n, np.int32), np.zeros(n, np.float32), np.zeros(n, np.float32)
+    rc = lib().orc_light_sample(C.byref(scene.desc), C.byref(ip), n, _fp(pos3), _fp(ns3), _fp(u), light_of.ctypes.data_as(PI),
+                                light.ctypes.data_as(PI), _fp(pmf), _fp(pmf_of))
+    assert rc == 0, rc
+    return light, pmf, pmf_of
+
+
 def guided_sample(scene, guiding, ip, is_surface, inputs):
     n = len(inputs)
     out = (A.GsOutput * n)()

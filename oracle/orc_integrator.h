@@ -10,6 +10,7 @@
 
 #include "orc_guiding.h"
 #include "orc_media.h"
+#include "orc_lightbvh.h"
 
 namespace orc {
 
@@ -164,6 +165,7 @@ struct Scene {
     std::vector<Medium> media;
     std::vector<float> quadArea;
     std::vector<float> lightCdf;  // power sampler pmf
+    BVHLightSampler lightBvh;     // "bvh" sampler (the reference's default)
     V3 sceneCenter; float sceneRadius = 0;
     int seed = 0;
     bool ownMajorant = false;
@@ -195,6 +197,7 @@ struct Scene {
         for (int i = 0; i < d->n_lights; i++) { lightCdf[i] = LightPower(i); sum += lightCdf[i]; }
         if (sum == 0) for (auto &v : lightCdf) v = 1.f, sum += 1.f;
         for (auto &v : lightCdf) v /= sum;
+        lightBvh.Build(d->lights, d->n_lights, d->quads, quadArea);
     }
     static bool IsRectangle(V3 p00, V3 p10, V3 p01, V3 p11) {  // shapes.h BilinearPatch::IsRectangle
         if (p00 == p01 || p01 == p11 || p11 == p10 || p10 == p00) return false;
@@ -547,9 +550,11 @@ struct Integrator {
     Counters cnt;
 
     // ---------------------------------------------------------------- light sampling
-    int SampleLight(float u, float *pmf) const {  // lightsamplers.h:33-38 (uniform) / power pmf via CDF walk
+    // ctxP / ctxNs: LightSampleContext::p() and ::ns of the vertex (ns = 0 in a medium)
+    int SampleLight(float u, float *pmf, V3 ctxP, V3 ctxNs) const {  // lightsamplers.h:33-38 (uniform) / power pmf via CDF walk / bvh
         int n = sc->d->n_lights;
         if (n == 0) return -1;
+        if (sc->ip.light_sampler == VSPG_LIGHTSAMPLER_BVH) return sc->lightBvh.Sample(ctxP, ctxNs, u, pmf);
         if (sc->ip.light_sampler == VSPG_LIGHTSAMPLER_UNIFORM) {
             int li = std::min<int>((int)(u * n), n - 1);
             *pmf = 1.f / n;
@@ -559,9 +564,10 @@ struct Integrator {
         for (int i = 0; i < n; i++) { c += sc->lightCdf[i]; if (u < c || i == n - 1) { *pmf = sc->lightCdf[i]; return i; } }
         return -1;
     }
-    float LightPMF(int light) const {
+    float LightPMF(int light, const LightSampleCtx &ctx) const {
         int n = sc->d->n_lights;
         if (n == 0) return 0;
+        if (sc->ip.light_sampler == VSPG_LIGHTSAMPLER_BVH) return sc->lightBvh.PMF(ctx.p, ctx.ns, light);
         if (sc->ip.light_sampler == VSPG_LIGHTSAMPLER_UNIFORM) return 1.f / n;
         return sc->lightCdf[light];
     }
@@ -647,7 +653,7 @@ struct Integrator {
         }
         float u = sampler.Get1D();
         float pmf = 0;
-        int light = SampleLight(u, &pmf);
+        int light = SampleLight(u, &pmf, ctx.p, ctx.ns);
         float uLight[2]; sampler.Get2D(uLight);
         if (light < 0) return S3(0.f);
         LiSample ls = SampleLi(light, ctx, uLight);
@@ -929,7 +935,7 @@ struct Integrator {
                     S3 Le(l.L);
                     if (ps.depth == 0 || ps.specularBounce) ps.L += ps.beta * Le / ps.r_u.Average();
                     else {
-                        float lightPDF = LightPMF(i) * 0.f;  // PDF_Li(..., allowIncompletePDF=true) = 0 (lights.cpp:1031-1036)
+                        float lightPDF = LightPMF(i, ps.prevCtx) * 0.f;  // PDF_Li(..., allowIncompletePDF=true) = 0 (lights.cpp:1031-1036)
                         ps.r_l *= lightPDF;
                         float w_b = ip.use_nee ? 1.0f / (ps.r_u + ps.r_l).Average() : 1.f;
                         ps.L += ps.beta * w_b * Le;
@@ -943,7 +949,7 @@ struct Integrator {
                 if (Le) {
                     if (ps.depth == 0 || ps.specularBounce) ps.L += ps.beta * Le / ps.r_u.Average();
                     else {
-                        float lightPDF = LightPMF(isect.areaLight) * AreaPDF_Li(isect.areaLight, ps.prevCtx, ps.ray.d, isect);
+                        float lightPDF = LightPMF(isect.areaLight, ps.prevCtx) * AreaPDF_Li(isect.areaLight, ps.prevCtx, ps.ray.d, isect);
                         ps.r_l *= lightPDF;
                         float w_l = ip.use_nee ? 1.0f / (ps.r_u + ps.r_l).Average() : 1.0f;
                         ps.L += ps.beta * w_l * Le;

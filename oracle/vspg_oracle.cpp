@@ -94,6 +94,21 @@ int orc_majorant_segments(const vspg_medium *m, int n, const float *rays7, int m
     return 0;
 }
 
+// LightSampler::Sample / PMF at explicit contexts (lightsamplers.h:33-38, 266-359)
+int orc_light_sample(const vspg_scene_desc *d, const vspg_integrator_params *ip, int n, const float *pos3, const float *ns3, const float *u,
+                     const int *light_of, int *out_light, float *out_pmf, float *out_pmf_of) {
+    Scene sc; sc.init(d, nullptr, ip, true);
+    Integrator in; in.sc = &sc;
+    for (int i = 0; i < n; i++) {
+        LightSampleCtx ctx; ctx.p = V3(pos3 + 3 * i); ctx.ns = V3(ns3 + 3 * i);
+        float pmf = 0;
+        int l = in.SampleLight(u[i], &pmf, ctx.p, ctx.ns);
+        out_light[i] = l; out_pmf[i] = l >= 0 ? pmf : 0.f;
+        out_pmf_of[i] = in.LightPMF(light_of[i], ctx);
+    }
+    return 0;
+}
+
 // ------------------------------------------------------------- guiding
 int orc_cache_lookup(const vspg_field *f, int n, const float *pos3, const float *u, int *out_leaf, int *out_region, float *out_u) {
     for (int i = 0; i < n; i++) {

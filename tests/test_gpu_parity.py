@@ -250,6 +250,7 @@ def test_guided_sample_parity_on_a_reference_trained_field(ctx, orc, surface):
 
 
 RENDER_CASES = [("C1", {}), ("C1T", {}), ("C1", dict(vsp_guiding=1)), ("C2", {}), ("C3", {}), ("C4", {}), ("C5", {}),
+                ("C5", dict(light_sampler=A.LIGHTSAMPLER_BVH)), ("C2", dict(light_sampler=A.LIGHTSAMPLER_BVH)), ("C1", dict(light_sampler=A.LIGHTSAMPLER_BVH)),
                 ("C2", dict(max_depth=1)), ("C3", dict(volume_guiding_ris=1, surface_guiding_ris=0))]
 
 
@@ -331,7 +332,7 @@ def test_errors_are_reported_not_fatal(ctx):
     assert "transmittance" in str(e.value)
     with pytest.raises(api.VspgError):
         ctx.render(0, 1, window=(0, 0, cfg.width + 1, cfg.height))
-    ip = api.integrator_defaults(light_sampler=A.LIGHTSAMPLER_BVH)
+    ip = api.integrator_defaults(light_sampler=7)
     with pytest.raises(api.VspgError):
         ctx.set_integrator(ip)
     with pytest.raises(KeyError):

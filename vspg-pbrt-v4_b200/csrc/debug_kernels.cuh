@@ -37,6 +37,17 @@ __global__ void k_debug_segments(const DScene sc, int medium, int n, const float
     }
 }
 
+__global__ void k_debug_light_sample(const DScene sc, int n, const float *pos3, const float *ns3, const float *u, const int *lightOf,
+                                     int *outLight, float *outPmf, float *outPmfOf) {
+    for (int i = gtid(); i < n; i += gstride()) {
+        V3 p(pos3[3 * i], pos3[3 * i + 1], pos3[3 * i + 2]), ns(ns3[3 * i], ns3[3 * i + 1], ns3[3 * i + 2]);
+        float pmf = 0;
+        int l = sample_light(sc, u[i], &pmf, p, ns);
+        outLight[i] = l; outPmf[i] = l >= 0 ? pmf : 0.f;
+        outPmfOf[i] = light_pmf(sc, lightOf[i], p, ns);
+    }
+}
+
 __global__ void k_debug_density(const DScene sc, int medium, int n, const float *pos3, float *out7) {
     for (int i = gtid(); i < n; i += gstride()) {
         MediumProps mp = sample_point(sc.media[medium], V3(pos3[3 * i], pos3[3 * i + 1], pos3[3 * i + 2]));

@@ -10,7 +10,7 @@ struct PathRegs {
     Rng rng;
     PathFlags fl;
     float rr_correction, vsp_next;
-    V3 prevP;
+    V3 prevP, prevNs;
     int pixel, sampleIndex;
 };
 
@@ -23,6 +23,7 @@ VD void path_load(const PathSoA &P, int s, PathRegs &r) {
     r.rng.state = q.x; r.rng.inc = q.y;
     r.rr_correction = f.x; r.vsp_next = f.y; r.prevP = V3(f.z, f.w, g.x);
     r.pixel = __float_as_int(g.y); r.sampleIndex = __float_as_int(g.z);
+    float4 h = P.prev_ns[s]; r.prevNs = V3(h.x, h.y, h.z);
 }
 VD void path_store(const PathSoA &P, int s, const PathRegs &r) {
     P.o_dx[s] = make_float4(r.ray.o.x, r.ray.o.y, r.ray.o.z, r.ray.d.x);
@@ -33,6 +34,7 @@ VD void path_store(const PathSoA &P, int s, const PathRegs &r) {
     P.rng[s] = make_ulonglong2(r.rng.state, r.rng.inc);
     P.misc[s] = make_float4(r.rr_correction, r.vsp_next, r.prevP.x, r.prevP.y);
     P.misc2[s] = make_float4(r.prevP.z, __int_as_float(r.pixel), __int_as_float(r.sampleIndex), 0.f);
+    P.prev_ns[s] = make_float4(r.prevNs.x, r.prevNs.y, r.prevNs.z, 0.f);
 }
 
 // cpu/integrators.cpp:272-334 EvaluatePixelSample (front half) + samplers.h:442-476, 797-814 + cameras.cpp:410-437

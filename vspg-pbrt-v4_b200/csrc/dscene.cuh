@@ -54,6 +54,13 @@ struct DLight {
     float pmf;            // light sampler probability (uniform / power)
 };
 
+// Light-BVH node (lightsamplers.h LightBVHNode), stored decoded -- see host_lightbvh.h.
+struct DLightNode {
+    float bmin[3], bmax[3], w[3];
+    float phi, cosTheta_o, cosTheta_e;
+    int twoSided, childOrLight, isLeaf, pad;
+};
+
 struct DField {
     int present, usable;
     float bmin[3], bmax[3];
@@ -74,6 +81,9 @@ struct DScene {
     int n_materials; const vspg_material *materials;
     int n_lights; const DLight *lights;
     int n_inf_lights; const int *inf_lights;
+    // BVHLightSampler (lightsamplers.h:258-404): tree nodes, per-light bit trail / in-tree flag, lights without bounds
+    int n_lbvh; const DLightNode *lbvh; const unsigned *light_trail; const int *light_in_tree;
+    int n_unbounded; const int *unbounded_lights;
     float scene_center[3]; float scene_radius;
     DField surf, vol;
     const DHGRow *hg_table;   // 128 rows
@@ -104,6 +114,7 @@ struct PathSoA {
     float4 *sh_pl;       // pLight xyz, nLight.x
     float4 *sh_ple;      // pLightErr xyz, nLight.y
     float *sh_nz;        // nLight.z
+    float4 *prev_ns;     // shading normal of the previous vertex (0 for a medium vertex): LightSampleContext::ns for the emission MIS
     int *lk;             // guiding-cache region chosen by k_lookup for the pending scatter vertex (-1 = none)
     float2 *rs_pre;      // resampling pre-pass (media_sampleTMaj.h:153-164): sum of sigma_maj[ch]*dt, DDA steps(int)
 };

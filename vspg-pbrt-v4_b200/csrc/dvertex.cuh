@@ -13,25 +13,115 @@ struct LightSampleCtx { V3 p; };
 
 struct LiSample { bool valid; V3 L, wi; float pdf; V3 pLight, pLightErr, nLight; bool delta; };
 
-// lightsamplers.h:33-38 UniformLightSampler / PowerLightSampler pmf (precomputed per light on the host)
-VD int sample_light(const DScene &sc, float u, float *pmf) {
-    int n = sc.n_lights;
-    if (n == 0) return -1;
+// lightsamplers.h:140-201 CompactLightBounds::Importance on a decoded node
+VD float light_importance(const DLightNode &nd, V3 p, V3 n) {
+    V3 bmin = ld3(nd.bmin), bmax = ld3(nd.bmax);
+    float cosTheta_o = nd.cosTheta_o, cosTheta_e = nd.cosTheta_e;
+    V3 pc = (bmin + bmax) / 2;
+    float d2 = dist_sq(p, pc);
+    d2 = fmaxf(d2, length(bmax - bmin) / 2);
+    V3 wi = normalize(p - pc);
+    float cosTheta_w = dot(ld3(nd.w), wi);
+    if (nd.twoSided) cosTheta_w = fabsf(cosTheta_w);
+    float sinTheta_w = safe_sqrt(1 - sqr(cosTheta_w));
+    // BoundSubtendedDirections(bounds, p).cosTheta  (util/vecmath.h:1815-1828)
+    float cosTheta_b;
+    {
+        bool inside = pc.x >= bmin.x && pc.x <= bmax.x && pc.y >= bmin.y && pc.y <= bmax.y && pc.z >= bmin.z && pc.z <= bmax.z;
+        float radius = inside ? length(pc - bmax) : 0;
+        if (dist_sq(p, pc) < sqr(radius)) cosTheta_b = -1;
+        else cosTheta_b = safe_sqrt(1 - sqr(radius) / dist_sq(pc, p));
+    }
+    float sinTheta_b = safe_sqrt(1 - sqr(cosTheta_b));
+    float sinTheta_o = safe_sqrt(1 - sqr(cosTheta_o));
+    // cosSubClamped / sinSubClamped
+    float cosTheta_x = cosTheta_w > cosTheta_o ? 1.f : cosTheta_w * cosTheta_o + sinTheta_w * sinTheta_o;
+    float sinTheta_x = cosTheta_w > cosTheta_o ? 0.f : sinTheta_w * cosTheta_o - cosTheta_w * sinTheta_o;
+    float cosThetap = cosTheta_x > cosTheta_b ? 1.f : cosTheta_x * cosTheta_b + sinTheta_x * sinTheta_b;
+    if (cosThetap <= cosTheta_e) return 0;
+    float importance = nd.phi * cosThetap / d2;
+    if (n.x != 0 || n.y != 0 || n.z != 0) {
+        float cosTheta_i = absdot(wi, n);
+        float sinTheta_i = safe_sqrt(1 - sqr(cosTheta_i));
+        float cosThetap_i = cosTheta_i > cosTheta_b ? 1.f : cosTheta_i * cosTheta_b + sinTheta_i * sinTheta_b;
+        importance *= cosThetap_i;
+    }
+    return fmaxf(importance, 0.f);
+}
+// lightsamplers.h:266-321 BVHLightSampler::Sample(ctx, u)
+VD int sample_light_bvh(const DScene &sc, V3 p, V3 n, float u, float *pmfOut) {
+    const int nInf = sc.n_unbounded;
+    const float pInfinite = float(nInf) / float(nInf + (sc.n_lbvh == 0 ? 0 : 1));
+    if (u < pInfinite) {
+        u /= pInfinite;
+        int index = min((int)(u * nInf), nInf - 1);
+        *pmfOut = pInfinite / nInf;
+        return sc.unbounded_lights[index];
+    }
+    if (sc.n_lbvh == 0) return -1;
+    u = fminf((u - pInfinite) / (1 - pInfinite), kOneMinusEpsilon);
+    int nodeIndex = 0;
+    float pmf = 1 - pInfinite;
+    while (true) {
+        const DLightNode &node = sc.lbvh[nodeIndex];
+        if (!node.isLeaf) {
+            float ci0 = light_importance(sc.lbvh[nodeIndex + 1], p, n), ci1 = light_importance(sc.lbvh[node.childOrLight], p, n);
+            if (ci0 == 0 && ci1 == 0) return -1;
+            // SampleDiscrete({ci0, ci1}, u, &nodePMF, &u)   util/sampling.h:79-112
+            float sumWeights = 0; sumWeights += ci0; sumWeights += ci1;
+            float up = u * sumWeights;
+            if (up == sumWeights) up = next_down(up);
+            int child = 0; float sum = 0, wsel = ci0;
+            if (sum + ci0 <= up) { sum += ci0; child = 1; wsel = ci1; }
+            pmf *= wsel / sumWeights;
+            u = fminf((up - sum) / wsel, kOneMinusEpsilon);
+            nodeIndex = child == 0 ? nodeIndex + 1 : node.childOrLight;
+        } else {
+            if (nodeIndex > 0 || light_importance(node, p, n) > 0) { *pmfOut = pmf; return node.childOrLight; }
+            return -1;
+        }
+    }
+}
+// lightsamplers.h:324-359 BVHLightSampler::PMF(ctx, light)
+VD float light_pmf_bvh(const DScene &sc, V3 p, V3 n, int light) {
+    const int nInf = sc.n_unbounded;
+    if (!sc.light_in_tree[light]) return 1.f / (nInf + (sc.n_lbvh == 0 ? 0 : 1));
+    unsigned bitTrail = sc.light_trail[light];
+    const float pInfinite = float(nInf) / float(nInf + (sc.n_lbvh == 0 ? 0 : 1));
+    float pmf = 1 - pInfinite;
+    int nodeIndex = 0;
+    while (true) {
+        const DLightNode &node = sc.lbvh[nodeIndex];
+        if (node.isLeaf) return pmf;
+        float ci[2] = {light_importance(sc.lbvh[nodeIndex + 1], p, n), light_importance(sc.lbvh[node.childOrLight], p, n)};
+        pmf *= ci[bitTrail & 1] / (ci[0] + ci[1]);
+        nodeIndex = (bitTrail & 1) ? node.childOrLight : (nodeIndex + 1);
+        bitTrail >>= 1;
+    }
+}
+
+// lightsamplers.h:33-38 UniformLightSampler / PowerLightSampler pmf (precomputed per light on the host) / BVHLightSampler.
+// p, n: LightSampleContext::p() and ::ns of the vertex (n = 0 in a medium).
+VD int sample_light(const DScene &sc, float u, float *pmf, V3 p, V3 n) {
+    int nl = sc.n_lights;
+    if (nl == 0) return -1;
+    if (sc.ip.light_sampler == VSPG_LIGHTSAMPLER_BVH) return sample_light_bvh(sc, p, n, u, pmf);
     if (sc.ip.light_sampler == VSPG_LIGHTSAMPLER_UNIFORM) {
-        int li = min((int)(u * n), n - 1);
-        *pmf = 1.f / n;
+        int li = min((int)(u * nl), nl - 1);
+        *pmf = 1.f / nl;
         return li;
     }
     float c = 0;
-    for (int i = 0; i < n; i++) {
-        float p = sc.lights[i].pmf;
-        c += p;
-        if (u < c || i == n - 1) { *pmf = p; return i; }
+    for (int i = 0; i < nl; i++) {
+        float pi = sc.lights[i].pmf;
+        c += pi;
+        if (u < c || i == nl - 1) { *pmf = pi; return i; }
     }
     return -1;
 }
-VD float light_pmf(const DScene &sc, int light) {
+VD float light_pmf(const DScene &sc, int light, V3 p, V3 n) {
     if (sc.n_lights == 0) return 0;
+    if (sc.ip.light_sampler == VSPG_LIGHTSAMPLER_BVH) return light_pmf_bvh(sc, p, n, light);
     if (sc.ip.light_sampler == VSPG_LIGHTSAMPLER_UNIFORM) return 1.f / sc.n_lights;
     return sc.lights[light].pmf;
 }

@@ -215,7 +215,7 @@ __global__ void __launch_bounds__(G > 0 ? kScatterBlock : kBlock) k_volscatter(c
             V3 wo = -ps.ray.d;
             float u = ps.rng.uniform();
             float pmf = 0;
-            int light = sample_light(sc, u, &pmf);
+            int light = sample_light(sc, u, &pmf, p, V3());
             float ul0 = ps.rng.uniform(), ul1 = ps.rng.uniform();
             if (light >= 0) {
                 LiSample ls = sample_li(sc, light, p, ul0, ul1);
@@ -252,7 +252,7 @@ __global__ void __launch_bounds__(G > 0 ? kScatterBlock : kBlock) k_volscatter(c
                 float phaseFunctionWeight = s.f.x / s.pdf;
                 ps.beta = ps.beta * phaseFunctionWeight;
                 ps.r_l = ps.r_u / s.pdf;
-                ps.prevP = p;
+                ps.prevP = p; ps.prevNs = V3();
                 ps.ray.o = p; ps.ray.d = s.wi;
                 ps.fl.specular = false; ps.fl.anyNonSpecular = true; ps.fl.lastVertexVolume = true;
                 ps.vsp_next = gphase.vsp(s.wi);

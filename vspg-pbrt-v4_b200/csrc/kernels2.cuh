@@ -22,7 +22,7 @@ __global__ void __launch_bounds__(kBlock) k_surface(const DScene sc, const Wavef
                 V3 Le = ld3(sc.lights[li].L);
                 if (ps.fl.depth == 0 || ps.fl.specular) ps.L = ps.L + ps.beta * Le / avg3(ps.r_u);
                 else {
-                    float lightPDF = light_pmf(sc, li) * 0.f;
+                    float lightPDF = light_pmf(sc, li, ps.prevP, ps.prevNs) * 0.f;
                     ps.r_l = ps.r_l * lightPDF;
                     float w_b = ip.use_nee ? 1.0f / avg3(ps.r_u + ps.r_l) : 1.f;
                     ps.L = ps.L + ps.beta * w_b * Le;
@@ -36,7 +36,7 @@ __global__ void __launch_bounds__(kBlock) k_surface(const DScene sc, const Wavef
                 if (nonzero(Le)) {
                     if (ps.fl.depth == 0 || ps.fl.specular) ps.L = ps.L + ps.beta * Le / avg3(ps.r_u);
                     else {
-                        float lightPDF = light_pmf(sc, isect.areaLight) * area_pdf_li(sc, isect.areaLight, ps.prevP, ps.ray.d, isect);
+                        float lightPDF = light_pmf(sc, isect.areaLight, ps.prevP, ps.prevNs) * area_pdf_li(sc, isect.areaLight, ps.prevP, ps.ray.d, isect);
                         ps.r_l = ps.r_l * lightPDF;
                         float w_l = ip.use_nee ? 1.0f / avg3(ps.r_u + ps.r_l) : 1.0f;
                         ps.L = ps.L + ps.beta * w_l * Le;
@@ -88,7 +88,7 @@ __global__ void __launch_bounds__(G > 0 ? kScatterBlock : kBlock) k_shade(const 
             V3 wo = isect.wo;
             float u = ps.rng.uniform();
             float pmf = 0;
-            int light = sample_light(sc, u, &pmf);
+            int light = sample_light(sc, u, &pmf, ctxP, isect.ns);
             float ul0 = ps.rng.uniform(), ul1 = ps.rng.uniform();
             if (light >= 0) {
                 LiSample ls = sample_li(sc, light, ctxP, ul0, ul1);
@@ -111,7 +111,7 @@ __global__ void __launch_bounds__(G > 0 ? kScatterBlock : kBlock) k_shade(const 
             }
         }
         scatter_phase_sync<G>();
-        ps.prevP = isect.p;
+        ps.prevP = isect.p; ps.prevNs = isect.ns;
         V3 wo = -ps.ray.d;
         float u = ps.rng.uniform();
         float u0 = ps.rng.uniform(), u1 = ps.rng.uniform();

@@ -10,6 +10,7 @@
 #include <vector>
 
 #include "host_util.h"
+#include "host_lightbvh.h"
 #include "kernels2.cuh"
 #include "debug_kernels.cuh"
 
@@ -257,6 +258,17 @@ int vspg_set_scene(vspg_ctx *ctx, const vspg_scene_desc *s) {
     CK(upload(ctx->scene_allocs, lights.data(), lights.size(), &sc.lights));
     CK(upload(ctx->scene_allocs, inf.data(), inf.size(), &sc.inf_lights));
     sc.n_lights = s->n_lights; sc.n_inf_lights = (int)inf.size();
+    {   // BVHLightSampler (the reference's default "lightsampler"), lightsamplers.cpp:107-236
+        std::vector<float> quadArea(s->n_quads);
+        for (int i = 0; i < s->n_quads; i++) quadArea[i] = quads[i].area;
+        HostLightBvh lb = build_light_bvh(s->lights, s->n_lights, s->quads, quadArea.data());
+        static_assert(sizeof(HostLightNode) == sizeof(DLightNode) && sizeof(DLightNode) == 64, "light BVH node layout");
+        CK(upload(ctx->scene_allocs, (const DLightNode *)lb.nodes.data(), lb.nodes.size(), &sc.lbvh));
+        CK(upload(ctx->scene_allocs, (const unsigned *)lb.bitTrail.data(), lb.bitTrail.size(), &sc.light_trail));
+        CK(upload(ctx->scene_allocs, lb.inTree.data(), lb.inTree.size(), &sc.light_in_tree));
+        CK(upload(ctx->scene_allocs, lb.infinite.data(), lb.infinite.size(), &sc.unbounded_lights));
+        sc.n_lbvh = (int)lb.nodes.size(); sc.n_unbounded = (int)lb.infinite.size();
+    }
     // ---- film
     if (ctx->film_w != s->camera.width || ctx->film_h != s->camera.height || !ctx->film) {
         if (ctx->film) cudaFree(ctx->film);

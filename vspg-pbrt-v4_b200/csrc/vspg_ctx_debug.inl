@@ -54,6 +54,28 @@ int vspg_debug_density(vspg_ctx *ctx, int medium, int n, const float *pos3, floa
     return VSPG_OK;
 }
 
+int vspg_debug_light_sample(vspg_ctx *ctx, int n, const float *pos3, const float *ns3, const float *u, const int *light_of,
+                            int *out_light, float *out_pmf, float *out_pmf_of) {
+    if (!ctx || n < 0 || !pos3 || !ns3 || !u || !light_of || !out_light || !out_pmf || !out_pmf_of) return VSPG_ERR_INVALID;
+    CK_STATE(ctx->have_scene, "debug_light_sample: set_scene has not been called");
+    for (int i = 0; i < n; i++)
+        if (light_of[i] < 0 || light_of[i] >= ctx->sc.n_lights) return fail(ctx, VSPG_ERR_INVALID, "debug_light_sample: item %d: light out of range", i);
+    if (n == 0) return VSPG_OK;
+    CK(cudaSetDevice(ctx->device));
+    DevBuf dp, dn, du, dl, ol, op, oq;
+    CK(dp.alloc((size_t)n * 12)); CK(dn.alloc((size_t)n * 12)); CK(du.alloc((size_t)n * 4)); CK(dl.alloc((size_t)n * 4));
+    CK(ol.alloc((size_t)n * 4)); CK(op.alloc((size_t)n * 4)); CK(oq.alloc((size_t)n * 4));
+    CK(cudaMemcpy(dp.p, pos3, (size_t)n * 12, cudaMemcpyHostToDevice)); CK(cudaMemcpy(dn.p, ns3, (size_t)n * 12, cudaMemcpyHostToDevice));
+    CK(cudaMemcpy(du.p, u, (size_t)n * 4, cudaMemcpyHostToDevice)); CK(cudaMemcpy(dl.p, light_of, (size_t)n * 4, cudaMemcpyHostToDevice));
+    int blocks = std::min((n + kBlock - 1) / kBlock, ctx->sm_count * 8);
+    k_debug_light_sample<<<blocks, kBlock>>>(ctx->sc, n, dp.as<float>(), dn.as<float>(), du.as<float>(), dl.as<int>(), ol.as<int>(), op.as<float>(), oq.as<float>());
+    ctx->launches++;
+    CK(cudaGetLastError());
+    CK(cudaMemcpy(out_light, ol.p, (size_t)n * 4, cudaMemcpyDeviceToHost)); CK(cudaMemcpy(out_pmf, op.p, (size_t)n * 4, cudaMemcpyDeviceToHost));
+    CK(cudaMemcpy(out_pmf_of, oq.p, (size_t)n * 4, cudaMemcpyDeviceToHost));
+    return VSPG_OK;
+}
+
 int vspg_debug_sample_distance(vspg_ctx *ctx, int n, const vspg_sd_input *in, vspg_sd_output *out) {
     if (!ctx || n < 0 || !in || !out) return VSPG_ERR_INVALID;
     CK_STATE(ctx->have_scene, "debug_sample_distance: set_scene has not been called");

@@ -70,9 +70,7 @@ int vspg_set_integrator(vspg_ctx *ctx, const vspg_integrator_params *p) {
     if (!ctx || !p) return VSPG_ERR_INVALID;
     if (p->max_depth < 0 || p->max_depth > 255) return fail(ctx, VSPG_ERR_INVALID, "set_integrator: maxdepth must be in [0,255]");
     if (!(p->vsp_mis_ratio >= 0.f && p->vsp_mis_ratio <= 1.f)) return fail(ctx, VSPG_ERR_INVALID, "set_integrator: vspmisratio must be in [0,1]");
-    if (p->light_sampler == VSPG_LIGHTSAMPLER_BVH)
-        return fail(ctx, VSPG_ERR_UNSUPPORTED, "set_integrator: lightsampler \"bvh\" is not built yet; use \"uniform\" or \"power\"");
-    if (p->light_sampler != VSPG_LIGHTSAMPLER_UNIFORM && p->light_sampler != VSPG_LIGHTSAMPLER_POWER) return fail(ctx, VSPG_ERR_INVALID, "set_integrator: bad lightsampler");
+    if (p->light_sampler != VSPG_LIGHTSAMPLER_UNIFORM && p->light_sampler != VSPG_LIGHTSAMPLER_POWER && p->light_sampler != VSPG_LIGHTSAMPLER_BVH) return fail(ctx, VSPG_ERR_INVALID, "set_integrator: bad lightsampler");
     ctx->sc.ip = *p;
     return VSPG_OK;
 }

@@ -19,7 +19,7 @@ static int ensure_wavefront(vspg_ctx *ctx, unsigned long long total) {
     };
     PathSoA &P = ctx->W.P;
     float4 **f4[] = {&P.o_dx, &P.d_med, &P.beta_ru, &P.ru_rl, &P.rl_L, &P.misc, &P.misc2, &P.hit, &P.ev,
-                     &P.sh_o, &P.sh_d, &P.sh_c, &P.sh_rl, &P.sh_ru, &P.sh_pl, &P.sh_ple};
+                     &P.sh_o, &P.sh_d, &P.sh_c, &P.sh_rl, &P.sh_ru, &P.sh_pl, &P.sh_ple, &P.prev_ns};
     for (auto pp : f4) CK(alloc((void **)pp, n * sizeof(float4)));
     CK(alloc((void **)&P.rng, n * sizeof(ulonglong2)));
     CK(alloc((void **)&P.sh_nz, n * sizeof(float)));

@@ -156,6 +156,18 @@ class Context:
                                                region.ctypes.data_as(C.POINTER(A.i32)), _fp(uo)))
         return leaf, region, uo
 
+    def debug_light_sample(self, pos3, ns3, u, light_of):
+        pos3 = np.ascontiguousarray(pos3, dtype=np.float32).reshape(-1, 3)
+        ns3 = np.ascontiguousarray(ns3, dtype=np.float32).reshape(-1, 3)
+        u = np.ascontiguousarray(u, dtype=np.float32)
+        light_of = np.ascontiguousarray(light_of, dtype=np.int32)
+        n = pos3.shape[0]
+        light, pmf, pmf_of = np.zeros(n, np.int32), np.zeros(n, np.float32), np.zeros(n, np.float32)
+        ip = C.POINTER(A.i32)
+        self._ck(lib().vspg_debug_light_sample(self._h, n, _fp(pos3), _fp(ns3), _fp(u), light_of.ctypes.data_as(ip), light.ctypes.data_as(ip),
+                                               _fp(pmf), _fp(pmf_of)))
+        return light, pmf, pmf_of
+
     def debug_guided_sample(self, is_surface, inputs):
         n = len(inputs)
         out = (A.GsOutput * n)()
