@@ -158,6 +158,63 @@ inline bool IntersectTriangle(V3 ro, V3 rd, float tMax, V3 p0, V3 p1, V3 p2, flo
 
 struct LightSampleCtx { V3 p, pError, n, ns; };
 
+// filters.h:26-45, filters.cpp:133-147 FilterSampler over a GaussianFilter (filters.h:80-118), with
+// util/sampling.h:603-790 PiecewiseConstant1D / 2D and util/math.h:508-519 FindInterval
+struct Piecewise1D {
+    std::vector<float> func, cdf; float mn = 0, mx = 1, funcInt = 0;
+    void init(const float *f, int n, float mn_, float mx_) {
+        func.assign(f, f + n); cdf.assign(n + 1, 0.f); mn = mn_; mx = mx_;
+        for (float &v : func) v = std::abs(v);
+        cdf[0] = 0;
+        for (int i = 1; i < n + 1; ++i) cdf[i] = cdf[i - 1] + func[i - 1] * (mx - mn) / n;
+        funcInt = cdf[n];
+        if (funcInt == 0) for (int i = 1; i < n + 1; ++i) cdf[i] = float(i) / float(n);
+        else for (int i = 1; i < n + 1; ++i) cdf[i] /= funcInt;
+    }
+    float Sample(float u, float *pdf, int *offset) const {
+        long sz = (long)cdf.size(), size = sz - 2, first = 1;
+        while (size > 0) {
+            long half = size >> 1, middle = first + half;
+            bool pr = cdf[middle] <= u;
+            first = pr ? middle + 1 : first;
+            size = pr ? size - (half + 1) : half;
+        }
+        int o = (int)std::min(std::max(first - 1, 0l), sz - 2);
+        *offset = o;
+        float du = u - cdf[o];
+        if (cdf[o + 1] - cdf[o] > 0) du /= cdf[o + 1] - cdf[o];
+        *pdf = (funcInt > 0) ? func[o] / funcInt : 0;
+        return Lerp((o + du) / (float)func.size(), mn, mx);
+    }
+};
+struct GaussianFilterSampler {
+    int nx = 0, ny = 0; std::vector<float> f; std::vector<Piecewise1D> cond; Piecewise1D marginal;
+    static float Gaussian(float x, float mu, float sigma) {   // util/math.h:477-480
+        return 1 / std::sqrt(2 * Pi * sigma * sigma) * FastExp(-Sqr(x - mu) / (2 * sigma * sigma));
+    }
+    void init(float rx, float ry, float sigma) {
+        nx = int(32 * rx); ny = int(32 * ry);
+        float expX = Gaussian(rx, 0, sigma), expY = Gaussian(ry, 0, sigma);
+        f.assign((size_t)nx * ny, 0.f);
+        for (int y = 0; y < ny; ++y)
+            for (int x = 0; x < nx; ++x) {
+                float px = Lerp((x + 0.5f) / nx, -rx, rx), py = Lerp((y + 0.5f) / ny, -ry, ry);   // Bounds2f::Lerp
+                f[(size_t)y * nx + x] = std::max<float>(0, Gaussian(px, 0, sigma) - expX) * std::max<float>(0, Gaussian(py, 0, sigma) - expY);
+            }
+        cond.resize(ny);
+        std::vector<float> marg(ny);
+        for (int v = 0; v < ny; ++v) { cond[v].init(&f[(size_t)v * nx], nx, -rx, rx); marg[v] = cond[v].funcInt; }
+        marginal.init(marg.data(), ny, -ry, ry);
+    }
+    void Sample(const float *u, float *p, float *weight) const {
+        float pdfs[2]; int uv[2];
+        float d1 = marginal.Sample(u[1], &pdfs[1], &uv[1]);
+        float d0 = cond[uv[1]].Sample(u[0], &pdfs[0], &uv[0]);
+        p[0] = d0; p[1] = d1;
+        *weight = f[(size_t)uv[1] * nx + uv[0]] / (pdfs[0] * pdfs[1]);
+    }
+};
+
 struct Scene {
     const vspg_scene_desc *d = nullptr;
     const vspg_guiding_desc *g = nullptr;
@@ -166,6 +223,7 @@ struct Scene {
     std::vector<float> quadArea;
     std::vector<float> lightCdf;  // power sampler pmf
     BVHLightSampler lightBvh;     // "bvh" sampler (the reference's default)
+    GaussianFilterSampler gaussFilter;   // PixelFilter "gaussian" (pbrt's default filter)
     V3 sceneCenter; float sceneRadius = 0;
     int seed = 0;
     bool ownMajorant = false;
@@ -198,6 +256,7 @@ struct Scene {
         if (sum == 0) for (auto &v : lightCdf) v = 1.f, sum += 1.f;
         for (auto &v : lightCdf) v /= sum;
         lightBvh.Build(d->lights, d->n_lights, d->quads, quadArea);
+        if (d->camera.filter_type == 1) gaussFilter.init(d->camera.filter_radius[0], d->camera.filter_radius[1], d->camera.filter_sigma);
     }
     static bool IsRectangle(V3 p00, V3 p10, V3 p01, V3 p11) {  // shapes.h BilinearPatch::IsRectangle
         if (p00 == p01 || p01 == p11 || p11 == p10 || p10 == p00) return false;
@@ -1012,6 +1071,7 @@ struct Integrator {
         // BoxFilter::Sample (filters.h): p = Lerp(u, -radius, radius), weight 1
         float fx = Lerp(uf[0], -c.filter_radius[0], c.filter_radius[0]), fy = Lerp(uf[1], -c.filter_radius[1], c.filter_radius[1]);
         *filterWeight = 1.f;
+        if (c.filter_type == 1) { float fp[2]; sc->gaussFilter.Sample(uf, fp, filterWeight); fx = fp[0]; fy = fp[1]; }
         float pFilmX = px + fx + 0.5f, pFilmY = py + fy + 0.5f;
         (void)sampler.Get1D();  // time
         float ul[2]; sampler.Get2D(ul);

@@ -11,6 +11,13 @@ def small(name, **kw):
     """The BASELINE configs at sizes the CPU oracle finishes in seconds."""
     if name == "C1":
         return configs.config1(res=kw.get("res", 48), spp=kw.get("spp", 4))
+    if name == "C1G":   # C1 under pbrt's default pixel filter: gaussian, radius 1.5, sigma 0.5 (filters.cpp GaussianFilter::Create)
+        cfg = configs.config1(res=kw.get("res", 48), spp=kw.get("spp", 4))
+        for cam in (cfg.scene.desc.camera, cfg.scene.camera):
+            cam.filter_type, cam.filter_sigma = 1, 0.5
+            cam.filter_radius[0] = cam.filter_radius[1] = 1.5
+        cfg.name = "C1-gaussian-filter"
+        return cfg
     if name == "C1T":
         return configs.config1_triangles(res=kw.get("res", 48), spp=kw.get("spp", 4))
     common = dict(grid_n=kw.get("grid_n", 32), vol_leaves=kw.get("vol_leaves", 256), surf_leaves=kw.get("surf_leaves", 128))

@@ -284,3 +284,19 @@ def test_vsp_guiding_is_unbiased_in_the_oracle(orc):
     for tag in ("resampling", "nds"):
         m, se = means[tag]
         assert abs(m - ref) <= 4 * np.hypot(se, ref_se) + 0.02 * ref, (tag, means)
+
+
+def test_gaussian_filter_sampling_is_filter_importance_sampling(orc):
+    """pbrt's default pixel filter (gaussian r=1.5 sigma=0.5) is sampled through the tabulated FilterSampler
+    (filters.h:26-45): every sample carries weight f/pdf, which for a non-negative filter is the constant
+    integral of the tabulated function, and offsets stay inside the radius.  Rendered through the oracle: weight sums per pixel
+    are spp * that constant, and the image agrees in expectation with the box-filtered one away from edges."""
+    g = H.small("C1G", res=24, spp=32)
+    b = H.small("C1", res=24, spp=32)
+    fg, _ = orc.render(g.scene, None, g.ip, 0, g.spp, seed=2, nthreads=8)
+    fb, _ = orc.render(b.scene, None, b.ip, 0, b.spp, seed=2, nthreads=8)
+    w = fg[..., 3] / g.spp
+    assert np.allclose(w, w.mean(), rtol=1e-3) and 0.5 < w.mean() < 1.5     # constant weight = table integral
+    assert np.array_equal(fb[..., 3], np.full_like(fb[..., 3], b.spp))
+    mg = (fg[..., :3] / fg[..., 3:4]).mean(); mb = (fb[..., :3] / fb[..., 3:4]).mean()
+    assert abs(mg - mb) < 0.08 * mb, (mg, mb)

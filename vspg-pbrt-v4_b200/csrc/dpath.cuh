@@ -12,6 +12,7 @@ struct PathRegs {
     float rr_correction, vsp_next;
     V3 prevP, prevNs;
     int pixel, sampleIndex;
+    float filterWeight;            // FilterSample::weight of the camera sample (1 for the box filter)
 };
 
 VD void path_load(const PathSoA &P, int s, PathRegs &r) {
@@ -22,7 +23,7 @@ VD void path_load(const PathSoA &P, int s, PathRegs &r) {
     r.beta = V3(c.x, c.y, c.z); r.r_u = V3(c.w, d.x, d.y); r.r_l = V3(d.z, d.w, e.x); r.L = V3(e.y, e.z, e.w);
     r.rng.state = q.x; r.rng.inc = q.y;
     r.rr_correction = f.x; r.vsp_next = f.y; r.prevP = V3(f.z, f.w, g.x);
-    r.pixel = __float_as_int(g.y); r.sampleIndex = __float_as_int(g.z);
+    r.pixel = __float_as_int(g.y); r.sampleIndex = __float_as_int(g.z); r.filterWeight = g.w;
     float4 h = P.prev_ns[s]; r.prevNs = V3(h.x, h.y, h.z);
 }
 VD void path_store(const PathSoA &P, int s, const PathRegs &r) {
@@ -33,8 +34,41 @@ VD void path_store(const PathSoA &P, int s, const PathRegs &r) {
     P.rl_L[s] = make_float4(r.r_l.z, r.L.x, r.L.y, r.L.z);
     P.rng[s] = make_ulonglong2(r.rng.state, r.rng.inc);
     P.misc[s] = make_float4(r.rr_correction, r.vsp_next, r.prevP.x, r.prevP.y);
-    P.misc2[s] = make_float4(r.prevP.z, __int_as_float(r.pixel), __int_as_float(r.sampleIndex), 0.f);
+    P.misc2[s] = make_float4(r.prevP.z, __int_as_float(r.pixel), __int_as_float(r.sampleIndex), r.filterWeight);
     P.prev_ns[s] = make_float4(r.prevNs.x, r.prevNs.y, r.prevNs.z, 0.f);
+}
+
+// util/sampling.h:657-675 PiecewiseConstant1D::Sample over cdf[n+1] with func value fo = func[offset] supplied by the caller
+VD int find_interval_cdf(const float *cdf, int sz, float u) {   // util/math.h:508-519 with pred = cdf[i] <= u
+    int size = sz - 2, first = 1;
+    while (size > 0) {
+        int half = size >> 1, middle = first + half;
+        bool pr = __ldg(&cdf[middle]) <= u;
+        first = pr ? middle + 1 : first;
+        size = pr ? size - (half + 1) : half;
+    }
+    return clampi(first - 1, 0, sz - 2);
+}
+// filters.h:33-38 FilterSampler::Sample for the tabulated gaussian
+VD void sample_gaussian_filter(const DScene &sc, float u0, float u1, float *px, float *py, float *weight) {
+    const int nx = sc.filt_nx, ny = sc.filt_ny;
+    const float rx = sc.cam.filter_radius[0], ry = sc.cam.filter_radius[1];
+    int ov = find_interval_cdf(sc.filt_marg_cdf, ny + 1, u1);
+    float c0 = __ldg(&sc.filt_marg_cdf[ov]), c1 = __ldg(&sc.filt_marg_cdf[ov + 1]);
+    float du = u1 - c0;
+    if (c1 - c0 > 0) du /= c1 - c0;
+    float rowInt = __ldg(&sc.filt_cond_int[ov]);
+    float pdf1 = sc.filt_marg_int > 0 ? rowInt / sc.filt_marg_int : 0.f;
+    *py = lerpf((ov + du) / (float)ny, -ry, ry);
+    const float *cdf = sc.filt_cond_cdf + (size_t)ov * (nx + 1);
+    int ou = find_interval_cdf(cdf, nx + 1, u0);
+    c0 = __ldg(&cdf[ou]); c1 = __ldg(&cdf[ou + 1]);
+    du = u0 - c0;
+    if (c1 - c0 > 0) du /= c1 - c0;
+    float fv = __ldg(&sc.filt_f[(size_t)ov * nx + ou]);
+    float pdf0 = rowInt > 0 ? fabsf(fv) / rowInt : 0.f;
+    *px = lerpf((ou + du) / (float)nx, -rx, rx);
+    *weight = fv / (pdf0 * pdf1);
 }
 
 // cpu/integrators.cpp:272-334 EvaluatePixelSample (front half) + samplers.h:442-476, 797-814 + cameras.cpp:410-437
@@ -45,7 +79,9 @@ VD void generate_camera_path(const DScene &sc, int px, int py, int sampleIndex, 
     float lu = r.rng.uniform();
     int ch = min((int)floorf(lu * 3), 2);  // util/spectrum.h:335-339 hero channel
     float uf0 = r.rng.uniform(), uf1 = r.rng.uniform();
-    float fx = lerpf(uf0, -c.filter_radius[0], c.filter_radius[0]), fy = lerpf(uf1, -c.filter_radius[1], c.filter_radius[1]);
+    float fx = lerpf(uf0, -c.filter_radius[0], c.filter_radius[0]), fy = lerpf(uf1, -c.filter_radius[1], c.filter_radius[1]);   // BoxFilter::Sample
+    r.filterWeight = 1.f;
+    if (sc.filt_nx > 0) sample_gaussian_filter(sc, uf0, uf1, &fx, &fy, &r.filterWeight);
     float pFilmX = px + fx + 0.5f, pFilmY = py + fy + 0.5f;
     (void)r.rng.uniform();  // time
     float ul0 = r.rng.uniform(), ul1 = r.rng.uniform();
@@ -78,13 +114,12 @@ VD void generate_camera_path(const DScene &sc, int px, int py, int sampleIndex, 
 }
 
 // film.h:251-267 RGBFilm::AddSample (fp64 accumulators), after the NaN/Inf guard of integrators.cpp:308-318
-VD void film_add(const DScene &sc, double *film, int pixel, V3 L) {
+VD void film_add(const DScene &sc, double *film, int pixel, V3 L, float fw) {
     if (has_nan(L) || y_is_inf(L)) L = V3();
     const vspg_camera &c = sc.cam;
     float r = c.imaging_ratio * L.x, g = c.imaging_ratio * L.y, b = c.imaging_ratio * L.z;
     float m = fmaxf(r, fmaxf(g, b));
     if (m > c.max_component_value) { float s = c.max_component_value / m; r *= s; g *= s; b *= s; }
-    const float fw = 1.f;  // BoxFilter::Sample weight
     double *pix = film + 4 * (size_t)pixel;
     atomicAdd(pix + 0, (double)(fw * r));
     atomicAdd(pix + 1, (double)(fw * g));

@@ -119,6 +119,50 @@ inline void build_majorant_grid(const vspg_medium *m, float *out) {
             }
 }
 
+// ------------------------------------------------------------------ PixelFilter "gaussian" sampling table
+// filters.h:80-118 GaussianFilter, filters.h:26-45 + filters.cpp:133-147 FilterSampler, util/sampling.h:603-760
+// PiecewiseConstant1D/2D construction.  Layout handed to the device: f[ny][nx], condCdf[ny][nx+1], condInt[ny]
+// (= the marginal's func), margCdf[ny+1], margInt.
+inline float host_fast_exp(float x) {   // util/math.h:450-475 (CPU branch)
+    float xp = x * 1.442695041f;
+    float fxp = std::floor(xp), f = xp - fxp;
+    int i = (int)fxp;
+    float twoToF = std::fma(f, std::fma(f, std::fma(f, 0.0781455737f, 0.226173572f), 0.695556856f), 1.f);
+    uint32_t bits; memcpy(&bits, &twoToF, 4);
+    int exponent = (int)(bits >> 23) - 127 + i;
+    if (exponent < -126) return 0.f;
+    if (exponent > 127) return std::numeric_limits<float>::infinity();
+    bits &= 0x807fffffu;
+    bits |= (uint32_t)(exponent + 127) << 23;
+    float r; memcpy(&r, &bits, 4);
+    return r;
+}
+struct HostFilterTable { int nx = 0, ny = 0; std::vector<float> f, condCdf, condInt, margCdf; float margInt = 0; };
+inline void piecewise_cdf(const float *func, int n, float mn, float mx, float *cdf, float *funcInt) {
+    cdf[0] = 0;
+    for (int i = 1; i < n + 1; ++i) cdf[i] = cdf[i - 1] + std::abs(func[i - 1]) * (mx - mn) / n;
+    *funcInt = cdf[n];
+    if (*funcInt == 0) for (int i = 1; i < n + 1; ++i) cdf[i] = float(i) / float(n);
+    else for (int i = 1; i < n + 1; ++i) cdf[i] /= *funcInt;
+}
+inline HostFilterTable build_gaussian_filter(float rx, float ry, float sigma) {
+    const float Pi = 3.14159265358979323846f;
+    auto gaussian = [&](float x) { return 1 / std::sqrt(2 * Pi * sigma * sigma) * host_fast_exp(-(x * x) / (2 * sigma * sigma)); };
+    auto lerp = [](float t, float a, float b) { return (1 - t) * a + t * b; };
+    HostFilterTable T;
+    T.nx = int(32 * rx); T.ny = int(32 * ry);
+    float expX = gaussian(rx), expY = gaussian(ry);
+    T.f.resize((size_t)T.nx * T.ny); T.condCdf.resize((size_t)T.ny * (T.nx + 1)); T.condInt.resize(T.ny); T.margCdf.resize(T.ny + 1);
+    for (int y = 0; y < T.ny; ++y)
+        for (int x = 0; x < T.nx; ++x) {
+            float px = lerp((x + 0.5f) / T.nx, -rx, rx), py = lerp((y + 0.5f) / T.ny, -ry, ry);
+            T.f[(size_t)y * T.nx + x] = std::max(0.f, gaussian(px) - expX) * std::max(0.f, gaussian(py) - expY);
+        }
+    for (int v = 0; v < T.ny; ++v) piecewise_cdf(&T.f[(size_t)v * T.nx], T.nx, -rx, rx, &T.condCdf[(size_t)v * (T.nx + 1)], &T.condInt[v]);
+    piecewise_cdf(T.condInt.data(), T.ny, -ry, ry, T.margCdf.data(), &T.margInt);
+    return T;
+}
+
 // ------------------------------------------------------------------ threaded BVH over quads
 struct HostBvhNode { float bmin[3]; int skip; float bmax[3]; int prim_begin; int prim_count; int pad[3]; };
 struct HostBvh { std::vector<HostBvhNode> nodes; std::vector<int> prim_ids; };

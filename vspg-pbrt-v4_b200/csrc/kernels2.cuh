@@ -224,8 +224,8 @@ __global__ void __launch_bounds__(kBlock) k_finish(const DScene sc, const Wavefr
     for (int i = gtid(); i < n; i += gstride()) {
         int slot = W.done.items[i];
         float4 e = W.P.rl_L[slot];
-        int pixel = __float_as_int(W.P.misc2[slot].y);
-        film_add(sc, W.film, pixel, V3(e.y, e.z, e.w));
+        float4 m2 = W.P.misc2[slot];
+        film_add(sc, W.film, __float_as_int(m2.y), V3(e.y, e.z, e.w), m2.w);
         paths++;
         PathRegs r;
         bool ok = regenerate(sc, W, slot, r);

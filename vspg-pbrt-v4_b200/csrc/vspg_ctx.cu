@@ -130,7 +130,9 @@ int vspg_set_scene(vspg_ctx *ctx, const vspg_scene_desc *s) {
     CK(cudaSetDevice(ctx->device));
     if (s->n_spheres > 0)
         return fail(ctx, VSPG_ERR_UNSUPPORTED, "set_scene: spheres are not on the supported path yet (bilinear patches and triangles are)");
-    if (s->camera.filter_type != 0) return fail(ctx, VSPG_ERR_UNSUPPORTED, "set_scene: only the box filter is supported");
+    if (s->camera.filter_type != 0 && s->camera.filter_type != 1) return fail(ctx, VSPG_ERR_UNSUPPORTED, "set_scene: pixel filter must be box (0) or gaussian (1)");
+    if (s->camera.filter_type == 1 && (int(32 * s->camera.filter_radius[0]) < 1 || int(32 * s->camera.filter_radius[1]) < 1 || !(s->camera.filter_sigma > 0)))
+        return fail(ctx, VSPG_ERR_INVALID, "set_scene: gaussian filter needs radius >= 1/32 and sigma > 0");
     if (s->camera.width <= 0 || s->camera.height <= 0) return fail(ctx, VSPG_ERR_INVALID, "set_scene: bad film resolution");
     free_all(ctx->scene_allocs);
     ctx->have_scene = false;
@@ -268,6 +270,16 @@ int vspg_set_scene(vspg_ctx *ctx, const vspg_scene_desc *s) {
         CK(upload(ctx->scene_allocs, lb.inTree.data(), lb.inTree.size(), &sc.light_in_tree));
         CK(upload(ctx->scene_allocs, lb.infinite.data(), lb.infinite.size(), &sc.unbounded_lights));
         sc.n_lbvh = (int)lb.nodes.size(); sc.n_unbounded = (int)lb.infinite.size();
+    }
+    // ---- pixel filter
+    sc.filt_nx = sc.filt_ny = 0; sc.filt_f = sc.filt_cond_cdf = sc.filt_cond_int = sc.filt_marg_cdf = nullptr; sc.filt_marg_int = 0;
+    if (s->camera.filter_type == 1) {
+        HostFilterTable T = build_gaussian_filter(s->camera.filter_radius[0], s->camera.filter_radius[1], s->camera.filter_sigma);
+        CK(upload(ctx->scene_allocs, T.f.data(), T.f.size(), &sc.filt_f));
+        CK(upload(ctx->scene_allocs, T.condCdf.data(), T.condCdf.size(), &sc.filt_cond_cdf));
+        CK(upload(ctx->scene_allocs, T.condInt.data(), T.condInt.size(), &sc.filt_cond_int));
+        CK(upload(ctx->scene_allocs, T.margCdf.data(), T.margCdf.size(), &sc.filt_marg_cdf));
+        sc.filt_nx = T.nx; sc.filt_ny = T.ny; sc.filt_marg_int = T.margInt;
     }
     // ---- film
     if (ctx->film_w != s->camera.width || ctx->film_h != s->camera.height || !ctx->film) {

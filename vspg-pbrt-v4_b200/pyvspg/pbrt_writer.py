@@ -55,7 +55,9 @@ def scene_text(cfg, out_dir=None, outfile="out.exr", seed=0, integrator_name="gu
          f'Camera "perspective" "float fov" [{_f(cp["fov"])}] "float lensradius" [{_f(cp["lens_radius"])}] "float focaldistance" [{_f(cp["focal_distance"])}]',
          f'Film "rgb" "integer xresolution" [{sc.camera.width}] "integer yresolution" [{sc.camera.height}] "string filename" "{outfile}"',
          f'Sampler "independent" "integer pixelsamples" [{cfg.spp}] "integer seed" [{seed}]',
-         'PixelFilter "box"',
+         ('PixelFilter "box"' if sc.desc.camera.filter_type == 0 else
+          f'PixelFilter "gaussian" "float xradius" [{_f(sc.desc.camera.filter_radius[0])}] "float yradius" [{_f(sc.desc.camera.filter_radius[1])}] '
+          f'"float sigma" [{_f(sc.desc.camera.filter_sigma)}]'),
          integrator_block(cfg.ip, integrator_name, cache_file, isg_file, tr_file),
          'WorldBegin']
     for kind, e in sc.log:
