@@ -145,6 +145,33 @@ def cpu_oracle_paths_per_s(cfg, spp, seed=0):
     return cnt["paths"] / dt, cores, dt, cnt["paths"]
 
 
+def relmse_check(ctx, args):
+    """SURVEY 8(d) "relMSE vs CPU ref at equal spp", on a bounded instance of the workload (same scene, reduced film):
+    relMSE of the CUDA render and of the CPU oracle render against a common 1024-spp reference, 4 seeds each.
+    Uses the oracle as the checker (cpu leg of the bench only)."""
+    sys.path.insert(0, os.path.join(ROOT, "oracle"))
+    import orc
+    from pyvspg import configs, stats
+    key, kw, _ = WORKLOADS[args.workload]
+    small = dict(C1=dict(res=64, spp=8), C1T=dict(res=64, spp=8), C2=dict(res=64, spp=8, grid_n=64, vol_leaves=512, surf_leaves=256),
+                 C3=dict(res=64, spp=8, grid_n=64, vol_leaves=512, surf_leaves=256),
+                 C4=dict(width=96, height=54, spp=8, grid_n=64, vol_leaves=512, surf_leaves=256),
+                 C5=dict(width=96, height=54, spp=8, grid_n=32, vol_leaves=512, surf_leaves=256))[key]
+    cfg = configs.BUILDERS[key](**small)
+    ctx.set_scene(cfg.scene); ctx.set_guiding(cfg.guiding); ctx.set_integrator(cfg.ip)
+    ctx.film_clear(); ctx.render(0, 1024, seed=4242)
+    ref = stats.resolve(ctx.film_download())
+    rg, rc = [], []
+    for seed in range(4):
+        ctx.film_clear(); ctx.render(0, cfg.spp, seed=seed)
+        rg.append(stats.rel_mse(stats.resolve(ctx.film_download()), ref))
+        film_o, _ = orc.render(cfg.scene, cfg.guiding, cfg.ip, 0, cfg.spp, seed=100 + seed, nthreads=os.cpu_count() or 1)
+        rc.append(stats.rel_mse(stats.resolve(film_o), ref))
+    r = stats.compare(rg, rc)
+    return {"gpu": r["a"], "cpu": r["b"], "abs_diff": r["diff"], "tolerance": r["tolerance"], "agree": r["agree"], "seeds": 4,
+            "instance": f"{cfg.name} at {cfg.width}x{cfg.height}, {cfg.spp} spp; reference = 1024 spp (GPU, disjoint seed)"}
+
+
 def run_reference(args):
     """--impl reference: the reference's CPU algorithm on the host cores (oracle port; kind = "port")."""
     rank = int(os.environ.get("RANK", "0"))
@@ -321,7 +348,9 @@ def run_b200(args):
             "kernel_ms_sum": sum(ks[n]["ms"] for n in names), "timed_region_ms": ms_total,
         }
         cpu = None
+        relmse = None
         if not args.no_cpu_baseline and world == 1:
+            relmse = relmse_check(ctx, args)
             v1, cores, dt1, _ = cpu_oracle_paths_per_s(cfg, 1)
             cspp = args.cpu_spp or max(1, min(spp, int(15.0 / max(dt1, 1e-3))))
             v, cores, dtc, n = cpu_oracle_paths_per_s(cfg, cspp, seed=1)
@@ -333,7 +362,7 @@ def run_b200(args):
             "warmup": args.warmup, "ms_per_step": ms_total / args.steps, "higher_is_better": True, "scaling": "weak",
             "vs_baseline": None, "dtype": "f32", "data": "synthetic", "config": config_dict(cfg, args, world),
             "e2e": {"value": e2e_value, "unit": "paths/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h, "steps": e2e_steps},
-            "gpu_launches": cnt["kernel_launches"], "clocks": clk, "roofline": roofline, "cpu_baseline": cpu,
+            "gpu_launches": cnt["kernel_launches"], "clocks": clk, "roofline": roofline, "cpu_baseline": cpu, "relmse": relmse,
             "counters": {k: cnt[k] for k in ("paths", "density_queries", "dda_steps", "cache_lookups", "bvh_nodes", "shadow_rays", "wave_iterations")},
             "mean_radiance": float(film_host[..., :3].sum() / max(1.0, float(film_host[..., 3].sum()))),
         }

@@ -337,3 +337,27 @@ def test_errors_are_reported_not_fatal(ctx):
         ctx.set_integrator(ip)
     with pytest.raises(KeyError):
         api.integrator_defaults(no_such_parameter=1)
+
+
+@pytest.mark.parametrize("name,over", [("C2", {}), ("C3", {}), ("C5", dict(light_sampler=A.LIGHTSAMPLER_BVH))])
+def test_relmse_at_equal_spp_agrees_with_the_cpu_oracle(ctx, orc, name, over):
+    """SURVEY 8(d) image-level check: relMSE of the CUDA render and of the CPU oracle render against a common
+    high-spp reference (256x the spp, rendered on the GPU with a disjoint seed) agree within 10 % + 3 sigma over 8 seeds."""
+    from pyvspg import stats
+    cfg = H.small(name, res=40, spp=4)
+    for k, v in over.items():
+        setattr(cfg.ip, k, v)
+    _setup(ctx, cfg)
+    ctx.set_capacity(0)
+    ctx.film_clear()
+    ctx.render(0, 1024, seed=999)
+    ref = stats.resolve(ctx.film_download())
+    rg, rc = [], []
+    for seed in range(8):
+        ctx.film_clear()
+        ctx.render(0, cfg.spp, seed=seed)
+        rg.append(stats.rel_mse(stats.resolve(ctx.film_download()), ref))
+        film_o, _ = orc.render(cfg.scene, cfg.guiding, cfg.ip, 0, cfg.spp, seed=100 + seed, nthreads=8)
+        rc.append(stats.rel_mse(stats.resolve(film_o), ref))
+    r = stats.compare(rg, rc)
+    assert r["agree"], r
