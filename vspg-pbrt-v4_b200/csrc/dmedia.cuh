@@ -107,6 +107,27 @@ VD float density_lookup(const DMedium &m, V3 p) {
                    grid_at(m, ix + 1, iy + 1, iz), grid_at(m, ix, iy, iz + 1), grid_at(m, ix + 1, iy, iz + 1),
                    grid_at(m, ix, iy + 1, iz + 1), grid_at(m, ix + 1, iy + 1, iz + 1));
 }
+// The same lookup split in two so that a caller can put independent work between the load and its first use
+// (k_medium_rs issues the fetch for collision k, searches for collision k+1, then consumes k).
+struct DensityFetch { float4 a, b; float dx, dy, dz; };
+VD DensityFetch density_fetch_issue(const DMedium &m, V3 p) {   // p in [0,1]^3 medium-bounds coordinates
+    DensityFetch f;
+    float psx = p.x * m.nx - .5f, psy = p.y * m.ny - .5f, psz = p.z * m.nz - .5f;
+    float fx = floorf(psx), fy = floorf(psy), fz = floorf(psz);
+    int ix = (int)fx, iy = (int)fy, iz = (int)fz;
+    f.dx = psx - (float)ix; f.dy = psy - (float)iy; f.dz = psz - (float)iz;
+    if (m.layout == GRID_CELL8) {
+        if (ix < -1 || iy < -1 || iz < -1 || ix >= m.nx || iy >= m.ny || iz >= m.nz) { f.a = make_float4(0, 0, 0, 0); f.b = f.a; return f; }
+        size_t cell = ((size_t)(iz + 1) * (m.ny + 1) + (iy + 1)) * (m.nx + 1) + (ix + 1);
+        f.a = __ldg(&m.cells[2 * cell]); f.b = __ldg(&m.cells[2 * cell + 1]);
+    } else {
+        f.a = make_float4(grid_at(m, ix, iy, iz), grid_at(m, ix + 1, iy, iz), grid_at(m, ix, iy + 1, iz), grid_at(m, ix + 1, iy + 1, iz));
+        f.b = make_float4(grid_at(m, ix, iy, iz + 1), grid_at(m, ix + 1, iy, iz + 1), grid_at(m, ix, iy + 1, iz + 1), grid_at(m, ix + 1, iy + 1, iz + 1));
+    }
+    return f;
+}
+VD float density_fetch_value(const DensityFetch &f) { return trilerp(f.dx, f.dy, f.dz, f.a.x, f.a.y, f.a.z, f.a.w, f.b.x, f.b.y, f.b.z, f.b.w); }
+
 VD V3 rgb_at(const DMedium &m, const float *g, int x, int y, int z) {
     if (x < 0 || y < 0 || z < 0 || x >= m.nx || y >= m.ny || z >= m.nz) return V3();
     const float *q = g + 3 * ((size_t)(z * m.ny + y) * m.nx + x);

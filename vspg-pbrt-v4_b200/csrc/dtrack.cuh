@@ -7,18 +7,21 @@ namespace vspg {
 
 // media_sampleTMaj.h:49-117  SampleT_maj (delta / ratio tracking driver).  `ray.d` is already normalised and
 // tMax already scaled by |d| (the callers do lines :55-56).
-template <typename F>
-VD V3 track_T_maj(const DMedium &med, const Ray &ray, float tMax, float u, Rng &rng, int ch, TrackCounters &tc, F cb) {
+// GRAY: sigma_maj / T_maj carried as one float (dmath.cuh G1) -- valid when the medium's sigma_a, sigma_s are equal across RGB.
+template <bool GRAY, typename F>
+VD typename SpecT<GRAY>::type track_T_maj_t(const DMedium &med, const Ray &ray, float tMax, float u, Rng &rng, int ch, TrackCounters &tc, F cb) {
+    typedef typename SpecT<GRAY>::type Sp;
     MajorantIterator iter = sample_ray(med, ray, tMax);
-    V3 T_maj = splat(1.f);
+    Sp T_maj = to_spec<GRAY>(splat(1.f));
     bool done = false;
     Segment seg;
     while (!done) {
         if (!iter.next(&seg)) { tc.dda += iter.steps; return T_maj; }
-        float smc = seg.sigma_maj[ch];
+        const Sp sm = to_spec<GRAY>(seg.sigma_maj);
+        float smc = sm[ch];
         if (smc == 0) {
             float dt = seg_dt(seg.tMax, seg.tMin);
-            T_maj = T_maj * fast_exp3(-dt * seg.sigma_maj);
+            T_maj = T_maj * fast_exp3(-dt * sm);
             continue;
         }
         float tMin = seg.tMin;
@@ -26,22 +29,26 @@ VD V3 track_T_maj(const DMedium &med, const Ray &ray, float tMax, float u, Rng &
             float t = tMin + sample_exponential(u, smc);
             u = rng.uniform();
             if (t < seg.tMax) {
-                T_maj = T_maj * fast_exp3(-(t - tMin) * seg.sigma_maj);
+                T_maj = T_maj * fast_exp3(-(t - tMin) * sm);
                 V3 p = ray.at(t);
                 MediumProps mp = sample_point(med, p);
                 tc.queries++;
-                if (!cb(p, mp, seg.sigma_maj, T_maj)) { done = true; break; }
-                T_maj = splat(1.f);
+                if (!cb(p, mp, sm, T_maj)) { done = true; break; }
+                T_maj = to_spec<GRAY>(splat(1.f));
                 tMin = t;
             } else {
                 float dt = seg_dt(seg.tMax, tMin);
-                T_maj = T_maj * fast_exp3(-dt * seg.sigma_maj);
+                T_maj = T_maj * fast_exp3(-dt * sm);
                 break;
             }
         }
     }
     tc.dda += iter.steps;
-    return splat(1.f);
+    return to_spec<GRAY>(splat(1.f));
+}
+template <typename F>
+VD V3 track_T_maj(const DMedium &med, const Ray &ray, float tMax, float u, Rng &rng, int ch, TrackCounters &tc, F cb) {
+    return track_T_maj_t<false>(med, ray, tMax, u, rng, ch, tc, cb);
 }
 
 // media_sampleTMaj.h:136-248  SampleT_maj_Resampling

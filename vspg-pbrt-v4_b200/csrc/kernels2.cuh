@@ -157,7 +157,10 @@ __global__ void __launch_bounds__(G > 0 ? kScatterBlock : kBlock) k_shade(const 
 }
 
 // ------------------------------------------------------------------ shadow rays (SampleLd back half, vspg.cpp:1193-1252)
-__global__ void __launch_bounds__(kBlock) k_shadow(const DScene sc, const Wavefront W) {
+// GRAY: all media gray (see dmath.cuh G1) -- T_ray, r_l, r_u of the ratio tracker are scalars until the final weighting.
+template <bool GRAY>
+__global__ void __launch_bounds__(kBlock, GRAY ? 5 : 4) k_shadow(const DScene sc, const Wavefront W) {
+    typedef typename SpecT<GRAY>::type Sp;
     const int n = *W.shadow.count;
     TrackCounters tc; tc.queries = 0; tc.dda = 0;
     unsigned nodes = 0;
@@ -166,7 +169,7 @@ __global__ void __launch_bounds__(kBlock) k_shadow(const DScene sc, const Wavefr
         ShadowRec sr; shadow_load(W.P, slot, sr);
         const int ch = sr.channel;
         Ray lightRay; lightRay.o = sr.o; lightRay.d = sr.d; lightRay.medium = sr.medium;
-        V3 T_ray = splat(1.f), r_l = splat(1.f), r_u = splat(1.f);
+        Sp T_ray = to_spec<GRAY>(splat(1.f)), r_l = T_ray, r_u = T_ray;
         Rng rng; rng.set_sequence(hash_v3(lightRay.o), hash_v3(lightRay.d));
         bool blocked = false;
         while (!(lightRay.d == V3(0, 0, 0))) {
@@ -178,17 +181,17 @@ __global__ void __launch_bounds__(kBlock) k_shadow(const DScene sc, const Wavefr
                 Ray tr = lightRay;
                 tMax *= length(tr.d);
                 tr.d = normalize(tr.d);
-                V3 T_maj = track_T_maj(sc.media[lightRay.medium], tr, tMax, uu, rng, ch, tc,
-                                       [&](V3, const MediumProps &mp, V3 sigma_maj, V3 T_maj) {
-                                           V3 sigma_n = clamp_zero(sigma_maj - mp.sigma_a - mp.sigma_s);
+                Sp T_maj = track_T_maj_t<GRAY>(sc.media[lightRay.medium], tr, tMax, uu, rng, ch, tc,
+                                       [&](V3, const MediumProps &mp, Sp sigma_maj, Sp T_maj) {
+                                           Sp sigma_n = clamp_zero(sigma_maj - to_spec<GRAY>(mp.sigma_a) - to_spec<GRAY>(mp.sigma_s));
                                            float pdf = T_maj[ch] * sigma_maj[ch];
                                            T_ray = T_ray * (T_maj * sigma_n / pdf);
                                            r_l = r_l * (T_maj * sigma_maj / pdf);
                                            r_u = r_u * (T_maj * sigma_n / pdf);
-                                           V3 Tr = T_ray / avg3(r_l + r_u);
+                                           Sp Tr = T_ray / avg3(r_l + r_u);
                                            if (max_comp(Tr) < 0.05f) {
                                                float q = 0.75f;
-                                               if (rng.uniform() < q) T_ray = V3();
+                                               if (rng.uniform() < q) T_ray = Sp();
                                                else T_ray = T_ray / (1 - q);
                                            }
                                            return nonzero(T_ray);
@@ -204,9 +207,9 @@ __global__ void __launch_bounds__(kBlock) k_shadow(const DScene sc, const Wavefr
             lightRay.medium = hs.get_medium(lightRay.d);
         }
         if (!blocked) {
-            r_l = r_l * sr.rl;
-            r_u = r_u * sr.ru;
-            V3 Ld = sr.delta ? sr.contrib * T_ray / avg3(r_l) : sr.contrib * T_ray / avg3(r_l + r_u);
+            V3 rl3 = to_v3(r_l) * sr.rl;
+            V3 ru3 = to_v3(r_u) * sr.ru;
+            V3 Ld = sr.delta ? sr.contrib * to_v3(T_ray) / avg3(rl3) : sr.contrib * to_v3(T_ray) / avg3(rl3 + ru3);
             float4 e = W.P.rl_L[slot];
             e.y += Ld.x; e.z += Ld.y; e.w += Ld.z;
             W.P.rl_L[slot] = e;

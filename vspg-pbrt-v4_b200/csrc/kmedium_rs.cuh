@@ -12,35 +12,6 @@
 
 namespace vspg {
 
-// A medium whose sigma_a and sigma_s are equal across R, G and B ("gray": every BASELINE config except the rgbgrid of
-// C5) makes every spectral quantity of the reservoir walk -- sigma_maj, T_maj, trRatioEst, beta_rs, r_u_rs, the
-// selected candidate's numerator / denominator -- three copies of one float: each channel performs the identical
-// IEEE operation sequence.  G1 carries that one float; the GRAY kernel is bit-identical to the V3 kernel on such
-// scenes at a third of the arithmetic (16 -> 6 IEEE divisions, 9 -> 3 FastExp per collision) and ~20 fewer registers.
-struct G1 {
-    float v;
-    VD G1() : v(0) {}
-    VD explicit G1(float a) : v(a) {}
-    VD float operator[](int) const { return v; }
-};
-VD G1 operator*(G1 a, G1 b) { return G1(a.v * b.v); }
-VD G1 operator*(G1 a, float s) { return G1(a.v * s); }
-VD G1 operator*(float s, G1 a) { return G1(a.v * s); }
-VD G1 operator/(G1 a, G1 b) { return G1(a.v / b.v); }
-VD G1 operator/(G1 a, float s) { return G1(a.v / s); }
-VD G1 operator+(G1 a, G1 b) { return G1(a.v + b.v); }
-VD G1 operator-(G1 a, G1 b) { return G1(a.v - b.v); }
-VD G1 operator-(G1 a) { return G1(-a.v); }
-VD G1 clamp_zero(G1 a) { return G1(fmaxf(0.f, a.v)); }
-VD G1 fast_exp3(G1 a) { return G1(fast_exp(a.v)); }
-template <bool GRAY> struct SpecT { typedef V3 type; };
-template <> struct SpecT<true> { typedef G1 type; };
-template <bool GRAY> VD typename SpecT<GRAY>::type to_spec(V3 v);
-template <> VD V3 to_spec<false>(V3 v) { return v; }
-template <> VD G1 to_spec<true>(V3 v) { return G1(v.x); }
-VD V3 to_v3(V3 v) { return v; }
-VD V3 to_v3(G1 g) { return splat(g.v); }
-
 enum { RS_NEED_SEG = 1, RS_IN_SEG = 2, RS_DONE = 3 };
 
 template <bool GRAY>
@@ -207,8 +178,8 @@ VD void rs_search_step(RsLane<GRAY> &s, float &t, bool &hit) {
 // Per trip: up to kRsSearchMax search steps, leaving early as soon as at least half of the lanes still walking have a
 // collision ready; then the collision body, predicated on `hit`.  Bounding the search keeps both halves of the trip
 // above ~60 % lane utilisation (an unbounded search ran at 7 lanes of 32, profiles/r01c).
-template <bool GRAY>
-__global__ void __launch_bounds__(kBlock, GRAY ? 5 : 4) k_medium_rs(const DScene sc, const Wavefront W, int *cursor) {
+template <bool GRAY, int MINB>
+__global__ void __launch_bounds__(kBlock, MINB) k_medium_rs(const DScene sc, const Wavefront W, int *cursor) {
     typedef typename SpecT<GRAY>::type Sp;
     const int n = *W.medium_rs.count;
     const int lane = threadIdx.x & 31;
@@ -216,6 +187,9 @@ __global__ void __launch_bounds__(kBlock, GRAY ? 5 : 4) k_medium_rs(const DScene
     RsLane<GRAY> s;
     s.phase = RS_DONE; s.it.init_empty(); s.medium = 0; s.ch = 0;
     bool busy = false, drained = false;
+    // pending collision of the software pipeline (GRAY only)
+    bool pend = false; Sp pT_maj, pSigma; V3 pP; DensityFetch pf;
+    pf.a = pf.b = make_float4(0, 0, 0, 0); pf.dx = pf.dy = pf.dz = 0;
     while (true) {
         __syncwarp();
         unsigned idle = __ballot_sync(kFull, !busy);
@@ -245,14 +219,29 @@ __global__ void __launch_bounds__(kBlock, GRAY ? 5 : 4) k_medium_rs(const DScene
                 unsigned walking = __ballot_sync(kFull, s.phase != RS_DONE && !hit);
                 if (2 * __popc(hits) >= __popc(hits | walking)) break;
             }
-            // ---- (2) density fetch + reservoir callback (vspg.cpp:690-731)
-            if (hit) {
-                const DMedium &med = sc.media[s.medium];
-                Sp T_maj = s.T_maj * fast_exp3(-(t - s.tMin) * s.segSigma);
-                V3 p = s.ray.at(t);
-                MediumProps mp = sample_point(med, p);
+            // ---- (2) reservoir callback (vspg.cpp:690-731).  GRAY (uniformgrid media): software-pipelined -- the
+            // density cell of collision k was requested at the end of the previous trip and is consumed here, after the
+            // search for collision k+1 has run, so the DRAM/L2 latency of the gather overlaps the search (the kernel was
+            // long_scoreboard-bound, profiles/r01j).  The search never reads the density: it only needs tMin / T_maj,
+            // which are committed when the fetch is issued.  Order of the path sampler's draws is unchanged (the
+            // search uses the tracking RNG only).
+            if (GRAY ? pend : hit) {
+                Sp T_maj, sigma_maj; V3 p; MediumProps mp;
+                if (GRAY) {
+                    const DMedium &med = sc.media[s.medium];
+                    T_maj = pT_maj; sigma_maj = pSigma; p = pP;
+                    float d = density_fetch_value(pf);
+                    mp.g = med.g; mp.sigma_a = ld3(med.sigma_a) * d; mp.sigma_s = ld3(med.sigma_s) * d;   // sample_point, GRID branch
+                    pend = false;
+                } else {
+                    T_maj = s.T_maj * fast_exp3(-(t - s.tMin) * s.segSigma);
+                    p = s.ray.at(t);
+                    mp = sample_point(sc.media[s.medium], p);
+                    sigma_maj = s.segSigma;
+                    s.T_maj = to_spec<GRAY>(splat(1.f));
+                    s.tMin = t;
+                }
                 tc.queries++;
-                Sp sigma_maj = s.segSigma;
                 Sp sigma_s = to_spec<GRAY>(mp.sigma_s);
                 Sp sigma_t = sigma_s + to_spec<GRAY>(mp.sigma_a);
                 Sp sigma_n = clamp_zero(sigma_maj - sigma_t);
@@ -272,12 +261,24 @@ __global__ void __launch_bounds__(kBlock, GRAY ? 5 : 4) k_medium_rs(const DScene
                 s.beta_rs = s.beta_rs * f;
                 s.r_u_rs = s.r_u_rs * f;
                 s.trRatioEst = s.trRatioEst * (sigma_n / sigma_maj);
+            }
+            // ---- (3) GRAY: request the density cell of the collision just found and commit the walk state
+            if (GRAY && hit) {
+                const DMedium &med = sc.media[s.medium];
+                pT_maj = s.T_maj * fast_exp3(-(t - s.tMin) * s.segSigma);
+                pP = s.ray.at(t);
+                pSigma = s.segSigma;
+                pf = density_fetch_issue(med, bounds_offset(med, apply_inverse_point(med, pP)));
                 s.T_maj = to_spec<GRAY>(splat(1.f));
                 s.tMin = t;
+                pend = true;
             }
-            if (__any_sync(kFull, busy && s.phase == RS_DONE)) break;
+            // leave the trip loop once enough lanes have finished their walk (or are idle) to finalise / refill as a batch:
+            // finalising one lane at a time cost 16 % of the kernel at 1.6 active lanes (profiles/r01j source page)
+            unsigned fin = __ballot_sync(kFull, !busy || (s.phase == RS_DONE && !pend));
+            if (__popc(fin) >= kRsRefillIdle) break;
         }
-        if (busy && s.phase == RS_DONE) {
+        if (busy && s.phase == RS_DONE && !pend) {
             tc.dda += s.it.steps;
             rs_finalize<GRAY>(sc, W, s);
             busy = false;

@@ -89,8 +89,9 @@ int vspg_render(vspg_ctx *ctx, int spp_begin, int spp_end, int spp_stride, int x
     while (true) {
         if (timing) CK(cudaEventRecord(ctx->ev[0], st));
         VSPG_STAGE(VSPG_K_INTERSECT, (k_intersect<<<grid, kBlock, 0, st>>>(sc, W)));
-        if (ctx->all_gray) k_medium_rs<true><<<ctx->sm_count * 5, kBlock, 0, st>>>(sc, W, ctx->qcounts + Q_COUNT);
-        else k_medium_rs<false><<<ctx->sm_count * 4, kBlock, 0, st>>>(sc, W, ctx->qcounts + Q_COUNT);
+        if (ctx->all_gray && ctx->rs_occ == 5) k_medium_rs<true, 5><<<ctx->sm_count * 5, kBlock, 0, st>>>(sc, W, ctx->qcounts + Q_COUNT);
+        else if (ctx->all_gray) k_medium_rs<true, 4><<<ctx->sm_count * 4, kBlock, 0, st>>>(sc, W, ctx->qcounts + Q_COUNT);
+        else k_medium_rs<false, 4><<<ctx->sm_count * 4, kBlock, 0, st>>>(sc, W, ctx->qcounts + Q_COUNT);
         VSPG_STAGE(VSPG_K_MEDIUM, (k_medium<<<grid, kBlock, 0, st>>>(sc, W)));
         if (guidedVol) {
             k_lookup<false><<<grid, kBlock, 0, st>>>(sc, W, W.volscatter, W.vol8, W.vol16, W.vol32);
@@ -107,7 +108,8 @@ int vspg_render(vspg_ctx *ctx, int spp_begin, int spp_end, int spp_stride, int x
             VSPG_STAGE(VSPG_K_SHADE, (k_shade<32><<<sgrid, sblock, 0, st>>>(sc, W, W.sh32)));
             ctx->launches += 3;
         } else VSPG_STAGE(VSPG_K_SHADE, (k_shade<0><<<grid, kBlock, 0, st>>>(sc, W, W.shade)));
-        VSPG_STAGE(VSPG_K_SHADOW, (k_shadow<<<grid, kBlock, 0, st>>>(sc, W)));
+        if (ctx->all_gray) VSPG_STAGE(VSPG_K_SHADOW, (k_shadow<true><<<grid, kBlock, 0, st>>>(sc, W)));
+        else VSPG_STAGE(VSPG_K_SHADOW, (k_shadow<false><<<grid, kBlock, 0, st>>>(sc, W)));
         VSPG_STAGE(VSPG_K_FINISH, (k_finish<<<grid, kBlock, 0, st>>>(sc, W)));
         ctx->launches += 8; ctx->iterations++;
         // swap roles: next becomes active; clear every other counter
