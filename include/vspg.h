@@ -363,6 +363,11 @@ int vspg_debug_cache_lookup(vspg_ctx *ctx, int is_surface, int n, const float *p
 int vspg_debug_light_sample(vspg_ctx *ctx, int n, const float *pos3, const float *ns3, const float *u, const int *light_of,
                             int *out_light, float *out_pmf, float *out_pmf_of);
 
+/* Integrator::Intersect (cpu/integrators.cpp:341-349 -> BVHAggregate::Intersect, cpu/aggregates.cpp:529-579) at n rays
+ * (rays7 = o, d, tMax) followed by the shape's InteractionFromIntersection: out_prim[i] = primitive id counted over
+ * quads, then triangles, then spheres (-1 = miss); out10[i] = tHit, p(), pi.Error(), n. */
+int vspg_debug_intersect(vspg_ctx *ctx, int n, const float *rays7, int *out_prim, float *out10);
+
 /* GuidedPhaseFunction / GuidedBSDF (cpu/guiding.h:57-638) on explicit inputs. */
 typedef struct vspg_gs_input {
     float p[3];

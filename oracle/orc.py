@@ -128,6 +128,15 @@ def light_sample(scene, ip, pos3, ns3, u, light_of):
     return light, pmf, pmf_of
 
 
+def intersect(scene, ip, rays7):
+    rays7 = np.ascontiguousarray(rays7, dtype=np.float32).reshape(-1, 7)
+    n = rays7.shape[0]
+    prim, out = np.zeros(n, np.int32), np.zeros((n, 10), np.float32)
+    rc = lib().orc_intersect(C.byref(scene.desc), C.byref(ip), n, _fp(rays7), prim.ctypes.data_as(PI), _fp(out))
+    assert rc == 0, rc
+    return prim, out
+
+
 def guided_sample(scene, guiding, ip, is_surface, inputs):
     n = len(inputs)
     out = (A.GsOutput * n)()

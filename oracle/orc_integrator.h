@@ -11,6 +11,7 @@
 #include "orc_guiding.h"
 #include "orc_media.h"
 #include "orc_lightbvh.h"
+#include "orc_sphere.h"
 
 namespace orc {
 
@@ -20,6 +21,7 @@ struct Hit {
     int kind = 0, index = -1;  // 0 quad, 1 triangle, 2 sphere
     float u = 0, v = 0;
     float b[3] = {0, 0, 0};  // triangle barycentrics (TriangleIntersection)
+    V3 pObj;                 // sphere: refined object-space hit point (QuadricIntersection)
 };
 
 // Surface interaction data the integrator consumes (interaction.h SurfaceInteraction subset)
@@ -246,9 +248,13 @@ struct Scene {
             for (V3 p : {V3(t.p0), V3(t.p1), V3(t.p2)})
                 for (int a = 0; a < 3; a++) { bmin[a] = std::min(bmin[a], p[a]); bmax[a] = std::max(bmax[a], p[a]); }
         }
+        for (int i = 0; i < d->n_spheres; i++) {   // shapes.cpp:33-36 Sphere::Bounds through translate(center)
+            const vspg_sphere &sp = d->spheres[i];
+            for (int a = 0; a < 3; a++) { bmin[a] = std::min(bmin[a], -sp.radius + sp.center[a]); bmax[a] = std::max(bmax[a], sp.radius + sp.center[a]); }
+        }
         // Bounds3::BoundingSphere: center = (pMin+pMax)/2, radius = Inside(center) ? Distance(center, pMax) : 0
         sceneCenter = (bmin + bmax) / 2;
-        sceneRadius = (d->n_quads + d->n_triangles) ? Distance(sceneCenter, bmax) : 0;
+        sceneRadius = (d->n_quads + d->n_triangles + d->n_spheres) ? Distance(sceneCenter, bmax) : 0;
         // PowerLightSampler pmf (lightsamplers.cpp:76-96): phi averaged over RGB
         lightCdf.assign(d->n_lights, 0.f);
         float sum = 0;
@@ -317,13 +323,34 @@ struct Scene {
                 h.b[0] = b[0]; h.b[1] = b[1]; h.b[2] = b[2];
             }
         }
+        // spheres: same convention (Sphere::BasicIntersect tests both roots against tMax)
+        for (int i = 0; i < d->n_spheres; i++) {
+            const vspg_sphere &q = d->spheres[i];
+            float t; V3 pObj;
+            if (IntersectSphere(ro, rd, tMax, V3(q.center), q.radius, &t, &pObj) && t < best) {
+                best = t; h.valid = true; h.t = t; h.kind = 2; h.index = i; h.u = h.v = 0; h.pObj = pObj;
+            }
+        }
         return h;
     }
     // shapes.h:1398-1500 BilinearPatch::InteractionFromIntersection (no mesh uv / normals) + primitive.cpp
     // GeometricPrimitive::Intersect -> SetIntersectionProperties (interaction.h:218-229)
-    int HitMaterial(const Hit &h) const { return h.kind == 1 ? d->triangles[h.index].material : d->quads[h.index].material; }
+    int HitMaterial(const Hit &h) const {
+        return h.kind == 2 ? d->spheres[h.index].material : h.kind == 1 ? d->triangles[h.index].material : d->quads[h.index].material;
+    }
     SurfaceIntr MakeIntr(const Hit &h, V3 rayD, int rayMedium) const {
         SurfaceIntr s;
+        if (h.kind == 2) {  // shapes.h:241-292 Sphere::InteractionFromIntersection (uv unused by the diffuse path: left 0)
+            const vspg_sphere &q = d->spheres[h.index];
+            SphereInteraction(h.pObj, V3(q.center), q.radius, q.flip_normal != 0, &s.p, &s.pError, &s.n, &s.dpdu);
+            s.ns = s.n;
+            s.wo = Normalize(-rayD);
+            s.uv[0] = s.uv[1] = 0;
+            s.material = q.material; s.areaLight = q.area_light;
+            s.hasInterface = q.has_interface && (q.medium_inside != q.medium_outside);
+            s.mediumInside = q.medium_inside; s.mediumOutside = q.medium_outside; s.rayMedium = rayMedium;
+            return s;
+        }
         if (h.kind == 1) {  // shapes.h:884-945 Triangle::InteractionFromIntersection, default uvs, no mesh normals
             const vspg_triangle &q = d->triangles[h.index];
             V3 p0(q.p0), p1(q.p1), p2(q.p2);

@@ -109,6 +109,24 @@ int orc_light_sample(const vspg_scene_desc *d, const vspg_integrator_params *ip,
     return 0;
 }
 
+int orc_intersect(const vspg_scene_desc *d, const vspg_integrator_params *ip, int n, const float *rays7, int *out_prim, float *out10) {
+    Scene sc; sc.init(d, nullptr, ip, true);
+    for (int i = 0; i < n; i++) {
+        const float *r = rays7 + 7 * i;
+        V3 o(r), dir(r + 3);
+        Hit h = sc.Intersect(o, dir, r[6]);
+        float *q = out10 + 10 * i;
+        for (int k = 0; k < 10; k++) q[k] = 0;
+        out_prim[i] = -1;
+        if (!h.valid) continue;
+        out_prim[i] = h.kind == 0 ? h.index : h.kind == 1 ? d->n_quads + h.index : d->n_quads + d->n_triangles + h.index;
+        SurfaceIntr s = sc.MakeIntr(h, dir, -1);
+        q[0] = h.t;
+        for (int k = 0; k < 3; k++) { q[1 + k] = s.p[k]; q[4 + k] = s.pError[k]; q[7 + k] = s.n[k]; }
+    }
+    return 0;
+}
+
 // ------------------------------------------------------------- guiding
 int orc_cache_lookup(const vspg_field *f, int n, const float *pos3, const float *u, int *out_leaf, int *out_region, float *out_u) {
     for (int i = 0; i < n; i++) {

@@ -42,6 +42,8 @@ def assert_descs_equal(d, e):
         assert raw(d.quads[i]) == raw(e.quads[i]), f"quad {i}"
     for i in range(d.n_triangles):
         assert raw(d.triangles[i]) == raw(e.triangles[i]), f"triangle {i}"
+    for i in range(d.n_spheres):
+        assert raw(d.spheres[i]) == raw(e.spheres[i]), f"sphere {i}"
     for i in range(d.n_materials):
         assert raw(d.materials[i]) == raw(e.materials[i]), f"material {i}"
     for i in range(d.n_lights):
@@ -92,7 +94,7 @@ def write_exr(path, channels):
 
 
 # ------------------------------------------------------------------ descs
-@pytest.mark.parametrize("name", ["C1", "C1T", "C1G", "C2-unguided", "C5-unguided"])
+@pytest.mark.parametrize("name", ["C1", "C1T", "C1S", "C1G", "C2-unguided", "C5-unguided"])
 def test_front_end_reproduces_the_harness_descs(name, tmp_path):
     base = name.split("-")[0]
     cfg = H.small(base, grid_n=8)

@@ -48,6 +48,22 @@ __global__ void k_debug_light_sample(const DScene sc, int n, const float *pos3, 
     }
 }
 
+__global__ void k_debug_intersect(const DScene sc, int n, const float *rays7, int *outPrim, float *out10) {
+    for (int i = gtid(); i < n; i += gstride()) {
+        const float *r = rays7 + 7 * i;
+        V3 o(r[0], r[1], r[2]), d(r[3], r[4], r[5]);
+        unsigned nodes = 0;
+        Hit h = scene_intersect(sc, o, d, r[6], nodes);
+        float *q = out10 + 10 * i;
+        outPrim[i] = h.prim;
+        for (int k = 0; k < 10; k++) q[k] = 0;
+        if (h.prim < 0) continue;
+        SurfaceIntr s = make_intr(sc, h, o, d, -1);
+        q[0] = h.t; q[1] = s.p.x; q[2] = s.p.y; q[3] = s.p.z; q[4] = s.pError.x; q[5] = s.pError.y; q[6] = s.pError.z;
+        q[7] = s.n.x; q[8] = s.n.y; q[9] = s.n.z;
+    }
+}
+
 __global__ void k_debug_density(const DScene sc, int medium, int n, const float *pos3, float *out7) {
     for (int i = gtid(); i < n; i += gstride()) {
         MediumProps mp = sample_point(sc.media[medium], V3(pos3[3 * i], pos3[3 * i + 1], pos3[3 * i + 2]));

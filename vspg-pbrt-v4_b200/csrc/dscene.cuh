@@ -29,14 +29,15 @@ struct DMedium {
 };
 
 // One surface primitive: a bilinear patch (p00,p10,p01,p11) or a triangle (p0,p1,p2 in p00,p10,p01; p11 unused).
-// Quads come first in the array (prim id == quad index, so area lights index it directly), triangles after them.
-enum { PRIM_QUAD = 0, PRIM_TRIANGLE = 1 };
+// Quads come first in the array (prim id == quad index, so area lights index it directly), triangles after them,
+// then full spheres.
+enum { PRIM_QUAD = 0, PRIM_TRIANGLE = 1, PRIM_SPHERE = 2 };   // sphere: centre in p00, radius in p10[0]
 struct DQuad {
     float p00[3], p10[3], p01[3], p11[3];
     int material, area_light, medium_inside, medium_outside, has_interface, flip_normal;
     int is_rect;          // BilinearPatch::IsRectangle (shapes.h), precomputed on the host
     float area;
-    int kind;             // PRIM_QUAD / PRIM_TRIANGLE
+    int kind;             // PRIM_QUAD / PRIM_TRIANGLE / PRIM_SPHERE
 };
 
 // Threaded (stackless) BVH node: DFS order, `skip` = next node when this subtree is done/missed.

@@ -2,6 +2,7 @@
 // (threaded, skip-link) BVH walk, surface interaction construction and ray spawning.
 #pragma once
 #include "dmedia.cuh"
+#include "dsphere.cuh"
 
 namespace vspg {
 
@@ -182,6 +183,13 @@ VD Hit scene_intersect(const DScene &sc, V3 ro, V3 rd, float tMax, unsigned &nod
                 int q = __ldg(&sc.prim_ids[primBegin + i]);
                 const DQuad &Q = sc.quads[q];
                 float u, v, t, b2;
+                if (Q.kind == PRIM_SPHERE) {   // tested against the ray's own tMax like triangles (both roots are compared with it)
+                    V3 pObj;
+                    if (intersect_sphere(ro, rd, rayTMax, ld3(Q.p00), Q.p10[0], &t, &pObj) && (t < h.t || (t == h.t && h.prim >= 0 && q < h.prim))) {
+                        h.t = t; h.u = 0; h.v = 0; h.prim = q;
+                    }
+                    continue;
+                }
                 bool got = Q.kind == PRIM_TRIANGLE ? intersect_triangle(ro, rd, rayTMax, ld3(Q.p00), ld3(Q.p10), ld3(Q.p01), &u, &v, &b2, &t)
                                                    : intersect_bilinear_patch(ro, rd, ld3(Q.p00), ld3(Q.p10), ld3(Q.p01), ld3(Q.p11), &u, &v, &t);
                 if (got && (t < h.t || (t == h.t && h.prim >= 0 && q < h.prim))) { h.t = t; h.u = u; h.v = v; h.prim = q; }
@@ -199,6 +207,18 @@ VD SurfaceIntr make_intr(const DScene &sc, const Hit &h, V3 rayO, V3 rayD, int r
     SurfaceIntr s;
     const DQuad &q = sc.quads[h.prim];
     V3 p00 = ld3(q.p00), p10 = ld3(q.p10), p01 = ld3(q.p01), p11 = ld3(q.p11);
+    if (q.kind == PRIM_SPHERE) {   // the hit record carries t only: the quadric hit point is recomputed from the ray
+        float t; V3 pObj;
+        intersect_sphere(rayO, rayD, inff(), p00, p10.x, &t, &pObj);
+        sphere_interaction(pObj, p00, p10.x, q.flip_normal != 0, &s.p, &s.pError, &s.n, &s.dpdu);
+        s.ns = s.n;
+        s.wo = normalize(-rayD);
+        s.u = s.v = 0;   // (phi, theta) parametrisation only feeds textures, which this path does not have
+        s.material = q.material; s.areaLight = q.area_light;
+        s.hasInterface = q.has_interface && (q.medium_inside != q.medium_outside);
+        s.mediumInside = q.medium_inside; s.mediumOutside = q.medium_outside; s.rayMedium = rayMedium;
+        return s;
+    }
     if (q.kind == PRIM_TRIANGLE) {
         V3 p0 = p00, p1 = p10, p2 = p01;
         float b0 = h.u, b1 = h.v, b2 = 0, t;

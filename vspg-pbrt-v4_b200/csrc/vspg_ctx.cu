@@ -130,8 +130,6 @@ int vspg_build_majorant_grid(const vspg_medium *m, float *out) {
 int vspg_set_scene(vspg_ctx *ctx, const vspg_scene_desc *s) {
     if (!ctx || !s) return VSPG_ERR_INVALID;
     CK(cudaSetDevice(ctx->device));
-    if (s->n_spheres > 0)
-        return fail(ctx, VSPG_ERR_UNSUPPORTED, "set_scene: spheres are not on the supported path yet (bilinear patches and triangles are)");
     if (s->camera.filter_type != 0 && s->camera.filter_type != 1) return fail(ctx, VSPG_ERR_UNSUPPORTED, "set_scene: pixel filter must be box (0) or gaussian (1)");
     if (s->camera.filter_type == 1 && (int(32 * s->camera.filter_radius[0]) < 1 || int(32 * s->camera.filter_radius[1]) < 1 || !(s->camera.filter_sigma > 0)))
         return fail(ctx, VSPG_ERR_INVALID, "set_scene: gaussian filter needs radius >= 1/32 and sigma > 0");
@@ -187,8 +185,9 @@ int vspg_set_scene(vspg_ctx *ctx, const vspg_scene_desc *s) {
         if (d.type == VSPG_MEDIUM_RGBGRID || d.sigma_a[0] != d.sigma_a[1] || d.sigma_a[0] != d.sigma_a[2] || d.sigma_s[0] != d.sigma_s[1] || d.sigma_s[0] != d.sigma_s[2])
             ctx->all_gray = false;
     // ---- quads + BVH
-    // prims = quads, then triangles stored in the same record (p0,p1,p2 in p00,p10,p01; kind = PRIM_TRIANGLE)
-    const int nPrims = s->n_quads + s->n_triangles;
+    // prims = quads, then triangles stored in the same record (p0,p1,p2 in p00,p10,p01; kind = PRIM_TRIANGLE), then full
+    // spheres (kind = PRIM_SPHERE; the host-side record holds the corners of Sphere::Bounds for the BVH build)
+    const int nPrims = s->n_quads + s->n_triangles + s->n_spheres;
     std::vector<vspg_quad> hostPrims(nPrims);
     std::vector<DQuad> quads(nPrims);
     for (int i = 0; i < s->n_triangles; i++) {
@@ -199,20 +198,38 @@ int vspg_set_scene(vspg_ctx *ctx, const vspg_scene_desc *s) {
         q.has_interface = t.has_interface; q.flip_normal = t.flip_normal;
         if (t.area_light >= 0) return fail(ctx, VSPG_ERR_UNSUPPORTED, "set_scene: triangle %d: area lights must be bilinear patches (emissive triangles are not built yet)", i);
     }
+    for (int i = 0; i < s->n_spheres; i++) {
+        const vspg_sphere &t = s->spheres[i];
+        vspg_quad &q = hostPrims[s->n_quads + s->n_triangles + i];
+        if (!(t.radius > 0)) return fail(ctx, VSPG_ERR_INVALID, "set_scene: sphere %d has radius <= 0", i);
+        for (int a = 0; a < 3; a++) {   // shapes.cpp:33-36 Sphere::Bounds through translate(center)
+            q.p00[a] = q.p10[a] = q.p01[a] = -t.radius + t.center[a];
+            q.p11[a] = t.radius + t.center[a];
+        }
+        q.material = t.material; q.area_light = t.area_light; q.medium_inside = t.medium_inside; q.medium_outside = t.medium_outside;
+        q.has_interface = t.has_interface; q.flip_normal = t.flip_normal;
+        if (t.area_light >= 0) return fail(ctx, VSPG_ERR_UNSUPPORTED, "set_scene: sphere %d: area lights must be bilinear patches (emissive spheres are not built yet)", i);
+    }
     float bmin[3] = {INFINITY, INFINITY, INFINITY}, bmax[3] = {-INFINITY, -INFINITY, -INFINITY};
     for (int i = 0; i < s->n_quads; i++) hostPrims[i] = s->quads[i];
     for (int i = 0; i < nPrims; i++) {
         const vspg_quad &q = hostPrims[i];
         DQuad &d = quads[i];
-        d.kind = i < s->n_quads ? PRIM_QUAD : PRIM_TRIANGLE;
+        d.kind = i < s->n_quads ? PRIM_QUAD : i < s->n_quads + s->n_triangles ? PRIM_TRIANGLE : PRIM_SPHERE;
         memcpy(d.p00, q.p00, 12); memcpy(d.p10, q.p10, 12); memcpy(d.p01, q.p01, 12); memcpy(d.p11, q.p11, 12);
+        if (d.kind == PRIM_SPHERE) {
+            const vspg_sphere &t = s->spheres[i - s->n_quads - s->n_triangles];
+            memcpy(d.p00, t.center, 12); d.p10[0] = t.radius; d.p10[1] = d.p10[2] = 0;
+            memset(d.p01, 0, 12); memset(d.p11, 0, 12);
+        }
         d.material = q.material; d.area_light = q.area_light; d.medium_inside = q.medium_inside; d.medium_outside = q.medium_outside;
         d.has_interface = q.has_interface; d.flip_normal = q.flip_normal;
         if (q.material >= s->n_materials || q.area_light >= s->n_lights || q.medium_inside >= s->n_media || q.medium_outside >= s->n_media)
             return fail(ctx, VSPG_ERR_INVALID, "set_scene: primitive %d references an out-of-range material/light/medium", i);
         H3 p00(q.p00), p10(q.p10), p01(q.p01), p11(q.p11);
         if (d.kind == PRIM_QUAD) { d.is_rect = quad_is_rectangle(p00, p10, p01, p11) ? 1 : 0; d.area = quad_area(p00, p10, p01, p11); }
-        else { d.is_rect = 0; d.area = 0.5f * hlen(hcross(p10 - p00, p01 - p00)); }   // shapes.h Triangle::Area
+        else if (d.kind == PRIM_TRIANGLE) { d.is_rect = 0; d.area = 0.5f * hlen(hcross(p10 - p00, p01 - p00)); }   // shapes.h Triangle::Area
+        else { d.is_rect = 0; d.area = 6.28318548f * d.p10[0] * (d.p10[0] - -d.p10[0]); }   // Sphere::Area = phiMax * radius * (zMax - zMin)
         const float *P[4] = {q.p00, q.p10, q.p01, q.p11};
         for (int k = 0; k < 4; k++)
             for (int a = 0; a < 3; a++) { bmin[a] = std::min(bmin[a], P[k][a]); bmax[a] = std::max(bmax[a], P[k][a]); }

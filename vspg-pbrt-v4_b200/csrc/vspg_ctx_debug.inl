@@ -76,6 +76,22 @@ int vspg_debug_light_sample(vspg_ctx *ctx, int n, const float *pos3, const float
     return VSPG_OK;
 }
 
+int vspg_debug_intersect(vspg_ctx *ctx, int n, const float *rays7, int *out_prim, float *out10) {
+    if (!ctx || n < 0 || !rays7 || !out_prim || !out10) return VSPG_ERR_INVALID;
+    CK_STATE(ctx->have_scene, "debug_intersect: set_scene has not been called");
+    if (n == 0) return VSPG_OK;
+    CK(cudaSetDevice(ctx->device));
+    DevBuf dr, dp, dout;
+    CK(dr.alloc((size_t)n * 28)); CK(dp.alloc((size_t)n * 4)); CK(dout.alloc((size_t)n * 40));
+    CK(cudaMemcpy(dr.p, rays7, (size_t)n * 28, cudaMemcpyHostToDevice));
+    int blocks = std::min((n + kBlock - 1) / kBlock, ctx->sm_count * 8);
+    k_debug_intersect<<<blocks, kBlock>>>(ctx->sc, n, dr.as<float>(), dp.as<int>(), dout.as<float>());
+    ctx->launches++;
+    CK(cudaGetLastError());
+    CK(cudaMemcpy(out_prim, dp.p, (size_t)n * 4, cudaMemcpyDeviceToHost)); CK(cudaMemcpy(out10, dout.p, (size_t)n * 40, cudaMemcpyDeviceToHost));
+    return VSPG_OK;
+}
+
 int vspg_debug_sample_distance(vspg_ctx *ctx, int n, const vspg_sd_input *in, vspg_sd_output *out) {
     if (!ctx || n < 0 || !in || !out) return VSPG_ERR_INVALID;
     CK_STATE(ctx->have_scene, "debug_sample_distance: set_scene has not been called");

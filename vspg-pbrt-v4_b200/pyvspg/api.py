@@ -168,6 +168,13 @@ class Context:
                                                _fp(pmf), _fp(pmf_of)))
         return light, pmf, pmf_of
 
+    def debug_intersect(self, rays7):
+        rays7 = np.ascontiguousarray(rays7, dtype=np.float32).reshape(-1, 7)
+        n = rays7.shape[0]
+        prim, out = np.zeros(n, np.int32), np.zeros((n, 10), np.float32)
+        self._ck(lib().vspg_debug_intersect(self._h, n, _fp(rays7), prim.ctypes.data_as(C.POINTER(A.i32)), _fp(out)))
+        return prim, out
+
     def debug_guided_sample(self, is_surface, inputs):
         n = len(inputs)
         out = (A.GsOutput * n)()

@@ -69,6 +69,20 @@ def config1_triangles(res=256, spp=16):
     return Config("C1-cornell-triangles", sc.finalize(), None, ip, spp, "Cornell box, triangle-mesh medium boundary and pyramid, vspguiding=false")
 
 
+def config1_spheres(res=256, spp=16):
+    """C1 with the homogeneous medium bounded by a sphere (interface material) and a diffuse sphere in the room: the
+    same path over Shape "sphere" (Sphere::BasicIntersect with interval arithmetic, shapes.h:147-233)."""
+    cam, eye = perspective_camera([0.5, 0.5, -1.4], [0.5, 0.5, 0.5], [0, 1, 0], 40.0, res, res)
+    sc = Scene(cam, eye)
+    white, red, green = sc.add_material([.73, .73, .73]), sc.add_material([.65, .05, .05]), sc.add_material([.12, .45, .15])
+    _cornell_room(sc, white, red, green)
+    med = sc.add_homogeneous_medium([0.5, 0.5, 0.5], [2.0, 2.0, 2.0], 1.0, 0.0)
+    sc.add_sphere([0.55, 0.5, 0.5], 0.28, material=-1, medium_inside=med, medium_outside=-1, has_interface=True)
+    sc.add_sphere([0.2, 0.15, 0.75], 0.15, material=green)
+    ip = api.integrator_defaults(vsp_guiding=0, surface_guiding=0, volume_guiding=0, light_sampler=A.LIGHTSAMPLER_UNIFORM)
+    return Config("C1-cornell-spheres", sc.finalize(), None, ip, spp, "Cornell box, sphere medium boundary and diffuse sphere, vspguiding=false")
+
+
 def _guiding_for(sc, rng, width, height, vol_leaves, surf_leaves, with_tr=False):
     g = syn.Guiding()
     e = sc.eye.astype(np.float32)
@@ -161,4 +175,4 @@ def config5(width=1920, height=1080, spp=1024, grid_n=256, vol_leaves=8192, surf
                   "mixed scene: emissive quads + diffuse surfaces (BVH) + chromatic heterogeneous medium, full VSPG")
 
 
-BUILDERS = {"C1T": config1_triangles, "C1": config1, "C2": config2, "C3": config3, "C4": config4, "C5": config5}
+BUILDERS = {"C1T": config1_triangles, "C1S": config1_spheres, "C1": config1, "C2": config2, "C3": config3, "C4": config4, "C5": config5}

@@ -110,6 +110,15 @@ def scene_text(cfg, out_dir=None, outfile="out.exr", seed=0, integrator_name="gu
             L.append('  Shape "trianglemesh" "point3 P" [' + "  ".join(_v(p) for p in e["points"]) + '] "integer indices" ['
                      + "  ".join(" ".join(str(i) for i in t) for t in e["indices"]) + "]")
             L.append("AttributeEnd")
+        elif kind == "sphere":
+            L.append("AttributeBegin")
+            if e["has_interface"]:
+                name = lambda i: f"medium{i}" if i >= 0 else ""
+                L.append(f'  MediumInterface "{name(e["medium_inside"])}" "{name(e["medium_outside"])}"')
+            L.append(f'  NamedMaterial "mat{e["material"]}"' if e["material"] >= 0 else '  Material "interface"')
+            L.append(f'  Translate {_v(e["center"])}')
+            L.append(f'  Shape "sphere" "float radius" [{_f(e["radius"])}]')
+            L.append("AttributeEnd")
         elif kind == "point":
             L.append(f'LightSource "point" "rgb I" [{_v(e["I"])}] "point3 from" [{_v(e["pos"])}]')
         elif kind == "distant":

@@ -78,7 +78,7 @@ class Scene:
 
     def __init__(self, camera, eye):
         self.camera, self.eye = camera, np.asarray(eye, dtype=np.float64)
-        self.quads, self.triangles, self.materials, self.lights, self.media = [], [], [], [], []
+        self.quads, self.triangles, self.spheres, self.materials, self.lights, self.media = [], [], [], [], [], []
         self._keep = []
         self.desc = None
         self.log = []   # world-space record of every add_* call, in order (pbrt_writer turns it into a .pbrt file)
@@ -129,6 +129,19 @@ class Scene:
             t.material, t.area_light = material, -1
             t.medium_inside, t.medium_outside, t.has_interface, t.flip_normal = medium_inside, medium_outside, int(has_interface), 0
             self.triangles.append(t)
+
+    def add_sphere(self, center, radius, material=-1, medium_inside=-1, medium_outside=-1, has_interface=False):
+        """Shape "sphere" (full sphere, shapes.h:107) under Translate(center); outward normal."""
+        c = np.asarray(center, dtype=np.float64)
+        self.log.append(("sphere", dict(center=[float(x) for x in c], radius=float(radius), material=material, medium_inside=medium_inside,
+                                        medium_outside=medium_outside, has_interface=bool(has_interface))))
+        sp = A.Sphere()
+        sp.center[:] = [float(np.float32(x)) for x in (c - self.eye)]
+        sp.radius = float(np.float32(radius))
+        sp.material, sp.area_light = material, -1
+        sp.medium_inside, sp.medium_outside, sp.has_interface, sp.flip_normal = medium_inside, medium_outside, int(has_interface), 0
+        self.spheres.append(sp)
+        return len(self.spheres) - 1
 
     def add_triangle_box(self, lo, hi, **kw):
         """Axis-aligned box as 12 outward-facing triangles (n = normalize(cross(p0 - p2, p1 - p2)))."""
@@ -235,12 +248,12 @@ class Scene:
         d.camera = self.camera
         arrs = {}
         for name, items, T in (("media", self.media, A.Medium), ("quads", self.quads, A.Quad), ("triangles", self.triangles, A.Triangle),
+                               ("spheres", self.spheres, A.Sphere),
                                ("materials", self.materials, A.Material), ("lights", self.lights, A.Light)):
             arr = (T * max(1, len(items)))(*items)
             arrs[name] = arr
             setattr(d, "n_" + name, len(items))
             setattr(d, name, arr)
-        d.n_spheres = 0
         self._arrs = arrs
         self.desc = d
         return self
