@@ -49,7 +49,7 @@ VD Ival ival_sqrt(Ival i) { return Ival(fmaxf(0.f, next_down(sqrtf(i.lo))), next
 
 // shapes.h:147-233 for zMin = -r, zMax = r, phiMax = 360: phi <= phiMax always holds (Radians(360) rounds to the
 // same float as 2*Pi), so the clipping re-test never fires and atan2 is not needed.
-VD bool intersect_sphere(V3 ro, V3 rd, float tMax, V3 center, float radius, float *tHit, V3 *pObj) {
+__device__ __noinline__ bool intersect_sphere(V3 ro, V3 rd, float tMax, V3 center, float radius, float *tHit, V3 *pObj) {
     const float g3 = gammaN(3);
     Ival ox = ival_from_error(ro.x + -center.x, g3 * (fabsf(ro.x) + fabsf(center.x)));
     Ival oy = ival_from_error(ro.y + -center.y, g3 * (fabsf(ro.y) + fabsf(center.y)));
@@ -84,7 +84,7 @@ VD bool intersect_sphere(V3 ro, V3 rd, float tMax, V3 center, float radius, floa
 
 // shapes.h:241-292 + transform.cpp:229-261 (+ SurfaceInteraction ctor, interaction.h): render-space point (midpoint
 // and half-width of the transformed Point3fi), geometric normal, dpdu.
-VD void sphere_interaction(V3 pHit, V3 center, float radius, bool flipNormal, V3 *p, V3 *pError, V3 *n, V3 *dpduOut) {
+__device__ __noinline__ void sphere_interaction(V3 pHit, V3 center, float radius, bool flipNormal, V3 *p, V3 *pError, V3 *n, V3 *dpduOut) {
     const float phiMax = 6.28318548f;      // Radians(360)
     const float dTheta = 0.f - 3.14159274f;   // thetaZMax - thetaZMin = acos(1) - acos(-1)
     float cosTheta = pHit.z / radius;
