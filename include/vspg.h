@@ -368,6 +368,13 @@ int vspg_debug_light_sample(vspg_ctx *ctx, int n, const float *pos3, const float
  * quads, then triangles, then spheres (-1 = miss); out10[i] = tHit, p(), pi.Error(), n. */
 int vspg_debug_intersect(vspg_ctx *ctx, int n, const float *rays7, int *out_prim, float *out10);
 
+/* Light::SampleLi(ctx, u) (lights.cpp:796-818 -> Shape::Sample(ctx, u), shapes.cpp:1254-1327) followed by
+ * Light::PDF_Li(ctx, wi) (lights.cpp:820-824 -> Shape::PDF(ctx, wi), shapes.cpp:1329-1368) along the sampled
+ * direction.  ctx9[i] = p(), n, ns of the reference point (n = ns = 0 in a medium); light[i] indexes the lights;
+ * u2[i] the 2-D sample.  out12[i] = valid, pdf, wi (3), pLight (3), L (3), PDF_Li(ctx, wi) evaluated at the scene
+ * intersection of the ray (ctx, wi) when that hit is the light's own shape, else -1. */
+int vspg_debug_sample_li(vspg_ctx *ctx, int n, const float *ctx9, const int *light, const float *u2, float *out12);
+
 /* GuidedPhaseFunction / GuidedBSDF (cpu/guiding.h:57-638) on explicit inputs. */
 typedef struct vspg_gs_input {
     float p[3];

@@ -137,6 +137,17 @@ def intersect(scene, ip, rays7):
     return prim, out
 
 
+def sample_li(scene, ip, ctx9, light, u2):
+    ctx9 = np.ascontiguousarray(ctx9, dtype=np.float32).reshape(-1, 9)
+    light = np.ascontiguousarray(light, dtype=np.int32)
+    u2 = np.ascontiguousarray(u2, dtype=np.float32).reshape(-1, 2)
+    n = ctx9.shape[0]
+    out = np.zeros((n, 12), np.float32)
+    rc = lib().orc_sample_li(C.byref(scene.desc), C.byref(ip), n, _fp(ctx9), light.ctypes.data_as(PI), _fp(u2), _fp(out))
+    assert rc == 0, rc
+    return out
+
+
 def guided_sample(scene, guiding, ip, is_surface, inputs):
     n = len(inputs)
     out = (A.GsOutput * n)()

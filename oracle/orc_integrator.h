@@ -12,6 +12,7 @@
 #include "orc_media.h"
 #include "orc_lightbvh.h"
 #include "orc_sphere.h"
+#include "orc_shapesample.h"
 
 namespace orc {
 
@@ -679,6 +680,33 @@ struct Integrator {
         const vspg_quad &q = sc->d->quads[l.shape_index];
         V3 p00(q.p00), p10(q.p10), p01(q.p01), p11(q.p11);
         float pdf = 1; float uv[2];
+        // shapes.cpp:1254-1327 BilinearPatch::Sample(ctx, u): rectangles that subtend enough solid angle are sampled
+        // as spherical rectangles (with the cos-theta bilinear warp at surface reference points)
+        V3 v00 = Normalize(p00 - ctx.p), v10 = Normalize(p10 - ctx.p), v01 = Normalize(p01 - ctx.p), v11 = Normalize(p11 - ctx.p);
+        if (Scene::IsRectangle(p00, p10, p01, p11) && !(SphericalQuadArea(v00, v10, v11, v01) <= MinSphericalSampleAreaQuad)) {
+            float us[2] = {u[0], u[1]};
+            if (!(ctx.ns.x == 0 && ctx.ns.y == 0 && ctx.ns.z == 0)) {
+                float w[4] = {std::max<float>(0.01, AbsDot(v00, ctx.ns)), std::max<float>(0.01, AbsDot(v10, ctx.ns)),
+                              std::max<float>(0.01, AbsDot(v01, ctx.ns)), std::max<float>(0.01, AbsDot(v11, ctx.ns))};
+                float uw[2];
+                SampleBilinear(us, w, uw);
+                us[0] = uw[0]; us[1] = uw[1];
+                pdf *= BilinearPDF(us, w);
+            }
+            V3 eu = p10 - p00, ev = p01 - p00;
+            float quadPDF;
+            V3 p = SampleSphericalRectangle(ctx.p, p00, eu, ev, us, &quadPDF);
+            pdf *= quadPDF;
+            V3 n = Normalize(Cross(eu, ev));
+            if (q.flip_normal) n = -n;
+            // DiffuseAreaLight::SampleLi (lights.cpp:796-818): Interaction(p, n, time, st) has no error bounds
+            if (pdf == 0 || LengthSquared(p - ctx.p) == 0) return ls;
+            V3 wi = Normalize(p - ctx.p);
+            S3 Le = sc->AreaL(light, n, -wi);
+            if (!Le) return ls;
+            ls.valid = true; ls.L = Le; ls.wi = wi; ls.pdf = pdf; ls.pLight = p; ls.pLightErr = V3(); ls.nLight = n;
+            return ls;
+        }
         if (!Scene::IsRectangle(p00, p10, p01, p11)) {
             float w[4] = {Length(Cross(p10 - p00, p01 - p00)), Length(Cross(p10 - p00, p11 - p10)),
                           Length(Cross(p01 - p00, p11 - p01)), Length(Cross(p11 - p10, p11 - p01))};
@@ -711,6 +739,19 @@ struct Integrator {
         const vspg_quad &q = sc->d->quads[l.shape_index];
         V3 p00(q.p00), p10(q.p10), p01(q.p01), p11(q.p11);
         float pdf = 1;
+        V3 v00 = Normalize(p00 - ctx.p), v10 = Normalize(p10 - ctx.p), v01 = Normalize(p01 - ctx.p), v11 = Normalize(p11 - ctx.p);
+        if (Scene::IsRectangle(p00, p10, p01, p11) && !(SphericalQuadArea(v00, v10, v11, v01) <= MinSphericalSampleAreaQuad)) {
+            // shapes.cpp:1352-1368 PDF for a sample in the spherical rectangle
+            float sp = 1 / SphericalQuadArea(v00, v10, v11, v01);
+            if (!(ctx.ns.x == 0 && ctx.ns.y == 0 && ctx.ns.z == 0)) {
+                float w[4] = {std::max<float>(0.01, AbsDot(v00, ctx.ns)), std::max<float>(0.01, AbsDot(v10, ctx.ns)),
+                              std::max<float>(0.01, AbsDot(v01, ctx.ns)), std::max<float>(0.01, AbsDot(v11, ctx.ns))};
+                float uu[2];
+                InvertSphericalRectangleSample(ctx.p, p00, p10 - p00, p01 - p00, hit.p, uu);
+                return BilinearPDF(uu, w) * sp;
+            }
+            return sp;
+        }
         if (!Scene::IsRectangle(p00, p10, p01, p11)) {
             float w[4] = {Length(Cross(p10 - p00, p01 - p00)), Length(Cross(p10 - p00, p11 - p10)),
                           Length(Cross(p01 - p00, p11 - p01)), Length(Cross(p11 - p10, p11 - p01))};

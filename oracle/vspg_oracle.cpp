@@ -127,6 +127,29 @@ int orc_intersect(const vspg_scene_desc *d, const vspg_integrator_params *ip, in
     return 0;
 }
 
+int orc_sample_li(const vspg_scene_desc *d, const vspg_integrator_params *ip, int n, const float *ctx9, const int *light, const float *u2, float *out12) {
+    Scene sc; sc.init(d, nullptr, ip, true);
+    Integrator in; in.sc = &sc;
+    for (int i = 0; i < n; i++) {
+        const float *c = ctx9 + 9 * i;
+        LightSampleCtx ctx; ctx.p = V3(c); ctx.n = V3(c + 3); ctx.ns = V3(c + 6);
+        Integrator::LiSample ls = in.SampleLi(light[i], ctx, u2 + 2 * i);
+        float *o = out12 + 12 * i;
+        for (int k = 0; k < 12; k++) o[k] = 0;
+        o[11] = -1;
+        if (!ls.valid) continue;
+        o[0] = 1; o[1] = ls.pdf;
+        for (int k = 0; k < 3; k++) { o[2 + k] = ls.wi[k]; o[5 + k] = ls.pLight[k]; o[8 + k] = ls.L[k]; }
+        if (d->lights[light[i]].type != VSPG_LIGHT_DIFFUSE_AREA) continue;
+        V3 ro = OffsetRayOrigin(ctx.p, V3(), ctx.n, ls.wi);
+        Hit h = sc.Intersect(ro, ls.wi, Infinity);
+        if (!h.valid) continue;
+        SurfaceIntr s = sc.MakeIntr(h, ls.wi, -1);
+        if (s.areaLight == light[i]) o[11] = in.AreaPDF_Li(light[i], ctx, ls.wi, s);
+    }
+    return 0;
+}
+
 // ------------------------------------------------------------- guiding
 int orc_cache_lookup(const vspg_field *f, int n, const float *pos3, const float *u, int *out_leaf, int *out_region, float *out_u) {
     for (int i = 0; i < n; i++) {

@@ -64,6 +64,27 @@ __global__ void k_debug_intersect(const DScene sc, int n, const float *rays7, in
     }
 }
 
+__global__ void k_debug_sample_li(const DScene sc, int n, const float *ctx9, const int *light, const float *u2, float *out12) {
+    for (int i = gtid(); i < n; i += gstride()) {
+        const float *c = ctx9 + 9 * i;
+        V3 p(c[0], c[1], c[2]), nn(c[3], c[4], c[5]), ns(c[6], c[7], c[8]);
+        LiSample ls = sample_li(sc, light[i], p, ns, u2[2 * i], u2[2 * i + 1]);
+        float *o = out12 + 12 * i;
+        for (int k = 0; k < 12; k++) o[k] = 0;
+        o[11] = -1;
+        if (!ls.valid) continue;
+        o[0] = 1; o[1] = ls.pdf; o[2] = ls.wi.x; o[3] = ls.wi.y; o[4] = ls.wi.z; o[5] = ls.pLight.x; o[6] = ls.pLight.y; o[7] = ls.pLight.z;
+        o[8] = ls.L.x; o[9] = ls.L.y; o[10] = ls.L.z;
+        if (sc.lights[light[i]].type != VSPG_LIGHT_DIFFUSE_AREA) continue;
+        V3 ro = offset_ray_origin(p, V3(), nn, ls.wi);   // ctx.SpawnRay(wi): pi is exact
+        unsigned nodes = 0;
+        Hit h = scene_intersect(sc, ro, ls.wi, inff(), nodes);
+        if (h.prim < 0) continue;
+        SurfaceIntr s = make_intr(sc, h, ro, ls.wi, -1);
+        if (s.areaLight == light[i]) o[11] = area_pdf_li(sc, light[i], p, ns, ls.wi, s);
+    }
+}
+
 __global__ void k_debug_density(const DScene sc, int medium, int n, const float *pos3, float *out7) {
     for (int i = gtid(); i < n; i += gstride()) {
         MediumProps mp = sample_point(sc.media[medium], V3(pos3[3 * i], pos3[3 * i + 1], pos3[3 * i + 2]));

@@ -4,6 +4,7 @@
 // spread over the group's lanes, see dguiding.cuh); G = 0 without a field -- one THREAD per vertex and every
 // mixture op compiled out.
 #pragma once
+#include "dshapesample.cuh"
 #include "dguiding.cuh"
 #include "dpath.cuh"
 
@@ -128,7 +129,7 @@ VD float light_pmf(const DScene &sc, int light, V3 p, V3 n) {
 
 // lights.cpp:796-818 DiffuseAreaLight::SampleLi -> shapes.cpp:1155-1214, 1254-1280 (area-sampling branch);
 // lights.h:243-250 (point), 316-323 (distant); uniform infinite: allowIncompletePDF (lights.cpp:1022-1023)
-VD LiSample sample_li(const DScene &sc, int light, V3 ctxP, float u0, float u1) {
+VD LiSample sample_li(const DScene &sc, int light, V3 ctxP, V3 ctxNs, float u0, float u1) {
     LiSample ls; ls.valid = false; ls.delta = false; ls.pdf = 0;
     const DLight &l = sc.lights[light];
     if (l.type == VSPG_LIGHT_POINT) {
@@ -148,6 +149,32 @@ VD LiSample sample_li(const DScene &sc, int light, V3 ctxP, float u0, float u1) 
     const DQuad &q = sc.quads[l.shape_index];
     V3 p00 = ld3(q.p00), p10 = ld3(q.p10), p01 = ld3(q.p01), p11 = ld3(q.p11);
     float pdf = 1, uvx, uvy;
+    if (q.is_rect) {
+        // shapes.cpp:1254-1327: rectangles that subtend enough solid angle are sampled as spherical rectangles, with the
+        // cos-theta bilinear warp at surface reference points
+        V3 v00 = normalize(p00 - ctxP), v10 = normalize(p10 - ctxP), v01 = normalize(p01 - ctxP), v11 = normalize(p11 - ctxP);
+        if (!(spherical_quad_area(v00, v10, v11, v01) <= kMinSphericalSampleAreaQuad)) {
+            if (!(ctxNs.x == 0 && ctxNs.y == 0 && ctxNs.z == 0)) {
+                float w[4] = {fmaxf(0.01f, absdot(v00, ctxNs)), fmaxf(0.01f, absdot(v10, ctxNs)), fmaxf(0.01f, absdot(v01, ctxNs)), fmaxf(0.01f, absdot(v11, ctxNs))};
+                float w0, w1;
+                sample_bilinear(u0, u1, w, &w0, &w1);
+                u0 = w0; u1 = w1;
+                pdf *= bilinear_pdf(u0, u1, w);
+            }
+            V3 eu = p10 - p00, ev = p01 - p00;
+            float quadPDF;
+            V3 p = sample_spherical_rectangle(ctxP, p00, eu, ev, u0, u1, &quadPDF);
+            pdf *= quadPDF;
+            V3 n = normalize(cross(eu, ev));
+            if (q.flip_normal) n = -n;
+            if (pdf == 0 || dist_sq(p, ctxP) == 0) return ls;   // lights.cpp:803
+            V3 wi = normalize(p - ctxP);
+            V3 Le = area_L(l, n, -wi);
+            if (!nonzero(Le)) return ls;
+            ls.valid = true; ls.L = Le; ls.wi = wi; ls.pdf = pdf; ls.pLight = p; ls.pLightErr = V3(); ls.nLight = n;
+            return ls;
+        }
+    }
     if (!q.is_rect) {
         float w[4] = {length(cross(p10 - p00, p01 - p00)), length(cross(p10 - p00, p11 - p10)),
                       length(cross(p01 - p00, p11 - p01)), length(cross(p11 - p10, p11 - p01))};
@@ -175,10 +202,24 @@ VD LiSample sample_li(const DScene &sc, int light, V3 ctxP, float u0, float u1) 
     return ls;
 }
 // lights.cpp:820-824 -> shapes.cpp:1329-1347 (area-sampling branch) evaluated at the actual hit
-VD float area_pdf_li(const DScene &sc, int light, V3 ctxP, V3 wi, const SurfaceIntr &hit) {
+VD float area_pdf_li(const DScene &sc, int light, V3 ctxP, V3 ctxNs, V3 wi, const SurfaceIntr &hit) {
     const DQuad &q = sc.quads[sc.lights[light].shape_index];
     V3 p00 = ld3(q.p00), p10 = ld3(q.p10), p01 = ld3(q.p01), p11 = ld3(q.p11);
     float pdf = 1;
+    if (q.is_rect) {   // shapes.cpp:1352-1368 PDF for a sample in the spherical rectangle
+        V3 v00 = normalize(p00 - ctxP), v10 = normalize(p10 - ctxP), v01 = normalize(p01 - ctxP), v11 = normalize(p11 - ctxP);
+        float area = spherical_quad_area(v00, v10, v11, v01);
+        if (!(area <= kMinSphericalSampleAreaQuad)) {
+            float sp = 1 / area;
+            if (!(ctxNs.x == 0 && ctxNs.y == 0 && ctxNs.z == 0)) {
+                float w[4] = {fmaxf(0.01f, absdot(v00, ctxNs)), fmaxf(0.01f, absdot(v10, ctxNs)), fmaxf(0.01f, absdot(v01, ctxNs)), fmaxf(0.01f, absdot(v11, ctxNs))};
+                float uu0, uu1;
+                invert_spherical_rectangle_sample(ctxP, p00, p10 - p00, p01 - p00, hit.p, &uu0, &uu1);
+                return bilinear_pdf(uu0, uu1, w) * sp;
+            }
+            return sp;
+        }
+    }
     if (!q.is_rect) {
         float w[4] = {length(cross(p10 - p00, p01 - p00)), length(cross(p10 - p00, p11 - p10)),
                       length(cross(p01 - p00, p11 - p01)), length(cross(p11 - p10, p11 - p01))};

@@ -108,6 +108,46 @@ VD void shadow_store(const PathSoA &P, int s, const ShadowRec &r) {
     P.sh_ple[s] = make_float4(r.pLightErr.x, r.pLightErr.y, r.pLightErr.z, r.nLight.y);
     P.sh_nz[s] = r.nLight.z;
 }
+
+// Next-event light sample drawn ahead of the lane-group scatter kernels.  The light pick and Light::SampleLi are
+// scalar work (one result per vertex), so for guided configurations k_lookup -- one THREAD per vertex -- computes
+// them from a copy of the vertex's sampler stream and parks the result in the slot's (still unused) shadow-record
+// streams; the G-lane kernels then only skip the three sampler dimensions and read the record back.  Same
+// arithmetic, same stream positions: bit-identical to sampling inside the scatter kernel.
+struct NeePre { bool valid, delta; V3 L, wi, pLight, pLightErr, nLight; float p_l; };
+VD NeePre nee_presample(const DScene &sc, Rng rng, V3 ctxP, V3 ctxNs) {
+    NeePre np; np.valid = false; np.delta = false; np.p_l = 0;
+    float u = rng.uniform();
+    float pmf = 0;
+    int light = sample_light(sc, u, &pmf, ctxP, ctxNs);
+    float ul0 = rng.uniform(), ul1 = rng.uniform();
+    if (light < 0) return np;
+    LiSample ls = sample_li(sc, light, ctxP, ctxNs, ul0, ul1);
+    if (!(ls.valid && nonzero(ls.L) && ls.pdf != 0)) return np;
+    np.valid = true; np.delta = ls.delta; np.L = ls.L; np.wi = ls.wi; np.pLight = ls.pLight; np.pLightErr = ls.pLightErr; np.nLight = ls.nLight;
+    np.p_l = pmf * ls.pdf;
+    return np;
+}
+VD void nee_store(const PathSoA &P, int s, const NeePre &n) {
+    P.sh_rl[s] = make_float4(n.wi.x, n.wi.y, n.wi.z, __int_as_float((n.valid ? 1 : 0) | (n.delta ? 2 : 0)));
+    if (!n.valid) return;
+    P.sh_c[s] = make_float4(n.L.x, n.L.y, n.L.z, n.p_l);
+    P.sh_pl[s] = make_float4(n.pLight.x, n.pLight.y, n.pLight.z, n.nLight.x);
+    P.sh_ple[s] = make_float4(n.pLightErr.x, n.pLightErr.y, n.pLightErr.z, n.nLight.y);
+    P.sh_nz[s] = n.nLight.z;
+}
+VD NeePre nee_load(const PathSoA &P, int s) {
+    NeePre n;
+    float4 a = P.sh_rl[s];
+    int fl = __float_as_int(a.w);
+    n.valid = fl & 1; n.delta = (fl >> 1) & 1; n.wi = V3(a.x, a.y, a.z); n.p_l = 0;
+    if (n.valid) {
+        float4 c = P.sh_c[s], pl = P.sh_pl[s], pe = P.sh_ple[s];
+        n.L = V3(c.x, c.y, c.z); n.p_l = c.w;
+        n.pLight = V3(pl.x, pl.y, pl.z); n.pLightErr = V3(pe.x, pe.y, pe.z); n.nLight = V3(pl.w, pe.w, P.sh_nz[s]);
+    }
+    return n;
+}
 VD void shadow_load(const PathSoA &P, int s, ShadowRec &r) {
     float4 a = P.sh_o[s], b = P.sh_d[s], c = P.sh_c[s], d = P.sh_rl[s], e = P.sh_ru[s], f = P.sh_pl[s], g = P.sh_ple[s];
     r.o = V3(a.x, a.y, a.z); r.d = V3(a.w, b.x, b.y); r.medium = __float_as_int(b.z);
@@ -176,6 +216,17 @@ __global__ void __launch_bounds__(kBlock) k_lookup(const DScene sc, const Wavefr
             if (r >= 0) { if (__ldg(&f.regions[r].valid)) nl = __ldg(&f.regions[r].num_components); else r = -1; }
         }
         W.P.lk[slot] = r;
+        if (sc.ip.use_nee) {
+            if (SURFACE) {
+                if (want) {   // GuidedBSDF::non_specular(): reflective-only BSDF, ctx.pi = intr.OffsetRayOrigin(intr.wo) (vspg.cpp:1147-1149)
+                    float4 a = W.P.o_dx[slot], b = W.P.d_med[slot], hr = W.P.hit[slot];
+                    Hit h; h.t = hr.x; h.u = hr.y; h.v = hr.z; h.prim = __float_as_int(hr.w);
+                    V3 ro(a.x, a.y, a.z), rd(a.w, b.x, b.y);
+                    SurfaceIntr isect = make_intr(sc, h, ro, rd, __float_as_int(b.z));
+                    nee_store(W.P, slot, nee_presample(sc, rng, offset_ray_origin(isect.p, isect.pError, isect.n, isect.wo), isect.ns));
+                }
+            } else nee_store(W.P, slot, nee_presample(sc, rng, p, V3()));
+        }
         queue_push(q8, nl <= 8, slot);
         queue_push(q16, nl > 8 && nl <= 16, slot);
         queue_push(q32, nl > 16, slot);
@@ -213,14 +264,15 @@ __global__ void __launch_bounds__(G > 0 ? kScatterBlock : kBlock) k_volscatter(c
         bool emitShadow = false;
         if (ip.use_nee) {
             V3 wo = -ps.ray.d;
-            float u = ps.rng.uniform();
-            float pmf = 0;
-            int light = sample_light(sc, u, &pmf, p, V3());
-            float ul0 = ps.rng.uniform(), ul1 = ps.rng.uniform();
-            if (light >= 0) {
-                LiSample ls = sample_li(sc, light, p, ul0, ul1);
-                if (ls.valid && nonzero(ls.L) && ls.pdf != 0) {
-                    float p_l = pmf * ls.pdf;
+            NeePre ls;
+            if (G > 0) {   // drawn by k_lookup from these three sampler dimensions
+                ps.rng.uniform(); ps.rng.uniform(); ps.rng.uniform();
+                ls = nee_load(W.P, slot);
+                __syncwarp();   // every lane of the group has read the parked record before the leader overwrites it
+            } else ls = nee_presample(sc, ps.rng, p, V3()), ps.rng.uniform(), ps.rng.uniform(), ps.rng.uniform();
+            {
+                if (ls.valid) {
+                    float p_l = ls.p_l;
                     float ph = gphase.p(wo, ls.wi);
                     float scatterPDF = 1.0f * gphase.pdf(wo, ls.wi);
                     if (ph != 0) {

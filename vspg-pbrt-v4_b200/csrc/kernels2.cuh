@@ -6,7 +6,7 @@
 namespace vspg {
 
 // ------------------------------------------------------------------ escape / emission / interface (vspg.cpp:353-446)
-__global__ void __launch_bounds__(kBlock) k_surface(const DScene sc, const Wavefront W) {
+__global__ void __launch_bounds__(kBlock, 5) k_surface(const DScene sc, const Wavefront W) {
     const int n = *W.surface.count;
     const vspg_integrator_params &ip = sc.ip;
     for (int i = gtid(); i < n; i += gstride()) {
@@ -36,7 +36,7 @@ __global__ void __launch_bounds__(kBlock) k_surface(const DScene sc, const Wavef
                 if (nonzero(Le)) {
                     if (ps.fl.depth == 0 || ps.fl.specular) ps.L = ps.L + ps.beta * Le / avg3(ps.r_u);
                     else {
-                        float lightPDF = light_pmf(sc, isect.areaLight, ps.prevP, ps.prevNs) * area_pdf_li(sc, isect.areaLight, ps.prevP, ps.ray.d, isect);
+                        float lightPDF = light_pmf(sc, isect.areaLight, ps.prevP, ps.prevNs) * area_pdf_li(sc, isect.areaLight, ps.prevP, ps.prevNs, ps.ray.d, isect);
                         ps.r_l = ps.r_l * lightPDF;
                         float w_l = ip.use_nee ? 1.0f / avg3(ps.r_u + ps.r_l) : 1.0f;
                         ps.L = ps.L + ps.beta * w_l * Le;
@@ -86,14 +86,15 @@ __global__ void __launch_bounds__(G > 0 ? kScatterBlock : kBlock) k_shade(const 
         if (ip.use_nee && gbsdf.non_specular()) {
             V3 ctxP = offset_ray_origin(isect.p, isect.pError, isect.n, isect.wo);  // reflective-only BSDF (vspg.cpp:1147-1149)
             V3 wo = isect.wo;
-            float u = ps.rng.uniform();
-            float pmf = 0;
-            int light = sample_light(sc, u, &pmf, ctxP, isect.ns);
-            float ul0 = ps.rng.uniform(), ul1 = ps.rng.uniform();
-            if (light >= 0) {
-                LiSample ls = sample_li(sc, light, ctxP, ul0, ul1);
-                if (ls.valid && nonzero(ls.L) && ls.pdf != 0) {
-                    float p_l = pmf * ls.pdf;
+            NeePre ls;
+            if (G > 0) {   // drawn by k_lookup from these three sampler dimensions
+                ps.rng.uniform(); ps.rng.uniform(); ps.rng.uniform();
+                ls = nee_load(W.P, slot);
+                __syncwarp();
+            } else ls = nee_presample(sc, ps.rng, ctxP, isect.ns), ps.rng.uniform(), ps.rng.uniform(), ps.rng.uniform();
+            {
+                if (ls.valid) {
+                    float p_l = ls.p_l;
                     V3 f_hat = gbsdf.f(wo, ls.wi) * absdot(ls.wi, isect.ns);
                     float scatterPDF = 1.0f * gbsdf.pdf(wo, ls.wi);
                     if (nonzero(f_hat)) {

@@ -92,6 +92,25 @@ int vspg_debug_intersect(vspg_ctx *ctx, int n, const float *rays7, int *out_prim
     return VSPG_OK;
 }
 
+int vspg_debug_sample_li(vspg_ctx *ctx, int n, const float *ctx9, const int *light, const float *u2, float *out12) {
+    if (!ctx || n < 0 || !ctx9 || !light || !u2 || !out12) return VSPG_ERR_INVALID;
+    CK_STATE(ctx->have_scene, "debug_sample_li: set_scene has not been called");
+    for (int i = 0; i < n; i++)
+        if (light[i] < 0 || light[i] >= ctx->sc.n_lights) return fail(ctx, VSPG_ERR_INVALID, "debug_sample_li: item %d: light out of range", i);
+    if (n == 0) return VSPG_OK;
+    CK(cudaSetDevice(ctx->device));
+    DevBuf dc, dl, du, dout;
+    CK(dc.alloc((size_t)n * 36)); CK(dl.alloc((size_t)n * 4)); CK(du.alloc((size_t)n * 8)); CK(dout.alloc((size_t)n * 48));
+    CK(cudaMemcpy(dc.p, ctx9, (size_t)n * 36, cudaMemcpyHostToDevice)); CK(cudaMemcpy(dl.p, light, (size_t)n * 4, cudaMemcpyHostToDevice));
+    CK(cudaMemcpy(du.p, u2, (size_t)n * 8, cudaMemcpyHostToDevice));
+    int blocks = std::min((n + kBlock - 1) / kBlock, ctx->sm_count * 8);
+    k_debug_sample_li<<<blocks, kBlock>>>(ctx->sc, n, dc.as<float>(), dl.as<int>(), du.as<float>(), dout.as<float>());
+    ctx->launches++;
+    CK(cudaGetLastError());
+    CK(cudaMemcpy(out12, dout.p, (size_t)n * 48, cudaMemcpyDeviceToHost));
+    return VSPG_OK;
+}
+
 int vspg_debug_sample_distance(vspg_ctx *ctx, int n, const vspg_sd_input *in, vspg_sd_output *out) {
     if (!ctx || n < 0 || !in || !out) return VSPG_ERR_INVALID;
     CK_STATE(ctx->have_scene, "debug_sample_distance: set_scene has not been called");

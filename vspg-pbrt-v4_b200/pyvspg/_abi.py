@@ -186,6 +186,7 @@ SYMBOLS = {
     "vspg_debug_sample_distance": (i32, [P, i32, C.POINTER(SdInput), C.POINTER(SdOutput)]),
     "vspg_debug_cache_lookup": (i32, [P, i32, i32, PF, PF, C.POINTER(i32), C.POINTER(i32), PF]),
     "vspg_debug_intersect": (i32, [P, i32, PF, C.POINTER(i32), PF]),
+    "vspg_debug_sample_li": (i32, [P, i32, PF, C.POINTER(i32), PF, PF]),
     "vspg_debug_light_sample": (i32, [P, i32, PF, PF, PF, C.POINTER(i32), C.POINTER(i32), PF, PF]),
     "vspg_debug_guided_sample": (i32, [P, i32, i32, C.POINTER(GsInput), C.POINTER(GsOutput)]),
 }

@@ -175,6 +175,15 @@ class Context:
         self._ck(lib().vspg_debug_intersect(self._h, n, _fp(rays7), prim.ctypes.data_as(C.POINTER(A.i32)), _fp(out)))
         return prim, out
 
+    def debug_sample_li(self, ctx9, light, u2):
+        ctx9 = np.ascontiguousarray(ctx9, dtype=np.float32).reshape(-1, 9)
+        light = np.ascontiguousarray(light, dtype=np.int32)
+        u2 = np.ascontiguousarray(u2, dtype=np.float32).reshape(-1, 2)
+        n = ctx9.shape[0]
+        out = np.zeros((n, 12), np.float32)
+        self._ck(lib().vspg_debug_sample_li(self._h, n, _fp(ctx9), light.ctypes.data_as(C.POINTER(A.i32)), _fp(u2), _fp(out)))
+        return out
+
     def debug_guided_sample(self, is_surface, inputs):
         n = len(inputs)
         out = (A.GsOutput * n)()
