@@ -223,7 +223,7 @@ struct Scene {
     const vspg_guiding_desc *g = nullptr;
     vspg_integrator_params ip;
     std::vector<Medium> media;
-    std::vector<float> quadArea;
+    std::vector<float> quadArea, triArea, sphereArea;
     std::vector<float> lightCdf;  // power sampler pmf
     BVHLightSampler lightBvh;     // "bvh" sampler (the reference's default)
     GaussianFilterSampler gaussFilter;   // PixelFilter "gaussian" (pbrt's default filter)
@@ -244,8 +244,11 @@ struct Scene {
             for (V3 p : {p00, p10, p01, p11})
                 for (int a = 0; a < 3; a++) { bmin[a] = std::min(bmin[a], p[a]); bmax[a] = std::max(bmax[a], p[a]); }
         }
+        triArea.resize(d->n_triangles); sphereArea.resize(d->n_spheres);
+        for (int i = 0; i < d->n_spheres; i++) sphereArea[i] = 6.28318548f * d->spheres[i].radius * (d->spheres[i].radius - -d->spheres[i].radius);  // shapes.h:295
         for (int i = 0; i < d->n_triangles; i++) {
             const vspg_triangle &t = d->triangles[i];
+            triArea[i] = 0.5f * Length(Cross(V3(t.p1) - V3(t.p0), V3(t.p2) - V3(t.p0)));   // shapes.h:853-860
             for (V3 p : {V3(t.p0), V3(t.p1), V3(t.p2)})
                 for (int a = 0; a < 3; a++) { bmin[a] = std::min(bmin[a], p[a]); bmax[a] = std::max(bmax[a], p[a]); }
         }
@@ -262,7 +265,7 @@ struct Scene {
         for (int i = 0; i < d->n_lights; i++) { lightCdf[i] = LightPower(i); sum += lightCdf[i]; }
         if (sum == 0) for (auto &v : lightCdf) v = 1.f, sum += 1.f;
         for (auto &v : lightCdf) v /= sum;
-        lightBvh.Build(d->lights, d->n_lights, d->quads, quadArea);
+        lightBvh.Build(d->lights, d->n_lights, d->quads, quadArea, d->triangles, &triArea, d->spheres, &sphereArea);
         if (d->camera.filter_type == 1) gaussFilter.init(d->camera.filter_radius[0], d->camera.filter_radius[1], d->camera.filter_sigma);
     }
     static bool IsRectangle(V3 p00, V3 p10, V3 p01, V3 p11) {  // shapes.h BilinearPatch::IsRectangle
@@ -291,11 +294,12 @@ struct Scene {
             for (int j = 0; j < na; ++j) area += 0.5f * Length(Cross(p[i + 1][j + 1] - p[i][j], p[i + 1][j] - p[i][j + 1]));
         return area;
     }
+    float ShapeArea(const vspg_light &l) const { return l.shape_kind == 2 ? sphereArea[l.shape_index] : l.shape_kind == 1 ? triArea[l.shape_index] : quadArea[l.shape_index]; }
     float LightPower(int i) const {  // lights.cpp Phi() for each type, averaged over RGB
         const vspg_light &l = d->lights[i];
         S3 L(l.L);
         switch (l.type) {
-        case VSPG_LIGHT_DIFFUSE_AREA: return (L * (Pi * (l.two_sided ? 2.f : 1.f) * quadArea[l.shape_index])).Average();
+        case VSPG_LIGHT_DIFFUSE_AREA: return (L * (Pi * (l.two_sided ? 2.f : 1.f) * ShapeArea(l))).Average();
         case VSPG_LIGHT_POINT: return (L * (4 * Pi)).Average();
         case VSPG_LIGHT_DISTANT: return (L * (Pi * Sqr(sceneRadius))).Average();
         default: return (L * (4 * Pi * Pi * Sqr(sceneRadius))).Average();
@@ -658,6 +662,89 @@ struct Integrator {
         if (sc->ip.light_sampler == VSPG_LIGHTSAMPLER_UNIFORM) return 1.f / n;
         return sc->lightCdf[light];
     }
+    // shapes.h:1053-1125 Triangle::Sample(ctx, u) (and :1014-1048 Sample(u) for the area-sampling fallback)
+    static bool SampleTriangle(const vspg_triangle &q, float area, const LightSampleCtx &ctx, const float *u, V3 *pOut, V3 *pErr, V3 *nOut, float *pdfOut) {
+        V3 p0(q.p0), p1(q.p1), p2(q.p2);
+        V3 n = Normalize(Cross(p1 - p0, p2 - p0));
+        if (q.flip_normal) n = -n;
+        float solidAngle = SphericalTriangleArea(Normalize(p0 - ctx.p), Normalize(p1 - ctx.p), Normalize(p2 - ctx.p));
+        float b[3];
+        if (solidAngle < MinSphericalSampleAreaTri || solidAngle > MaxSphericalSampleAreaTri) {
+            SampleUniformTriangle(u, b);
+            V3 p = b[0] * p0 + b[1] * p1 + b[2] * p2;
+            *pErr = gamma_(6) * (Abs(b[0] * p0) + Abs(b[1] * p1) + Abs((1 - b[0] - b[1]) * p2));
+            V3 wi = p - ctx.p;
+            if (LengthSquared(wi) == 0) return false;
+            wi = Normalize(wi);
+            float pdf = (1 / area) / (AbsDot(n, -wi) / DistanceSquared(ctx.p, p));
+            if (std::isinf(pdf)) return false;
+            *pOut = p; *nOut = n; *pdfOut = pdf;
+            return true;
+        }
+        float pdf = 1, us[2] = {u[0], u[1]};
+        if (!(ctx.ns.x == 0 && ctx.ns.y == 0 && ctx.ns.z == 0)) {
+            V3 wi[3] = {Normalize(p0 - ctx.p), Normalize(p1 - ctx.p), Normalize(p2 - ctx.p)};
+            float w[4] = {std::max<float>(0.01, AbsDot(ctx.ns, wi[1])), std::max<float>(0.01, AbsDot(ctx.ns, wi[1])),
+                          std::max<float>(0.01, AbsDot(ctx.ns, wi[0])), std::max<float>(0.01, AbsDot(ctx.ns, wi[2]))};
+            float uw[2];
+            SampleBilinear(us, w, uw);
+            us[0] = uw[0]; us[1] = uw[1];
+            pdf = BilinearPDF(us, w);
+        }
+        float triPDF;
+        V3 v[3] = {p0, p1, p2};
+        if (!SampleSphericalTriangle(v, ctx.p, us, b, &triPDF)) { b[0] = b[1] = b[2] = 0; }
+        if (triPDF == 0) return false;
+        pdf *= triPDF;
+        *pErr = gamma_(6) * (Abs(b[0] * p0) + Abs(b[1] * p1) + Abs((1 - b[0] - b[1]) * p2));
+        *pOut = b[0] * p0 + b[1] * p1 + b[2] * p2; *nOut = n; *pdfOut = pdf;
+        return true;
+    }
+    // shapes.h:300-361 Sphere::Sample(ctx, u) (and shapes.cpp:38-59 Sample(u) for reference points inside the sphere).
+    // ctx.pi is exact here, so ctx.OffsetRayOrigin(pCenter) == ctx.p().
+    static bool SampleSphere(const vspg_sphere &q, float area, const LightSampleCtx &ctx, const float *u, V3 *pOut, V3 *pErr, V3 *nOut, float *pdfOut) {
+        V3 pCenter(q.center); float radius = q.radius;
+        if (DistanceSquared(ctx.p, pCenter) <= Sqr(radius)) {
+            V3 pObj = radius * SampleUniformSphere(u);
+            pObj = pObj * (radius / Length(pObj - V3(0, 0, 0)));
+            V3 pObjError = gamma_(5) * Abs(pObj);
+            V3 n = Normalize(pObj);
+            if (q.flip_normal) n = -n;
+            V3i pi = XfPoint(TranslateM(pCenter), V3i::FromValueAndError(pObj, pObjError));
+            V3 p = pi.Mid();
+            V3 wi = p - ctx.p;
+            if (LengthSquared(wi) == 0) return false;
+            wi = Normalize(wi);
+            float pdf = (1 / area) / (AbsDot(n, -wi) / DistanceSquared(ctx.p, p));
+            if (std::isinf(pdf)) return false;
+            *pOut = p; *pErr = pi.Error(); *nOut = n; *pdfOut = pdf;
+            return true;
+        }
+        float sinThetaMax = radius / Distance(ctx.p, pCenter);
+        float sin2ThetaMax = Sqr(sinThetaMax);
+        float cosThetaMax = SafeSqrt(1 - sin2ThetaMax);
+        float oneMinusCosThetaMax = 1 - cosThetaMax;
+        float cosTheta = (cosThetaMax - 1) * u[0] + 1;
+        float sin2Theta = 1 - Sqr(cosTheta);
+        if (sin2ThetaMax < 0.00068523f) {
+            sin2Theta = sin2ThetaMax * u[0];
+            cosTheta = std::sqrt(1 - sin2Theta);
+            oneMinusCosThetaMax = sin2ThetaMax / 2;
+        }
+        float cosAlpha = sin2Theta / sinThetaMax + cosTheta * SafeSqrt(1 - sin2Theta / Sqr(sinThetaMax));
+        float sinAlpha = SafeSqrt(1 - Sqr(cosAlpha));
+        float phi = u[1] * 2 * Pi;
+        V3 w = SphericalDirection(sinAlpha, cosAlpha, phi);
+        V3 fz = Normalize(pCenter - ctx.p), fx, fy;
+        CoordinateSystem(fz, &fx, &fy);
+        V3 mw = -w;
+        V3 n = mw.x * fx + mw.y * fy + mw.z * fz;
+        V3 p = pCenter + radius * n;
+        if (q.flip_normal) n = -n;
+        *pErr = gamma_(5) * Abs(p);
+        *pOut = p; *nOut = n; *pdfOut = 1 / (2 * Pi * oneMinusCosThetaMax);
+        return true;
+    }
     struct LiSample { bool valid = false; S3 L; V3 wi; float pdf = 0; V3 pLight, pLightErr, nLight; bool delta = false; };
     // shapes.cpp:1155-1214 Sample(u) (area sampling) + :1254-1280 conversion to solid angle; lights.cpp:796-818
     LiSample SampleLi(int light, const LightSampleCtx &ctx, const float *u) const {
@@ -677,6 +764,17 @@ struct Integrator {
             return ls;
         }
         if (l.type == VSPG_LIGHT_UNIFORM_INFINITE) return ls;  // allowIncompletePDF = true (lights.cpp:1022-1023)
+        if (l.shape_kind == 1 || l.shape_kind == 2) {
+            V3 p, pErr, n; float pdf = 0;
+            bool ok = l.shape_kind == 1 ? SampleTriangle(sc->d->triangles[l.shape_index], sc->triArea[l.shape_index], ctx, u, &p, &pErr, &n, &pdf)
+                                        : SampleSphere(sc->d->spheres[l.shape_index], sc->sphereArea[l.shape_index], ctx, u, &p, &pErr, &n, &pdf);
+            if (!ok || pdf == 0 || LengthSquared(p - ctx.p) == 0) return ls;   // lights.cpp:803
+            V3 wi = Normalize(p - ctx.p);
+            S3 Le = sc->AreaL(light, n, -wi);
+            if (!Le) return ls;
+            ls.valid = true; ls.L = Le; ls.wi = wi; ls.pdf = pdf; ls.pLight = p; ls.pLightErr = pErr; ls.nLight = n;
+            return ls;
+        }
         const vspg_quad &q = sc->d->quads[l.shape_index];
         V3 p00(q.p00), p10(q.p10), p01(q.p01), p11(q.p11);
         float pdf = 1; float uv[2];
@@ -736,6 +834,39 @@ struct Integrator {
     // lights.cpp:820-824 -> shapes.cpp:1329-1347 (area-sampling branch), evaluated at the actual hit
     float AreaPDF_Li(int light, const LightSampleCtx &ctx, V3 wi, const SurfaceIntr &hit) const {
         const vspg_light &l = sc->d->lights[light];
+        if (l.shape_kind == 1) {   // shapes.h:1128-1173 Triangle::PDF(ctx, wi)
+            const vspg_triangle &t = sc->d->triangles[l.shape_index];
+            V3 p0(t.p0), p1(t.p1), p2(t.p2);
+            float solidAngle = SphericalTriangleArea(Normalize(p0 - ctx.p), Normalize(p1 - ctx.p), Normalize(p2 - ctx.p));
+            if (solidAngle < MinSphericalSampleAreaTri || solidAngle > MaxSphericalSampleAreaTri) {
+                float r = (1 / sc->triArea[l.shape_index]) / (AbsDot(hit.n, -wi) / DistanceSquared(ctx.p, hit.p));
+                return std::isinf(r) ? 0 : r;
+            }
+            float pdf = 1 / solidAngle;
+            if (!(ctx.ns.x == 0 && ctx.ns.y == 0 && ctx.ns.z == 0)) {
+                V3 v[3] = {p0, p1, p2};
+                float uu[2];
+                InvertSphericalTriangleSample(v, ctx.p, wi, uu);
+                V3 wv[3] = {Normalize(p0 - ctx.p), Normalize(p1 - ctx.p), Normalize(p2 - ctx.p)};
+                float w[4] = {std::max<float>(0.01, AbsDot(ctx.ns, wv[1])), std::max<float>(0.01, AbsDot(ctx.ns, wv[1])),
+                              std::max<float>(0.01, AbsDot(ctx.ns, wv[0])), std::max<float>(0.01, AbsDot(ctx.ns, wv[2]))};
+                pdf *= BilinearPDF(uu, w);
+            }
+            return pdf;
+        }
+        if (l.shape_kind == 2) {   // shapes.h:364-392 Sphere::PDF(ctx, wi)
+            const vspg_sphere &sp = sc->d->spheres[l.shape_index];
+            V3 pCenter(sp.center);
+            if (DistanceSquared(ctx.p, pCenter) <= Sqr(sp.radius)) {
+                float r = (1 / sc->sphereArea[l.shape_index]) / (AbsDot(hit.n, -wi) / DistanceSquared(ctx.p, hit.p));
+                return std::isinf(r) ? 0 : r;
+            }
+            float sin2ThetaMax = sp.radius * sp.radius / DistanceSquared(ctx.p, pCenter);
+            float cosThetaMax = SafeSqrt(1 - sin2ThetaMax);
+            float oneMinusCosThetaMax = 1 - cosThetaMax;
+            if (sin2ThetaMax < 0.00068523f) oneMinusCosThetaMax = sin2ThetaMax / 2;
+            return 1 / (2 * Pi * oneMinusCosThetaMax);
+        }
         const vspg_quad &q = sc->d->quads[l.shape_index];
         V3 p00(q.p00), p10(q.p10), p01(q.p01), p11(q.p11);
         float pdf = 1;

@@ -192,7 +192,10 @@ struct BVHLightSampler {
         return b.phi * M_omega * Kr * b.bounds.SurfaceArea();
     }
     // lights: the scene's lights; quads + quadArea: the emitting bilinear patches
-    void Build(const vspg_light *lights, int nLights, const vspg_quad *quads, const std::vector<float> &quadArea) {
+    // tris / spheres + their areas: emitting triangles (shapes.cpp:290-314) and full spheres (shapes.cpp:33-36, shapes.h:134)
+    void Build(const vspg_light *lights, int nLights, const vspg_quad *quads, const std::vector<float> &quadArea,
+               const vspg_triangle *tris = nullptr, const std::vector<float> *triArea = nullptr,
+               const vspg_sphere *spheres = nullptr, const std::vector<float> *sphereArea = nullptr) {
         nodes.clear(); infiniteLights.clear();
         lightToBitTrail.assign(nLights, 0u); hasKey.assign(nLights, 0);
         allLightBounds = LBox();
@@ -204,6 +207,21 @@ struct BVHLightSampler {
             if (l.type == VSPG_LIGHT_POINT) {   // lights.cpp:200-205
                 lb.bounds.pMin = lb.bounds.pMax = V3(l.pos);
                 lb.w = V3(0, 0, 1); lb.phi = 4 * Pi * maxL; lb.cosTheta_o = std::cos(Pi); lb.cosTheta_e = std::cos(Pi / 2); lb.twoSided = false;
+            } else if (l.type == VSPG_LIGHT_DIFFUSE_AREA && l.shape_kind == 1) {   // Triangle::Bounds / NormalBounds
+                const vspg_triangle &q = tris[l.shape_index];
+                V3 p0(q.p0), p1(q.p1), p2(q.p2);
+                lb.bounds = Union(Union(Union(LBox(), p0), p1), p2);
+                V3 n = Normalize(Cross(p1 - p0, p2 - p0));
+                if (q.flip_normal) n = -n;
+                lb.w = Normalize(n); lb.phi = maxL * ((*triArea)[l.shape_index] * Pi); lb.cosTheta_o = 1; lb.cosTheta_e = std::cos(Pi / 2);
+                lb.twoSided = l.two_sided != 0;
+            } else if (l.type == VSPG_LIGHT_DIFFUSE_AREA && l.shape_kind == 2) {   // Sphere::Bounds, NormalBounds = EntireSphere
+                const vspg_sphere &q = spheres[l.shape_index];
+                V3 c(q.center);
+                lb.bounds.pMin = V3(-q.radius + c.x, -q.radius + c.y, -q.radius + c.z);
+                lb.bounds.pMax = V3(q.radius + c.x, q.radius + c.y, q.radius + c.z);
+                lb.w = V3(0, 0, 1); lb.phi = maxL * ((*sphereArea)[l.shape_index] * Pi); lb.cosTheta_o = -1; lb.cosTheta_e = std::cos(Pi / 2);
+                lb.twoSided = l.two_sided != 0;
             } else if (l.type == VSPG_LIGHT_DIFFUSE_AREA) {   // lights.cpp:845-864 + shapes.cpp:1070-1126
                 const vspg_quad &q = quads[l.shape_index];
                 V3 p00(q.p00), p10(q.p10), p01(q.p01), p11(q.p11);

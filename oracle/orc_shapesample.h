@@ -103,4 +103,88 @@ inline void InvertSphericalRectangleSample(V3 pRef, V3 s, V3 ex, V3 ey, V3 pRect
     uOut[1] = (std::abs(yz[0] - yv) < std::abs(yz[1] - yv)) ? u1[0] : u1[1];
 }
 
+// ---------------------------------------------------------------------------------------------------- triangles
+constexpr float MinSphericalSampleAreaTri = 3e-4f, MaxSphericalSampleAreaTri = 6.22f;   // shapes.h:1190-1191
+
+inline float SumOfProducts(float a, float b, float c, float d) {  // util/math.h:577-582
+    float cd = c * d;
+    float sop = FMA(a, b, cd);
+    float err = FMA(c, d, -cd);
+    return sop + err;
+}
+inline V3 GramSchmidt(V3 v, V3 w) { return v - Dot(v, w) * w; }   // vecmath.h:994
+inline float SphericalTriangleArea(V3 a, V3 b, V3 c) {            // vecmath.h:1638-1641
+    return std::abs(2 * std::atan2(Dot(a, Cross(b, c)), 1 + Dot(a, b) + Dot(a, c) + Dot(b, c)));
+}
+inline void SampleUniformTriangle(const float *u, float *b) {     // sampling.h:173-183
+    float b0, b1;
+    if (u[0] < u[1]) { b0 = u[0] / 2; b1 = u[1] - b0; }
+    else { b1 = u[1] / 2; b0 = u[0] - b1; }
+    b[0] = b0; b[1] = b1; b[2] = 1 - b0 - b1;
+}
+// util/sampling.cpp:28-107.  Returns false for the reference's empty return (all-zero barycentrics, pdf 0).
+inline bool SampleSphericalTriangle(const V3 *v, V3 p, const float *u, float *bary, float *pdf) {
+    *pdf = 0;
+    V3 a = Normalize(v[0] - p), b = Normalize(v[1] - p), c = Normalize(v[2] - p);
+    V3 n_ab = Cross(a, b), n_bc = Cross(b, c), n_ca = Cross(c, a);
+    if (LengthSquared(n_ab) == 0 || LengthSquared(n_bc) == 0 || LengthSquared(n_ca) == 0) return false;
+    n_ab = Normalize(n_ab); n_bc = Normalize(n_bc); n_ca = Normalize(n_ca);
+    float alpha = AngleBetween(n_ab, -n_ca), beta = AngleBetween(n_bc, -n_ab), gamma = AngleBetween(n_ca, -n_bc);
+    float A_pi = alpha + beta + gamma;
+    float Ap_pi = Lerp(u[0], Pi, A_pi);
+    float A = A_pi - Pi;
+    *pdf = (A <= 0) ? 0 : 1 / A;
+    float cosAlpha = std::cos(alpha), sinAlpha = std::sin(alpha);
+    float sinPhi = std::sin(Ap_pi) * cosAlpha - std::cos(Ap_pi) * sinAlpha;
+    float cosPhi = std::cos(Ap_pi) * cosAlpha + std::sin(Ap_pi) * sinAlpha;
+    float k1 = cosPhi + cosAlpha;
+    float k2 = sinPhi - sinAlpha * Dot(a, b);
+    float cosBp = (k2 + (DifferenceOfProducts(k2, cosPhi, k1, sinPhi)) * cosAlpha) / ((SumOfProducts(k2, sinPhi, k1, cosPhi)) * sinAlpha);
+    cosBp = Clamp(cosBp, -1, 1);
+    float sinBp = SafeSqrt(1 - Sqr(cosBp));
+    V3 cp = cosBp * a + sinBp * Normalize(GramSchmidt(c, a));
+    float cosTheta = 1 - u[1] * (1 - Dot(cp, b));
+    float sinTheta = SafeSqrt(1 - Sqr(cosTheta));
+    V3 w = cosTheta * b + sinTheta * Normalize(GramSchmidt(cp, b));
+    V3 e1 = v[1] - v[0], e2 = v[2] - v[0];
+    V3 s1 = Cross(w, e2);
+    float divisor = Dot(s1, e1);
+    if (divisor == 0) { bary[0] = bary[1] = bary[2] = 1.f / 3.f; return true; }
+    float invDivisor = 1 / divisor;
+    V3 s = p - v[0];
+    float b1 = Dot(s, s1) * invDivisor;
+    float b2 = Dot(w, Cross(s, e1)) * invDivisor;
+    b1 = Clamp(b1, 0, 1);
+    b2 = Clamp(b2, 0, 1);
+    if (b1 + b2 > 1) {   // as written in the reference: b2 is divided by the sum with the already rescaled b1
+        b1 /= b1 + b2;
+        b2 /= b1 + b2;
+    }
+    bary[0] = 1 - b1 - b2; bary[1] = b1; bary[2] = b2;
+    return true;
+}
+// util/sampling.cpp:110-161
+inline void InvertSphericalTriangleSample(const V3 *v, V3 p, V3 w, float *uo) {
+    uo[0] = uo[1] = 0;
+    V3 a = Normalize(v[0] - p), b = Normalize(v[1] - p), c = Normalize(v[2] - p);
+    V3 n_ab = Cross(a, b), n_bc = Cross(b, c), n_ca = Cross(c, a);
+    if (LengthSquared(n_ab) == 0 || LengthSquared(n_bc) == 0 || LengthSquared(n_ca) == 0) return;
+    n_ab = Normalize(n_ab); n_bc = Normalize(n_bc); n_ca = Normalize(n_ca);
+    float alpha = AngleBetween(n_ab, -n_ca), beta = AngleBetween(n_bc, -n_ab), gamma = AngleBetween(n_ca, -n_bc);
+    V3 cp = Normalize(Cross(Cross(b, w), Cross(c, a)));
+    if (Dot(cp, a + c) < 0) cp = -cp;
+    float u0;
+    if (Dot(a, cp) > 0.99999847691f) u0 = 0;
+    else {
+        V3 n_cpb = Cross(cp, b), n_acp = Cross(a, cp);
+        if (LengthSquared(n_cpb) == 0 || LengthSquared(n_acp) == 0) { uo[0] = uo[1] = 0.5f; return; }
+        n_cpb = Normalize(n_cpb); n_acp = Normalize(n_acp);
+        float Ap = alpha + AngleBetween(n_ab, n_cpb) + AngleBetween(n_acp, -n_cpb) - Pi;
+        float A = alpha + beta + gamma - Pi;
+        u0 = Ap / A;
+    }
+    float u1 = (1 - Dot(w, b)) / (1 - Dot(cp, b));
+    uo[0] = Clamp(u0, 0, 1); uo[1] = Clamp(u1, 0, 1);
+}
+
 }  // namespace orc

@@ -20,6 +20,8 @@ def small(name, **kw):
         return cfg
     if name == "C1S":
         return configs.config1_spheres(res=kw.get("res", 48), spp=kw.get("spp", 4))
+    if name == "C1E":
+        return configs.config1_emitters(res=kw.get("res", 48), spp=kw.get("spp", 4))
     if name == "C1T":
         return configs.config1_triangles(res=kw.get("res", 48), spp=kw.get("spp", 4))
     common = dict(grid_n=kw.get("grid_n", 32), vol_leaves=kw.get("vol_leaves", 256), surf_leaves=kw.get("surf_leaves", 128))

@@ -94,7 +94,7 @@ def write_exr(path, channels):
 
 
 # ------------------------------------------------------------------ descs
-@pytest.mark.parametrize("name", ["C1", "C1T", "C1S", "C1G", "C2-unguided", "C5-unguided"])
+@pytest.mark.parametrize("name", ["C1", "C1T", "C1S", "C1E", "C1G", "C2-unguided", "C5-unguided"])
 def test_front_end_reproduces_the_harness_descs(name, tmp_path):
     base = name.split("-")[0]
     cfg = H.small(base, grid_n=8)

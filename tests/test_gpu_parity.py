@@ -249,7 +249,7 @@ def test_guided_sample_parity_on_a_reference_trained_field(ctx, orc, surface):
         assert err.max() <= REL_TOL, f"{k}: max rel err {err.max():.3e}"
 
 
-RENDER_CASES = [("C1", {}), ("C1T", {}), ("C1S", {}), ("C1G", {}), ("C1", dict(vsp_guiding=1)), ("C2", {}), ("C3", {}), ("C4", {}), ("C5", {}),
+RENDER_CASES = [("C1", {}), ("C1T", {}), ("C1S", {}), ("C1E", {}), ("C1E", dict(light_sampler=A.LIGHTSAMPLER_POWER)), ("C1G", {}), ("C1", dict(vsp_guiding=1)), ("C2", {}), ("C3", {}), ("C4", {}), ("C5", {}),
                 ("C5", dict(light_sampler=A.LIGHTSAMPLER_BVH)), ("C2", dict(light_sampler=A.LIGHTSAMPLER_BVH)), ("C1", dict(light_sampler=A.LIGHTSAMPLER_BVH)),
                 ("C2", dict(max_depth=1)), ("C3", dict(volume_guiding_ris=1, surface_guiding_ris=0))]
 
@@ -272,7 +272,7 @@ def _render_both(ctx, orc, name, over, seed=7):
     return cfg, film_g, cnt_g, film_o, cnt_o
 
 
-@pytest.mark.parametrize("name", ["C1", "C1T", "C1S", "C1G", "C2", "C3", "C4", "C5"])
+@pytest.mark.parametrize("name", ["C1", "C1T", "C1S", "C1E", "C1G", "C2", "C3", "C4", "C5"])
 def test_render_without_nee_is_path_exact(ctx, orc, name):
     """usenee=false: every random decision of a path comes from its own (pixel, sampleIndex) PCG32 stream, which is
     identical on both sides, so whole films agree path by path (camera ray, BVH, DDA, SampleDistance, cache lookup,

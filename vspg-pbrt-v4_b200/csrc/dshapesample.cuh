@@ -105,4 +105,84 @@ __device__ __noinline__ void invert_spherical_rectangle_sample(V3 pRef, V3 s, V3
     *uo1 = fabsf(yza - yv) < fabsf(yzb - yv) ? u1a : u1b;
 }
 
+// ---------------------------------------------------------------------------------------------------- triangles
+constexpr float kMinSphericalSampleAreaTri = 3e-4f, kMaxSphericalSampleAreaTri = 6.22f;   // shapes.h:1190-1191
+
+VD float sum_of_products(float a, float b, float c, float d) {   // util/math.h:577-582
+    float cd = c * d;
+    float sop = fmaf(a, b, cd);
+    float err = fmaf(c, d, -cd);
+    return sop + err;
+}
+VD V3 gram_schmidt(V3 v, V3 w) { return v - dot(v, w) * w; }
+VD float spherical_triangle_area(V3 a, V3 b, V3 c) {              // util/vecmath.h:1638-1641
+    return fabsf(2 * atan2f(dot(a, cross(b, c)), 1 + dot(a, b) + dot(a, c) + dot(b, c)));
+}
+
+// util/sampling.cpp:28-107; false = the reference's empty return
+__device__ __noinline__ bool sample_spherical_triangle(V3 v0, V3 v1, V3 v2, V3 p, float u0, float u1, float *bary, float *pdf) {
+    *pdf = 0;
+    V3 a = normalize(v0 - p), b = normalize(v1 - p), c = normalize(v2 - p);
+    V3 n_ab = cross(a, b), n_bc = cross(b, c), n_ca = cross(c, a);
+    if (length_sq(n_ab) == 0 || length_sq(n_bc) == 0 || length_sq(n_ca) == 0) return false;
+    n_ab = normalize(n_ab); n_bc = normalize(n_bc); n_ca = normalize(n_ca);
+    float alpha = angle_between(n_ab, -n_ca), beta = angle_between(n_bc, -n_ab), gamma = angle_between(n_ca, -n_bc);
+    float A_pi = alpha + beta + gamma;
+    float Ap_pi = lerpf(u0, kPi, A_pi);
+    float A = A_pi - kPi;
+    *pdf = (A <= 0) ? 0 : 1 / A;
+    float cosAlpha = cosf(alpha), sinAlpha = sinf(alpha);
+    float sinPhi = sinf(Ap_pi) * cosAlpha - cosf(Ap_pi) * sinAlpha;
+    float cosPhi = cosf(Ap_pi) * cosAlpha + sinf(Ap_pi) * sinAlpha;
+    float k1 = cosPhi + cosAlpha;
+    float k2 = sinPhi - sinAlpha * dot(a, b);
+    float cosBp = (k2 + (diff_of_products(k2, cosPhi, k1, sinPhi)) * cosAlpha) / ((sum_of_products(k2, sinPhi, k1, cosPhi)) * sinAlpha);
+    cosBp = clampf(cosBp, -1.f, 1.f);
+    float sinBp = safe_sqrt(1 - sqr(cosBp));
+    V3 cp = cosBp * a + sinBp * normalize(gram_schmidt(c, a));
+    float cosTheta = 1 - u1 * (1 - dot(cp, b));
+    float sinTheta = safe_sqrt(1 - sqr(cosTheta));
+    V3 w = cosTheta * b + sinTheta * normalize(gram_schmidt(cp, b));
+    V3 e1 = v1 - v0, e2 = v2 - v0;
+    V3 s1 = cross(w, e2);
+    float divisor = dot(s1, e1);
+    if (divisor == 0) { bary[0] = bary[1] = bary[2] = 1.f / 3.f; return true; }
+    float invDivisor = 1 / divisor;
+    V3 s = p - v0;
+    float b1 = dot(s, s1) * invDivisor;
+    float b2 = dot(w, cross(s, e1)) * invDivisor;
+    b1 = clampf(b1, 0.f, 1.f);
+    b2 = clampf(b2, 0.f, 1.f);
+    if (b1 + b2 > 1) {   // as the reference writes it: b2 is divided by the sum with the already rescaled b1
+        b1 /= b1 + b2;
+        b2 /= b1 + b2;
+    }
+    bary[0] = 1 - b1 - b2; bary[1] = b1; bary[2] = b2;
+    return true;
+}
+
+// util/sampling.cpp:110-161
+__device__ __noinline__ void invert_spherical_triangle_sample(V3 v0, V3 v1, V3 v2, V3 p, V3 w, float *uo0, float *uo1) {
+    *uo0 = *uo1 = 0;
+    V3 a = normalize(v0 - p), b = normalize(v1 - p), c = normalize(v2 - p);
+    V3 n_ab = cross(a, b), n_bc = cross(b, c), n_ca = cross(c, a);
+    if (length_sq(n_ab) == 0 || length_sq(n_bc) == 0 || length_sq(n_ca) == 0) return;
+    n_ab = normalize(n_ab); n_bc = normalize(n_bc); n_ca = normalize(n_ca);
+    float alpha = angle_between(n_ab, -n_ca), beta = angle_between(n_bc, -n_ab), gamma = angle_between(n_ca, -n_bc);
+    V3 cp = normalize(cross(cross(b, w), cross(c, a)));
+    if (dot(cp, a + c) < 0) cp = -cp;
+    float u0;
+    if (dot(a, cp) > 0.99999847691f) u0 = 0;
+    else {
+        V3 n_cpb = cross(cp, b), n_acp = cross(a, cp);
+        if (length_sq(n_cpb) == 0 || length_sq(n_acp) == 0) { *uo0 = *uo1 = 0.5f; return; }
+        n_cpb = normalize(n_cpb); n_acp = normalize(n_acp);
+        float Ap = alpha + angle_between(n_ab, n_cpb) + angle_between(n_acp, -n_cpb) - kPi;
+        float A = alpha + beta + gamma - kPi;
+        u0 = Ap / A;
+    }
+    float u1 = (1 - dot(w, b)) / (1 - dot(cp, b));
+    *uo0 = clampf(u0, 0.f, 1.f); *uo1 = clampf(u1, 0.f, 1.f);
+}
+
 }  // namespace vspg

@@ -5,6 +5,7 @@
 // mixture op compiled out.
 #pragma once
 #include "dshapesample.cuh"
+#include "dsphere.cuh"
 #include "dguiding.cuh"
 #include "dpath.cuh"
 
@@ -127,6 +128,118 @@ VD float light_pmf(const DScene &sc, int light, V3 p, V3 n) {
     return sc.lights[light].pmf;
 }
 
+// shapes.h:1053-1125 Triangle::Sample(ctx, u) (and :1014-1048 Sample(u) for the area-sampling fallback)
+__device__ __noinline__ bool sample_triangle_light(const DQuad &q, V3 ctxP, V3 ctxNs, float u0, float u1, V3 *pOut, V3 *pErr, V3 *nOut, float *pdfOut) {
+    V3 p0 = ld3(q.p00), p1 = ld3(q.p10), p2 = ld3(q.p01);
+    V3 n = normalize(cross(p1 - p0, p2 - p0));
+    if (q.flip_normal) n = -n;
+    V3 w0 = normalize(p0 - ctxP), w1 = normalize(p1 - ctxP), w2 = normalize(p2 - ctxP);
+    float solidAngle = spherical_triangle_area(w0, w1, w2);
+    float b[3];
+    if (solidAngle < kMinSphericalSampleAreaTri || solidAngle > kMaxSphericalSampleAreaTri) {
+        if (u0 < u1) { b[0] = u0 / 2; b[1] = u1 - b[0]; } else { b[1] = u1 / 2; b[0] = u0 - b[1]; }   // SampleUniformTriangle
+        b[2] = 1 - b[0] - b[1];
+        V3 p = b[0] * p0 + b[1] * p1 + b[2] * p2;
+        *pErr = gammaN(6) * (vabs(b[0] * p0) + vabs(b[1] * p1) + vabs((1 - b[0] - b[1]) * p2));
+        V3 wi = p - ctxP;
+        if (length_sq(wi) == 0) return false;
+        wi = normalize(wi);
+        float pdf = (1 / q.area) / (absdot(n, -wi) / dist_sq(ctxP, p));
+        if (isinf(pdf)) return false;
+        *pOut = p; *nOut = n; *pdfOut = pdf;
+        return true;
+    }
+    float pdf = 1;
+    if (!(ctxNs.x == 0 && ctxNs.y == 0 && ctxNs.z == 0)) {
+        float w[4] = {fmaxf(0.01f, absdot(ctxNs, w1)), fmaxf(0.01f, absdot(ctxNs, w1)), fmaxf(0.01f, absdot(ctxNs, w0)), fmaxf(0.01f, absdot(ctxNs, w2))};
+        float a0, a1;
+        sample_bilinear(u0, u1, w, &a0, &a1);
+        u0 = a0; u1 = a1;
+        pdf = bilinear_pdf(u0, u1, w);
+    }
+    float triPDF;
+    if (!sample_spherical_triangle(p0, p1, p2, ctxP, u0, u1, b, &triPDF)) b[0] = b[1] = b[2] = 0;
+    if (triPDF == 0) return false;
+    pdf *= triPDF;
+    *pErr = gammaN(6) * (vabs(b[0] * p0) + vabs(b[1] * p1) + vabs((1 - b[0] - b[1]) * p2));
+    *pOut = b[0] * p0 + b[1] * p1 + b[2] * p2; *nOut = n; *pdfOut = pdf;
+    return true;
+}
+// shapes.h:1128-1173 Triangle::PDF(ctx, wi) evaluated at the actual hit
+__device__ __noinline__ float triangle_light_pdf(const DQuad &q, V3 ctxP, V3 ctxNs, V3 wi, V3 hitP, V3 hitN) {
+    V3 p0 = ld3(q.p00), p1 = ld3(q.p10), p2 = ld3(q.p01);
+    V3 w0 = normalize(p0 - ctxP), w1 = normalize(p1 - ctxP), w2 = normalize(p2 - ctxP);
+    float solidAngle = spherical_triangle_area(w0, w1, w2);
+    if (solidAngle < kMinSphericalSampleAreaTri || solidAngle > kMaxSphericalSampleAreaTri) {
+        float r = (1 / q.area) / (absdot(hitN, -wi) / dist_sq(ctxP, hitP));
+        return isinf(r) ? 0 : r;
+    }
+    float pdf = 1 / solidAngle;
+    if (!(ctxNs.x == 0 && ctxNs.y == 0 && ctxNs.z == 0)) {
+        float uu0, uu1;
+        invert_spherical_triangle_sample(p0, p1, p2, ctxP, wi, &uu0, &uu1);
+        float w[4] = {fmaxf(0.01f, absdot(ctxNs, w1)), fmaxf(0.01f, absdot(ctxNs, w1)), fmaxf(0.01f, absdot(ctxNs, w0)), fmaxf(0.01f, absdot(ctxNs, w2))};
+        pdf *= bilinear_pdf(uu0, uu1, w);
+    }
+    return pdf;
+}
+// shapes.h:300-361 Sphere::Sample(ctx, u) (shapes.cpp:38-59 Sample(u) for reference points inside the sphere); the
+// reference point is exact here, so ctx.OffsetRayOrigin(pCenter) == ctx.p()
+__device__ __noinline__ bool sample_sphere_light(const DQuad &q, V3 ctxP, float u0, float u1, V3 *pOut, V3 *pErr, V3 *nOut, float *pdfOut) {
+    V3 pCenter = ld3(q.p00); float radius = q.p10[0];
+    if (dist_sq(ctxP, pCenter) <= sqr(radius)) {
+        float z = 1 - 2 * u0, r = safe_sqrt(1 - sqr(z));
+        float sp, cp; sincospif(2.f * u1, &sp, &cp);
+        V3 pObj = radius * V3(r * cp, r * sp, z);
+        pObj = pObj * (radius / length(pObj));
+        V3 n = normalize(pObj);
+        if (q.flip_normal) n = -n;
+        V3 p, dummyN, dummyDpdu;
+        sphere_interaction(pObj, pCenter, radius, false, &p, pErr, &dummyN, &dummyDpdu);   // renderFromObject(Point3fi(pObj, gamma(5)|pObj|))
+        V3 wi = p - ctxP;
+        if (length_sq(wi) == 0) return false;
+        wi = normalize(wi);
+        float pdf = (1 / q.area) / (absdot(n, -wi) / dist_sq(ctxP, p));
+        if (isinf(pdf)) return false;
+        *pOut = p; *nOut = n; *pdfOut = pdf;
+        return true;
+    }
+    float sinThetaMax = radius / sqrtf(dist_sq(ctxP, pCenter));
+    float sin2ThetaMax = sqr(sinThetaMax);
+    float cosThetaMax = safe_sqrt(1 - sin2ThetaMax);
+    float oneMinusCosThetaMax = 1 - cosThetaMax;
+    float cosTheta = (cosThetaMax - 1) * u0 + 1;
+    float sin2Theta = 1 - sqr(cosTheta);
+    if (sin2ThetaMax < 0.00068523f) {
+        sin2Theta = sin2ThetaMax * u0;
+        cosTheta = sqrtf(1 - sin2Theta);
+        oneMinusCosThetaMax = sin2ThetaMax / 2;
+    }
+    float cosAlpha = sin2Theta / sinThetaMax + cosTheta * safe_sqrt(1 - sin2Theta / sqr(sinThetaMax));
+    float sinAlpha = safe_sqrt(1 - sqr(cosAlpha));
+    V3 w = spherical_direction_2pi(sinAlpha, cosAlpha, u1);
+    Frame f = Frame::from_z(normalize(pCenter - ctxP));
+    V3 n = f.from_local(-w);
+    V3 p = pCenter + radius * n;
+    if (q.flip_normal) n = -n;
+    *pErr = gammaN(5) * vabs(p);
+    *pOut = p; *nOut = n; *pdfOut = 1 / (2 * kPi * oneMinusCosThetaMax);
+    return true;
+}
+// shapes.h:364-392 Sphere::PDF(ctx, wi)
+VD float sphere_light_pdf(const DQuad &q, V3 ctxP, V3 wi, V3 hitP, V3 hitN) {
+    V3 pCenter = ld3(q.p00); float radius = q.p10[0];
+    if (dist_sq(ctxP, pCenter) <= sqr(radius)) {
+        float r = (1 / q.area) / (absdot(hitN, -wi) / dist_sq(ctxP, hitP));
+        return isinf(r) ? 0 : r;
+    }
+    float sin2ThetaMax = radius * radius / dist_sq(ctxP, pCenter);
+    float cosThetaMax = safe_sqrt(1 - sin2ThetaMax);
+    float oneMinusCosThetaMax = 1 - cosThetaMax;
+    if (sin2ThetaMax < 0.00068523f) oneMinusCosThetaMax = sin2ThetaMax / 2;
+    return 1 / (2 * kPi * oneMinusCosThetaMax);
+}
+
 // lights.cpp:796-818 DiffuseAreaLight::SampleLi -> shapes.cpp:1155-1214, 1254-1280 (area-sampling branch);
 // lights.h:243-250 (point), 316-323 (distant); uniform infinite: allowIncompletePDF (lights.cpp:1022-1023)
 VD LiSample sample_li(const DScene &sc, int light, V3 ctxP, V3 ctxNs, float u0, float u1) {
@@ -146,7 +259,18 @@ VD LiSample sample_li(const DScene &sc, int light, V3 ctxP, V3 ctxNs, float u0, 
         return ls;
     }
     if (l.type == VSPG_LIGHT_UNIFORM_INFINITE) return ls;
-    const DQuad &q = sc.quads[l.shape_index];
+    const DQuad &q = sc.quads[l.shape_index];   // global primitive id
+    if (q.kind != PRIM_QUAD) {
+        V3 p, pErr, n; float pdf = 0;
+        bool ok = q.kind == PRIM_TRIANGLE ? sample_triangle_light(q, ctxP, ctxNs, u0, u1, &p, &pErr, &n, &pdf)
+                                          : sample_sphere_light(q, ctxP, u0, u1, &p, &pErr, &n, &pdf);
+        if (!ok || pdf == 0 || dist_sq(p, ctxP) == 0) return ls;   // lights.cpp:803
+        V3 wi = normalize(p - ctxP);
+        V3 Le = area_L(l, n, -wi);
+        if (!nonzero(Le)) return ls;
+        ls.valid = true; ls.L = Le; ls.wi = wi; ls.pdf = pdf; ls.pLight = p; ls.pLightErr = pErr; ls.nLight = n;
+        return ls;
+    }
     V3 p00 = ld3(q.p00), p10 = ld3(q.p10), p01 = ld3(q.p01), p11 = ld3(q.p11);
     float pdf = 1, uvx, uvy;
     if (q.is_rect) {
@@ -204,6 +328,8 @@ VD LiSample sample_li(const DScene &sc, int light, V3 ctxP, V3 ctxNs, float u0, 
 // lights.cpp:820-824 -> shapes.cpp:1329-1347 (area-sampling branch) evaluated at the actual hit
 VD float area_pdf_li(const DScene &sc, int light, V3 ctxP, V3 ctxNs, V3 wi, const SurfaceIntr &hit) {
     const DQuad &q = sc.quads[sc.lights[light].shape_index];
+    if (q.kind == PRIM_TRIANGLE) return triangle_light_pdf(q, ctxP, ctxNs, wi, hit.p, hit.n);
+    if (q.kind == PRIM_SPHERE) return sphere_light_pdf(q, ctxP, wi, hit.p, hit.n);
     V3 p00 = ld3(q.p00), p10 = ld3(q.p10), p01 = ld3(q.p01), p11 = ld3(q.p11);
     float pdf = 1;
     if (q.is_rect) {   // shapes.cpp:1352-1368 PDF for a sample in the spherical rectangle

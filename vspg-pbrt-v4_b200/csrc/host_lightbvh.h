@@ -205,9 +205,13 @@ struct Builder {
 };
 }  // namespace lbvh
 
-// quads: the scene's bilinear patches (render space); area[i] their areas (as set_scene computes them)
-inline HostLightBvh build_light_bvh(const vspg_light *lights, int nLights, const vspg_quad *quads, const float *quadArea) {
+// scene: lights + the shapes they emit from (render space); primArea[i]: area of the i-th primitive counted over
+// quads, then triangles, then spheres (as set_scene computes them)
+inline HostLightBvh build_light_bvh(const vspg_scene_desc *scene, const float *primArea) {
     using namespace lbvh;
+    const vspg_light *lights = scene->lights; const int nLights = scene->n_lights;
+    const vspg_quad *quads = scene->quads;
+    const float *quadArea = primArea, *triArea = primArea + scene->n_quads, *sphereArea = primArea + scene->n_quads + scene->n_triangles;
     HostLightBvh out;
     out.bitTrail.assign(nLights, 0u); out.inTree.assign(nLights, 0);
     std::vector<Builder::Item> items;
@@ -220,6 +224,19 @@ inline HostLightBvh build_light_bvh(const vspg_light *lights, int nLights, const
         if (l.type == VSPG_LIGHT_POINT) {   // lights.cpp:200-205
             for (int k = 0; k < 3; k++) lb.bmin[k] = lb.bmax[k] = l.pos[k];
             lb.w = H3(0, 0, 1); lb.phi = 4 * kPi * maxL; lb.cosTheta_o = std::cos(kPi); lb.cosTheta_e = cosHalfPi; lb.twoSided = false;
+        } else if (l.type == VSPG_LIGHT_DIFFUSE_AREA && l.shape_kind == 1) {   // shapes.cpp:290-314 Triangle::Bounds / NormalBounds
+            const vspg_triangle &q = scene->triangles[l.shape_index];
+            H3 p0(q.p0), p1(q.p1), p2(q.p2);
+            for (int k = 0; k < 3; k++) { lb.bmin[k] = std::min(std::min(p0[k], p1[k]), p2[k]); lb.bmax[k] = std::max(std::max(p0[k], p1[k]), p2[k]); }
+            H3 n = hnormalize(hcross(p1 - p0, p2 - p0));
+            if (q.flip_normal) n = -1.f * n;
+            lb.w = hnormalize(n); lb.phi = maxL * (triArea[l.shape_index] * kPi); lb.cosTheta_o = 1; lb.cosTheta_e = cosHalfPi;
+            lb.twoSided = l.two_sided != 0;
+        } else if (l.type == VSPG_LIGHT_DIFFUSE_AREA && l.shape_kind == 2) {   // shapes.cpp:33-36 Sphere::Bounds, shapes.h:134 EntireSphere
+            const vspg_sphere &q = scene->spheres[l.shape_index];
+            for (int k = 0; k < 3; k++) { lb.bmin[k] = -q.radius + q.center[k]; lb.bmax[k] = q.radius + q.center[k]; }
+            lb.w = H3(0, 0, 1); lb.phi = maxL * (sphereArea[l.shape_index] * kPi); lb.cosTheta_o = -1; lb.cosTheta_e = cosHalfPi;
+            lb.twoSided = l.two_sided != 0;
         } else if (l.type == VSPG_LIGHT_DIFFUSE_AREA) {   // lights.cpp:845-864
             const vspg_quad &q = quads[l.shape_index];
             H3 p00(q.p00), p10(q.p10), p01(q.p01), p11(q.p11);

@@ -196,7 +196,6 @@ int vspg_set_scene(vspg_ctx *ctx, const vspg_scene_desc *s) {
         memcpy(q.p00, t.p0, 12); memcpy(q.p10, t.p1, 12); memcpy(q.p01, t.p2, 12); memcpy(q.p11, t.p2, 12);
         q.material = t.material; q.area_light = t.area_light; q.medium_inside = t.medium_inside; q.medium_outside = t.medium_outside;
         q.has_interface = t.has_interface; q.flip_normal = t.flip_normal;
-        if (t.area_light >= 0) return fail(ctx, VSPG_ERR_UNSUPPORTED, "set_scene: triangle %d: area lights must be bilinear patches (emissive triangles are not built yet)", i);
     }
     for (int i = 0; i < s->n_spheres; i++) {
         const vspg_sphere &t = s->spheres[i];
@@ -208,7 +207,6 @@ int vspg_set_scene(vspg_ctx *ctx, const vspg_scene_desc *s) {
         }
         q.material = t.material; q.area_light = t.area_light; q.medium_inside = t.medium_inside; q.medium_outside = t.medium_outside;
         q.has_interface = t.has_interface; q.flip_normal = t.flip_normal;
-        if (t.area_light >= 0) return fail(ctx, VSPG_ERR_UNSUPPORTED, "set_scene: sphere %d: area lights must be bilinear patches (emissive spheres are not built yet)", i);
     }
     float bmin[3] = {INFINITY, INFINITY, INFINITY}, bmax[3] = {-INFINITY, -INFINITY, -INFINITY};
     for (int i = 0; i < s->n_quads; i++) hostPrims[i] = s->quads[i];
@@ -265,8 +263,14 @@ int vspg_set_scene(vspg_ctx *ctx, const vspg_scene_desc *s) {
         auto avgScaled = [&](float c) { float v = l.L[0] * c; v += l.L[1] * c; v += l.L[2] * c; return v / 3; };  // (L * c).Average()
         switch (l.type) {  // lights.cpp Phi(), averaged over RGB
         case VSPG_LIGHT_DIFFUSE_AREA:
-            if (l.shape_kind != 0 || l.shape_index < 0 || l.shape_index >= s->n_quads) return fail(ctx, VSPG_ERR_UNSUPPORTED, "set_scene: light %d: area lights must reference a quad", i);
-            power[i] = avgScaled(Pi * (l.two_sided ? 2.f : 1.f) * quads[l.shape_index].area); break;
+        {   // the device light carries the GLOBAL primitive id (quads, then triangles, then spheres)
+            const int nOf[3] = {s->n_quads, s->n_triangles, s->n_spheres}, baseOf[3] = {0, s->n_quads, s->n_quads + s->n_triangles};
+            if (l.shape_kind < 0 || l.shape_kind > 2 || l.shape_index < 0 || l.shape_index >= nOf[l.shape_kind])
+                return fail(ctx, VSPG_ERR_INVALID, "set_scene: light %d: area light references shape kind %d index %d, which does not exist", i, l.shape_kind, l.shape_index);
+            d.shape_index = baseOf[l.shape_kind] + l.shape_index;
+            if (quads[d.shape_index].area_light != i) return fail(ctx, VSPG_ERR_INVALID, "set_scene: light %d and its shape do not reference each other", i);
+            power[i] = avgScaled(Pi * (l.two_sided ? 2.f : 1.f) * quads[d.shape_index].area); break;
+        }
         case VSPG_LIGHT_POINT: power[i] = avgScaled(4 * Pi); break;
         case VSPG_LIGHT_DISTANT: power[i] = avgScaled(Pi * (sc.scene_radius * sc.scene_radius)); break;
         case VSPG_LIGHT_UNIFORM_INFINITE: power[i] = avgScaled(4 * Pi * Pi * (sc.scene_radius * sc.scene_radius)); inf.push_back(i); break;
@@ -280,9 +284,9 @@ int vspg_set_scene(vspg_ctx *ctx, const vspg_scene_desc *s) {
     CK(upload(ctx->scene_allocs, inf.data(), inf.size(), &sc.inf_lights));
     sc.n_lights = s->n_lights; sc.n_inf_lights = (int)inf.size();
     {   // BVHLightSampler (the reference's default "lightsampler"), lightsamplers.cpp:107-236
-        std::vector<float> quadArea(s->n_quads);
-        for (int i = 0; i < s->n_quads; i++) quadArea[i] = quads[i].area;
-        HostLightBvh lb = build_light_bvh(s->lights, s->n_lights, s->quads, quadArea.data());
+        std::vector<float> primArea(nPrims);
+        for (int i = 0; i < nPrims; i++) primArea[i] = quads[i].area;
+        HostLightBvh lb = build_light_bvh(s, primArea.data());
         static_assert(sizeof(HostLightNode) == sizeof(DLightNode) && sizeof(DLightNode) == 64, "light BVH node layout");
         CK(upload(ctx->scene_allocs, (const DLightNode *)lb.nodes.data(), lb.nodes.size(), &sc.lbvh));
         CK(upload(ctx->scene_allocs, (const unsigned *)lb.bitTrail.data(), lb.bitTrail.size(), &sc.light_trail));

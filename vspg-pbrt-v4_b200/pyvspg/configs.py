@@ -83,6 +83,27 @@ def config1_spheres(res=256, spp=16):
     return Config("C1-cornell-spheres", sc.finalize(), None, ip, spp, "Cornell box, sphere medium boundary and diffuse sphere, vspguiding=false")
 
 
+def config1_emitters(res=256, spp=16):
+    """C1 lit by an emissive triangle pair (the usual way .pbrt scenes model a ceiling light) and a small emissive
+    sphere instead of the bilinear patch: Triangle::Sample(ctx) / Sphere::Sample(ctx) (shapes.h:1053-1173, 300-392)."""
+    cam, eye = perspective_camera([0.5, 0.5, -1.4], [0.5, 0.5, 0.5], [0, 1, 0], 40.0, res, res)
+    sc = Scene(cam, eye)
+    white, red, green = sc.add_material([.73, .73, .73]), sc.add_material([.65, .05, .05]), sc.add_material([.12, .45, .15])
+    sc.add_quad([0, 0, 0], [1, 0, 0], [0, 0, 1], material=white)
+    sc.add_quad([0, 1, 0], [0, 0, 1], [1, 0, 0], material=white)
+    sc.add_quad([0, 0, 1], [1, 0, 0], [0, 1, 0], material=white)
+    sc.add_quad([0, 0, 0], [0, 0, 1], [0, 1, 0], material=red)
+    sc.add_quad([1, 0, 0], [0, 1, 0], [0, 0, 1], material=green)
+    # ceiling light as two triangles, normals pointing down: n = normalize(cross(p1 - p0, p2 - p0))
+    P = [[0.35, 0.998, 0.35], [0.65, 0.998, 0.35], [0.65, 0.998, 0.65], [0.35, 0.998, 0.65]]
+    sc.add_triangles(P, [(0, 1, 2), (0, 2, 3)], material=white, emission=[14.0, 10.0, 4.0])
+    sc.add_sphere([0.82, 0.2, 0.25], 0.06, material=white, emission=[6.0, 9.0, 12.0])
+    med = sc.add_homogeneous_medium([0.5, 0.5, 0.5], [2.0, 2.0, 2.0], 1.0, 0.0)
+    sc.add_box([0.3, 0.3, 0.3], [0.7, 0.7, 0.7], material=-1, medium_inside=med, medium_outside=-1, has_interface=True)
+    ip = api.integrator_defaults(vsp_guiding=0, surface_guiding=0, volume_guiding=0, light_sampler=A.LIGHTSAMPLER_BVH)
+    return Config("C1-cornell-emitters", sc.finalize(), None, ip, spp, "Cornell box lit by emissive triangles and an emissive sphere, bvh light sampler, vspguiding=false")
+
+
 def _guiding_for(sc, rng, width, height, vol_leaves, surf_leaves, with_tr=False):
     g = syn.Guiding()
     e = sc.eye.astype(np.float32)
@@ -175,4 +196,4 @@ def config5(width=1920, height=1080, spp=1024, grid_n=256, vol_leaves=8192, surf
                   "mixed scene: emissive quads + diffuse surfaces (BVH) + chromatic heterogeneous medium, full VSPG")
 
 
-BUILDERS = {"C1T": config1_triangles, "C1S": config1_spheres, "C1": config1, "C2": config2, "C3": config3, "C4": config4, "C5": config5}
+BUILDERS = {"C1T": config1_triangles, "C1S": config1_spheres, "C1E": config1_emitters, "C1": config1, "C2": config2, "C3": config3, "C4": config4, "C5": config5}

@@ -107,6 +107,8 @@ def scene_text(cfg, out_dir=None, outfile="out.exr", seed=0, integrator_name="gu
                 name = lambda i: f"medium{i}" if i >= 0 else ""
                 L.append(f'  MediumInterface "{name(e["medium_inside"])}" "{name(e["medium_outside"])}"')
             L.append(f'  NamedMaterial "mat{e["material"]}"' if e["material"] >= 0 else '  Material "interface"')
+            if e.get("emission") is not None:
+                L.append(f'  AreaLightSource "diffuse" "rgb L" [{_v(e["emission"])}] "bool twosided" {_b(e["two_sided"])}')
             L.append('  Shape "trianglemesh" "point3 P" [' + "  ".join(_v(p) for p in e["points"]) + '] "integer indices" ['
                      + "  ".join(" ".join(str(i) for i in t) for t in e["indices"]) + "]")
             L.append("AttributeEnd")
@@ -116,6 +118,8 @@ def scene_text(cfg, out_dir=None, outfile="out.exr", seed=0, integrator_name="gu
                 name = lambda i: f"medium{i}" if i >= 0 else ""
                 L.append(f'  MediumInterface "{name(e["medium_inside"])}" "{name(e["medium_outside"])}"')
             L.append(f'  NamedMaterial "mat{e["material"]}"' if e["material"] >= 0 else '  Material "interface"')
+            if e.get("emission") is not None:
+                L.append(f'  AreaLightSource "diffuse" "rgb L" [{_v(e["emission"])}] "bool twosided" {_b(e["two_sided"])}')
             L.append(f'  Translate {_v(e["center"])}')
             L.append(f'  Shape "sphere" "float radius" [{_f(e["radius"])}]')
             L.append("AttributeEnd")

@@ -116,12 +116,23 @@ class Scene:
             q.area_light = len(self.lights) - 1
         return qi
 
-    def add_triangles(self, points, indices, material=-1, medium_inside=-1, medium_outside=-1, has_interface=False):
-        """Shape "trianglemesh": points [n][3] (world space), indices [m][3]."""
+    def _area_light(self, kind, index, emission, two_sided):
+        l = A.Light()
+        l.type = A.LIGHT_DIFFUSE_AREA
+        l.L[:] = [float(x) for x in emission]
+        l.shape_kind, l.shape_index, l.two_sided, l.medium = kind, index, int(two_sided), -1
+        self.lights.append(l)
+        return len(self.lights) - 1
+
+    def add_triangles(self, points, indices, material=-1, medium_inside=-1, medium_outside=-1, has_interface=False, emission=None,
+                      two_sided=False):
+        """Shape "trianglemesh": points [n][3] (world space), indices [m][3].  With `emission` every triangle becomes
+        its own DiffuseAreaLight, as the reference creates one light per shape."""
         pts = np.asarray(points, dtype=np.float64).reshape(-1, 3)
         idx = np.asarray(indices, dtype=np.int64).reshape(-1, 3)
         self.log.append(("trimesh", dict(points=pts.tolist(), indices=idx.tolist(), material=material, medium_inside=medium_inside,
-                                         medium_outside=medium_outside, has_interface=bool(has_interface))))
+                                         medium_outside=medium_outside, has_interface=bool(has_interface),
+                                         emission=None if emission is None else [float(x) for x in emission], two_sided=bool(two_sided))))
         for tri in idx:
             t = A.Triangle()
             for name, vi in zip(("p0", "p1", "p2"), tri):
@@ -129,18 +140,23 @@ class Scene:
             t.material, t.area_light = material, -1
             t.medium_inside, t.medium_outside, t.has_interface, t.flip_normal = medium_inside, medium_outside, int(has_interface), 0
             self.triangles.append(t)
+            if emission is not None:
+                t.area_light = self._area_light(1, len(self.triangles) - 1, emission, two_sided)
 
-    def add_sphere(self, center, radius, material=-1, medium_inside=-1, medium_outside=-1, has_interface=False):
+    def add_sphere(self, center, radius, material=-1, medium_inside=-1, medium_outside=-1, has_interface=False, emission=None, two_sided=False):
         """Shape "sphere" (full sphere, shapes.h:107) under Translate(center); outward normal."""
         c = np.asarray(center, dtype=np.float64)
         self.log.append(("sphere", dict(center=[float(x) for x in c], radius=float(radius), material=material, medium_inside=medium_inside,
-                                        medium_outside=medium_outside, has_interface=bool(has_interface))))
+                                        medium_outside=medium_outside, has_interface=bool(has_interface),
+                                        emission=None if emission is None else [float(x) for x in emission], two_sided=bool(two_sided))))
         sp = A.Sphere()
         sp.center[:] = [float(np.float32(x)) for x in (c - self.eye)]
         sp.radius = float(np.float32(radius))
         sp.material, sp.area_light = material, -1
         sp.medium_inside, sp.medium_outside, sp.has_interface, sp.flip_normal = medium_inside, medium_outside, int(has_interface), 0
         self.spheres.append(sp)
+        if emission is not None:
+            sp.area_light = self._area_light(2, len(self.spheres) - 1, emission, two_sided)
         return len(self.spheres) - 1
 
     def add_triangle_box(self, lo, hi, **kw):
