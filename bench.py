@@ -314,7 +314,8 @@ def run_b200(args):
         multi.combine_film(film_t, world, dst=0)
         ctx.film_download_to(film_host.data_ptr())   # D2H: fp64 film
 
-    e2e_step(7)
+    for i in range(max(3, min(args.warmup, 5))):   # the first set_scene calls pay cudaMalloc of the staged blocks; later ones reuse them
+        e2e_step(7 + i)
     barrier()
     t0 = time.perf_counter()
     for i in range(e2e_steps):

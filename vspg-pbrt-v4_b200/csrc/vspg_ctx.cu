@@ -6,7 +6,9 @@
 #include <cstdarg>
 #include <cstdio>
 #include <cstdlib>
+#include <map>
 #include <string>
+#include <unordered_map>
 #include <vector>
 
 #include "host_util.h"
@@ -24,6 +26,12 @@ struct vspg_ctx {
     int sm_count = 148;
     std::string err;
     std::vector<void *> scene_allocs, guide_allocs, wf_allocs;
+    // Device blocks released by the previous set_scene / set_guiding, keyed by size: a caller that re-stages inputs of
+    // the same shape every frame (bench.py's e2e leg, an animation) reuses them instead of paying cudaFree + cudaMalloc
+    // (each a device-wide synchronisation, 25-30 ms for the 67 MB cell grid).  Blocks not reused by the end of the call
+    // that could have reused them are returned to the driver (dev_trim).
+    std::multimap<size_t, void *> block_cache;
+    std::unordered_map<void *, size_t> block_size;
     DScene sc{};
     bool have_scene = false;
     Wavefront W{};
@@ -61,17 +69,37 @@ static int fail(vspg_ctx *c, int code, const char *fmt, ...) {
         if (e_ != cudaSuccess) return fail(ctx, VSPG_ERR_CUDA, "%s failed: %s", #call, cudaGetErrorString(e_)); \
     } while (0)
 
+static cudaError_t dev_alloc(vspg_ctx *ctx, std::vector<void *> &owner, void **p, size_t bytes) {
+    auto it = ctx->block_cache.find(bytes);
+    if (it != ctx->block_cache.end()) { *p = it->second; ctx->block_cache.erase(it); owner.push_back(*p); return cudaSuccess; }
+    cudaError_t e = cudaMalloc(p, bytes);
+    if (e != cudaSuccess) return e;
+    ctx->block_size[*p] = bytes;
+    owner.push_back(*p);
+    return e;
+}
 template <typename T>
-static cudaError_t upload(std::vector<void *> &owner, const T *host, size_t n, const T **dev) {
+static cudaError_t upload(vspg_ctx *ctx, std::vector<void *> &owner, const T *host, size_t n, const T **dev) {
     *dev = nullptr;
     if (n == 0) return cudaSuccess;
     void *p = nullptr;
-    cudaError_t e = cudaMalloc(&p, n * sizeof(T));
+    cudaError_t e = dev_alloc(ctx, owner, &p, n * sizeof(T));
     if (e != cudaSuccess) return e;
-    owner.push_back(p);
     e = cudaMemcpy(p, host, n * sizeof(T), cudaMemcpyHostToDevice);
     *dev = (const T *)p;
     return e;
+}
+// release: park the blocks in the cache;  trim: give whatever is still parked back to the driver
+static void dev_release(vspg_ctx *ctx, std::vector<void *> &v) {
+    for (void *p : v) {
+        auto it = ctx->block_size.find(p);
+        if (it == ctx->block_size.end()) cudaFree(p); else ctx->block_cache.emplace(it->second, p);
+    }
+    v.clear();
+}
+static void dev_trim(vspg_ctx *ctx) {
+    for (auto &kv : ctx->block_cache) { ctx->block_size.erase(kv.second); cudaFree(kv.second); }
+    ctx->block_cache.clear();
 }
 static void free_all(std::vector<void *> &v) { for (void *p : v) cudaFree(p); v.clear(); }
 
@@ -115,7 +143,7 @@ int vspg_create(vspg_ctx **out, int device_ordinal) {
 void vspg_destroy(vspg_ctx *ctx) {
     if (!ctx) return;
     cudaSetDevice(ctx->device);
-    free_all(ctx->scene_allocs); free_all(ctx->guide_allocs); free_all(ctx->wf_allocs);
+    dev_release(ctx, ctx->scene_allocs); dev_release(ctx, ctx->guide_allocs); dev_trim(ctx); free_all(ctx->wf_allocs);
     if (ctx->h_pinned) cudaFreeHost(ctx->h_pinned);
     for (auto e : ctx->ev) if (e) cudaEventDestroy(e);
     delete ctx;
@@ -134,8 +162,9 @@ int vspg_set_scene(vspg_ctx *ctx, const vspg_scene_desc *s) {
     if (s->camera.filter_type == 1 && (int(32 * s->camera.filter_radius[0]) < 1 || int(32 * s->camera.filter_radius[1]) < 1 || !(s->camera.filter_sigma > 0)))
         return fail(ctx, VSPG_ERR_INVALID, "set_scene: gaussian filter needs radius >= 1/32 and sigma > 0");
     if (s->camera.width <= 0 || s->camera.height <= 0) return fail(ctx, VSPG_ERR_INVALID, "set_scene: bad film resolution");
-    free_all(ctx->scene_allocs);
+    dev_release(ctx, ctx->scene_allocs);
     ctx->have_scene = false;
+    struct Trim { vspg_ctx *c; ~Trim() { dev_trim(c); } } trimOnExit{ctx};   // every return path drops the blocks this call did not reuse
     DScene &sc = ctx->sc;
     sc.cam = s->camera;
     // ---- media
@@ -155,30 +184,29 @@ int vspg_set_scene(vspg_ctx *ctx, const vspg_scene_desc *s) {
         if (nvox == 0 || m.maj_res[0] <= 0 || m.maj_res[1] <= 0 || m.maj_res[2] <= 0) return fail(ctx, VSPG_ERR_INVALID, "set_scene: medium %d has empty grid", i);
         if (m.type == VSPG_MEDIUM_GRID) {
             if (!m.density) return fail(ctx, VSPG_ERR_INVALID, "set_scene: medium %d has no density grid", i);
-            CK(upload(ctx->scene_allocs, m.density, nvox, &d.density));
+            CK(upload(ctx, ctx->scene_allocs, m.density, nvox, &d.density));
         } else {
-            if (m.sigma_a_rgb) CK(upload(ctx->scene_allocs, m.sigma_a_rgb, nvox * 3, &d.sa_rgb));
-            if (m.sigma_s_rgb) CK(upload(ctx->scene_allocs, m.sigma_s_rgb, nvox * 3, &d.ss_rgb));
+            if (m.sigma_a_rgb) CK(upload(ctx, ctx->scene_allocs, m.sigma_a_rgb, nvox * 3, &d.sa_rgb));
+            if (m.sigma_s_rgb) CK(upload(ctx, ctx->scene_allocs, m.sigma_s_rgb, nvox * 3, &d.ss_rgb));
         }
         size_t nmaj = (size_t)m.maj_res[0] * m.maj_res[1] * m.maj_res[2];
-        if (m.majorant) CK(upload(ctx->scene_allocs, m.majorant, nmaj, &d.majorant));
+        if (m.majorant) CK(upload(ctx, ctx->scene_allocs, m.majorant, nmaj, &d.majorant));
         else {
             std::vector<float> maj(nmaj);
             build_majorant_grid(&m, maj.data());
-            CK(upload(ctx->scene_allocs, maj.data(), nmaj, &d.majorant));
+            CK(upload(ctx, ctx->scene_allocs, maj.data(), nmaj, &d.majorant));
         }
         if (m.type == VSPG_MEDIUM_GRID && ctx->grid_layout == GRID_CELL8) {
             size_t ncell = (size_t)(m.nx + 1) * (m.ny + 1) * (m.nz + 1);
             void *cells = nullptr;
-            CK(cudaMalloc(&cells, ncell * 32));
-            ctx->scene_allocs.push_back(cells);
+            CK(dev_alloc(ctx, ctx->scene_allocs, &cells, ncell * 32));
             int blocks = (int)std::min<size_t>((ncell + 255) / 256, 148 * 32);
             k_build_cells<<<blocks, 256>>>(d.density, m.nx, m.ny, m.nz, (float4 *)cells);
             CK(cudaGetLastError());
             d.cells = (const float4 *)cells; d.layout = GRID_CELL8;
         }
     }
-    CK(upload(ctx->scene_allocs, media.data(), media.size(), &sc.media));
+    CK(upload(ctx, ctx->scene_allocs, media.data(), media.size(), &sc.media));
     sc.n_media = s->n_media;
     ctx->all_gray = !getenv("VSPG_NO_GRAY");
     for (const DMedium &d : media)
@@ -232,12 +260,12 @@ int vspg_set_scene(vspg_ctx *ctx, const vspg_scene_desc *s) {
         for (int k = 0; k < 4; k++)
             for (int a = 0; a < 3; a++) { bmin[a] = std::min(bmin[a], P[k][a]); bmax[a] = std::max(bmax[a], P[k][a]); }
     }
-    CK(upload(ctx->scene_allocs, quads.data(), quads.size(), &sc.quads));
+    CK(upload(ctx, ctx->scene_allocs, quads.data(), quads.size(), &sc.quads));
     sc.n_quads = nPrims;
     HostBvh bvh = build_bvh(hostPrims.data(), nPrims);
     static_assert(sizeof(HostBvhNode) == sizeof(DBvhNode) && sizeof(DBvhNode) == 48, "BVH node layout");
-    CK(upload(ctx->scene_allocs, (const DBvhNode *)bvh.nodes.data(), bvh.nodes.size(), &sc.bvh));
-    CK(upload(ctx->scene_allocs, bvh.prim_ids.data(), bvh.prim_ids.size(), &sc.prim_ids));
+    CK(upload(ctx, ctx->scene_allocs, (const DBvhNode *)bvh.nodes.data(), bvh.nodes.size(), &sc.bvh));
+    CK(upload(ctx, ctx->scene_allocs, bvh.prim_ids.data(), bvh.prim_ids.size(), &sc.prim_ids));
     sc.n_bvh = (int)bvh.nodes.size();
     // Bounds3::BoundingSphere of the aggregate bounds (lights' Preprocess)
     if (nPrims) {
@@ -248,7 +276,7 @@ int vspg_set_scene(vspg_ctx *ctx, const vspg_scene_desc *s) {
     // ---- materials, lights
     for (int i = 0; i < s->n_materials; i++)
         if (s->materials[i].type != VSPG_MATERIAL_DIFFUSE) return fail(ctx, VSPG_ERR_UNSUPPORTED, "set_scene: material %d: only diffuse is supported", i);
-    CK(upload(ctx->scene_allocs, s->materials, (size_t)s->n_materials, &sc.materials));
+    CK(upload(ctx, ctx->scene_allocs, s->materials, (size_t)s->n_materials, &sc.materials));
     sc.n_materials = s->n_materials;
     std::vector<DLight> lights(s->n_lights);
     std::vector<int> inf;
@@ -280,28 +308,28 @@ int vspg_set_scene(vspg_ctx *ctx, const vspg_scene_desc *s) {
     }
     if (sum == 0) { for (auto &p : power) p = 1.f; sum = (float)s->n_lights; }
     for (int i = 0; i < s->n_lights; i++) lights[i].pmf = power[i] / sum;
-    CK(upload(ctx->scene_allocs, lights.data(), lights.size(), &sc.lights));
-    CK(upload(ctx->scene_allocs, inf.data(), inf.size(), &sc.inf_lights));
+    CK(upload(ctx, ctx->scene_allocs, lights.data(), lights.size(), &sc.lights));
+    CK(upload(ctx, ctx->scene_allocs, inf.data(), inf.size(), &sc.inf_lights));
     sc.n_lights = s->n_lights; sc.n_inf_lights = (int)inf.size();
     {   // BVHLightSampler (the reference's default "lightsampler"), lightsamplers.cpp:107-236
         std::vector<float> primArea(nPrims);
         for (int i = 0; i < nPrims; i++) primArea[i] = quads[i].area;
         HostLightBvh lb = build_light_bvh(s, primArea.data());
         static_assert(sizeof(HostLightNode) == sizeof(DLightNode) && sizeof(DLightNode) == 64, "light BVH node layout");
-        CK(upload(ctx->scene_allocs, (const DLightNode *)lb.nodes.data(), lb.nodes.size(), &sc.lbvh));
-        CK(upload(ctx->scene_allocs, (const unsigned *)lb.bitTrail.data(), lb.bitTrail.size(), &sc.light_trail));
-        CK(upload(ctx->scene_allocs, lb.inTree.data(), lb.inTree.size(), &sc.light_in_tree));
-        CK(upload(ctx->scene_allocs, lb.infinite.data(), lb.infinite.size(), &sc.unbounded_lights));
+        CK(upload(ctx, ctx->scene_allocs, (const DLightNode *)lb.nodes.data(), lb.nodes.size(), &sc.lbvh));
+        CK(upload(ctx, ctx->scene_allocs, (const unsigned *)lb.bitTrail.data(), lb.bitTrail.size(), &sc.light_trail));
+        CK(upload(ctx, ctx->scene_allocs, lb.inTree.data(), lb.inTree.size(), &sc.light_in_tree));
+        CK(upload(ctx, ctx->scene_allocs, lb.infinite.data(), lb.infinite.size(), &sc.unbounded_lights));
         sc.n_lbvh = (int)lb.nodes.size(); sc.n_unbounded = (int)lb.infinite.size();
     }
     // ---- pixel filter
     sc.filt_nx = sc.filt_ny = 0; sc.filt_f = sc.filt_cond_cdf = sc.filt_cond_int = sc.filt_marg_cdf = nullptr; sc.filt_marg_int = 0;
     if (s->camera.filter_type == 1) {
         HostFilterTable T = build_gaussian_filter(s->camera.filter_radius[0], s->camera.filter_radius[1], s->camera.filter_sigma);
-        CK(upload(ctx->scene_allocs, T.f.data(), T.f.size(), &sc.filt_f));
-        CK(upload(ctx->scene_allocs, T.condCdf.data(), T.condCdf.size(), &sc.filt_cond_cdf));
-        CK(upload(ctx->scene_allocs, T.condInt.data(), T.condInt.size(), &sc.filt_cond_int));
-        CK(upload(ctx->scene_allocs, T.margCdf.data(), T.margCdf.size(), &sc.filt_marg_cdf));
+        CK(upload(ctx, ctx->scene_allocs, T.f.data(), T.f.size(), &sc.filt_f));
+        CK(upload(ctx, ctx->scene_allocs, T.condCdf.data(), T.condCdf.size(), &sc.filt_cond_cdf));
+        CK(upload(ctx, ctx->scene_allocs, T.condInt.data(), T.condInt.size(), &sc.filt_cond_int));
+        CK(upload(ctx, ctx->scene_allocs, T.margCdf.data(), T.margCdf.size(), &sc.filt_marg_cdf));
         sc.filt_nx = T.nx; sc.filt_ny = T.ny; sc.filt_marg_int = T.margInt;
     }
     // ---- film

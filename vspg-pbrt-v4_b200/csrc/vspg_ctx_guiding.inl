@@ -15,14 +15,14 @@ static int upload_field(vspg_ctx *ctx, const vspg_field *f, DField *d) {
             return fail(ctx, VSPG_ERR_INVALID, "set_guiding: region %d has %d lobes", i, f->regions[i].num_components);
     d->present = 1; d->usable = f->usable; d->n_nodes = f->n_nodes; d->n_regions = f->n_regions; d->stochastic_nn = f->stochastic_nn;
     for (int a = 0; a < 3; a++) { d->bmin[a] = f->bounds_min[a]; d->bmax[a] = f->bounds_max[a]; }
-    CK(upload(ctx->guide_allocs, f->nodes, (size_t)f->n_nodes, &d->nodes));
-    CK(upload(ctx->guide_allocs, f->regions, (size_t)f->n_regions, &d->regions));
+    CK(upload(ctx, ctx->guide_allocs, f->nodes, (size_t)f->n_nodes, &d->nodes));
+    CK(upload(ctx, ctx->guide_allocs, f->regions, (size_t)f->n_regions, &d->regions));
     if (f->neighbours) {
         for (int i = 0; i < f->n_regions; i++)
             for (int s = 0; s < 8; s++)
                 if (f->neighbours[i].ids[s] != ~0u && f->neighbours[i].ids[s] >= (uint32_t)f->n_regions)
                     return fail(ctx, VSPG_ERR_INVALID, "set_guiding: neighbour table of region %d is out of range", i);
-        CK(upload(ctx->guide_allocs, f->neighbours, (size_t)f->n_regions, &d->neigh));
+        CK(upload(ctx, ctx->guide_allocs, f->neighbours, (size_t)f->n_regions, &d->neigh));
     }
     return VSPG_OK;
 }
@@ -32,7 +32,8 @@ extern "C" {
 int vspg_set_guiding(vspg_ctx *ctx, const vspg_guiding_desc *g) {
     if (!ctx) return VSPG_ERR_INVALID;
     CK(cudaSetDevice(ctx->device));
-    free_all(ctx->guide_allocs);
+    dev_release(ctx, ctx->guide_allocs);
+    struct Trim { vspg_ctx *c; ~Trim() { dev_trim(c); } } trimOnExit{ctx};
     DScene &sc = ctx->sc;
     memset(&sc.surf, 0, sizeof sc.surf); memset(&sc.vol, 0, sizeof sc.vol);
     sc.hg_table = nullptr; sc.isg_vsp = nullptr; sc.tr_rgb = nullptr; sc.isg_w = sc.isg_h = sc.tr_w = sc.tr_h = 0;
@@ -49,18 +50,18 @@ int vspg_set_guiding(vspg_ctx *ctx, const vspg_guiding_desc *g) {
             for (int j = 0; j < 4; j++) { rows[i].w[j] = r[2 + j]; rows[i].mc[j] = r[6 + j]; rows[i].kappa[j] = r[10 + j]; rows[i].norm[j] = r[14 + j]; }
             if (rows[i].K < 0 || rows[i].K > 3) return fail(ctx, VSPG_ERR_INVALID, "HG table row %d has K=%d", i, rows[i].K);
         }
-        CK(upload(ctx->guide_allocs, rows.data(), rows.size(), &sc.hg_table));
+        CK(upload(ctx, ctx->guide_allocs, rows.data(), rows.size(), &sc.hg_table));
     }
     if (g->isg_vsp) {
         if (g->isg_width != sc.cam.width || g->isg_height != sc.cam.height)
             return fail(ctx, VSPG_ERR_INVALID, "set_guiding: ISG buffer is %dx%d but the film is %dx%d (call set_scene first)", g->isg_width, g->isg_height, sc.cam.width, sc.cam.height);
-        CK(upload(ctx->guide_allocs, g->isg_vsp, (size_t)g->isg_width * g->isg_height, &sc.isg_vsp));
+        CK(upload(ctx, ctx->guide_allocs, g->isg_vsp, (size_t)g->isg_width * g->isg_height, &sc.isg_vsp));
         sc.isg_w = g->isg_width; sc.isg_h = g->isg_height;
     }
     if (g->tr_rgb) {
         if (g->tr_width != sc.cam.width || g->tr_height != sc.cam.height)
             return fail(ctx, VSPG_ERR_INVALID, "set_guiding: Tr buffer is %dx%d but the film is %dx%d", g->tr_width, g->tr_height, sc.cam.width, sc.cam.height);
-        CK(upload(ctx->guide_allocs, g->tr_rgb, (size_t)g->tr_width * g->tr_height * 3, &sc.tr_rgb));
+        CK(upload(ctx, ctx->guide_allocs, g->tr_rgb, (size_t)g->tr_width * g->tr_height * 3, &sc.tr_rgb));
         sc.tr_w = g->tr_width; sc.tr_h = g->tr_height;
     }
     return VSPG_OK;
