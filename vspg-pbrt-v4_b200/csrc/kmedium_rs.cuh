@@ -138,7 +138,7 @@ VD void rs_finalize(const DScene &sc, const Wavefront &W, RsLane<GRAY> &s) {
     queue_push(W.surface, !dead && !scat, slot);
 }
 
-constexpr int kRsRefillIdle = 8;    // fetch new rays once this many lanes of the warp are idle
+constexpr int kRsRefillIdleDefault = 12;    // fetch new rays once this many lanes of the warp are idle (kernel argument: VSPG_RS_REFILL for A/B runs)
 constexpr int kRsTripsPerCheck = 4; // collisions between two refill checks
 constexpr int kRsSearchMax = 4;     // search steps before the collision body runs for the lanes that are ready
 
@@ -179,7 +179,7 @@ VD void rs_search_step(RsLane<GRAY> &s, float &t, bool &hit) {
 // collision ready; then the collision body, predicated on `hit`.  Bounding the search keeps both halves of the trip
 // above ~60 % lane utilisation (an unbounded search ran at 7 lanes of 32, profiles/r01c).
 template <bool GRAY, int MINB>
-__global__ void __launch_bounds__(kBlock, MINB) k_medium_rs(const DScene sc, const Wavefront W, int *cursor) {
+__global__ void __launch_bounds__(kBlock, MINB) k_medium_rs(const DScene sc, const Wavefront W, int *cursor, const int kRsRefillIdle) {
     typedef typename SpecT<GRAY>::type Sp;
     const int n = *W.medium_rs.count;
     const int lane = threadIdx.x & 31;
@@ -207,6 +207,7 @@ __global__ void __launch_bounds__(kBlock, MINB) k_medium_rs(const DScene sc, con
         }
         if (idle == kFull) { if (drained) break; else continue; }
         const int ch = s.ch;
+        bool flush = false;
 #pragma unroll 1
         for (int trip = 0; trip < kRsTripsPerCheck; trip++) {
             // ---- (1) advance towards the next tentative collision inside the medium (or the end of the ray)
@@ -275,10 +276,16 @@ __global__ void __launch_bounds__(kBlock, MINB) k_medium_rs(const DScene sc, con
             }
             // leave the trip loop once enough lanes have finished their walk (or are idle) to finalise / refill as a batch:
             // finalising one lane at a time cost 16 % of the kernel at 1.6 active lanes (profiles/r01j source page)
-            unsigned fin = __ballot_sync(kFull, !busy || (s.phase == RS_DONE && !pend));
-            if (__popc(fin) >= kRsRefillIdle) break;
+            // While the queue still has rays: flush when finished + idle lanes make up a refill batch.  Once it is
+            // drained nothing refills, so wait for a full batch of finished lanes or for the last walker (r01u: the
+            // unconditional flush after kRsTripsPerCheck trips still finalised 2 lanes at a time, 12 % of the samples).
+            const unsigned doneMask = __ballot_sync(kFull, busy && s.phase == RS_DONE && !pend);
+            const unsigned busyMask = __ballot_sync(kFull, busy);
+            flush = drained ? (__popc(doneMask) >= kRsRefillIdle || doneMask == busyMask)
+                            : (__popc(doneMask) + 32 - __popc(busyMask) >= kRsRefillIdle);
+            if (flush) break;
         }
-        if (busy && s.phase == RS_DONE && !pend) {
+        if (flush && busy && s.phase == RS_DONE && !pend) {
             tc.dda += s.it.steps;
             rs_finalize<GRAY>(sc, W, s);
             busy = false;

@@ -46,6 +46,7 @@ struct vspg_ctx {
     int grid_layout = GRID_CELL8;
     int scatter_block = 256;   // VSPG_SCATTER_BLOCK overrides (A/B runs)
     int rs_occ = 4;               // CTAs/SM the gray resampling kernel is compiled for (VSPG_RS_OCC=4|5, A/B runs)
+    int rs_refill = kRsRefillIdleDefault;   // VSPG_RS_REFILL overrides (A/B runs)
     bool all_gray = false;        // every medium has sigma_a / sigma_s equal across RGB => scalar tracking kernels (kmedium_rs.cuh)
     // timing (vspg_kernel_stats_get)
     bool timing = false;
@@ -133,6 +134,7 @@ int vspg_create(vspg_ctx **out, int device_ordinal) {
     vspg_integrator_defaults(&ctx->sc.ip);
     ctx->sc.ip.light_sampler = VSPG_LIGHTSAMPLER_UNIFORM;
     if (const char *sb = getenv("VSPG_SCATTER_BLOCK")) { int v = atoi(sb); if (v >= 32 && v <= kScatterBlock && v % 32 == 0) ctx->scatter_block = v; }
+    if (const char *rr = getenv("VSPG_RS_REFILL")) { int v = atoi(rr); if (v >= 1 && v <= 32) ctx->rs_refill = v; }
     if (const char *ro = getenv("VSPG_RS_OCC")) { int v = atoi(ro); if (v == 4 || v == 5) ctx->rs_occ = v; }
     const char *lay = getenv("VSPG_GRID_LAYOUT");
     if (lay && std::string(lay) == "linear") ctx->grid_layout = GRID_LINEAR;

@@ -89,9 +89,9 @@ int vspg_render(vspg_ctx *ctx, int spp_begin, int spp_end, int spp_stride, int x
     while (true) {
         if (timing) CK(cudaEventRecord(ctx->ev[0], st));
         VSPG_STAGE(VSPG_K_INTERSECT, (k_intersect<<<grid, kBlock, 0, st>>>(sc, W)));
-        if (ctx->all_gray && ctx->rs_occ == 5) k_medium_rs<true, 5><<<ctx->sm_count * 5, kBlock, 0, st>>>(sc, W, ctx->qcounts + Q_COUNT);
-        else if (ctx->all_gray) k_medium_rs<true, 4><<<ctx->sm_count * 4, kBlock, 0, st>>>(sc, W, ctx->qcounts + Q_COUNT);
-        else k_medium_rs<false, 4><<<ctx->sm_count * 4, kBlock, 0, st>>>(sc, W, ctx->qcounts + Q_COUNT);
+        if (ctx->all_gray && ctx->rs_occ == 5) k_medium_rs<true, 5><<<ctx->sm_count * 5, kBlock, 0, st>>>(sc, W, ctx->qcounts + Q_COUNT, ctx->rs_refill);
+        else if (ctx->all_gray) k_medium_rs<true, 4><<<ctx->sm_count * 4, kBlock, 0, st>>>(sc, W, ctx->qcounts + Q_COUNT, ctx->rs_refill);
+        else k_medium_rs<false, 4><<<ctx->sm_count * 4, kBlock, 0, st>>>(sc, W, ctx->qcounts + Q_COUNT, ctx->rs_refill);
         VSPG_STAGE(VSPG_K_MEDIUM, (k_medium<<<grid, kBlock, 0, st>>>(sc, W)));
         if (guidedVol) {
             k_lookup<false><<<grid, kBlock, 0, st>>>(sc, W, W.volscatter, W.vol8, W.vol16, W.vol32);
