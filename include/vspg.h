@@ -292,6 +292,9 @@ const vspg_integrator_params *vspg_host_scene_integrator(const vspg_host_scene *
 int vspg_host_scene_spp(const vspg_host_scene *s);        /* Sampler "pixelsamples"        */
 int vspg_host_scene_seed(const vspg_host_scene *s);       /* Sampler "seed" / Options seed */
 const char *vspg_host_scene_outfile(const vspg_host_scene *s); /* Film "filename"           */
+/* "storeTrBuffer" true: resolved "trBufferFileName" the caller writes after the render (vspg_tr_store_* +
+ * vspg_exr_write_channels, as `vspg-pbrt` does); "" otherwise. */
+const char *vspg_host_scene_store_tr_file(const vspg_host_scene *s);
 
 /* loaders, usable on their own (replace pglFieldLoadFromFile, ISGB/Tr EXR readers) */
 typedef struct vspg_host_field vspg_host_field;
@@ -304,6 +307,9 @@ const vspg_field *vspg_host_field_volume(const vspg_host_field *f);
 int vspg_exr_read_channel(const char *path, const char *channel, float **out, int *w, int *h,
                           char *err, size_t err_len); /* free with vspg_free */
 int vspg_exr_write_rgb(const char *path, const float *rgb, int w, int h, int as_half);
+/* Float ZIP EXR with n named channels, planes[i] = w*h floats of channel names[i] (TrBuffer::Store writes
+ * "Transmittance.R/G/B" this way, cpu/trbuffer.h:52-73). */
+int vspg_exr_write_channels(const char *path, int w, int h, int n, const char *const *names, const float *const *planes);
 void vspg_free(void *p);
 
 /* 16^3 majorant grid exactly as GridMedium / RGBGridMedium ctors build it
@@ -362,6 +368,14 @@ int vspg_debug_cache_lookup(vspg_ctx *ctx, int is_surface, int n, const float *p
  * -1, out_pmf[i] its pmf, out_pmf_of[i] = PMF(ctx, light_of[i]). */
 int vspg_debug_light_sample(vspg_ctx *ctx, int n, const float *pos3, const float *ns3, const float *u, const int *light_of,
                             int *out_light, float *out_pmf, float *out_pmf_of);
+
+/* storeTrBuffer (cpu/guidedvolpathvspgintegrator.cpp:190-193, 727-728; TrBuffer::AddSample cpu/trbuffer.h:40-45): between
+ * begin and end every depth-0 traversal of the resampling routine adds its ratio-tracking transmittance estimate
+ * (trRatioEst, RGB) to a per-pixel mean.  download returns the means (h*w*3 floats, 0 where a pixel has no sample)
+ * and, if out_count is not NULL, the per-pixel sample counts.  The film resolution is the scene's; begin clears. */
+int vspg_tr_store_begin(vspg_ctx *ctx);
+int vspg_tr_store_download(vspg_ctx *ctx, float *out_rgb, int *out_count);
+int vspg_tr_store_end(vspg_ctx *ctx);
 
 /* Integrator::Intersect (cpu/integrators.cpp:341-349 -> BVHAggregate::Intersect, cpu/aggregates.cpp:529-579) at n rays
  * (rays7 = o, d, tMax) followed by the shape's InteractionFromIntersection: out_prim[i] = primitive id counted over

@@ -176,6 +176,19 @@ def render(scene, guiding, ip, spp_begin, spp_end, spp_stride=1, window=None, se
     return film, dict(paths=cnt[0], density_queries=cnt[1], dda_steps=cnt[2], cache_lookups=cnt[3], shadow_rays=cnt[4])
 
 
+def render_tr(scene, guiding, ip, spp_begin, spp_end, seed=0, nthreads=1):
+    """Render with the storeTrBuffer pre-pass on: returns film, counters, tr_rgb [h, w, 3] float32, tr_spp [h, w] int32."""
+    cam = scene.desc.camera
+    film = np.zeros((cam.height, cam.width, 4), dtype=np.float64)
+    tr = np.zeros((cam.height, cam.width, 3), dtype=np.float32)
+    n = np.zeros((cam.height, cam.width), dtype=np.int32)
+    cnt = (C.c_longlong * 5)()
+    rc = lib().orc_render_ex(C.byref(scene.desc), _gp(guiding), C.byref(ip), spp_begin, spp_end, 1, 0, 0, cam.width, cam.height, int(seed),
+                             int(nthreads), film.ctypes.data_as(P), cnt, _fp(tr), n.ctypes.data_as(PI))
+    assert rc == 0, rc
+    return film, dict(paths=cnt[0], density_queries=cnt[1]), tr, n
+
+
 def camera_ray(scene, px, py, sample_index, seed=0):
     o, d, ch = np.zeros(3, np.float32), np.zeros(3, np.float32), C.c_int()
     lib().orc_camera_ray(C.byref(scene.desc), px, py, sample_index, seed, _fp(o), _fp(d), C.byref(ch))

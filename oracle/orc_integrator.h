@@ -639,6 +639,15 @@ struct Counters { long paths = 0, queries = 0, dda = 0, lookups = 0, shadow = 0;
 struct Integrator {
     const Scene *sc;
     Counters cnt;
+    // storeTrBuffer (vspg.cpp:190-193, 727-728; cpu/trbuffer.h:40-45): per-pixel running mean of the depth-0 ratio-tracking
+    // transmittance estimate.  Shared by the worker threads (each pixel is rendered by one thread, samples in order).
+    float *trBuf = nullptr; int *trSpp = nullptr;
+    void TrAddSample(int px, int py, S3 tr) {
+        int pixIdx = py * sc->d->camera.width + px;
+        trSpp[pixIdx] += 1;
+        float alpha = 1.f / trSpp[pixIdx];
+        for (int k = 0; k < 3; k++) trBuf[3 * pixIdx + k] = (1.f - alpha) * trBuf[3 * pixIdx + k] + alpha * tr[k];
+    }
 
     // ---------------------------------------------------------------- light sampling
     // ctxP / ctxNs: LightSampleContext::p() and ::ns of the vertex (ns = 0 in a medium)
@@ -1074,6 +1083,7 @@ struct Integrator {
             r_u_rs *= T_maj / T_maj[ch];
             cnt.queries += st.queries; cnt.dda += st.dda;
             if (ev) { ev->queries = (int)st.queries; ev->dda = (int)st.dda; }
+            if (ps.depth == 0 && trBuf) TrAddSample(px, py, trRatioEst);
             float trS = trRatioEst[ch];
             Cand surf; surf.p = ps.ray.at(tMax); surf.wi = trS; surf.sigmaTTrEst = trS; surf.num = beta_rs; surf.den = r_u_rs;
             if (guideScatterDecision && trS < 1 && trS > 0 && weightSum > 0) {

@@ -257,8 +257,17 @@ int orc_sample_distance(const vspg_scene_desc *scene, const vspg_guiding_desc *g
 
 // ------------------------------------------------------------- full render (ImageTileIntegrator::Render restated)
 // film_rgbw: H*W*4 doubles, accumulated into.  counters5: paths, queries, dda, lookups, shadow.
+int orc_render_ex(const vspg_scene_desc *scene, const vspg_guiding_desc *g, const vspg_integrator_params *ip, int spp_begin, int spp_end,
+                  int spp_stride, int x0, int y0, int x1, int y1, int seed, int nthreads, double *film_rgbw, long long *counters5,
+                  float *tr_rgb, int *tr_spp);
 int orc_render(const vspg_scene_desc *scene, const vspg_guiding_desc *g, const vspg_integrator_params *ip, int spp_begin, int spp_end,
                int spp_stride, int x0, int y0, int x1, int y1, int seed, int nthreads, double *film_rgbw, long long *counters5) {
+    return orc_render_ex(scene, g, ip, spp_begin, spp_end, spp_stride, x0, y0, x1, y1, seed, nthreads, film_rgbw, counters5, nullptr, nullptr);
+}
+// tr_rgb [h*w*3] / tr_spp [h*w] (zero-initialised by the caller, or carrying earlier passes): the storeTrBuffer pre-pass
+int orc_render_ex(const vspg_scene_desc *scene, const vspg_guiding_desc *g, const vspg_integrator_params *ip, int spp_begin, int spp_end,
+                  int spp_stride, int x0, int y0, int x1, int y1, int seed, int nthreads, double *film_rgbw, long long *counters5,
+                  float *tr_rgb, int *tr_spp) {
     if ((ip->volume_guiding || ip->vsp_secondary_guiding) && g && g->volume && !g_hg_table_set) return -2;
     Scene sc; sc.init(scene, g, ip, true); sc.seed = seed;
     if (nthreads < 1) nthreads = 1;
@@ -268,6 +277,7 @@ int orc_render(const vspg_scene_desc *scene, const vspg_guiding_desc *g, const v
     long long tot[5] = {0, 0, 0, 0, 0};
     auto worker = [&]() {
         Integrator integ; integ.sc = &sc;
+        if (tr_rgb && tr_spp) { integ.trBuf = tr_rgb; integ.trSpp = tr_spp; }
         while (true) {
             int y = nextRow.fetch_add(1);
             if (y >= y1) break;

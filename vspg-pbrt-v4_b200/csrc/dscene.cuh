@@ -90,6 +90,7 @@ struct DScene {
     const DHGRow *hg_table;   // 128 rows
     const float *isg_vsp; int isg_w, isg_h;
     const float *tr_rgb; int tr_w, tr_h;
+    double *tr_acc;      // storeTrBuffer accumulators {sumR, sumG, sumB, count} per pixel, or null (vspg_tr_store_begin)
     // PixelFilter "gaussian" sampling table (host_util.h build_gaussian_filter); filt_nx == 0 for the box filter
     int filt_nx, filt_ny; const float *filt_f, *filt_cond_cdf, *filt_cond_int, *filt_marg_cdf; float filt_marg_int;
     vspg_integrator_params ip;

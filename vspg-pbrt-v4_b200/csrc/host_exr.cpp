@@ -175,8 +175,31 @@ int vspg_exr_read_channel(const char *path, const char *channel, float **out, in
     return VSPG_OK;
 }
 
+namespace {
+struct ExrChan { std::string name; const float *base; size_t stride; };   // value(x, y) = base[stride * (y * w + x)]
+}
+static int write_exr_channels(const char *path, std::vector<ExrChan> chans, int w, int h, int as_half);
+
 int vspg_exr_write_rgb(const char *path, const float *rgb, int w, int h, int as_half) {
     if (!path || !rgb || w <= 0 || h <= 0) return VSPG_ERR_INVALID;
+    return write_exr_channels(path, {{"R", rgb, 3}, {"G", rgb + 1, 3}, {"B", rgb + 2, 3}}, w, h, as_half);
+}
+
+int vspg_exr_write_channels(const char *path, int w, int h, int n, const char *const *names, const float *const *planes) {
+    if (!path || w <= 0 || h <= 0 || n <= 0 || !names || !planes) return VSPG_ERR_INVALID;
+    std::vector<ExrChan> chans;
+    for (int i = 0; i < n; i++) {
+        if (!names[i] || !names[i][0] || !planes[i]) return VSPG_ERR_INVALID;
+        chans.push_back({names[i], planes[i], 1});
+    }
+    return write_exr_channels(path, chans, w, h, 0);
+}
+
+}  // extern "C"
+
+static int write_exr_channels(const char *path, std::vector<ExrChan> chans, int w, int h, int as_half) {
+    std::sort(chans.begin(), chans.end(), [](const ExrChan &a, const ExrChan &b) { return a.name < b.name; });   // chlist is alphabetical
+    const int nch = (int)chans.size();
     std::vector<unsigned char> hdr;
     auto put = [&](const void *p, size_t n) { const unsigned char *q = (const unsigned char *)p; hdr.insert(hdr.end(), q, q + n); };
     auto puts0 = [&](const char *s) { put(s, strlen(s) + 1); };
@@ -184,10 +207,10 @@ int vspg_exr_write_rgb(const char *path, const float *rgb, int w, int h, int as_
     auto putf = [&](float v) { put(&v, 4); };
     puti(20000630); puti(2);
     const int ptype = as_half ? 1 : 2;
-    {   // channels (alphabetical: B, G, R)
+    {
         std::vector<unsigned char> cl;
-        for (const char *n : {"B", "G", "R"}) {
-            cl.push_back((unsigned char)n[0]); cl.push_back(0);
+        for (const ExrChan &c : chans) {
+            cl.insert(cl.end(), c.name.begin(), c.name.end()); cl.push_back(0);
             int32_t v = ptype; cl.insert(cl.end(), (unsigned char *)&v, (unsigned char *)&v + 4);
             cl.insert(cl.end(), {0, 0, 0, 0});
             v = 1; cl.insert(cl.end(), (unsigned char *)&v, (unsigned char *)&v + 4); cl.insert(cl.end(), (unsigned char *)&v, (unsigned char *)&v + 4);
@@ -205,16 +228,16 @@ int vspg_exr_write_rgb(const char *path, const float *rgb, int w, int h, int as_
     puts0("screenWindowWidth"); puts0("float"); puti(4); putf(1.f);
     { unsigned char z = 0; put(&z, 1); }
     const int nBlocks = (h + 15) / 16;
-    const size_t bpp = as_half ? 2 : 4, lineBytes = 3 * bpp * w;
+    const size_t bpp = as_half ? 2 : 4, lineBytes = nch * bpp * w;
     std::vector<std::vector<unsigned char>> chunks(nBlocks);
     for (int b = 0; b < nBlocks; b++) {
         int y0 = b * 16, lines = std::min(16, h - y0);
         std::vector<unsigned char> raw(lineBytes * lines);
         for (int l = 0; l < lines; l++)
-            for (int ch = 0; ch < 3; ch++) {       // file order B, G, R  <- rgb index 2, 1, 0
+            for (int ch = 0; ch < nch; ch++) {
                 unsigned char *dst = raw.data() + lineBytes * l + (size_t)ch * bpp * w;
                 for (int x = 0; x < w; x++) {
-                    float v = rgb[3 * ((size_t)(y0 + l) * w + x) + (2 - ch)];
+                    float v = chans[ch].base[chans[ch].stride * ((size_t)(y0 + l) * w + x)];
                     if (as_half) { uint16_t hv = float_to_half(v); memcpy(dst + 2 * x, &hv, 2); }
                     else memcpy(dst + 4 * x, &v, 4);
                 }
@@ -239,5 +262,3 @@ int vspg_exr_write_rgb(const char *path, const float *rgb, int w, int h, int as_
     ok = (fclose(fp) == 0) && ok;
     return ok ? VSPG_OK : VSPG_ERR_IO;
 }
-
-}  // extern "C"

@@ -333,7 +333,8 @@ struct vspg_host_scene {
     double fov = 90, lens_radius = 0, focal_distance = 1e6, frame_aspect = -1; std::vector<double> screen_window;
     int xres = 1280, yres = 720; float iso = 100, exposure = 1, max_comp = INFINITY;
     int filter_type = 1; float filter_r[2] = {1.5f, 1.5f}, filter_sigma = 0.5f;   // pbrt's default filter is "gaussian"
-    std::string guiding_cache_file, isg_file, tr_file; bool load_cache = false, load_isg = false, load_tr = false;
+    std::string guiding_cache_file, isg_file, tr_file; bool load_cache = false, load_isg = false, load_tr = false, store_tr = false;
+    std::string store_tr_path;
     ~vspg_host_scene() { if (field) vspg_host_field_free(field); if (isg) vspg_free(isg); if (tr) vspg_free(tr); }
 };
 
@@ -437,7 +438,7 @@ struct Builder {
         bool store_isg = ps.one_bool("storeISGBuffer", false);
         S.load_isg = ps.one_bool("loadISGBuffer", false);
         S.isg_file = ps.one_string("isgBufferFileName", "");
-        bool store_tr = ps.one_bool("storeTrBuffer", false);
+        S.store_tr = ps.one_bool("storeTrBuffer", false);
         S.load_tr = ps.one_bool("loadTrBuffer", false);
         S.tr_file = ps.one_string("trBufferFileName", "");
         // guided RR needs OPENPGL_RADIANCE_CACHES, which the reference builds OFF: the flags are inert.
@@ -449,9 +450,13 @@ struct Builder {
         else lx.fail("Integrator: lightsampler \"" + ls + "\" unknown");
         ip.regularize = ps.one_bool("regularize", false);
         ps.report_unused();
-        if (store_cache || store_isg || store_tr)
-            lx.fail("Integrator: storeGuidingCache / storeISGBuffer / storeTrBuffer request a training pass; this library "
-                    "renders with frozen, loaded inputs only (guiding-cache training is out of scope)", VSPG_ERR_UNSUPPORTED);
+        if (store_cache || store_isg)
+            lx.fail("Integrator: storeGuidingCache / storeISGBuffer request a training pass; this library renders with frozen, "
+                    "loaded inputs only (guiding-cache training is out of scope; storeTrBuffer is supported)", VSPG_ERR_UNSUPPORTED);
+        if (S.store_tr) {   // vspg.cpp:190-193, 219-221: the Tr buffer is accumulated by the render itself and written afterwards
+            if (S.tr_file.empty()) lx.fail("Integrator: storeTrBuffer without trBufferFileName");
+            if (S.load_tr) lx.fail("Integrator: storeTrBuffer together with loadTrBuffer (the reference would only re-write the loaded file)", VSPG_ERR_UNSUPPORTED);
+        }
         S.have_integrator = true;
     }
 
@@ -908,6 +913,7 @@ void finish(vspg_host_scene &S) {
         S.guiding.isg_vsp = S.isg; S.guiding.isg_width = w; S.guiding.isg_height = h;
         S.has_guiding = true;
     }
+    if (S.store_tr) S.store_tr_path = S.tr_file[0] == '/' ? S.tr_file : S.base_dir + "/" + S.tr_file;
     if (S.load_tr) {
         if (S.tr_file.empty()) throw ParseError(VSPG_ERR_INVALID, "Integrator: loadTrBuffer without trBufferFileName");
         std::string p = S.tr_file[0] == '/' ? S.tr_file : S.base_dir + "/" + S.tr_file;
@@ -973,5 +979,6 @@ const vspg_integrator_params *vspg_host_scene_integrator(const vspg_host_scene *
 int vspg_host_scene_spp(const vspg_host_scene *s) { return s ? s->spp : 0; }
 int vspg_host_scene_seed(const vspg_host_scene *s) { return s ? s->seed : 0; }
 const char *vspg_host_scene_outfile(const vspg_host_scene *s) { return s ? s->outfile.c_str() : ""; }
+const char *vspg_host_scene_store_tr_file(const vspg_host_scene *s) { return s ? s->store_tr_path.c_str() : ""; }
 
 }  // extern "C"

@@ -98,6 +98,14 @@ VD void rs_finalize(const DScene &sc, const Wavefront &W, RsLane<GRAY> &s) {
     Sp T_maj = s.T_maj;
     s.beta_rs = s.beta_rs * (T_maj / T_maj[ch]);
     s.r_u_rs = s.r_u_rs * (T_maj / T_maj[ch]);
+    if (sc.tr_acc) {   // vspg.cpp:727-728: depth == 0 && calculateTrBuffer -> TrBuffer::AddSample(pPixel, trRatioEst RGB)
+        PathFlags fl0 = PathFlags::unpack(__float_as_int(W.P.d_med[slot].w));
+        if (fl0.depth == 0) {
+            V3 tr = to_v3(s.trRatioEst);
+            double *acc = sc.tr_acc + 4 * (size_t)__float_as_int(W.P.misc2[slot].y);
+            atomicAdd(acc, (double)tr.x); atomicAdd(acc + 1, (double)tr.y); atomicAdd(acc + 2, (double)tr.z); atomicAdd(acc + 3, 1.0);
+        }
+    }
     float trS = s.trRatioEst[ch];
     float surfWi = trS;
     if (s.guide && trS < 1 && trS > 0 && s.weightSum > 0) {

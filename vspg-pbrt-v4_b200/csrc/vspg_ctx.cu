@@ -40,6 +40,7 @@ struct vspg_ctx {
     int *qcounts = nullptr;       // device: 8 queue counters
     int *h_pinned = nullptr;      // pinned readback
     double *film = nullptr;
+    double *tr_acc = nullptr; size_t tr_acc_pixels = 0;   // storeTrBuffer accumulators (vspg_tr_store_*)
     unsigned long long *counters = nullptr;
     unsigned long long launches = 0, iterations = 0;
     int film_w = 0, film_h = 0;
@@ -79,6 +80,8 @@ static cudaError_t dev_alloc(vspg_ctx *ctx, std::vector<void *> &owner, void **p
     owner.push_back(*p);
     return e;
 }
+#define CK_STATE(cond, msg) do { if (!(cond)) return fail(ctx, VSPG_ERR_STATE, msg); } while (0)
+
 template <typename T>
 static cudaError_t upload(vspg_ctx *ctx, std::vector<void *> &owner, const T *host, size_t n, const T **dev) {
     *dev = nullptr;
@@ -147,6 +150,9 @@ void vspg_destroy(vspg_ctx *ctx) {
     cudaSetDevice(ctx->device);
     dev_release(ctx, ctx->scene_allocs); dev_release(ctx, ctx->guide_allocs); dev_trim(ctx); free_all(ctx->wf_allocs);
     if (ctx->h_pinned) cudaFreeHost(ctx->h_pinned);
+    if (ctx->film) cudaFree(ctx->film);
+    if (ctx->tr_acc) cudaFree(ctx->tr_acc);
+    if (ctx->counters) cudaFree(ctx->counters);
     for (auto e : ctx->ev) if (e) cudaEventDestroy(e);
     delete ctx;
 }
@@ -166,6 +172,7 @@ int vspg_set_scene(vspg_ctx *ctx, const vspg_scene_desc *s) {
     if (s->camera.width <= 0 || s->camera.height <= 0) return fail(ctx, VSPG_ERR_INVALID, "set_scene: bad film resolution");
     dev_release(ctx, ctx->scene_allocs);
     ctx->have_scene = false;
+    ctx->sc.tr_acc = nullptr;   // a Tr store belongs to one scene (resolution): vspg_tr_store_begin again after set_scene
     struct Trim { vspg_ctx *c; ~Trim() { dev_trim(c); } } trimOnExit{ctx};   // every return path drops the blocks this call did not reuse
     DScene &sc = ctx->sc;
     sc.cam = s->camera;

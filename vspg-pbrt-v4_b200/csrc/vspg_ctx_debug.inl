@@ -11,7 +11,6 @@ struct DevBuf {
 };
 }  // namespace
 
-#define CK_STATE(cond, msg) do { if (!(cond)) return fail(ctx, VSPG_ERR_STATE, msg); } while (0)
 
 extern "C" {
 

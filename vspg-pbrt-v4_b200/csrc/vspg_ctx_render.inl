@@ -143,6 +143,40 @@ int vspg_film_clear(vspg_ctx *ctx) {
     CK(cudaMemset(ctx->film, 0, (size_t)ctx->film_w * ctx->film_h * 4 * sizeof(double)));
     return VSPG_OK;
 }
+int vspg_tr_store_begin(vspg_ctx *ctx) {
+    if (!ctx) return VSPG_ERR_INVALID;
+    CK_STATE(ctx->have_scene && ctx->film, "tr_store_begin: set_scene has not been called");
+    CK(cudaSetDevice(ctx->device));
+    const size_t bytes = (size_t)ctx->film_w * ctx->film_h * 4 * sizeof(double);
+    if (!ctx->tr_acc || ctx->tr_acc_pixels != (size_t)ctx->film_w * ctx->film_h) {
+        if (ctx->tr_acc) cudaFree(ctx->tr_acc);
+        ctx->tr_acc = nullptr;
+        CK(cudaMalloc((void **)&ctx->tr_acc, bytes));
+        ctx->tr_acc_pixels = (size_t)ctx->film_w * ctx->film_h;
+    }
+    CK(cudaMemset(ctx->tr_acc, 0, bytes));
+    ctx->sc.tr_acc = ctx->tr_acc;
+    return VSPG_OK;
+}
+int vspg_tr_store_download(vspg_ctx *ctx, float *out_rgb, int *out_count) {
+    if (!ctx || !out_rgb) return VSPG_ERR_INVALID;
+    CK_STATE(ctx->sc.tr_acc != nullptr, "tr_store_download: tr_store_begin has not been called");
+    CK(cudaSetDevice(ctx->device));
+    const size_t n = ctx->tr_acc_pixels;
+    std::vector<double> acc(4 * n);
+    CK(cudaMemcpy(acc.data(), ctx->tr_acc, acc.size() * sizeof(double), cudaMemcpyDeviceToHost));
+    for (size_t i = 0; i < n; i++) {
+        double c = acc[4 * i + 3];
+        for (int k = 0; k < 3; k++) out_rgb[3 * i + k] = c > 0 ? (float)(acc[4 * i + k] / c) : 0.f;
+        if (out_count) out_count[i] = (int)c;
+    }
+    return VSPG_OK;
+}
+int vspg_tr_store_end(vspg_ctx *ctx) {
+    if (!ctx) return VSPG_ERR_INVALID;
+    ctx->sc.tr_acc = nullptr;
+    return VSPG_OK;
+}
 int vspg_film_device_ptr(vspg_ctx *ctx, double **rgbw, size_t *n_doubles) {
     if (!ctx || !ctx->film || !rgbw) return VSPG_ERR_STATE;
     *rgbw = ctx->film;

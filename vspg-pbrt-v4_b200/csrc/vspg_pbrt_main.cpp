@@ -56,12 +56,23 @@ int main(int argc, char **argv) {
     ck(vspg_set_guiding(ctx, vspg_host_scene_guiding(hs)), "set_guiding");
     ck(vspg_set_integrator(ctx, vspg_host_scene_integrator(hs)), "set_integrator");
     int W = sd->camera.width, H = sd->camera.height;
+    const std::string trStore = vspg_host_scene_store_tr_file(hs);   // "storeTrBuffer" (vspg.cpp:190-193, 219-221)
+    if (!trStore.empty()) ck(vspg_tr_store_begin(ctx), "tr_store_begin");
     auto t0 = std::chrono::steady_clock::now();
     ck(vspg_render(ctx, 0, spp, 1, 0, 0, W, H, seed, nullptr), "render");
     std::vector<float> rgb((size_t)W * H * 3);
     ck(vspg_film_resolve(ctx, rgb.data()), "film_resolve");
     double sec = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
     if (vspg_exr_write_rgb(outfile.c_str(), rgb.data(), W, H, fp32 ? 0 : 1) != VSPG_OK) { fprintf(stderr, "vspg-pbrt: cannot write %s\n", outfile.c_str()); return 1; }
+    if (!trStore.empty()) {   // TrBuffer::Store (cpu/trbuffer.h:52-73): float EXR, channels Transmittance.R/G/B
+        std::vector<float> tr((size_t)W * H * 3), planes[3];
+        ck(vspg_tr_store_download(ctx, tr.data(), nullptr), "tr_store_download");
+        for (int k = 0; k < 3; k++) { planes[k].resize((size_t)W * H); for (size_t i = 0; i < (size_t)W * H; i++) planes[k][i] = tr[3 * i + k]; }
+        const char *names[3] = {"Transmittance.R", "Transmittance.G", "Transmittance.B"};
+        const float *pp[3] = {planes[0].data(), planes[1].data(), planes[2].data()};
+        if (vspg_exr_write_channels(trStore.c_str(), W, H, 3, names, pp) != VSPG_OK) { fprintf(stderr, "vspg-pbrt: cannot write %s\n", trStore.c_str()); return 1; }
+        if (!quiet) printf("vspg-pbrt: transmittance buffer -> %s\n", trStore.c_str());
+    }
     if (!quiet) {
         vspg_counters c;
         vspg_counters_get(ctx, &c);

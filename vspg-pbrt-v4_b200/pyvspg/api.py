@@ -168,6 +168,19 @@ class Context:
                                                _fp(pmf), _fp(pmf_of)))
         return light, pmf, pmf_of
 
+    def tr_store_begin(self):
+        self._ck(lib().vspg_tr_store_begin(self._h))
+
+    def tr_store_download(self):
+        """(mean transmittance [h, w, 3] float32, sample counts [h, w] int32) of the storeTrBuffer pre-pass."""
+        rgb = np.zeros((self.height, self.width, 3), np.float32)
+        cnt = np.zeros((self.height, self.width), np.int32)
+        self._ck(lib().vspg_tr_store_download(self._h, _fp(rgb), cnt.ctypes.data_as(C.POINTER(A.i32))))
+        return rgb, cnt
+
+    def tr_store_end(self):
+        self._ck(lib().vspg_tr_store_end(self._h))
+
     def debug_intersect(self, rays7):
         rays7 = np.ascontiguousarray(rays7, dtype=np.float32).reshape(-1, 7)
         n = rays7.shape[0]
@@ -213,6 +226,7 @@ class HostScene:
         self.spp = lib().vspg_host_scene_spp(self._h)
         self.seed = lib().vspg_host_scene_seed(self._h)
         self.outfile = lib().vspg_host_scene_outfile(self._h).decode()
+        self.store_tr_file = lib().vspg_host_scene_store_tr_file(self._h).decode()   # "" unless "storeTrBuffer" true
 
     def close(self):
         if self._h:
@@ -247,6 +261,18 @@ def exr_read_channel(path, channel):
 def exr_write_rgb(path, rgb, as_half=False):
     rgb = np.ascontiguousarray(rgb, dtype=np.float32)
     rc = lib().vspg_exr_write_rgb(str(path).encode(), _fp(rgb), rgb.shape[1], rgb.shape[0], int(as_half))
+    if rc != 0:
+        raise VspgError(rc, f"cannot write {path}")
+
+
+def exr_write_channels(path, channels):
+    """channels: {name: [h, w] float array}; float ZIP EXR (the layout TrBuffer::Store writes)."""
+    names = list(channels)
+    planes = [np.ascontiguousarray(channels[n], dtype=np.float32) for n in names]
+    h, w = planes[0].shape
+    cn = (C.c_char_p * len(names))(*[n.encode() for n in names])
+    cp = (A.PF * len(names))(*[_fp(p) for p in planes])
+    rc = lib().vspg_exr_write_channels(str(path).encode(), w, h, len(names), cn, cp)
     if rc != 0:
         raise VspgError(rc, f"cannot write {path}")
 
