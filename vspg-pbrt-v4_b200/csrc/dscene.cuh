@@ -98,27 +98,36 @@ struct DScene {
 };
 
 // ------------------------------------------------------------------ wavefront state (SoA, one slot per path in flight)
+// One float4 stream of the path state.  Slots are visited in queue order, i.e. at random, and a DRAM/L2 sector is 32 B:
+// a lone 16-byte element wastes half of every sector it touches (k_surface moved 375 MB per launch for 190 MB of state,
+// profiles/r01j).  Streams that are always read or written together therefore share 32-byte records (STRIDE 2, OFF 0/1);
+// the accessor keeps the `P.name[slot]` spelling of a plain array.
+template <int STRIDE, int OFF>
+struct F4S {
+    float4 *base;
+    __device__ __forceinline__ float4 &operator[](int s) const { return base[(size_t)s * STRIDE + OFF]; }
+};
 struct PathSoA {
-    float4 *o_dx;        // ray.o xyz, d.x
-    float4 *d_med;       // d.y d.z, medium(int), packed flags(int)
-    float4 *beta_ru;     // beta xyz, r_u.x
-    float4 *ru_rl;       // r_u.y r_u.z r_l.x r_l.y
-    float4 *rl_L;        // r_l.z, L xyz
+    F4S<2, 0> o_dx;      // ray.o xyz, d.x
+    F4S<2, 1> d_med;     // d.y d.z, medium(int), packed flags(int)
+    F4S<2, 0> beta_ru;   // beta xyz, r_u.x
+    F4S<2, 1> ru_rl;     // r_u.y r_u.z r_l.x r_l.y
+    F4S<2, 0> rl_L;      // r_l.z, L xyz
     ulonglong2 *rng;     // sampler PCG32 state, inc
-    float4 *misc;        // rr_correction, vsp_next, prevCtx.p.x, prevCtx.p.y
-    float4 *misc2;       // prevCtx.p.z, pixel(int), sampleIndex(int), unused
+    F4S<2, 1> misc;      // rr_correction, vsp_next, prevCtx.p.x, prevCtx.p.y
+    F4S<2, 0> misc2;     // prevCtx.p.z, pixel(int), sampleIndex(int), unused
     float4 *hit;         // t, u, v, prim(int)  (prim < 0: no hit)
     float4 *ev;          // medium scatter event: p xyz, g
     // shadow-ray record emitted by the scatter kernels
-    float4 *sh_o;        // o xyz, d.x
-    float4 *sh_d;        // d.y d.z, medium(int), flags(int: bit0 delta light, bits 8.. channel)
-    float4 *sh_c;        // contribution  beta*f_hat*L  xyz, unused
-    float4 *sh_rl;       // r_p*p_l xyz, unused
-    float4 *sh_ru;       // r_p*scatterPDF xyz, unused
-    float4 *sh_pl;       // pLight xyz, nLight.x
+    F4S<2, 0> sh_o;      // o xyz, d.x
+    F4S<2, 1> sh_d;      // d.y d.z, medium(int), flags(int: bit0 delta light, bits 8.. channel)
+    F4S<2, 0> sh_c;      // contribution  beta*f_hat*L  xyz, unused
+    F4S<2, 1> sh_rl;     // r_p*p_l xyz, unused
+    F4S<2, 0> sh_ru;     // r_p*scatterPDF xyz, unused
+    F4S<2, 1> sh_pl;     // pLight xyz, nLight.x
     float4 *sh_ple;      // pLightErr xyz, nLight.y
     float *sh_nz;        // nLight.z
-    float4 *prev_ns;     // shading normal of the previous vertex (0 for a medium vertex): LightSampleContext::ns for the emission MIS
+    F4S<2, 1> prev_ns;   // (shares records with misc2) shading normal of the previous vertex (0 for a medium vertex): LightSampleContext::ns for the emission MIS
     int *lk;             // guiding-cache region chosen by k_lookup for the pending scatter vertex (-1 = none)
     float2 *rs_pre;      // resampling pre-pass (media_sampleTMaj.h:153-164): sum of sigma_maj[ch]*dt, DDA steps(int)
 };
