@@ -107,26 +107,29 @@ struct F4S {
     float4 *base;
     __device__ __forceinline__ float4 &operator[](int s) const { return base[(size_t)s * STRIDE + OFF]; }
 };
+struct RngS {   // the sampler state shares 32-byte records with the hit record (both are read at every surface vertex)
+    float4 *base;
+    __device__ __forceinline__ ulonglong2 &operator[](int s) const { return reinterpret_cast<ulonglong2 *>(base)[(size_t)s * 2]; }
+};
 struct PathSoA {
     F4S<2, 0> o_dx;      // ray.o xyz, d.x
     F4S<2, 1> d_med;     // d.y d.z, medium(int), packed flags(int)
     F4S<2, 0> beta_ru;   // beta xyz, r_u.x
     F4S<2, 1> ru_rl;     // r_u.y r_u.z r_l.x r_l.y
     F4S<2, 0> rl_L;      // r_l.z, L xyz
-    ulonglong2 *rng;     // sampler PCG32 state, inc
+    RngS rng;            // sampler PCG32 state, inc
     F4S<2, 1> misc;      // rr_correction, vsp_next, prevCtx.p.x, prevCtx.p.y
     F4S<2, 0> misc2;     // prevCtx.p.z, pixel(int), sampleIndex(int), unused
-    float4 *hit;         // t, u, v, prim(int)  (prim < 0: no hit)
+    F4S<2, 1> hit;       // t, u, v, prim(int)  (prim < 0: no hit)
     float4 *ev;          // medium scatter event: p xyz, g
     // shadow-ray record emitted by the scatter kernels
     F4S<2, 0> sh_o;      // o xyz, d.x
     F4S<2, 1> sh_d;      // d.y d.z, medium(int), flags(int: bit0 delta light, bits 8.. channel)
     F4S<2, 0> sh_c;      // contribution  beta*f_hat*L  xyz, unused
     F4S<2, 1> sh_rl;     // r_p*p_l xyz, unused
-    F4S<2, 0> sh_ru;     // r_p*scatterPDF xyz, unused
+    F4S<2, 0> sh_ru;     // r_p*scatterPDF xyz, nLight.z
     F4S<2, 1> sh_pl;     // pLight xyz, nLight.x
     float4 *sh_ple;      // pLightErr xyz, nLight.y
-    float *sh_nz;        // nLight.z
     F4S<2, 1> prev_ns;   // (shares records with misc2) shading normal of the previous vertex (0 for a medium vertex): LightSampleContext::ns for the emission MIS
     int *lk;             // guiding-cache region chosen by k_lookup for the pending scatter vertex (-1 = none)
     float2 *rs_pre;      // resampling pre-pass (media_sampleTMaj.h:153-164): sum of sigma_maj[ch]*dt, DDA steps(int)

@@ -103,10 +103,9 @@ VD void shadow_store(const PathSoA &P, int s, const ShadowRec &r) {
     P.sh_d[s] = make_float4(r.d.y, r.d.z, __int_as_float(r.medium), __int_as_float((r.delta ? 1 : 0) | (r.channel << 8)));
     P.sh_c[s] = make_float4(r.contrib.x, r.contrib.y, r.contrib.z, 0);
     P.sh_rl[s] = make_float4(r.rl.x, r.rl.y, r.rl.z, 0);
-    P.sh_ru[s] = make_float4(r.ru.x, r.ru.y, r.ru.z, 0);
+    P.sh_ru[s] = make_float4(r.ru.x, r.ru.y, r.ru.z, r.nLight.z);
     P.sh_pl[s] = make_float4(r.pLight.x, r.pLight.y, r.pLight.z, r.nLight.x);
     P.sh_ple[s] = make_float4(r.pLightErr.x, r.pLightErr.y, r.pLightErr.z, r.nLight.y);
-    P.sh_nz[s] = r.nLight.z;
 }
 
 // Next-event light sample drawn ahead of the lane-group scatter kernels.  The light pick and Light::SampleLi are
@@ -134,7 +133,7 @@ VD void nee_store(const PathSoA &P, int s, const NeePre &n) {
     P.sh_c[s] = make_float4(n.L.x, n.L.y, n.L.z, n.p_l);
     P.sh_pl[s] = make_float4(n.pLight.x, n.pLight.y, n.pLight.z, n.nLight.x);
     P.sh_ple[s] = make_float4(n.pLightErr.x, n.pLightErr.y, n.pLightErr.z, n.nLight.y);
-    P.sh_nz[s] = n.nLight.z;
+    P.sh_ru[s] = make_float4(0.f, 0.f, 0.f, n.nLight.z);   // same 32-byte record as sh_pl
 }
 VD NeePre nee_load(const PathSoA &P, int s) {
     NeePre n;
@@ -144,7 +143,7 @@ VD NeePre nee_load(const PathSoA &P, int s) {
     if (n.valid) {
         float4 c = P.sh_c[s], pl = P.sh_pl[s], pe = P.sh_ple[s];
         n.L = V3(c.x, c.y, c.z); n.p_l = c.w;
-        n.pLight = V3(pl.x, pl.y, pl.z); n.pLightErr = V3(pe.x, pe.y, pe.z); n.nLight = V3(pl.w, pe.w, P.sh_nz[s]);
+        n.pLight = V3(pl.x, pl.y, pl.z); n.pLightErr = V3(pe.x, pe.y, pe.z); n.nLight = V3(pl.w, pe.w, P.sh_ru[s].w);
     }
     return n;
 }
@@ -153,7 +152,7 @@ VD void shadow_load(const PathSoA &P, int s, ShadowRec &r) {
     r.o = V3(a.x, a.y, a.z); r.d = V3(a.w, b.x, b.y); r.medium = __float_as_int(b.z);
     int fl = __float_as_int(b.w); r.delta = fl & 1; r.channel = (fl >> 8) & 3;
     r.contrib = V3(c.x, c.y, c.z); r.rl = V3(d.x, d.y, d.z); r.ru = V3(e.x, e.y, e.z);
-    r.pLight = V3(f.x, f.y, f.z); r.pLightErr = V3(g.x, g.y, g.z); r.nLight = V3(f.w, g.w, P.sh_nz[s]);
+    r.pLight = V3(f.x, f.y, f.z); r.pLightErr = V3(g.x, g.y, g.z); r.nLight = V3(f.w, g.w, e.w);
 }
 // interaction.h:105-109 SpawnRayTo(pFrom, pTo): both ends offset (ray.h:104-109)
 VD void spawn_ray_to(V3 pf_, V3 pfErr, V3 nf, V3 pLight, V3 pLightErr, V3 nLight, V3 *o, V3 *d) {
