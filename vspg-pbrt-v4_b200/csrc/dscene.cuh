@@ -111,6 +111,10 @@ struct RngS {   // the sampler state shares 32-byte records with the hit record 
     float4 *base;
     __device__ __forceinline__ ulonglong2 &operator[](int s) const { return reinterpret_cast<ulonglong2 *>(base)[(size_t)s * 2]; }
 };
+struct LkS {    // the region id chosen by k_lookup rides in the record of sh_ple, which k_lookup writes and the scatter kernels read anyway
+    float4 *base;
+    __device__ __forceinline__ int &operator[](int s) const { return *reinterpret_cast<int *>(base + (size_t)s * 2 + 1); }
+};
 struct PathSoA {
     F4S<2, 0> o_dx;      // ray.o xyz, d.x
     F4S<2, 1> d_med;     // d.y d.z, medium(int), packed flags(int)
@@ -129,9 +133,9 @@ struct PathSoA {
     F4S<2, 1> sh_rl;     // r_p*p_l xyz, unused
     F4S<2, 0> sh_ru;     // r_p*scatterPDF xyz, nLight.z
     F4S<2, 1> sh_pl;     // pLight xyz, nLight.x
-    float4 *sh_ple;      // pLightErr xyz, nLight.y
+    F4S<2, 0> sh_ple;    // pLightErr xyz, nLight.y
     F4S<2, 1> prev_ns;   // (shares records with misc2) shading normal of the previous vertex (0 for a medium vertex): LightSampleContext::ns for the emission MIS
-    int *lk;             // guiding-cache region chosen by k_lookup for the pending scatter vertex (-1 = none)
+    LkS lk;              // guiding-cache region chosen by k_lookup for the pending scatter vertex (-1 = none)
     float2 *rs_pre;      // resampling pre-pass (media_sampleTMaj.h:153-164): sum of sigma_maj[ch]*dt, DDA steps(int)
 };
 

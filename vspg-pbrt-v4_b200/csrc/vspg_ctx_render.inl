@@ -18,14 +18,13 @@ static int ensure_wavefront(vspg_ctx *ctx, unsigned long long total) {
         return e;
     };
     PathSoA &P = ctx->W.P;
-    float4 **f4[] = {&P.ev, &P.sh_ple};
+    float4 **f4[] = {&P.ev};
     for (auto pp : f4) CK(alloc((void **)pp, n * sizeof(float4)));
     // 32-byte records shared by two streams (dscene.cuh F4S)
     float4 **pairs[][2] = {{&P.o_dx.base, &P.d_med.base}, {&P.beta_ru.base, &P.ru_rl.base}, {&P.rl_L.base, &P.misc.base}, {&P.misc2.base, &P.prev_ns.base},
-                           {&P.sh_o.base, &P.sh_d.base}, {&P.sh_c.base, &P.sh_rl.base}, {&P.sh_ru.base, &P.sh_pl.base}, {&P.rng.base, &P.hit.base}};
+                           {&P.sh_o.base, &P.sh_d.base}, {&P.sh_c.base, &P.sh_rl.base}, {&P.sh_ru.base, &P.sh_pl.base}, {&P.rng.base, &P.hit.base}, {&P.sh_ple.base, &P.lk.base}};
     for (auto &pr : pairs) { CK(alloc((void **)pr[0], 2 * n * sizeof(float4))); *pr[1] = *pr[0]; }
     CK(alloc((void **)&P.rs_pre, n * sizeof(float2)));
-    CK(alloc((void **)&P.lk, n * sizeof(int)));
     CK(alloc((void **)&ctx->qcounts, Q_INTS * sizeof(int)));
     int *items = nullptr;
     CK(alloc((void **)&items, Q_COUNT * n * sizeof(int)));
