@@ -39,6 +39,8 @@ struct vspg_ctx {
     int capacity = 0, requested_capacity = 0;
     int *qcounts = nullptr;       // device: 8 queue counters
     int *h_pinned = nullptr;      // pinned readback
+    const void *cells_ptr = nullptr; size_t cells_bytes = 0;      // cell-record grid of the (first) uniformgrid medium
+    size_t l2_persist_bytes = 0, l2_window_max = 0;               // persisting-L2 carve-out granted by the device (0 = off)
     double *film = nullptr;
     double *tr_acc = nullptr; size_t tr_acc_pixels = 0;   // storeTrBuffer accumulators (vspg_tr_store_*)
     unsigned long long *counters = nullptr;
@@ -137,6 +139,19 @@ int vspg_create(vspg_ctx **out, int device_ordinal) {
     vspg_integrator_defaults(&ctx->sc.ip);
     ctx->sc.ip.light_sampler = VSPG_LIGHTSAMPLER_UNIFORM;
     if (const char *sb = getenv("VSPG_SCATTER_BLOCK")) { int v = atoi(sb); if (v >= 32 && v <= kScatterBlock && v % 32 == 0) ctx->scatter_block = v; }
+    {   // persisting-L2 carve-out for the density cell grid (vspg_ctx_render.inl)
+        const char *lp = getenv("VSPG_L2_PERSIST");
+        cudaDeviceProp prop;
+        // Off unless asked for: measured on C2 (profiles/r01z_summary.md) the set-aside takes L2 away from the state-bound
+        // kernels (k_surface 22.6 -> 63.6 ms per 3 renders) for a 3 ms gain in k_medium_rs.
+        if (lp && atoi(lp) != 0 && cudaGetDeviceProperties(&prop, ctx->device) == cudaSuccess && prop.persistingL2CacheMaxSize > 0) {
+            size_t want = (size_t)prop.persistingL2CacheMaxSize;
+            if (lp && atoi(lp) > 1) want = std::min(want, (size_t)atoi(lp) << 20);     // VSPG_L2_PERSIST=<MiB>
+            if (cudaDeviceSetLimit(cudaLimitPersistingL2CacheSize, want) == cudaSuccess) {
+                ctx->l2_persist_bytes = want; ctx->l2_window_max = (size_t)prop.accessPolicyMaxWindowSize;
+            } else cudaGetLastError();
+        }
+    }
     if (const char *rr = getenv("VSPG_RS_REFILL")) { int v = atoi(rr); if (v >= 1 && v <= 32) ctx->rs_refill = v; }
     if (const char *ro = getenv("VSPG_RS_OCC")) { int v = atoi(ro); if (v == 4 || v == 5) ctx->rs_occ = v; }
     const char *lay = getenv("VSPG_GRID_LAYOUT");
@@ -172,6 +187,7 @@ int vspg_set_scene(vspg_ctx *ctx, const vspg_scene_desc *s) {
     if (s->camera.width <= 0 || s->camera.height <= 0) return fail(ctx, VSPG_ERR_INVALID, "set_scene: bad film resolution");
     dev_release(ctx, ctx->scene_allocs);
     ctx->have_scene = false;
+    ctx->cells_ptr = nullptr; ctx->cells_bytes = 0;
     ctx->sc.tr_acc = nullptr;   // a Tr store belongs to one scene (resolution): vspg_tr_store_begin again after set_scene
     struct Trim { vspg_ctx *c; ~Trim() { dev_trim(c); } } trimOnExit{ctx};   // every return path drops the blocks this call did not reuse
     DScene &sc = ctx->sc;
@@ -213,6 +229,7 @@ int vspg_set_scene(vspg_ctx *ctx, const vspg_scene_desc *s) {
             k_build_cells<<<blocks, 256>>>(d.density, m.nx, m.ny, m.nz, (float4 *)cells);
             CK(cudaGetLastError());
             d.cells = (const float4 *)cells; d.layout = GRID_CELL8;
+            if (!ctx->cells_ptr) { ctx->cells_ptr = cells; ctx->cells_bytes = ncell * 32; }
         }
     }
     CK(upload(ctx, ctx->scene_allocs, media.data(), media.size(), &sc.media));

@@ -84,14 +84,34 @@ int vspg_render(vspg_ctx *ctx, int spp_begin, int spp_end, int spp_stride, int x
         CK(cudaEventRecord(ctx->ev[0], st)); CK(cudaEventSynchronize(ctx->ev[0]));
         float ms = 0; CK(cudaEventElapsedTime(&ms, evStart, ctx->ev[0])); ctx->ms_kernel[VSPG_K_GENERATE] += ms;
     }
+    // The tracking kernels gather from the cell-record grid at random while the path state streams through L2: give the
+    // grid a persisting access-policy window (per launch, so it does not depend on which stream the caller passed) and
+    // let everything else those kernels touch be streaming.  Opt-in (VSPG_L2_PERSIST=1 or =<MiB>): a net loss on C2, see vspg_create.
+    cudaLaunchAttribute gridWin[1];
+    int nGridWin = 0;
+    if (ctx->cells_bytes && ctx->l2_persist_bytes) {
+        gridWin[0].id = cudaLaunchAttributeAccessPolicyWindow;
+        cudaAccessPolicyWindow &w = gridWin[0].val.accessPolicyWindow;
+        w.base_ptr = (void *)ctx->cells_ptr;
+        w.num_bytes = std::min(ctx->cells_bytes, ctx->l2_window_max);
+        w.hitRatio = (float)std::min(1.0, (double)ctx->l2_persist_bytes / (double)w.num_bytes);
+        w.hitProp = cudaAccessPropertyPersisting; w.missProp = cudaAccessPropertyStreaming;
+        nGridWin = 1;
+    }
+    auto launch_tracking = [&](auto kernel, int nblocks, auto... args) {
+        cudaLaunchConfig_t cfg = {};
+        cfg.gridDim = dim3(nblocks); cfg.blockDim = dim3(kBlock); cfg.dynamicSmemBytes = 0; cfg.stream = st;
+        cfg.attrs = gridWin; cfg.numAttrs = nGridWin;
+        return cudaLaunchKernelEx(&cfg, kernel, args...);
+    };
     int cur = 0;  // physical index of the active queue
 #define VSPG_STAGE(K, launch) do { launch; ctx->launches_kernel[K]++; if (timing) CK(cudaEventRecord(ctx->ev[K], st)); } while (0)
     while (true) {
         if (timing) CK(cudaEventRecord(ctx->ev[0], st));
         VSPG_STAGE(VSPG_K_INTERSECT, (k_intersect<<<grid, kBlock, 0, st>>>(sc, W)));
-        if (ctx->all_gray && ctx->rs_occ == 5) k_medium_rs<true, 5><<<ctx->sm_count * 5, kBlock, 0, st>>>(sc, W, ctx->qcounts + Q_COUNT, ctx->rs_refill);
-        else if (ctx->all_gray) k_medium_rs<true, 4><<<ctx->sm_count * 4, kBlock, 0, st>>>(sc, W, ctx->qcounts + Q_COUNT, ctx->rs_refill);
-        else k_medium_rs<false, 4><<<ctx->sm_count * 4, kBlock, 0, st>>>(sc, W, ctx->qcounts + Q_COUNT, ctx->rs_refill);
+        if (ctx->all_gray && ctx->rs_occ == 5) CK(launch_tracking(k_medium_rs<true, 5>, ctx->sm_count * 5, sc, W, ctx->qcounts + Q_COUNT, ctx->rs_refill));
+        else if (ctx->all_gray) CK(launch_tracking(k_medium_rs<true, 4>, ctx->sm_count * 4, sc, W, ctx->qcounts + Q_COUNT, ctx->rs_refill));
+        else CK(launch_tracking(k_medium_rs<false, 4>, ctx->sm_count * 4, sc, W, ctx->qcounts + Q_COUNT, ctx->rs_refill));
         VSPG_STAGE(VSPG_K_MEDIUM, (k_medium<<<grid, kBlock, 0, st>>>(sc, W)));
         if (guidedVol) {
             k_lookup<false><<<grid, kBlock, 0, st>>>(sc, W, W.volscatter, W.vol8, W.vol16, W.vol32);
@@ -108,8 +128,8 @@ int vspg_render(vspg_ctx *ctx, int spp_begin, int spp_end, int spp_stride, int x
             VSPG_STAGE(VSPG_K_SHADE, (k_shade<32><<<sgrid, sblock, 0, st>>>(sc, W, W.sh32)));
             ctx->launches += 3;
         } else VSPG_STAGE(VSPG_K_SHADE, (k_shade<0><<<grid, kBlock, 0, st>>>(sc, W, W.shade)));
-        if (ctx->all_gray) VSPG_STAGE(VSPG_K_SHADOW, (k_shadow<true><<<grid, kBlock, 0, st>>>(sc, W)));
-        else VSPG_STAGE(VSPG_K_SHADOW, (k_shadow<false><<<grid, kBlock, 0, st>>>(sc, W)));
+        if (ctx->all_gray) VSPG_STAGE(VSPG_K_SHADOW, CK(launch_tracking(k_shadow<true>, grid, sc, W)));
+        else VSPG_STAGE(VSPG_K_SHADOW, CK(launch_tracking(k_shadow<false>, grid, sc, W)));
         VSPG_STAGE(VSPG_K_FINISH, (k_finish<<<grid, kBlock, 0, st>>>(sc, W)));
         ctx->launches += 8; ctx->iterations++;
         // swap roles: next becomes active; clear every other counter
