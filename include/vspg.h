@@ -242,7 +242,7 @@ int vspg_set_guiding(vspg_ctx *ctx, const vspg_guiding_desc *guiding);
 /* replaces GuidedVolPathVSPGIntegrator::Create (vspg.cpp:1260-1322) */
 int vspg_set_integrator(vspg_ctx *ctx, const vspg_integrator_params *params);
 
-/* Maximum number of paths resident in HBM at once (wavefront capacity). 0 = default. */
+/* Maximum number of paths resident in HBM at once (wavefront capacity). 0 = default (min(job size, 2^24), ~340 B per path). */
 int vspg_set_capacity(vspg_ctx *ctx, int max_paths_in_flight);
 
 /* ------------------------------------------------------------------ rendering */
