@@ -171,7 +171,7 @@ VD void spawn_ray_to(V3 pf_, V3 pfErr, V3 nf, V3 pLight, V3 pLightErr, V3 nLight
 // the top stall was instruction fetch (ncu r01c: no_instruction 3.8-5.9 per issue).  Trip counts are therefore
 // uniform over the whole CTA (`base` is a CTA quantity) and the loop body carries __syncthreads() between its
 // phases (scatter_phase_sync), so that the warps of a CTA walk the code together and share instruction-cache lines.
-constexpr int kScatterBlock = 512;        // launch bound; the default launch uses 256 (r01e A/B: 512 -> 116.5, 256 -> 118.0, 128 -> 109.4 Mpaths/s)
+constexpr int kScatterBlock = 256;        // launch bound and default block of the lane-group scatter kernels (r01e A/B: 512 -> 116.5, 256 -> 118.0, 128 -> 109.4 Mpaths/s)
 template <int G> struct GroupIter {
     static constexpr int W = G > 0 ? G : 1;        // lanes per vertex
     int first, step, warpOff, sub; bool leader;
@@ -235,7 +235,7 @@ __global__ void __launch_bounds__(kBlock) k_lookup(const DScene sc, const Wavefr
 
 // ------------------------------------------------------------------ volume scatter vertex (vspg.cpp:804-875 / 988-1058)
 template <int G>
-__global__ void __launch_bounds__(G > 0 ? kScatterBlock : kBlock) k_volscatter(const DScene sc, const Wavefront W, const Queue in) {
+__global__ void __launch_bounds__(G > 0 ? 256 : kBlock, G > 0 ? 3 : 1) k_volscatter(const DScene sc, const Wavefront W, const Queue in) {
     const int n = *in.count;
     const GroupIter<G> gi;
     const bool leader = gi.leader;

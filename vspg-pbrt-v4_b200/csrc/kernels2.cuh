@@ -60,7 +60,7 @@ __global__ void __launch_bounds__(kBlock, 5) k_surface(const DScene sc, const Wa
 
 // ------------------------------------------------------------------ surface scatter vertex (vspg.cpp:448-607)
 template <int G>
-__global__ void __launch_bounds__(G > 0 ? kScatterBlock : kBlock) k_shade(const DScene sc, const Wavefront W, const Queue in) {
+__global__ void __launch_bounds__(G > 0 ? 256 : kBlock, G > 0 ? 3 : 1) k_shade(const DScene sc, const Wavefront W, const Queue in) {
     const int n = *in.count;
     const GroupIter<G> gi;
     const bool leader = gi.leader;

@@ -48,6 +48,7 @@ struct vspg_ctx {
     int film_w = 0, film_h = 0;
     int grid_layout = GRID_CELL8;
     int scatter_block = 256;   // VSPG_SCATTER_BLOCK overrides (A/B runs)
+    int volscatter_ctas = 2, shade_ctas = 2, scatter_ctas_block = 0;   // resident CTAs/SM of the scatter kernels (occupancy API, per scatter_block)
     int rs_occ = 4;               // CTAs/SM the gray resampling kernel is compiled for (VSPG_RS_OCC=4|5, A/B runs)
     int rs_refill = kRsRefillIdleDefault;   // VSPG_RS_REFILL overrides (A/B runs)
     bool all_gray = false;        // every medium has sigma_a / sigma_s equal across RGB => scalar tracking kernels (kmedium_rs.cuh)
@@ -138,7 +139,7 @@ int vspg_create(vspg_ctx **out, int device_ordinal) {
     if (cudaGetDeviceProperties(&prop, device_ordinal) == cudaSuccess) ctx->sm_count = prop.multiProcessorCount;
     vspg_integrator_defaults(&ctx->sc.ip);
     ctx->sc.ip.light_sampler = VSPG_LIGHTSAMPLER_UNIFORM;
-    if (const char *sb = getenv("VSPG_SCATTER_BLOCK")) { int v = atoi(sb); if (v >= 32 && v <= kScatterBlock && v % 32 == 0) ctx->scatter_block = v; }
+    if (const char *sb = getenv("VSPG_SCATTER_BLOCK")) { int v = atoi(sb); if (v >= 32 && v <= 256 && v % 32 == 0) ctx->scatter_block = v; }
     {   // persisting-L2 carve-out for the density cell grid (vspg_ctx_render.inl)
         const char *lp = getenv("VSPG_L2_PERSIST");
         cudaDeviceProp prop;

@@ -71,7 +71,16 @@ int vspg_render(vspg_ctx *ctx, int spp_begin, int spp_end, int spp_stride, int x
     CK(cudaMemsetAsync(ctx->qcounts, 0, Q_INTS * sizeof(int), st));
     CK(cudaMemsetAsync(W.next_sample, 0, sizeof(unsigned long long), st));
     const int grid = ctx->sm_count * 8;
-    const int sblock = ctx->scatter_block, sgrid = ctx->sm_count * std::max(1, 512 / sblock);   // lane-group scatter kernels (kernels.cuh GroupIter)
+    // lane-group scatter kernels (kernels.cuh GroupIter): persistent grids of exactly the CTAs one wave of the device holds
+    const int sblock = ctx->scatter_block;
+    if (ctx->scatter_ctas_block != sblock) {
+        int ov = 0, os = 0;
+        CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&ov, k_volscatter<8>, sblock, 0));
+        CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&os, k_shade<8>, sblock, 0));
+        ctx->volscatter_ctas = std::max(1, ov); ctx->shade_ctas = std::max(1, os); ctx->scatter_ctas_block = sblock;
+        if (const char *e = getenv("VSPG_SCATTER_CTAS")) { int v = atoi(e); if (v >= 1 && v <= 32) ctx->volscatter_ctas = ctx->shade_ctas = v; }
+    }
+    const int vgrid = ctx->sm_count * ctx->volscatter_ctas, sgrid = ctx->sm_count * ctx->shade_ctas;
     const bool guidedVol = sc.vol.present, guidedSurf = sc.surf.present;
     int nslots = (int)std::min<unsigned long long>((unsigned long long)ctx->capacity, total);
     W.active = qa; W.next = qb;
@@ -117,9 +126,9 @@ int vspg_render(vspg_ctx *ctx, int spp_begin, int spp_end, int spp_stride, int x
         VSPG_STAGE(VSPG_K_MEDIUM, (k_medium<<<grid, kBlock, 0, st>>>(sc, W)));
         if (guidedVol) {
             k_lookup<false><<<grid, kBlock, 0, st>>>(sc, W, W.volscatter, W.vol8, W.vol16, W.vol32);
-            k_volscatter<8><<<sgrid, sblock, 0, st>>>(sc, W, W.vol8);
-            k_volscatter<16><<<sgrid, sblock, 0, st>>>(sc, W, W.vol16);
-            VSPG_STAGE(VSPG_K_VOLSCATTER, (k_volscatter<32><<<sgrid, sblock, 0, st>>>(sc, W, W.vol32)));
+            k_volscatter<8><<<vgrid, sblock, 0, st>>>(sc, W, W.vol8);
+            k_volscatter<16><<<vgrid, sblock, 0, st>>>(sc, W, W.vol16);
+            VSPG_STAGE(VSPG_K_VOLSCATTER, (k_volscatter<32><<<vgrid, sblock, 0, st>>>(sc, W, W.vol32)));
             ctx->launches += 3;
         } else VSPG_STAGE(VSPG_K_VOLSCATTER, (k_volscatter<0><<<grid, kBlock, 0, st>>>(sc, W, W.volscatter)));
         VSPG_STAGE(VSPG_K_SURFACE, (k_surface<<<grid, kBlock, 0, st>>>(sc, W)));
