@@ -235,7 +235,7 @@ __global__ void __launch_bounds__(kBlock) k_lookup(const DScene sc, const Wavefr
 
 // ------------------------------------------------------------------ volume scatter vertex (vspg.cpp:804-875 / 988-1058)
 template <int G>
-__global__ void __launch_bounds__(G > 0 ? 256 : kBlock, G > 0 ? 3 : 1) k_volscatter(const DScene sc, const Wavefront W, const Queue in) {
+__global__ void __launch_bounds__(G > 0 ? 256 : kBlock, G > 0 ? 4 : 1) k_volscatter(const DScene sc, const Wavefront W, const Queue in) {
     const int n = *in.count;
     const GroupIter<G> gi;
     const bool leader = gi.leader;
