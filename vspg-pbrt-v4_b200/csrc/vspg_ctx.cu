@@ -49,7 +49,10 @@ struct vspg_ctx {
     int grid_layout = GRID_CELL8;
     int scatter_block = 256;   // VSPG_SCATTER_BLOCK overrides (A/B runs)
     int volscatter_ctas = 2, shade_ctas = 2, scatter_ctas_block = 0;   // resident CTAs/SM of the scatter kernels (occupancy API, per scatter_block)
-    int rs_occ = 4;               // CTAs/SM the gray resampling kernel is compiled for (VSPG_RS_OCC=4|5, A/B runs)
+    bool grids_ready = false;   // one-wave grids of the grid-stride kernels (occupancy API, vspg_ctx_render.inl)
+    int g_generate = 0, g_intersect = 0, g_medium = 0, g_lookup0 = 0, g_lookup1 = 0, g_surface = 0, g_volscatter0 = 0, g_shade0 = 0, g_finish = 0,
+        g_shadow_gray = 0, g_shadow_rgb = 0;
+    int rs_occ = 5;               // CTAs/SM the gray resampling kernel is compiled for (VSPG_RS_OCC=4|5, A/B runs)
     int rs_refill = kRsRefillIdleDefault;   // VSPG_RS_REFILL overrides (A/B runs)
     bool all_gray = false;        // every medium has sigma_a / sigma_s equal across RGB => scalar tracking kernels (kmedium_rs.cuh)
     // timing (vspg_kernel_stats_get)

@@ -98,6 +98,19 @@ int vspg_render(vspg_ctx *ctx, int spp_begin, int spp_end, int spp_stride, int x
     // The tracking kernels gather from the cell-record grid at random while the path state streams through L2: give the
     // grid a persisting access-policy window (per launch, so it does not depend on which stream the caller passed) and
     // let everything else those kernels touch be streaming.  Opt-in (VSPG_L2_PERSIST=1 or =<MiB>): a net loss on C2, see vspg_create.
+    // Grid-stride kernels get exactly one resident wave: sm_count x (CTAs of kBlock threads that fit one SM).  A fixed 8
+    // CTAs/SM left k_surface (5 resident) and k_intersect / k_lookup (6 resident) with a partial second wave.
+    if (!ctx->grids_ready) {
+        auto occ = [&](auto kernel, int *out) -> cudaError_t {
+            int o = 0; cudaError_t e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&o, kernel, kBlock, 0);
+            *out = ctx->sm_count * std::max(1, o); return e;
+        };
+        CK(occ(k_generate, &ctx->g_generate)); CK(occ(k_intersect, &ctx->g_intersect)); CK(occ(k_medium, &ctx->g_medium));
+        CK(occ(k_lookup<false>, &ctx->g_lookup0)); CK(occ(k_lookup<true>, &ctx->g_lookup1)); CK(occ(k_surface, &ctx->g_surface));
+        CK(occ(k_volscatter<0>, &ctx->g_volscatter0)); CK(occ(k_shade<0>, &ctx->g_shade0)); CK(occ(k_finish, &ctx->g_finish));
+        CK(occ(k_shadow<true>, &ctx->g_shadow_gray)); CK(occ(k_shadow<false>, &ctx->g_shadow_rgb));
+        ctx->grids_ready = true;
+    }
     cudaLaunchAttribute gridWin[1];
     int nGridWin = 0;
     if (ctx->cells_bytes && ctx->l2_persist_bytes) {
@@ -119,29 +132,29 @@ int vspg_render(vspg_ctx *ctx, int spp_begin, int spp_end, int spp_stride, int x
 #define VSPG_STAGE(K, launch) do { launch; ctx->launches_kernel[K]++; if (timing) CK(cudaEventRecord(ctx->ev[K], st)); } while (0)
     while (true) {
         if (timing) CK(cudaEventRecord(ctx->ev[0], st));
-        VSPG_STAGE(VSPG_K_INTERSECT, (k_intersect<<<grid, kBlock, 0, st>>>(sc, W)));
+        VSPG_STAGE(VSPG_K_INTERSECT, (k_intersect<<<ctx->g_intersect, kBlock, 0, st>>>(sc, W)));
         if (ctx->all_gray && ctx->rs_occ == 5) CK(launch_tracking(k_medium_rs<true, 5>, ctx->sm_count * 5, sc, W, ctx->qcounts + Q_COUNT, ctx->rs_refill));
         else if (ctx->all_gray) CK(launch_tracking(k_medium_rs<true, 4>, ctx->sm_count * 4, sc, W, ctx->qcounts + Q_COUNT, ctx->rs_refill));
         else CK(launch_tracking(k_medium_rs<false, 4>, ctx->sm_count * 4, sc, W, ctx->qcounts + Q_COUNT, ctx->rs_refill));
-        VSPG_STAGE(VSPG_K_MEDIUM, (k_medium<<<grid, kBlock, 0, st>>>(sc, W)));
+        VSPG_STAGE(VSPG_K_MEDIUM, (k_medium<<<ctx->g_medium, kBlock, 0, st>>>(sc, W)));
         if (guidedVol) {
-            k_lookup<false><<<grid, kBlock, 0, st>>>(sc, W, W.volscatter, W.vol8, W.vol16, W.vol32);
+            k_lookup<false><<<ctx->g_lookup0, kBlock, 0, st>>>(sc, W, W.volscatter, W.vol8, W.vol16, W.vol32);
             k_volscatter<8><<<vgrid, sblock, 0, st>>>(sc, W, W.vol8);
             k_volscatter<16><<<vgrid, sblock, 0, st>>>(sc, W, W.vol16);
             VSPG_STAGE(VSPG_K_VOLSCATTER, (k_volscatter<32><<<vgrid, sblock, 0, st>>>(sc, W, W.vol32)));
             ctx->launches += 3;
-        } else VSPG_STAGE(VSPG_K_VOLSCATTER, (k_volscatter<0><<<grid, kBlock, 0, st>>>(sc, W, W.volscatter)));
-        VSPG_STAGE(VSPG_K_SURFACE, (k_surface<<<grid, kBlock, 0, st>>>(sc, W)));
+        } else VSPG_STAGE(VSPG_K_VOLSCATTER, (k_volscatter<0><<<ctx->g_volscatter0, kBlock, 0, st>>>(sc, W, W.volscatter)));
+        VSPG_STAGE(VSPG_K_SURFACE, (k_surface<<<ctx->g_surface, kBlock, 0, st>>>(sc, W)));
         if (guidedSurf) {
-            k_lookup<true><<<grid, kBlock, 0, st>>>(sc, W, W.shade, W.sh8, W.sh16, W.sh32);
+            k_lookup<true><<<ctx->g_lookup1, kBlock, 0, st>>>(sc, W, W.shade, W.sh8, W.sh16, W.sh32);
             k_shade<8><<<sgrid, sblock, 0, st>>>(sc, W, W.sh8);
             k_shade<16><<<sgrid, sblock, 0, st>>>(sc, W, W.sh16);
             VSPG_STAGE(VSPG_K_SHADE, (k_shade<32><<<sgrid, sblock, 0, st>>>(sc, W, W.sh32)));
             ctx->launches += 3;
-        } else VSPG_STAGE(VSPG_K_SHADE, (k_shade<0><<<grid, kBlock, 0, st>>>(sc, W, W.shade)));
-        if (ctx->all_gray) VSPG_STAGE(VSPG_K_SHADOW, CK(launch_tracking(k_shadow<true>, grid, sc, W)));
-        else VSPG_STAGE(VSPG_K_SHADOW, CK(launch_tracking(k_shadow<false>, grid, sc, W)));
-        VSPG_STAGE(VSPG_K_FINISH, (k_finish<<<grid, kBlock, 0, st>>>(sc, W)));
+        } else VSPG_STAGE(VSPG_K_SHADE, (k_shade<0><<<ctx->g_shade0, kBlock, 0, st>>>(sc, W, W.shade)));
+        if (ctx->all_gray) VSPG_STAGE(VSPG_K_SHADOW, CK(launch_tracking(k_shadow<true>, ctx->g_shadow_gray, sc, W)));
+        else VSPG_STAGE(VSPG_K_SHADOW, CK(launch_tracking(k_shadow<false>, ctx->g_shadow_rgb, sc, W)));
+        VSPG_STAGE(VSPG_K_FINISH, (k_finish<<<ctx->g_finish, kBlock, 0, st>>>(sc, W)));
         ctx->launches += 8; ctx->iterations++;
         // swap roles: next becomes active; clear every other counter
         cur ^= 1;
