@@ -160,7 +160,7 @@ __global__ void __launch_bounds__(G > 0 ? 256 : kBlock, G > 0 ? 3 : 1) k_shade(c
 // ------------------------------------------------------------------ shadow rays (SampleLd back half, vspg.cpp:1193-1252)
 // GRAY: all media gray (see dmath.cuh G1) -- T_ray, r_l, r_u of the ratio tracker are scalars until the final weighting.
 template <bool GRAY>
-__global__ void __launch_bounds__(kBlock, GRAY ? 8 : 6) k_shadow(const DScene sc, const Wavefront W) {
+__global__ void __launch_bounds__(kBlock, 8) k_shadow(const DScene sc, const Wavefront W) {
     typedef typename SpecT<GRAY>::type Sp;
     const int n = *W.shadow.count;
     TrackCounters tc; tc.queries = 0; tc.dda = 0;
