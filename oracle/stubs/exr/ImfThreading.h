@@ -1,0 +1,4 @@
+// Test-infrastructure stub: see ImfStub.h
+#pragma once
+#include "ImfStub.h"
+namespace Imf { inline void setGlobalThreadCount(int) {} }
