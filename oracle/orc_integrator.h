@@ -34,16 +34,16 @@ struct SurfaceIntr {
     int mediumInside = -1, mediumOutside = -1;
     int rayMedium = -1;
     int GetMedium(V3 w) const {  // interaction.h:117-121
-        if (hasInterface) return Dot(w, n) > 0 ? mediumOutside : mediumInside;
+        if (hasInterface) return DotN(w, n) > 0 ? mediumOutside : mediumInside;
         return rayMedium;
     }
 };
 
 // ray.h:75-92
 inline V3 OffsetRayOrigin(V3 p, V3 pError, V3 n, V3 w) {
-    float d = Dot(Abs(n), pError);
+    float d = DotN(Abs(n), pError);
     V3 offset = d * n;
-    if (Dot(w, n) < 0) offset = -offset;
+    if (DotN(w, n) < 0) offset = -offset;
     V3 po = p + offset;
     for (int i = 0; i < 3; ++i) {
         if (offset[i] > 0) po[i] = NextFloatUp(po[i]);
@@ -271,7 +271,7 @@ struct Scene {
     static bool IsRectangle(V3 p00, V3 p10, V3 p01, V3 p11) {  // shapes.h BilinearPatch::IsRectangle
         if (p00 == p01 || p01 == p11 || p11 == p10 || p10 == p00) return false;
         V3 n = Normalize(Cross(p10 - p00, p01 - p00));
-        if (AbsDot(Normalize(p11 - p00), n) > 1e-5f) return false;
+        if (AbsDotN(Normalize(p11 - p00), n) > 1e-5f) return false;
         V3 pCenter = (p00 + p01 + p10 + p11) / 4;
         float d2[4] = {DistanceSquared(p00, pCenter), DistanceSquared(p01, pCenter), DistanceSquared(p10, pCenter), DistanceSquared(p11, pCenter)};
         for (int i = 1; i < 4; ++i)
@@ -338,6 +338,24 @@ struct Scene {
         }
         return h;
     }
+    // One shape's own Intersect (Shape::Intersect(ray, tMax)), as Shape::PDF(ctx, wi) calls it
+    Hit IntersectPrim(int kind, int index, V3 ro, V3 rd, float tMax) const {
+        Hit h;
+        if (kind == 0) {
+            const vspg_quad &q = d->quads[index];
+            float u, v, t;
+            if (IntersectBilinearPatch(ro, rd, tMax, V3(q.p00), V3(q.p10), V3(q.p01), V3(q.p11), &u, &v, &t)) { h.valid = true; h.t = t; h.kind = 0; h.index = index; h.u = u; h.v = v; }
+        } else if (kind == 1) {
+            const vspg_triangle &q = d->triangles[index];
+            float b[3], t;
+            if (IntersectTriangle(ro, rd, tMax, V3(q.p0), V3(q.p1), V3(q.p2), b, &t)) { h.valid = true; h.t = t; h.kind = 1; h.index = index; h.u = b[0]; h.v = b[1]; h.b[0] = b[0]; h.b[1] = b[1]; h.b[2] = b[2]; }
+        } else {
+            const vspg_sphere &q = d->spheres[index];
+            float t; V3 pObj;
+            if (IntersectSphere(ro, rd, tMax, V3(q.center), q.radius, &t, &pObj)) { h.valid = true; h.t = t; h.kind = 2; h.index = index; h.pObj = pObj; }
+        }
+        return h;
+    }
     // shapes.h:1398-1500 BilinearPatch::InteractionFromIntersection (no mesh uv / normals) + primitive.cpp
     // GeometricPrimitive::Intersect -> SetIntersectionProperties (interaction.h:218-229)
     int HitMaterial(const Hit &h) const {
@@ -371,8 +389,9 @@ struct Scene {
                 V3 ng = Cross(p2 - p0, p1 - p0);
                 CoordinateSystem(Normalize(ng), &dpdu, &dpdv);
             }
-            s.p = h.b[0] * p0 + h.b[1] * p1 + h.b[2] * p2;
-            s.pError = gamma_(7) * (Abs(h.b[0] * p0) + Abs(h.b[1] * p1) + Abs(h.b[2] * p2));
+            // Point3fi(pHit, pError) (shapes.h:929-935): the interval is rounded outwards, p() is its midpoint and Error() half its width
+            V3i pi = V3i::FromValueAndError(h.b[0] * p0 + h.b[1] * p1 + h.b[2] * p2, gamma_(7) * (Abs(h.b[0] * p0) + Abs(h.b[1] * p1) + Abs(h.b[2] * p2)));
+            s.p = pi.Mid(); s.pError = pi.Error();
             s.n = Normalize(Cross(dp02, dp12));
             if (q.flip_normal) s.n = -s.n;
             s.ns = s.n; s.dpdu = dpdu;
@@ -385,11 +404,12 @@ struct Scene {
         }
         const vspg_quad &q = d->quads[h.index];
         V3 p00(q.p00), p10(q.p10), p01(q.p01), p11(q.p11);
-        s.p = LerpV(h.u, LerpV(h.v, p00, p01), LerpV(h.v, p10, p11));
+        V3 pLerp = LerpV(h.u, LerpV(h.v, p00, p01), LerpV(h.v, p10, p11));
         V3 dpdu = LerpV(h.v, p10, p11) - LerpV(h.v, p00, p01);
         V3 dpdv = LerpV(h.u, p01, p11) - LerpV(h.u, p00, p10);
         V3 pAbsSum = Abs(p00) + Abs(p01) + Abs(p10) + Abs(p11);
-        s.pError = gamma_(6) * pAbsSum;
+        V3i pi = V3i::FromValueAndError(pLerp, gamma_(6) * pAbsSum);   // shapes.h:1464-1472 Point3fi(p, pError): outward-rounded interval
+        s.p = pi.Mid(); s.pError = pi.Error();
         s.n = Normalize(Cross(dpdu, dpdv));
         if (q.flip_normal) s.n = -s.n;
         s.ns = s.n; s.dpdu = dpdu;
@@ -403,7 +423,7 @@ struct Scene {
     // lights.h:492-515 DiffuseAreaLight::L
     S3 AreaL(int light, V3 n, V3 w) const {
         const vspg_light &l = d->lights[light];
-        if (!l.two_sided && Dot(n, w) < 0) return S3(0.f);
+        if (!l.two_sided && DotN(n, w) < 0) return S3(0.f);
         return S3(l.L);
     }
 };
@@ -455,7 +475,7 @@ struct GuidedBSDF {
                 dist.init(&sc->g->surface->regions[r], p);
                 dist.region = r;
                 V3 n = ns;
-                if (Dot(-rayD, ns) < 0.f) n = -n;
+                if (DotN(-rayD, ns) < 0.f) n = -n;
                 dist.applyCosineProduct(n);
                 success = true;
             }
@@ -685,7 +705,7 @@ struct Integrator {
             V3 wi = p - ctx.p;
             if (LengthSquared(wi) == 0) return false;
             wi = Normalize(wi);
-            float pdf = (1 / area) / (AbsDot(n, -wi) / DistanceSquared(ctx.p, p));
+            float pdf = (1 / area) / (AbsDotN(n, -wi) / DistanceSquared(ctx.p, p));
             if (std::isinf(pdf)) return false;
             *pOut = p; *nOut = n; *pdfOut = pdf;
             return true;
@@ -693,8 +713,8 @@ struct Integrator {
         float pdf = 1, us[2] = {u[0], u[1]};
         if (!(ctx.ns.x == 0 && ctx.ns.y == 0 && ctx.ns.z == 0)) {
             V3 wi[3] = {Normalize(p0 - ctx.p), Normalize(p1 - ctx.p), Normalize(p2 - ctx.p)};
-            float w[4] = {std::max<float>(0.01, AbsDot(ctx.ns, wi[1])), std::max<float>(0.01, AbsDot(ctx.ns, wi[1])),
-                          std::max<float>(0.01, AbsDot(ctx.ns, wi[0])), std::max<float>(0.01, AbsDot(ctx.ns, wi[2]))};
+            float w[4] = {std::max<float>(0.01, AbsDotN(ctx.ns, wi[1])), std::max<float>(0.01, AbsDotN(ctx.ns, wi[1])),
+                          std::max<float>(0.01, AbsDotN(ctx.ns, wi[0])), std::max<float>(0.01, AbsDotN(ctx.ns, wi[2]))};
             float uw[2];
             SampleBilinear(us, w, uw);
             us[0] = uw[0]; us[1] = uw[1];
@@ -724,7 +744,7 @@ struct Integrator {
             V3 wi = p - ctx.p;
             if (LengthSquared(wi) == 0) return false;
             wi = Normalize(wi);
-            float pdf = (1 / area) / (AbsDot(n, -wi) / DistanceSquared(ctx.p, p));
+            float pdf = (1 / area) / (AbsDotN(n, -wi) / DistanceSquared(ctx.p, p));
             if (std::isinf(pdf)) return false;
             *pOut = p; *pErr = pi.Error(); *nOut = n; *pdfOut = pdf;
             return true;
@@ -793,8 +813,8 @@ struct Integrator {
         if (Scene::IsRectangle(p00, p10, p01, p11) && !(SphericalQuadArea(v00, v10, v11, v01) <= MinSphericalSampleAreaQuad)) {
             float us[2] = {u[0], u[1]};
             if (!(ctx.ns.x == 0 && ctx.ns.y == 0 && ctx.ns.z == 0)) {
-                float w[4] = {std::max<float>(0.01, AbsDot(v00, ctx.ns)), std::max<float>(0.01, AbsDot(v10, ctx.ns)),
-                              std::max<float>(0.01, AbsDot(v01, ctx.ns)), std::max<float>(0.01, AbsDot(v11, ctx.ns))};
+                float w[4] = {std::max<float>(0.01, AbsDotN(v00, ctx.ns)), std::max<float>(0.01, AbsDotN(v10, ctx.ns)),
+                              std::max<float>(0.01, AbsDotN(v01, ctx.ns)), std::max<float>(0.01, AbsDotN(v11, ctx.ns))};
                 float uw[2];
                 SampleBilinear(us, w, uw);
                 us[0] = uw[0]; us[1] = uw[1];
@@ -832,7 +852,7 @@ struct Integrator {
         V3 wi = p - ctx.p;
         if (LengthSquared(wi) == 0) return ls;
         wi = Normalize(wi);
-        float pdfW = pdfA / (AbsDot(n, -wi) / DistanceSquared(ctx.p, p));
+        float pdfW = pdfA / (AbsDotN(n, -wi) / DistanceSquared(ctx.p, p));
         if (std::isinf(pdfW)) return ls;
         if (pdfW == 0) return ls;
         S3 Le = sc->AreaL(light, n, -wi);
@@ -841,14 +861,19 @@ struct Integrator {
         return ls;
     }
     // lights.cpp:820-824 -> shapes.cpp:1329-1347 (area-sampling branch), evaluated at the actual hit
-    float AreaPDF_Li(int light, const LightSampleCtx &ctx, V3 wi, const SurfaceIntr &hit) const {
+    // Light::PDF_Li -> Shape::PDF(ctx, wi): every shape first intersects ITSELF with ctx.SpawnRay(wi) (shapes.cpp:1337-1341,
+    // shapes.h:1133-1137, 366-370) -- not the path's own hit, whose ray may have been re-spawned at interfaces on the way.
+    float AreaPDF_Li(int light, const LightSampleCtx &ctx, V3 wi, const SurfaceIntr &) const {
         const vspg_light &l = sc->d->lights[light];
+        Hit sh = sc->IntersectPrim(l.shape_kind, l.shape_index, OffsetRayOrigin(ctx.p, ctx.pError, ctx.n, wi), wi, Infinity);
+        if (!sh.valid) return 0;
+        const SurfaceIntr hit = sc->MakeIntr(sh, wi, -1);
         if (l.shape_kind == 1) {   // shapes.h:1128-1173 Triangle::PDF(ctx, wi)
             const vspg_triangle &t = sc->d->triangles[l.shape_index];
             V3 p0(t.p0), p1(t.p1), p2(t.p2);
             float solidAngle = SphericalTriangleArea(Normalize(p0 - ctx.p), Normalize(p1 - ctx.p), Normalize(p2 - ctx.p));
             if (solidAngle < MinSphericalSampleAreaTri || solidAngle > MaxSphericalSampleAreaTri) {
-                float r = (1 / sc->triArea[l.shape_index]) / (AbsDot(hit.n, -wi) / DistanceSquared(ctx.p, hit.p));
+                float r = (1 / sc->triArea[l.shape_index]) / (AbsDotN(hit.n, -wi) / DistanceSquared(ctx.p, hit.p));
                 return std::isinf(r) ? 0 : r;
             }
             float pdf = 1 / solidAngle;
@@ -857,8 +882,8 @@ struct Integrator {
                 float uu[2];
                 InvertSphericalTriangleSample(v, ctx.p, wi, uu);
                 V3 wv[3] = {Normalize(p0 - ctx.p), Normalize(p1 - ctx.p), Normalize(p2 - ctx.p)};
-                float w[4] = {std::max<float>(0.01, AbsDot(ctx.ns, wv[1])), std::max<float>(0.01, AbsDot(ctx.ns, wv[1])),
-                              std::max<float>(0.01, AbsDot(ctx.ns, wv[0])), std::max<float>(0.01, AbsDot(ctx.ns, wv[2]))};
+                float w[4] = {std::max<float>(0.01, AbsDotN(ctx.ns, wv[1])), std::max<float>(0.01, AbsDotN(ctx.ns, wv[1])),
+                              std::max<float>(0.01, AbsDotN(ctx.ns, wv[0])), std::max<float>(0.01, AbsDotN(ctx.ns, wv[2]))};
                 pdf *= BilinearPDF(uu, w);
             }
             return pdf;
@@ -867,7 +892,7 @@ struct Integrator {
             const vspg_sphere &sp = sc->d->spheres[l.shape_index];
             V3 pCenter(sp.center);
             if (DistanceSquared(ctx.p, pCenter) <= Sqr(sp.radius)) {
-                float r = (1 / sc->sphereArea[l.shape_index]) / (AbsDot(hit.n, -wi) / DistanceSquared(ctx.p, hit.p));
+                float r = (1 / sc->sphereArea[l.shape_index]) / (AbsDotN(hit.n, -wi) / DistanceSquared(ctx.p, hit.p));
                 return std::isinf(r) ? 0 : r;
             }
             float sin2ThetaMax = sp.radius * sp.radius / DistanceSquared(ctx.p, pCenter);
@@ -884,8 +909,8 @@ struct Integrator {
             // shapes.cpp:1352-1368 PDF for a sample in the spherical rectangle
             float sp = 1 / SphericalQuadArea(v00, v10, v11, v01);
             if (!(ctx.ns.x == 0 && ctx.ns.y == 0 && ctx.ns.z == 0)) {
-                float w[4] = {std::max<float>(0.01, AbsDot(v00, ctx.ns)), std::max<float>(0.01, AbsDot(v10, ctx.ns)),
-                              std::max<float>(0.01, AbsDot(v01, ctx.ns)), std::max<float>(0.01, AbsDot(v11, ctx.ns))};
+                float w[4] = {std::max<float>(0.01, AbsDotN(v00, ctx.ns)), std::max<float>(0.01, AbsDotN(v10, ctx.ns)),
+                              std::max<float>(0.01, AbsDotN(v01, ctx.ns)), std::max<float>(0.01, AbsDotN(v11, ctx.ns))};
                 float uu[2];
                 InvertSphericalRectangleSample(ctx.p, p00, p10 - p00, p01 - p00, hit.p, uu);
                 return BilinearPDF(uu, w) * sp;
@@ -901,7 +926,7 @@ struct Integrator {
         V3 dpdu = pu1 - pu0;
         V3 dpdv = LerpV(hit.uv[0], p01, p11) - LerpV(hit.uv[0], p00, p10);
         float pdfA = pdf / Length(Cross(dpdu, dpdv));
-        float r = pdfA * (DistanceSquared(ctx.p, hit.p) / AbsDot(hit.n, -wi));
+        float r = pdfA * (DistanceSquared(ctx.p, hit.p) / AbsDotN(hit.n, -wi));
         return std::isinf(r) ? 0 : r;
     }
 
@@ -924,11 +949,12 @@ struct Integrator {
         float uLight[2]; sampler.Get2D(uLight);
         if (light < 0) return S3(0.f);
         LiSample ls = SampleLi(light, ctx, uLight);
+        if (getenv("ORC_TRACE")) fprintf(stderr, "SampleLd surface=%d ctx.p=%.9g %.9g %.9g n=%.9g %.9g %.9g ns=%.9g %.9g %.9g light=%d u=%.9g %.9g valid=%d pdf=%.9g wi=%.9g %.9g %.9g pL=%.9g %.9g %.9g L=%g %g %g\n", (int)surface, ctx.p.x, ctx.p.y, ctx.p.z, ctx.n.x, ctx.n.y, ctx.n.z, ctx.ns.x, ctx.ns.y, ctx.ns.z, light, uLight[0], uLight[1], (int)ls.valid, ls.pdf, ls.wi.x, ls.wi.y, ls.wi.z, ls.pLight.x, ls.pLight.y, ls.pLight.z, ls.L[0], ls.L[1], ls.L[2]);
         if (!ls.valid || !ls.L || ls.pdf == 0) return S3(0.f);
         float p_l = pmf * ls.pdf;
         float scatterPDF; S3 f_hat;
         V3 wi = ls.wi;
-        if (surface) { f_hat = gb->f(wo, wi) * AbsDot(wi, si->ns); scatterPDF = 1.0f * gb->PDF(wo, wi); }
+        if (surface) { f_hat = gb->f(wo, wi) * AbsDotN(wi, si->ns); scatterPDF = 1.0f * gb->PDF(wo, wi); }
         else { f_hat = S3(gp->p(wo, wi)); scatterPDF = 1.0f * gp->PDF(wo, wi); }
         if (!f_hat) return S3(0.f);
         // Ray lightRay = intr.SpawnRayTo(ls->pLight)   (interaction.h:105-109 -> ray.h:104-109, both ends offset)
@@ -945,6 +971,7 @@ struct Integrator {
         cnt.shadow++;
         while (lightRay.d != V3(0, 0, 0)) {
             Hit h = sc->Intersect(lightRay.o, lightRay.d, 1 - ShadowEpsilon);
+            if (getenv("ORC_TRACE")) fprintf(stderr, "  lightRay o=%.9g %.9g %.9g d=%.9g %.9g %.9g medium=%d hit=%d t=%.9g mat=%d f_hat=%g scatterPDF=%g\n", lightRay.o.x, lightRay.o.y, lightRay.o.z, lightRay.d.x, lightRay.d.y, lightRay.d.z, lightRay.medium, (int)h.valid, h.valid ? h.t : -1.f, h.valid ? sc->HitMaterial(h) : -9, f_hat[0], scatterPDF);
             if (h.valid && sc->HitMaterial(h) >= 0) return S3(0.f);
             if (lightRay.medium >= 0) {
                 float tMax = h.valid ? h.t : (1 - ShadowEpsilon);
@@ -1249,7 +1276,7 @@ struct Integrator {
             if (!bs.valid) break;
             ps.lastVertexVolume = false;
             ps.rr_correction *= bs.pdf / bs.bsdfPdf;
-            S3 bsdfWeight = bs.f * AbsDot(bs.wi, isect.ns) / bs.pdf;
+            S3 bsdfWeight = bs.f * AbsDotN(bs.wi, isect.ns) / bs.pdf;
             ps.beta *= bsdfWeight;
             ps.r_l = ps.r_u / bs.misPdf;
             ps.specularBounce = false; ps.anyNonSpecularBounces = true;

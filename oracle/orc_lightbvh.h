@@ -161,7 +161,7 @@ struct CompactLightBounds {
         if (cosThetap <= cosTheta_e) return 0;
         float importance = phi * cosThetap / d2;
         if (n != V3(0, 0, 0)) {
-            float cosTheta_i = AbsDot(wi, n);
+            float cosTheta_i = AbsDotN(wi, n);
             float sinTheta_i = SafeSqrt(1 - Sqr(cosTheta_i));
             float cosThetap_i = cosSubClamped(sinTheta_i, cosTheta_i, sinTheta_b, cosTheta_b);
             importance *= cosThetap_i;

@@ -95,6 +95,16 @@ inline bool operator==(V3 a, V3 b) { return a.x == b.x && a.y == b.y && a.z == b
 inline bool operator!=(V3 a, V3 b) { return !(a == b); }
 inline float Dot(V3 a, V3 b) { return a.x * b.x + a.y * b.y + a.z * b.z; }  // vecmath.h:964
 inline float AbsDot(V3 a, V3 b) { return std::abs(Dot(a, b)); }
+// Any Dot with a Normal3 operand is a different function in the reference (vecmath.h:1056-1077):
+// FMA(n.x, v.x, SumOfProducts(n.y, v.y, n.z, v.z)), with SumOfProducts the error-compensated form of math.h:577-582.
+inline float SumOfProducts(float a, float b, float c, float d) {
+    float cd = c * d;
+    float sop = FMA(a, b, cd);
+    float err = FMA(c, d, -cd);
+    return sop + err;
+}
+inline float DotN(V3 a, V3 b) { return FMA(a.x, b.x, SumOfProducts(a.y, b.y, a.z, b.z)); }
+inline float AbsDotN(V3 a, V3 b) { return std::abs(DotN(a, b)); }
 inline V3 Cross(V3 v, V3 w) {  // vecmath.h:999
     return {DifferenceOfProducts(v.y, w.z, v.z, w.y), DifferenceOfProducts(v.z, w.x, v.x, w.z),
             DifferenceOfProducts(v.x, w.y, v.y, w.x)};

@@ -106,12 +106,6 @@ inline void InvertSphericalRectangleSample(V3 pRef, V3 s, V3 ex, V3 ey, V3 pRect
 // ---------------------------------------------------------------------------------------------------- triangles
 constexpr float MinSphericalSampleAreaTri = 3e-4f, MaxSphericalSampleAreaTri = 6.22f;   // shapes.h:1190-1191
 
-inline float SumOfProducts(float a, float b, float c, float d) {  // util/math.h:577-582
-    float cd = c * d;
-    float sop = FMA(a, b, cd);
-    float err = FMA(c, d, -cd);
-    return sop + err;
-}
 inline V3 GramSchmidt(V3 v, V3 w) { return v - Dot(v, w) * w; }   // vecmath.h:994
 inline float SphericalTriangleArea(V3 a, V3 b, V3 c) {            // vecmath.h:1638-1641
     return std::abs(2 * std::atan2(Dot(a, Cross(b, c)), 1 + Dot(a, b) + Dot(a, c) + Dot(b, c)));

@@ -50,6 +50,7 @@ using namespace pbrt;
 namespace {
 struct RefScene {
     std::unique_ptr<BasicScene> scene;
+    std::unique_ptr<BasicSceneBuilder> builder;   // owns the transform cache the shapes point into: lives as long as the scene
     std::map<std::string, Medium> media;
     NamedTextures textures;
     std::map<int, pstd::vector<Light> *> shapeIndexToAreaLights;
@@ -85,11 +86,9 @@ void *refp_open(const char *scene_file) {
     if (!g_inited) return nullptr;
     auto *rs = new RefScene;
     rs->scene = std::make_unique<BasicScene>();
-    {
-        BasicSceneBuilder builder(rs->scene.get());
-        std::vector<std::string> files{std::string(scene_file)};
-        ParseFiles(&builder, files);
-    }
+    rs->builder = std::make_unique<BasicSceneBuilder>(rs->scene.get());
+    std::vector<std::string> files{std::string(scene_file)};
+    ParseFiles(rs->builder.get(), files);
     BasicScene &ps = *rs->scene;
     rs->media = ps.CreateMedia();
     rs->textures = ps.CreateTextures();
@@ -163,6 +162,7 @@ int refp_pixel_sample(void *h, int px, int py, int sampleIndex, float *out) {
         Float rayDiffScale = std::max<Float>(.125f, 1 / std::sqrt((Float)sampler.SamplesPerPixel()));
         cr->ray.ScaleDifferentials(rayDiffScale);
         L = cr->weight * ri->Li({px, py}, cr->ray, lambda, sampler, rs->scratch, nullptr);
+        out[4] = L[0]; out[5] = L[1]; out[6] = L[2]; out[7] = L.y(lambda);
         if (L.HasNaNs() || IsInf(L.y(lambda))) L = SampledSpectrum(0.f);
         rs->scratch.Reset();
     }
@@ -189,6 +189,138 @@ int refp_intersect(void *h, int n, const float *rays7, int *hit, float *out10) {
             o[7] = si->intr.shading.n.x; o[8] = si->intr.shading.n.y; o[9] = si->intr.shading.n.z;
         }
     }
+    return 0;
+}
+
+// Light::SampleLi(ctx, u, lambda, true) (lights.cpp:796-818) then Light::PDF_Li(ctx, wi, true) (:820-824), same layout as
+// vspg_debug_sample_li: ctx9 = p, n, ns; out12 = valid, pdf, wi, pLight, L, PDF_Li(ctx, wi).
+int refp_sample_li(void *h, int n, const float *ctx9, const int *light, const float *u2, float *out12) {
+    RefScene *rs = (RefScene *)h;
+    SampledWavelengths lambda = rs->camera.GetFilm().SampleWavelengths(0.1f);
+    for (int i = 0; i < n; ++i) {
+        const float *c = ctx9 + 9 * i;
+        LightSampleContext ctx(Point3fi(Point3f(c[0], c[1], c[2])), Normal3f(c[3], c[4], c[5]), Normal3f(c[6], c[7], c[8]));
+        float *o = out12 + 12 * i;
+        for (int k = 0; k < 12; ++k) o[k] = 0;
+        o[11] = -1;
+        if (light[i] < 0 || light[i] >= (int)rs->lights.size()) return 1;
+        Light l = rs->lights[light[i]];
+        pstd::optional<LightLiSample> ls = l.SampleLi(ctx, Point2f(u2[2 * i], u2[2 * i + 1]), lambda, true);
+        if (!ls || !ls->L || ls->pdf == 0) continue;
+        o[0] = 1; o[1] = ls->pdf;
+        o[2] = ls->wi.x; o[3] = ls->wi.y; o[4] = ls->wi.z;
+        Point3f pl = ls->pLight.p();
+        o[5] = pl.x; o[6] = pl.y; o[7] = pl.z;
+        o[8] = ls->L[0]; o[9] = ls->L[1]; o[10] = ls->L[2];
+        o[11] = l.PDF_Li(ctx, ls->wi, true);
+    }
+    return 0;
+}
+
+// SampleT_maj (media_sampleTMaj.h:39-117) on medium `name` for the ray {o, d} up to tMax (in units of |d|), first sample u,
+// tracking RNG(seq, off), hero channel `ch`.  The callback records {p.xyz, sigma_a.rgb, sigma_s.rgb, sigma_maj.rgb,
+// T_maj.rgb} (15 floats) per tentative collision and returns true until `stop_after` collisions were seen (< 0: never
+// stops).  Returns the number of callbacks; out_final = returned T_maj.rgb + the next rng.Uniform<Float>().
+int refp_sample_tmaj(void *h, const char *name, const float *ray6, float tMax, float u, uint64_t seq, uint64_t off, int ch,
+                     int stop_after, int max_records, float *records15, float *out_final) {
+    RefScene *rs = (RefScene *)h;
+    auto it = rs->media.find(name);
+    if (it == rs->media.end()) return -1;
+    Ray ray(Point3f(ray6[0], ray6[1], ray6[2]), Vector3f(ray6[3], ray6[4], ray6[5]), 0.f, it->second);
+    SampledWavelengths lambda = rs->camera.GetFilm().SampleWavelengths((ch + 0.5f) / 3.f);
+    RNG rng(seq, off);
+    int n = 0;
+    SampledSpectrum T = SampleT_maj(ray, tMax, u, rng, lambda,
+                                    [&](Point3f p, MediumProperties mp, SampledSpectrum sigma_maj, SampledSpectrum T_maj) {
+                                        if (n < max_records) {
+                                            float *r = records15 + 15 * n;
+                                            r[0] = p.x; r[1] = p.y; r[2] = p.z;
+                                            for (int k = 0; k < 3; ++k) { r[3 + k] = mp.sigma_a[k]; r[6 + k] = mp.sigma_s[k]; r[9 + k] = sigma_maj[k]; r[12 + k] = T_maj[k]; }
+                                        }
+                                        ++n;
+                                        return stop_after < 0 || n < stop_after;
+                                    });
+    out_final[0] = T[0]; out_final[1] = T[1]; out_final[2] = T[2];
+    out_final[3] = rng.Uniform<Float>();
+    return n;
+}
+
+// GuidedVolPathVSPGIntegrator::SampleLd (guidedvolpathvspgintegrator.cpp:1136-1252) at one vertex, set up the way Li does
+// (:398-480 surface, :805-835 volume).  The sampler is IndependentSampler positioned at (pixel, sampleIndex, dim): the
+// guiding-lookup draw v, then SampleLd's own u, uLight come from it, so a restatement given the same position draws
+// the same numbers.
+//   surface vertex (is_surface = 1): ray6 = incoming ray {o, d}; the vertex is Intersect(ray).  Returns 2 when the ray
+//       misses or hits an interface (no BSDF).
+//   volume vertex  (is_surface = 0): ray6 = {p, d} with p the scattering point and d the incoming ray direction; the
+//       medium is `medium_name`, the phase function its HG(g) as SamplePoint returns it.
+// r_p3 = the path's r_u at the vertex, ch = hero channel.  out = Ld.rgb.
+int refp_sample_ld(void *h, int is_surface, const float *ray6, const char *medium_name, int px, int py, int sampleIndex, int dim,
+                   const float *r_p3, int ch, float *out) {
+    RefScene *rs = (RefScene *)h;
+    auto *integ = dynamic_cast<GuidedVolPathVSPGIntegrator *>(rs->integrator.get());
+    if (!integ) return 1;
+    Sampler sampler = rs->sampler.Clone(Allocator());
+    sampler.StartPixelSample({px, py}, sampleIndex, dim);
+    SampledWavelengths lambda = rs->camera.GetFilm().SampleWavelengths((ch + 0.5f) / 3.f);
+    SampledSpectrum r_p; r_p[0] = r_p3[0]; r_p[1] = r_p3[1]; r_p[2] = r_p3[2];
+    const auto &gs = integ->guideSettings;
+    auto *sdist = integ->guiding_threadSurfaceSamplingDistribution->Get();
+    auto *vdist = integ->guiding_threadVolumeSamplingDistribution->Get();
+    GuidedBSDF gbsdf(&sampler, integ->guiding_field, sdist, gs.guideSurface, gs.guideSecondaryVSP, gs.surfaceGuidingType);
+    GuidedPhaseFunction gphase(&sampler, integ->guiding_field, vdist, gs.guideVolume, gs.guideSecondaryVSP, gs.volumeGuidingType);
+    SampledSpectrum Ld(0.f);
+    if (is_surface) {
+        RayDifferential ray(Point3f(ray6[0], ray6[1], ray6[2]), Vector3f(ray6[3], ray6[4], ray6[5]));
+        if (medium_name && *medium_name) { auto it = rs->media.find(medium_name); if (it == rs->media.end()) return 3; ray.medium = it->second; }
+        pstd::optional<ShapeIntersection> si = integ->Intersect(ray);
+        if (!si) return 2;
+        SurfaceInteraction &isect = si->intr;
+        BSDF bsdf = isect.GetBSDF(ray, lambda, rs->camera, rs->scratch, sampler);
+        if (!bsdf) return 2;
+        Float v = sampler.Get1D();
+        gbsdf.init(&bsdf, ray, si, v);
+        Ld = integ->SampleLd(isect, &gbsdf, nullptr, 1.0f, lambda, sampler, r_p);
+        rs->scratch.Reset();
+    } else {
+        auto it = rs->media.find(medium_name ? medium_name : "");
+        if (it == rs->media.end()) return 3;
+        Point3f p(ray6[0], ray6[1], ray6[2]);
+        Vector3f d(ray6[3], ray6[4], ray6[5]);
+        MediumProperties mp = it->second.SamplePoint(p, lambda);
+        MediumInteraction intr(p, -d, 0.f, it->second, mp.phase);
+        Float v = sampler.Get1D();
+        gphase.init(&intr.phase, p, d, v);
+        Ld = integ->SampleLd(intr, nullptr, &gphase, 1.0f, lambda, sampler, r_p);
+    }
+    out[0] = Ld[0]; out[1] = Ld[1]; out[2] = Ld[2];
+    return 0;
+}
+
+// The geometric front half of SampleLd at a surface vertex, piece by piece, with the reference's own calls: the hit's
+// pi (point + error), n, shading.n, wo; ctx.pi = intr.OffsetRayOrigin(intr.wo); light.SampleLi(ctx, uLight); the
+// shadow ray intr.SpawnRayTo(ls->pLight) and the two hashes that seed its tracker.
+// out = p(3) pError(3) n(3) ns(3) wo(3) ctxp(3) pLight(3) nLight(3) ray.o(3) ray.d(3)  [30], then hash(o), hash(d) in out_hash.
+int refp_surface_nee_geometry(void *h, const float *ray6, int light, const float *uLight, float *out, uint64_t *out_hash) {
+    RefScene *rs = (RefScene *)h;
+    RayDifferential ray(Point3f(ray6[0], ray6[1], ray6[2]), Vector3f(ray6[3], ray6[4], ray6[5]));
+    pstd::optional<ShapeIntersection> si = rs->integrator->Intersect(ray);
+    if (!si) return 2;
+    SurfaceInteraction &isect = si->intr;
+    auto put = [&](int k, Float x, Float y, Float z) { out[3 * k] = x; out[3 * k + 1] = y; out[3 * k + 2] = z; };
+    Point3f p = isect.p(); Vector3f e = isect.pi.Error();
+    put(0, p.x, p.y, p.z); put(1, e.x, e.y, e.z); put(2, isect.n.x, isect.n.y, isect.n.z);
+    put(3, isect.shading.n.x, isect.shading.n.y, isect.shading.n.z); put(4, isect.wo.x, isect.wo.y, isect.wo.z);
+    LightSampleContext ctx(isect);
+    ctx.pi = isect.OffsetRayOrigin(isect.wo);
+    put(5, ctx.p().x, ctx.p().y, ctx.p().z);
+    SampledWavelengths lambda = rs->camera.GetFilm().SampleWavelengths(0.1f);
+    pstd::optional<LightLiSample> ls = rs->lights[light].SampleLi(ctx, Point2f(uLight[0], uLight[1]), lambda, true);
+    if (!ls) return 3;
+    Point3f pl = ls->pLight.p();
+    put(6, pl.x, pl.y, pl.z); put(7, ls->pLight.n.x, ls->pLight.n.y, ls->pLight.n.z);
+    Ray lr = isect.SpawnRayTo(ls->pLight);
+    put(8, lr.o.x, lr.o.y, lr.o.z); put(9, lr.d.x, lr.d.y, lr.d.z);
+    out_hash[0] = Hash(lr.o); out_hash[1] = Hash(lr.d);
     return 0;
 }
 

@@ -150,6 +150,62 @@ int orc_sample_li(const vspg_scene_desc *d, const vspg_integrator_params *ip, in
     return 0;
 }
 
+// SampleT_maj on medium `medium` of the scene: same contract as oracle/ref_harness/pbrt_harness.cpp refp_sample_tmaj.
+int orc_sample_tmaj(const vspg_scene_desc *d, int medium, const float *ray6, float tMax, float u, uint64_t seq, uint64_t off, int ch,
+                    int stop_after, int max_records, float *records15, float *out_final) {
+    if (medium < 0 || medium >= d->n_media) return -1;
+    Medium med; med.init(&d->media[medium], true);
+    Ray ray; ray.o = V3(ray6); ray.d = V3(ray6 + 3); ray.medium = medium;
+    RNG rng(seq, off);
+    int n = 0;
+    S3 T = SampleT_maj(med, ray, tMax, u, rng, ch, nullptr, [&](V3 p, const MediumProps &mp, S3 sigma_maj, S3 T_maj) {
+        if (n < max_records) {
+            float *r = records15 + 15 * n;
+            r[0] = p.x; r[1] = p.y; r[2] = p.z;
+            for (int k = 0; k < 3; ++k) { r[3 + k] = mp.sigma_a[k]; r[6 + k] = mp.sigma_s[k]; r[9 + k] = sigma_maj[k]; r[12 + k] = T_maj[k]; }
+        }
+        ++n;
+        return stop_after < 0 || n < stop_after;
+    });
+    out_final[0] = T[0]; out_final[1] = T[1]; out_final[2] = T[2];
+    out_final[3] = rng.Uniform();
+    return n;
+}
+
+// SampleLd at one vertex: same contract as oracle/ref_harness/pbrt_harness.cpp refp_sample_ld (medium = index, -1 none).
+int orc_sample_ld(const vspg_scene_desc *d, const vspg_guiding_desc *g, const vspg_integrator_params *ip, int is_surface, const float *ray6,
+                  int medium, int px, int py, int sampleIndex, int dim, int seed, const float *r_p3, int ch, float *out) {
+    Scene sc; sc.init(d, g, ip, true); sc.seed = seed;
+    Integrator in; in.sc = &sc;
+    Sampler sampler; sampler.StartPixelSample(px, py, seed, sampleIndex, dim);
+    GuidedBSDF gbsdf; gbsdf.sc = &sc; gbsdf.sampler = &sampler; gbsdf.enableGuiding = ip->surface_guiding;
+    gbsdf.enableScatterGuiding = ip->vsp_secondary_guiding; gbsdf.ris = ip->surface_guiding_ris;
+    GuidedPhase gphase; gphase.sc = &sc; gphase.sampler = &sampler; gphase.enableGuiding = ip->volume_guiding;
+    gphase.enableScatterGuiding = ip->vsp_secondary_guiding; gphase.ris = ip->volume_guiding_ris;
+    S3 r_p(r_p3[0], r_p3[1], r_p3[2]);
+    S3 Ld(0.f);
+    V3 ro(ray6), rd(ray6 + 3);
+    if (is_surface) {
+        Hit h = sc.Intersect(ro, rd, Infinity);
+        if (!h.valid) return 2;
+        SurfaceIntr isect = sc.MakeIntr(h, rd, medium);
+        if (isect.material < 0) return 2;
+        const vspg_material &mat = d->materials[isect.material];
+        gbsdf.setBSDF(isect.ns, isect.dpdu, S3(mat.reflectance));
+        float v = sampler.Get1D();
+        gbsdf.init(ro + h.t * rd, rd, isect.ns, v);
+        Ld = in.SampleLd(true, &isect, V3(), V3(), medium, &gbsdf, nullptr, sampler, r_p, ch);
+    } else {
+        if (medium < 0 || medium >= d->n_media) return 3;
+        MediumProps mp = sc.media[medium].SamplePoint(ro);
+        float v = sampler.Get1D();
+        gphase.init(mp.g, ro, rd, v);
+        Ld = in.SampleLd(false, nullptr, ro, -rd, medium, nullptr, &gphase, sampler, r_p, ch);
+    }
+    out[0] = Ld[0]; out[1] = Ld[1]; out[2] = Ld[2];
+    return 0;
+}
+
 // ------------------------------------------------------------- guiding
 int orc_cache_lookup(const vspg_field *f, int n, const float *pos3, const float *u, int *out_leaf, int *out_region, float *out_u) {
     for (int i = 0; i < n; i++) {

@@ -14,8 +14,9 @@
 // One process-wide difference, stated in the header: a requested store*/training run, or a load* whose file is
 // missing, is a hard error here (the reference would fall back to training a fresh cache on the CPU).
 //
-// Transforms are composed in double and rounded to float once at the end (the reference composes float matrices;
-// camera-matrix parity with the reference binary is unpinned).
+// Transforms are float (m, mInv) pairs composed with the reference's own compensated arithmetic (host_xform.h), so
+// camera matrices, render-space vertices and medium transforms equal the reference's bit for bit
+// (tests/test_ref_pbrt.py pins them against the reference's own objects).
 #include <cctype>
 #include <cerrno>
 #include <cmath>
@@ -31,6 +32,7 @@
 #include <vector>
 
 #include "../../include/vspg.h"
+#include "host_xform.h"
 
 namespace {
 
@@ -39,83 +41,14 @@ struct ParseError : std::runtime_error {
     ParseError(int c, const std::string &m) : std::runtime_error(m), code(c) {}
 };
 
-// ------------------------------------------------------------------------------------------------ 4x4 double
-struct M4 {
-    double m[4][4];
-    static M4 identity() { M4 r; for (int i = 0; i < 4; i++) for (int j = 0; j < 4; j++) r.m[i][j] = i == j; return r; }
-};
-M4 mul(const M4 &a, const M4 &b) {
-    M4 r;
-    for (int i = 0; i < 4; i++)
-        for (int j = 0; j < 4; j++) {
-            double s = 0;
-            for (int k = 0; k < 4; k++) s += a.m[i][k] * b.m[k][j];
-            r.m[i][j] = s;
-        }
-    return r;
-}
-M4 inverse(const M4 &a) {  // Gauss-Jordan with partial pivoting
-    double w[4][8];
-    for (int i = 0; i < 4; i++)
-        for (int j = 0; j < 4; j++) { w[i][j] = a.m[i][j]; w[i][j + 4] = i == j; }
-    for (int c = 0; c < 4; c++) {
-        int p = c;
-        for (int r = c + 1; r < 4; r++) if (std::fabs(w[r][c]) > std::fabs(w[p][c])) p = r;
-        if (w[p][c] == 0) throw ParseError(VSPG_ERR_INVALID, "singular transformation matrix");
-        if (p != c) for (int j = 0; j < 8; j++) std::swap(w[p][j], w[c][j]);
-        double d = w[c][c];
-        for (int j = 0; j < 8; j++) w[c][j] /= d;
-        for (int r = 0; r < 4; r++) if (r != c) {
-            double f = w[r][c];
-            if (f != 0) for (int j = 0; j < 8; j++) w[r][j] -= f * w[c][j];
-        }
-    }
-    M4 r;
-    for (int i = 0; i < 4; i++) for (int j = 0; j < 4; j++) r.m[i][j] = w[i][j + 4];
-    return r;
-}
-M4 translate(double x, double y, double z) { M4 r = M4::identity(); r.m[0][3] = x; r.m[1][3] = y; r.m[2][3] = z; return r; }
-M4 scale(double x, double y, double z) { M4 r = M4::identity(); r.m[0][0] = x; r.m[1][1] = y; r.m[2][2] = z; return r; }
-M4 rotate(double deg, double x, double y, double z) {  // util/transform.cpp Rotate(theta, axis)
-    double l = std::sqrt(x * x + y * y + z * z);
-    if (l == 0) throw ParseError(VSPG_ERR_INVALID, "Rotate: zero-length axis");
-    x /= l; y /= l; z /= l;
-    double t = deg * M_PI / 180.0, s = std::sin(t), c = std::cos(t);
-    M4 r = M4::identity();
-    r.m[0][0] = x * x + (1 - x * x) * c; r.m[0][1] = x * y * (1 - c) - z * s; r.m[0][2] = x * z * (1 - c) + y * s;
-    r.m[1][0] = x * y * (1 - c) + z * s; r.m[1][1] = y * y + (1 - y * y) * c; r.m[1][2] = y * z * (1 - c) - x * s;
-    r.m[2][0] = x * z * (1 - c) - y * s; r.m[2][1] = y * z * (1 - c) + x * s; r.m[2][2] = z * z + (1 - z * z) * c;
-    return r;
-}
-void xpoint(const M4 &t, const double p[3], double out[3]) {
-    double r[4];
-    for (int i = 0; i < 4; i++) r[i] = t.m[i][0] * p[0] + t.m[i][1] * p[1] + t.m[i][2] * p[2] + t.m[i][3];
-    double w = r[3] == 0 ? 1 : r[3];
-    for (int i = 0; i < 3; i++) out[i] = r[i] / w;
-}
-void xvector(const M4 &t, const double v[3], double out[3]) {
-    for (int i = 0; i < 3; i++) out[i] = t.m[i][0] * v[0] + t.m[i][1] * v[1] + t.m[i][2] * v[2];
-}
-double det3(const M4 &t) {
-    return t.m[0][0] * (t.m[1][1] * t.m[2][2] - t.m[1][2] * t.m[2][1]) - t.m[0][1] * (t.m[1][0] * t.m[2][2] - t.m[1][2] * t.m[2][0]) +
-           t.m[0][2] * (t.m[1][0] * t.m[2][1] - t.m[1][1] * t.m[2][0]);
-}
-vspg_transform to_abi(const M4 &t) {
+// ------------------------------------------------------------------------------------------------ transforms
+using xf::XF;
+using xf::M4f;
+vspg_transform to_abi(const XF &t) {
     vspg_transform r;
-    M4 ti = inverse(t);
-    for (int i = 0; i < 4; i++) for (int j = 0; j < 4; j++) { r.m[i][j] = (float)t.m[i][j]; r.mInv[i][j] = (float)ti.m[i][j]; }
+    for (int i = 0; i < 4; i++) for (int j = 0; j < 4; j++) { r.m[i][j] = t.m.m[i][j]; r.mInv[i][j] = t.inv.m[i][j]; }
     return r;
 }
-
-// A transformation and its inverse carried together, as pbrt::Transform does (util/transform.h): LookAt / Translate /
-// Scale / Rotate know their inverses analytically, so the camera position is exactly the LookAt eye point.
-struct XF {
-    M4 m = M4::identity(), inv = M4::identity();
-    XF() = default;
-    XF(const M4 &a, const M4 &ai) : m(a), inv(ai) {}
-    explicit XF(const M4 &a) : m(a), inv(inverse(a)) {}
-};
-XF operator*(const XF &a, const XF &b) { return XF(mul(a.m, b.m), mul(b.inv, a.inv)); }
 
 // ------------------------------------------------------------------------------------------------ tokens
 struct Tok { enum K { END, WORD, STR, LB, RB } kind = END; std::string s; int line = 0; };
@@ -327,10 +260,10 @@ struct vspg_host_scene {
     std::map<std::string, int> medium_ids, named_materials;
     std::map<std::string, XF> named_cs;
     std::vector<GState> stack; GState gs;
-    M4 world_from_camera = M4::identity(); double eye[3] = {0, 0, 0};
+    XF world_from_camera, render_from_world; float eye[3] = {0, 0, 0};
     std::string camera_medium;
     bool have_camera = false, world = false, have_integrator = false;
-    double fov = 90, lens_radius = 0, focal_distance = 1e6, frame_aspect = -1; std::vector<double> screen_window;
+    float fov = 90, lens_radius = 0, focal_distance = 1e6f, frame_aspect = -1; std::vector<double> screen_window;
     int xres = 1280, yres = 720; float iso = 100, exposure = 1, max_comp = INFINITY;
     int filter_type = 1; float filter_r[2] = {1.5f, 1.5f}, filter_sigma = 0.5f;   // pbrt's default filter is "gaussian"
     std::string guiding_cache_file, isg_file, tr_file; bool load_cache = false, load_isg = false, load_tr = false, store_tr = false;
@@ -345,31 +278,38 @@ struct Builder {
     explicit Builder(vspg_host_scene &s) : S(s) {}
 
     std::string resolve(const std::string &f) const { return (!f.empty() && f[0] == '/') ? f : S.base_dir + "/" + f; }
-    M4 render_from_object() const { return mul(translate(-S.eye[0], -S.eye[1], -S.eye[2]), S.gs.ctm.m); }
+    // scene.h:477-479: Transform((renderFromWorld * ctm).GetMatrix()) -- the inverse is re-derived from the product
+    XF render_from_object() const { return XF(xf::mul(S.render_from_world.m, S.gs.ctm.m)); }
     int medium_id(const std::string &name, const Lexer &lx) const {
         if (name.empty()) return -1;
         auto it = S.medium_ids.find(name);
         if (it == S.medium_ids.end()) lx.fail("medium \"" + name + "\" is not defined");
         return it->second;
     }
-    void to_render(const M4 &rfo, const double p[3], float out[3]) const { double r[3]; xpoint(rfo, p, r); for (int i = 0; i < 3; i++) out[i] = (float)r[i]; }
+    void to_render(const XF &rfo, const double p[3], float out[3]) const {
+        float pf[3] = {(float)p[0], (float)p[1], (float)p[2]};   // the parser hands Float values to the shapes (parser.cpp)
+        xf::apply_point(rfo.m, pf, out);
+    }
 
     float *own(std::vector<float> &&v) { S.arrays.emplace_back(new std::vector<float>(std::move(v))); return S.arrays.back()->data(); }
 
     // ---------------------------------------------------------------- directives
     void camera(const std::string &type, const Params &ps, Lexer &lx) {
         if (type != "perspective") lx.fail("Camera \"" + type + "\": only \"perspective\" is on the supported path", VSPG_ERR_UNSUPPORTED);
-        S.fov = ps.one_float("fov", 90);
-        S.lens_radius = ps.one_float("lensradius", 0);
-        S.focal_distance = ps.one_float("focaldistance", 1e6);
-        S.frame_aspect = ps.one_float("frameaspectratio", -1);
+        S.fov = (float)ps.one_float("fov", 90);
+        S.lens_radius = (float)ps.one_float("lensradius", 0);
+        S.focal_distance = (float)ps.one_float("focaldistance", 1e6);
+        S.frame_aspect = (float)ps.one_float("frameaspectratio", -1);
         if (const auto *sw = ps.floats("screenwindow")) { if (sw->size() != 4) lx.fail("\"screenwindow\" expects 4 values"); S.screen_window = *sw; }
         ps.one_float("shutteropen", 0); ps.one_float("shutterclose", 1);   // no motion on this path
         ps.report_unused();
-        S.world_from_camera = S.gs.ctm.inv;
-        double o[3] = {0, 0, 0};
-        xpoint(S.world_from_camera, o, S.eye);
-        S.named_cs["camera"] = XF(S.gs.ctm.inv, S.gs.ctm.m);
+        // scene.cpp:139-156 + CameraTransform (cameras.cpp:26-57), rendering space "cameraworld" (the default):
+        // worldFromRender = Translate(worldFromCamera(0,0,0)), renderFromWorld = its inverse
+        S.world_from_camera = xf::inverse(S.gs.ctm);
+        const float o[3] = {0, 0, 0};
+        xf::apply_point(S.world_from_camera.m, o, S.eye);
+        S.render_from_world = xf::inverse(xf::translate(S.eye[0], S.eye[1], S.eye[2]));
+        S.named_cs["camera"] = xf::inverse(S.gs.ctm);
         S.camera_medium = S.gs.outside;
         S.have_camera = true;
     }
@@ -540,36 +480,47 @@ struct Builder {
         l.shape_index = -1; l.medium = -1;
         float L[3] = {1, 1, 1};   // RGB build: the colour space's illuminant samples to (1,1,1)
         float sc = (float)ps.one_float("scale", 1);
-        M4 rfl = render_from_object();
+        XF rfl = render_from_object();
         if (type == "point") {
             l.type = VSPG_LIGHT_POINT;
             ps.rgb("I", L);
             double from[3] = {0, 0, 0};
             ps.point3("from", from);
-            double pw = ps.one_float("power", -1);
-            if (pw > 0) sc *= (float)(pw / (4 * M_PI));   // lights.cpp PointLight::Create: k_e = 4 Pi (photometric == 1)
+            float pw = (float)ps.one_float("power", -1);
+            if (pw > 0) sc *= pw / (4 * 3.14159265358979323846f);   // lights.cpp:234-238 PointLight::Create: k_e = 4 Pi (photometric == 1)
+            // lights.cpp:240-242: finalRenderFromLight = renderFromLight * Translate(from); the light sits at its origin
             const double origin[3] = {0, 0, 0};
-            to_render(mul(rfl, translate(from[0], from[1], from[2])), origin, l.pos);
+            to_render(rfl * xf::translate((float)from[0], (float)from[1], (float)from[2]), origin, l.pos);
             l.medium = medium_id(S.gs.outside, lx);
         } else if (type == "distant") {
             l.type = VSPG_LIGHT_DISTANT;
             ps.rgb("L", L);
             double from[3] = {0, 0, 0}, to[3] = {0, 0, 1};
             ps.point3("from", from); ps.point3("to", to);
-            double ev = ps.one_float("illuminance", -1);
-            if (ev > 0) sc *= (float)ev;
-            double w[3] = {from[0] - to[0], from[1] - to[1], from[2] - to[2]}, wr[3];
-            xvector(rfl, w, wr);
-            double len = std::sqrt(wr[0] * wr[0] + wr[1] * wr[1] + wr[2] * wr[2]);
-            if (len == 0) lx.fail("distant light: from == to");
-            for (int i = 0; i < 3; i++) l.pos[i] = (float)(wr[i] / len);
+            float ev = (float)ps.one_float("illuminance", -1);
+            if (ev > 0) sc *= ev;
+            // lights.cpp:289-298: w = Normalize(from - to) becomes the z column of a frame t; finalRenderFromLight =
+            // renderFromLight * t; the light direction is Normalize(finalRenderFromLight(Vector3f(0,0,1))) (lights.cpp:259)
+            float w[3] = {(float)from[0] - (float)to[0], (float)from[1] - (float)to[1], (float)from[2] - (float)to[2]};
+            if (xf::length3(w[0], w[1], w[2]) == 0) lx.fail("distant light: from == to");
+            xf::normalize3(w);
+            M4f t = M4f::identity();
+            float sign = std::copysign(1.f, w[2]), ca = -1 / (sign + w[2]), cb = w[0] * w[1] * ca;   // CoordinateSystem (util/vecmath.h:1007-1013)
+            float v1[3] = {1 + sign * (w[0] * w[0]) * ca, sign * cb, -sign * w[0]}, v2[3] = {cb, sign + (w[1] * w[1]) * ca, -w[1]};
+            for (int i = 0; i < 3; i++) { t.m[i][0] = v1[i]; t.m[i][1] = v2[i]; t.m[i][2] = w[i]; }
+            M4f fin = xf::mul(rfl.m, t);
+            const float z[3] = {0, 0, 1};
+            float wr[3];
+            xf::apply_vector(fin, z, wr);
+            xf::normalize3(wr);
+            for (int i = 0; i < 3; i++) l.pos[i] = wr[i];
         } else if (type == "infinite") {
             l.type = VSPG_LIGHT_UNIFORM_INFINITE;
             ps.rgb("L", L);
             if (!ps.one_string("filename", "").empty() || ps.find("portal", {"point3", "point"}))
                 lx.fail("image / portal infinite lights are outside the hot-path scope (SURVEY 8f3)", VSPG_ERR_UNSUPPORTED);
-            double ev = ps.one_float("illuminance", -1);
-            if (ev > 0) sc *= (float)(ev / M_PI);
+            float ev = (float)ps.one_float("illuminance", -1);
+            if (ev > 0) sc *= ev / 3.14159265358979323846f;
         } else lx.fail("LightSource \"" + type + "\": supported types are point, distant, infinite (uniform)", VSPG_ERR_UNSUPPORTED);
         ps.report_unused();
         for (int i = 0; i < 3; i++) l.L[i] = L[i] * sc;
@@ -591,7 +542,7 @@ struct Builder {
 
     // shared per-shape attributes (scene.cpp BasicSceneBuilder::Shape + cpu/render.cpp primitive creation)
     struct ShapeAttr { int material, area_light, mi, mo, has_interface, flip; };
-    ShapeAttr shape_attr(Lexer &lx, const M4 &rfo) {
+    ShapeAttr shape_attr(Lexer &lx, const XF &rfo) {
         ShapeAttr a;
         a.material = S.gs.material;
         a.area_light = -1;
@@ -599,7 +550,7 @@ struct Builder {
         // interaction.h:117-121 / primitive.h GeometricPrimitive: a MediumInterface is attached only when it
         // marks a transition (inside != outside); otherwise rays keep their current medium.
         a.has_interface = (a.mi != a.mo) ? 1 : 0;
-        a.flip = (S.gs.reverse ? 1 : 0) ^ (det3(rfo) < 0 ? 1 : 0);
+        a.flip = (S.gs.reverse ? 1 : 0) ^ (xf::det3(rfo.m) < 0 ? 1 : 0);   // Transform::SwapsHandedness
         return a;
     }
     int attach_area_light(int kind, int index, float area, Lexer &lx) {
@@ -625,7 +576,7 @@ float tri_area(const float *a, const float *b, const float *c) {
 }
 
 void Builder::shape(const std::string &type, const Params &ps, Lexer &lx) {
-    M4 rfo = render_from_object();
+    XF rfo = render_from_object();
     ShapeAttr a = shape_attr(lx, rfo);
     if (ps.find("alpha", {"texture", "float"})) lx.fail("Shape: alpha textures are not supported", VSPG_ERR_UNSUPPORTED);
     if (type == "bilinearmesh") {
@@ -684,9 +635,9 @@ void Builder::shape(const std::string &type, const Params &ps, Lexer &lx) {
         ps.report_unused();
         if (zmin > -r || zmax < r || phimax < 360) lx.fail("sphere: partial spheres are not supported", VSPG_ERR_UNSUPPORTED);
         // object space must be translate(center) * uniform scale: the sphere stays a sphere in render space
-        double sx = std::sqrt(rfo.m[0][0] * rfo.m[0][0] + rfo.m[1][0] * rfo.m[1][0] + rfo.m[2][0] * rfo.m[2][0]);
-        double sy = std::sqrt(rfo.m[0][1] * rfo.m[0][1] + rfo.m[1][1] * rfo.m[1][1] + rfo.m[2][1] * rfo.m[2][1]);
-        double sz = std::sqrt(rfo.m[0][2] * rfo.m[0][2] + rfo.m[1][2] * rfo.m[1][2] + rfo.m[2][2] * rfo.m[2][2]);
+        double sx = std::sqrt((double)rfo.m.m[0][0] * (double)rfo.m.m[0][0] + (double)rfo.m.m[1][0] * (double)rfo.m.m[1][0] + (double)rfo.m.m[2][0] * (double)rfo.m.m[2][0]);
+        double sy = std::sqrt((double)rfo.m.m[0][1] * (double)rfo.m.m[0][1] + (double)rfo.m.m[1][1] * (double)rfo.m.m[1][1] + (double)rfo.m.m[2][1] * (double)rfo.m.m[2][1]);
+        double sz = std::sqrt((double)rfo.m.m[0][2] * (double)rfo.m.m[0][2] + (double)rfo.m.m[1][2] * (double)rfo.m.m[1][2] + (double)rfo.m.m[2][2] * (double)rfo.m.m[2][2]);
         if (std::fabs(sx - sy) > 1e-6 * sx || std::fabs(sx - sz) > 1e-6 * sx) lx.fail("sphere: non-uniform scaling is not supported", VSPG_ERR_UNSUPPORTED);
         vspg_sphere d{};
         const double origin[3] = {0, 0, 0};
@@ -712,15 +663,19 @@ std::string str(Lexer &lx, const char *what) {
     if (t.kind != Tok::STR) lx.fail(std::string(what) + ": expected a quoted string");
     return t.s;
 }
-M4 matrix16(Lexer &lx, const char *what) {
+XF matrix16(Lexer &lx, const char *what) {
     bool br = lx.peek().kind == Tok::LB;
     if (br) lx.next();
     double v[16];
     for (double &x : v) x = num(lx, what);
     if (br && lx.next().kind != Tok::RB) lx.fail(std::string(what) + ": expected ]");
-    M4 m;   // pbrt files give matrices column-major (parser.cpp: Transpose(Transform(m)))
-    for (int i = 0; i < 4; i++) for (int j = 0; j < 4; j++) m.m[i][j] = v[4 * j + i];
-    return m;
+    // scene.cpp:583-593: Transpose(Transform(SquareMatrix<4>(tr))) -- the inverse is taken of the matrix as given
+    // (row-major), then both are transposed (pbrt files list matrices column-major)
+    M4f m;
+    for (int i = 0; i < 4; i++) for (int j = 0; j < 4; j++) m.m[i][j] = (float)v[4 * i + j];
+    XF t(m);
+    if (std::isnan(t.inv.m[0][0])) lx.fail(std::string(what) + ": singular transformation matrix");
+    return xf::transpose(t);
 }
 
 void run(Lexer &lx, Builder &B, int depth);
@@ -754,29 +709,23 @@ void directive(Lexer &lx, Builder &B, int depth, const Tok &t) {
         auto pre_world = [&] { if (S.world) lx.fail(d + " is not allowed after WorldBegin"); };
         auto in_world = [&] { if (!S.world) lx.fail(d + " is not allowed before WorldBegin"); };
         if (d == "Identity") S.gs.ctm = XF();
-        else if (d == "Translate") { double x = num(lx, "Translate"), y = num(lx, "Translate"), z = num(lx, "Translate"); S.gs.ctm = S.gs.ctm * XF(translate(x, y, z), translate(-x, -y, -z)); }
-        else if (d == "Scale") { double x = num(lx, "Scale"), y = num(lx, "Scale"), z = num(lx, "Scale"); if (x == 0 || y == 0 || z == 0) lx.fail("Scale: zero factor"); S.gs.ctm = S.gs.ctm * XF(scale(x, y, z), scale(1 / x, 1 / y, 1 / z)); }
-        else if (d == "Rotate") { double a = num(lx, "Rotate"), x = num(lx, "Rotate"), y = num(lx, "Rotate"), z = num(lx, "Rotate"); S.gs.ctm = S.gs.ctm * XF(rotate(a, x, y, z), rotate(-a, x, y, z)); }
-        else if (d == "Transform") S.gs.ctm = XF(matrix16(lx, "Transform"));
-        else if (d == "ConcatTransform") S.gs.ctm = S.gs.ctm * XF(matrix16(lx, "ConcatTransform"));
+        else if (d == "Translate") { float x = (float)num(lx, "Translate"), y = (float)num(lx, "Translate"), z = (float)num(lx, "Translate"); S.gs.ctm = S.gs.ctm * xf::translate(x, y, z); }
+        else if (d == "Scale") { float x = (float)num(lx, "Scale"), y = (float)num(lx, "Scale"), z = (float)num(lx, "Scale"); if (x == 0 || y == 0 || z == 0) lx.fail("Scale: zero factor"); S.gs.ctm = S.gs.ctm * xf::scale(x, y, z); }
+        else if (d == "Rotate") {
+            float a = (float)num(lx, "Rotate"), x = (float)num(lx, "Rotate"), y = (float)num(lx, "Rotate"), z = (float)num(lx, "Rotate");
+            XF r;
+            if (!xf::rotate(a, x, y, z, &r)) lx.fail("Rotate: zero-length axis");
+            S.gs.ctm = S.gs.ctm * r;
+        }
+        else if (d == "Transform") S.gs.ctm = matrix16(lx, "Transform");
+        else if (d == "ConcatTransform") S.gs.ctm = S.gs.ctm * matrix16(lx, "ConcatTransform");
         else if (d == "LookAt") {
-            double v[9];
-            for (double &x : v) x = num(lx, "LookAt");
-            // util/transform.cpp LookAt: worldFromCamera columns = right, newUp, dir, pos; returns its inverse
-            double dir[3] = {v[3] - v[0], v[4] - v[1], v[5] - v[2]};
-            double dl = std::sqrt(dir[0] * dir[0] + dir[1] * dir[1] + dir[2] * dir[2]);
-            if (dl == 0) lx.fail("LookAt: eye and look-at point coincide");
-            for (double &x : dir) x /= dl;
-            double ul = std::sqrt(v[6] * v[6] + v[7] * v[7] + v[8] * v[8]);
-            double up[3] = {v[6] / ul, v[7] / ul, v[8] / ul};
-            double right[3] = {up[1] * dir[2] - up[2] * dir[1], up[2] * dir[0] - up[0] * dir[2], up[0] * dir[1] - up[1] * dir[0]};
-            double rl = std::sqrt(right[0] * right[0] + right[1] * right[1] + right[2] * right[2]);
-            if (rl == 0) lx.fail("LookAt: up vector and viewing direction are collinear");
-            for (double &x : right) x /= rl;
-            double nu[3] = {dir[1] * right[2] - dir[2] * right[1], dir[2] * right[0] - dir[0] * right[2], dir[0] * right[1] - dir[1] * right[0]};
-            M4 wfc = M4::identity();
-            for (int i = 0; i < 3; i++) { wfc.m[i][0] = right[i]; wfc.m[i][1] = nu[i]; wfc.m[i][2] = dir[i]; wfc.m[i][3] = v[i]; }
-            S.gs.ctm = S.gs.ctm * XF(inverse(wfc), wfc);
+            float v[9];
+            for (float &x : v) x = (float)num(lx, "LookAt");
+            if (v[0] == v[3] && v[1] == v[4] && v[2] == v[5]) lx.fail("LookAt: eye and look-at point coincide");
+            XF la;
+            if (!xf::look_at(v, v + 3, v + 6, &la)) lx.fail("LookAt: up vector and viewing direction are collinear");
+            S.gs.ctm = S.gs.ctm * la;
         }
         else if (d == "CoordinateSystem") S.named_cs[str(lx, "CoordinateSystem")] = S.gs.ctm;
         else if (d == "CoordSysTransform") {
@@ -855,23 +804,20 @@ void finish(vspg_host_scene &S) {
     }
     // ---- camera (cameras.h ProjectiveCamera ctor / cameras.cpp PerspectiveCamera::Create)
     vspg_camera &c = S.desc.camera;
-    double aspect = (double)S.xres / (double)S.yres;
-    double frame = S.frame_aspect > 0 ? S.frame_aspect : aspect;
-    double sw[4];
-    if (!S.screen_window.empty()) for (int i = 0; i < 4; i++) sw[i] = S.screen_window[i];
-    else if (frame > 1) { sw[0] = -frame; sw[1] = frame; sw[2] = -1; sw[3] = 1; }
-    else { sw[0] = -1; sw[1] = 1; sw[2] = -1 / frame; sw[3] = 1 / frame; }
-    const double n = 1e-2, f = 1000.0;
-    M4 persp = M4::identity();
-    persp.m[2][2] = f / (f - n); persp.m[2][3] = -f * n / (f - n); persp.m[3][2] = 1; persp.m[3][3] = 0;
-    double inv_tan = 1.0 / std::tan(S.fov * M_PI / 180.0 / 2);
-    M4 screen_from_camera = mul(scale(inv_tan, inv_tan, 1), persp);
-    M4 ndc_from_screen = mul(scale(1 / (sw[1] - sw[0]), 1 / (sw[3] - sw[2]), 1), translate(-sw[0], -sw[3], 0));
-    M4 raster_from_screen = mul(scale(S.xres, -S.yres, 1), ndc_from_screen);
-    M4 camera_from_raster = mul(inverse(screen_from_camera), inverse(raster_from_screen));
+    // cameras.cpp:499-533 PerspectiveCamera::Create, cameras.h:259-278 ProjectiveCamera, :348-351 Perspective(fov, 1e-2, 1000)
+    float frame = S.frame_aspect > 0 ? S.frame_aspect : float(S.xres) / float(S.yres);
+    float sw[4];
+    if (frame > 1.f) { sw[0] = -frame; sw[1] = frame; sw[2] = -1.f; sw[3] = 1.f; }
+    else { sw[0] = -1.f; sw[1] = 1.f; sw[2] = -1.f / frame; sw[3] = 1.f / frame; }
+    if (!S.screen_window.empty()) for (int i = 0; i < 4; i++) sw[i] = (float)S.screen_window[i];
+    XF screen_from_camera = xf::perspective(S.fov, 1e-2f, 1000.f);
+    XF ndc_from_screen = xf::scale(1 / (sw[1] - sw[0]), 1 / (sw[3] - sw[2]), 1) * xf::translate(-sw[0], -sw[3], 0);
+    XF raster_from_ndc = xf::scale((float)S.xres, -(float)S.yres, 1);
+    XF raster_from_screen = raster_from_ndc * ndc_from_screen;
+    XF camera_from_raster = xf::inverse(screen_from_camera) * xf::inverse(raster_from_screen);
     c.camera_from_raster = to_abi(camera_from_raster);
-    c.render_from_camera = to_abi(mul(translate(-S.eye[0], -S.eye[1], -S.eye[2]), S.world_from_camera));
-    c.lens_radius = (float)S.lens_radius; c.focal_distance = (float)S.focal_distance;
+    c.render_from_camera = to_abi(S.render_from_world * S.world_from_camera);   // cameras.cpp:52-56
+    c.lens_radius = S.lens_radius; c.focal_distance = S.focal_distance;
     auto mid = S.medium_ids.find(S.camera_medium);
     if (!S.camera_medium.empty() && mid == S.medium_ids.end()) throw ParseError(VSPG_ERR_INVALID, "camera medium \"" + S.camera_medium + "\" is not defined");
     c.medium = S.camera_medium.empty() ? -1 : mid->second;
