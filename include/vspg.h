@@ -118,7 +118,10 @@ enum {
 };
 typedef struct vspg_light {
     int type;
-    float L[3];        /* emitted radiance / intensity, already times "scale" (RGB mode) */
+    float L[3];        /* emitted radiance / intensity as the "rgb L" / "rgb I" parameter gives it (RGB mode)  */
+    float scale;       /* the light's scale (the "scale" parameter, times power / illuminance normalisation): the
+                          reference keeps it apart from the spectrum (lights.h LightBase) and the light samplers'
+                          power estimates multiply the two in their own order, so the boundary keeps both   */
     float pos[3];      /* point: position (render space); distant: direction TO the light */
     int shape_kind;    /* area: 0 quad, 1 triangle, 2 sphere                             */
     int shape_index;   /* area: index into that shape array                              */

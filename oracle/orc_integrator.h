@@ -224,7 +224,7 @@ struct Scene {
     vspg_integrator_params ip;
     std::vector<Medium> media;
     std::vector<float> quadArea, triArea, sphereArea;
-    std::vector<float> lightCdf;  // power sampler pmf
+    std::vector<float> aliasP, aliasQ; std::vector<int> aliasIdx;  // PowerLightSampler AliasTable bins (p, q, alias)
     BVHLightSampler lightBvh;     // "bvh" sampler (the reference's default)
     GaussianFilterSampler gaussFilter;   // PixelFilter "gaussian" (pbrt's default filter)
     V3 sceneCenter; float sceneRadius = 0;
@@ -259,12 +259,48 @@ struct Scene {
         // Bounds3::BoundingSphere: center = (pMin+pMax)/2, radius = Inside(center) ? Distance(center, pMax) : 0
         sceneCenter = (bmin + bmax) / 2;
         sceneRadius = (d->n_quads + d->n_triangles + d->n_spheres) ? Distance(sceneCenter, bmax) : 0;
-        // PowerLightSampler pmf (lightsamplers.cpp:76-96): phi averaged over RGB
-        lightCdf.assign(d->n_lights, 0.f);
-        float sum = 0;
-        for (int i = 0; i < d->n_lights; i++) { lightCdf[i] = LightPower(i); sum += lightCdf[i]; }
-        if (sum == 0) for (auto &v : lightCdf) v = 1.f, sum += 1.f;
-        for (auto &v : lightCdf) v /= sum;
+        // PowerLightSampler (lightsamplers.cpp:76-96): power = (Phi(lambda) / lambda.PDF()).Average() with
+        // lambda = SampledWavelengths::SampleVisible(0.5f) (spectrum.h:369-386; sampling.h:163-171), then an AliasTable
+        // (sampling.cpp:563-618)
+        {
+            S3 pdf;
+            for (int i = 0; i < 3; ++i) {
+                float up = 0.5f + float(i) / 3;
+                if (up > 1) up -= 1;
+                float lambda = 538 - 138.888889f * std::atanh(0.85691062f - 1.82750197f * up);
+                pdf[i] = (lambda < 360 || lambda > 830) ? 0.f : 0.0039398042f / Sqr(std::cosh(0.0072f * (lambda - 538)));
+            }
+            int n = d->n_lights;
+            std::vector<float> lightPower;
+            for (int i = 0; i < n; i++) {
+                S3 phi = LightPhi(i), r;
+                for (int c = 0; c < 3; ++c) r[c] = (pdf[c] != 0) ? phi[c] / pdf[c] : 0.f;
+                lightPower.push_back(r.Average());
+            }
+            float acc = 0.f;
+            for (float v : lightPower) acc += v;
+            if (acc == 0.f) for (float &v : lightPower) v = 1.f;
+            double dsum = 0.;
+            for (float v : lightPower) dsum += v;
+            float sum = (float)dsum;   // Float sum = std::accumulate(weights.begin(), weights.end(), 0.)
+            aliasP.assign(n, 0.f); aliasQ.assign(n, 1.f); aliasIdx.assign(n, -1);
+            for (int i = 0; i < n; i++) aliasP[i] = lightPower[i] / sum;
+            struct Outcome { float pHat; int index; };
+            std::vector<Outcome> under, over;
+            for (int i = 0; i < n; i++) {
+                float pHat = aliasP[i] * n;
+                if (pHat < 1) under.push_back(Outcome{pHat, i}); else over.push_back(Outcome{pHat, i});
+            }
+            while (!under.empty() && !over.empty()) {
+                Outcome un = under.back(), ov = over.back();
+                under.pop_back(); over.pop_back();
+                aliasQ[un.index] = un.pHat; aliasIdx[un.index] = ov.index;
+                float pExcess = un.pHat + ov.pHat - 1;
+                if (pExcess < 1) under.push_back(Outcome{pExcess, ov.index}); else over.push_back(Outcome{pExcess, ov.index});
+            }
+            while (!over.empty()) { aliasQ[over.back().index] = 1; aliasIdx[over.back().index] = -1; over.pop_back(); }
+            while (!under.empty()) { aliasQ[under.back().index] = 1; aliasIdx[under.back().index] = -1; under.pop_back(); }
+        }
         lightBvh.Build(d->lights, d->n_lights, d->quads, quadArea, d->triangles, &triArea, d->spheres, &sphereArea);
         if (d->camera.filter_type == 1) gaussFilter.init(d->camera.filter_radius[0], d->camera.filter_radius[1], d->camera.filter_sigma);
     }
@@ -295,14 +331,15 @@ struct Scene {
         return area;
     }
     float ShapeArea(const vspg_light &l) const { return l.shape_kind == 2 ? sphereArea[l.shape_index] : l.shape_kind == 1 ? triArea[l.shape_index] : quadArea[l.shape_index]; }
-    float LightPower(int i) const {  // lights.cpp Phi() for each type, averaged over RGB
+    static S3 LightL(const vspg_light &l) { return l.scale * S3(l.L); }   // scale * Lemit->Sample(lambda), RGB build: Sample = rgb (spectrum.h:786-803)
+    S3 LightPhi(int i) const {  // lights.cpp:196-198, 251-253, 826-842, 1038-1040
         const vspg_light &l = d->lights[i];
         S3 L(l.L);
         switch (l.type) {
-        case VSPG_LIGHT_DIFFUSE_AREA: return (L * (Pi * (l.two_sided ? 2.f : 1.f) * ShapeArea(l))).Average();
-        case VSPG_LIGHT_POINT: return (L * (4 * Pi)).Average();
-        case VSPG_LIGHT_DISTANT: return (L * (Pi * Sqr(sceneRadius))).Average();
-        default: return (L * (4 * Pi * Pi * Sqr(sceneRadius))).Average();
+        case VSPG_LIGHT_DIFFUSE_AREA: return Pi * (l.two_sided ? 2 : 1) * ShapeArea(l) * (L * l.scale);
+        case VSPG_LIGHT_POINT: return 4 * Pi * l.scale * L;
+        case VSPG_LIGHT_DISTANT: return l.scale * L * Pi * Sqr(sceneRadius);
+        default: return 4 * Pi * Pi * Sqr(sceneRadius) * l.scale * L;
         }
     }
 
@@ -424,7 +461,7 @@ struct Scene {
     S3 AreaL(int light, V3 n, V3 w) const {
         const vspg_light &l = d->lights[light];
         if (!l.two_sided && DotN(n, w) < 0) return S3(0.f);
-        return S3(l.L);
+        return Scene::LightL(l);
     }
 };
 
@@ -680,16 +717,20 @@ struct Integrator {
             *pmf = 1.f / n;
             return li;
         }
-        float c = 0;
-        for (int i = 0; i < n; i++) { c += sc->lightCdf[i]; if (u < c || i == n - 1) { *pmf = sc->lightCdf[i]; return i; } }
-        return -1;
+        // AliasTable::Sample (sampling.cpp:620-645)
+        int offset = std::min<int>(u * n, n - 1);
+        float up = std::min<float>(u * n - offset, OneMinusEpsilon);
+        if (up < sc->aliasQ[offset]) { *pmf = sc->aliasP[offset]; return offset; }
+        int alias = sc->aliasIdx[offset];
+        *pmf = sc->aliasP[alias];
+        return alias;
     }
     float LightPMF(int light, const LightSampleCtx &ctx) const {
         int n = sc->d->n_lights;
         if (n == 0) return 0;
         if (sc->ip.light_sampler == VSPG_LIGHTSAMPLER_BVH) return sc->lightBvh.PMF(ctx.p, ctx.ns, light);
         if (sc->ip.light_sampler == VSPG_LIGHTSAMPLER_UNIFORM) return 1.f / n;
-        return sc->lightCdf[light];
+        return sc->aliasP[light];
     }
     // shapes.h:1053-1125 Triangle::Sample(ctx, u) (and :1014-1048 Sample(u) for the area-sampling fallback)
     static bool SampleTriangle(const vspg_triangle &q, float area, const LightSampleCtx &ctx, const float *u, V3 *pOut, V3 *pErr, V3 *nOut, float *pdfOut) {
@@ -782,13 +823,13 @@ struct Integrator {
         if (l.type == VSPG_LIGHT_POINT) {  // lights.h:243-250
             V3 p(l.pos);
             ls.wi = Normalize(p - ctx.p);
-            ls.L = S3(l.L) / DistanceSquared(p, ctx.p);
+            ls.L = Scene::LightL(l) / DistanceSquared(p, ctx.p);
             ls.pdf = 1; ls.pLight = p; ls.delta = true; ls.valid = true;
             return ls;
         }
         if (l.type == VSPG_LIGHT_DISTANT) {  // lights.h:316-323
             V3 wi = Normalize(V3(l.pos));
-            ls.wi = wi; ls.L = S3(l.L); ls.pdf = 1; ls.delta = true; ls.valid = true;
+            ls.wi = wi; ls.L = Scene::LightL(l); ls.pdf = 1; ls.delta = true; ls.valid = true;
             ls.pLight = ctx.p + wi * (2 * sc->sceneRadius);
             return ls;
         }
@@ -1227,7 +1268,7 @@ struct Integrator {
                 for (int i = 0; i < sc->d->n_lights; i++) {
                     const vspg_light &l = sc->d->lights[i];
                     if (l.type != VSPG_LIGHT_UNIFORM_INFINITE) continue;  // infiniteLights: only LightType::Infinite
-                    S3 Le(l.L);
+                    S3 Le = Scene::LightL(l);
                     if (ps.depth == 0 || ps.specularBounce) ps.L += ps.beta * Le / ps.r_u.Average();
                     else {
                         float lightPDF = LightPMF(i, ps.prevCtx) * 0.f;  // PDF_Li(..., allowIncompletePDF=true) = 0 (lights.cpp:1031-1036)

@@ -206,21 +206,21 @@ struct BVHLightSampler {
             float maxL = std::max({l.L[0], l.L[1], l.L[2]});
             if (l.type == VSPG_LIGHT_POINT) {   // lights.cpp:200-205
                 lb.bounds.pMin = lb.bounds.pMax = V3(l.pos);
-                lb.w = V3(0, 0, 1); lb.phi = 4 * Pi * maxL; lb.cosTheta_o = std::cos(Pi); lb.cosTheta_e = std::cos(Pi / 2); lb.twoSided = false;
+                lb.w = V3(0, 0, 1); lb.phi = 4 * Pi * l.scale * maxL; lb.cosTheta_o = std::cos(Pi); lb.cosTheta_e = std::cos(Pi / 2); lb.twoSided = false;
             } else if (l.type == VSPG_LIGHT_DIFFUSE_AREA && l.shape_kind == 1) {   // Triangle::Bounds / NormalBounds
                 const vspg_triangle &q = tris[l.shape_index];
                 V3 p0(q.p0), p1(q.p1), p2(q.p2);
                 lb.bounds = Union(Union(Union(LBox(), p0), p1), p2);
                 V3 n = Normalize(Cross(p1 - p0, p2 - p0));
                 if (q.flip_normal) n = -n;
-                lb.w = Normalize(n); lb.phi = maxL * ((*triArea)[l.shape_index] * Pi); lb.cosTheta_o = 1; lb.cosTheta_e = std::cos(Pi / 2);
+                lb.w = Normalize(n); lb.phi = maxL; lb.phi *= l.scale * (*triArea)[l.shape_index] * Pi; lb.cosTheta_o = 1; lb.cosTheta_e = std::cos(Pi / 2);
                 lb.twoSided = l.two_sided != 0;
             } else if (l.type == VSPG_LIGHT_DIFFUSE_AREA && l.shape_kind == 2) {   // Sphere::Bounds, NormalBounds = EntireSphere
                 const vspg_sphere &q = spheres[l.shape_index];
                 V3 c(q.center);
                 lb.bounds.pMin = V3(-q.radius + c.x, -q.radius + c.y, -q.radius + c.z);
                 lb.bounds.pMax = V3(q.radius + c.x, q.radius + c.y, q.radius + c.z);
-                lb.w = V3(0, 0, 1); lb.phi = maxL * ((*sphereArea)[l.shape_index] * Pi); lb.cosTheta_o = -1; lb.cosTheta_e = std::cos(Pi / 2);
+                lb.w = V3(0, 0, 1); lb.phi = maxL; lb.phi *= l.scale * (*sphereArea)[l.shape_index] * Pi; lb.cosTheta_o = -1; lb.cosTheta_e = std::cos(Pi / 2);
                 lb.twoSided = l.two_sided != 0;
             } else if (l.type == VSPG_LIGHT_DIFFUSE_AREA) {   // lights.cpp:845-864 + shapes.cpp:1070-1126
                 const vspg_quad &q = quads[l.shape_index];
@@ -242,7 +242,7 @@ struct BVHLightSampler {
                     cosTheta = std::min({Dot(n, n00), Dot(n, n01), Dot(n, n10), Dot(n, n11)});
                     cosTheta = std::min(1.f, std::max(-1.f, cosTheta));
                 }
-                lb.w = Normalize(n); lb.phi = maxL * (quadArea[l.shape_index] * Pi); lb.cosTheta_o = cosTheta; lb.cosTheta_e = std::cos(Pi / 2);
+                lb.w = Normalize(n); lb.phi = maxL; lb.phi *= l.scale * quadArea[l.shape_index] * Pi;   // lights.cpp:858-859 lb.cosTheta_o = cosTheta; lb.cosTheta_e = std::cos(Pi / 2);
                 lb.twoSided = l.two_sided != 0;
             } else { infiniteLights.push_back(i); continue; }
             if (lb.phi > 0) {

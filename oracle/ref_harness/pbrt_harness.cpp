@@ -44,6 +44,9 @@
 
 #include <chrono>
 #include <cstring>
+#include <csignal>
+#include <execinfo.h>
+#include <unistd.h>
 
 using namespace pbrt;
 
@@ -64,6 +67,12 @@ struct RefScene {
     ScratchBuffer scratch{65536};
 };
 bool g_inited = false;
+void segv_backtrace(int sig) {   // debugging aid for the harness: where did the reference crash
+    void *frames[64];
+    int n = backtrace(frames, 64);
+    backtrace_symbols_fd(frames, n, 2);
+    _exit(128 + sig);
+}
 }  // namespace
 
 extern "C" {
@@ -76,6 +85,7 @@ int refp_init(int nthreads, int render_space_world) {
     opt.quiet = true;
     opt.renderingSpace = render_space_world ? RenderingCoordinateSystem::World : RenderingCoordinateSystem::CameraWorld;
     InitPBRT(opt);
+    if (getenv("REFP_BACKTRACE")) std::signal(SIGSEGV, segv_backtrace);
     g_inited = true;
     return 0;
 }
@@ -322,6 +332,37 @@ int refp_surface_nee_geometry(void *h, const float *ray6, int light, const float
     put(8, lr.o.x, lr.o.y, lr.o.z); put(9, lr.d.x, lr.d.y, lr.d.z);
     out_hash[0] = Hash(lr.o); out_hash[1] = Hash(lr.d);
     return 0;
+}
+
+// The integrator's own light sampler: LightSampler::Sample(ctx, u) (lightsamplers.h:60-360) and PMF(ctx, light_of).
+// ctx9 = p, n, ns.  out_light = index into the scene's light array (-1 none).
+int refp_light_sample(void *h, int n, const float *ctx9, const float *u, const int *light_of, int *out_light, float *out_pmf, float *out_pmf_of) {
+    RefScene *rs = (RefScene *)h;
+    auto *integ = dynamic_cast<GuidedVolPathVSPGIntegrator *>(rs->integrator.get());
+    if (!integ) return 1;
+    for (int i = 0; i < n; ++i) {
+        const float *c = ctx9 + 9 * i;
+        LightSampleContext ctx(Point3fi(Point3f(c[0], c[1], c[2])), Normal3f(c[3], c[4], c[5]), Normal3f(c[6], c[7], c[8]));
+        pstd::optional<SampledLight> sl = integ->lightSampler.Sample(ctx, u[i]);
+        out_light[i] = -1; out_pmf[i] = 0;
+        if (sl) {
+            for (size_t k = 0; k < rs->lights.size(); ++k) if (rs->lights[k] == sl->light) out_light[i] = (int)k;
+            out_pmf[i] = sl->p;
+        }
+        out_pmf_of[i] = (light_of[i] >= 0 && light_of[i] < (int)rs->lights.size()) ? integ->lightSampler.PMF(ctx, rs->lights[light_of[i]]) : 0.f;
+    }
+    return 0;
+}
+
+// Light::Phi(SampledWavelengths::SampleVisible(0.5f)) and that lambda's PDF, per light: out = phi.rgb, pdf.rgb (6 floats each)
+int refp_light_phi(void *h, float *out6) {
+    RefScene *rs = (RefScene *)h;
+    SampledWavelengths lambda = SampledWavelengths::SampleVisible(0.5f);
+    for (size_t i = 0; i < rs->lights.size(); ++i) {
+        SampledSpectrum phi = rs->lights[i].Phi(lambda), pdf = lambda.PDF();
+        for (int c = 0; c < 3; ++c) { out6[6 * i + c] = phi[c]; out6[6 * i + 3 + c] = pdf[c]; }
+    }
+    return (int)rs->lights.size();
 }
 
 // ProjectiveCamera's matrices (cameras.h:198-236): out = cameraFromRaster[16], screenFromCamera[16],

@@ -52,7 +52,8 @@ struct DLight {
     float L[3];
     float pos[3];
     int shape_index, two_sided, medium;
-    float pmf;            // light sampler probability (uniform / power)
+    float pmf;            // PowerLightSampler: AliasTable bins[i].p
+    float q; int alias;   //                    bins[i].q, bins[i].alias (util/sampling.cpp:563-618)
 };
 
 // Light-BVH node (lightsamplers.h LightBVHNode), stored decoded -- see host_lightbvh.h.

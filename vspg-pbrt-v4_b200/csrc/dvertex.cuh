@@ -113,13 +113,13 @@ VD int sample_light(const DScene &sc, float u, float *pmf, V3 p, V3 n) {
         *pmf = 1.f / nl;
         return li;
     }
-    float c = 0;
-    for (int i = 0; i < nl; i++) {
-        float pi = sc.lights[i].pmf;
-        c += pi;
-        if (u < c || i == nl - 1) { *pmf = pi; return i; }
-    }
-    return -1;
+    // AliasTable::Sample (util/sampling.cpp:620-645)
+    int offset = min((int)(u * nl), nl - 1);
+    float up = fminf(u * nl - offset, kOneMinusEpsilon);
+    if (up < sc.lights[offset].q) { *pmf = sc.lights[offset].pmf; return offset; }
+    int alias = sc.lights[offset].alias;
+    *pmf = sc.lights[alias].pmf;
+    return alias;
 }
 VD float light_pmf(const DScene &sc, int light, V3 p, V3 n) {
     if (sc.n_lights == 0) return 0;

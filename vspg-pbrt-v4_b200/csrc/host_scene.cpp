@@ -523,7 +523,8 @@ struct Builder {
             if (ev > 0) sc *= ev / 3.14159265358979323846f;
         } else lx.fail("LightSource \"" + type + "\": supported types are point, distant, infinite (uniform)", VSPG_ERR_UNSUPPORTED);
         ps.report_unused();
-        for (int i = 0; i < 3; i++) l.L[i] = L[i] * sc;
+        for (int i = 0; i < 3; i++) l.L[i] = L[i];
+        l.scale = sc;
         S.lights.push_back(l);
     }
 
@@ -560,7 +561,8 @@ struct Builder {
         l.type = VSPG_LIGHT_DIFFUSE_AREA;
         float sc = g.area_scale;
         if (g.area_power > 0) sc *= (float)(g.area_power / ((g.area_two ? 2 : 1) * (double)area * M_PI));   // lights.cpp DiffuseAreaLight::Create
-        for (int i = 0; i < 3; i++) l.L[i] = g.area_L[i] * sc;
+        for (int i = 0; i < 3; i++) l.L[i] = g.area_L[i];
+        l.scale = sc;
         l.shape_kind = kind; l.shape_index = index; l.two_sided = g.area_two; l.medium = -1;
         S.lights.push_back(l);
         return (int)S.lights.size() - 1;
@@ -825,6 +827,22 @@ void finish(vspg_host_scene &S) {
     c.filter_type = S.filter_type; c.filter_radius[0] = S.filter_r[0]; c.filter_radius[1] = S.filter_r[1]; c.filter_sigma = S.filter_type == 1 ? S.filter_sigma : 0.f;
     c.imaging_ratio = S.exposure * S.iso / 100.f;   // film.cpp:233
     c.max_component_value = S.max_comp;
+    // ---- light order: BasicScene::CreateLights (scene.cpp:1320-1376) appends the area lights first, in shape order, and
+    // the LightSource lights after them.  Light samplers index this array (uniform pick, alias table, light BVH), so the
+    // order is part of the result.
+    {
+        std::vector<int> order;
+        for (int pass = 0; pass < 2; pass++)
+            for (int i = 0; i < (int)S.lights.size(); i++)
+                if ((S.lights[i].type == VSPG_LIGHT_DIFFUSE_AREA) == (pass == 0)) order.push_back(i);
+        std::vector<vspg_light> sorted;
+        std::vector<int> new_index(S.lights.size());
+        for (int k = 0; k < (int)order.size(); k++) { sorted.push_back(S.lights[order[k]]); new_index[order[k]] = k; }
+        S.lights.swap(sorted);
+        for (auto &q : S.quads) if (q.area_light >= 0) q.area_light = new_index[q.area_light];
+        for (auto &q : S.tris) if (q.area_light >= 0) q.area_light = new_index[q.area_light];
+        for (auto &q : S.spheres) if (q.area_light >= 0) q.area_light = new_index[q.area_light];
+    }
     // ---- arrays
     vspg_scene_desc &d = S.desc;
     d.n_media = (int)S.media.size(); d.media = S.media.data();

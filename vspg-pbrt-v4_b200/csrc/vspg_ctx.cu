@@ -13,6 +13,7 @@
 
 #include "host_util.h"
 #include "host_lightbvh.h"
+#include "host_lightpower.h"
 #include "kernels2.cuh"
 #include "debug_kernels.cuh"
 
@@ -310,16 +311,14 @@ int vspg_set_scene(vspg_ctx *ctx, const vspg_scene_desc *s) {
     sc.n_materials = s->n_materials;
     std::vector<DLight> lights(s->n_lights);
     std::vector<int> inf;
-    std::vector<float> power(s->n_lights);
-    float sum = 0;
+    std::vector<float> lightArea(s->n_lights, 0.f);
     for (int i = 0; i < s->n_lights; i++) {
         const vspg_light &l = s->lights[i];
         DLight &d = lights[i];
-        d.type = l.type; memcpy(d.L, l.L, 12); memcpy(d.pos, l.pos, 12);
-        d.shape_index = l.shape_index; d.two_sided = l.two_sided; d.medium = l.medium; d.pmf = 0;
-        const float Pi = 3.14159265358979323846f;
-        auto avgScaled = [&](float c) { float v = l.L[0] * c; v += l.L[1] * c; v += l.L[2] * c; return v / 3; };  // (L * c).Average()
-        switch (l.type) {  // lights.cpp Phi(), averaged over RGB
+        d.type = l.type; memcpy(d.pos, l.pos, 12);
+        for (int c = 0; c < 3; c++) d.L[c] = l.scale * l.L[c];   // scale * Lemit->Sample(lambda) (lights.h:169-171, 495-506; lights.cpp:267, 1031)
+        d.shape_index = l.shape_index; d.two_sided = l.two_sided; d.medium = l.medium; d.pmf = 0; d.q = 1; d.alias = -1;
+        switch (l.type) {
         case VSPG_LIGHT_DIFFUSE_AREA:
         {   // the device light carries the GLOBAL primitive id (quads, then triangles, then spheres)
             const int nOf[3] = {s->n_quads, s->n_triangles, s->n_spheres}, baseOf[3] = {0, s->n_quads, s->n_quads + s->n_triangles};
@@ -327,17 +326,18 @@ int vspg_set_scene(vspg_ctx *ctx, const vspg_scene_desc *s) {
                 return fail(ctx, VSPG_ERR_INVALID, "set_scene: light %d: area light references shape kind %d index %d, which does not exist", i, l.shape_kind, l.shape_index);
             d.shape_index = baseOf[l.shape_kind] + l.shape_index;
             if (quads[d.shape_index].area_light != i) return fail(ctx, VSPG_ERR_INVALID, "set_scene: light %d and its shape do not reference each other", i);
-            power[i] = avgScaled(Pi * (l.two_sided ? 2.f : 1.f) * quads[d.shape_index].area); break;
+            lightArea[i] = quads[d.shape_index].area;
+            break;
         }
-        case VSPG_LIGHT_POINT: power[i] = avgScaled(4 * Pi); break;
-        case VSPG_LIGHT_DISTANT: power[i] = avgScaled(Pi * (sc.scene_radius * sc.scene_radius)); break;
-        case VSPG_LIGHT_UNIFORM_INFINITE: power[i] = avgScaled(4 * Pi * Pi * (sc.scene_radius * sc.scene_radius)); inf.push_back(i); break;
+        case VSPG_LIGHT_POINT: case VSPG_LIGHT_DISTANT: break;
+        case VSPG_LIGHT_UNIFORM_INFINITE: inf.push_back(i); break;
         default: return fail(ctx, VSPG_ERR_UNSUPPORTED, "set_scene: light %d has unsupported type %d", i, l.type);
         }
-        sum += power[i];
     }
-    if (sum == 0) { for (auto &p : power) p = 1.f; sum = (float)s->n_lights; }
-    for (int i = 0; i < s->n_lights; i++) lights[i].pmf = power[i] / sum;
+    {   // PowerLightSampler: alias table over Phi / lambda.PDF() (host_lightpower.h)
+        HostPowerSampler ps = build_power_sampler(s->lights, s->n_lights, lightArea.data(), sc.scene_radius);
+        for (int i = 0; i < s->n_lights; i++) { lights[i].pmf = ps.p[i]; lights[i].q = ps.q[i]; lights[i].alias = ps.alias[i]; }
+    }
     CK(upload(ctx, ctx->scene_allocs, lights.data(), lights.size(), &sc.lights));
     CK(upload(ctx, ctx->scene_allocs, inf.data(), inf.size(), &sc.inf_lights));
     sc.n_lights = s->n_lights; sc.n_inf_lights = (int)inf.size();

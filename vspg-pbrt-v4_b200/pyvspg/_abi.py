@@ -59,7 +59,7 @@ class Material(C.Structure):
 
 
 class Light(C.Structure):
-    _fields_ = [("type", i32), ("L", F3), ("pos", F3), ("shape_kind", i32), ("shape_index", i32), ("two_sided", i32),
+    _fields_ = [("type", i32), ("L", F3), ("scale", C.c_float), ("pos", F3), ("shape_kind", i32), ("shape_index", i32), ("two_sided", i32),
                 ("medium", i32)]
 
 

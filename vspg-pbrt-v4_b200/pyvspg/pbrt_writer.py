@@ -45,19 +45,20 @@ def integrator_block(ip, name="guidedvolpathvspg", cache_file=None, isg_file=Non
 
 
 def scene_text(cfg, out_dir=None, outfile="out.exr", seed=0, integrator_name="guidedvolpathvspg", cache_file=None, isg_file=None,
-               tr_file=None, raw_density=False):
+               tr_file=None, raw_density=False, placeholder_grids=False):
     """Returns the .pbrt text of `cfg` (a pyvspg.configs.Config).  With raw_density=True grids are written next to
     the scene as raw little-endian float32 files ("string densityfile", the front end's extension for grids too large
     for text) -- needs out_dir."""
     sc = cfg.scene
     cp = sc.camera._params
+    fc = sc.desc.camera if sc.desc is not None else sc.camera   # the filter may have been changed on the finalised desc
     L = [f'LookAt {_v(cp["eye"])}  {_v(cp["look"])}  {_v(cp["up"])}',
          f'Camera "perspective" "float fov" [{_f(cp["fov"])}] "float lensradius" [{_f(cp["lens_radius"])}] "float focaldistance" [{_f(cp["focal_distance"])}]',
          f'Film "rgb" "integer xresolution" [{sc.camera.width}] "integer yresolution" [{sc.camera.height}] "string filename" "{outfile}"',
          f'Sampler "independent" "integer pixelsamples" [{cfg.spp}] "integer seed" [{seed}]',
-         ('PixelFilter "box"' if sc.desc.camera.filter_type == 0 else
-          f'PixelFilter "gaussian" "float xradius" [{_f(sc.desc.camera.filter_radius[0])}] "float yradius" [{_f(sc.desc.camera.filter_radius[1])}] '
-          f'"float sigma" [{_f(sc.desc.camera.filter_sigma)}]'),
+         ('PixelFilter "box"' if fc.filter_type == 0 else
+          f'PixelFilter "gaussian" "float xradius" [{_f(fc.filter_radius[0])}] "float yradius" [{_f(fc.filter_radius[1])}] '
+          f'"float sigma" [{_f(fc.filter_sigma)}]'),
          integrator_block(cfg.ip, integrator_name, cache_file, isg_file, tr_file),
          'WorldBegin']
     for kind, e in sc.log:
@@ -72,7 +73,7 @@ def scene_text(cfg, out_dir=None, outfile="out.exr", seed=0, integrator_name="gu
             if e["type"] == "homogeneous":
                 L.append(head + f' "rgb sigma_a" [{_v(e["sigma_a"])}] "rgb sigma_s" [{_v(e["sigma_s"])}]')
             elif e["type"] == "uniformgrid":
-                d = e["density"]
+                d = e["density"][:1, :1, :1] if placeholder_grids else e["density"]
                 nz, ny, nx = d.shape
                 head += (f' "rgb sigma_a" [{_v(e["sigma_a"])}] "rgb sigma_s" [{_v(e["sigma_s"])}] "integer nx" [{nx}] "integer ny" [{ny}] "integer nz" [{nz}]'
                          f' "point3 p0" [{_v(e["lo"])}] "point3 p1" [{_v(e["hi"])}]')
@@ -84,6 +85,8 @@ def scene_text(cfg, out_dir=None, outfile="out.exr", seed=0, integrator_name="gu
                     L.append(head + ' "float density" [' + " ".join(repr(float(x)) for x in d.reshape(-1)) + "]")
             else:
                 sa, ss = e["sigma_a_rgb"], e["sigma_s_rgb"]
+                if placeholder_grids:
+                    sa, ss = sa[:1, :1, :1], ss[:1, :1, :1]
                 nz, ny, nx = sa.shape[:3]
                 L.append(head + f' "integer nx" [{nx}] "integer ny" [{ny}] "integer nz" [{nz}] "point3 p0" [{_v(e["lo"])}] "point3 p1" [{_v(e["hi"])}]'
                          + ' "rgb sigma_a" [' + " ".join(repr(float(x)) for x in sa.reshape(-1)) + ']'
