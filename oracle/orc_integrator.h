@@ -741,8 +741,9 @@ struct Integrator {
         float b[3];
         if (solidAngle < MinSphericalSampleAreaTri || solidAngle > MaxSphericalSampleAreaTri) {
             SampleUniformTriangle(u, b);
-            V3 p = b[0] * p0 + b[1] * p1 + b[2] * p2;
-            *pErr = gamma_(6) * (Abs(b[0] * p0) + Abs(b[1] * p1) + Abs((1 - b[0] - b[1]) * p2));
+            // Interaction(Point3fi(p, pError), ...) (shapes.h:1040-1046): outward-rounded interval, p() = midpoint
+            V3i pi = V3i::FromValueAndError(b[0] * p0 + b[1] * p1 + b[2] * p2, gamma_(6) * (Abs(b[0] * p0) + Abs(b[1] * p1) + Abs((1 - b[0] - b[1]) * p2)));
+            V3 p = pi.Mid(); *pErr = pi.Error();
             V3 wi = p - ctx.p;
             if (LengthSquared(wi) == 0) return false;
             wi = Normalize(wi);
@@ -766,8 +767,9 @@ struct Integrator {
         if (!SampleSphericalTriangle(v, ctx.p, us, b, &triPDF)) { b[0] = b[1] = b[2] = 0; }
         if (triPDF == 0) return false;
         pdf *= triPDF;
-        *pErr = gamma_(6) * (Abs(b[0] * p0) + Abs(b[1] * p1) + Abs((1 - b[0] - b[1]) * p2));
-        *pOut = b[0] * p0 + b[1] * p1 + b[2] * p2; *nOut = n; *pdfOut = pdf;
+        V3i pi = V3i::FromValueAndError(b[0] * p0 + b[1] * p1 + b[2] * p2, gamma_(6) * (Abs(b[0] * p0) + Abs(b[1] * p1) + Abs((1 - b[0] - b[1]) * p2)));   // shapes.h:1117-1123
+        *pErr = pi.Error();
+        *pOut = pi.Mid(); *nOut = n; *pdfOut = pdf;
         return true;
     }
     // shapes.h:300-361 Sphere::Sample(ctx, u) (and shapes.cpp:38-59 Sample(u) for reference points inside the sphere).
@@ -811,8 +813,9 @@ struct Integrator {
         V3 n = mw.x * fx + mw.y * fy + mw.z * fz;
         V3 p = pCenter + radius * n;
         if (q.flip_normal) n = -n;
-        *pErr = gamma_(5) * Abs(p);
-        *pOut = p; *nOut = n; *pdfOut = 1 / (2 * Pi * oneMinusCosThetaMax);
+        V3i pi = V3i::FromValueAndError(p, gamma_(5) * Abs(p));   // shapes.h:352-360 Interaction(Point3fi(p, pError), ...)
+        *pErr = pi.Error();
+        *pOut = pi.Mid(); *nOut = n; *pdfOut = 1 / (2 * Pi * oneMinusCosThetaMax);
         return true;
     }
     struct LiSample { bool valid = false; S3 L; V3 wi; float pdf = 0; V3 pLight, pLightErr, nLight; bool delta = false; };
@@ -882,13 +885,14 @@ struct Integrator {
             pdf = BilinearPDF(uv, w);
         } else { uv[0] = u[0]; uv[1] = u[1]; }
         V3 pu0 = LerpV(uv[1], p00, p01), pu1 = LerpV(uv[1], p10, p11);
-        V3 p = LerpV(uv[0], pu0, pu1);
+        V3 pLerp = LerpV(uv[0], pu0, pu1);
         V3 dpdu = pu1 - pu0;
         V3 dpdv = LerpV(uv[0], p01, p11) - LerpV(uv[0], p00, p10);
         if (LengthSquared(dpdu) == 0 || LengthSquared(dpdv) == 0) return ls;
         V3 n = Normalize(Cross(dpdu, dpdv));
         if (q.flip_normal) n = -n;
-        V3 pError = gamma_(6) * (Abs(p00) + Abs(p01) + Abs(p10) + Abs(p11));
+        V3i pi = V3i::FromValueAndError(pLerp, gamma_(6) * (Abs(p00) + Abs(p01) + Abs(p10) + Abs(p11)));   // shapes.cpp:1200-1213
+        V3 p = pi.Mid(), pError = pi.Error();
         float pdfA = pdf / Length(Cross(dpdu, dpdv));
         V3 wi = p - ctx.p;
         if (LengthSquared(wi) == 0) return ls;
@@ -1267,8 +1271,11 @@ struct Integrator {
             if (!h.valid) {
                 for (int i = 0; i < sc->d->n_lights; i++) {
                     const vspg_light &l = sc->d->lights[i];
-                    if (l.type != VSPG_LIGHT_UNIFORM_INFINITE) continue;  // infiniteLights: only LightType::Infinite
+                    // infiniteLights holds LightType::Infinite AND LightType::DeltaDirection lights in this fork (cpu/integrators.h:77-81);
+                    // DistantLight::Le returns scale * Lemit (lights.h:290-293) and only counts at depth 0 (vspg.cpp:356-358)
+                    if (l.type != VSPG_LIGHT_UNIFORM_INFINITE && l.type != VSPG_LIGHT_DISTANT) continue;
                     S3 Le = Scene::LightL(l);
+                    if (l.type == VSPG_LIGHT_DISTANT && ps.depth != 0) Le = S3(0.f);
                     if (ps.depth == 0 || ps.specularBounce) ps.L += ps.beta * Le / ps.r_u.Average();
                     else {
                         float lightPDF = LightPMF(i, ps.prevCtx) * 0.f;  // PDF_Li(..., allowIncompletePDF=true) = 0 (lights.cpp:1031-1036)

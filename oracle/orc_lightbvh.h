@@ -242,7 +242,7 @@ struct BVHLightSampler {
                     cosTheta = std::min({Dot(n, n00), Dot(n, n01), Dot(n, n10), Dot(n, n11)});
                     cosTheta = std::min(1.f, std::max(-1.f, cosTheta));
                 }
-                lb.w = Normalize(n); lb.phi = maxL; lb.phi *= l.scale * quadArea[l.shape_index] * Pi;   // lights.cpp:858-859 lb.cosTheta_o = cosTheta; lb.cosTheta_e = std::cos(Pi / 2);
+                lb.w = Normalize(n); lb.phi = maxL; lb.phi *= l.scale * quadArea[l.shape_index] * Pi; lb.cosTheta_o = cosTheta; lb.cosTheta_e = std::cos(Pi / 2);
                 lb.twoSided = l.two_sided != 0;
             } else { infiniteLights.push_back(i); continue; }
             if (lb.phi > 0) {

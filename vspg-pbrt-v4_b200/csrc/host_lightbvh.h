@@ -230,12 +230,12 @@ inline HostLightBvh build_light_bvh(const vspg_scene_desc *scene, const float *p
             for (int k = 0; k < 3; k++) { lb.bmin[k] = std::min(std::min(p0[k], p1[k]), p2[k]); lb.bmax[k] = std::max(std::max(p0[k], p1[k]), p2[k]); }
             H3 n = hnormalize(hcross(p1 - p0, p2 - p0));
             if (q.flip_normal) n = -1.f * n;
-            lb.w = hnormalize(n); lb.phi = maxL; lb.phi *= l.scale * triArea[l.shape_index] * kPi;   // lights.cpp:858-859 lb.cosTheta_o = 1; lb.cosTheta_e = cosHalfPi;
+            lb.w = hnormalize(n); lb.phi = maxL; lb.phi *= l.scale * triArea[l.shape_index] * kPi; lb.cosTheta_o = 1; lb.cosTheta_e = cosHalfPi;
             lb.twoSided = l.two_sided != 0;
         } else if (l.type == VSPG_LIGHT_DIFFUSE_AREA && l.shape_kind == 2) {   // shapes.cpp:33-36 Sphere::Bounds, shapes.h:134 EntireSphere
             const vspg_sphere &q = scene->spheres[l.shape_index];
             for (int k = 0; k < 3; k++) { lb.bmin[k] = -q.radius + q.center[k]; lb.bmax[k] = q.radius + q.center[k]; }
-            lb.w = H3(0, 0, 1); lb.phi = maxL; lb.phi *= l.scale * sphereArea[l.shape_index] * kPi;   // lights.cpp:858-859 lb.cosTheta_o = -1; lb.cosTheta_e = cosHalfPi;
+            lb.w = H3(0, 0, 1); lb.phi = maxL; lb.phi *= l.scale * sphereArea[l.shape_index] * kPi; lb.cosTheta_o = -1; lb.cosTheta_e = cosHalfPi;
             lb.twoSided = l.two_sided != 0;
         } else if (l.type == VSPG_LIGHT_DIFFUSE_AREA) {   // lights.cpp:845-864
             const vspg_quad &q = quads[l.shape_index];
@@ -258,7 +258,7 @@ inline HostLightBvh build_light_bvh(const vspg_scene_desc *scene, const float *p
                 cosTheta = std::min({hdot(n, n00), hdot(n, n01), hdot(n, n10), hdot(n, n11)});
                 cosTheta = std::min(1.f, std::max(-1.f, cosTheta));
             }
-            lb.w = hnormalize(n); lb.phi = maxL; lb.phi *= l.scale * quadArea[l.shape_index] * kPi;   // lights.cpp:858-859 lb.cosTheta_o = cosTheta; lb.cosTheta_e = cosHalfPi;
+            lb.w = hnormalize(n); lb.phi = maxL; lb.phi *= l.scale * quadArea[l.shape_index] * kPi; lb.cosTheta_o = cosTheta; lb.cosTheta_e = cosHalfPi;
             lb.twoSided = l.two_sided != 0;
         } else { out.infinite.push_back(i); continue; }
         if (lb.phi > 0) {
