@@ -206,15 +206,15 @@ LightSource "infinite"
     assert np.allclose(s.center, -eye) and s.radius == 0.5 and s.flip_normal == 1 and s.material == 1 and s.area_light == 0
     assert list(d.materials[1].reflectance) == [0.25, 0.25, 0.25]
     al = d.lights[0]
-    assert (al.type, al.shape_kind, al.shape_index, al.two_sided) == (A.LIGHT_DIFFUSE_AREA, 2, 0, 1) and list(al.L) == [4, 6, 8]
+    assert (al.type, al.shape_kind, al.shape_index, al.two_sided) == (A.LIGHT_DIFFUSE_AREA, 2, 0, 1) and list(al.L) == [2, 3, 4] and al.scale == 2   # spectrum and scale stay apart (lights.h LightBase)
     q = d.quads[0]
     assert (q.material, q.medium_inside, q.medium_outside, q.has_interface) == (-1, 0, -1, 1)
     assert np.allclose(q.p11, np.array([6, 7, 7]) - eye)   # column-major Transform: translation in the last four numbers
     m = d.media[0]
     assert list(m.sigma_a) == [0.5, 1.0, 1.5] and list(m.sigma_s) == [2.0, 2.5, 3.0] and m.g == 0.25 and m.type == A.MEDIUM_HOMOGENEOUS
     dl, il = d.lights[1], d.lights[2]
-    assert dl.type == A.LIGHT_DISTANT and np.allclose(dl.pos, [0, 1, 0]) and list(dl.L) == [3, 3, 3]
-    assert il.type == A.LIGHT_UNIFORM_INFINITE and list(il.L) == [1, 1, 1]
+    assert dl.type == A.LIGHT_DISTANT and np.allclose(dl.pos, [0, 1, 0]) and list(dl.L) == [1, 1, 1] and dl.scale == 3
+    assert il.type == A.LIGHT_UNIFORM_INFINITE and list(il.L) == [1, 1, 1] and il.scale == 1
     assert (d.camera.width, d.camera.height) == (16, 8) and d.camera.filter_type == 0 and hs.spp == 2 and hs.outfile == "a.exr"
     hs.close()
 

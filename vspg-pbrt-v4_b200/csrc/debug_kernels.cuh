@@ -81,7 +81,7 @@ __global__ void k_debug_sample_li(const DScene sc, int n, const float *ctx9, con
         Hit h = scene_intersect(sc, ro, ls.wi, inff(), nodes);
         if (h.prim < 0) continue;
         SurfaceIntr s = make_intr(sc, h, ro, ls.wi, -1);
-        if (s.areaLight == light[i]) o[11] = area_pdf_li(sc, light[i], p, ns, ls.wi, s);
+        if (s.areaLight == light[i]) o[11] = area_pdf_li(sc, light[i], p, ns, ls.wi, ro);
     }
 }
 

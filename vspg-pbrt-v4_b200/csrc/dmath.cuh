@@ -81,6 +81,16 @@ VD V3 operator/(V3 a, float s) { return V3(a.x / s, a.y / s, a.z / s); }
 VD bool operator==(V3 a, V3 b) { return a.x == b.x && a.y == b.y && a.z == b.z; }
 VD float dot(V3 a, V3 b) { return a.x * b.x + a.y * b.y + a.z * b.z; }  // util/vecmath.h:964
 VD float absdot(V3 a, V3 b) { return fabsf(dot(a, b)); }
+// A Dot with a Normal3 operand is a different function in the reference (util/vecmath.h:1056-1077):
+// FMA(n.x, v.x, SumOfProducts(n.y, v.y, n.z, v.z)), SumOfProducts being the compensated form of util/math.h:577-582.
+VD float sum_of_products(float a, float b, float c, float d) {
+    float cd = c * d;
+    float sop = fmaf(a, b, cd);
+    float err = fmaf(c, d, -cd);
+    return sop + err;
+}
+VD float dotn(V3 a, V3 b) { return fmaf(a.x, b.x, sum_of_products(a.y, b.y, a.z, b.z)); }
+VD float absdotn(V3 a, V3 b) { return fabsf(dotn(a, b)); }
 VD V3 cross(V3 v, V3 w) {  // util/vecmath.h:999
     return V3(diff_of_products(v.y, w.z, v.z, w.y), diff_of_products(v.z, w.x, v.x, w.z),
               diff_of_products(v.x, w.y, v.y, w.x));
@@ -89,6 +99,18 @@ VD float length_sq(V3 v) { return sqr(v.x) + sqr(v.y) + sqr(v.z); }
 VD float length(V3 v) { return sqrtf(length_sq(v)); }
 VD V3 normalize(V3 v) { return v / length(v); }
 VD V3 vabs(V3 v) { return V3(fabsf(v.x), fabsf(v.y), fabsf(v.z)); }
+// Point3fi(p, err) (util/vecmath.h Point3fi, util/math.h Interval::FromValueAndError): every coordinate becomes the
+// interval [SubRoundDown(v, e), AddRoundUp(v, e)]; p() is its midpoint and Error() half its width -- both differ from
+// (p, err) in the last bits, and ray origins spawned from them (hence the shadow trackers' RNG seeds) follow.
+VD void point_interval(V3 p, V3 e, V3 *mid, V3 *err) {
+    float lo, hi;
+    if (e.x == 0) { lo = hi = p.x; } else { lo = next_down(p.x - e.x); hi = next_up(p.x + e.x); }
+    mid->x = (lo + hi) / 2; err->x = (hi - lo) / 2;
+    if (e.y == 0) { lo = hi = p.y; } else { lo = next_down(p.y - e.y); hi = next_up(p.y + e.y); }
+    mid->y = (lo + hi) / 2; err->y = (hi - lo) / 2;
+    if (e.z == 0) { lo = hi = p.z; } else { lo = next_down(p.z - e.z); hi = next_up(p.z + e.z); }
+    mid->z = (lo + hi) / 2; err->z = (hi - lo) / 2;
+}
 VD float max_comp(V3 v) { return fmaxf(v.x, fmaxf(v.y, v.z)); }
 VD V3 lerpv(float t, V3 a, V3 b) { return (1 - t) * a + t * b; }
 VD float dist_sq(V3 a, V3 b) { return length_sq(a - b); }

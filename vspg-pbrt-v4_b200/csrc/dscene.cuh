@@ -127,6 +127,8 @@ struct PathSoA {
     F4S<2, 0> misc2;     // prevCtx.p.z, pixel(int), sampleIndex(int), unused
     F4S<2, 1> hit;       // t, u, v, prim(int)  (prim < 0: no hit)
     float4 *ev;          // medium scatter event: p xyz, g
+    float4 *prev_o;      // ray origin spawned at the previous SURFACE vertex (isect.SpawnRay(wi)): Shape::PDF re-intersects the
+                         // emitter from there for the emission MIS weight; written by k_shade, read by k_surface on emitter hits only
     // shadow-ray record emitted by the scatter kernels
     F4S<2, 0> sh_o;      // o xyz, d.x
     F4S<2, 1> sh_d;      // d.y d.z, medium(int), flags(int: bit0 delta light, bits 8.. channel)

@@ -15,16 +15,16 @@ struct SurfaceIntr {
     bool hasInterface;
     int mediumInside, mediumOutside, rayMedium;
     VD int get_medium(V3 w) const {  // interaction.h:117-121
-        if (hasInterface) return dot(w, n) > 0 ? mediumOutside : mediumInside;
+        if (hasInterface) return dotn(w, n) > 0 ? mediumOutside : mediumInside;
         return rayMedium;
     }
 };
 
 // ray.h:75-92
 VD V3 offset_ray_origin(V3 p, V3 pError, V3 n, V3 w) {
-    float d = dot(vabs(n), pError);
+    float d = dotn(vabs(n), pError);
     V3 offset = d * n;
-    if (dot(w, n) < 0) offset = -offset;
+    if (dotn(w, n) < 0) offset = -offset;
     V3 po = p + offset;
     if (offset.x > 0) po.x = next_up(po.x); else if (offset.x < 0) po.x = next_down(po.x);
     if (offset.y > 0) po.y = next_up(po.y); else if (offset.y < 0) po.y = next_down(po.y);
@@ -231,8 +231,7 @@ VD SurfaceIntr make_intr(const DScene &sc, const Hit &h, V3 rayO, V3 rayD, int r
             V3 ng = cross(p2 - p0, p1 - p0);
             coordinate_system(normalize(ng), &dpdu, &dpdv);
         }
-        s.p = b0 * p0 + b1 * p1 + b2 * p2;
-        s.pError = gammaN(7) * (vabs(b0 * p0) + vabs(b1 * p1) + vabs(b2 * p2));
+        point_interval(b0 * p0 + b1 * p1 + b2 * p2, gammaN(7) * (vabs(b0 * p0) + vabs(b1 * p1) + vabs(b2 * p2)), &s.p, &s.pError);   // Point3fi(pHit, pError), shapes.h:929-935
         s.n = normalize(cross(dp02, dp12));
         if (q.flip_normal) s.n = -s.n;
         s.ns = s.n; s.dpdu = dpdu;
@@ -243,11 +242,11 @@ VD SurfaceIntr make_intr(const DScene &sc, const Hit &h, V3 rayO, V3 rayD, int r
         s.mediumInside = q.medium_inside; s.mediumOutside = q.medium_outside; s.rayMedium = rayMedium;
         return s;
     }
-    s.p = lerpv(h.u, lerpv(h.v, p00, p01), lerpv(h.v, p10, p11));
+    V3 pLerp = lerpv(h.u, lerpv(h.v, p00, p01), lerpv(h.v, p10, p11));
     V3 dpdu = lerpv(h.v, p10, p11) - lerpv(h.v, p00, p01);
     V3 dpdv = lerpv(h.u, p01, p11) - lerpv(h.u, p00, p10);
     V3 pAbsSum = vabs(p00) + vabs(p01) + vabs(p10) + vabs(p11);
-    s.pError = gammaN(6) * pAbsSum;
+    point_interval(pLerp, gammaN(6) * pAbsSum, &s.p, &s.pError);   // Point3fi(p, pError), shapes.h:1464-1472
     s.n = normalize(cross(dpdu, dpdv));
     if (q.flip_normal) s.n = -s.n;
     s.ns = s.n; s.dpdu = dpdu;
@@ -261,7 +260,7 @@ VD SurfaceIntr make_intr(const DScene &sc, const Hit &h, V3 rayO, V3 rayD, int r
 
 // lights.h:492-515 DiffuseAreaLight::L
 VD V3 area_L(const DLight &l, V3 n, V3 w) {
-    if (!l.two_sided && dot(n, w) < 0) return V3();
+    if (!l.two_sided && dotn(n, w) < 0) return V3();
     return ld3(l.L);
 }
 

@@ -108,12 +108,6 @@ __device__ __noinline__ void invert_spherical_rectangle_sample(V3 pRef, V3 s, V3
 // ---------------------------------------------------------------------------------------------------- triangles
 constexpr float kMinSphericalSampleAreaTri = 3e-4f, kMaxSphericalSampleAreaTri = 6.22f;   // shapes.h:1190-1191
 
-VD float sum_of_products(float a, float b, float c, float d) {   // util/math.h:577-582
-    float cd = c * d;
-    float sop = fmaf(a, b, cd);
-    float err = fmaf(c, d, -cd);
-    return sop + err;
-}
 VD V3 gram_schmidt(V3 v, V3 w) { return v - dot(v, w) * w; }
 VD float spherical_triangle_area(V3 a, V3 b, V3 c) {              // util/vecmath.h:1638-1641
     return fabsf(2 * atan2f(dot(a, cross(b, c)), 1 + dot(a, b) + dot(a, c) + dot(b, c)));

@@ -43,7 +43,7 @@ VD float light_importance(const DLightNode &nd, V3 p, V3 n) {
     if (cosThetap <= cosTheta_e) return 0;
     float importance = nd.phi * cosThetap / d2;
     if (n.x != 0 || n.y != 0 || n.z != 0) {
-        float cosTheta_i = absdot(wi, n);
+        float cosTheta_i = absdotn(wi, n);
         float sinTheta_i = safe_sqrt(1 - sqr(cosTheta_i));
         float cosThetap_i = cosTheta_i > cosTheta_b ? 1.f : cosTheta_i * cosTheta_b + sinTheta_i * sinTheta_b;
         importance *= cosThetap_i;
@@ -139,19 +139,19 @@ __device__ __noinline__ bool sample_triangle_light(const DQuad &q, V3 ctxP, V3 c
     if (solidAngle < kMinSphericalSampleAreaTri || solidAngle > kMaxSphericalSampleAreaTri) {
         if (u0 < u1) { b[0] = u0 / 2; b[1] = u1 - b[0]; } else { b[1] = u1 / 2; b[0] = u0 - b[1]; }   // SampleUniformTriangle
         b[2] = 1 - b[0] - b[1];
-        V3 p = b[0] * p0 + b[1] * p1 + b[2] * p2;
-        *pErr = gammaN(6) * (vabs(b[0] * p0) + vabs(b[1] * p1) + vabs((1 - b[0] - b[1]) * p2));
+        V3 p;   // Interaction(Point3fi(p, pError), ...) (shapes.h:1040-1046)
+        point_interval(b[0] * p0 + b[1] * p1 + b[2] * p2, gammaN(6) * (vabs(b[0] * p0) + vabs(b[1] * p1) + vabs((1 - b[0] - b[1]) * p2)), &p, pErr);
         V3 wi = p - ctxP;
         if (length_sq(wi) == 0) return false;
         wi = normalize(wi);
-        float pdf = (1 / q.area) / (absdot(n, -wi) / dist_sq(ctxP, p));
+        float pdf = (1 / q.area) / (absdotn(n, -wi) / dist_sq(ctxP, p));
         if (isinf(pdf)) return false;
         *pOut = p; *nOut = n; *pdfOut = pdf;
         return true;
     }
     float pdf = 1;
     if (!(ctxNs.x == 0 && ctxNs.y == 0 && ctxNs.z == 0)) {
-        float w[4] = {fmaxf(0.01f, absdot(ctxNs, w1)), fmaxf(0.01f, absdot(ctxNs, w1)), fmaxf(0.01f, absdot(ctxNs, w0)), fmaxf(0.01f, absdot(ctxNs, w2))};
+        float w[4] = {fmaxf(0.01f, absdotn(ctxNs, w1)), fmaxf(0.01f, absdotn(ctxNs, w1)), fmaxf(0.01f, absdotn(ctxNs, w0)), fmaxf(0.01f, absdotn(ctxNs, w2))};
         float a0, a1;
         sample_bilinear(u0, u1, w, &a0, &a1);
         u0 = a0; u1 = a1;
@@ -161,8 +161,8 @@ __device__ __noinline__ bool sample_triangle_light(const DQuad &q, V3 ctxP, V3 c
     if (!sample_spherical_triangle(p0, p1, p2, ctxP, u0, u1, b, &triPDF)) b[0] = b[1] = b[2] = 0;
     if (triPDF == 0) return false;
     pdf *= triPDF;
-    *pErr = gammaN(6) * (vabs(b[0] * p0) + vabs(b[1] * p1) + vabs((1 - b[0] - b[1]) * p2));
-    *pOut = b[0] * p0 + b[1] * p1 + b[2] * p2; *nOut = n; *pdfOut = pdf;
+    point_interval(b[0] * p0 + b[1] * p1 + b[2] * p2, gammaN(6) * (vabs(b[0] * p0) + vabs(b[1] * p1) + vabs((1 - b[0] - b[1]) * p2)), pOut, pErr);   // shapes.h:1117-1123
+    *nOut = n; *pdfOut = pdf;
     return true;
 }
 // shapes.h:1128-1173 Triangle::PDF(ctx, wi) evaluated at the actual hit
@@ -171,14 +171,14 @@ __device__ __noinline__ float triangle_light_pdf(const DQuad &q, V3 ctxP, V3 ctx
     V3 w0 = normalize(p0 - ctxP), w1 = normalize(p1 - ctxP), w2 = normalize(p2 - ctxP);
     float solidAngle = spherical_triangle_area(w0, w1, w2);
     if (solidAngle < kMinSphericalSampleAreaTri || solidAngle > kMaxSphericalSampleAreaTri) {
-        float r = (1 / q.area) / (absdot(hitN, -wi) / dist_sq(ctxP, hitP));
+        float r = (1 / q.area) / (absdotn(hitN, -wi) / dist_sq(ctxP, hitP));
         return isinf(r) ? 0 : r;
     }
     float pdf = 1 / solidAngle;
     if (!(ctxNs.x == 0 && ctxNs.y == 0 && ctxNs.z == 0)) {
         float uu0, uu1;
         invert_spherical_triangle_sample(p0, p1, p2, ctxP, wi, &uu0, &uu1);
-        float w[4] = {fmaxf(0.01f, absdot(ctxNs, w1)), fmaxf(0.01f, absdot(ctxNs, w1)), fmaxf(0.01f, absdot(ctxNs, w0)), fmaxf(0.01f, absdot(ctxNs, w2))};
+        float w[4] = {fmaxf(0.01f, absdotn(ctxNs, w1)), fmaxf(0.01f, absdotn(ctxNs, w1)), fmaxf(0.01f, absdotn(ctxNs, w0)), fmaxf(0.01f, absdotn(ctxNs, w2))};
         pdf *= bilinear_pdf(uu0, uu1, w);
     }
     return pdf;
@@ -199,7 +199,7 @@ __device__ __noinline__ bool sample_sphere_light(const DQuad &q, V3 ctxP, float 
         V3 wi = p - ctxP;
         if (length_sq(wi) == 0) return false;
         wi = normalize(wi);
-        float pdf = (1 / q.area) / (absdot(n, -wi) / dist_sq(ctxP, p));
+        float pdf = (1 / q.area) / (absdotn(n, -wi) / dist_sq(ctxP, p));
         if (isinf(pdf)) return false;
         *pOut = p; *nOut = n; *pdfOut = pdf;
         return true;
@@ -222,15 +222,15 @@ __device__ __noinline__ bool sample_sphere_light(const DQuad &q, V3 ctxP, float 
     V3 n = f.from_local(-w);
     V3 p = pCenter + radius * n;
     if (q.flip_normal) n = -n;
-    *pErr = gammaN(5) * vabs(p);
-    *pOut = p; *nOut = n; *pdfOut = 1 / (2 * kPi * oneMinusCosThetaMax);
+    point_interval(p, gammaN(5) * vabs(p), pOut, pErr);   // shapes.h:352-360 Interaction(Point3fi(p, pError), ...)
+    *nOut = n; *pdfOut = 1 / (2 * kPi * oneMinusCosThetaMax);
     return true;
 }
 // shapes.h:364-392 Sphere::PDF(ctx, wi)
 VD float sphere_light_pdf(const DQuad &q, V3 ctxP, V3 wi, V3 hitP, V3 hitN) {
     V3 pCenter = ld3(q.p00); float radius = q.p10[0];
     if (dist_sq(ctxP, pCenter) <= sqr(radius)) {
-        float r = (1 / q.area) / (absdot(hitN, -wi) / dist_sq(ctxP, hitP));
+        float r = (1 / q.area) / (absdotn(hitN, -wi) / dist_sq(ctxP, hitP));
         return isinf(r) ? 0 : r;
     }
     float sin2ThetaMax = radius * radius / dist_sq(ctxP, pCenter);
@@ -279,7 +279,7 @@ VD LiSample sample_li(const DScene &sc, int light, V3 ctxP, V3 ctxNs, float u0, 
         V3 v00 = normalize(p00 - ctxP), v10 = normalize(p10 - ctxP), v01 = normalize(p01 - ctxP), v11 = normalize(p11 - ctxP);
         if (!(spherical_quad_area(v00, v10, v11, v01) <= kMinSphericalSampleAreaQuad)) {
             if (!(ctxNs.x == 0 && ctxNs.y == 0 && ctxNs.z == 0)) {
-                float w[4] = {fmaxf(0.01f, absdot(v00, ctxNs)), fmaxf(0.01f, absdot(v10, ctxNs)), fmaxf(0.01f, absdot(v01, ctxNs)), fmaxf(0.01f, absdot(v11, ctxNs))};
+                float w[4] = {fmaxf(0.01f, absdotn(v00, ctxNs)), fmaxf(0.01f, absdotn(v10, ctxNs)), fmaxf(0.01f, absdotn(v01, ctxNs)), fmaxf(0.01f, absdotn(v11, ctxNs))};
                 float w0, w1;
                 sample_bilinear(u0, u1, w, &w0, &w1);
                 u0 = w0; u1 = w1;
@@ -306,18 +306,19 @@ VD LiSample sample_li(const DScene &sc, int light, V3 ctxP, V3 ctxNs, float u0, 
         pdf = bilinear_pdf(uvx, uvy, w);
     } else { uvx = u0; uvy = u1; }
     V3 pu0 = lerpv(uvy, p00, p01), pu1 = lerpv(uvy, p10, p11);
-    V3 p = lerpv(uvx, pu0, pu1);
+    V3 pLerp = lerpv(uvx, pu0, pu1);
     V3 dpdu = pu1 - pu0;
     V3 dpdv = lerpv(uvx, p01, p11) - lerpv(uvx, p00, p10);
     if (length_sq(dpdu) == 0 || length_sq(dpdv) == 0) return ls;
     V3 n = normalize(cross(dpdu, dpdv));
     if (q.flip_normal) n = -n;
-    V3 pError = gammaN(6) * (vabs(p00) + vabs(p01) + vabs(p10) + vabs(p11));
+    V3 p, pError;   // shapes.cpp:1200-1213 Interaction(Point3fi(p, pError), ...)
+    point_interval(pLerp, gammaN(6) * (vabs(p00) + vabs(p01) + vabs(p10) + vabs(p11)), &p, &pError);
     float pdfA = pdf / length(cross(dpdu, dpdv));
     V3 wi = p - ctxP;
     if (length_sq(wi) == 0) return ls;
     wi = normalize(wi);
-    float pdfW = pdfA / (absdot(n, -wi) / dist_sq(ctxP, p));
+    float pdfW = pdfA / (absdotn(n, -wi) / dist_sq(ctxP, p));
     if (isinf(pdfW)) return ls;
     if (pdfW == 0) return ls;
     V3 Le = area_L(l, n, -wi);
@@ -325,9 +326,24 @@ VD LiSample sample_li(const DScene &sc, int light, V3 ctxP, V3 ctxNs, float u0, 
     ls.valid = true; ls.L = Le; ls.wi = wi; ls.pdf = pdfW; ls.pLight = p; ls.pLightErr = pError; ls.nLight = n;
     return ls;
 }
-// lights.cpp:820-824 -> shapes.cpp:1329-1347 (area-sampling branch) evaluated at the actual hit
-VD float area_pdf_li(const DScene &sc, int light, V3 ctxP, V3 ctxNs, V3 wi, const SurfaceIntr &hit) {
-    const DQuad &q = sc.quads[sc.lights[light].shape_index];
+// lights.cpp:820-824 Light::PDF_Li -> Shape::PDF(ctx, wi): every shape first intersects ITSELF with ctx.SpawnRay(wi)
+// (shapes.cpp:1337-1341, shapes.h:1133-1137, 366-370) -- not the path's own hit, whose ray may have been re-spawned at
+// interfaces on the way.  `spawnO` is that ray's origin: OffsetRayOrigin(ctx.pi, ctx.n, wi), i.e. where the path left
+// its previous vertex (ctxP itself for a medium vertex).
+VD float area_pdf_li(const DScene &sc, int light, V3 ctxP, V3 ctxNs, V3 wi, V3 spawnO) {
+    const int prim = sc.lights[light].shape_index;
+    const DQuad &q = sc.quads[prim];
+    Hit sh; sh.prim = -1;
+    {
+        float t, u = 0, v = 0, b2;
+        bool ok;
+        if (q.kind == PRIM_SPHERE) { V3 pObj; ok = intersect_sphere(spawnO, wi, inff(), ld3(q.p00), q.p10[0], &t, &pObj); }
+        else if (q.kind == PRIM_TRIANGLE) ok = intersect_triangle(spawnO, wi, inff(), ld3(q.p00), ld3(q.p10), ld3(q.p01), &u, &v, &b2, &t);
+        else ok = intersect_bilinear_patch(spawnO, wi, ld3(q.p00), ld3(q.p10), ld3(q.p01), ld3(q.p11), &u, &v, &t);
+        if (!ok) return 0;
+        sh.t = t; sh.u = u; sh.v = v; sh.prim = prim;
+    }
+    const SurfaceIntr hit = make_intr(sc, sh, spawnO, wi, -1);
     if (q.kind == PRIM_TRIANGLE) return triangle_light_pdf(q, ctxP, ctxNs, wi, hit.p, hit.n);
     if (q.kind == PRIM_SPHERE) return sphere_light_pdf(q, ctxP, wi, hit.p, hit.n);
     V3 p00 = ld3(q.p00), p10 = ld3(q.p10), p01 = ld3(q.p01), p11 = ld3(q.p11);
@@ -338,7 +354,7 @@ VD float area_pdf_li(const DScene &sc, int light, V3 ctxP, V3 ctxNs, V3 wi, cons
         if (!(area <= kMinSphericalSampleAreaQuad)) {
             float sp = 1 / area;
             if (!(ctxNs.x == 0 && ctxNs.y == 0 && ctxNs.z == 0)) {
-                float w[4] = {fmaxf(0.01f, absdot(v00, ctxNs)), fmaxf(0.01f, absdot(v10, ctxNs)), fmaxf(0.01f, absdot(v01, ctxNs)), fmaxf(0.01f, absdot(v11, ctxNs))};
+                float w[4] = {fmaxf(0.01f, absdotn(v00, ctxNs)), fmaxf(0.01f, absdotn(v10, ctxNs)), fmaxf(0.01f, absdotn(v01, ctxNs)), fmaxf(0.01f, absdotn(v11, ctxNs))};
                 float uu0, uu1;
                 invert_spherical_rectangle_sample(ctxP, p00, p10 - p00, p01 - p00, hit.p, &uu0, &uu1);
                 return bilinear_pdf(uu0, uu1, w) * sp;
@@ -355,7 +371,7 @@ VD float area_pdf_li(const DScene &sc, int light, V3 ctxP, V3 ctxNs, V3 wi, cons
     V3 dpdu = pu1 - pu0;
     V3 dpdv = lerpv(hit.u, p01, p11) - lerpv(hit.u, p00, p10);
     float pdfA = pdf / length(cross(dpdu, dpdv));
-    float r = pdfA * (dist_sq(ctxP, hit.p) / absdot(hit.n, -wi));
+    float r = pdfA * (dist_sq(ctxP, hit.p) / absdotn(hit.n, -wi));
     return isinf(r) ? 0 : r;
 }
 
@@ -512,7 +528,7 @@ struct GuidedBSDF {
                 dist.init(&sc.surf.regions[r], p);
                 region = r;
                 V3 n = ns;
-                if (dot(-rayD, ns) < 0.f) n = -n;
+                if (dotn(-rayD, ns) < 0.f) n = -n;
                 dist.apply_cosine_product(n);
                 success = true;
             }

@@ -33,6 +33,12 @@ inline float hdop(float a, float b, float c, float d) {  // util/math.h:569 Diff
     return dop + err;
 }
 inline float hdot(H3 a, H3 b) { return a.x * b.x + a.y * b.y + a.z * b.z; }
+inline float hdotn(H3 a, H3 b) {   // Dot with a Normal3 operand (util/vecmath.h:1056-1077): FMA + compensated SumOfProducts
+    float cd = a.z * b.z;
+    float sop = std::fma(a.y, b.y, cd);
+    float err = std::fma(a.z, b.z, -cd);
+    return std::fma(a.x, b.x, sop + err);
+}
 inline H3 hcross(H3 v, H3 w) { return {hdop(v.y, w.z, v.z, w.y), hdop(v.z, w.x, v.x, w.z), hdop(v.x, w.y, v.y, w.x)}; }
 inline float hlen2(H3 v) { return v.x * v.x + v.y * v.y + v.z * v.z; }
 inline float hlen(H3 v) { return std::sqrt(hlen2(v)); }
@@ -45,7 +51,7 @@ inline float hdist(H3 a, H3 b) { return hlen(a - b); }
 inline bool quad_is_rectangle(H3 p00, H3 p10, H3 p01, H3 p11) {
     if (p00 == p01 || p01 == p11 || p11 == p10 || p10 == p00) return false;
     H3 n = hnormalize(hcross(p10 - p00, p01 - p00));
-    if (std::abs(hdot(hnormalize(p11 - p00), n)) > 1e-5f) return false;
+    if (std::abs(hdotn(hnormalize(p11 - p00), n)) > 1e-5f) return false;
     H3 pCenter = (p00 + p01 + p10 + p11) / 4;
     float d2[4] = {hdist2(p00, pCenter), hdist2(p01, pCenter), hdist2(p10, pCenter), hdist2(p11, pCenter)};
     for (int i = 1; i < 4; ++i)

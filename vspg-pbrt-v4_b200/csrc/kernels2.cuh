@@ -16,10 +16,13 @@ __global__ void __launch_bounds__(kBlock, 5) k_surface(const DScene sc, const Wa
         Hit h; h.t = hr.x; h.u = hr.y; h.v = hr.z; h.prim = __float_as_int(hr.w);
         bool toDone = false, toNext = false, toShade = false;
         if (h.prim < 0) {
-            // infinite lights (only LightType::Infinite); PDF_Li(..., allowIncompletePDF = true) = 0 for the uniform one
+            // infiniteLights = LightType::Infinite and LightType::DeltaDirection lights in this fork (cpu/integrators.h:77-81);
+            // DistantLight::Le = scale * Lemit (lights.h:290-293), zeroed beyond depth 0 (vspg.cpp:356-358);
+            // PDF_Li(..., allowIncompletePDF = true) = 0 for both
             for (int k = 0; k < sc.n_inf_lights; k++) {
                 int li = sc.inf_lights[k];
                 V3 Le = ld3(sc.lights[li].L);
+                if (sc.lights[li].type == VSPG_LIGHT_DISTANT && ps.fl.depth != 0) Le = V3();
                 if (ps.fl.depth == 0 || ps.fl.specular) ps.L = ps.L + ps.beta * Le / avg3(ps.r_u);
                 else {
                     float lightPDF = light_pmf(sc, li, ps.prevP, ps.prevNs) * 0.f;
@@ -36,7 +39,9 @@ __global__ void __launch_bounds__(kBlock, 5) k_surface(const DScene sc, const Wa
                 if (nonzero(Le)) {
                     if (ps.fl.depth == 0 || ps.fl.specular) ps.L = ps.L + ps.beta * Le / avg3(ps.r_u);
                     else {
-                        float lightPDF = light_pmf(sc, isect.areaLight, ps.prevP, ps.prevNs) * area_pdf_li(sc, isect.areaLight, ps.prevP, ps.prevNs, ps.ray.d, isect);
+                        V3 spawnO = ps.prevP;   // medium vertex: ctx.pi is exact and n = 0, SpawnRay starts at p
+                        if (nonzero(ps.prevNs)) { float4 po = W.P.prev_o[slot]; spawnO = V3(po.x, po.y, po.z); }
+                        float lightPDF = light_pmf(sc, isect.areaLight, ps.prevP, ps.prevNs) * area_pdf_li(sc, isect.areaLight, ps.prevP, ps.prevNs, ps.ray.d, spawnO);
                         ps.r_l = ps.r_l * lightPDF;
                         float w_l = ip.use_nee ? 1.0f / avg3(ps.r_u + ps.r_l) : 1.0f;
                         ps.L = ps.L + ps.beta * w_l * Le;
@@ -95,7 +100,7 @@ __global__ void __launch_bounds__(G > 0 ? 256 : kBlock, G > 0 ? 3 : 1) k_shade(c
             {
                 if (ls.valid) {
                     float p_l = ls.p_l;
-                    V3 f_hat = gbsdf.f(wo, ls.wi) * absdot(ls.wi, isect.ns);
+                    V3 f_hat = gbsdf.f(wo, ls.wi) * absdotn(ls.wi, isect.ns);
                     float scatterPDF = 1.0f * gbsdf.pdf(wo, ls.wi);
                     if (nonzero(f_hat)) {
                         ShadowRec sr;
@@ -121,13 +126,14 @@ __global__ void __launch_bounds__(G > 0 ? 256 : kBlock, G > 0 ? 3 : 1) k_shade(c
         if (alive) {
             ps.fl.lastVertexVolume = false;
             ps.rr_correction *= bs.pdf / bs.scatPdf;
-            V3 bsdfWeight = bs.f * absdot(bs.wi, isect.ns) / bs.pdf;
+            V3 bsdfWeight = bs.f * absdotn(bs.wi, isect.ns) / bs.pdf;
             ps.beta = ps.beta * bsdfWeight;
             ps.r_l = ps.r_u / bs.misPdf;
             ps.fl.specular = false; ps.fl.anyNonSpecular = true;
             ps.ray.o = offset_ray_origin(isect.p, isect.pError, isect.n, bs.wi);
             ps.ray.d = bs.wi;
             ps.ray.medium = isect.get_medium(bs.wi);
+            if (leader && live) W.P.prev_o[slot] = make_float4(ps.ray.o.x, ps.ray.o.y, ps.ray.o.z, 0.f);
             ps.vsp_next = gbsdf.vsp(bs.wi);
             if (!nonzero(ps.beta)) alive = false;
         }

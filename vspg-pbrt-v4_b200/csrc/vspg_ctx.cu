@@ -329,8 +329,8 @@ int vspg_set_scene(vspg_ctx *ctx, const vspg_scene_desc *s) {
             lightArea[i] = quads[d.shape_index].area;
             break;
         }
-        case VSPG_LIGHT_POINT: case VSPG_LIGHT_DISTANT: break;
-        case VSPG_LIGHT_UNIFORM_INFINITE: inf.push_back(i); break;
+        case VSPG_LIGHT_POINT: break;
+        case VSPG_LIGHT_DISTANT: case VSPG_LIGHT_UNIFORM_INFINITE: inf.push_back(i); break;   // Integrator::infiniteLights (cpu/integrators.h:77-81)
         default: return fail(ctx, VSPG_ERR_UNSUPPORTED, "set_scene: light %d has unsupported type %d", i, l.type);
         }
     }
