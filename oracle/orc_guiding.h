@@ -268,14 +268,14 @@ struct VMM {
         if (sK == 0.0f) {  // openpgl_common.h:330 squareToUniformSphere
             float z = 1.0f - 2.0f * s1;
             float r = std::sqrt(std::max(0.f, (1.0f - z * z)));
-            float sp, cp; sincosf(2.0f * M_PI_F * s0, &sp, &cp);
+            float sp, cp; vspg_sincosf(2.0f * M_PI_F * s0, &sp, &cp);
             dir = V3(r * cp, r * sp, z);
         } else {
             float cosTheta = 1.f + (pgl_log(1.0f + ((sE - 1.f) * s0))) / sK;
             cosTheta = std::min(1.0f, std::max(cosTheta, -1.f));
             float sinTheta = std::sqrt(1.f - cosTheta * cosTheta);
             float phi = 2.f * M_PI_F * s1;
-            float sp, cp; sincosf(phi, &sp, &cp);
+            float sp, cp; vspg_sincosf(phi, &sp, &cp);
             dir = V3(sinTheta * cp, sinTheta * sp, cosTheta);
         }
         // embree::frame(N) linearspace3.h:117-124; normalize(a) = a*rsqrt(dot(a,a)) with the scalar
@@ -320,7 +320,7 @@ struct SamplingDistribution {
     }
     void applyCosineProduct(V3 normal) {
         const float cosine_kappa = 2.18853f;
-        const float cosine_normalization = 2.18853f / (2.0f * M_PI_F * (1.0f - std::exp(-2.0f * 2.18853f)));
+        const float cosine_normalization = 2.18853f / (2.0f * M_PI_F * (1.0f - vspg_expf(-2.0f * 2.18853f)));
         if (numDist > 0) productIntegral = dists[0].product(1.0f, normal, cosine_kappa, cosine_normalization);
     }
     void applyHGProduct(V3 dir, float meanCosine) {

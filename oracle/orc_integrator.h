@@ -267,8 +267,8 @@ struct Scene {
             for (int i = 0; i < 3; ++i) {
                 float up = 0.5f + float(i) / 3;
                 if (up > 1) up -= 1;
-                float lambda = 538 - 138.888889f * std::atanh(0.85691062f - 1.82750197f * up);
-                pdf[i] = (lambda < 360 || lambda > 830) ? 0.f : 0.0039398042f / Sqr(std::cosh(0.0072f * (lambda - 538)));
+                float lambda = 538 - 138.888889f * vspg_atanhf(0.85691062f - 1.82750197f * up);
+                pdf[i] = (lambda < 360 || lambda > 830) ? 0.f : 0.0039398042f / Sqr(vspg_coshf(0.0072f * (lambda - 538)));
             }
             int n = d->n_lights;
             std::vector<float> lightPower;
@@ -1195,7 +1195,7 @@ struct Integrator {
                         NDS_plus = true;
                         float trEstCache = sc->g->tr_rgb[3 * ((size_t)py * sc->g->tr_width + px) + ch];
                         float gamma = 1 + trEstCache;
-                        pScatter = std::pow(pScatter, 1 / gamma);
+                        pScatter = vspg_powf(pScatter, 1 / gamma);
                     }
                     float pNull = std::max<float>(0, 1 - pScatter);
                     float um = rng.Uniform();

@@ -31,7 +31,7 @@ struct DirectionCone {
     bool IsEmpty() const { return cosTheta == Infinity; }
     static DirectionCone EntireSphere() { DirectionCone c; c.w = V3(0, 0, 1); c.cosTheta = -1; return c; }
 };
-inline float SafeACos_(float x) { return std::acos(std::min(1.f, std::max(-1.f, x))); }
+inline float SafeACos_(float x) { return vspg_acosf(std::min(1.f, std::max(-1.f, x))); }
 inline float AngleBetween(V3 v1, V3 v2) {  // vecmath.h:972-977
     if (Dot(v1, v2) < 0) return Pi - 2 * SafeASin(Length(v1 + v2) / 2);
     return 2 * SafeASin(Length(v2 - v1) / 2);
@@ -39,7 +39,7 @@ inline float AngleBetween(V3 v1, V3 v2) {  // vecmath.h:972-977
 // util/transform.cpp Rotate(theta degrees, axis) applied to a vector
 inline V3 RotateDeg(float thetaDeg, V3 axis, V3 v) {
     float th = (Pi / 180) * thetaDeg;
-    float sinTheta = std::sin(th), cosTheta = std::cos(th);
+    float sinTheta = vspg_sinf(th), cosTheta = vspg_cosf(th);
     V3 a = Normalize(axis);
     float m00 = a.x * a.x + (1 - a.x * a.x) * cosTheta, m01 = a.x * a.y * (1 - cosTheta) - a.z * sinTheta, m02 = a.x * a.z * (1 - cosTheta) + a.y * sinTheta;
     float m10 = a.x * a.y * (1 - cosTheta) + a.z * sinTheta, m11 = a.y * a.y + (1 - a.y * a.y) * cosTheta, m12 = a.y * a.z * (1 - cosTheta) - a.x * sinTheta;
@@ -59,7 +59,7 @@ inline DirectionCone Union(const DirectionCone &a, const DirectionCone &b) {  //
     V3 wr = Cross(a.w, b.w);
     if (LengthSquared(wr) == 0) return DirectionCone::EntireSphere();
     V3 w = RotateDeg((180 / Pi) * theta_r, wr, a.w);
-    DirectionCone r; r.w = Normalize(w); r.cosTheta = std::cos(theta_o);
+    DirectionCone r; r.w = Normalize(w); r.cosTheta = vspg_cosf(theta_o);
     return r;
 }
 
@@ -182,11 +182,11 @@ struct BVHLightSampler {
 
     static float EvaluateCost(const LightBounds &b, const LBox &bounds, int dim) {   // lightsamplers.h:383-396
         if (b.phi == 0) return 0;   // an empty side; the reference reads uninitialised cosines here (see host_lightbvh.h)
-        float theta_o = std::acos(b.cosTheta_o), theta_e = std::acos(b.cosTheta_e);
+        float theta_o = vspg_acosf(b.cosTheta_o), theta_e = vspg_acosf(b.cosTheta_e);
         float theta_w = std::min(theta_o + theta_e, Pi);
         float sinTheta_o = SafeSqrt(1 - Sqr(b.cosTheta_o));
         float M_omega = 2 * Pi * (1 - b.cosTheta_o) +
-                        Pi / 2 * (2 * theta_w * sinTheta_o - std::cos(theta_o - 2 * theta_w) - 2 * theta_o * sinTheta_o + b.cosTheta_o);
+                        Pi / 2 * (2 * theta_w * sinTheta_o - vspg_cosf(theta_o - 2 * theta_w) - 2 * theta_o * sinTheta_o + b.cosTheta_o);
         V3 d = bounds.Diagonal();
         float Kr = std::max({d.x, d.y, d.z}) / d[dim];
         return b.phi * M_omega * Kr * b.bounds.SurfaceArea();
@@ -206,21 +206,21 @@ struct BVHLightSampler {
             float maxL = std::max({l.L[0], l.L[1], l.L[2]});
             if (l.type == VSPG_LIGHT_POINT) {   // lights.cpp:200-205
                 lb.bounds.pMin = lb.bounds.pMax = V3(l.pos);
-                lb.w = V3(0, 0, 1); lb.phi = 4 * Pi * l.scale * maxL; lb.cosTheta_o = std::cos(Pi); lb.cosTheta_e = std::cos(Pi / 2); lb.twoSided = false;
+                lb.w = V3(0, 0, 1); lb.phi = 4 * Pi * l.scale * maxL; lb.cosTheta_o = vspg_cosf(Pi); lb.cosTheta_e = vspg_cosf(Pi / 2); lb.twoSided = false;
             } else if (l.type == VSPG_LIGHT_DIFFUSE_AREA && l.shape_kind == 1) {   // Triangle::Bounds / NormalBounds
                 const vspg_triangle &q = tris[l.shape_index];
                 V3 p0(q.p0), p1(q.p1), p2(q.p2);
                 lb.bounds = Union(Union(Union(LBox(), p0), p1), p2);
                 V3 n = Normalize(Cross(p1 - p0, p2 - p0));
                 if (q.flip_normal) n = -n;
-                lb.w = Normalize(n); lb.phi = maxL; lb.phi *= l.scale * (*triArea)[l.shape_index] * Pi; lb.cosTheta_o = 1; lb.cosTheta_e = std::cos(Pi / 2);
+                lb.w = Normalize(n); lb.phi = maxL; lb.phi *= l.scale * (*triArea)[l.shape_index] * Pi; lb.cosTheta_o = 1; lb.cosTheta_e = vspg_cosf(Pi / 2);
                 lb.twoSided = l.two_sided != 0;
             } else if (l.type == VSPG_LIGHT_DIFFUSE_AREA && l.shape_kind == 2) {   // Sphere::Bounds, NormalBounds = EntireSphere
                 const vspg_sphere &q = spheres[l.shape_index];
                 V3 c(q.center);
                 lb.bounds.pMin = V3(-q.radius + c.x, -q.radius + c.y, -q.radius + c.z);
                 lb.bounds.pMax = V3(q.radius + c.x, q.radius + c.y, q.radius + c.z);
-                lb.w = V3(0, 0, 1); lb.phi = maxL; lb.phi *= l.scale * (*sphereArea)[l.shape_index] * Pi; lb.cosTheta_o = -1; lb.cosTheta_e = std::cos(Pi / 2);
+                lb.w = V3(0, 0, 1); lb.phi = maxL; lb.phi *= l.scale * (*sphereArea)[l.shape_index] * Pi; lb.cosTheta_o = -1; lb.cosTheta_e = vspg_cosf(Pi / 2);
                 lb.twoSided = l.two_sided != 0;
             } else if (l.type == VSPG_LIGHT_DIFFUSE_AREA) {   // lights.cpp:845-864 + shapes.cpp:1070-1126
                 const vspg_quad &q = quads[l.shape_index];
@@ -242,7 +242,7 @@ struct BVHLightSampler {
                     cosTheta = std::min({Dot(n, n00), Dot(n, n01), Dot(n, n10), Dot(n, n11)});
                     cosTheta = std::min(1.f, std::max(-1.f, cosTheta));
                 }
-                lb.w = Normalize(n); lb.phi = maxL; lb.phi *= l.scale * quadArea[l.shape_index] * Pi; lb.cosTheta_o = cosTheta; lb.cosTheta_e = std::cos(Pi / 2);
+                lb.w = Normalize(n); lb.phi = maxL; lb.phi *= l.scale * quadArea[l.shape_index] * Pi; lb.cosTheta_o = cosTheta; lb.cosTheta_e = vspg_cosf(Pi / 2);
                 lb.twoSided = l.two_sided != 0;
             } else { infiniteLights.push_back(i); continue; }
             if (lb.phi > 0) {

@@ -7,6 +7,7 @@
 // This header: scalar/vector helpers, PCG32, MurmurHash, FastExp, sampling routines.
 // Each function cites the reference file:line it follows (paths relative to /root/reference/src).
 #pragma once
+#include "../include/vspg_libm.h"   // the libm the path is defined with (portable: same bits as the CUDA kernels; oracle/portm_shim.cpp gives it to the reference)
 #include <algorithm>
 #include <cmath>
 #include <cstdint>
@@ -28,7 +29,7 @@ static constexpr float ShadowEpsilon = 0.0001f;                                 
 inline constexpr float gamma_(int n) { return (n * MachineEpsilon) / (1 - n * MachineEpsilon); }  // float.h:195
 inline float Sqr(float v) { return v * v; }
 inline float SafeSqrt(float x) { return std::sqrt(std::max(0.f, x)); }
-inline float SafeASin(float x) { return std::asin(std::min(1.f, std::max(-1.f, x))); }
+inline float SafeASin(float x) { return vspg_asinf(std::min(1.f, std::max(-1.f, x))); }
 inline float Lerp(float x, float a, float b) { return (1 - x) * a + x * b; }  // math.h:210
 template <typename T, typename U, typename V>
 inline T Clamp(T val, U low, V high) {  // math.h:137
@@ -133,7 +134,7 @@ struct Frame {  // vecmath.h Frame
     V3 FromLocal(V3 v) const { return v.x * x + v.y * y + v.z * z; }
 };
 inline V3 SphericalDirection(float sinTheta, float cosTheta, float phi) {  // vecmath.h
-    return {Clamp(sinTheta, -1, 1) * std::cos(phi), Clamp(sinTheta, -1, 1) * std::sin(phi), Clamp(cosTheta, -1, 1)};
+    return {Clamp(sinTheta, -1, 1) * vspg_cosf(phi), Clamp(sinTheta, -1, 1) * vspg_sinf(phi), Clamp(cosTheta, -1, 1)};
 }
 
 // RGB "SampledSpectrum" (NSpectrumSamples = 3 in the reference's RGB build, util/spectrum.h:40-44)
@@ -249,7 +250,7 @@ struct Sampler {
     void Get2D(float *u) { u[0] = rng.Uniform(); u[1] = rng.Uniform(); }
 };
 
-inline float SampleExponential(float u, float a) { return -std::log(1 - u) / a; }  // sampling.h:222
+inline float SampleExponential(float u, float a) { return -vspg_logf(1 - u) / a; }  // sampling.h:222
 inline float HenyeyGreenstein(float cosTheta, float g) {                             // scattering.h:50
     g = Clamp(g, -.99, .99);
     float denom = 1 + Sqr(g) + 2 * g * cosTheta;
@@ -273,7 +274,7 @@ inline void SampleUniformDiskConcentric(const float *u, float *d) {  // sampling
     float theta, r;
     if (std::abs(ox) > std::abs(oy)) { r = ox; theta = PiOver4 * (oy / ox); }
     else { r = oy; theta = PiOver2 - PiOver4 * (ox / oy); }
-    d[0] = r * std::cos(theta); d[1] = r * std::sin(theta);
+    d[0] = r * vspg_cosf(theta); d[1] = r * vspg_sinf(theta);
 }
 inline V3 SampleCosineHemisphere(const float *u) {
     float d[2]; SampleUniformDiskConcentric(u, d);
@@ -285,7 +286,7 @@ inline V3 SampleUniformSphere(const float *u) {
     float z = 1 - 2 * u[0];
     float r = SafeSqrt(1 - Sqr(z));
     float phi = 2 * Pi * u[1];
-    return {r * std::cos(phi), r * std::sin(phi), z};
+    return {r * vspg_cosf(phi), r * vspg_sinf(phi), z};
 }
 // sampling.h:134-160
 inline float BilinearPDF(const float *p, const float *w) {

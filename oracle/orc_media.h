@@ -346,7 +346,7 @@ S3 SampleT_maj_Resampling(const Medium &med, Ray ray, float tMax, float u, RNG &
     majorantScale = 1.0f;
     volumeRatioZeroCandidateCompensation = volScatterProb;
     if (guideScatterDecision) {
-        float minTotalLength = -std::log(1 - volScatterProb);
+        float minTotalLength = -vspg_logf(1 - volScatterProb);
         if (minTotalLength > totalLength) {
             majorantScale = minTotalLength / totalLength;
             totalLength = minTotalLength;
@@ -418,7 +418,7 @@ S3 SampleT_maj_OpticalDepthSpace(const Medium &med, Ray ray, float tMax, float u
     if (NDS) {
         if (vsp < 1 - FastExp(-t_v)) return SampleT_maj(med, ray, tMax, u, rng, ch, st, plain);  // (already-normalised ray, as in the reference)
         else {
-            t_n = (float)(-std::log(1.0 - OneMinusENegTv / vsp));  // double arithmetic as in the reference (1.0 literal)
+            t_n = (float)(-vspg_log(1.0 - OneMinusENegTv / vsp));  // double arithmetic as in the reference (1.0 literal)
             t_n_current = t_n;
         }
     }
@@ -465,14 +465,14 @@ S3 SampleT_maj_OpticalDepthSpace(const Medium &med, Ray ray, float tMax, float u
             S3 tpSingle;
             if (NDS) {
                 tpSingle = S3(1.0f) - FastExp(-t_n_current * normalizedMaj);
-                if (!deltaTracking) dist = (float)(-std::log(1.0 - u * tpSingle[ch]));
+                if (!deltaTracking) dist = (float)(-vspg_log(1.0 - u * tpSingle[ch]));
             } else {
                 tpSingle = (S3(1.0f) - FastExp(-t_v_current * normalizedMaj)) / vsp;
                 if (!deltaTracking) {
-                    if (u < vsp) dist = (float)(-std::log(1.0 - u * tpSingle[ch]));
+                    if (u < vsp) dist = (float)(-vspg_log(1.0 - u * tpSingle[ch]));
                 }
             }
-            if (deltaTracking) dist = (float)(-std::log(1.0 - u));
+            if (deltaTracking) dist = (float)(-vspg_log(1.0 - u));
             bool passThrough = t_v_current - dist < ScatterEpsilon || dist == 0;
             if (NDS || !passThrough) tpScaleFactor *= tpSingle;
             if (passThrough) {

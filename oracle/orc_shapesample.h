@@ -41,7 +41,7 @@ inline V3 SampleSphericalRectangle(V3 pRef, V3 s, V3 ex, V3 ey, const float *u, 
     if (solidAngle < 1e-3) return s + u[0] * ex + u[1] * ey;
     float b0 = n0.z, b1 = n2.z;
     float au = u[0] * (g0 + g1 - 2 * Pi) + (u[0] - 1) * (g2 + g3);
-    float fu = (std::cos(au) * b0 - b1) / std::sin(au);
+    float fu = (vspg_cosf(au) * b0 - b1) / vspg_sinf(au);
     float cu = std::copysign(1 / std::sqrt(Sqr(fu) + Sqr(b0)), fu);
     cu = Clamp(cu, -OneMinusEpsilon, OneMinusEpsilon);
     float xu = -(cu * z0) / SafeSqrt(1 - Sqr(cu));
@@ -85,7 +85,7 @@ inline void InvertSphericalRectangleSample(V3 pRef, V3 s, V3 ex, V3 ey, V3 pRect
     float fusq = invcusq - b0sq;
     float fu = std::copysign(std::sqrt(fusq), xu);
     float sqrt_ = SafeSqrt(DifferenceOfProducts(b0, b0, b1, b1) + fusq);
-    float au = std::atan2(-(b1 * fu) - std::copysign(b0 * sqrt_, fu * b0), b0 * b1 - sqrt_ * std::abs(fu));
+    float au = vspg_atan2f(-(b1 * fu) - std::copysign(b0 * sqrt_, fu * b0), b0 * b1 - sqrt_ * std::abs(fu));
     if (au > 0) au -= 2 * Pi;
     if (fu == 0) au = Pi;
     float u0 = (au + g2 + g3) / solidAngle;
@@ -108,7 +108,7 @@ constexpr float MinSphericalSampleAreaTri = 3e-4f, MaxSphericalSampleAreaTri = 6
 
 inline V3 GramSchmidt(V3 v, V3 w) { return v - Dot(v, w) * w; }   // vecmath.h:994
 inline float SphericalTriangleArea(V3 a, V3 b, V3 c) {            // vecmath.h:1638-1641
-    return std::abs(2 * std::atan2(Dot(a, Cross(b, c)), 1 + Dot(a, b) + Dot(a, c) + Dot(b, c)));
+    return std::abs(2 * vspg_atan2f(Dot(a, Cross(b, c)), 1 + Dot(a, b) + Dot(a, c) + Dot(b, c)));
 }
 inline void SampleUniformTriangle(const float *u, float *b) {     // sampling.h:173-183
     float b0, b1;
@@ -128,9 +128,9 @@ inline bool SampleSphericalTriangle(const V3 *v, V3 p, const float *u, float *ba
     float Ap_pi = Lerp(u[0], Pi, A_pi);
     float A = A_pi - Pi;
     *pdf = (A <= 0) ? 0 : 1 / A;
-    float cosAlpha = std::cos(alpha), sinAlpha = std::sin(alpha);
-    float sinPhi = std::sin(Ap_pi) * cosAlpha - std::cos(Ap_pi) * sinAlpha;
-    float cosPhi = std::cos(Ap_pi) * cosAlpha + std::sin(Ap_pi) * sinAlpha;
+    float cosAlpha = vspg_cosf(alpha), sinAlpha = vspg_sinf(alpha);
+    float sinPhi = vspg_sinf(Ap_pi) * cosAlpha - vspg_cosf(Ap_pi) * sinAlpha;
+    float cosPhi = vspg_cosf(Ap_pi) * cosAlpha + vspg_sinf(Ap_pi) * sinAlpha;
     float k1 = cosPhi + cosAlpha;
     float k2 = sinPhi - sinAlpha * Dot(a, b);
     float cosBp = (k2 + (DifferenceOfProducts(k2, cosPhi, k1, sinPhi)) * cosAlpha) / ((SumOfProducts(k2, sinPhi, k1, cosPhi)) * sinAlpha);

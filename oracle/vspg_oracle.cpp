@@ -365,7 +365,7 @@ int orc_render_pixel_sample(const vspg_scene_desc *scene, const vspg_guiding_des
 
 int orc_camera_ray(const vspg_scene_desc *scene, int px, int py, int sampleIndex, int seed, float *o3, float *d3, int *ch) {
     vspg_integrator_params ip; std::memset(&ip, 0, sizeof(ip));
-    Scene sc; sc.d = scene; sc.seed = seed;
+    Scene sc; sc.init(scene, nullptr, &ip, true); sc.seed = seed;   // (the tabulated gaussian filter is part of the scene set-up)
     Integrator integ; integ.sc = &sc;
     Sampler sampler; sampler.StartPixelSample(px, py, seed, sampleIndex);
     Ray ray; float fw;

@@ -251,13 +251,14 @@ template <int G> __device__ __noinline__ V3 mix_sample(Lobe L, int n, float s0, 
     if (sK == 0.0f) {  // openpgl_common.h:330 squareToUniformSphere
         float z = 1.0f - 2.0f * s1;
         float r = sqrtf(fmaxf(0.f, (1.0f - z * z)));
-        float sp, cp; sincospif(2.0f * s0, &sp, &cp);   // sincosf(2*pi*s0) up to the rounding of the product
+        float sp, cp; vspg_sincosf(2.0f * kPi * s0, &sp, &cp);   // sincosf(2.0f * M_PI_F * s0)
         dir = V3(r * cp, r * sp, z);
     } else {
         float cosTheta = 1.f + (pgl_log(1.0f + ((sE - 1.f) * s0))) / sK;
         cosTheta = fminf(1.0f, fmaxf(cosTheta, -1.f));
         float sinTheta = sqrtf(1.f - cosTheta * cosTheta);
-        float sp, cp; sincospif(2.f * s1, &sp, &cp);    // sincosf(2*pi*s1) up to the rounding of the product
+        float phi = 2.f * kPi * s1;
+        float sp, cp; vspg_sincosf(phi, &sp, &cp);
         dir = V3(sinTheta * cp, sinTheta * sp, cosTheta);
     }
     // embree::frame(N), linearspace3.h:117-124 (the CPU's rsqrtss+Newton normalise is replaced by an exact one)

@@ -5,6 +5,7 @@
 #pragma once
 #include <cuda_runtime.h>
 #include <stdint.h>
+#include "../../include/vspg_libm.h"   // log / sin / cos / asin / atan2 / pow: the path's portable libm (bit-identical on host and device)
 
 #define VD __device__ __forceinline__
 
@@ -173,7 +174,7 @@ struct Frame {
 // float rounding of the product 2*pi*u (<= 4e-7 rad), without dragging libdevice's large-argument reduction into
 // every scatter kernel (it was 470 SASS instructions per call site).
 VD V3 spherical_direction_2pi(float sinTheta, float cosTheta, float u) {
-    float sp, cp; sincospif(2.f * u, &sp, &cp);
+    float sp, cp; vspg_sincosf(2 * kPi * u, &sp, &cp);   // phi = 2 * Pi * u[1]; cos(phi), sin(phi)
     return V3(clampf(sinTheta, -1, 1) * cp, clampf(sinTheta, -1, 1) * sp, clampf(cosTheta, -1, 1));
 }
 
@@ -239,7 +240,7 @@ struct Rng {
 };
 
 // ------------------------------------------------------------------ sampling routines
-VD float sample_exponential(float u, float a) { return -logf(1 - u) / a; }  // util/sampling.h:222
+VD float sample_exponential(float u, float a) { return -vspg_logf(1 - u) / a; }  // util/sampling.h:222
 VD float henyey_greenstein(float cosTheta, float g) {                        // util/scattering.h:50
     g = clampf(g, -.99f, .99f);
     float denom = 1 + sqr(g) + 2 * g * cosTheta;
@@ -262,7 +263,7 @@ VD void sample_uniform_disk_concentric(float u0, float u1, float *dx, float *dy)
     float theta, r;
     if (fabsf(ox) > fabsf(oy)) { r = ox; theta = kPiOver4 * (oy / ox); }
     else { r = oy; theta = kPiOver2 - kPiOver4 * (ox / oy); }
-    *dx = r * cosf(theta); *dy = r * sinf(theta);
+    *dx = r * vspg_cosf(theta); *dy = r * vspg_sinf(theta);
 }
 VD V3 sample_cosine_hemisphere(float u0, float u1) {
     float dx, dy; sample_uniform_disk_concentric(u0, u1, &dx, &dy);

@@ -111,7 +111,7 @@ VD void sample_distance(const DScene &sc, PathRegs &ps, float tHit, TrackCounter
                     NDS_plus = true;
                     float trEstCache = __ldg(&sc.tr_rgb[3 * ((size_t)py * sc.tr_w + px) + ch]);
                     float gamma = 1 + trEstCache;
-                    pScatter = powf(pScatter, 1 / gamma);
+                    pScatter = vspg_powf(pScatter, 1 / gamma);
                 }
                 float pNull = fmaxf(0.f, 1 - pScatter);
                 float um = rng.uniform();

@@ -10,7 +10,7 @@ namespace vspg {
 
 constexpr float kMinSphericalSampleAreaQuad = 1e-4f;   // shapes.h:1538
 
-VD float safe_asin(float x) { return asinf(fminf(1.f, fmaxf(-1.f, x))); }
+VD float safe_asin(float x) { return vspg_asinf(fminf(1.f, fmaxf(-1.f, x))); }
 VD float angle_between(V3 v1, V3 v2) {   // util/vecmath.h:972-977
     if (dot(v1, v2) < 0) return kPi - 2 * safe_asin(length(v1 + v2) / 2);
     return 2 * safe_asin(length(v2 - v1) / 2);
@@ -57,7 +57,7 @@ __device__ __noinline__ V3 sample_spherical_rectangle(V3 pRef, V3 s, V3 ex, V3 e
     *pdf = fmaxf(0.f, 1 / solidAngle);
     if (solidAngle < 0.001f) return s + u0 * ex + u1 * ey;   // `< 1e-3` in double: the same set of floats
     float au = u0 * (q.g0 + q.g1 - 2 * kPi) + (u0 - 1) * (q.g2 + q.g3);
-    float fu = (cosf(au) * q.b0 - q.b1) / sinf(au);
+    float fu = (vspg_cosf(au) * q.b0 - q.b1) / vspg_sinf(au);
     float cu = copysignf(1 / sqrtf(sqr(fu) + sqr(q.b0)), fu);
     cu = clampf(cu, -kOneMinusEpsilon, kOneMinusEpsilon);
     float xu = -(cu * q.z0) / safe_sqrt(1 - sqr(cu));
@@ -87,7 +87,7 @@ __device__ __noinline__ void invert_spherical_rectangle_sample(V3 pRef, V3 s, V3
     float fusq = invcusq - b0sq;
     float fu = copysignf(sqrtf(fusq), xu);
     float root = safe_sqrt(diff_of_products(q.b0, q.b0, q.b1, q.b1) + fusq);
-    float au = atan2f(-(q.b1 * fu) - copysignf(q.b0 * root, fu * q.b0), q.b0 * q.b1 - root * fabsf(fu));
+    float au = vspg_atan2f(-(q.b1 * fu) - copysignf(q.b0 * root, fu * q.b0), q.b0 * q.b1 - root * fabsf(fu));
     if (au > 0) au -= 2 * kPi;
     if (fu == 0) au = kPi;
     float u0 = (au + q.g2 + q.g3) / solidAngle;
@@ -110,7 +110,7 @@ constexpr float kMinSphericalSampleAreaTri = 3e-4f, kMaxSphericalSampleAreaTri =
 
 VD V3 gram_schmidt(V3 v, V3 w) { return v - dot(v, w) * w; }
 VD float spherical_triangle_area(V3 a, V3 b, V3 c) {              // util/vecmath.h:1638-1641
-    return fabsf(2 * atan2f(dot(a, cross(b, c)), 1 + dot(a, b) + dot(a, c) + dot(b, c)));
+    return fabsf(2 * vspg_atan2f(dot(a, cross(b, c)), 1 + dot(a, b) + dot(a, c) + dot(b, c)));
 }
 
 // util/sampling.cpp:28-107; false = the reference's empty return
@@ -125,9 +125,9 @@ __device__ __noinline__ bool sample_spherical_triangle(V3 v0, V3 v1, V3 v2, V3 p
     float Ap_pi = lerpf(u0, kPi, A_pi);
     float A = A_pi - kPi;
     *pdf = (A <= 0) ? 0 : 1 / A;
-    float cosAlpha = cosf(alpha), sinAlpha = sinf(alpha);
-    float sinPhi = sinf(Ap_pi) * cosAlpha - cosf(Ap_pi) * sinAlpha;
-    float cosPhi = cosf(Ap_pi) * cosAlpha + sinf(Ap_pi) * sinAlpha;
+    float cosAlpha = vspg_cosf(alpha), sinAlpha = vspg_sinf(alpha);
+    float sinPhi = vspg_sinf(Ap_pi) * cosAlpha - vspg_cosf(Ap_pi) * sinAlpha;
+    float cosPhi = vspg_cosf(Ap_pi) * cosAlpha + vspg_sinf(Ap_pi) * sinAlpha;
     float k1 = cosPhi + cosAlpha;
     float k2 = sinPhi - sinAlpha * dot(a, b);
     float cosBp = (k2 + (diff_of_products(k2, cosPhi, k1, sinPhi)) * cosAlpha) / ((sum_of_products(k2, sinPhi, k1, cosPhi)) * sinAlpha);

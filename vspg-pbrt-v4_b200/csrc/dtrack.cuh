@@ -70,7 +70,7 @@ VD V3 track_resampling(const DMedium &med, const Ray &ray, float tMax, float u, 
     majorantScale = 1.0f;
     volumeRatioComp = volScatterProb;
     if (guideScatterDecision) {
-        float minTotalLength = -logf(1 - volScatterProb);
+        float minTotalLength = -vspg_logf(1 - volScatterProb);
         if (minTotalLength > totalLength) {
             majorantScale = minTotalLength / totalLength;
             totalLength = minTotalLength;
@@ -140,7 +140,7 @@ VD V3 track_optical_depth(const DMedium &med, const Ray &ray, float tMax, float 
     float t_n = -1.f, t_n_current = -1.f;
     if (NDS) {
         if (vsp < 1 - fast_exp(-t_v)) return track_T_maj(med, ray, tMax, u, rng, ch, tc, plain);
-        t_n = (float)(-log(1.0 - (double)(OneMinusENegTv / vsp)));  // the reference's 1.0 literal promotes to double
+        t_n = (float)(-vspg_log(1.0 - (double)(OneMinusENegTv / vsp)));  // the reference's 1.0 literal promotes to double
         t_n_current = t_n;
     }
     V3 T_maj = splat(1.f), tpScaleFactor = splat(1.f);
@@ -186,14 +186,14 @@ VD V3 track_optical_depth(const DMedium &med, const Ray &ray, float tMax, float 
             V3 tpSingle;
             if (NDS) {
                 tpSingle = splat(1.0f) - fast_exp3(-t_n_current * normalizedMaj);
-                if (!deltaTracking) dist = (float)(-log(1.0 - (double)(u * tpSingle[ch])));
+                if (!deltaTracking) dist = (float)(-vspg_log(1.0 - (double)(u * tpSingle[ch])));
             } else {
                 tpSingle = (splat(1.0f) - fast_exp3(-t_v_current * normalizedMaj)) / vsp;
                 if (!deltaTracking) {
-                    if (u < vsp) dist = (float)(-log(1.0 - (double)(u * tpSingle[ch])));
+                    if (u < vsp) dist = (float)(-vspg_log(1.0 - (double)(u * tpSingle[ch])));
                 }
             }
-            if (deltaTracking) dist = (float)(-log(1.0 - (double)u));
+            if (deltaTracking) dist = (float)(-vspg_log(1.0 - (double)u));
             bool passThrough = t_v_current - dist < ScatterEpsilon || dist == 0;
             if (NDS || !passThrough) tpScaleFactor = tpScaleFactor * tpSingle;
             if (passThrough) {

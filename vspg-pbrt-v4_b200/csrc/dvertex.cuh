@@ -189,7 +189,7 @@ __device__ __noinline__ bool sample_sphere_light(const DQuad &q, V3 ctxP, float 
     V3 pCenter = ld3(q.p00); float radius = q.p10[0];
     if (dist_sq(ctxP, pCenter) <= sqr(radius)) {
         float z = 1 - 2 * u0, r = safe_sqrt(1 - sqr(z));
-        float sp, cp; sincospif(2.f * u1, &sp, &cp);
+        float sp, cp; vspg_sincosf(2 * kPi * u1, &sp, &cp);   // SampleUniformSphere: phi = 2 * Pi * u[1]
         V3 pObj = radius * V3(r * cp, r * sp, z);
         pObj = pObj * (radius / length(pObj));
         V3 n = normalize(pObj);

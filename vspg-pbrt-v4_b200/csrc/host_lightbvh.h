@@ -9,6 +9,7 @@
 // Vector3f(w) return): the decode is a fixed sequence of IEEE operations, so doing it once here gives the device the
 // same numbers the reference recomputes at every Importance() call.
 #pragma once
+#include "../../include/vspg_libm.h"   // the path's libm (portable, identical on host and device)
 #include <algorithm>
 #include <cmath>
 #include <cstdint>
@@ -42,8 +43,8 @@ struct HostLightBvh {
 
 namespace lbvh {
 constexpr float kPi = 3.14159265358979323846f;
-inline float safe_acos(float x) { return std::acos(std::min(1.f, std::max(-1.f, x))); }
-inline float safe_asin(float x) { return std::asin(std::min(1.f, std::max(-1.f, x))); }
+inline float safe_acos(float x) { return vspg_acosf(std::min(1.f, std::max(-1.f, x))); }
+inline float safe_asin(float x) { return vspg_asinf(std::min(1.f, std::max(-1.f, x))); }
 inline float safe_sqrt(float x) { return std::sqrt(std::max(0.f, x)); }
 inline float angle_between(H3 a, H3 b) {   // util/vecmath.h:972-977
     if (hdot(a, b) < 0) return kPi - 2 * safe_asin(hlen(a + b) / 2);
@@ -57,7 +58,7 @@ inline H3 rotate_about(float thetaRad, H3 axis, H3 v) {
     // Rotate(Degrees(theta_r), wr): the reference converts to degrees and back; sin/cos of the round-tripped angle
     float deg = (180 / kPi) * thetaRad;
     float th = (kPi / 180) * deg;
-    float s = std::sin(th), c = std::cos(th);
+    float s = vspg_sinf(th), c = vspg_cosf(th);
     float m[3][3] = {{a.x * a.x + (1 - a.x * a.x) * c, a.x * a.y * (1 - c) - a.z * s, a.x * a.z * (1 - c) + a.y * s},
                      {a.x * a.y * (1 - c) + a.z * s, a.y * a.y + (1 - a.y * a.y) * c, a.y * a.z * (1 - c) - a.x * s},
                      {a.x * a.z * (1 - c) - a.y * s, a.y * a.z * (1 - c) + a.x * s, a.z * a.z + (1 - a.z * a.z) * c}};
@@ -76,7 +77,7 @@ inline Cone cone_union(const Cone &a, const Cone &b) {   // util/vecmath.cpp:56-
     float theta_r = theta_o - theta_a;
     H3 wr = hcross(a.w, b.w);
     if (hlen2(wr) == 0) return entire_sphere();
-    Cone r; r.w = hnormalize(rotate_about(theta_r, wr, a.w)); r.cosTheta = std::cos(theta_o);
+    Cone r; r.w = hnormalize(rotate_about(theta_r, wr, a.w)); r.cosTheta = vspg_cosf(theta_o);
     return r;
 }
 inline LBounds lb_union(const LBounds &a, const LBounds &b) {   // lights.h:137-152
@@ -93,11 +94,11 @@ inline LBounds lb_union(const LBounds &a, const LBounds &b) {   // lights.h:137-
 }
 inline float evaluate_cost(const LBounds &b, const float *bmin, const float *bmax, int dim) {   // lightsamplers.h:383-396
     if (b.phi == 0) return 0;   // an empty side: the reference reads uninitialised cosines here; defined as zero cost
-    float theta_o = std::acos(b.cosTheta_o), theta_e = std::acos(b.cosTheta_e);
+    float theta_o = vspg_acosf(b.cosTheta_o), theta_e = vspg_acosf(b.cosTheta_e);
     float theta_w = std::min(theta_o + theta_e, kPi);
     float sinTheta_o = safe_sqrt(1 - b.cosTheta_o * b.cosTheta_o);
     float M_omega = 2 * kPi * (1 - b.cosTheta_o) +
-                    kPi / 2 * (2 * theta_w * sinTheta_o - std::cos(theta_o - 2 * theta_w) - 2 * theta_o * sinTheta_o + b.cosTheta_o);
+                    kPi / 2 * (2 * theta_w * sinTheta_o - vspg_cosf(theta_o - 2 * theta_w) - 2 * theta_o * sinTheta_o + b.cosTheta_o);
     float d[3] = {bmax[0] - bmin[0], bmax[1] - bmin[1], bmax[2] - bmin[2]};
     float Kr = std::max({d[0], d[1], d[2]}) / d[dim];
     float e[3] = {b.bmax[0] - b.bmin[0], b.bmax[1] - b.bmin[1], b.bmax[2] - b.bmin[2]};
@@ -216,14 +217,14 @@ inline HostLightBvh build_light_bvh(const vspg_scene_desc *scene, const float *p
     out.bitTrail.assign(nLights, 0u); out.inTree.assign(nLights, 0);
     std::vector<Builder::Item> items;
     float amin[3] = {INFINITY, INFINITY, INFINITY}, amax[3] = {-INFINITY, -INFINITY, -INFINITY};
-    const float cosHalfPi = std::cos(kPi / 2);
+    const float cosHalfPi = vspg_cosf(kPi / 2);
     for (int i = 0; i < nLights; i++) {
         const vspg_light &l = lights[i];
         LBounds lb;
         float maxL = std::max({l.L[0], l.L[1], l.L[2]});
         if (l.type == VSPG_LIGHT_POINT) {   // lights.cpp:200-205
             for (int k = 0; k < 3; k++) lb.bmin[k] = lb.bmax[k] = l.pos[k];
-            lb.w = H3(0, 0, 1); lb.phi = 4 * kPi * l.scale * maxL; lb.cosTheta_o = std::cos(kPi); lb.cosTheta_e = cosHalfPi; lb.twoSided = false;
+            lb.w = H3(0, 0, 1); lb.phi = 4 * kPi * l.scale * maxL; lb.cosTheta_o = vspg_cosf(kPi); lb.cosTheta_e = cosHalfPi; lb.twoSided = false;
         } else if (l.type == VSPG_LIGHT_DIFFUSE_AREA && l.shape_kind == 1) {   // shapes.cpp:290-314 Triangle::Bounds / NormalBounds
             const vspg_triangle &q = scene->triangles[l.shape_index];
             H3 p0(q.p0), p1(q.p1), p2(q.p2);

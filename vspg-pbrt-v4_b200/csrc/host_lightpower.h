@@ -6,6 +6,7 @@
 #include <cmath>
 #include <vector>
 #include "../../include/vspg.h"
+#include "../../include/vspg_libm.h"
 
 struct HostPowerSampler {
     std::vector<float> p, q;      // bins[i].p (the pmf), bins[i].q
@@ -19,8 +20,8 @@ inline HostPowerSampler build_power_sampler(const vspg_light *lights, int n, con
     for (int i = 0; i < 3; i++) {
         float up = 0.5f + float(i) / 3;
         if (up > 1) up -= 1;
-        float lambda = 538 - 138.888889f * std::atanh(0.85691062f - 1.82750197f * up);   // SampleVisibleWavelengths (util/sampling.h:169-171)
-        float c = std::cosh(0.0072f * (lambda - 538));
+        float lambda = 538 - 138.888889f * vspg_atanhf(0.85691062f - 1.82750197f * up);   // SampleVisibleWavelengths (util/sampling.h:169-171)
+        float c = vspg_coshf(0.0072f * (lambda - 538));
         pdf[i] = (lambda < 360 || lambda > 830) ? 0.f : 0.0039398042f / (c * c);        // VisibleWavelengthsPDF (:163-167)
     }
     std::vector<float> power(n);

@@ -11,6 +11,7 @@
 // -ffp-contract=off so a*b+c stays two roundings unless std::fma is written out.
 #pragma once
 #include <cmath>
+#include "../../include/vspg_libm.h"   // sin / cos / tan of the CTM and the projection: the path's portable libm
 
 namespace xf {
 
@@ -113,7 +114,7 @@ inline bool rotate(float deg, float ax, float ay, float az, XF *out) {   // util
     float l = length3(ax, ay, az);
     if (l == 0) return false;
     float x = ax / l, y = ay / l, z = az / l;
-    float s = std::sin(radians(deg)), c = std::cos(radians(deg));
+    float s = vspg_sinf(radians(deg)), c = vspg_cosf(radians(deg));
     M4f r = M4f::identity();
     r.m[0][0] = x * x + (1 - x * x) * c; r.m[0][1] = x * y * (1 - c) - z * s; r.m[0][2] = x * z * (1 - c) + y * s;
     r.m[1][0] = x * y * (1 - c) + z * s; r.m[1][1] = y * y + (1 - y * y) * c; r.m[1][2] = y * z * (1 - c) - x * s;
@@ -148,7 +149,7 @@ inline bool look_at(const float pos[3], const float look[3], const float up_in[3
 inline XF perspective(float fov, float n, float f) {   // util/transform.cpp:119-131
     M4f p = M4f::identity();
     p.m[2][2] = f / (f - n); p.m[2][3] = -f * n / (f - n); p.m[3][2] = 1; p.m[3][3] = 0;
-    float inv_tan = 1 / std::tan(radians(fov) / 2);
+    float inv_tan = 1 / vspg_tanf(radians(fov) / 2);
     return scale(inv_tan, inv_tan, 1) * XF(p);
 }
 

@@ -77,7 +77,7 @@ VD void rs_fetch(const DScene &sc, const Wavefront &W, int slot, RsLane<GRAY> &s
     s.volumeRatioComp = vsp;
     if (totalLength == 0.f) { s.phase = RS_DONE; s.it.init_empty(); return; }   // T_maj = (1,1,1)
     if (s.guide) {
-        float minTotalLength = -logf(1 - vsp);
+        float minTotalLength = -vspg_logf(1 - vsp);
         if (minTotalLength > totalLength) {
             s.majorantScale = minTotalLength / totalLength;
             totalLength = minTotalLength;
