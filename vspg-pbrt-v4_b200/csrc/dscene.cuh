@@ -132,8 +132,9 @@ struct PathSoA {
     // shadow-ray record emitted by the scatter kernels
     F4S<2, 0> sh_o;      // o xyz, d.x
     F4S<2, 1> sh_d;      // d.y d.z, medium(int), flags(int: bit0 delta light, bits 8.. channel)
-    F4S<2, 0> sh_c;      // contribution  beta*f_hat*L  xyz, unused
-    F4S<2, 1> sh_rl;     // r_p*p_l xyz, unused
+    F4S<2, 0> sh_c;      // ls.L xyz, beta.x
+    F4S<2, 1> sh_rl;     // r_p*p_l xyz, beta.y
+    float4 *sh_f;        // f_hat xyz, beta.z
     F4S<2, 0> sh_ru;     // r_p*scatterPDF xyz, nLight.z
     F4S<2, 1> sh_pl;     // pLight xyz, nLight.x
     F4S<2, 0> sh_ple;    // pLightErr xyz, nLight.y

@@ -97,12 +97,15 @@ __global__ void __launch_bounds__(kBlock) k_medium(const DScene sc, const Wavefr
 }
 
 // ------------------------------------------------------------------ shadow-ray record (SampleLd front half, vspg.cpp:1136-1192)
-struct ShadowRec { V3 o, d; int medium; V3 contrib, rl, ru; V3 pLight, pLightErr, nLight; bool delta; int channel; };
+// f_hat, L and beta travel apart: the reference forms ((f_hat * T_ray) * L) / w first and multiplies by beta last
+// (vspg.cpp:1247-1250, :479 / :833), and float products do not re-associate
+struct ShadowRec { V3 o, d; int medium; V3 f_hat, L, beta, rl, ru; V3 pLight, pLightErr, nLight; bool delta; int channel; };
 VD void shadow_store(const PathSoA &P, int s, const ShadowRec &r) {
     P.sh_o[s] = make_float4(r.o.x, r.o.y, r.o.z, r.d.x);
     P.sh_d[s] = make_float4(r.d.y, r.d.z, __int_as_float(r.medium), __int_as_float((r.delta ? 1 : 0) | (r.channel << 8)));
-    P.sh_c[s] = make_float4(r.contrib.x, r.contrib.y, r.contrib.z, 0);
-    P.sh_rl[s] = make_float4(r.rl.x, r.rl.y, r.rl.z, 0);
+    P.sh_c[s] = make_float4(r.L.x, r.L.y, r.L.z, r.beta.x);
+    P.sh_rl[s] = make_float4(r.rl.x, r.rl.y, r.rl.z, r.beta.y);
+    P.sh_f[s] = make_float4(r.f_hat.x, r.f_hat.y, r.f_hat.z, r.beta.z);
     P.sh_ru[s] = make_float4(r.ru.x, r.ru.y, r.ru.z, r.nLight.z);
     P.sh_pl[s] = make_float4(r.pLight.x, r.pLight.y, r.pLight.z, r.nLight.x);
     P.sh_ple[s] = make_float4(r.pLightErr.x, r.pLightErr.y, r.pLightErr.z, r.nLight.y);
@@ -151,7 +154,8 @@ VD void shadow_load(const PathSoA &P, int s, ShadowRec &r) {
     float4 a = P.sh_o[s], b = P.sh_d[s], c = P.sh_c[s], d = P.sh_rl[s], e = P.sh_ru[s], f = P.sh_pl[s], g = P.sh_ple[s];
     r.o = V3(a.x, a.y, a.z); r.d = V3(a.w, b.x, b.y); r.medium = __float_as_int(b.z);
     int fl = __float_as_int(b.w); r.delta = fl & 1; r.channel = (fl >> 8) & 3;
-    r.contrib = V3(c.x, c.y, c.z); r.rl = V3(d.x, d.y, d.z); r.ru = V3(e.x, e.y, e.z);
+    float4 ff = P.sh_f[s];
+    r.L = V3(c.x, c.y, c.z); r.beta = V3(c.w, d.w, ff.w); r.f_hat = V3(ff.x, ff.y, ff.z); r.rl = V3(d.x, d.y, d.z); r.ru = V3(e.x, e.y, e.z);
     r.pLight = V3(f.x, f.y, f.z); r.pLightErr = V3(g.x, g.y, g.z); r.nLight = V3(f.w, g.w, e.w);
 }
 // interaction.h:105-109 SpawnRayTo(pFrom, pTo): both ends offset (ray.h:104-109)
@@ -278,7 +282,7 @@ __global__ void __launch_bounds__(G > 0 ? 256 : kBlock, G > 0 ? 4 : 1) k_volscat
                         ShadowRec sr;
                         spawn_ray_to(p, V3(), V3(), ls.pLight, ls.pLightErr, ls.nLight, &sr.o, &sr.d);
                         sr.medium = ps.ray.medium;
-                        sr.contrib = ps.beta * (splat(ph) * ls.L);
+                        sr.f_hat = splat(ph); sr.L = ls.L; sr.beta = ps.beta;
                         sr.rl = ps.r_u * p_l; sr.ru = ps.r_u * scatterPDF;
                         sr.pLight = ls.pLight; sr.pLightErr = ls.pLightErr; sr.nLight = ls.nLight;
                         sr.delta = ls.delta; sr.channel = ps.fl.channel;

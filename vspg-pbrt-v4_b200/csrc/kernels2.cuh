@@ -106,7 +106,7 @@ __global__ void __launch_bounds__(G > 0 ? 256 : kBlock, G > 0 ? 3 : 1) k_shade(c
                         ShadowRec sr;
                         spawn_ray_to(isect.p, isect.pError, isect.n, ls.pLight, ls.pLightErr, ls.nLight, &sr.o, &sr.d);
                         sr.medium = isect.get_medium(sr.d);
-                        sr.contrib = ps.beta * (f_hat * ls.L);
+                        sr.f_hat = f_hat; sr.L = ls.L; sr.beta = ps.beta;
                         sr.rl = ps.r_u * p_l; sr.ru = ps.r_u * scatterPDF;
                         sr.pLight = ls.pLight; sr.pLightErr = ls.pLightErr; sr.nLight = ls.nLight;
                         sr.delta = ls.delta; sr.channel = ps.fl.channel;
@@ -216,7 +216,9 @@ __global__ void __launch_bounds__(kBlock, 8) k_shadow(const DScene sc, const Wav
         if (!blocked) {
             V3 rl3 = to_v3(r_l) * sr.rl;
             V3 ru3 = to_v3(r_u) * sr.ru;
-            V3 Ld = sr.delta ? sr.contrib * to_v3(T_ray) / avg3(rl3) : sr.contrib * to_v3(T_ray) / avg3(rl3 + ru3);
+            // f_hat * T_ray * ls->L / (r_l + r_u).Average()  (vspg.cpp:1247-1250), then L += beta * Ld (:479, :833)
+            V3 Ld = sr.delta ? sr.f_hat * to_v3(T_ray) * sr.L / avg3(rl3) : sr.f_hat * to_v3(T_ray) * sr.L / avg3(rl3 + ru3);
+            Ld = sr.beta * Ld;
             float4 e = W.P.rl_L[slot];
             e.y += Ld.x; e.z += Ld.y; e.w += Ld.z;
             W.P.rl_L[slot] = e;

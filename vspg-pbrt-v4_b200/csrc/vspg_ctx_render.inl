@@ -20,7 +20,7 @@ static int ensure_wavefront(vspg_ctx *ctx, unsigned long long total) {
         return e;
     };
     PathSoA &P = ctx->W.P;
-    float4 **f4[] = {&P.ev, &P.prev_o};
+    float4 **f4[] = {&P.ev, &P.prev_o, &P.sh_f};
     for (auto pp : f4) CK(alloc((void **)pp, n * sizeof(float4)));
     // 32-byte records shared by two streams (dscene.cuh F4S)
     float4 **pairs[][2] = {{&P.o_dx.base, &P.d_med.base}, {&P.beta_ru.base, &P.ru_rl.base}, {&P.rl_L.base, &P.misc.base}, {&P.misc2.base, &P.prev_ns.base},
