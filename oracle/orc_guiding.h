@@ -9,6 +9,7 @@
 // k = 0..cnt-1, then reduce_add = (l0+l1)+(l2+l3)  (embree vfloat4 vreduce_add: shuffle<1,0,3,2>+v,
 // then shuffle<2,3,0,1>+h).
 #pragma once
+#include "../include/vspg_rsqrtss.h"
 #include "../include/vspg.h"
 #include "orc_math.h"
 #if defined(__SSE__)
@@ -70,17 +71,11 @@ inline float pgl_log(float v) {
     return r;
 }
 
-inline float embree_rsqrt(float x) {
-#if defined(__SSE__)
-    const __m128 a = _mm_set_ss(x);
-    __m128 r = _mm_rsqrt_ss(a);
-    const __m128 c = _mm_add_ss(_mm_mul_ss(_mm_set_ss(1.5f), r),
-                                _mm_mul_ss(_mm_mul_ss(_mm_mul_ss(a, _mm_set_ss(-0.5f)), r), _mm_mul_ss(r, r)));
-    return _mm_cvtss_f32(c);
-#else
-    return 1.f / std::sqrt(x);
-#endif
-}
+// embree::rsqrt (emath.h:129-149): RSQRTSS estimate + one Newton step.  The estimate is taken from the table of
+// include/vspg_rsqrtss.h (what Intel processors return, verified exhaustively), not from this machine's instruction,
+// so the oracle gives the same bits on every host.
+inline float embree_rsqrt(float x) { return vspg_embree_rsqrt(x); }
+
 inline float reduce4(const float *l) { return (l[0] + l[1]) + (l[2] + l[3]); }
 
 // ---------------------------------------------------------------- spatial lookup
@@ -279,7 +274,7 @@ struct VMM {
             dir = V3(sinTheta * cp, sinTheta * sp, cosTheta);
         }
         // embree::frame(N) linearspace3.h:117-124; normalize(a) = a*rsqrt(dot(a,a)) with the scalar
-        // rsqrt of math/emath.h:129-149 (rsqrtss + one Newton step), reproduced with the same intrinsics.
+        // rsqrt of math/emath.h:129-149 (rsqrtss + one Newton step), with the Intel RSQRTSS table of include/vspg_rsqrtss.h.
         V3 dx0(0, mu.z, -mu.y), dx1(-mu.z, 0, mu.x);
         auto dot3 = [](V3 a, V3 b) { return a.x * b.x + (a.y * b.y + a.z * b.z); };
         V3 dxs = dot3(dx0, dx0) > dot3(dx1, dx1) ? dx0 : dx1;

@@ -28,7 +28,10 @@ def fp(a):
 
 
 def bits(a):
-    return np.ascontiguousarray(a, dtype=np.float32).view(np.uint32)
+    """Bit patterns, with every NaN mapped to one pattern (the reference's light-BVH PMF is 0/0 = NaN for a light whose
+    importance is zero at every node on its path; payload bits of a NaN carry no meaning)."""
+    a = np.ascontiguousarray(a, dtype=np.float32)
+    return np.where(np.isnan(a), np.uint32(0x7fc00000), a.view(np.uint32))
 
 
 def load(name):

@@ -9,12 +9,14 @@ import orc
 GOLD = os.path.join(ROOT, "tests", "golden", "pbrt")
 ctx = api.Context(0)
 PF = C.POINTER(C.c_float)
-VARIANTS = [("full", {}), ("nonee", dict(use_nee=0)), ("nonee_d1", dict(use_nee=0, max_depth=1)), ("nee_d1", dict(max_depth=1)), ("nee_d2", dict(max_depth=2))]
+VARIANTS = [("full", {}), ("nonee", dict(use_nee=0)), ("nee_d1", dict(max_depth=1)), ("nee_d2", dict(max_depth=2)),
+            ("noguide", dict(surface_guiding=0, volume_guiding=0)), ("novsp", dict(vsp_guiding=0)), ("uniform", dict(light_sampler=0)), ("power", dict(light_sampler=1)),
+            ("noguide_novsp", dict(surface_guiding=0, volume_guiding=0, vsp_guiding=0))]
 for name in sys.argv[1:]:
     hs = api.HostScene(path=os.path.join(GOLD, name + ".pbrt")); g = np.load(os.path.join(GOLD, name + ".npz"))
     ctx.set_scene(hs)
     if hs.guiding is not None: ctx.set_guiding(hs.guiding)
-    smp, w = g["samples"][:600], g["rays"][:600, 7]
+    smp, w = g["samples"], g["rays"][:, 7]
     gp = C.byref(hs.guiding.desc) if hs.guiding is not None else None
     for vn, over in VARIANTS:
         ip = api.integrator_defaults()

@@ -261,13 +261,14 @@ template <int G> __device__ __noinline__ V3 mix_sample(Lobe L, int n, float s0, 
         float sp, cp; vspg_sincosf(phi, &sp, &cp);
         dir = V3(sinTheta * cp, sinTheta * sp, cosTheta);
     }
-    // embree::frame(N), linearspace3.h:117-124 (the CPU's rsqrtss+Newton normalise is replaced by an exact one)
+    // embree::frame(N), linearspace3.h:117-124; normalize(a) = a * rsqrt(dot(a, a)) with embree::rsqrt = RSQRTSS estimate
+    // (Intel's lookup, include/vspg_rsqrtss.h) + one Newton step
     V3 dx0(0, mu.z, -mu.y), dx1(-mu.z, 0, mu.x);
     float l0 = dot_e(dx0.x, dx0.y, dx0.z, dx0.x, dx0.y, dx0.z), l1 = dot_e(dx1.x, dx1.y, dx1.z, dx1.x, dx1.y, dx1.z);
     V3 dxs = l0 > l1 ? dx0 : dx1;
-    V3 dx = dxs * (1.f / sqrtf(fmaxf(l0, l1)));
+    V3 dx = dxs * vspg_embree_rsqrt(l0 > l1 ? l0 : l1);
     V3 cr(mu.y * dx.z - mu.z * dx.y, mu.z * dx.x - mu.x * dx.z, mu.x * dx.y - mu.y * dx.x);
-    V3 dy = cr * (1.f / sqrtf(dot_e(cr.x, cr.y, cr.z, cr.x, cr.y, cr.z)));
+    V3 dy = cr * vspg_embree_rsqrt(dot_e(cr.x, cr.y, cr.z, cr.x, cr.y, cr.z));
     return V3(dir.x * dx.x + (dir.y * dy.x + dir.z * mu.x), dir.x * dx.y + (dir.y * dy.y + dir.z * mu.y),
               dir.x * dx.z + (dir.y * dy.z + dir.z * mu.z));
 }

@@ -5,6 +5,7 @@
 #pragma once
 #include <cuda_runtime.h>
 #include <stdint.h>
+#include "../../include/vspg_rsqrtss.h"   // embree::rsqrt as OpenPGL evaluates it on Intel hardware
 #include "../../include/vspg_libm.h"   // log / sin / cos / asin / atan2 / pow: the path's portable libm (bit-identical on host and device)
 
 #define VD __device__ __forceinline__
