@@ -118,21 +118,22 @@ def test_sample_distance_parity(ctx, orc, name, over):
     got = ctx.debug_sample_distance(inp)
     want = orc.sample_distance(cfg.scene, cfg.guiding, cfg.ip, inp)
     f = lambda a, k: H.struct_array_to_np(a, k)
-    # discrete decisions: identical except where a 1-ulp libm difference flips a comparison (must be very rare)
-    same = (f(got, "scattered") == f(want, "scattered")) & (f(got, "terminated") == f(want, "terminated")) & \
-           (f(got, "depth") == f(want, "depth")) & (f(got, "rng_state") == f(want, "rng_state")) & \
-           (f(got, "density_queries") == f(want, "density_queries")) & (f(got, "dda_steps") == f(want, "dda_steps"))
-    assert same.mean() >= 0.995, f"decision mismatch fraction {1 - same.mean():.4f}"
+    # every decision and every number is the oracle's, bit for bit (NaNs compare equal to NaNs)
+    for k in ("scattered", "terminated", "depth", "rng_state", "density_queries", "dda_steps"):
+        assert np.array_equal(f(got, k), f(want, k)), k
     assert f(want, "scattered").sum() > n * 0.05 and (f(want, "scattered") == 0).sum() > n * 0.02
     for k in ("p", "sigma_a", "sigma_s", "beta", "r_u", "r_l"):
-        a, b = f(got, k)[same], f(want, k)[same]
-        fin = np.isfinite(b).all(axis=1)
-        assert np.array_equal(np.isfinite(a).all(axis=1), fin)
-        if k == "p":   # a position: error relative to the vector's magnitude (components cancel against ray.o)
-            err = np.abs(a[fin] - b[fin]) / np.maximum(np.abs(b[fin]).max(axis=1, keepdims=True), 1e-12)
-        else:          # throughputs below 1e-9 carry nothing (products of hundreds of per-collision weights)
-            err = H.rel_err(a[fin], b[fin], floor=1e-9)
-        assert err.max() <= REL_TOL, f"{k}: max rel err {err.max():.3e}"
+        a, b = f(got, k).astype(np.float32), f(want, k).astype(np.float32)
+        same = (a.view(np.uint32) == b.view(np.uint32)) | (np.isnan(a) & np.isnan(b))
+        assert same.all(), f"{k}: {(~same.all(axis=1)).sum()} of {n} differ"
+
+
+def _assert_bits_equal(got, want, keys, mask):
+    for k in keys:
+        a = np.asarray(H.struct_array_to_np(got, k), dtype=np.float32)[mask]
+        b = np.asarray(H.struct_array_to_np(want, k), dtype=np.float32)[mask]
+        same = (a.view(np.uint32) == b.view(np.uint32)) | (np.isnan(a) & np.isnan(b))
+        assert same.all(), f"{k}: {int((~same).sum())} values differ, first {a[~same][:1]} vs {b[~same][:1]}"
 
 
 @pytest.mark.parametrize("surface,ris", [(1, 1), (1, 0), (0, 0), (0, 1)])
@@ -171,25 +172,13 @@ def test_guided_sample_parity(ctx, orc, surface, ris):
     g = lambda a, k: H.struct_array_to_np(a, k)
     assert np.array_equal(g(got, "ok"), g(want, "ok"))
     assert np.array_equal(g(got, "region"), g(want, "region"))           # cache-node selection: bit-exact
-    same = (g(got, "valid") == g(want, "valid")) & (g(got, "rng_state") == g(want, "rng_state"))
-    assert same.mean() >= 0.999
-    v = same & (g(want, "valid") == 1)
+    assert np.array_equal(g(got, "valid"), g(want, "valid")) and np.array_equal(g(got, "rng_state"), g(want, "rng_state"))
+    v = g(want, "valid") == 1
     assert v.sum() > n * 0.5
-    # direction: compare by angle (components near zero have no relative meaning)
-    wi_g, wi_o = g(got, "wi")[v], g(want, "wi")[v]
-    cosang = np.clip((wi_g * wi_o).sum(1) / np.linalg.norm(wi_g, axis=1) / np.linalg.norm(wi_o, axis=1), -1, 1)
-    close = np.arccos(cosang) < 1e-3
-    assert close.mean() >= 0.998, f"direction mismatch fraction {1 - close.mean():.4f}"  # lobe picks flip only at CDF ties
-    idx = np.where(v)[0][close]
-    for k in ("pdf", "scatter_pdf", "mis_pdf", "f"):
-        a, b = g(got, k)[idx], g(want, k)[idx]
-        err = H.rel_err(a, b, floor=1e-7)
-        # the sampled direction itself carries ~1e-7 relative error; a kappa<=200 lobe amplifies it by <= kappa
-        assert np.quantile(err, 0.99) <= 2e-4 and err.max() <= 5e-3, f"{k}: q99 {np.quantile(err, 0.99):.2e} max {err.max():.2e}"
-    for k in ("pdf_wq", "vsp_wq"):                  # evaluated at an input direction: pure arithmetic parity
-        a, b = g(got, k), g(want, k)
-        err = H.rel_err(a, b, floor=1e-12)
-        assert err.max() <= REL_TOL, f"{k}: max rel err {err.max():.3e}"
+    # sampled direction, pdfs and f: the oracle's numbers bit for bit (sincos through the portable libm, embree::rsqrt
+    # through the RSQRTSS table, sums in the 4-wide order of the reference)
+    _assert_bits_equal(got, want, ("wi", "pdf", "scatter_pdf", "mis_pdf", "f"), v)
+    _assert_bits_equal(got, want, ("pdf_wq", "vsp_wq"), np.ones(n, bool))
 
 
 def _real_field_guiding():
@@ -244,9 +233,9 @@ def test_guided_sample_parity_on_a_reference_trained_field(ctx, orc, surface):
     q = lambda a, k: H.struct_array_to_np(a, k)
     assert np.array_equal(q(got, "ok"), q(want, "ok")) and q(want, "ok").sum() > n * 0.8
     assert np.array_equal(q(got, "region"), q(want, "region"))
-    for k in ("pdf_wq", "vsp_wq"):
-        err = H.rel_err(q(got, k), q(want, k), floor=1e-12)
-        assert err.max() <= REL_TOL, f"{k}: max rel err {err.max():.3e}"
+    assert np.array_equal(q(got, "valid"), q(want, "valid")) and np.array_equal(q(got, "rng_state"), q(want, "rng_state"))
+    _assert_bits_equal(got, want, ("wi", "pdf", "scatter_pdf", "mis_pdf", "f"), q(want, "valid") == 1)
+    _assert_bits_equal(got, want, ("pdf_wq", "vsp_wq"), np.ones(n, bool))
 
 
 RENDER_CASES = [("C1", {}), ("C1T", {}), ("C1S", {}), ("C1E", {}), ("C1E", dict(light_sampler=A.LIGHTSAMPLER_POWER)), ("C1G", {}), ("C1", dict(vsp_guiding=1)), ("C2", {}), ("C3", {}), ("C4", {}), ("C5", {}),
@@ -272,36 +261,31 @@ def _render_both(ctx, orc, name, over, seed=7):
     return cfg, film_g, cnt_g, film_o, cnt_o
 
 
+def _assert_films_identical(cfg, film_g, cnt_g, film_o, cnt_o):
+    """Every path of the CUDA render is the oracle's path, bit for bit (the oracle is itself bit-equal to the reference,
+    tests/test_ref_pbrt.py): each pixel's fp64 sum holds the same float terms.  The GPU adds them with atomics in
+    arbitrary order, so the sums are compared to 1e-12 relative; the counters -- density queries, DDA steps, cache
+    lookups, shadow rays -- are integers and must be equal."""
+    a, b = film_g[..., :3], film_o[..., :3]
+    same = np.abs(a - b) <= 1e-12 * np.maximum(np.abs(b), 1e-30)
+    assert same.all(), f"{(~same.all(axis=2)).sum()} of {same.shape[0] * same.shape[1]} pixels differ"
+    for k in ("density_queries", "dda_steps", "cache_lookups", "shadow_rays"):
+        assert cnt_g[k] == cnt_o[k], (k, cnt_g[k], cnt_o[k])
+
+
 @pytest.mark.parametrize("name", ["C1", "C1T", "C1S", "C1E", "C1G", "C2", "C3", "C4", "C5"])
 def test_render_without_nee_is_path_exact(ctx, orc, name):
-    """usenee=false: every random decision of a path comes from its own (pixel, sampleIndex) PCG32 stream, which is
-    identical on both sides, so whole films agree path by path (camera ray, BVH, DDA, SampleDistance, cache lookup,
-    guided phase/BSDF sampling, RR, emission, film).  A last-ulp libm difference may flip a rare comparison."""
-    cfg, a, cg, b, co = _render_both(ctx, orc, name, dict(use_nee=0))
-    err = H.rel_err(a[..., :3], b[..., :3], floor=1e-3)
-    frac_close = (err.max(axis=2) < 1e-3).mean()
-    assert frac_close >= 0.995, f"only {frac_close:.4f} of pixels agree"
-    for k in ("density_queries", "dda_steps", "cache_lookups"):
-        assert abs(cg[k] - co[k]) <= 0.002 * max(1, co[k]) + 2, (k, cg[k], co[k])
+    """usenee=false: camera ray, BVH, DDA, SampleDistance, cache lookup, guided phase/BSDF sampling, RR, emission, film."""
+    _assert_films_identical(*_render_both(ctx, orc, name, dict(use_nee=0)))
 
 
 @pytest.mark.parametrize("name,over", RENDER_CASES)
 def test_render_matches_oracle_on_fixed_streams(ctx, orc, name, over):
-    """With NEE the shadow-ray tracker is seeded by Hash(ray.o), Hash(ray.d) (vspg.cpp:1193): a 1-ulp libm difference
-    (CUDA logf vs glibc logf) in a scatter position re-seeds that tracker, so such paths agree only in distribution.
-    Checked: identical sample counts, counters within 1 %, most pixels still identical, and a paired test that the
-    per-pixel difference image is zero-mean (common random numbers make this far tighter than an unpaired test)."""
-    cfg, film_g, cnt_g, film_o, cnt_o = _render_both(ctx, orc, name, over)
-    a, b = film_g[..., :3] / cfg.spp, film_o[..., :3] / cfg.spp
-    err = H.rel_err(a, b, floor=1e-3)
-    frac_close = (err.max(axis=2) < 1e-3).mean()
-    assert frac_close >= 0.5, f"only {frac_close:.4f} of pixels agree"
-    d = (a - b).mean(axis=2).ravel()
-    sem = d.std(ddof=1) / np.sqrt(d.size)
-    assert abs(d.mean()) <= 4.5 * sem + 1e-7, f"paired difference {d.mean():.3e} vs standard error {sem:.3e}"
-    assert abs(a.mean() - b.mean()) <= 0.10 * b.mean() + 1e-6   # gross-error guard; the paired test above is the statistical one
-    for k in ("density_queries", "dda_steps", "cache_lookups", "shadow_rays"):
-        assert abs(cnt_g[k] - cnt_o[k]) <= 0.01 * max(1, cnt_o[k]), (k, cnt_g[k], cnt_o[k])
+    """With NEE: the shadow-ray trackers are seeded by Hash(ray.o), Hash(ray.d) (vspg.cpp:1193), so one last-bit
+    difference anywhere upstream -- a sampled position, a spawned origin, a light sample -- would send that path elsewhere.
+    There is none: the kernels compute with the path's portable libm (include/vspg_libm.h), Normal3 dot products,
+    Point3fi intervals and the reference's product orders, and whole films are identical."""
+    _assert_films_identical(*_render_both(ctx, orc, name, over))
 
 
 def test_render_window_and_sample_stride_compose(ctx):
@@ -342,16 +326,16 @@ def test_errors_are_reported_not_fatal(ctx):
 @pytest.mark.parametrize("name,over", [("C2", {}), ("C3", {}), ("C5", dict(light_sampler=A.LIGHTSAMPLER_BVH))])
 def test_relmse_at_equal_spp_agrees_with_the_cpu_oracle(ctx, orc, name, over):
     """SURVEY 8(d) image-level check: relMSE of the CUDA render and of the CPU oracle render against a common
-    high-spp reference (256x the spp, rendered on the GPU with a disjoint seed) agree within 10 % + 3 sigma over 8 seeds."""
+    high-spp reference (256x the spp, rendered by the CPU ORACLE with a disjoint seed, so a bias of the CUDA path could
+    not hide in the reference) agree within 10 % + 3 sigma over 8 seeds."""
     from pyvspg import stats
     cfg = H.small(name, res=40, spp=4)
     for k, v in over.items():
         setattr(cfg.ip, k, v)
     _setup(ctx, cfg)
     ctx.set_capacity(0)
-    ctx.film_clear()
-    ctx.render(0, 1024, seed=999)
-    ref = stats.resolve(ctx.film_download())
+    film_ref, _ = orc.render(cfg.scene, cfg.guiding, cfg.ip, 0, 1024, seed=999, nthreads=16)
+    ref = stats.resolve(film_ref)
     rg, rc = [], []
     for seed in range(8):
         ctx.film_clear()

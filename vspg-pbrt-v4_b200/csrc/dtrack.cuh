@@ -121,6 +121,15 @@ VD V3 track_optical_depth(const DMedium &med, const Ray &ray, float tMax, float 
                           float vsp, float vspMISRatio, bool NDS, V3 &beta_factor, V3 &r_u_factor, TrackCounters &tc, F cb) {
     auto plain = [&](V3 p, const MediumProps &mp, V3 sm, V3 tm) { return cb(p, mp, sm, tm, false); };
     if (!guideScatterDecision || vspMISRatio == 0.f) return track_T_maj(med, ray, tMax, u, rng, ch, tc, plain);
+    // The two later fall-backs (:305-307 infinite segment, :330-332 NDS with vsp below the segment's scatter probability)
+    // call SampleT_maj with the ALREADY normalised ray and scaled tMax, and SampleT_maj normalises again (:55-56):
+    // |normalize(d)| is not exactly 1, so tMax and d move by an ulp -- and so do the collision points.
+    auto plain_renormalised = [&]() {
+        Ray r2 = ray;
+        float tMax2 = tMax * length(r2.d);
+        r2.d = normalize(r2.d);
+        return track_T_maj(med, r2, tMax2, u, rng, ch, tc, plain);
+    };
     MajorantIterator iter = sample_ray(med, ray, tMax);
     float t_v = 0.f;
     Segment seg;
@@ -133,13 +142,13 @@ VD V3 track_optical_depth(const DMedium &med, const Ray &ray, float tMax, float 
             t_v += seg.sigma_maj[ch] * (seg.tMax - seg.tMin);
         }
         tc.dda += pre.steps;
-        if (infinite) return track_T_maj(med, ray, tMax, u, rng, ch, tc, plain);
+        if (infinite) return plain_renormalised();
     }
     if (t_v == 0.f) return splat(1.f);
     float OneMinusENegTv = 1.f - fast_exp(-t_v);
     float t_n = -1.f, t_n_current = -1.f;
     if (NDS) {
-        if (vsp < 1 - fast_exp(-t_v)) return track_T_maj(med, ray, tMax, u, rng, ch, tc, plain);
+        if (vsp < 1 - fast_exp(-t_v)) return plain_renormalised();
         t_n = (float)(-vspg_log(1.0 - (double)(OneMinusENegTv / vsp)));  // the reference's 1.0 literal promotes to double
         t_n_current = t_n;
     }
