@@ -27,6 +27,8 @@ def small(name, **kw):
     common = dict(grid_n=kw.get("grid_n", 32), vol_leaves=kw.get("vol_leaves", 256), surf_leaves=kw.get("surf_leaves", 128))
     if name == "C2":
         return configs.config2(res=kw.get("res", 48), spp=kw.get("spp", 4), **common)
+    if name == "C2K":   # C2 with reflectance-0 patches among the lit surfaces: vertices that take no NEE share warps with ones that do
+        return configs.config2(res=kw.get("res", 48), spp=kw.get("spp", 4), black_patches=True, **common)
     if name == "C3":
         return configs.config3(res=kw.get("res", 48), spp=kw.get("spp", 4), **common)
     if name == "C4":

@@ -240,7 +240,8 @@ def test_guided_sample_parity_on_a_reference_trained_field(ctx, orc, surface):
 
 RENDER_CASES = [("C1", {}), ("C1T", {}), ("C1S", {}), ("C1E", {}), ("C1E", dict(light_sampler=A.LIGHTSAMPLER_POWER)), ("C1G", {}), ("C1", dict(vsp_guiding=1)), ("C2", {}), ("C3", {}), ("C4", {}), ("C5", {}),
                 ("C5", dict(light_sampler=A.LIGHTSAMPLER_BVH)), ("C2", dict(light_sampler=A.LIGHTSAMPLER_BVH)), ("C1", dict(light_sampler=A.LIGHTSAMPLER_BVH)),
-                ("C2", dict(max_depth=1)), ("C3", dict(volume_guiding_ris=1, surface_guiding_ris=0))]
+                ("C2", dict(max_depth=1)), ("C3", dict(volume_guiding_ris=1, surface_guiding_ris=0)),
+                ("C2K", {}), ("C2K", dict(surface_guiding_ris=0))]
 
 
 def _render_both(ctx, orc, name, over, seed=7):
@@ -321,6 +322,16 @@ def test_errors_are_reported_not_fatal(ctx):
         ctx.set_integrator(ip)
     with pytest.raises(KeyError):
         api.integrator_defaults(no_such_parameter=1)
+    # a set_scene with another film size after set_guiding: the per-pixel buffers no longer fit -> refused, not read past the end
+    small, big = H.small("C2", res=24), H.small("C2", res=40)
+    ctx.set_scene(small.scene); ctx.set_guiding(small.guiding); ctx.set_integrator(small.ip)
+    ctx.render(0, 1)
+    ctx.set_scene(big.scene)
+    with pytest.raises(api.VspgError) as e:
+        ctx.render(0, 1)
+    assert "ISG buffer" in str(e.value)
+    ctx.set_guiding(big.guiding)
+    ctx.render(0, 1)
 
 
 @pytest.mark.parametrize("name,over", [("C2", {}), ("C3", {}), ("C5", dict(light_sampler=A.LIGHTSAMPLER_BVH))])

@@ -270,8 +270,11 @@ __global__ void __launch_bounds__(G > 0 ? 256 : kBlock, G > 0 ? 4 : 1) k_volscat
             NeePre ls;
             if (G > 0) {   // drawn by k_lookup from these three sampler dimensions
                 ps.rng.uniform(); ps.rng.uniform(); ps.rng.uniform();
-                ls = nee_load(W.P, slot);
-                __syncwarp();   // every lane of the group has read the parked record before the leader overwrites it
+                // A lane group past the end of the queue re-runs the CTA's first item for the barriers only: it must not read
+                // that slot's parked record, which the owning group's leader (possibly in another warp) overwrites below.
+                if (live) ls = nee_load(W.P, slot); else { ls.valid = false; ls.delta = false; ls.p_l = 0; }
+                __syncwarp(grp_mask<G>());   // every lane of THIS group has read the parked record before its leader overwrites it
+                                             // (the branch is per vertex: other groups of the warp may not be here)
             } else ls = nee_presample(sc, ps.rng, p, V3()), ps.rng.uniform(), ps.rng.uniform(), ps.rng.uniform();
             {
                 if (ls.valid) {

@@ -94,8 +94,8 @@ __global__ void __launch_bounds__(G > 0 ? 256 : kBlock, G > 0 ? 3 : 1) k_shade(c
             NeePre ls;
             if (G > 0) {   // drawn by k_lookup from these three sampler dimensions
                 ps.rng.uniform(); ps.rng.uniform(); ps.rng.uniform();
-                ls = nee_load(W.P, slot);
-                __syncwarp();
+                if (live) ls = nee_load(W.P, slot); else { ls.valid = false; ls.delta = false; ls.p_l = 0; }   // see k_volscatter
+                __syncwarp(grp_mask<G>());   // per-vertex branch: only this group's lanes are known to be here
             } else ls = nee_presample(sc, ps.rng, ctxP, isect.ns), ps.rng.uniform(), ps.rng.uniform(), ps.rng.uniform();
             {
                 if (ls.valid) {

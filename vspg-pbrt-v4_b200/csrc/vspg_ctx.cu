@@ -190,6 +190,9 @@ int vspg_set_scene(vspg_ctx *ctx, const vspg_scene_desc *s) {
     if (s->camera.filter_type == 1 && (int(32 * s->camera.filter_radius[0]) < 1 || int(32 * s->camera.filter_radius[1]) < 1 || !(s->camera.filter_sigma > 0)))
         return fail(ctx, VSPG_ERR_INVALID, "set_scene: gaussian filter needs radius >= 1/32 and sigma > 0");
     if (s->camera.width <= 0 || s->camera.height <= 0) return fail(ctx, VSPG_ERR_INVALID, "set_scene: bad film resolution");
+    if (s->camera.medium >= s->n_media) return fail(ctx, VSPG_ERR_INVALID, "set_scene: camera medium %d does not exist", s->camera.medium);
+    for (int i = 0; i < s->n_lights; i++)
+        if (s->lights[i].medium >= s->n_media) return fail(ctx, VSPG_ERR_INVALID, "set_scene: light %d: medium %d does not exist", i, s->lights[i].medium);
     dev_release(ctx, ctx->scene_allocs);
     ctx->have_scene = false;
     ctx->cells_ptr = nullptr; ctx->cells_bytes = 0;
@@ -370,7 +373,7 @@ int vspg_set_scene(vspg_ctx *ctx, const vspg_scene_desc *s) {
         CK(cudaMalloc((void **)&ctx->film, (size_t)ctx->film_w * ctx->film_h * 4 * sizeof(double)));
     }
     CK(cudaMemset(ctx->film, 0, (size_t)ctx->film_w * ctx->film_h * 4 * sizeof(double)));
-    if (!ctx->counters) { CK(cudaMalloc((void **)&ctx->counters, 8 * sizeof(unsigned long long))); CK(cudaMemset(ctx->counters, 0, 64)); }
+    if (!ctx->counters) { CK(cudaMalloc((void **)&ctx->counters, CNT_COUNT * sizeof(unsigned long long))); CK(cudaMemset(ctx->counters, 0, CNT_COUNT * sizeof(unsigned long long))); }
     CK(cudaDeviceSynchronize());
     ctx->have_scene = true;
     return VSPG_OK;

@@ -13,7 +13,7 @@ static int upload_field(vspg_ctx *ctx, const vspg_field *f, DField *d) {
     for (int i = 0; i < f->n_regions; i++)
         if (f->regions[i].num_components < 0 || f->regions[i].num_components > VSPG_MAX_LOBES)
             return fail(ctx, VSPG_ERR_INVALID, "set_guiding: region %d has %d lobes", i, f->regions[i].num_components);
-    d->present = 1; d->usable = f->usable; d->n_nodes = f->n_nodes; d->n_regions = f->n_regions; d->stochastic_nn = f->stochastic_nn;
+    d->usable = f->usable; d->n_nodes = f->n_nodes; d->n_regions = f->n_regions; d->stochastic_nn = f->stochastic_nn;
     for (int a = 0; a < 3; a++) { d->bmin[a] = f->bounds_min[a]; d->bmax[a] = f->bounds_max[a]; }
     CK(upload(ctx, ctx->guide_allocs, f->nodes, (size_t)f->n_nodes, &d->nodes));
     CK(upload(ctx, ctx->guide_allocs, f->regions, (size_t)f->n_regions, &d->regions));
@@ -24,6 +24,7 @@ static int upload_field(vspg_ctx *ctx, const vspg_field *f, DField *d) {
                     return fail(ctx, VSPG_ERR_INVALID, "set_guiding: neighbour table of region %d is out of range", i);
         CK(upload(ctx, ctx->guide_allocs, f->neighbours, (size_t)f->n_regions, &d->neigh));
     }
+    d->present = 1;   // only once every table is on the device: a failed upload leaves the field absent, not half-present
     return VSPG_OK;
 }
 

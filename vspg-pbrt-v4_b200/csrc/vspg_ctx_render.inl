@@ -10,7 +10,7 @@ static int ensure_wavefront(vspg_ctx *ctx, unsigned long long total) {
     int want = ctx->requested_capacity > 0 ? ctx->requested_capacity : (1 << 24);
     if ((unsigned long long)want > total) want = (int)total;
     want = std::max(want, 1024);
-    if (ctx->capacity >= want && ctx->capacity <= 4 * want) return VSPG_OK;
+    if (ctx->capacity >= want && (long long)ctx->capacity <= 4ll * want) return VSPG_OK;
     free_all(ctx->wf_allocs);
     ctx->capacity = 0;
     const size_t n = (size_t)want;
@@ -51,7 +51,13 @@ int vspg_render(vspg_ctx *ctx, int spp_begin, int spp_end, int spp_stride, int x
     if (x0 < 0 || y0 < 0 || x1 > ctx->film_w || y1 > ctx->film_h || x0 >= x1 || y0 >= y1) return fail(ctx, VSPG_ERR_INVALID, "render: bad pixel window");
     if (spp_begin < 0 || spp_end < spp_begin) return fail(ctx, VSPG_ERR_INVALID, "render: bad sample range");
     const DScene &scRef = ctx->sc;
-    if ((scRef.ip.volume_guiding_ris == 0 || true) && scRef.ip.vsp_sampling_nds && scRef.ip.collision_probability_bias && !scRef.tr_rgb) {
+    // per-pixel inputs are indexed by the film's pixels: a set_scene with another film size after set_guiding must not
+    // leave the kernels reading past them (set_guiding checks the same when it runs after set_scene)
+    if (scRef.isg_vsp && (scRef.isg_w != scRef.cam.width || scRef.isg_h != scRef.cam.height))
+        return fail(ctx, VSPG_ERR_STATE, "render: the ISG buffer is %dx%d but the film is %dx%d (call set_guiding again after set_scene)", scRef.isg_w, scRef.isg_h, scRef.cam.width, scRef.cam.height);
+    if (scRef.tr_rgb && (scRef.tr_w != scRef.cam.width || scRef.tr_h != scRef.cam.height))
+        return fail(ctx, VSPG_ERR_STATE, "render: the Tr buffer is %dx%d but the film is %dx%d (call set_guiding again after set_scene)", scRef.tr_w, scRef.tr_h, scRef.cam.width, scRef.cam.height);
+    if (scRef.ip.vsp_sampling_nds && scRef.ip.collision_probability_bias && !scRef.tr_rgb) {
         // the reference falls back to *training* a Tr buffer here; this build has no training pass
         return fail(ctx, VSPG_ERR_STATE, "render: collisionProbabilityBias needs a loaded transmittance buffer (loadTrBuffer)");
     }
@@ -260,7 +266,7 @@ int vspg_counters_get(vspg_ctx *ctx, vspg_counters *out) {
 int vspg_counters_reset(vspg_ctx *ctx) {
     if (!ctx) return VSPG_ERR_INVALID;
     CK(cudaSetDevice(ctx->device));
-    if (ctx->counters) CK(cudaMemset(ctx->counters, 0, 64));
+    if (ctx->counters) CK(cudaMemset(ctx->counters, 0, CNT_COUNT * sizeof(unsigned long long)));
     ctx->launches = 0; ctx->iterations = 0; ctx->ms_total = 0;
     for (int k = 0; k < VSPG_K_COUNT; k++) { ctx->ms_kernel[k] = 0; ctx->launches_kernel[k] = 0; }
     return VSPG_OK;

@@ -118,11 +118,15 @@ def _guiding_for(sc, rng, width, height, vol_leaves, surf_leaves, with_tr=False)
     return g
 
 
-def _fbm_scene(res, grid_n, density=None):
+def _fbm_scene(res, grid_n, density=None, black_patches=False):
     cam, eye = perspective_camera([0.5, 0.6, -2.2], [0.5, 0.45, 0.5], [0, 1, 0], 40.0, res, res)
     sc = Scene(cam, eye)
     white = sc.add_material([.6, .6, .6])
     sc.add_quad([-2, -0.05, -2], [5, 0, 0], [0, 0, 5], material=white)       # ground
+    if black_patches:   # reflectance 0: a diffuse BSDF without the DiffuseReflection flag (bxdfs.h:82-84) -- no NEE, no scattering
+        black = sc.add_material([0.0, 0.0, 0.0])
+        sc.add_quad([-0.6, -0.04, -0.4], [0.9, 0, 0], [0, 0, 0.9], material=black)
+        sc.add_quad([1.05, -0.04, 0.1], [0.5, 0, 0], [0, 0.6, 0.3], material=black)
     if density is None:
         density = syn.fbm_grid(grid_n, seed=1337)
     med = sc.add_grid_medium(density, (0, 0, 0), (1, 1, 1), [0.1, 0.1, 0.1], [6.0, 6.0, 6.0], 8.0, 0.6)
@@ -132,9 +136,9 @@ def _fbm_scene(res, grid_n, density=None):
     return sc
 
 
-def config2(res=512, spp=64, grid_n=128, vol_leaves=4096, surf_leaves=1024, density=None):
+def config2(res=512, spp=64, grid_n=128, vol_leaves=4096, surf_leaves=1024, density=None, black_patches=False):
     """C2: fBm 128^3 grid medium, VSPG resampling + variance criterion, loaded cache + ISG buffer, 512x512, 64 spp."""
-    sc = _fbm_scene(res, grid_n, density)
+    sc = _fbm_scene(res, grid_n, density, black_patches)
     rng = np.random.default_rng(2024)
     g = _guiding_for(sc, rng, res, res, vol_leaves, surf_leaves)
     ip = api.integrator_defaults(vsp_sampling_nds=0, vsp_criterion_variance=1, light_sampler=A.LIGHTSAMPLER_POWER)
