@@ -15,9 +15,9 @@ JSON line keys (see DESIGN.md "Measurement"):
             render, film download (D2H) inside the timed region
   roofline  the dominant kernel's algorithmic grid bytes (Q*b_q + S*4) / its CUDA-event time vs the
             measured HBM copy peak (MEASURED_PEAKS.json)
-  cpu_baseline  the CPU oracle port of the reference integrator on this box's host cores, bounded sample
---impl reference: the reference's CPU algorithm (oracle port; the full pbrt binary is unbuildable here, see
-DESIGN.md) timed on the host cores, same metric/config.
+  cpu_baseline  the reference renderer (oracle/_ref, kind "reference") on this box's host cores, bounded sample
+--impl reference: the REFERENCE RENDERER ITSELF (oracle/_ref: its own sources, compiled by oracle/build_ref_pbrt.sh) runs
+the workload from the scene / cache / buffer files on all host cores, same metric/config; nothing of libvspg.so is loaded.
 """
 import argparse
 import json
@@ -74,14 +74,19 @@ def build_config(args):
 
 
 def config_dict(cfg, args, world):
-    med = cfg.scene.desc.media[0]
+    grid = "homogeneous"
+    for kind, e in cfg.scene.log:
+        if kind == "medium" and e["type"] != "homogeneous":
+            g = e["density"] if e["type"] == "uniformgrid" else e["sigma_a_rgb"]
+            grid = [int(g.shape[2]), int(g.shape[1]), int(g.shape[0])]
+            break
     return {
         "workload": cfg.name, "description": cfg.description, "width": cfg.width, "height": cfg.height, "spp_per_gpu": cfg.spp,
-        "spp_total": cfg.spp * world, "grid": [med.nx, med.ny, med.nz] if med.type != 0 else "homogeneous",
+        "spp_total": cfg.spp * world, "grid": grid,
         "sampler": "independent", "maxdepth": cfg.ip.max_depth,
         "parallelism": f"{'sample-pass' if args.shard == 'samples' else 'interleaved-band'} sharding x{world}" + (" + NCCL film reduce" if world > 1 else ""),
-        "l2": "path-state working set (2M paths x ~330 B = 0.7 GB) exceeds the 126 MB L2 each wave iteration; density grid "
-              "itself is L2-resident for 128^3 (8 MiB), HBM-resident for 512^3",
+        "l2": "inputs larger than L2: the path-state working set (up to 2^24 paths x ~380 B = 6.4 GB) streams through the 126 MB L2 every wave "
+              "iteration; the density cell records are 67 MB for 128^3 (L2-sized, evicted by the state traffic) and 4.3 GB for 512^3",
     }
 
 
@@ -132,8 +137,63 @@ class ClockSampler:
                 "samples": len(s)}
 
 
+REF_DRIVER = r"""
+import ctypes as C, json, os, sys
+L = C.CDLL(sys.argv[1])                      # oracle/_ref/libpbrtharness.so (+ libpbrt_ref.so: the reference's own code)
+L.refp_open.restype = C.c_void_p; L.refp_open.argtypes = [C.c_char_p]
+L.refp_render.restype = C.c_double; L.refp_render.argtypes = [C.c_void_p, C.c_void_p]
+L.refp_init(int(sys.argv[3]), 0)             # --nthreads N, rendering space "cameraworld" (the reference's default)
+h = L.refp_open(sys.argv[2].encode())
+t = L.refp_render(h, None)                   # integrator->Render(), timed around the call
+sys.stdout.flush()
+os.write(1, ("\nREFP_RESULT " + json.dumps({"render_s": t}) + "\n").encode())
+os._exit(0)
+"""
+
+
+def reference_available():
+    return os.path.exists(os.path.join(ROOT, "oracle", "_ref", "libpbrtharness.so")) and os.path.exists(os.path.join(ROOT, "oracle", "_ref", "libpbrt_ref.so"))
+
+
+class ReferenceArm:
+    """The REFERENCE RENDERER ITSELF on this box's host cores: oracle/_ref/libpbrt_ref.so is the reference's own source
+    compiled by oracle/build_ref_pbrt.sh; this class writes the workload as the files the reference's scene language
+    names (scene.pbrt, guiding cache, ISG / Tr buffers) and runs GuidedVolPathVSPGIntegrator::Render() on them in a
+    child process with all host threads.  Nothing of the product (libvspg.so, CUDA) is loaded on this path."""
+
+    def __init__(self, cfg):
+        import tempfile
+        from pyvspg import export
+        self.cfg = cfg
+        self.dir = tempfile.mkdtemp(prefix="vspg_ref_")
+        self.export = export
+        self.cores = os.cpu_count() or 1
+        self.template = os.path.join(ROOT, "tests", "golden", "field_small.pgl")
+        self._written = {}
+
+    def scene(self, spp):
+        if spp not in self._written:
+            self._written[spp] = self.export.export_config(self.cfg, self.dir, self.template, name=f"w{spp}", outfile=f"w{spp}.pfm", spp=spp)
+        return self._written[spp]
+
+    def render(self, spp):
+        """One Render() of W x H x spp paths; returns (paths, seconds inside Render())."""
+        import subprocess
+        path = self.scene(spp)
+        r = subprocess.run([sys.executable, "-c", REF_DRIVER, os.path.join(ROOT, "oracle", "_ref", "libpbrtharness.so"), path, str(self.cores)],
+                           cwd=self.dir, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)
+        for line in r.stdout.splitlines():
+            if line.startswith("REFP_RESULT "):
+                return self.cfg.width * self.cfg.height * spp, json.loads(line[len("REFP_RESULT "):])["render_s"]
+        raise RuntimeError("reference render failed:\n" + r.stdout[-2000:])
+
+    def close(self):
+        import shutil
+        shutil.rmtree(self.dir, ignore_errors=True)
+
+
 def cpu_oracle_paths_per_s(cfg, spp, seed=0):
-    """Times the CPU oracle port (oracle/liboracle.so) of the reference integrator on all host cores.
+    """Fallback when oracle/_ref is absent: the CPU oracle port (oracle/liboracle.so) on all host cores.
     Checker/baseline use only: nothing on the product path calls this."""
     sys.path.insert(0, os.path.join(ROOT, "oracle"))
     import orc
@@ -145,56 +205,96 @@ def cpu_oracle_paths_per_s(cfg, spp, seed=0):
     return cnt["paths"] / dt, cores, dt, cnt["paths"]
 
 
+def cpu_reference_sample(cfg, target_s, fixed_spp=0):
+    """A bounded sample of the workload on the host cores: (value paths/s, cores, kind, sample text)."""
+    if reference_available() and os.path.exists(os.path.join(ROOT, "tests", "golden", "field_small.pgl")):
+        arm = ReferenceArm(cfg)
+        try:
+            n1, t1 = arm.render(1)                                   # calibration (and page-in) pass
+            spp = fixed_spp or max(1, min(cfg.spp, int(target_s / max(t1, 1e-3))))
+            n, t = arm.render(spp)
+        finally:
+            arm.close()
+        return n / t, arm.cores, "reference", (f"{cfg.width}x{cfg.height} x {spp} spp of the {cfg.spp}-spp workload ({n} paths, {t:.1f} s inside "
+                                               f"GuidedVolPathVSPGIntegrator::Render()); the reference's own sources built by oracle/build_ref_pbrt.sh, --nthreads {arm.cores}")
+    v1, cores, dt1, _ = cpu_oracle_paths_per_s(cfg, 1)
+    spp = fixed_spp or max(1, min(cfg.spp, int(target_s / max(dt1, 1e-3))))
+    v, cores, dt, n = cpu_oracle_paths_per_s(cfg, spp, seed=1)
+    return v, cores, "port", (f"{cfg.width}x{cfg.height} x {spp} spp of the {cfg.spp}-spp workload ({n} paths, {dt:.1f} s); oracle/liboracle.so "
+                              "(CPU restatement; oracle/_ref not present), all host threads")
+
+
 def relmse_check(ctx, args):
-    """SURVEY 8(d) "relMSE vs CPU ref at equal spp", on a bounded instance of the workload (same scene, reduced film):
-    relMSE of the CUDA render and of the CPU oracle render against a common 1024-spp reference, 4 seeds each.
-    Uses the oracle as the checker (cpu leg of the bench only)."""
+    """SURVEY 8(d) "relMSE vs CPU ref at equal spp", on a bounded instance of the workload (same scene, 128-pixel film):
+    relMSE of the CUDA render and of the CPU oracle render against a common high-spp reference rendered BY THE CPU ORACLE
+    (so a bias of the CUDA path cannot hide in the reference), 8 seeds each.  The oracle is the checker here (cpu leg of
+    the bench only); it is itself pinned bit for bit to the reference renderer (tests/test_ref_pbrt.py)."""
     sys.path.insert(0, os.path.join(ROOT, "oracle"))
     import orc
     from pyvspg import configs, stats
     key, kw, _ = WORKLOADS[args.workload]
-    small = dict(C1=dict(res=64, spp=8), C1T=dict(res=64, spp=8), C2=dict(res=64, spp=8, grid_n=64, vol_leaves=512, surf_leaves=256),
-                 C3=dict(res=64, spp=8, grid_n=64, vol_leaves=512, surf_leaves=256),
-                 C4=dict(width=96, height=54, spp=8, grid_n=64, vol_leaves=512, surf_leaves=256),
-                 C5=dict(width=96, height=54, spp=8, grid_n=32, vol_leaves=512, surf_leaves=256))[key]
+    small = dict(C1=dict(res=128, spp=8), C2=dict(res=128, spp=8, grid_n=64, vol_leaves=512, surf_leaves=256),
+                 C3=dict(res=128, spp=8, grid_n=64, vol_leaves=512, surf_leaves=256),
+                 C4=dict(width=160, height=90, spp=8, grid_n=64, vol_leaves=512, surf_leaves=256),
+                 C5=dict(width=160, height=90, spp=8, grid_n=32, vol_leaves=512, surf_leaves=256))[key]
     cfg = configs.BUILDERS[key](**small)
+    cores = os.cpu_count() or 1
+    ref_spp = 512
+    film_ref, _ = orc.render(cfg.scene, cfg.guiding, cfg.ip, 0, ref_spp, seed=4242, nthreads=cores)
+    ref = stats.resolve(film_ref)
     ctx.set_scene(cfg.scene); ctx.set_guiding(cfg.guiding); ctx.set_integrator(cfg.ip)
-    ctx.film_clear(); ctx.render(0, 1024, seed=4242)
-    ref = stats.resolve(ctx.film_download())
     rg, rc = [], []
-    for seed in range(4):
+    for seed in range(8):
         ctx.film_clear(); ctx.render(0, cfg.spp, seed=seed)
         rg.append(stats.rel_mse(stats.resolve(ctx.film_download()), ref))
-        film_o, _ = orc.render(cfg.scene, cfg.guiding, cfg.ip, 0, cfg.spp, seed=100 + seed, nthreads=os.cpu_count() or 1)
+        film_o, _ = orc.render(cfg.scene, cfg.guiding, cfg.ip, 0, cfg.spp, seed=100 + seed, nthreads=cores)
         rc.append(stats.rel_mse(stats.resolve(film_o), ref))
     r = stats.compare(rg, rc)
-    return {"gpu": r["a"], "cpu": r["b"], "abs_diff": r["diff"], "tolerance": r["tolerance"], "agree": r["agree"], "seeds": 4,
-            "instance": f"{cfg.name} at {cfg.width}x{cfg.height}, {cfg.spp} spp; reference = 1024 spp (GPU, disjoint seed)"}
+    return {"gpu": r["a"], "cpu": r["b"], "abs_diff": r["diff"], "tolerance": r["tolerance"], "agree": r["agree"], "seeds": 8,
+            "instance": f"{cfg.name} at {cfg.width}x{cfg.height}, {cfg.spp} spp; reference = {ref_spp} spp rendered by the CPU oracle (disjoint seed)"}
 
 
 def run_reference(args):
-    """--impl reference: the reference's CPU algorithm on the host cores (oracle port; kind = "port")."""
+    """--impl reference: the reference's own CPU implementation of the path on the host cores (oracle/_ref when it was
+    built -- kind "reference" --, else the oracle port), same metric / config; each step is a bounded sample."""
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
     cfg, _ = build_config(args)
-    # bounded sample per step: calibrate with 1 spp, then size each step to ~8 s
-    v1, cores, dt1, _ = cpu_oracle_paths_per_s(cfg, 1)
-    spp_step = args.cpu_spp or max(1, min(cfg.spp, int(8.0 / max(dt1, 1e-3))))
-    for _ in range(max(0, args.warmup - 1)):
-        cpu_oracle_paths_per_s(cfg, 1)
-    tot_paths, tot_t = 0, 0.0
-    for s in range(args.steps):
-        v, cores, dt, n = cpu_oracle_paths_per_s(cfg, spp_step, seed=s)
-        tot_paths += n
-        tot_t += dt
+    cores = os.cpu_count() or 1
+    if reference_available():
+        arm = ReferenceArm(cfg)
+        try:
+            n1, t1 = arm.render(1)
+            spp_step = args.cpu_spp or max(1, min(cfg.spp, int(8.0 / max(t1, 1e-3))))
+            for _ in range(max(0, min(args.warmup, 3) - 1)):
+                arm.render(1)
+            tot_paths, tot_t = 0, 0.0
+            for s in range(args.steps):
+                n, t = arm.render(spp_step)
+                tot_paths += n
+                tot_t += t
+        finally:
+            arm.close()
+        kind = "reference"
+        how = "the reference's own sources (oracle/_ref, built by oracle/build_ref_pbrt.sh), Render() timed, --nthreads %d" % cores
+    else:
+        v1, cores, dt1, _ = cpu_oracle_paths_per_s(cfg, 1)
+        spp_step = args.cpu_spp or max(1, min(cfg.spp, int(8.0 / max(dt1, 1e-3))))
+        tot_paths, tot_t = 0, 0.0
+        for s in range(args.steps):
+            v, cores, dt, n = cpu_oracle_paths_per_s(cfg, spp_step, seed=s)
+            tot_paths += n
+            tot_t += dt
+        kind = "port"
+        how = "oracle/liboracle.so (CPU restatement; oracle/_ref not present)"
     val = tot_paths / tot_t
-    sample = f"{cfg.width}x{cfg.height} x {spp_step} spp per step of the {cfg.spp}-spp workload (waves are independent)"
+    sample = f"{cfg.width}x{cfg.height} x {spp_step} spp per step of the {cfg.spp}-spp workload (sample passes are independent); {how}"
     print(json.dumps({
         "impl": "reference", "metric": "paths/sec (guidedvolpathvspg render pass)", "value": val, "unit": "paths/s", "n_gpus": args.gpus,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * tot_t / max(1, args.steps), "higher_is_better": True,
         "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic", "config": config_dict(cfg, args, 1),
-        "cpu_baseline": {"value": val, "unit": "paths/s", "cores": cores, "kind": "port", "sample": sample},
+        "cpu_baseline": {"value": val, "unit": "paths/s", "cores": cores, "kind": kind, "sample": sample},
         "e2e": {"value": val, "unit": "paths/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }))
@@ -280,8 +380,7 @@ def run_b200(args):
     for i in range(args.warmup):
         step(i)
     barrier()
-    ctx.counters_reset()
-    ctx.kernel_stats(enable_timing=True)
+    ctx.kernel_stats(enable_timing=False)     # the headline is timed without the per-kernel events / syncs
     clocks = ClockSampler(local)
     clocks.start()
     ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
@@ -296,9 +395,21 @@ def run_b200(args):
     if world > 1:
         dist.all_reduce(ms, op=dist.ReduceOp.MAX)
     ms_total = float(ms.item())
+    value = paths_per_step * args.steps / (ms_total * 1e-3)
+    # per-kernel shares / roofline inputs: a separate pass of the same steps with the stage events on
+    ctx.counters_reset()
+    ctx.kernel_stats(enable_timing=True)
+    barrier()
+    sev0, sev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    sev0.record()
+    stat_steps = max(1, min(args.steps, 3))
+    for i in range(stat_steps):
+        step(100 + i)
+    sev1.record()
+    barrier()
+    ms_stats = sev0.elapsed_time(sev1)
     cnt = ctx.counters()
     ks = ctx.kernel_stats(enable_timing=False)
-    value = paths_per_step * args.steps / (ms_total * 1e-3)
 
     # ---- e2e: host buffers -> C ABI -> host film, copies inside the timed region
     h2d = input_bytes(cfg)
@@ -346,24 +457,20 @@ def run_b200(args):
             "algorithmic_bytes_per_launch": alg_bytes / max(1, kk["launches"]), "avg_launch_ms": per_launch_ms,
             "bytes_per_query": b_q, "queries": kk["density_queries"], "dda_steps": kk["dda_steps"],
             "kernel_ms_share": {k: round(ks[k]["ms"] / max(1e-9, sum(ks[n]["ms"] for n in names)), 4) for k in names},
-            "kernel_ms_sum": sum(ks[n]["ms"] for n in names), "timed_region_ms": ms_total,
+            "kernel_ms_sum": sum(ks[n]["ms"] for n in names), "stats_pass_ms": ms_stats, "stats_pass_steps": stat_steps, "timed_region_ms": ms_total,
         }
         cpu = None
         relmse = None
         if not args.no_cpu_baseline and world == 1:
             relmse = relmse_check(ctx, args)
-            v1, cores, dt1, _ = cpu_oracle_paths_per_s(cfg, 1)
-            cspp = args.cpu_spp or max(1, min(spp, int(15.0 / max(dt1, 1e-3))))
-            v, cores, dtc, n = cpu_oracle_paths_per_s(cfg, cspp, seed=1)
-            cpu = {"value": v, "unit": "paths/s", "cores": cores, "kind": "port",
-                   "sample": f"{W}x{Hh} x {cspp} spp of the {spp}-spp workload ({n} paths, {dtc:.1f} s); oracle/liboracle.so "
-                             "(CPU restatement of the reference integrator), all host threads"}
+            v, cores, kind, sample = cpu_reference_sample(cfg, 15.0, args.cpu_spp)
+            cpu = {"value": v, "unit": "paths/s", "cores": cores, "kind": kind, "sample": sample}
         out = {
             "metric": "paths/sec (guidedvolpathvspg render pass)", "value": value, "unit": "paths/s", "n_gpus": world, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": ms_total / args.steps, "higher_is_better": True, "scaling": "weak",
             "vs_baseline": None, "dtype": "f32", "data": "synthetic", "config": config_dict(cfg, args, world),
             "e2e": {"value": e2e_value, "unit": "paths/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h, "steps": e2e_steps},
-            "gpu_launches": cnt["kernel_launches"], "clocks": clk, "roofline": roofline, "cpu_baseline": cpu, "relmse": relmse,
+            "gpu_launches": int(round(cnt["kernel_launches"] * args.steps / stat_steps)), "clocks": clk, "roofline": roofline, "cpu_baseline": cpu, "relmse": relmse,
             "counters": {k: cnt[k] for k in ("paths", "density_queries", "dda_steps", "cache_lookups", "bvh_nodes", "shadow_rays", "wave_iterations")},
             "mean_radiance": float(film_host[..., :3].sum() / max(1.0, float(film_host[..., 3].sum()))),
         }

@@ -50,6 +50,9 @@ def test_integrator_defaults_follow_the_reference_create():
     assert (ip.vsp_guiding, ip.vsp_primary_guiding, ip.vsp_secondary_guiding) == (1, 1, 1)
     assert ip.vsp_mis_ratio == 0.5 and ip.vsp_criterion_variance == 1 and ip.vsp_sampling_nds == 0
     assert ip.collision_probability_bias == 0 and ip.light_sampler == A.LIGHTSAMPLER_BVH and ip.regularize == 0
+    c_side = A.IntegratorParams()
+    api.lib().vspg_integrator_defaults(C.byref(c_side))          # the C ABI's defaults are the same values
+    assert bytes(c_side) == bytes(ip)
 
 
 # ------------------------------------------------------------------ known answers for the integer / polynomial pieces

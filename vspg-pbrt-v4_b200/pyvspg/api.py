@@ -24,10 +24,19 @@ class VspgError(RuntimeError):
         self.code = code
 
 
+_DEFAULTS = dict(max_depth=5, min_rr_depth=1, use_nee=1, surface_guiding=1, volume_guiding=1, surface_guiding_ris=1, volume_guiding_ris=0,
+                 vsp_guiding=1, vsp_primary_guiding=1, vsp_secondary_guiding=1, vsp_mis_ratio=0.5, vsp_criterion_variance=1,
+                 vsp_sampling_nds=0, collision_probability_bias=0, light_sampler=A.LIGHTSAMPLER_BVH, regularize=0)
+
+
 def integrator_defaults(**over):
     """guidedvolpathvspgintegrator.cpp:1260-1322 defaults, overridable by keyword (field names of vspg_integrator_params)."""
     ip = A.IntegratorParams()
-    lib().vspg_integrator_defaults(C.byref(ip))
+    # the same values vspg_integrator_defaults() fills in (tests/test_cpu.py checks the two against each other); kept in
+    # Python so that building a configuration -- e.g. to write its scene file for the reference arm of bench.py -- does
+    # not need the CUDA library
+    for k, v in _DEFAULTS.items():
+        setattr(ip, k, v)
     for k, v in over.items():
         if not hasattr(ip, k):
             raise KeyError(f"unknown integrator parameter {k!r}")  # the reference ErrorExits on unused parameters

@@ -51,7 +51,7 @@ def scene_text(cfg, out_dir=None, outfile="out.exr", seed=0, integrator_name="gu
     for text) -- needs out_dir."""
     sc = cfg.scene
     cp = sc.camera._params
-    fc = sc.desc.camera if sc.desc is not None else sc.camera   # the filter may have been changed on the finalised desc
+    fc = sc._desc.camera if getattr(sc, "_desc", None) is not None else sc.camera   # the filter may have been changed on the finalised desc
     L = [f'LookAt {_v(cp["eye"])}  {_v(cp["look"])}  {_v(cp["up"])}',
          f'Camera "perspective" "float fov" [{_f(cp["fov"])}] "float lensradius" [{_f(cp["lens_radius"])}] "float focaldistance" [{_f(cp["focal_distance"])}]',
          f'Film "rgb" "integer xresolution" [{sc.camera.width}] "integer yresolution" [{sc.camera.height}] "string filename" "{outfile}"',

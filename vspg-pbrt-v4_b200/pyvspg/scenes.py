@@ -37,7 +37,7 @@ class Scene:
         self.camera, self.eye = camera, np.asarray(eye, dtype=np.float64)
         self.n_quads = self.n_triangles = self.n_spheres = self.n_materials = self.n_lights = self.n_media = 0
         self._keep = []
-        self.desc = None
+        self._desc = None
         self._hs = None
         self.log = []   # world-space record of every add_* call, in order (pbrt_writer turns it into a .pbrt file)
 
@@ -147,6 +147,17 @@ class Scene:
         return self.n_media - 1
 
     def finalize(self):
+        """Closes the scene description.  The POD desc is built on first use (`.desc`): writing the scene as files for
+        the reference renderer needs only the world-space log, not the CUDA library."""
+        return self
+
+    @property
+    def desc(self):
+        if self._desc is None:
+            self._build_desc()
+        return self._desc
+
+    def _build_desc(self):
         """Parses the scene through the C++ front end (vspg_host_scene_parse_string).  Grids travel by pointer, not
         as text: the scene text carries 1x1x1 placeholders and the parsed vspg_medium records are then pointed at the
         numpy arrays (the front end only stores grids; majorants / cell records are built by vspg_set_scene)."""
@@ -166,8 +177,7 @@ class Scene:
                 m.nz, m.ny, m.nx = e["sigma_a_rgb"].shape[:3]
                 m.sigma_a_rgb = e["sigma_a_rgb"].ctypes.data_as(A.PF)
                 m.sigma_s_rgb = e["sigma_s_rgb"].ctypes.data_as(A.PF)
-        self.desc = d
-        return self
+        self._desc = d
 
     @property
     def n_pixels(self):

@@ -130,10 +130,13 @@ class Guiding:
         self.desc = A.GuidingDesc()
         self._keep = []
         self.fields = {}
+        self.points = {}     # per field: the regions' sample means (the KNN points), for pgl_writer
 
     def set_field(self, which, field_struct, keep):
         self._keep.append((field_struct, keep))
         self.fields[which] = field_struct
+        if isinstance(keep, tuple) and len(keep) == 4:
+            self.points[which] = keep[3]
         setattr(self.desc, which, C.pointer(field_struct))
 
     def set_isg(self, vsp):
