@@ -13,10 +13,12 @@
  * reference itself can be run with it (LD_PRELOAD) -- that pairing is what the golden vectors in tests/golden/pbrt/
  * were produced with, and it is how a maintainer reproduces the product's images with the reference binary.
  *
- * Accuracy: every float function evaluates in double to < 1e-13 relative error and rounds once, i.e. the result is the
- * correctly rounded float except when the exact value lies within ~1e-13 of a rounding boundary (< 1 ulp always).
- * sin / cos / tan reduce with a three-part pi/2 and are accurate for |x| < 2^20 (the path's arguments are below 7);
- * beyond that they stay deterministic but lose accuracy.
+ * Accuracy.  logf and sincosf (|x| <= 16) -- the two the kernels call per tentative collision / per sampled direction --
+ * are float-only algorithms (short dependency chains on the GPU): logf is within 1 ulp; sin / cos are within 1 ulp
+ * except next to their zeros, where the absolute error stays below 2e-13.  Every other float function evaluates in
+ * double to < 1e-13 relative error and rounds once (the correctly rounded float except when the exact value lies
+ * within ~1e-13 of a rounding boundary).  sin / cos / tan beyond 16 reduce in double with a three-part pi/2 and are
+ * accurate for |x| < 2^20; beyond that they stay deterministic but lose accuracy.
  */
 #ifndef VSPG_LIBM_H
 #define VSPG_LIBM_H
@@ -82,7 +84,30 @@ VSPG_HD double vspg_log(double x) {
     if (x == vspg_m_inf()) return x;
     return vspg_k_log(x);
 }
-VSPG_HD float vspg_logf(float x) { return (float)vspg_log((double)x); }
+/* logf in float arithmetic only (the walk through a medium takes one per tentative collision): x = 2^e m with
+ * m in [2/3, 4/3), f = m - 1, log m = f - f^2/2 + f^3 P(f) with a degree-7 fit of (log(1+f) - f + f^2/2) / f^3 on
+ * [-1/3, 1/3] (relative error 1.6e-8 before rounding); every step is an IEEE float operation or an fmaf, so host and
+ * device agree bit for bit.  Zero, subnormal, negative, inf and NaN arguments take the double path above. */
+VSPG_HD float vspg_logf(float x) {
+    uint32_t ix = vspg_m_fbits(x);
+    if (ix - 0x00800000u >= 0x7f000000u) return (float)vspg_log((double)x);
+    int32_t e = (int32_t)(ix - 0x3f2aaaabu) >> 23;
+    float m = vspg_m_bitsf(ix - ((uint32_t)e << 23));
+    float f = m - 1.0f, f2 = f * f;
+    float p = -0.124309964f;
+    p = fmaf(p, f, 0.134348407f);
+    p = fmaf(p, f, -0.122870483f);
+    p = fmaf(p, f, 0.141168296f);
+    p = fmaf(p, f, -0.16673407f);
+    p = fmaf(p, f, 0.200038403f);
+    p = fmaf(p, f, -0.249999434f);
+    p = fmaf(p, f, 0.333333194f);
+    float r = fmaf(f2 * f, p, -0.5f * f2);
+    float fe = (float)e;
+    r = fmaf(fe, 1.42860677e-06f, r);          /* e * ln2_lo */
+    r = r + f;
+    return fmaf(fe, 0.693145752f, r);          /* e * ln2_hi (15 significant bits: the product is exact) */
+}
 
 /* ------------------------------------------------------------------------------------------------ exp */
 /* exp(x), |x| <= 745.2: x = k ln2 + r, |r| <= 0.3466, Taylor through r^13 (remainder < 5e-18), scaled in two steps */
@@ -211,11 +236,41 @@ VSPG_HD void vspg_sincos_d(double x, double *s, double *c) {
     default: *s = -cr; *c = sr; break;
     }
 }
+/* sincosf in float arithmetic only for |x| <= 16 (every phase / polar angle of the path is below 7): three-part
+ * Cody-Waite reduction by pi/2 (the first two parts have 11 significant bits, so j * part is exact for |j| < 2^12),
+ * then r + r^3 S(r^2) and 1 - r^2/2 + r^4 C(r^2) with degree-3 fits (relative error 3.5e-9 / 7.8e-10 before rounding).
+ * Larger arguments take the double path. */
 VSPG_HD void vspg_sincosf(float x, float *s, float *c) {
     if (x == 0) { *s = x; *c = 1.f; return; } /* keeps the sign of zero */
-    double ds, dc;
-    vspg_sincos_d((double)x, &ds, &dc);
-    *s = (float)ds; *c = (float)dc;
+    float ax = x < 0 ? -x : x;
+    if (!(ax <= 16.f)) {
+        double ds, dc;
+        vspg_sincos_d((double)x, &ds, &dc);
+        *s = (float)ds; *c = (float)dc;
+        return;
+    }
+    float j = (x * 0.636619747f + 12582912.f) - 12582912.f;   /* nearest integer of x * 2/pi (ties to even) */
+    float r = fmaf(-j, 1.5703125f, x);
+    r = fmaf(-j, 0.0004837512969970703f, r);
+    r = fmaf(-j, 7.54979013e-08f, r);
+    float z = r * r;
+    float ps = 2.72342027e-06f;
+    ps = fmaf(ps, z, -0.000198399619f);
+    ps = fmaf(ps, z, 0.00833333191f);
+    ps = fmaf(ps, z, -0.166666672f);
+    float sr = fmaf(r * z, ps, r);
+    float pc = -2.7287831e-07f;
+    pc = fmaf(pc, z, 2.48004962e-05f);
+    pc = fmaf(pc, z, -0.00138888869f);
+    pc = fmaf(pc, z, 0.0416666679f);
+    float cr = fmaf(z * z, pc, fmaf(-0.5f, z, 1.0f));
+    int q = (int)j & 3;
+    switch (q) {
+    case 0: *s = sr; *c = cr; break;
+    case 1: *s = cr; *c = -sr; break;
+    case 2: *s = -sr; *c = -cr; break;
+    default: *s = -cr; *c = sr; break;
+    }
 }
 VSPG_HD float vspg_sinf(float x) { float s, c; vspg_sincosf(x, &s, &c); return s; }
 VSPG_HD float vspg_cosf(float x) { float s, c; vspg_sincosf(x, &s, &c); return c; }

@@ -58,11 +58,20 @@ def probe(L, h, mode, pos, u, aux, g, s2, wq):
 
 
 def main():
+    # The probes are answered by the reference library running with the path's portable libm (include/vspg_libm.h through
+    # oracle/libportm.so), like the pbrt-side vectors (make_golden_pbrt.py): sincosf in the vMF sampler is then the same
+    # function on every machine.  `--probe-only` keeps the committed field / ISG files and re-answers the probes.
+    shim = os.path.join(ROOT, "oracle", "libportm.so")
+    if shim not in os.environ.get("LD_PRELOAD", ""):
+        os.environ["LD_PRELOAD"] = shim
+        os.execv(sys.executable, [sys.executable] + sys.argv)
+    probe_only = "--probe-only" in sys.argv
     L = harness()
     path = os.path.join(HERE, "field_small.pgl")
     bmin, bmax = np.float32([-1, -1, -1]), np.float32([2, 2, 2])
-    it = L.ref_field_train(path.encode(), fp(bmin), fp(bmax), 6000, 14000, 3, 7, 1, 1500)
-    assert it == 3, it
+    if not probe_only:
+        it = L.ref_field_train(path.encode(), fp(bmin), fp(bmax), 6000, 14000, 3, 7, 1, 1500)
+        assert it == 3, it
     h = L.ref_field_load(path.encode())
     assert L.ref_field_iteration(h) == 3
     rng = np.random.default_rng(99)
@@ -82,6 +91,9 @@ def main():
             out[f"{name}_{k}"] = v
     L.ref_field_free(h)
     np.savez_compressed(os.path.join(HERE, "pgl_probe.npz"), **out)
+    if probe_only:
+        print("re-answered the probes on the committed field")
+        return
     w, hgt = 40, 24
     vsp = np.zeros((hgt, w), np.float32)
     assert L.ref_isgb_make(os.path.join(HERE, "isg_small.exr").encode(), w, hgt, 8, 5, fp(vsp)) == 1
