@@ -175,6 +175,9 @@ VD void spawn_ray_to(V3 pf_, V3 pfErr, V3 nf, V3 pLight, V3 pLightErr, V3 nLight
 // the top stall was instruction fetch (ncu r01c: no_instruction 3.8-5.9 per issue).  Trip counts are therefore
 // uniform over the whole CTA (`base` is a CTA quantity) and the loop body carries __syncthreads() between its
 // phases (scatter_phase_sync), so that the warps of a CTA walk the code together and share instruction-cache lines.
+#ifndef VSPG_VOL_MINB
+#define VSPG_VOL_MINB 3                   // resident CTAs/SM the volume scatter kernel is compiled for (A/B knob, see profiles/)
+#endif
 constexpr int kScatterBlock = 256;        // launch bound and default block of the lane-group scatter kernels (r01e A/B: 512 -> 116.5, 256 -> 118.0, 128 -> 109.4 Mpaths/s)
 template <int G> struct GroupIter {
     static constexpr int W = G > 0 ? G : 1;        // lanes per vertex
@@ -238,89 +241,121 @@ __global__ void __launch_bounds__(kBlock) k_lookup(const DScene sc, const Wavefr
 }
 
 // ------------------------------------------------------------------ volume scatter vertex (vspg.cpp:804-875 / 988-1058)
+// Register discipline (profiles/r02n: the 64-register build spilled 540 B per lane and its local-memory sectors were 5x
+// its global ones): the G lanes of a group only carry what the mixture operations need -- the sampling distribution,
+// the sampler, p and the incoming direction.  The path record is never held as a whole: the Russian-roulette factor
+// is formed from a transient read of beta / r_u, NEE only evaluates the phase function and the guided pdf towards the
+// pre-drawn light sample, and the group's leader assembles the shadow-ray record and the outgoing path record in a
+// scalar epilogue, straight from the SoA streams, once the mixture is dead.
 template <int G>
-__global__ void __launch_bounds__(G > 0 ? 256 : kBlock, G > 0 ? 4 : 1) k_volscatter(const DScene sc, const Wavefront W, const Queue in) {
+__global__ void __launch_bounds__(G > 0 ? 256 : kBlock, G > 0 ? VSPG_VOL_MINB : 1) k_volscatter(const DScene sc, const Wavefront W, const Queue in) {
     const int n = *in.count;
     const GroupIter<G> gi;
     const bool leader = gi.leader;
+    const vspg_integrator_params &ip = sc.ip;
     unsigned lookups = 0, shadows = 0;
     for (int base = gi.first; base < n; base += gi.step) {
         const int i0 = base + gi.warpOff;
         const bool live = i0 + gi.sub < n;
         if (G == 0 && !live) continue;             // one thread per vertex: no group shuffles, no barriers
         scatter_phase_sync<G>();
-        int slot = in.items[live ? i0 + gi.sub : base];
-        PathRegs ps; path_load(W.P, slot, ps);
-        float4 e = W.P.ev[slot];
-        V3 p(e.x, e.y, e.z);
-        const vspg_integrator_params &ip = sc.ip;
+        const int slot = in.items[live ? i0 + gi.sub : base];
+        V3 p, rd; float g_; int flw;
+        {
+            float4 e = W.P.ev[slot], a = W.P.o_dx[slot], b = W.P.d_med[slot];
+            p = V3(e.x, e.y, e.z); g_ = e.w; rd = V3(a.w, b.x, b.y); flw = __float_as_int(b.w);
+        }
+        const int depth = flw & 0xff;
+        Rng rng; { ulonglong2 q = W.P.rng[slot]; rng.state = q.x; rng.inc = q.y; }
         GuidedPhase<G> gphase;
         gphase.enableGuiding = ip.volume_guiding; gphase.enableScatterGuiding = ip.vsp_secondary_guiding; gphase.ris = ip.volume_guiding_ris;
-        if (G > 0) gphase.init_region(sc, e.w, p, ps.ray.d, W.P.lk[slot]);   // `v` was drawn by k_lookup
-        else { float v = ps.rng.uniform(); gphase.init(sc, e.w, p, ps.ray.d, v, lookups); }
+        if (G > 0) gphase.init_region(sc, g_, p, rd, W.P.lk[slot]);   // `v` was drawn by k_lookup
+        else { float v = rng.uniform(); gphase.init(sc, g_, p, rd, v, lookups); }
         scatter_phase_sync<G>();
         float survivalProb = 1.0f;
-        if (ps.fl.depth > ip.min_rr_depth) {
-            V3 rrw = (ps.beta / avg3(ps.r_u)) * ps.rr_correction;   // openpgl/cpp/RussianRoulette.h:32-35
-            survivalProb = ps.fl.specular ? 0.95f : fmaxf(0.f, fminf(1.f, max_comp(rrw)));
+        if (depth > ip.min_rr_depth) {
+            float4 c = W.P.beta_ru[slot], d = W.P.ru_rl[slot];
+            V3 rrw = (V3(c.x, c.y, c.z) / avg3(V3(c.w, d.x, d.y))) * W.P.misc[slot].x;   // openpgl/cpp/RussianRoulette.h:32-35
+            survivalProb = ((flw >> 10) & 1) ? 0.95f : fmaxf(0.f, fminf(1.f, max_comp(rrw)));
         }
         bool emitShadow = false;
+        float nee_ph = 0, nee_pdf = 0;
         if (ip.use_nee) {
-            V3 wo = -ps.ray.d;
-            NeePre ls;
+            bool valid; V3 wi;
             if (G > 0) {   // drawn by k_lookup from these three sampler dimensions
-                ps.rng.uniform(); ps.rng.uniform(); ps.rng.uniform();
+                rng.uniform(); rng.uniform(); rng.uniform();
                 // A lane group past the end of the queue re-runs the CTA's first item for the barriers only: it must not read
                 // that slot's parked record, which the owning group's leader (possibly in another warp) overwrites below.
-                if (live) ls = nee_load(W.P, slot); else { ls.valid = false; ls.delta = false; ls.p_l = 0; }
-                __syncwarp(grp_mask<G>());   // every lane of THIS group has read the parked record before its leader overwrites it
-                                             // (the branch is per vertex: other groups of the warp may not be here)
-            } else ls = nee_presample(sc, ps.rng, p, V3()), ps.rng.uniform(), ps.rng.uniform(), ps.rng.uniform();
-            {
-                if (ls.valid) {
-                    float p_l = ls.p_l;
-                    float ph = gphase.p(wo, ls.wi);
-                    float scatterPDF = 1.0f * gphase.pdf(wo, ls.wi);
-                    if (ph != 0) {
-                        ShadowRec sr;
-                        spawn_ray_to(p, V3(), V3(), ls.pLight, ls.pLightErr, ls.nLight, &sr.o, &sr.d);
-                        sr.medium = ps.ray.medium;
-                        sr.f_hat = splat(ph); sr.L = ls.L; sr.beta = ps.beta;
-                        sr.rl = ps.r_u * p_l; sr.ru = ps.r_u * scatterPDF;
-                        sr.pLight = ls.pLight; sr.pLightErr = ls.pLightErr; sr.nLight = ls.nLight;
-                        sr.delta = ls.delta; sr.channel = ps.fl.channel;
-                        if (leader && live) shadow_store(W.P, slot, sr);
-                        emitShadow = true;
-                    }
-                }
+                float4 r = live ? W.P.sh_rl[slot] : make_float4(0, 0, 0, 0);
+                valid = __float_as_int(r.w) & 1; wi = V3(r.x, r.y, r.z);
+            } else {
+                NeePre ls = nee_presample(sc, rng, p, V3());
+                rng.uniform(); rng.uniform(); rng.uniform();
+                nee_store(W.P, slot, ls);      // the epilogue reads the record back like the lane-group builds do
+                valid = ls.valid; wi = ls.wi;
+            }
+            if (valid) {
+                nee_ph = gphase.p(-rd, wi);
+                nee_pdf = 1.0f * gphase.pdf(-rd, wi);
+                emitShadow = nee_ph != 0;
             }
         }
         scatter_phase_sync<G>();
-        bool alive = true;
-        if (survivalProb < 1 && ps.fl.depth > ip.min_rr_depth) {
+        bool alive = true, rr = false;
+        if (survivalProb < 1 && depth > ip.min_rr_depth) {
             float q = fmaxf(0.f, 1 - survivalProb);
-            if (ps.rng.uniform() < q) alive = false;
-            else ps.beta = ps.beta / (1 - q);
+            if (rng.uniform() < q) alive = false;
+            else rr = true;
         }
+        V3 wiNext; float pfw = 0, sPdf = 0, vspNext = 0;
         if (alive) {
-            float u0 = ps.rng.uniform(), u1 = ps.rng.uniform();
-            ScatterSample s = gphase.sample_p(-ps.ray.d, u0, u1, ps.rng);
+            float u0 = rng.uniform(), u1 = rng.uniform();
+            ScatterSample s = gphase.sample_p(-rd, u0, u1, rng);
             if (!s.valid || s.pdf == 0) alive = false;
             else {
-                float phaseFunctionWeight = s.f.x / s.pdf;
-                ps.beta = ps.beta * phaseFunctionWeight;
-                ps.r_l = ps.r_u / s.pdf;
-                ps.prevP = p; ps.prevNs = V3();
-                ps.ray.o = p; ps.ray.d = s.wi;
-                ps.fl.specular = false; ps.fl.anyNonSpecular = true; ps.fl.lastVertexVolume = true;
-                ps.vsp_next = gphase.vsp(s.wi);
+                pfw = s.f.x / s.pdf; sPdf = s.pdf; wiNext = s.wi;
+                vspNext = gphase.vsp(s.wi);
             }
         }
         scatter_phase_sync<G>();
         const bool w = leader && live;
-        if (w) {
-            path_store(W.P, slot, ps);
-            if (emitShadow) shadows++;
+        if (w && (emitShadow || alive)) {
+            float4 c = W.P.beta_ru[slot], d = W.P.ru_rl[slot];
+            V3 beta(c.x, c.y, c.z), r_u(c.w, d.x, d.y);
+            if (emitShadow) {
+                // sh_pl / sh_ple / sh_ru.w (light point, its error bounds, its normal) and sh_c.xyz (L) already hold the
+                // shadow record's values: the parked NEE record shares their layout
+                float4 lc = W.P.sh_c[slot], pl = W.P.sh_pl[slot], pe = W.P.sh_ple[slot], nr = W.P.sh_rl[slot];
+                const float nz = W.P.sh_ru[slot].w;
+                V3 so, sd;
+                spawn_ray_to(p, V3(), V3(), V3(pl.x, pl.y, pl.z), V3(pe.x, pe.y, pe.z), V3(pl.w, pe.w, nz), &so, &sd);
+                const int delta = (__float_as_int(nr.w) >> 1) & 1, channel = (flw >> 8) & 3;
+                V3 rl = r_u * lc.w, ru = r_u * nee_pdf;
+                W.P.sh_o[slot] = make_float4(so.x, so.y, so.z, sd.x);
+                W.P.sh_d[slot] = make_float4(sd.y, sd.z, W.P.d_med[slot].z, __int_as_float(delta | (channel << 8)));
+                W.P.sh_c[slot] = make_float4(lc.x, lc.y, lc.z, beta.x);
+                W.P.sh_rl[slot] = make_float4(rl.x, rl.y, rl.z, beta.y);
+                W.P.sh_f[slot] = make_float4(nee_ph, nee_ph, nee_ph, beta.z);
+                W.P.sh_ru[slot] = make_float4(ru.x, ru.y, ru.z, nz);
+                shadows++;
+            }
+            if (alive) {
+                if (rr) beta = beta / (1 - fmaxf(0.f, 1 - survivalProb));
+                beta = beta * pfw;
+                V3 r_l = r_u / sPdf;
+                PathFlags fl = PathFlags::unpack(flw);
+                fl.specular = false; fl.anyNonSpecular = true; fl.lastVertexVolume = true;
+                float4 b = W.P.d_med[slot], e = W.P.rl_L[slot], f = W.P.misc[slot], g2 = W.P.misc2[slot];
+                W.P.o_dx[slot] = make_float4(p.x, p.y, p.z, wiNext.x);
+                W.P.d_med[slot] = make_float4(wiNext.y, wiNext.z, b.z, __int_as_float(fl.pack()));
+                W.P.beta_ru[slot] = make_float4(beta.x, beta.y, beta.z, r_u.x);
+                W.P.ru_rl[slot] = make_float4(r_u.y, r_u.z, r_l.x, r_l.y);
+                W.P.rl_L[slot] = make_float4(r_l.z, e.y, e.z, e.w);
+                W.P.rng[slot] = make_ulonglong2(rng.state, rng.inc);
+                W.P.misc[slot] = make_float4(f.x, vspNext, p.x, p.y);
+                W.P.misc2[slot] = make_float4(p.z, g2.y, g2.z, g2.w);
+                W.P.prev_ns[slot] = make_float4(0.f, 0.f, 0.f, 0.f);
+            }
         }
         queue_push(W.shadow, w && emitShadow, slot);
         queue_push(W.next, w && alive, slot);

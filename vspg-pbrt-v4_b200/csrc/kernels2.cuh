@@ -64,8 +64,17 @@ __global__ void __launch_bounds__(kBlock, 5) k_surface(const DScene sc, const Wa
 }
 
 // ------------------------------------------------------------------ surface scatter vertex (vspg.cpp:448-607)
+// Same register discipline as k_volscatter: the lanes carry the mixture, the shading frame and the sampler; what the
+// scalar epilogue needs of the intersection (point interval, normals, media) waits in a small shared-memory record per
+// vertex, and the path record is read and written by the group's leader only, straight from / to the SoA streams.
+struct ShadeKeep { float p[3], pe[3], n[3], ns[3]; int mIn, mOut, rayMed, hasIf; };
+#ifndef VSPG_SHADE_MINB
+#define VSPG_SHADE_MINB 3
+#endif
 template <int G>
-__global__ void __launch_bounds__(G > 0 ? 256 : kBlock, G > 0 ? 3 : 1) k_shade(const DScene sc, const Wavefront W, const Queue in) {
+__global__ void __launch_bounds__(G > 0 ? 256 : kBlock, G > 0 ? VSPG_SHADE_MINB : 1) k_shade(const DScene sc, const Wavefront W, const Queue in) {
+    __shared__ ShadeKeep keep_s[G > 0 ? 256 / G : kBlock];
+    ShadeKeep &K = keep_s[G > 0 ? threadIdx.x / (G > 0 ? G : 1) : threadIdx.x];
     const int n = *in.count;
     const GroupIter<G> gi;
     const bool leader = gi.leader;
@@ -75,86 +84,125 @@ __global__ void __launch_bounds__(G > 0 ? 256 : kBlock, G > 0 ? 3 : 1) k_shade(c
         const int i0 = base + gi.warpOff;
         const bool live = i0 + gi.sub < n;
         if (G == 0 && !live) continue;             // one thread per vertex: no group shuffles, no barriers
-        scatter_phase_sync<G>();
-        int slot = in.items[live ? i0 + gi.sub : base];
-        PathRegs ps; path_load(W.P, slot, ps);
-        float4 hr = W.P.hit[slot];
-        Hit h; h.t = hr.x; h.u = hr.y; h.v = hr.z; h.prim = __float_as_int(hr.w);
-        SurfaceIntr isect = make_intr(sc, h, ps.ray.o, ps.ray.d, ps.ray.medium);
+        scatter_phase_sync<G>();                   // also: the previous trip's epilogue is done with K
+        const int slot = in.items[live ? i0 + gi.sub : base];
+        Rng rng; { ulonglong2 q = W.P.rng[slot]; rng.state = q.x; rng.inc = q.y; }
         GuidedBSDF<G> gbsdf;
         gbsdf.enableGuiding = ip.surface_guiding; gbsdf.enableScatterGuiding = ip.vsp_secondary_guiding; gbsdf.ris = ip.surface_guiding_ris;
-        gbsdf.set_bsdf(isect.ns, isect.dpdu, ld3(sc.materials[isect.material].reflectance));
-        if (G > 0) gbsdf.init_region(sc, ps.ray.o + h.t * ps.ray.d, ps.ray.d, isect.ns, W.P.lk[slot]);   // `v` was drawn by k_lookup
-        else { float v = ps.rng.uniform(); gbsdf.init(sc, ps.ray.o + h.t * ps.ray.d, ps.ray.d, isect.ns, v, lookups); }
+        V3 rd, woN;
+        {
+            float4 a = W.P.o_dx[slot], b = W.P.d_med[slot], hr = W.P.hit[slot];
+            Hit h; h.t = hr.x; h.u = hr.y; h.v = hr.z; h.prim = __float_as_int(hr.w);
+            V3 ro(a.x, a.y, a.z);
+            rd = V3(a.w, b.x, b.y);
+            SurfaceIntr isect = make_intr(sc, h, ro, rd, __float_as_int(b.z));
+            woN = isect.wo;
+            if (leader) {
+                K.p[0] = isect.p.x; K.p[1] = isect.p.y; K.p[2] = isect.p.z;
+                K.pe[0] = isect.pError.x; K.pe[1] = isect.pError.y; K.pe[2] = isect.pError.z;
+                K.n[0] = isect.n.x; K.n[1] = isect.n.y; K.n[2] = isect.n.z;
+                K.ns[0] = isect.ns.x; K.ns[1] = isect.ns.y; K.ns[2] = isect.ns.z;
+                K.mIn = isect.mediumInside; K.mOut = isect.mediumOutside; K.rayMed = isect.rayMedium; K.hasIf = isect.hasInterface;
+            }
+            gbsdf.set_bsdf(isect.ns, isect.dpdu, ld3(sc.materials[isect.material].reflectance));
+            if (G > 0) gbsdf.init_region(sc, ro + h.t * rd, rd, isect.ns, W.P.lk[slot]);   // `v` was drawn by k_lookup
+            else { float v = rng.uniform(); gbsdf.init(sc, ro + h.t * rd, rd, isect.ns, v, lookups); }
+        }
         scatter_phase_sync<G>();
         bool emitShadow = false;
+        V3 nee_f; float nee_pdf = 0;
         if (ip.use_nee && gbsdf.non_specular()) {
-            V3 ctxP = offset_ray_origin(isect.p, isect.pError, isect.n, isect.wo);  // reflective-only BSDF (vspg.cpp:1147-1149)
-            V3 wo = isect.wo;
-            NeePre ls;
+            bool valid; V3 wi;
             if (G > 0) {   // drawn by k_lookup from these three sampler dimensions
-                ps.rng.uniform(); ps.rng.uniform(); ps.rng.uniform();
-                if (live) ls = nee_load(W.P, slot); else { ls.valid = false; ls.delta = false; ls.p_l = 0; }   // see k_volscatter
-                __syncwarp(grp_mask<G>());   // per-vertex branch: only this group's lanes are known to be here
-            } else ls = nee_presample(sc, ps.rng, ctxP, isect.ns), ps.rng.uniform(), ps.rng.uniform(), ps.rng.uniform();
-            {
-                if (ls.valid) {
-                    float p_l = ls.p_l;
-                    V3 f_hat = gbsdf.f(wo, ls.wi) * absdotn(ls.wi, isect.ns);
-                    float scatterPDF = 1.0f * gbsdf.pdf(wo, ls.wi);
-                    if (nonzero(f_hat)) {
-                        ShadowRec sr;
-                        spawn_ray_to(isect.p, isect.pError, isect.n, ls.pLight, ls.pLightErr, ls.nLight, &sr.o, &sr.d);
-                        sr.medium = isect.get_medium(sr.d);
-                        sr.f_hat = f_hat; sr.L = ls.L; sr.beta = ps.beta;
-                        sr.rl = ps.r_u * p_l; sr.ru = ps.r_u * scatterPDF;
-                        sr.pLight = ls.pLight; sr.pLightErr = ls.pLightErr; sr.nLight = ls.nLight;
-                        sr.delta = ls.delta; sr.channel = ps.fl.channel;
-                        if (leader && live) shadow_store(W.P, slot, sr);
-                        emitShadow = true;
-                    }
-                }
+                rng.uniform(); rng.uniform(); rng.uniform();
+                float4 r = live ? W.P.sh_rl[slot] : make_float4(0, 0, 0, 0);   // see k_volscatter
+                valid = __float_as_int(r.w) & 1; wi = V3(r.x, r.y, r.z);
+            } else {
+                V3 ctxP = offset_ray_origin(ld3(K.p), ld3(K.pe), ld3(K.n), woN);  // reflective-only BSDF (vspg.cpp:1147-1149)
+                NeePre ls = nee_presample(sc, rng, ctxP, ld3(K.ns));
+                rng.uniform(); rng.uniform(); rng.uniform();
+                nee_store(W.P, slot, ls);
+                valid = ls.valid; wi = ls.wi;
+            }
+            if (valid) {
+                nee_f = gbsdf.f(woN, wi) * absdotn(wi, gbsdf.frame.z);
+                nee_pdf = 1.0f * gbsdf.pdf(woN, wi);
+                emitShadow = nonzero(nee_f);
             }
         }
         scatter_phase_sync<G>();
-        ps.prevP = isect.p; ps.prevNs = isect.ns;
-        V3 wo = -ps.ray.d;
-        float u = ps.rng.uniform();
-        float u0 = ps.rng.uniform(), u1 = ps.rng.uniform();
-        ScatterSample bs = gbsdf.sample_f(wo, u, u0, u1, ps.rng);
-        bool alive = bs.valid;
-        if (alive) {
-            ps.fl.lastVertexVolume = false;
-            ps.rr_correction *= bs.pdf / bs.scatPdf;
-            V3 bsdfWeight = bs.f * absdotn(bs.wi, isect.ns) / bs.pdf;
-            ps.beta = ps.beta * bsdfWeight;
-            ps.r_l = ps.r_u / bs.misPdf;
-            ps.fl.specular = false; ps.fl.anyNonSpecular = true;
-            ps.ray.o = offset_ray_origin(isect.p, isect.pError, isect.n, bs.wi);
-            ps.ray.d = bs.wi;
-            ps.ray.medium = isect.get_medium(bs.wi);
-            if (leader && live) W.P.prev_o[slot] = make_float4(ps.ray.o.x, ps.ray.o.y, ps.ray.o.z, 0.f);
-            ps.vsp_next = gbsdf.vsp(bs.wi);
-            if (!nonzero(ps.beta)) alive = false;
-        }
-        if (alive) {
-            float survivalProb = 1.f;
-            if (ps.fl.depth > ip.min_rr_depth) {
-                const float etaScale = 1.f;  // no transmissive BxDFs on this path
-                V3 rrw = (ps.beta / avg3(ps.r_u)) * ps.rr_correction * etaScale;
-                survivalProb = ps.fl.specular ? 0.95f : fmaxf(0.f, fminf(1.f, max_comp(rrw)));
-            }
-            if (survivalProb < 1 && ps.fl.depth > ip.min_rr_depth) {
-                float q = fmaxf(0.f, 1 - survivalProb);
-                if (ps.rng.uniform() < q) alive = false;
-                else ps.beta = ps.beta / (1 - q);
-            }
+        float vspNext = 0;
+        ScatterSample bs;
+        {
+            float u = rng.uniform();
+            float u0 = rng.uniform(), u1 = rng.uniform();
+            bs = gbsdf.sample_f(-rd, u, u0, u1, rng);
+            if (bs.valid) vspNext = gbsdf.vsp(bs.wi);
         }
         scatter_phase_sync<G>();
         const bool w = leader && live;
+        bool alive = false;
         if (w) {
-            path_store(W.P, slot, ps);
-            if (emitShadow) shadows++;
+            const V3 ip_ = ld3(K.p), ipe = ld3(K.pe), in_ = ld3(K.n), ins = ld3(K.ns);
+            float4 c = W.P.beta_ru[slot], d = W.P.ru_rl[slot];
+            V3 beta(c.x, c.y, c.z), r_u(c.w, d.x, d.y);
+            const int flw = __float_as_int(W.P.d_med[slot].w);
+            if (emitShadow) {
+                // sh_pl / sh_ple / sh_ru.w and sh_c.xyz already hold the shadow record's values (see k_volscatter)
+                float4 lc = W.P.sh_c[slot], pl = W.P.sh_pl[slot], pe = W.P.sh_ple[slot], nr = W.P.sh_rl[slot];
+                const float nz = W.P.sh_ru[slot].w;
+                V3 so, sd;
+                spawn_ray_to(ip_, ipe, in_, V3(pl.x, pl.y, pl.z), V3(pe.x, pe.y, pe.z), V3(pl.w, pe.w, nz), &so, &sd);
+                const int smed = K.hasIf ? (dotn(sd, in_) > 0 ? K.mOut : K.mIn) : K.rayMed;   // isect.get_medium(sr.d)
+                const int delta = (__float_as_int(nr.w) >> 1) & 1, channel = (flw >> 8) & 3;
+                V3 rl = r_u * lc.w, ru = r_u * nee_pdf;
+                W.P.sh_o[slot] = make_float4(so.x, so.y, so.z, sd.x);
+                W.P.sh_d[slot] = make_float4(sd.y, sd.z, __int_as_float(smed), __int_as_float(delta | (channel << 8)));
+                W.P.sh_c[slot] = make_float4(lc.x, lc.y, lc.z, beta.x);
+                W.P.sh_rl[slot] = make_float4(rl.x, rl.y, rl.z, beta.y);
+                W.P.sh_f[slot] = make_float4(nee_f.x, nee_f.y, nee_f.z, beta.z);
+                W.P.sh_ru[slot] = make_float4(ru.x, ru.y, ru.z, nz);
+                shadows++;
+            }
+            alive = bs.valid;
+            if (alive) {
+                PathFlags fl = PathFlags::unpack(flw);
+                float4 f = W.P.misc[slot];
+                float rr_correction = f.x * (bs.pdf / bs.scatPdf);
+                V3 bsdfWeight = bs.f * absdotn(bs.wi, ins) / bs.pdf;
+                beta = beta * bsdfWeight;
+                V3 r_l = r_u / bs.misPdf;
+                fl.lastVertexVolume = false; fl.specular = false; fl.anyNonSpecular = true;
+                V3 no = offset_ray_origin(ip_, ipe, in_, bs.wi);
+                const int nmed = K.hasIf ? (dotn(bs.wi, in_) > 0 ? K.mOut : K.mIn) : K.rayMed;   // isect.get_medium(bs.wi)
+                if (!nonzero(beta)) alive = false;
+                if (alive) {
+                    float survivalProb = 1.f;
+                    if (fl.depth > ip.min_rr_depth) {
+                        const float etaScale = 1.f;  // no transmissive BxDFs on this path
+                        V3 rrw = (beta / avg3(r_u)) * rr_correction * etaScale;
+                        survivalProb = fl.specular ? 0.95f : fmaxf(0.f, fminf(1.f, max_comp(rrw)));
+                    }
+                    if (survivalProb < 1 && fl.depth > ip.min_rr_depth) {
+                        float q = fmaxf(0.f, 1 - survivalProb);
+                        if (rng.uniform() < q) alive = false;
+                        else beta = beta / (1 - q);
+                    }
+                }
+                if (alive) {
+                    float4 e = W.P.rl_L[slot], g2 = W.P.misc2[slot];
+                    W.P.o_dx[slot] = make_float4(no.x, no.y, no.z, bs.wi.x);
+                    W.P.d_med[slot] = make_float4(bs.wi.y, bs.wi.z, __int_as_float(nmed), __int_as_float(fl.pack()));
+                    W.P.beta_ru[slot] = make_float4(beta.x, beta.y, beta.z, r_u.x);
+                    W.P.ru_rl[slot] = make_float4(r_u.y, r_u.z, r_l.x, r_l.y);
+                    W.P.rl_L[slot] = make_float4(r_l.z, e.y, e.z, e.w);
+                    W.P.rng[slot] = make_ulonglong2(rng.state, rng.inc);
+                    W.P.misc[slot] = make_float4(rr_correction, vspNext, ip_.x, ip_.y);
+                    W.P.misc2[slot] = make_float4(ip_.z, g2.y, g2.z, g2.w);
+                    W.P.prev_ns[slot] = make_float4(ins.x, ins.y, ins.z, 0.f);
+                    W.P.prev_o[slot] = make_float4(no.x, no.y, no.z, 0.f);
+                }
+            }
         }
         queue_push(W.shadow, w && emitShadow, slot);
         queue_push(W.next, w && alive, slot);

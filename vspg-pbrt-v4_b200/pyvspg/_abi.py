@@ -7,7 +7,7 @@ import ctypes as C
 import os
 
 PKG_DIR = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
-LIB_PATH = os.path.join(PKG_DIR, "libvspg.so")
+LIB_PATH = os.environ.get("VSPG_LIB") or os.path.join(PKG_DIR, "libvspg.so")   # VSPG_LIB: A/B builds of the same ABI (tools/ab_run.py)
 
 VSPG_OK = 0
 ERR_INVALID, ERR_CUDA, ERR_IO, ERR_UNSUPPORTED, ERR_STATE = -1, -2, -3, -4, -5
