@@ -72,9 +72,9 @@ VD void sample_gaussian_filter(const DScene &sc, float u0, float u1, float *px, 
 }
 
 // cpu/integrators.cpp:272-334 EvaluatePixelSample (front half) + samplers.h:442-476, 797-814 + cameras.cpp:410-437
-VD void generate_camera_path(const DScene &sc, int px, int py, int sampleIndex, PathRegs &r) {
+VD void generate_camera_path(const DScene &sc, int seed, int px, int py, int sampleIndex, PathRegs &r) {
     const vspg_camera &c = sc.cam;
-    r.rng.set_sequence(hash_3u32((uint32_t)px, (uint32_t)py, (uint32_t)sc.seed));  // Hash(Point2i p, int seed)
+    r.rng.set_sequence(hash_3u32((uint32_t)px, (uint32_t)py, (uint32_t)seed));  // Hash(Point2i p, int seed)
     r.rng.advance((uint64_t)sampleIndex * 65536ull);
     float lu = r.rng.uniform();
     int ch = min((int)floorf(lu * 3), 2);  // util/spectrum.h:335-339 hero channel

@@ -95,7 +95,6 @@ struct DScene {
     // PixelFilter "gaussian" sampling table (host_util.h build_gaussian_filter); filt_nx == 0 for the box filter
     int filt_nx, filt_ny; const float *filt_f, *filt_cond_cdf, *filt_cond_int, *filt_marg_cdf; float filt_marg_int;
     vspg_integrator_params ip;
-    int seed;
 };
 
 // ------------------------------------------------------------------ wavefront state (SoA, one slot per path in flight)
@@ -155,13 +154,16 @@ struct PathFlags {
 
 struct Queue { int *items; int *count; };
 
+// Per-render arguments of vspg_render (window, sample-index range, sampler seed), uploaded before each render.
+struct RenderVars { unsigned long long total_samples; int x0, y0, x1, y1, spp_begin, spp_stride, n_spp, seed; };
+
 struct Wavefront {
     PathSoA P;
     int capacity;
     Queue active, next, medium, surface, shade, volscatter, shadow, done, medium_rs, vol8, vol16, vol32, sh8, sh16, sh32;
     unsigned long long *next_sample;   // regeneration cursor
-    unsigned long long total_samples;
-    int x0, y0, x1, y1, spp_begin, spp_stride, n_spp;
+    const RenderVars *rv;              // what changes from one render() to the next; in device memory so that the
+                                       // captured wave graph (vspg_ctx_render.inl) stays valid across renders
     double *film;                      // H*W*4
     unsigned long long *counters;      // vspg_counters layout (8 x u64)
     int *cursors;                      // per-kernel dynamic work cursors

@@ -20,11 +20,12 @@ VD bool regenerate(const DScene &sc, const Wavefront &W, int slot, PathRegs &r) 
     if (lane == leader) base = atomicAdd(W.next_sample, (unsigned long long)__popc(mask));
     base = __shfl_sync(mask, base, leader);
     unsigned long long id = base + __popc(mask & ((1u << lane) - 1));
-    if (id >= W.total_samples) return false;
-    const int w = W.x1 - W.x0, npix = w * (W.y1 - W.y0);
+    const RenderVars rv = *W.rv;
+    if (id >= rv.total_samples) return false;
+    const int w = rv.x1 - rv.x0, npix = w * (rv.y1 - rv.y0);
     int s = (int)(id / (unsigned long long)npix), pix = (int)(id % (unsigned long long)npix);
-    int px = W.x0 + pix % w, py = W.y0 + pix / w;
-    generate_camera_path(sc, px, py, W.spp_begin + s * W.spp_stride, r);
+    int px = rv.x0 + pix % w, py = rv.y0 + pix / w;
+    generate_camera_path(sc, rv.seed, px, py, rv.spp_begin + s * rv.spp_stride, r);
     path_store(W.P, slot, r);
     return true;
 }
@@ -190,7 +191,12 @@ template <int G> struct GroupIter {
         } else { first = blockIdx.x * blockDim.x; step = gstride(); warpOff = threadIdx.x; sub = 0; leader = true; }
     }
 };
-template <int G> VD void scatter_phase_sync() { if (G > 0) __syncthreads(); }
+#ifndef VSPG_SCATTER_SYNC
+#define VSPG_SCATTER_SYNC 1
+#endif
+template <int G> VD void scatter_phase_sync() {
+    if (G > 0) { if (VSPG_SCATTER_SYNC) __syncthreads(); else __syncwarp(); }
+}
 
 // ------------------------------------------------------------------ Field::getRegion for a whole stage queue
 // (field/Field.h:114-150; guiding.h:83-109 / 383-398 front half).  One THREAD per vertex: draws the sampler's `v`,

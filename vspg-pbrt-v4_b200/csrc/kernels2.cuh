@@ -213,8 +213,11 @@ __global__ void __launch_bounds__(G > 0 ? 256 : kBlock, G > 0 ? VSPG_SHADE_MINB 
 
 // ------------------------------------------------------------------ shadow rays (SampleLd back half, vspg.cpp:1193-1252)
 // GRAY: all media gray (see dmath.cuh G1) -- T_ray, r_l, r_u of the ratio tracker are scalars until the final weighting.
+#ifndef VSPG_SHADOW_MINB
+#define VSPG_SHADOW_MINB 8
+#endif
 template <bool GRAY>
-__global__ void __launch_bounds__(kBlock, 8) k_shadow(const DScene sc, const Wavefront W) {
+__global__ void __launch_bounds__(kBlock, VSPG_SHADOW_MINB) k_shadow(const DScene sc, const Wavefront W) {
     typedef typename SpecT<GRAY>::type Sp;
     const int n = *W.shadow.count;
     TrackCounters tc; tc.queries = 0; tc.dda = 0;
@@ -292,6 +295,12 @@ __global__ void __launch_bounds__(kBlock) k_finish(const DScene sc, const Wavefr
         queue_push(W.next, ok, slot);
     }
     counter_add(W.counters, CNT_PATHS, paths);
+}
+
+// Last node of the wave graph's loop body: counts the trip and keeps the WHILE node going while paths are in flight.
+__global__ void k_wave_condition(cudaGraphConditionalHandle handle, const int *activeCount, int *trips) {
+    *trips += 1;
+    cudaGraphSetConditional(handle, *activeCount > 0 ? 1u : 0u);
 }
 
 __global__ void k_reset_counts(int *counts, int n, int keep) {

@@ -146,6 +146,9 @@ VD void rs_finalize(const DScene &sc, const Wavefront &W, RsLane<GRAY> &s) {
     queue_push(W.surface, !dead && !scat, slot);
 }
 
+#ifndef VSPG_RS_MINB
+#define VSPG_RS_MINB 5                    // resident CTAs/SM of the gray resampling kernel's default build (A/B knob)
+#endif
 constexpr int kRsRefillIdleDefault = 12;    // fetch new rays once this many lanes of the warp are idle (kernel argument: VSPG_RS_REFILL for A/B runs)
 constexpr int kRsTripsPerCheck = 4; // collisions between two refill checks
 constexpr int kRsSearchMax = 4;     // search steps before the collision body runs for the lanes that are ready

@@ -39,7 +39,13 @@ struct vspg_ctx {
     Queue phys_q[2]{};            // the two ping-pong path queues (roles swap each wave iteration)
     int capacity = 0, requested_capacity = 0;
     int *qcounts = nullptr;       // device: 8 queue counters
-    int *h_pinned = nullptr;      // pinned readback
+    int *h_pinned = nullptr;      // pinned readback (int[0]) + RenderVars staging (from int[4])
+    RenderVars *d_rv = nullptr;   // per-render variables the kernels read through Wavefront::rv
+    int *d_iters = nullptr;       // trips of the wave graph's WHILE node in the current render
+    bool use_graph = true;        // device-driven wave loop (VSPG_GRAPH=0: host-driven loop)
+    cudaGraph_t wave_graph = nullptr; cudaGraphExec_t wave_exec = nullptr; struct WaveGraphKey *wave_key = nullptr;
+    cudaStream_t cap_stream = nullptr;
+    unsigned graph_builds = 0;
     const void *cells_ptr = nullptr; size_t cells_bytes = 0;      // cell-record grid of the (first) uniformgrid medium
     size_t l2_persist_bytes = 0, l2_window_max = 0;               // persisting-L2 carve-out granted by the device (0 = off)
     double *film = nullptr;
@@ -158,6 +164,7 @@ int vspg_create(vspg_ctx **out, int device_ordinal) {
         }
     }
     if (const char *rr = getenv("VSPG_RS_REFILL")) { int v = atoi(rr); if (v >= 1 && v <= 32) ctx->rs_refill = v; }
+    if (const char *g = getenv("VSPG_GRAPH")) ctx->use_graph = atoi(g) != 0;
     if (const char *ro = getenv("VSPG_RS_OCC")) { int v = atoi(ro); if (v == 4 || v == 5) ctx->rs_occ = v; }
     const char *lay = getenv("VSPG_GRID_LAYOUT");
     if (lay && std::string(lay) == "linear") ctx->grid_layout = GRID_LINEAR;
@@ -169,6 +176,10 @@ void vspg_destroy(vspg_ctx *ctx) {
     if (!ctx) return;
     cudaSetDevice(ctx->device);
     dev_release(ctx, ctx->scene_allocs); dev_release(ctx, ctx->guide_allocs); dev_trim(ctx); free_all(ctx->wf_allocs);
+    if (ctx->wave_exec) cudaGraphExecDestroy(ctx->wave_exec);
+    if (ctx->wave_graph) cudaGraphDestroy(ctx->wave_graph);
+    if (ctx->cap_stream) cudaStreamDestroy(ctx->cap_stream);
+    free(ctx->wave_key);
     if (ctx->h_pinned) cudaFreeHost(ctx->h_pinned);
     if (ctx->film) cudaFree(ctx->film);
     if (ctx->tr_acc) cudaFree(ctx->tr_acc);

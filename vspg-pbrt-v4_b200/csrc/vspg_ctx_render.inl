@@ -4,6 +4,9 @@
 enum { Q_A = 0, Q_B = 1, Q_MEDIUM = 2, Q_SURFACE = 3, Q_SHADE = 4, Q_VOLSCATTER = 5, Q_SHADOW = 6, Q_DONE = 7, Q_MEDIUM_RS = 8, Q_VOL8 = 9, Q_VOL16 = 10, Q_VOL32 = 11, Q_SH8 = 12, Q_SH16 = 13, Q_SH32 = 14, Q_COUNT = 15,
        Q_CURSORS = 4, Q_INTS = Q_COUNT + Q_CURSORS };  // + per-kernel dynamic work cursors
 
+// Everything the captured wave graph depends on; compared bytewise against the current values before each replay.
+struct WaveGraphKey { DScene sc; Wavefront W; int vgrid, sgrid, sblock, rs_refill, rs_occ, nGridWin; cudaAccessPolicyWindow win; };
+
 static int ensure_wavefront(vspg_ctx *ctx, unsigned long long total) {
     // Default: up to 16.8 M paths in flight (5.7 GB of the 180 GB).  Measured on C2 (profiles/r01z_summary.md, r02b/c): 2 M ->
     // 131.9, 4 M -> 137.1, 8 M -> 142.9, 16.8 M -> 147.0 Mpaths/s -- fewer, larger and more coherent waves.
@@ -35,7 +38,10 @@ static int ensure_wavefront(vspg_ctx *ctx, unsigned long long total) {
     for (int i = 0; i < Q_COUNT; i++) { qs[i]->items = items + (size_t)i * n; qs[i]->count = ctx->qcounts + i; }
     ctx->phys_q[0] = ctx->W.active; ctx->phys_q[1] = ctx->W.next;
     CK(alloc((void **)&ctx->W.next_sample, sizeof(unsigned long long)));
-    if (!ctx->h_pinned) CK(cudaMallocHost((void **)&ctx->h_pinned, 64));
+    CK(alloc((void **)&ctx->d_rv, sizeof(RenderVars)));
+    CK(alloc((void **)&ctx->d_iters, sizeof(int)));
+    ctx->W.rv = ctx->d_rv;
+    if (!ctx->h_pinned) CK(cudaMallocHost((void **)&ctx->h_pinned, 128));
     ctx->capacity = want;
     ctx->W.capacity = want;
     return VSPG_OK;
@@ -69,14 +75,19 @@ int vspg_render(vspg_ctx *ctx, int spp_begin, int spp_end, int spp_stride, int x
     if (rc != VSPG_OK) return rc;
     cudaStream_t st = (cudaStream_t)cuda_stream;
     Wavefront &W = ctx->W;
-    W.total_samples = total; W.x0 = x0; W.y0 = y0; W.x1 = x1; W.y1 = y1; W.spp_begin = spp_begin; W.spp_stride = spp_stride; W.n_spp = nspp;
     W.film = ctx->film; W.counters = ctx->counters;
-    ctx->sc.seed = seed;
     const DScene sc = ctx->sc;
     Queue qa = ctx->phys_q[0], qb = ctx->phys_q[1];   // physical queues 0 and 1; roles swap each iteration
+    // what changes from render to render goes through device memory (RenderVars): kernel arguments stay the same, so
+    // the captured wave graph below can be replayed
+    {
+        RenderVars *hv = reinterpret_cast<RenderVars *>(ctx->h_pinned + 4);
+        hv->total_samples = total; hv->x0 = x0; hv->y0 = y0; hv->x1 = x1; hv->y1 = y1;
+        hv->spp_begin = spp_begin; hv->spp_stride = spp_stride; hv->n_spp = nspp; hv->seed = seed;
+        CK(cudaMemcpyAsync(ctx->d_rv, hv, sizeof(RenderVars), cudaMemcpyHostToDevice, st));
+    }
     CK(cudaMemsetAsync(ctx->qcounts, 0, Q_INTS * sizeof(int), st));
     CK(cudaMemsetAsync(W.next_sample, 0, sizeof(unsigned long long), st));
-    const int grid = ctx->sm_count * 8;
     // lane-group scatter kernels (kernels.cuh GroupIter): persistent grids of exactly the CTAs one wave of the device holds
     const int sblock = ctx->scatter_block;
     if (ctx->scatter_ctas_block != sblock) {
@@ -95,15 +106,6 @@ int vspg_render(vspg_ctx *ctx, int spp_begin, int spp_end, int spp_stride, int x
         for (auto &e : ctx->ev) CK(cudaEventCreate(&e));
     cudaEvent_t evStart = nullptr, evStop = nullptr;
     if (timing) { CK(cudaEventCreate(&evStart)); CK(cudaEventCreate(&evStop)); CK(cudaEventRecord(evStart, st)); }
-    k_generate<<<grid, kBlock, 0, st>>>(sc, W, nslots);
-    ctx->launches++; ctx->launches_kernel[VSPG_K_GENERATE]++;
-    if (timing) {
-        CK(cudaEventRecord(ctx->ev[0], st)); CK(cudaEventSynchronize(ctx->ev[0]));
-        float ms = 0; CK(cudaEventElapsedTime(&ms, evStart, ctx->ev[0])); ctx->ms_kernel[VSPG_K_GENERATE] += ms;
-    }
-    // The tracking kernels gather from the cell-record grid at random while the path state streams through L2: give the
-    // grid a persisting access-policy window (per launch, so it does not depend on which stream the caller passed) and
-    // let everything else those kernels touch be streaming.  Opt-in (VSPG_L2_PERSIST=1 or =<MiB>): a net loss on C2, see vspg_create.
     // Grid-stride kernels get exactly one resident wave: sm_count x (CTAs of kBlock threads that fit one SM).  A fixed 8
     // CTAs/SM left k_surface (5 resident) and k_intersect / k_lookup (6 resident) with a partial second wave.
     if (!ctx->grids_ready) {
@@ -118,6 +120,15 @@ int vspg_render(vspg_ctx *ctx, int spp_begin, int spp_end, int spp_stride, int x
         ctx->g_surface = ctx->sm_count * 8;   // memory-latency bound with very uneven items: measured better oversubscribed (16.8 vs 18.8 ms)
         ctx->grids_ready = true;
     }
+    k_generate<<<ctx->g_generate, kBlock, 0, st>>>(sc, W, nslots);
+    ctx->launches++; ctx->launches_kernel[VSPG_K_GENERATE]++;
+    if (timing) {
+        CK(cudaEventRecord(ctx->ev[0], st)); CK(cudaEventSynchronize(ctx->ev[0]));
+        float ms = 0; CK(cudaEventElapsedTime(&ms, evStart, ctx->ev[0])); ctx->ms_kernel[VSPG_K_GENERATE] += ms;
+    }
+    // The tracking kernels gather from the cell-record grid at random while the path state streams through L2: give the
+    // grid a persisting access-policy window (per launch, so it does not depend on which stream the caller passed) and
+    // let everything else those kernels touch be streaming.  Opt-in (VSPG_L2_PERSIST=1 or =<MiB>): a net loss on C2, see vspg_create.
     cudaLaunchAttribute gridWin[1];
     int nGridWin = 0;
     if (ctx->cells_bytes && ctx->l2_persist_bytes) {
@@ -129,55 +140,109 @@ int vspg_render(vspg_ctx *ctx, int spp_begin, int spp_end, int spp_stride, int x
         w.hitProp = cudaAccessPropertyPersisting; w.missProp = cudaAccessPropertyStreaming;
         nGridWin = 1;
     }
-    auto launch_tracking = [&](auto kernel, int nblocks, auto... args) {
-        cudaLaunchConfig_t cfg = {};
-        cfg.gridDim = dim3(nblocks); cfg.blockDim = dim3(kBlock); cfg.dynamicSmemBytes = 0; cfg.stream = st;
-        cfg.attrs = gridWin; cfg.numAttrs = nGridWin;
-        return cudaLaunchKernelEx(&cfg, kernel, args...);
-    };
-    int cur = 0;  // physical index of the active queue
-#define VSPG_STAGE(K, launch) do { launch; ctx->launches_kernel[K]++; if (timing) CK(cudaEventRecord(ctx->ev[K], st)); } while (0)
-    while (true) {
-        if (timing) CK(cudaEventRecord(ctx->ev[0], st));
-        VSPG_STAGE(VSPG_K_INTERSECT, (k_intersect<<<ctx->g_intersect, kBlock, 0, st>>>(sc, W)));
-        if (ctx->all_gray && ctx->rs_occ == 5) CK(launch_tracking(k_medium_rs<true, 5>, ctx->sm_count * 5, sc, W, ctx->qcounts + Q_COUNT, ctx->rs_refill));
-        else if (ctx->all_gray) CK(launch_tracking(k_medium_rs<true, 4>, ctx->sm_count * 4, sc, W, ctx->qcounts + Q_COUNT, ctx->rs_refill));
-        else CK(launch_tracking(k_medium_rs<false, 4>, ctx->sm_count * 4, sc, W, ctx->qcounts + Q_COUNT, ctx->rs_refill));
-        VSPG_STAGE(VSPG_K_MEDIUM, (k_medium<<<ctx->g_medium, kBlock, 0, st>>>(sc, W)));
+    // One wave iteration = the stage kernels below, in stream order, over the queues of `Wh`; afterwards every counter but
+    // the new active queue's (`keep`) is cleared.  `timed` brackets each stage with events (stage-split measurements only).
+    const int perIter = 9 + (guidedVol ? 3 : 0) + (guidedSurf ? 3 : 0);
+    auto enqueue_iteration = [&](const Wavefront &Wh, int keep, cudaStream_t s, bool timed) -> int {
+        auto launch_tracking = [&](auto kernel, int nblocks, auto... args) {
+            cudaLaunchConfig_t cfg = {};
+            cfg.gridDim = dim3(nblocks); cfg.blockDim = dim3(kBlock); cfg.dynamicSmemBytes = 0; cfg.stream = s;
+            cfg.attrs = gridWin; cfg.numAttrs = nGridWin;
+            return cudaLaunchKernelEx(&cfg, kernel, args...);
+        };
+#define VSPG_STAGE(K, launch) do { launch; if (timed) { ctx->launches_kernel[K]++; CK(cudaEventRecord(ctx->ev[K], s)); } } while (0)
+        if (timed) CK(cudaEventRecord(ctx->ev[0], s));
+        VSPG_STAGE(VSPG_K_INTERSECT, (k_intersect<<<ctx->g_intersect, kBlock, 0, s>>>(sc, Wh)));
+        if (ctx->all_gray && ctx->rs_occ == 5) CK(launch_tracking(k_medium_rs<true, VSPG_RS_MINB>, ctx->sm_count * VSPG_RS_MINB, sc, Wh, ctx->qcounts + Q_COUNT, ctx->rs_refill));
+        else if (ctx->all_gray) CK(launch_tracking(k_medium_rs<true, 4>, ctx->sm_count * 4, sc, Wh, ctx->qcounts + Q_COUNT, ctx->rs_refill));
+        else CK(launch_tracking(k_medium_rs<false, 4>, ctx->sm_count * 4, sc, Wh, ctx->qcounts + Q_COUNT, ctx->rs_refill));
+        VSPG_STAGE(VSPG_K_MEDIUM, (k_medium<<<ctx->g_medium, kBlock, 0, s>>>(sc, Wh)));
         if (guidedVol) {
-            k_lookup<false><<<ctx->g_lookup0, kBlock, 0, st>>>(sc, W, W.volscatter, W.vol8, W.vol16, W.vol32);
-            k_volscatter<8><<<vgrid, sblock, 0, st>>>(sc, W, W.vol8);
-            k_volscatter<16><<<vgrid, sblock, 0, st>>>(sc, W, W.vol16);
-            VSPG_STAGE(VSPG_K_VOLSCATTER, (k_volscatter<32><<<vgrid, sblock, 0, st>>>(sc, W, W.vol32)));
-            ctx->launches += 3;
-        } else VSPG_STAGE(VSPG_K_VOLSCATTER, (k_volscatter<0><<<ctx->g_volscatter0, kBlock, 0, st>>>(sc, W, W.volscatter)));
-        VSPG_STAGE(VSPG_K_SURFACE, (k_surface<<<ctx->g_surface, kBlock, 0, st>>>(sc, W)));
+            k_lookup<false><<<ctx->g_lookup0, kBlock, 0, s>>>(sc, Wh, Wh.volscatter, Wh.vol8, Wh.vol16, Wh.vol32);
+            k_volscatter<8><<<vgrid, sblock, 0, s>>>(sc, Wh, Wh.vol8);
+            k_volscatter<16><<<vgrid, sblock, 0, s>>>(sc, Wh, Wh.vol16);
+            VSPG_STAGE(VSPG_K_VOLSCATTER, (k_volscatter<32><<<vgrid, sblock, 0, s>>>(sc, Wh, Wh.vol32)));
+        } else VSPG_STAGE(VSPG_K_VOLSCATTER, (k_volscatter<0><<<ctx->g_volscatter0, kBlock, 0, s>>>(sc, Wh, Wh.volscatter)));
+        VSPG_STAGE(VSPG_K_SURFACE, (k_surface<<<ctx->g_surface, kBlock, 0, s>>>(sc, Wh)));
         if (guidedSurf) {
-            k_lookup<true><<<ctx->g_lookup1, kBlock, 0, st>>>(sc, W, W.shade, W.sh8, W.sh16, W.sh32);
-            k_shade<8><<<sgrid, sblock, 0, st>>>(sc, W, W.sh8);
-            k_shade<16><<<sgrid, sblock, 0, st>>>(sc, W, W.sh16);
-            VSPG_STAGE(VSPG_K_SHADE, (k_shade<32><<<sgrid, sblock, 0, st>>>(sc, W, W.sh32)));
-            ctx->launches += 3;
-        } else VSPG_STAGE(VSPG_K_SHADE, (k_shade<0><<<ctx->g_shade0, kBlock, 0, st>>>(sc, W, W.shade)));
-        if (ctx->all_gray) VSPG_STAGE(VSPG_K_SHADOW, CK(launch_tracking(k_shadow<true>, ctx->g_shadow_gray, sc, W)));
-        else VSPG_STAGE(VSPG_K_SHADOW, CK(launch_tracking(k_shadow<false>, ctx->g_shadow_rgb, sc, W)));
-        VSPG_STAGE(VSPG_K_FINISH, (k_finish<<<ctx->g_finish, kBlock, 0, st>>>(sc, W)));
-        ctx->launches += 8; ctx->iterations++;
-        // swap roles: next becomes active; clear every other counter
-        cur ^= 1;
-        Queue t = W.active; W.active = W.next; W.next = t;
-        CK(cudaMemcpyAsync(ctx->h_pinned, W.active.count, sizeof(int), cudaMemcpyDeviceToHost, st));
-        k_reset_counts<<<1, 32, 0, st>>>(ctx->qcounts, Q_INTS, cur);
-        ctx->launches++;
-        CK(cudaStreamSynchronize(st));
-        if (timing)
-            for (int k = VSPG_K_INTERSECT; k < VSPG_K_COUNT; k++) {
-                float ms = 0; CK(cudaEventElapsedTime(&ms, ctx->ev[k == VSPG_K_INTERSECT ? 0 : k - 1], ctx->ev[k]));
-                ctx->ms_kernel[k] += ms;
-            }
-        if (ctx->h_pinned[0] == 0) break;
-    }
+            k_lookup<true><<<ctx->g_lookup1, kBlock, 0, s>>>(sc, Wh, Wh.shade, Wh.sh8, Wh.sh16, Wh.sh32);
+            k_shade<8><<<sgrid, sblock, 0, s>>>(sc, Wh, Wh.sh8);
+            k_shade<16><<<sgrid, sblock, 0, s>>>(sc, Wh, Wh.sh16);
+            VSPG_STAGE(VSPG_K_SHADE, (k_shade<32><<<sgrid, sblock, 0, s>>>(sc, Wh, Wh.sh32)));
+        } else VSPG_STAGE(VSPG_K_SHADE, (k_shade<0><<<ctx->g_shade0, kBlock, 0, s>>>(sc, Wh, Wh.shade)));
+        if (ctx->all_gray) VSPG_STAGE(VSPG_K_SHADOW, CK(launch_tracking(k_shadow<true>, ctx->g_shadow_gray, sc, Wh)));
+        else VSPG_STAGE(VSPG_K_SHADOW, CK(launch_tracking(k_shadow<false>, ctx->g_shadow_rgb, sc, Wh)));
+        VSPG_STAGE(VSPG_K_FINISH, (k_finish<<<ctx->g_finish, kBlock, 0, s>>>(sc, Wh)));
+        k_reset_counts<<<1, 32, 0, s>>>(ctx->qcounts, Q_INTS, keep);
 #undef VSPG_STAGE
+        return VSPG_OK;
+    };
+    Wavefront Wab = W, Wba = W;            // iteration with (active, next) = (A, B) and the one with the roles swapped
+    Wba.active = qb; Wba.next = qa;
+    unsigned iterations = 0;
+    if (timing || !ctx->use_graph) {
+        // host-driven loop: one stream sync + counter read per iteration (stage-split measurements, VSPG_GRAPH=0)
+        for (int cur = 0;; cur ^= 1) {
+            int rc2 = enqueue_iteration(cur ? Wba : Wab, cur ^ 1, st, timing);
+            if (rc2 != VSPG_OK) return rc2;
+            iterations++;
+            CK(cudaMemcpyAsync(ctx->h_pinned, ctx->phys_q[cur ^ 1].count, sizeof(int), cudaMemcpyDeviceToHost, st));
+            CK(cudaStreamSynchronize(st));
+            if (timing)
+                for (int k = VSPG_K_INTERSECT; k < VSPG_K_COUNT; k++) {
+                    float ms = 0; CK(cudaEventElapsedTime(&ms, ctx->ev[k == VSPG_K_INTERSECT ? 0 : k - 1], ctx->ev[k]));
+                    ctx->ms_kernel[k] += ms;
+                }
+            if (ctx->h_pinned[0] == 0) break;
+        }
+    } else {
+        // Device-driven loop: a CUDA graph whose WHILE node repeats {iteration A->B, iteration B->A} until the active queue
+        // is empty -- no host round trip between waves.  The graph only depends on kernel arguments (scene, queues, grids),
+        // all of which are compared below; it is rebuilt when any of them changed.
+        WaveGraphKey key;
+        memset(&key, 0, sizeof key);
+        key.sc = sc; key.W = Wab; key.vgrid = vgrid; key.sgrid = sgrid; key.sblock = sblock; key.rs_refill = ctx->rs_refill; key.rs_occ = ctx->rs_occ;
+        key.nGridWin = nGridWin; if (nGridWin) key.win = gridWin[0].val.accessPolicyWindow;
+        if (!ctx->wave_exec || memcmp(&key, ctx->wave_key, sizeof key) != 0) {
+            if (ctx->wave_exec) { cudaGraphExecDestroy(ctx->wave_exec); ctx->wave_exec = nullptr; }
+            if (ctx->wave_graph) { cudaGraphDestroy(ctx->wave_graph); ctx->wave_graph = nullptr; }
+            if (!ctx->cap_stream) CK(cudaStreamCreateWithFlags(&ctx->cap_stream, cudaStreamNonBlocking));
+            CK(cudaGraphCreate(&ctx->wave_graph, 0));
+            cudaGraphConditionalHandle handle;
+            CK(cudaGraphConditionalHandleCreate(&handle, ctx->wave_graph, 1, cudaGraphCondAssignDefault));
+            cudaGraphNodeParams np = {};
+            np.type = cudaGraphNodeTypeConditional;
+            np.conditional.handle = handle; np.conditional.type = cudaGraphCondTypeWhile; np.conditional.size = 1;
+            cudaGraphNode_t whileNode;
+            CK(cudaGraphAddNode(&whileNode, ctx->wave_graph, nullptr, 0, &np));
+            cudaGraph_t body = np.conditional.phGraph_out[0];
+            CK(cudaStreamBeginCaptureToGraph(ctx->cap_stream, body, nullptr, nullptr, 0, cudaStreamCaptureModeRelaxed));
+            int rc2 = enqueue_iteration(Wab, 1, ctx->cap_stream, false);
+            if (rc2 == VSPG_OK) rc2 = enqueue_iteration(Wba, 0, ctx->cap_stream, false);
+            if (rc2 == VSPG_OK) k_wave_condition<<<1, 1, 0, ctx->cap_stream>>>(handle, qa.count, ctx->d_iters);
+            cudaGraph_t captured = nullptr;
+            cudaError_t ce = cudaStreamEndCapture(ctx->cap_stream, &captured);
+            if (rc2 != VSPG_OK) return rc2;
+            CK(ce);
+            CK(cudaGraphInstantiate(&ctx->wave_exec, ctx->wave_graph, 0));
+            if (!ctx->wave_key) ctx->wave_key = (WaveGraphKey *)malloc(sizeof(WaveGraphKey));
+            memcpy(ctx->wave_key, &key, sizeof key);
+            ctx->graph_builds++;
+            if (getenv("VSPG_VERBOSE")) fprintf(stderr, "vspg: wave graph built (#%u)\n", ctx->graph_builds);
+        }
+        CK(cudaMemsetAsync(ctx->d_iters, 0, sizeof(int), st));
+        CK(cudaGraphLaunch(ctx->wave_exec, st));
+        CK(cudaMemcpyAsync(ctx->h_pinned, ctx->d_iters, sizeof(int), cudaMemcpyDeviceToHost, st));
+        CK(cudaStreamSynchronize(st));
+        iterations = 2u * (unsigned)ctx->h_pinned[0];
+    }
+    ctx->iterations += iterations;
+    ctx->launches += (unsigned long long)iterations * perIter;
+    if (!timing) {   // launch bookkeeping per stage (the timed path counts inside VSPG_STAGE)
+        const unsigned it = iterations;
+        ctx->launches_kernel[VSPG_K_INTERSECT] += it; ctx->launches_kernel[VSPG_K_MEDIUM] += it; ctx->launches_kernel[VSPG_K_VOLSCATTER] += it;
+        ctx->launches_kernel[VSPG_K_SURFACE] += it; ctx->launches_kernel[VSPG_K_SHADE] += it; ctx->launches_kernel[VSPG_K_SHADOW] += it; ctx->launches_kernel[VSPG_K_FINISH] += it;
+    }
     if (timing) {
         CK(cudaEventRecord(evStop, st)); CK(cudaEventSynchronize(evStop));
         float ms = 0; CK(cudaEventElapsedTime(&ms, evStart, evStop));
