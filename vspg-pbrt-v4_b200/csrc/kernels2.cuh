@@ -6,15 +6,37 @@
 namespace vspg {
 
 // ------------------------------------------------------------------ escape / emission / interface (vspg.cpp:353-446)
-__global__ void __launch_bounds__(kBlock, 5) k_surface(const DScene sc, const Wavefront W) {
+#ifndef VSPG_SURFACE_MINB
+#define VSPG_SURFACE_MINB 8
+#endif
+// Streams are touched per branch (profiles/r02n: a whole-record load/store moved 2.9 GB per launch for a kernel that
+// mostly re-spawns rays at interfaces): the hit, the ray and the flags always; throughput / MIS weights / radiance only
+// where light is picked up.
+__global__ void __launch_bounds__(kBlock, VSPG_SURFACE_MINB) k_surface(const DScene sc, const Wavefront W) {
     const int n = *W.surface.count;
     const vspg_integrator_params &ip = sc.ip;
     for (int i = gtid(); i < n; i += gstride()) {
-        int slot = W.surface.items[i];
-        PathRegs ps; path_load(W.P, slot, ps);
-        float4 hr = W.P.hit[slot];
+        const int slot = W.surface.items[i];
+        const float4 hr = W.P.hit[slot];
+        float4 b = W.P.d_med[slot];
         Hit h; h.t = hr.x; h.u = hr.y; h.v = hr.z; h.prim = __float_as_int(hr.w);
+        PathFlags fl = PathFlags::unpack(__float_as_int(b.w));
         bool toDone = false, toNext = false, toShade = false;
+        // radiance pick-up: L += beta * Le / avg(r_u) on camera / specular vertices, else the MIS-weighted form
+        auto add_emission = [&](V3 Le, auto lightPdfOf) {
+            float4 c = W.P.beta_ru[slot], d = W.P.ru_rl[slot], e = W.P.rl_L[slot];
+            V3 beta(c.x, c.y, c.z), r_u(c.w, d.x, d.y), r_l(d.z, d.w, e.x), L(e.y, e.z, e.w);
+            if (fl.depth == 0 || fl.specular) L = L + beta * Le / avg3(r_u);
+            else {
+                float4 f = W.P.misc[slot], g = W.P.misc2[slot], pn = W.P.prev_ns[slot];
+                float lightPDF = lightPdfOf(V3(f.z, f.w, g.x), V3(pn.x, pn.y, pn.z));
+                r_l = r_l * lightPDF;
+                float w_l = ip.use_nee ? 1.0f / avg3(r_u + r_l) : 1.0f;
+                L = L + beta * w_l * Le;
+            }
+            W.P.ru_rl[slot] = make_float4(d.x, d.y, r_l.x, r_l.y);
+            W.P.rl_L[slot] = make_float4(r_l.z, L.x, L.y, L.z);
+        };
         if (h.prim < 0) {
             // infiniteLights = LightType::Infinite and LightType::DeltaDirection lights in this fork (cpu/integrators.h:77-81);
             // DistantLight::Le = scale * Lemit (lights.h:290-293), zeroed beyond depth 0 (vspg.cpp:356-358);
@@ -22,41 +44,36 @@ __global__ void __launch_bounds__(kBlock, 5) k_surface(const DScene sc, const Wa
             for (int k = 0; k < sc.n_inf_lights; k++) {
                 int li = sc.inf_lights[k];
                 V3 Le = ld3(sc.lights[li].L);
-                if (sc.lights[li].type == VSPG_LIGHT_DISTANT && ps.fl.depth != 0) Le = V3();
-                if (ps.fl.depth == 0 || ps.fl.specular) ps.L = ps.L + ps.beta * Le / avg3(ps.r_u);
-                else {
-                    float lightPDF = light_pmf(sc, li, ps.prevP, ps.prevNs) * 0.f;
-                    ps.r_l = ps.r_l * lightPDF;
-                    float w_b = ip.use_nee ? 1.0f / avg3(ps.r_u + ps.r_l) : 1.f;
-                    ps.L = ps.L + ps.beta * w_b * Le;
-                }
+                if (sc.lights[li].type == VSPG_LIGHT_DISTANT && fl.depth != 0) Le = V3();
+                add_emission(Le, [&](V3 prevP, V3 prevNs) { return light_pmf(sc, li, prevP, prevNs) * 0.f; });
             }
             toDone = true;
         } else {
-            SurfaceIntr isect = make_intr(sc, h, ps.ray.o, ps.ray.d, ps.ray.medium);
+            const float4 a = W.P.o_dx[slot];
+            const V3 ro(a.x, a.y, a.z), rd(a.w, b.x, b.y);
+            SurfaceIntr isect = make_intr(sc, h, ro, rd, __float_as_int(b.z));
             if (isect.areaLight >= 0) {
-                V3 Le = area_L(sc.lights[isect.areaLight], isect.n, -ps.ray.d);
-                if (nonzero(Le)) {
-                    if (ps.fl.depth == 0 || ps.fl.specular) ps.L = ps.L + ps.beta * Le / avg3(ps.r_u);
-                    else {
-                        V3 spawnO = ps.prevP;   // medium vertex: ctx.pi is exact and n = 0, SpawnRay starts at p
-                        if (nonzero(ps.prevNs)) { float4 po = W.P.prev_o[slot]; spawnO = V3(po.x, po.y, po.z); }
-                        float lightPDF = light_pmf(sc, isect.areaLight, ps.prevP, ps.prevNs) * area_pdf_li(sc, isect.areaLight, ps.prevP, ps.prevNs, ps.ray.d, spawnO);
-                        ps.r_l = ps.r_l * lightPDF;
-                        float w_l = ip.use_nee ? 1.0f / avg3(ps.r_u + ps.r_l) : 1.0f;
-                        ps.L = ps.L + ps.beta * w_l * Le;
-                    }
-                }
+                V3 Le = area_L(sc.lights[isect.areaLight], isect.n, -rd);
+                if (nonzero(Le))
+                    add_emission(Le, [&](V3 prevP, V3 prevNs) {
+                        V3 spawnO = prevP;   // medium vertex: ctx.pi is exact and n = 0, SpawnRay starts at p
+                        if (nonzero(prevNs)) { float4 po = W.P.prev_o[slot]; spawnO = V3(po.x, po.y, po.z); }
+                        return light_pmf(sc, isect.areaLight, prevP, prevNs) * area_pdf_li(sc, isect.areaLight, prevP, prevNs, rd, spawnO);
+                    });
             }
             if (isect.material < 0) {  // interface material: SkipIntersection (interaction.cpp:91-97)
-                V3 d = ps.ray.d;
-                ps.ray.o = offset_ray_origin(isect.p, isect.pError, isect.n, d);
-                ps.ray.medium = isect.get_medium(d);
+                V3 o = offset_ray_origin(isect.p, isect.pError, isect.n, rd);
+                W.P.o_dx[slot] = make_float4(o.x, o.y, o.z, a.w);
+                b.z = __int_as_float(isect.get_medium(rd));
+                W.P.d_med[slot] = b;
                 toNext = true;
-            } else if (ps.fl.depth++ >= ip.max_depth) toDone = true;
-            else toShade = true;
+            } else if (fl.depth++ >= ip.max_depth) toDone = true;
+            else {
+                b.w = __int_as_float(fl.pack());
+                W.P.d_med[slot] = b;
+                toShade = true;
+            }
         }
-        path_store(W.P, slot, ps);
         queue_push(W.done, toDone, slot);
         queue_push(W.next, toNext, slot);
         queue_push(W.shade, toShade, slot);
@@ -216,60 +233,68 @@ __global__ void __launch_bounds__(G > 0 ? 256 : kBlock, G > 0 ? VSPG_SHADE_MINB 
 #ifndef VSPG_SHADOW_MINB
 #define VSPG_SHADOW_MINB 8
 #endif
+// One shadow ray: the chain of segments through interface surfaces towards the light point with ratio tracking + Russian
+// roulette in every medium segment.  Returns false when the ray is blocked / its transmittance was terminated; else *Ld is
+// beta * (f_hat * T_ray * L / avg(MIS weights)).
+template <bool GRAY>
+VD bool shadow_trace(const DScene &sc, const ShadowRec &sr, TrackCounters &tc, unsigned &nodes, V3 *Ld) {
+    typedef typename SpecT<GRAY>::type Sp;
+    const int ch = sr.channel;
+    Ray lightRay; lightRay.o = sr.o; lightRay.d = sr.d; lightRay.medium = sr.medium;
+    Sp T_ray = to_spec<GRAY>(splat(1.f)), r_l = T_ray, r_u = T_ray;
+    Rng rng; rng.set_sequence(hash_v3(lightRay.o), hash_v3(lightRay.d));
+    while (!(lightRay.d == V3(0, 0, 0))) {
+        Hit h = scene_intersect(sc, lightRay.o, lightRay.d, 1 - kShadowEpsilon, nodes);
+        if (h.prim >= 0 && sc.quads[h.prim].material >= 0) return false;
+        if (lightRay.medium >= 0) {
+            float tMax = h.prim >= 0 ? h.t : (1 - kShadowEpsilon);
+            float uu = rng.uniform();
+            Ray tr = lightRay;
+            tMax *= length(tr.d);
+            tr.d = normalize(tr.d);
+            Sp T_maj = track_T_maj_t<GRAY>(sc.media[lightRay.medium], tr, tMax, uu, rng, ch, tc,
+                                   [&](V3, const MediumProps &mp, Sp sigma_maj, Sp T_maj) {
+                                       Sp sigma_n = clamp_zero(sigma_maj - to_spec<GRAY>(mp.sigma_a) - to_spec<GRAY>(mp.sigma_s));
+                                       float pdf = T_maj[ch] * sigma_maj[ch];
+                                       T_ray = T_ray * (T_maj * sigma_n / pdf);
+                                       r_l = r_l * (T_maj * sigma_maj / pdf);
+                                       r_u = r_u * (T_maj * sigma_n / pdf);
+                                       Sp Tr = T_ray / avg3(r_l + r_u);
+                                       if (max_comp(Tr) < 0.05f) {
+                                           float q = 0.75f;
+                                           if (rng.uniform() < q) T_ray = Sp();
+                                           else T_ray = T_ray / (1 - q);
+                                       }
+                                       return nonzero(T_ray);
+                                   });
+            T_ray = T_ray * (T_maj / T_maj[ch]);
+            r_l = r_l * (T_maj / T_maj[ch]);
+            r_u = r_u * (T_maj / T_maj[ch]);
+        }
+        if (!nonzero(T_ray)) return false;
+        if (h.prim < 0) break;
+        SurfaceIntr hs = make_intr(sc, h, lightRay.o, lightRay.d, lightRay.medium);
+        spawn_ray_to(hs.p, hs.pError, hs.n, sr.pLight, sr.pLightErr, sr.nLight, &lightRay.o, &lightRay.d);
+        lightRay.medium = hs.get_medium(lightRay.d);
+    }
+    V3 rl3 = to_v3(r_l) * sr.rl;
+    V3 ru3 = to_v3(r_u) * sr.ru;
+    // f_hat * T_ray * ls->L / (r_l + r_u).Average()  (vspg.cpp:1247-1250), then L += beta * Ld (:479, :833)
+    V3 v = sr.delta ? sr.f_hat * to_v3(T_ray) * sr.L / avg3(rl3) : sr.f_hat * to_v3(T_ray) * sr.L / avg3(rl3 + ru3);
+    *Ld = sr.beta * v;
+    return true;
+}
+
 template <bool GRAY>
 __global__ void __launch_bounds__(kBlock, VSPG_SHADOW_MINB) k_shadow(const DScene sc, const Wavefront W) {
-    typedef typename SpecT<GRAY>::type Sp;
     const int n = *W.shadow.count;
     TrackCounters tc; tc.queries = 0; tc.dda = 0;
     unsigned nodes = 0;
     for (int i = gtid(); i < n; i += gstride()) {
         int slot = W.shadow.items[i];
         ShadowRec sr; shadow_load(W.P, slot, sr);
-        const int ch = sr.channel;
-        Ray lightRay; lightRay.o = sr.o; lightRay.d = sr.d; lightRay.medium = sr.medium;
-        Sp T_ray = to_spec<GRAY>(splat(1.f)), r_l = T_ray, r_u = T_ray;
-        Rng rng; rng.set_sequence(hash_v3(lightRay.o), hash_v3(lightRay.d));
-        bool blocked = false;
-        while (!(lightRay.d == V3(0, 0, 0))) {
-            Hit h = scene_intersect(sc, lightRay.o, lightRay.d, 1 - kShadowEpsilon, nodes);
-            if (h.prim >= 0 && sc.quads[h.prim].material >= 0) { blocked = true; break; }
-            if (lightRay.medium >= 0) {
-                float tMax = h.prim >= 0 ? h.t : (1 - kShadowEpsilon);
-                float uu = rng.uniform();
-                Ray tr = lightRay;
-                tMax *= length(tr.d);
-                tr.d = normalize(tr.d);
-                Sp T_maj = track_T_maj_t<GRAY>(sc.media[lightRay.medium], tr, tMax, uu, rng, ch, tc,
-                                       [&](V3, const MediumProps &mp, Sp sigma_maj, Sp T_maj) {
-                                           Sp sigma_n = clamp_zero(sigma_maj - to_spec<GRAY>(mp.sigma_a) - to_spec<GRAY>(mp.sigma_s));
-                                           float pdf = T_maj[ch] * sigma_maj[ch];
-                                           T_ray = T_ray * (T_maj * sigma_n / pdf);
-                                           r_l = r_l * (T_maj * sigma_maj / pdf);
-                                           r_u = r_u * (T_maj * sigma_n / pdf);
-                                           Sp Tr = T_ray / avg3(r_l + r_u);
-                                           if (max_comp(Tr) < 0.05f) {
-                                               float q = 0.75f;
-                                               if (rng.uniform() < q) T_ray = Sp();
-                                               else T_ray = T_ray / (1 - q);
-                                           }
-                                           return nonzero(T_ray);
-                                       });
-                T_ray = T_ray * (T_maj / T_maj[ch]);
-                r_l = r_l * (T_maj / T_maj[ch]);
-                r_u = r_u * (T_maj / T_maj[ch]);
-            }
-            if (!nonzero(T_ray)) { blocked = true; break; }
-            if (h.prim < 0) break;
-            SurfaceIntr hs = make_intr(sc, h, lightRay.o, lightRay.d, lightRay.medium);
-            spawn_ray_to(hs.p, hs.pError, hs.n, sr.pLight, sr.pLightErr, sr.nLight, &lightRay.o, &lightRay.d);
-            lightRay.medium = hs.get_medium(lightRay.d);
-        }
-        if (!blocked) {
-            V3 rl3 = to_v3(r_l) * sr.rl;
-            V3 ru3 = to_v3(r_u) * sr.ru;
-            // f_hat * T_ray * ls->L / (r_l + r_u).Average()  (vspg.cpp:1247-1250), then L += beta * Ld (:479, :833)
-            V3 Ld = sr.delta ? sr.f_hat * to_v3(T_ray) * sr.L / avg3(rl3) : sr.f_hat * to_v3(T_ray) * sr.L / avg3(rl3 + ru3);
-            Ld = sr.beta * Ld;
+        V3 Ld;
+        if (shadow_trace<GRAY>(sc, sr, tc, nodes, &Ld)) {
             float4 e = W.P.rl_L[slot];
             e.y += Ld.x; e.z += Ld.y; e.w += Ld.z;
             W.P.rl_L[slot] = e;
