@@ -419,6 +419,27 @@ typedef struct vspg_gs_output {
 int vspg_debug_guided_sample(vspg_ctx *ctx, int is_surface, int n, const vspg_gs_input *in,
                              vspg_gs_output *out);
 
+/* SampleLd at one path vertex (next-event estimation, reference: cpu/guidedvolpathvspgintegrator.cpp:1136-1252): light
+ * pick, Light::SampleLi, guided scatter pdf at the light direction, then the shadow-ray chain through interface
+ * surfaces with ratio tracking + Russian roulette and the MIS weighting.  The vertex is described the way the
+ * reference's harness (oracle/ref_harness/pbrt_harness.cpp refp_sample_ld) describes it: a surface vertex is the first
+ * hit of `ray`; a volume vertex sits at ray.o inside `medium` with incoming direction ray.d.  The sampler is the
+ * pixel sampler of (px, py, sample_index) positioned at dimension `dim`; it first yields the cache-lookup draw, then the
+ * three light-sampling dimensions.  status: 0 = evaluated, 2 = no (non-interface) surface hit, 3 = bad medium. */
+typedef struct vspg_ld_input {
+    int is_surface;
+    float ray_o[3], ray_d[3];
+    int medium;             /* medium the ray travels in (-1 none); for a volume vertex: the vertex's medium */
+    int px, py, sample_index, dim, seed;
+    float r_p[3];           /* path MIS weight the estimate is formed with (r_u of the caller) */
+    int channel;            /* hero channel of the path */
+} vspg_ld_input;
+typedef struct vspg_ld_output {
+    int status;
+    float Ld[3];
+} vspg_ld_output;
+int vspg_debug_sample_ld(vspg_ctx *ctx, int n, const vspg_ld_input *in, vspg_ld_output *out);
+
 #ifdef __cplusplus
 }
 #endif

@@ -167,4 +167,76 @@ __global__ void __launch_bounds__(kBlock) k_debug_guided_sample(const DScene sc,
     }
 }
 
+// SampleLd at explicit vertices (vspg.cpp:1136-1252): one warp per item.  The same pieces the wavefront runs in
+// k_lookup (nee_presample), k_shade / k_volscatter (f, guided pdf, shadow record) and k_shadow (shadow_trace).
+template <bool GRAY>
+__global__ void __launch_bounds__(kBlock) k_debug_sample_ld(const DScene sc, int n, const vspg_ld_input *in, vspg_ld_output *out) {
+    const vspg_integrator_params &ip = sc.ip;
+    const bool leader = (threadIdx.x & 31) == 0;
+    for (int i = gtid() >> 5; i < n; i += gstride() >> 5) {
+        const vspg_ld_input &I = in[i];
+        vspg_ld_output O; O.status = 0; O.Ld[0] = O.Ld[1] = O.Ld[2] = 0;
+        Rng rng;   // samplers.h:442-476 IndependentSampler::StartPixelSample
+        rng.set_sequence(hash_3u32((uint32_t)I.px, (uint32_t)I.py, (uint32_t)I.seed));
+        rng.advance((uint64_t)I.sample_index * 65536ull + (uint64_t)I.dim);
+        V3 ro(I.ray_o[0], I.ray_o[1], I.ray_o[2]), rd(I.ray_d[0], I.ray_d[1], I.ray_d[2]);
+        V3 r_p(I.r_p[0], I.r_p[1], I.r_p[2]);
+        unsigned lookups = 0, nodes = 0;
+        ShadowRec sr; bool emit = false;
+        sr.beta = splat(1.f); sr.channel = I.channel;
+        if (I.is_surface) {
+            Hit h = scene_intersect(sc, ro, rd, inff(), nodes);
+            if (h.prim < 0 || sc.quads[h.prim].material < 0) O.status = 2;
+            else {
+                SurfaceIntr isect = make_intr(sc, h, ro, rd, I.medium);
+                GuidedBSDF<32> gb;
+                gb.enableGuiding = ip.surface_guiding; gb.enableScatterGuiding = ip.vsp_secondary_guiding; gb.ris = ip.surface_guiding_ris;
+                gb.set_bsdf(isect.ns, isect.dpdu, ld3(sc.materials[isect.material].reflectance));
+                float v = rng.uniform();
+                gb.init(sc, ro + h.t * rd, rd, isect.ns, v, lookups);
+                if (gb.non_specular()) {
+                    V3 ctxP = offset_ray_origin(isect.p, isect.pError, isect.n, isect.wo);
+                    NeePre ls = nee_presample(sc, rng, ctxP, isect.ns);
+                    if (ls.valid) {
+                        V3 f_hat = gb.f(isect.wo, ls.wi) * absdotn(ls.wi, isect.ns);
+                        float scatterPDF = 1.0f * gb.pdf(isect.wo, ls.wi);
+                        if (nonzero(f_hat)) {
+                            spawn_ray_to(isect.p, isect.pError, isect.n, ls.pLight, ls.pLightErr, ls.nLight, &sr.o, &sr.d);
+                            sr.medium = isect.get_medium(sr.d);
+                            sr.f_hat = f_hat; sr.L = ls.L; sr.rl = r_p * ls.p_l; sr.ru = r_p * scatterPDF;
+                            sr.pLight = ls.pLight; sr.pLightErr = ls.pLightErr; sr.nLight = ls.nLight; sr.delta = ls.delta;
+                            emit = true;
+                        }
+                    }
+                }
+            }
+        } else if (I.medium < 0 || I.medium >= sc.n_media) O.status = 3;
+        else {
+            MediumProps mp = sample_point(sc.media[I.medium], ro);
+            GuidedPhase<32> gp;
+            gp.enableGuiding = ip.volume_guiding; gp.enableScatterGuiding = ip.vsp_secondary_guiding; gp.ris = ip.volume_guiding_ris;
+            float v = rng.uniform();
+            gp.init(sc, mp.g, ro, rd, v, lookups);
+            NeePre ls = nee_presample(sc, rng, ro, V3());
+            if (ls.valid) {
+                float ph = gp.p(-rd, ls.wi);
+                float scatterPDF = 1.0f * gp.pdf(-rd, ls.wi);
+                if (ph != 0) {
+                    spawn_ray_to(ro, V3(), V3(), ls.pLight, ls.pLightErr, ls.nLight, &sr.o, &sr.d);
+                    sr.medium = I.medium;
+                    sr.f_hat = splat(ph); sr.L = ls.L; sr.rl = r_p * ls.p_l; sr.ru = r_p * scatterPDF;
+                    sr.pLight = ls.pLight; sr.pLightErr = ls.pLightErr; sr.nLight = ls.nLight; sr.delta = ls.delta;
+                    emit = true;
+                }
+            }
+        }
+        if (emit) {
+            TrackCounters tc; tc.queries = 0; tc.dda = 0;
+            V3 Ld;
+            if (shadow_trace<GRAY>(sc, sr, tc, nodes, &Ld)) { O.Ld[0] = Ld.x; O.Ld[1] = Ld.y; O.Ld[2] = Ld.z; }
+        }
+        if (leader) out[i] = O;
+    }
+}
+
 }  // namespace vspg

@@ -174,4 +174,22 @@ int vspg_debug_guided_sample(vspg_ctx *ctx, int is_surface, int n, const vspg_gs
     return VSPG_OK;
 }
 
+int vspg_debug_sample_ld(vspg_ctx *ctx, int n, const vspg_ld_input *in, vspg_ld_output *out) {
+    if (!ctx || n < 0 || !in || !out) return VSPG_ERR_INVALID;
+    CK_STATE(ctx->have_scene, "debug_sample_ld: set_scene has not been called");
+    if (n == 0) return VSPG_OK;
+    CK(cudaSetDevice(ctx->device));
+    DevBuf din, dout;
+    CK(din.alloc((size_t)n * sizeof(vspg_ld_input)));
+    CK(dout.alloc((size_t)n * sizeof(vspg_ld_output)));
+    CK(cudaMemcpy(din.p, in, (size_t)n * sizeof(vspg_ld_input), cudaMemcpyHostToDevice));
+    int blocks = std::min((n * 32 + kBlock - 1) / kBlock, ctx->sm_count * 8);
+    if (ctx->all_gray) k_debug_sample_ld<true><<<blocks, kBlock>>>(ctx->sc, n, din.as<vspg_ld_input>(), dout.as<vspg_ld_output>());
+    else k_debug_sample_ld<false><<<blocks, kBlock>>>(ctx->sc, n, din.as<vspg_ld_input>(), dout.as<vspg_ld_output>());
+    ctx->launches++;
+    CK(cudaGetLastError());
+    CK(cudaMemcpy(out, dout.p, (size_t)n * sizeof(vspg_ld_output), cudaMemcpyDeviceToHost));
+    return VSPG_OK;
+}
+
 }  // extern "C"

@@ -134,6 +134,15 @@ class SdOutput(C.Structure):
                 ("beta", F3), ("r_u", F3), ("r_l", F3), ("rng_state", u64), ("density_queries", i32), ("dda_steps", i32)]
 
 
+class LdInput(C.Structure):
+    _fields_ = [("is_surface", C.c_int), ("ray_o", C.c_float * 3), ("ray_d", C.c_float * 3), ("medium", C.c_int), ("px", C.c_int), ("py", C.c_int),
+                ("sample_index", C.c_int), ("dim", C.c_int), ("seed", C.c_int), ("r_p", C.c_float * 3), ("channel", C.c_int)]
+
+
+class LdOutput(C.Structure):
+    _fields_ = [("status", C.c_int), ("Ld", C.c_float * 3)]
+
+
 class GsInput(C.Structure):
     _fields_ = [("p", F3), ("wo", F3), ("n", F3), ("g", f32), ("reflectance", F3), ("v", f32), ("u1", f32), ("u2", f32 * 2),
                 ("wq", F3), ("rng_state", u64), ("rng_inc", u64)]
@@ -194,6 +203,7 @@ SYMBOLS = {
     "vspg_debug_sample_li": (i32, [P, i32, PF, C.POINTER(i32), PF, PF]),
     "vspg_debug_light_sample": (i32, [P, i32, PF, PF, PF, C.POINTER(i32), C.POINTER(i32), PF, PF]),
     "vspg_debug_guided_sample": (i32, [P, i32, i32, C.POINTER(GsInput), C.POINTER(GsOutput)]),
+    "vspg_debug_sample_ld": (i32, [P, i32, C.POINTER(LdInput), C.POINTER(LdOutput)]),
 }
 
 

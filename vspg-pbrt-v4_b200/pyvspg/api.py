@@ -206,6 +206,14 @@ class Context:
         self._ck(lib().vspg_debug_sample_li(self._h, n, _fp(ctx9), light.ctypes.data_as(C.POINTER(A.i32)), _fp(u2), _fp(out)))
         return out
 
+    def debug_sample_ld(self, inputs):
+        """SampleLd at explicit vertices (A.LdInput array) -> (status[n], Ld[n,3])."""
+        n = len(inputs)
+        out = (A.LdOutput * n)()
+        self._ck(lib().vspg_debug_sample_ld(self._h, n, inputs, out))
+        return (np.array([o.status for o in out], dtype=np.int32),
+                np.array([[o.Ld[0], o.Ld[1], o.Ld[2]] for o in out], dtype=np.float32).reshape(n, 3))
+
     def debug_guided_sample(self, is_surface, inputs):
         n = len(inputs)
         out = (A.GsOutput * n)()
