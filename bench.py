@@ -50,6 +50,8 @@ def parse_args():
     ap.add_argument("--res-scale", type=float, default=1.0, help="scale film resolution (reported in config)")
     ap.add_argument("--capacity", type=int, default=0, help="paths in flight (0 = library default)")
     ap.add_argument("--shard", default="samples", choices=["samples", "bands"], help="multi-GPU partition (pyvspg.multi)")
+    ap.add_argument("--scaling", default="weak", choices=["weak", "strong"],
+                    help="weak: every rank renders the workload's spp (job = spp x N); strong: the workload's spp is split over the ranks")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--cpu-spp", type=int, default=0, help="spp of the CPU sample (0 = auto, ~10-30 s)")
     return ap.parse_args()
@@ -81,8 +83,8 @@ def config_dict(cfg, args, world):
             grid = [int(g.shape[2]), int(g.shape[1]), int(g.shape[0])]
             break
     return {
-        "workload": cfg.name, "description": cfg.description, "width": cfg.width, "height": cfg.height, "spp_per_gpu": cfg.spp,
-        "spp_total": cfg.spp * world, "grid": grid,
+        "workload": cfg.name, "description": cfg.description, "width": cfg.width, "height": cfg.height,
+        "spp_per_gpu": cfg.spp if args.scaling == "weak" else cfg.spp / world, "spp_total": cfg.spp * (world if args.scaling == "weak" else 1), "grid": grid,
         "sampler": "independent", "maxdepth": cfg.ip.max_depth,
         "parallelism": f"{'sample-pass' if args.shard == 'samples' else 'interleaved-band'} sharding x{world}" + (" + NCCL film reduce" if world > 1 else ""),
         "l2": "inputs larger than L2: the path-state working set (up to 2^24 paths x ~380 B = 6.4 GB) streams through the 126 MB L2 every wave "
@@ -365,7 +367,8 @@ def run_b200(args):
     fptr, fn = ctx.film_device_ptr()
     film_t = torch.as_tensor(_DevArray(fptr, fn), device=f"cuda:{local}")
     W, Hh, spp = cfg.width, cfg.height, cfg.spp
-    paths_per_step = W * Hh * spp * world
+    spp_job = spp * world if args.scaling == "weak" else spp      # sample indices of one step, over all ranks
+    paths_per_step = W * Hh * spp_job
 
     def render(b, e, s, window, seed):
         ctx.render(b, e, spp_stride=s, window=window, seed=seed, stream=stream)
@@ -374,7 +377,7 @@ def run_b200(args):
         # weak scaling: a (spp*world)-spp render of the image; rank r takes its shard (sample indices r, r+world, ...
         # or its interleaved row bands), then the fp64 films are summed onto rank 0 (the one exchange step)
         ctx.film_clear()
-        multi.render_shard(render, W, Hh, spp * world, rank, world, seed, mode=args.shard)
+        multi.render_shard(render, W, Hh, spp_job, rank, world, seed, mode=args.shard)
         multi.combine_film(film_t, world, dst=0)
 
     for i in range(args.warmup):
@@ -421,7 +424,7 @@ def run_b200(args):
         ctx.set_scene(cfg.scene)          # H2D: density grid(s), majorant grid, shapes, lights
         ctx.set_guiding(cfg.guiding)      # H2D: guiding cache (KD nodes, mixtures, neighbour tables), ISG / Tr buffers
         ctx.set_integrator(cfg.ip)
-        multi.render_shard(render, W, Hh, spp * world, rank, world, seed, mode=args.shard)
+        multi.render_shard(render, W, Hh, spp_job, rank, world, seed, mode=args.shard)
         multi.combine_film(film_t, world, dst=0)
         ctx.film_download_to(film_host.data_ptr())   # D2H: fp64 film
 
@@ -459,6 +462,26 @@ def run_b200(args):
             "kernel_ms_share": {k: round(ks[k]["ms"] / max(1e-9, sum(ks[n]["ms"] for n in names)), 4) for k in names},
             "kernel_ms_sum": sum(ks[n]["ms"] for n in names), "stats_pass_ms": ms_stats, "stats_pass_steps": stat_steps, "timed_region_ms": ms_total,
         }
+        # ---- what only a profiler can count: DRAM bytes and issued instructions, from the committed ncu metric pass of this
+        # workload (tools/ncu_metrics_summary.py -> profiles/); the durations they are divided by are this run's own
+        prof_path = os.path.join(ROOT, "profiles", f"r02_ncu_metrics_{args.workload}.json")
+        if os.path.exists(prof_path) and not args.spp and args.res_scale == 1.0:
+            prof = json.load(open(prof_path))
+            dk = max((k for k in prof["kernels"] if k.startswith("k_" + tracked)), key=lambda k: prof["kernels"][k]["ms"], default=None)
+            if dk:
+                roofline["traffic"] = prof["kernels"][dk]["dram_bytes_per_launch"]
+                roofline["traffic_kernel"] = dk
+                roofline["traffic_source"] = os.path.relpath(prof_path, ROOT)
+            big = max(names, key=lambda k: ks[k]["ms"])
+            if big in prof["stages"]:
+                ps_ = prof["stages"][big]
+                sm_mhz = (clk or {}).get("sm_mhz") or 1965.0
+                issue_peak = 148 * 4 * sm_mhz * 1e6          # warp instructions / s: 148 SMs x 4 schedulers x SM clock under load
+                ach = ps_["warp_inst"] / max(1e-12, ks[big]["ms"] / stat_steps * 1e-3)
+                roofline["issue"] = {"stage": big, "warp_inst_per_step": ps_["warp_inst"], "lanes_per_inst": ps_["lanes_per_inst"],
+                                     "stage_ms_per_step": ks[big]["ms"] / stat_steps, "achieved": ach / 1e9, "peak": issue_peak / 1e9, "unit": "Gwarp-inst/s",
+                                     "frac": ach / issue_peak, "useful_lane_frac": ach / issue_peak * ps_["lanes_per_inst"] / 32.0,
+                                     "source": os.path.relpath(prof_path, ROOT)}
         cpu = None
         relmse = None
         if not args.no_cpu_baseline and world == 1:
@@ -467,7 +490,7 @@ def run_b200(args):
             cpu = {"value": v, "unit": "paths/s", "cores": cores, "kind": kind, "sample": sample}
         out = {
             "metric": "paths/sec (guidedvolpathvspg render pass)", "value": value, "unit": "paths/s", "n_gpus": world, "steps": args.steps,
-            "warmup": args.warmup, "ms_per_step": ms_total / args.steps, "higher_is_better": True, "scaling": "weak",
+            "warmup": args.warmup, "ms_per_step": ms_total / args.steps, "higher_is_better": True, "scaling": args.scaling,
             "vs_baseline": None, "dtype": "f32", "data": "synthetic", "config": config_dict(cfg, args, world),
             "e2e": {"value": e2e_value, "unit": "paths/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h, "steps": e2e_steps},
             "gpu_launches": int(round(cnt["kernel_launches"] * args.steps / stat_steps)), "clocks": clk, "roofline": roofline, "cpu_baseline": cpu, "relmse": relmse,

@@ -79,4 +79,8 @@ $CXX $FLAGS $DEFS $INC -o "$OUT/pbrt" "$S/pbrt/cmd/pbrt.cpp" -L"$OUT" -lpbrt_ref
 if [ -f "$HERE/ref_harness/pbrt_harness.cpp" ]; then
   $CXX $FLAGS $DEFS $INC -shared -o "$OUT/libpbrtharness.so" "$HERE/ref_harness/pbrt_harness.cpp" -L"$OUT" -lpbrt_ref -lopenpgl_ref -ltbb_ref -lpthread -ldl -Wl,-rpath,'$ORIGIN'
 fi
+# .nvdb files for the NanoVDB medium tests come from the reference's vendored NanoVDB itself (header-only)
+if [ -f "$HERE/ref_harness/nvdb_writer.cpp" ]; then
+  $CXX -std=c++17 -O2 -w -DNANOVDB_USE_ZIP -I"$EXT/openvdb/nanovdb" -o "$OUT/nvdb_writer" "$HERE/ref_harness/nvdb_writer.cpp" -lz -lpthread
+fi
 echo "build_ref_pbrt: ok -> $OUT"

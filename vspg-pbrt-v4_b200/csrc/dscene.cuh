@@ -169,8 +169,9 @@ struct Wavefront {
     int *cursors;                      // per-kernel dynamic work cursors
 };
 
-// CNT_QUERIES / CNT_DDA: issued by the SampleDistance kernel; *_SH: issued by the shadow-ray kernel
-enum { CNT_PATHS = 0, CNT_QUERIES = 1, CNT_DDA = 2, CNT_LOOKUPS = 3, CNT_BVH = 4, CNT_SHADOW = 5, CNT_QUERIES_SH = 6, CNT_DDA_SH = 7, CNT_COUNT = 8 };
+// CNT_QUERIES / CNT_DDA: issued by the SampleDistance kernels; *_SH: by the shadow-ray kernel; CNT_DDA_PRE: the
+// resampling routine's pre-pass (total majorant optical depth), which runs inside k_intersect
+enum { CNT_PATHS = 0, CNT_QUERIES = 1, CNT_DDA = 2, CNT_LOOKUPS = 3, CNT_BVH = 4, CNT_SHADOW = 5, CNT_QUERIES_SH = 6, CNT_DDA_SH = 7, CNT_DDA_PRE = 8, CNT_COUNT = 9 };
 
 // ------------------------------------------------------------------ warp-aggregated queue push (ballot + popc prefix)
 VD void queue_push(const Queue &q, bool pred, int value) {

@@ -41,7 +41,7 @@ __global__ void __launch_bounds__(kBlock) k_generate(const DScene sc, const Wave
 // ------------------------------------------------------------------ closest hit (vspg.cpp:314)
 __global__ void __launch_bounds__(kBlock) k_intersect(const DScene sc, const Wavefront W) {
     const int n = *W.active.count;
-    unsigned nodes = 0;
+    unsigned nodes = 0, preSteps = 0;
     for (int i = gtid(); i < n; i += gstride()) {
         int slot = W.active.items[i];
         float4 a = W.P.o_dx[slot], b = W.P.d_med[slot];
@@ -67,12 +67,14 @@ __global__ void __launch_bounds__(kBlock) k_intersect(const DScene sc, const Wav
                 totalLength += seg.sigma_maj[ch] * (seg.tMax - seg.tMin);
             }
             W.P.rs_pre[slot] = make_float2(totalLength, __int_as_float((int)pre.steps));
+            preSteps += pre.steps;
         }
         queue_push(W.medium_rs, rs, slot);
         queue_push(W.medium, toMedium && !rs, slot);
         queue_push(W.surface, !toMedium, slot);
     }
     counter_add(W.counters, CNT_BVH, nodes);
+    counter_add(W.counters, CNT_DDA_PRE, preSteps);
 }
 
 // ------------------------------------------------------------------ SampleDistance (vspg.cpp:318-351, 637-1096)

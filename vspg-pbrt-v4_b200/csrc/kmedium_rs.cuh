@@ -70,7 +70,6 @@ VD void rs_fetch(const DScene &sc, const Wavefront &W, int slot, RsLane<GRAY> &s
     s.selP = V3(); s.selNum = Sp(); s.selDen = Sp();
     s.T_maj = to_spec<GRAY>(splat(1.f));
     s.count = 0;
-    ddaSteps += (unsigned)__float_as_int(pre.y);
     // media_sampleTMaj.h:166-181 with the pre-pass sum from k_intersect
     float totalLength = pre.x;
     s.majorantScale = 1.0f;

@@ -324,7 +324,7 @@ int vspg_counters_get(vspg_ctx *ctx, vspg_counters *out) {
     CK(cudaSetDevice(ctx->device));
     unsigned long long h[CNT_COUNT];
     CK(cudaMemcpy(h, ctx->counters, sizeof h, cudaMemcpyDeviceToHost));
-    out->paths = h[CNT_PATHS]; out->density_queries = h[CNT_QUERIES] + h[CNT_QUERIES_SH]; out->dda_steps = h[CNT_DDA] + h[CNT_DDA_SH]; out->cache_lookups = h[CNT_LOOKUPS];
+    out->paths = h[CNT_PATHS]; out->density_queries = h[CNT_QUERIES] + h[CNT_QUERIES_SH]; out->dda_steps = h[CNT_DDA] + h[CNT_DDA_SH] + h[CNT_DDA_PRE]; out->cache_lookups = h[CNT_LOOKUPS];
     out->bvh_nodes = h[CNT_BVH]; out->shadow_rays = h[CNT_SHADOW]; out->kernel_launches = ctx->launches; out->wave_iterations = ctx->iterations;
     return VSPG_OK;
 }
@@ -349,6 +349,7 @@ int vspg_kernel_stats_get(vspg_ctx *ctx, int enable_timing, vspg_kernel_stats *o
         CK(cudaMemcpy(h, ctx->counters, sizeof h, cudaMemcpyDeviceToHost));
         out->density_queries[VSPG_K_MEDIUM] = h[CNT_QUERIES]; out->dda_steps[VSPG_K_MEDIUM] = h[CNT_DDA];
         out->density_queries[VSPG_K_SHADOW] = h[CNT_QUERIES_SH]; out->dda_steps[VSPG_K_SHADOW] = h[CNT_DDA_SH];
+        out->dda_steps[VSPG_K_INTERSECT] = h[CNT_DDA_PRE];
     }
     return VSPG_OK;
 }
