@@ -59,7 +59,7 @@ typedef struct vspg_camera {
     float max_component_value; /* film.h:257 clamp; +inf = none         */
 } vspg_camera;
 
-enum { VSPG_MEDIUM_HOMOGENEOUS = 0, VSPG_MEDIUM_GRID = 1, VSPG_MEDIUM_RGBGRID = 2 };
+enum { VSPG_MEDIUM_HOMOGENEOUS = 0, VSPG_MEDIUM_GRID = 1, VSPG_MEDIUM_RGBGRID = 2, VSPG_MEDIUM_NANOVDB = 3 };
 
 /* media.h:221-467.  sigma_a/sigma_s are the RGB spectra ALREADY multiplied by
  * the medium's "scale" for homogeneous/uniformgrid (their ctors call
@@ -78,6 +78,17 @@ typedef struct vspg_medium {
     const float *sigma_s_rgb;  /* rgbgrid: nx*ny*nz*3 or NULL (=> 1)                     */
     int maj_res[3];            /* 16,16,16 for grid/rgbgrid (media.cpp:246,382)          */
     const float *majorant;     /* maj_res product floats; NULL => built by set_scene     */
+    /* nanovdb (media.h:657-753, media.cpp:549-734): `density` is the float grid flattened over its index bounding box
+     * [index_min, index_min + (nx,ny,nz)) -- voxels outside hold `background` --, sampled at
+     * pIndex = index_from_medium * (p - index_origin) (NanoVDB Map::applyInverseMapF) with NanoVDB's trilinear sampler,
+     * plus density_offset; bounds = the grid's world bounding box; maj_res = 64^3 and `majorant` is given (the front end
+     * builds it as NanoVDBMedium's constructor does, majorantscale included). */
+    int index_min[3];
+    float index_from_medium[9];
+    float index_origin[3];
+    float density_offset;
+    float background;
+    float majorant_scale;      /* "majorantscale" the given majorant grid was built with (informational) */
 } vspg_medium;
 
 /* One bilinear patch (shapes.h:1350) in render space; vertex order p00,p10,p01,p11. */

@@ -30,7 +30,7 @@ JOBS="${JOBS:-$(nproc)}"
 if [ -x /usr/bin/g++ ]; then CXX="${VSPG_REF_CXX:-/usr/bin/g++}"; CC="${VSPG_REF_CC:-/usr/bin/gcc}"; else CXX="${VSPG_REF_CXX:-g++}"; CC="${VSPG_REF_CC:-gcc}"; fi
 [ -f "$OUT/libopenpgl_ref.so" ] || bash "$HERE/build_ref.sh"
 
-DEFS="-DPBRT_IS_LINUX -DPBRT_RGB_RENDERING -DPBRT_WITH_PATH_GUIDING -DPBRT_WITH_OIDN -DPTEX_STATIC -DNDEBUG -DPBRT_HAVE_MMAP -DPBRT_HAVE_POSIX_MEMALIGN -DPBRT_NOINLINE=__attribute__((noinline)) -DPBRT_RESTRICT=__restrict__"
+DEFS="-DPBRT_IS_LINUX -DPBRT_RGB_RENDERING -DPBRT_WITH_PATH_GUIDING -DPBRT_WITH_OIDN -DPTEX_STATIC -DNDEBUG -DPBRT_HAVE_MMAP -DPBRT_HAVE_POSIX_MEMALIGN -DNANOVDB_USE_ZIP -DPBRT_NOINLINE=__attribute__((noinline)) -DPBRT_RESTRICT=__restrict__"
 INC="-I$HERE/stubs/pbrt_shadow -I$HERE/stubs -I$HERE/stubs/exr -I$GEN -I$S -I$EXT -I$EXT/stb -I$EXT/qoi -I$EXT/libdeflate \
 -I$EXT/filesystem -I$EXT/ptex/src/ptex -I$EXT/double-conversion -I$EXT/openvdb/nanovdb -I$EXT/utf8proc \
 -I$HERE/stubs/ptex -I$HERE/stubs/openpgl -I$PGL/openpgl/include -I$PGL/openpgl/include/openpgl -I$EXT/tbb/include"

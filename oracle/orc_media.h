@@ -3,6 +3,8 @@
 // trilinear density lookup and the three SampleT_maj variants of the fork.
 // Paths are relative to /root/reference/src/pbrt/.
 #pragma once
+#include <cstring>
+#include <mutex>
 #include <vector>
 
 #include "../include/vspg.h"
@@ -149,11 +151,46 @@ struct Medium {
         S3 d11 = L(d.x, rgbAt(g, ix, iy + 1, iz + 1), rgbAt(g, ix + 1, iy + 1, iz + 1));
         return L(d.z, L(d.y, d00, d10), L(d.y, d01, d11));
     }
-    // media.h:256-261, 316-348, 417-441 SamplePoint (emission branches out of scope: configs have none)
+    // ReadAccessor::getValue on the flattened grid: voxels outside the index bounding box read the background
+    float nvdbAt(int i, int j, int k) const {
+        int x = i - m->index_min[0], y = j - m->index_min[1], z = k - m->index_min[2];
+        if (x < 0 || y < 0 || z < 0 || x >= m->nx || y >= m->ny || z >= m->nz) return m->background;
+        return m->density[(size_t)(z * m->ny + y) * m->nx + x];
+    }
+    // media.h:699-703: worldToIndexF (NanoVDB.h:2028-2031 applyInverseMapF, :1408-1414 matMult with explicit fmaf) and
+    // SampleFromVoxels<Tree, 1, false>::operator() (util/SampleFromVoxels.h:57-65 Floor, :421-463)
+    float nvdbLookup(V3 p) const {
+        const float *mt = m->index_from_medium;
+        float x = p.x - m->index_origin[0], y = p.y - m->index_origin[1], z = p.z - m->index_origin[2];
+        float xyz[3] = {std::fmaf(x, mt[0], std::fmaf(y, mt[1], z * mt[2])), std::fmaf(x, mt[3], std::fmaf(y, mt[4], z * mt[5])),
+                        std::fmaf(x, mt[6], std::fmaf(y, mt[7], z * mt[8]))};
+        const float fl[3] = {std::floor(xyz[0]), std::floor(xyz[1]), std::floor(xyz[2])};
+        for (int a = 0; a < 3; a++) xyz[a] -= fl[a];
+        int c[3] = {(int)fl[0], (int)fl[1], (int)fl[2]};
+        auto lerp = [](float a, float b, float w) { return a + w * (b - a); };
+        float vx, vx1, vy, vy1, vz, vz1;
+        vz = nvdbAt(c[0], c[1], c[2]); c[2] += 1; vz1 = nvdbAt(c[0], c[1], c[2]); vy = lerp(vz, vz1, xyz[2]);
+        c[1] += 1;
+        vz1 = nvdbAt(c[0], c[1], c[2]); c[2] -= 1; vz = nvdbAt(c[0], c[1], c[2]); vy1 = lerp(vz, vz1, xyz[2]);
+        vx = lerp(vy, vy1, xyz[1]);
+        c[0] += 1;
+        vz = nvdbAt(c[0], c[1], c[2]); c[2] += 1; vz1 = nvdbAt(c[0], c[1], c[2]); vy1 = lerp(vz, vz1, xyz[2]);
+        c[1] -= 1;
+        vz1 = nvdbAt(c[0], c[1], c[2]); c[2] -= 1; vz = nvdbAt(c[0], c[1], c[2]); vy = lerp(vz, vz1, xyz[2]);
+        vx1 = lerp(vy, vy1, xyz[1]);
+        return lerp(vx, vx1, xyz[0]);
+    }
+    // media.h:256-261, 316-348, 417-441, 692-705 SamplePoint (emission branches out of scope: configs have none)
     MediumProps SamplePoint(V3 p) const {
         MediumProps mp; mp.g = m->g;
         if (m->type == VSPG_MEDIUM_HOMOGENEOUS) { mp.sigma_a = S3(m->sigma_a); mp.sigma_s = S3(m->sigma_s); return mp; }
         p = ApplyInversePoint(m->render_from_medium, p);
+        if (m->type == VSPG_MEDIUM_NANOVDB) {
+            float d = nvdbLookup(p);
+            d += m->density_offset;
+            mp.sigma_a = S3(m->sigma_a) * d; mp.sigma_s = S3(m->sigma_s) * d;
+            return mp;
+        }
         p = bounds.Offset(p);
         if (m->type == VSPG_MEDIUM_GRID) {
             float d = densityLookup(p);
@@ -179,7 +216,37 @@ struct Medium {
         return maxValue;
     }
     // media.cpp:256-269 (GridMedium) and media.cpp:393-408 (RGBGridMedium)
+    // media.cpp:605-670 NanoVDBMedium's majorant grid: per cell, the maximum over the index-space box of the cell +- 1 voxel
+    void BuildMajorantNanoVDB(float *out) const {
+        const int rx = m->maj_res[0], ry = m->maj_res[1], rz = m->maj_res[2];
+        const int bmax[3] = {m->index_min[0] + m->nx - 1, m->index_min[1] + m->ny - 1, m->index_min[2] + m->nz - 1};
+        auto toIndex = [&](V3 w, double *o) {   // worldToIndexF(Vec3R): the float map applied to double coordinates
+            double d[3] = {(double)w.x - (double)m->index_origin[0], (double)w.y - (double)m->index_origin[1], (double)w.z - (double)m->index_origin[2]};
+            for (int r = 0; r < 3; r++) {
+                const float *mt = m->index_from_medium + 3 * r;
+                o[r] = (double)fmaf((float)d[0], mt[0], fmaf((float)d[1], mt[1], (float)(d[2] * (double)mt[2])));
+            }
+        };
+        for (int z = 0; z < rz; ++z)
+            for (int y = 0; y < ry; ++y)
+                for (int x = 0; x < rx; ++x) {
+                    V3 t0(float(x) / rx, float(y) / ry, float(z) / rz), t1(float(x + 1) / rx, float(y + 1) / ry, float(z + 1) / rz);
+                    V3 w0(Lerp(t0.x, bounds.pMin.x, bounds.pMax.x), Lerp(t0.y, bounds.pMin.y, bounds.pMax.y), Lerp(t0.z, bounds.pMin.z, bounds.pMax.z));
+                    V3 w1(Lerp(t1.x, bounds.pMin.x, bounds.pMax.x), Lerp(t1.y, bounds.pMin.y, bounds.pMax.y), Lerp(t1.z, bounds.pMin.z, bounds.pMax.z));
+                    double i0[3], i1[3];
+                    toIndex(w0, i0); toIndex(w1, i1);
+                    float delta = 1.f;
+                    int n0[3], n1[3];
+                    for (int a = 0; a < 3; a++) { n0[a] = std::max(int(i0[a] - delta), m->index_min[a]); n1[a] = std::min(int(i1[a] + delta), bmax[a]); }
+                    float maxValue = 0;
+                    for (int nz = n0[2]; nz <= n1[2]; ++nz)
+                        for (int ny = n0[1]; ny <= n1[1]; ++ny)
+                            for (int nx = n0[0]; nx <= n1[0]; ++nx) maxValue = std::max(maxValue, nvdbAt(nx, ny, nz));
+                    out[x + rx * (y + ry * z)] = (maxValue + m->density_offset) * m->majorant_scale;
+                }
+    }
     void BuildMajorant(float *out) const {
+        if (m->type == VSPG_MEDIUM_NANOVDB) { BuildMajorantNanoVDB(out); return; }
         int rx = m->maj_res[0], ry = m->maj_res[1], rz = m->maj_res[2];
         for (int z = 0; z < rz; ++z)
             for (int y = 0; y < ry; ++y)
@@ -201,8 +268,26 @@ struct Medium {
         bounds.pMin = V3(m->bounds_min); bounds.pMax = V3(m->bounds_max);
         maj = m->majorant;
         if (m->type != VSPG_MEDIUM_HOMOGENEOUS && (ownMajorant || !maj)) {
-            ownMaj.resize((size_t)m->maj_res[0] * m->maj_res[1] * m->maj_res[2]);
-            BuildMajorant(ownMaj.data());
+            const size_t n = (size_t)m->maj_res[0] * m->maj_res[1] * m->maj_res[2];
+            if (m->type == VSPG_MEDIUM_NANOVDB) {
+                // the per-sample entry points build a Scene per call: keep the last 64^3 grid (0.1 s to build) while the
+                // medium it was built from is unchanged
+                static std::mutex mu;
+                static std::vector<float> cached;
+                static vspg_medium key;
+                std::lock_guard<std::mutex> lock(mu);
+                vspg_medium k = *m; k.majorant = nullptr; k.g = 0; memset(k.sigma_a, 0, sizeof k.sigma_a); memset(k.sigma_s, 0, sizeof k.sigma_s);
+                memset(&k.render_from_medium, 0, sizeof k.render_from_medium);
+                if (cached.size() != n || memcmp(&k, &key, sizeof k) != 0) {
+                    cached.assign(n, 0.f);
+                    BuildMajorant(cached.data());
+                    key = k;
+                }
+                ownMaj = cached;
+            } else {
+                ownMaj.resize(n);
+                BuildMajorant(ownMaj.data());
+            }
             maj = ownMaj.data();
         }
     }
@@ -278,7 +363,7 @@ inline MajorantIterator SampleRay(const Medium &med, Ray ray, float raytMax) {
     ApplyInverseRay(m->render_from_medium, ray.o, ray.d, &raytMax, &o, &d);
     float tMin, tMax;
     if (!med.bounds.IntersectP(o, d, raytMax, &tMin, &tMax)) return it;  // default iterator: tMin=inf >= tMax=-inf
-    S3 sigma_t = (m->type == VSPG_MEDIUM_GRID) ? (S3(m->sigma_a) + S3(m->sigma_s)) : S3(1.f);
+    S3 sigma_t = (m->type == VSPG_MEDIUM_GRID || m->type == VSPG_MEDIUM_NANOVDB) ? (S3(m->sigma_a) + S3(m->sigma_s)) : S3(1.f);
     it.initDDA(o, d, tMin, tMax, med, sigma_t);
     return it;
 }

@@ -40,6 +40,24 @@ PF, PI = C.POINTER(C.c_float), C.POINTER(C.c_int)
 from ref_scenes import SCENES, build_scene, write_inputs  # noqa: E402  (tests/ref_scenes.py: the scene builders, shared with the tests)
 
 
+def write_nvdb(golden_dir):
+    """tests/golden/nvdb_small.nvdb through the reference's vendored NanoVDB (oracle/_ref/nvdb_writer, built by
+    oracle/build_ref_pbrt.sh from oracle/ref_harness/nvdb_writer.cpp): a sparse blob of 20 x 18 x 16 seeded values at index
+    offset (-5, 3, 100), voxel size 0.05, ZIP codec (12 KB; the same grid uncompressed is 660 KB of mostly empty nodes)."""
+    import subprocess
+    import tempfile
+    rng = np.random.default_rng(77)
+    nx, ny, nz = 20, 18, 16
+    g = rng.random((nz, ny, nx), dtype=np.float32)
+    z, y, x = np.mgrid[0:nz, 0:ny, 0:nx]
+    mask = ((x - 10) ** 2 / 90 + (y - 9) ** 2 / 70 + (z - 8) ** 2 / 50) < 1.0
+    g = np.where(mask, g * 2.0 + 0.05, 0).astype(np.float32)
+    with tempfile.NamedTemporaryFile(suffix=".f32") as t:
+        g.tofile(t.name)
+        subprocess.run([os.path.join(ROOT, "oracle", "_ref", "nvdb_writer"), os.path.join(golden_dir, "nvdb_small.nvdb"), t.name, str(nx), str(ny), str(nz),
+                        "-5", "3", "100", "0.05", "0.22", "-0.15", "-4.95", "zip"], check=True)
+
+
 def harness():
     path = os.path.join(ROOT, "oracle", "_ref", "libpbrtharness.so")
     if not os.path.exists(path):
@@ -113,6 +131,7 @@ def main():
         import subprocess
         os.makedirs(OUT, exist_ok=True)
         write_inputs(HERE)
+        write_nvdb(HERE)
         env = dict(os.environ, LD_PRELOAD=shim)
         for name in SCENES:
             r = subprocess.run([sys.executable, os.path.abspath(__file__), name], env=env, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)

@@ -10,7 +10,7 @@ from pyvspg import _abi as A
 from pyvspg import api, configs, pbrt_writer
 from pyvspg.scenes import Scene, perspective_camera
 
-SCENES = ["c1", "c1t", "c1e", "c1s", "c2", "c2u", "c3", "c3nds", "c3contrib", "c4", "c4r", "c5", "c5u", "ch", "cg"]
+SCENES = ["c1", "c1t", "c1e", "c1s", "c2", "c2u", "c3", "c3nds", "c3contrib", "c4", "c4r", "c5", "c5u", "ch", "cg", "cn", "cnu"]
 
 
 def write_inputs(golden_dir):
@@ -35,6 +35,11 @@ def _guided(name, kind="grid", filt=None, lights="pa", **ipkw):
         sa = rng.random((6, 5, 4, 3), dtype=np.float32) * np.float32([0.02, 0.05, 0.2])
         ss = rng.random((6, 5, 4, 3), dtype=np.float32) * np.float32([4, 3, 2])
         med = sc.add_rgbgrid_medium(sa, ss, (0, 0, 0), (1, 1, 1), 3.0, 0.4)
+    elif kind == "nvdb":
+        # tests/golden/nvdb_small.nvdb: written by the reference's vendored NanoVDB (oracle/ref_harness/nvdb_writer.cpp, see
+        # make_golden_pbrt.py): a sparse 19x17x15 blob at index offset (-4, 4, 101), voxel 0.05, world box (.02,.05,.1)-(.97,.9,.85)
+        med = sc.add_nanovdb_medium(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "nvdb_small.nvdb"), [0.1, 0.1, 0.1], [3.0, 3.0, 3.0],
+                                    4.0, 0.5, density_offset=0.02, majorant_scale=1.25, written_name="../nvdb_small.nvdb")
     else:
         med = sc.add_homogeneous_medium([0.2, 0.3, 0.5], [3.0, 2.0, 1.5], 1.5, 0.3)
     sc.add_box([0, 0, 0], [1, 1, 1], material=-1, medium_inside=med, medium_outside=-1, has_interface=True)
@@ -89,6 +94,10 @@ def _config(name):
         return _guided(name, kind="rgb", lights="patdb", light_sampler=B)
     if name == "c5u":
         return _guided(name, kind="rgb", lights="patdb", light_sampler=U)
+    if name == "cn":     # NanoVDB medium, full VSPG
+        return _guided(name, kind="nvdb", light_sampler=B)
+    if name == "cnu":    # NanoVDB medium, guiding off
+        return _guided(name, kind="nvdb", light_sampler=P, surface_guiding=0, volume_guiding=0, vsp_guiding=0)
     if name == "ch":
         return _guided(name, kind="hom", light_sampler=B, vsp_mis_ratio=0.3)
     if name == "cg":

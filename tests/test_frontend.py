@@ -228,7 +228,9 @@ LightSource "infinite"
     ("WorldBegin\nNamedMaterial \"nope\"\n", A.ERR_INVALID, "not defined"),
     ("WorldBegin\nAttributeBegin\nMediumInterface \"nope\" \"\"\nShape \"sphere\"\nAttributeEnd\n", A.ERR_INVALID, "not defined"),
     ("WorldBegin\nMakeNamedMedium \"m\" \"string type\" \"uniformgrid\" \"float density\" [1 2 3] \"integer nx\" 2\n", A.ERR_INVALID, "expected nx*ny*nz"),
-    ("WorldBegin\nMakeNamedMedium \"m\" \"string type\" \"nanovdb\" \"string filename\" \"a.nvdb\"\n", A.ERR_UNSUPPORTED, "nanovdb"),
+    ("WorldBegin\nMakeNamedMedium \"m\" \"string type\" \"nanovdb\" \"string filename\" \"a.nvdb\"\n", A.ERR_IO, "cannot open"),
+    ("WorldBegin\nMakeNamedMedium \"m\" \"string type\" \"nanovdb\"\n", A.ERR_INVALID, "Must supply \"filename\""),
+    ("WorldBegin\nMakeNamedMedium \"m\" \"string type\" \"cloud\"\n", A.ERR_UNSUPPORTED, "outside the hot-path scope"),
     ("WorldBegin\nShape \"sphere\" \"float radius\" [1\n", A.ERR_INVALID, "missing ]"),
     ("Camera \"perspective\"\nWorldBegin\n", A.ERR_INVALID, "not allowed after WorldBegin"),
 ])

@@ -5,13 +5,13 @@
 namespace vspg {
 
 // CELL8 layout: cell (cx,cy,cz), cx in [0,nx], holds the corners of interpolation cell ix = cx-1 .. (see dscene.cuh)
-__global__ void k_build_cells(const float *density, int nx, int ny, int nz, float4 *cells) {
+__global__ void k_build_cells(const float *density, int nx, int ny, int nz, float bg, float4 *cells) {
     size_t ncell = (size_t)(nx + 1) * (ny + 1) * (nz + 1);
     for (size_t c = (size_t)blockIdx.x * blockDim.x + threadIdx.x; c < ncell; c += (size_t)gridDim.x * blockDim.x) {
         int cx = (int)(c % (nx + 1)), cy = (int)((c / (nx + 1)) % (ny + 1)), cz = (int)(c / ((size_t)(nx + 1) * (ny + 1)));
         int ix = cx - 1, iy = cy - 1, iz = cz - 1;
         auto at = [&](int x, int y, int z) -> float {
-            if (x < 0 || y < 0 || z < 0 || x >= nx || y >= ny || z >= nz) return 0.f;
+            if (x < 0 || y < 0 || z < 0 || x >= nx || y >= ny || z >= nz) return bg;   // 0 for pbrt's grids, the tree's background for nanovdb
             return density[(size_t)(z * ny + y) * nx + x];
         };
         cells[2 * c] = make_float4(at(ix, iy, iz), at(ix + 1, iy, iz), at(ix, iy + 1, iz), at(ix + 1, iy + 1, iz));

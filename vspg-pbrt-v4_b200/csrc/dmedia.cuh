@@ -80,7 +80,7 @@ VD V3 apply_inverse_point(const DMedium &m, V3 p) {  // util/transform.h Transfo
 
 // ------------------------------------------------------------------ density fetch (util/containers.h:804-818)
 VD float grid_at(const DMedium &m, int x, int y, int z) {
-    if (x < 0 || y < 0 || z < 0 || x >= m.nx || y >= m.ny || z >= m.nz) return 0.f;
+    if (x < 0 || y < 0 || z < 0 || x >= m.nx || y >= m.ny || z >= m.nz) return m.bg;
     return __ldg(&m.density[(size_t)(z * m.ny + y) * m.nx + x]);
 }
 VD float trilerp(float dx, float dy, float dz, float v000, float v100, float v010, float v110, float v001, float v101,
@@ -91,42 +91,63 @@ VD float trilerp(float dx, float dy, float dz, float v000, float v100, float v01
     float d11 = lerpf(dx, v011, v111);
     return lerpf(dz, lerpf(dy, d00, d10), lerpf(dy, d01, d11));
 }
-VD float density_lookup(const DMedium &m, V3 p) {
-    float psx = p.x * m.nx - .5f, psy = p.y * m.ny - .5f, psz = p.z * m.nz - .5f;
-    float fx = floorf(psx), fy = floorf(psy), fz = floorf(psz);
-    int ix = (int)fx, iy = (int)fy, iz = (int)fz;
-    float dx = psx - (float)ix, dy = psy - (float)iy, dz = psz - (float)iz;
-    if (m.layout == GRID_CELL8) {
-        // one aligned 32-byte sector: the 8 corners of cell (ix,iy,iz); cells outside [-1,n-1] are all-zero
-        if (ix < -1 || iy < -1 || iz < -1 || ix >= m.nx || iy >= m.ny || iz >= m.nz) return trilerp(dx, dy, dz, 0, 0, 0, 0, 0, 0, 0, 0);
-        size_t cell = ((size_t)(iz + 1) * (m.ny + 1) + (iy + 1)) * (m.nx + 1) + (ix + 1);
-        float4 a = __ldg(&m.cells[2 * cell]), b = __ldg(&m.cells[2 * cell + 1]);
-        return trilerp(dx, dy, dz, a.x, a.y, a.z, a.w, b.x, b.y, b.z, b.w);
-    }
-    return trilerp(dx, dy, dz, grid_at(m, ix, iy, iz), grid_at(m, ix + 1, iy, iz), grid_at(m, ix, iy + 1, iz),
-                   grid_at(m, ix + 1, iy + 1, iz), grid_at(m, ix, iy, iz + 1), grid_at(m, ix + 1, iy, iz + 1),
-                   grid_at(m, ix, iy + 1, iz + 1), grid_at(m, ix + 1, iy + 1, iz + 1));
-}
-// The same lookup split in two so that a caller can put independent work between the load and its first use
-// (k_medium_rs issues the fetch for collision k, searches for collision k+1, then consumes k).
+// The 8 corners of interpolation cell (ix,iy,iz) (grid-local voxel indices): one aligned 32-byte record in the CELL8 layout.
 struct DensityFetch { float4 a, b; float dx, dy, dz; };
-VD DensityFetch density_fetch_issue(const DMedium &m, V3 p) {   // p in [0,1]^3 medium-bounds coordinates
+VD void density_gather(const DMedium &m, int ix, int iy, int iz, float4 *a, float4 *b) {
+    if (m.layout == GRID_CELL8) {
+        // cells outside [-1,n-1] only see voxels outside the grid
+        if (ix < -1 || iy < -1 || iz < -1 || ix >= m.nx || iy >= m.ny || iz >= m.nz) { *a = make_float4(m.bg, m.bg, m.bg, m.bg); *b = *a; return; }
+        size_t cell = ((size_t)(iz + 1) * (m.ny + 1) + (iy + 1)) * (m.nx + 1) + (ix + 1);
+        *a = __ldg(&m.cells[2 * cell]); *b = __ldg(&m.cells[2 * cell + 1]);
+    } else {
+        *a = make_float4(grid_at(m, ix, iy, iz), grid_at(m, ix + 1, iy, iz), grid_at(m, ix, iy + 1, iz), grid_at(m, ix + 1, iy + 1, iz));
+        *b = make_float4(grid_at(m, ix, iy, iz + 1), grid_at(m, ix + 1, iy, iz + 1), grid_at(m, ix, iy + 1, iz + 1), grid_at(m, ix + 1, iy + 1, iz + 1));
+    }
+}
+// util/containers.h:804-818 SampledGrid<Float>::Lookup(Point3f): p in [0,1]^3 medium-bounds coordinates
+VD DensityFetch density_fetch_issue(const DMedium &m, V3 p) {
     DensityFetch f;
     float psx = p.x * m.nx - .5f, psy = p.y * m.ny - .5f, psz = p.z * m.nz - .5f;
     float fx = floorf(psx), fy = floorf(psy), fz = floorf(psz);
     int ix = (int)fx, iy = (int)fy, iz = (int)fz;
     f.dx = psx - (float)ix; f.dy = psy - (float)iy; f.dz = psz - (float)iz;
-    if (m.layout == GRID_CELL8) {
-        if (ix < -1 || iy < -1 || iz < -1 || ix >= m.nx || iy >= m.ny || iz >= m.nz) { f.a = make_float4(0, 0, 0, 0); f.b = f.a; return f; }
-        size_t cell = ((size_t)(iz + 1) * (m.ny + 1) + (iy + 1)) * (m.nx + 1) + (ix + 1);
-        f.a = __ldg(&m.cells[2 * cell]); f.b = __ldg(&m.cells[2 * cell + 1]);
-    } else {
-        f.a = make_float4(grid_at(m, ix, iy, iz), grid_at(m, ix + 1, iy, iz), grid_at(m, ix, iy + 1, iz), grid_at(m, ix + 1, iy + 1, iz));
-        f.b = make_float4(grid_at(m, ix, iy, iz + 1), grid_at(m, ix + 1, iy, iz + 1), grid_at(m, ix, iy + 1, iz + 1), grid_at(m, ix + 1, iy + 1, iz + 1));
-    }
+    density_gather(m, ix, iy, iz, &f.a, &f.b);
     return f;
 }
 VD float density_fetch_value(const DensityFetch &f) { return trilerp(f.dx, f.dy, f.dz, f.a.x, f.a.y, f.a.z, f.a.w, f.b.x, f.b.y, f.b.z, f.b.w); }
+VD float density_lookup(const DMedium &m, V3 p) { return density_fetch_value(density_fetch_issue(m, p)); }
+
+// NanoVDB grids (media.h:692-705): pIndex = Map::applyInverseMapF(p) (NanoVDB.h:2028-2031 with matMult, :1408-1414),
+// Floor + fractional part (util/SampleFromVoxels.h:57-65), then the order-1 sampler (:421-463): lerps along z, then y,
+// then x, each as a + w * (b - a).  p is in medium space.
+VD DensityFetch nvdb_fetch_issue(const DMedium &m, V3 p) {
+    DensityFetch f;
+    float x = p.x - m.nvVec[0], y = p.y - m.nvVec[1], z = p.z - m.nvVec[2];
+    float px = fmaf(x, m.nvInv[0], fmaf(y, m.nvInv[1], z * m.nvInv[2]));
+    float py = fmaf(x, m.nvInv[3], fmaf(y, m.nvInv[4], z * m.nvInv[5]));
+    float pz = fmaf(x, m.nvInv[6], fmaf(y, m.nvInv[7], z * m.nvInv[8]));
+    float fx = floorf(px), fy = floorf(py), fz = floorf(pz);
+    f.dx = px - fx; f.dy = py - fy; f.dz = pz - fz;
+    density_gather(m, (int)fx - m.imin[0], (int)fy - m.imin[1], (int)fz - m.imin[2], &f.a, &f.b);
+    return f;
+}
+VD float nvdb_lerp(float a, float b, float w) { return a + w * (b - a); }
+VD float nvdb_fetch_value(const DMedium &m, const DensityFetch &f) {
+    // a = (v000, v100, v010, v110), b = the same at k + 1, indices in (i, j, k) order
+    float vy = nvdb_lerp(f.a.x, f.b.x, f.dz), vy1 = nvdb_lerp(f.a.z, f.b.z, f.dz);
+    float vx = nvdb_lerp(vy, vy1, f.dy);
+    vy1 = nvdb_lerp(f.a.w, f.b.w, f.dz); vy = nvdb_lerp(f.a.y, f.b.y, f.dz);
+    float vx1 = nvdb_lerp(vy, vy1, f.dy);
+    return nvdb_lerp(vx, vx1, f.dx) + m.densityOffset;
+}
+// The density at render-space point p of a uniformgrid or nanovdb medium, split in two so that a caller can put
+// independent work between the load and its first use (k_medium_rs issues the fetch for collision k, searches for
+// collision k+1, then consumes k).
+VD DensityFetch medium_density_issue(const DMedium &m, V3 pRender) {
+    V3 p = apply_inverse_point(m, pRender);
+    return m.type == VSPG_MEDIUM_NANOVDB ? nvdb_fetch_issue(m, p) : density_fetch_issue(m, bounds_offset(m, p));
+}
+VD float medium_density_value(const DMedium &m, const DensityFetch &f) { return m.type == VSPG_MEDIUM_NANOVDB ? nvdb_fetch_value(m, f) : density_fetch_value(f); }
 
 VD V3 rgb_at(const DMedium &m, const float *g, int x, int y, int z) {
     if (x < 0 || y < 0 || z < 0 || x >= m.nx || y >= m.ny || z >= m.nz) return V3();
@@ -147,6 +168,11 @@ VD V3 rgb_lookup(const DMedium &m, const float *g, V3 p) {  // util/containers.h
 VD MediumProps sample_point(const DMedium &m, V3 p) {
     MediumProps mp; mp.g = m.g;
     if (m.type == VSPG_MEDIUM_HOMOGENEOUS) { mp.sigma_a = ld3(m.sigma_a); mp.sigma_s = ld3(m.sigma_s); return mp; }
+    if (m.type == VSPG_MEDIUM_NANOVDB) {
+        float d = medium_density_value(m, medium_density_issue(m, p));
+        mp.sigma_a = ld3(m.sigma_a) * d; mp.sigma_s = ld3(m.sigma_s) * d;
+        return mp;
+    }
     p = apply_inverse_point(m, p);
     p = bounds_offset(m, p);
     if (m.type == VSPG_MEDIUM_GRID) {
@@ -231,7 +257,7 @@ VD MajorantIterator sample_ray(const DMedium &m, const Ray &ray, float raytMax) 
     apply_inverse_ray(m, ray.o, ray.d, &raytMax, &o, &d);
     float tMin, tMax;
     if (!bounds_intersect(m, o, d, raytMax, &tMin, &tMax)) return it;
-    V3 sigma_t = (m.type == VSPG_MEDIUM_GRID) ? (ld3(m.sigma_a) + ld3(m.sigma_s)) : splat(1.f);
+    V3 sigma_t = (m.type == VSPG_MEDIUM_GRID || m.type == VSPG_MEDIUM_NANOVDB) ? (ld3(m.sigma_a) + ld3(m.sigma_s)) : splat(1.f);
     it.init_dda(m, o, d, tMin, tMax, sigma_t);
     return it;
 }

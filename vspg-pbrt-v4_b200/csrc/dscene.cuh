@@ -26,6 +26,11 @@ struct DMedium {
     int mres[3];
     const float *majorant;
     int layout;
+    // VSPG_MEDIUM_NANOVDB: `density` / `cells` hold the grid flattened over [imin, imin + (nx,ny,nz)); voxels outside
+    // read `bg`.  pIndex = nvInv * (p - nvVec) (NanoVDB Map::applyInverseMapF), the density gets `densityOffset` added.
+    int imin[3];
+    float nvInv[9], nvVec[3];
+    float densityOffset, bg;       // bg = 0 for pbrt's own grids (SampledGrid::Lookup outside the grid)
 };
 
 // One surface primitive: a bilinear patch (p00,p10,p01,p11) or a triangle (p0,p1,p2 in p00,p10,p01; p11 unused).

@@ -32,6 +32,7 @@
 #include <vector>
 
 #include "../../include/vspg.h"
+#include "host_nvdb.h"
 #include "host_xform.h"
 
 namespace {
@@ -454,11 +455,82 @@ struct Builder {
             grid_dims(n);
             if (sa) m.sigma_a_rgb = own(std::vector<float>(sa->begin(), sa->end()));
             if (ss) m.sigma_s_rgb = own(std::vector<float>(ss->begin(), ss->end()));
-        } else lx.fail("medium type \"" + type + "\" is outside the hot-path scope (homogeneous, uniformgrid, rgbgrid; nanovdb is SURVEY 8f1)", VSPG_ERR_UNSUPPORTED);
+        } else if (type == "nanovdb") {
+            make_nanovdb_medium(m, name, scale_, ps, lx);
+        } else lx.fail("medium type \"" + type + "\" is outside the hot-path scope (homogeneous, uniformgrid, rgbgrid, nanovdb)", VSPG_ERR_UNSUPPORTED);
         ps.report_unused();
         if (S.medium_ids.count(name)) lx.fail("medium \"" + name + "\" redefined");
         S.medium_ids[name] = (int)S.media.size();
         S.media.push_back(m);
+    }
+
+    // media.cpp:683-734 NanoVDBMedium::Create + :549-670 the constructor (bounds, 64^3 majorant grid with the +-1 voxel
+    // filter slop).  The sparse tree is flattened over its index bounding box (host_nvdb.cpp); the CUDA path turns that
+    // into cell records like any other density grid.
+    void make_nanovdb_medium(vspg_medium &m, const std::string &name, float scale_, const Params &ps, Lexer &lx) {
+        m.type = VSPG_MEDIUM_NANOVDB;
+        std::string filename = ps.one_string("filename", "");
+        if (filename.empty()) lx.fail("Must supply \"filename\" to \"nanovdb\" medium.");
+        filename = resolve(filename);
+        std::string gridname = ps.one_string("gridname", "density");
+        std::string temperaturename = ps.one_string("temperaturename", "temperature");
+        float LeScale = (float)ps.one_float("Lescale", 1);
+        ps.one_float("temperatureoffset", ps.one_float("temperaturecutoff", 0)); ps.one_float("temperaturescale", 1);
+        const float densityOffset = (float)ps.one_float("densityoffset", 0), majorantScale = (float)ps.one_float("majorantscale", 1);
+        float sa[3] = {1, 1, 1}, ss[3] = {1, 1, 1};
+        ps.rgb("sigma_a", sa); ps.rgb("sigma_s", ss);
+        for (int i = 0; i < 3; i++) { m.sigma_a[i] = sa[i] * scale_; m.sigma_s[i] = ss[i] * scale_; }   // media.cpp:582-583
+        vspg_host::NvdbGrid g;
+        std::string err;
+        if (!vspg_host::read_nvdb_float_grid(filename, gridname, &g, &err)) lx.fail("nanovdb medium \"" + name + "\": " + err, VSPG_ERR_IO);
+        if (LeScale > 0 && vspg_host::nvdb_has_grid(filename, temperaturename))   // media.h:687 IsEmissive
+            lx.fail("nanovdb medium \"" + name + "\": the file has a \"" + temperaturename + "\" grid (blackbody emission), which is outside the hot-path scope; pass \"float Lescale\" 0", VSPG_ERR_UNSUPPORTED);
+        if (g.nx == 0) lx.fail("nanovdb medium \"" + name + "\": grid \"" + gridname + "\" is empty");
+        for (int i = 0; i < 3; i++) {   // media.cpp:585-587: Bounds3f from the double world bounding box
+            m.bounds_min[i] = (float)g.world_min[i]; m.bounds_max[i] = (float)g.world_max[i];
+            m.index_min[i] = g.bbox_min[i]; m.index_origin[i] = g.vec_f[i];
+        }
+        for (int i = 0; i < 9; i++) m.index_from_medium[i] = g.inv_mat_f[i];
+        m.nx = g.nx; m.ny = g.ny; m.nz = g.nz;
+        m.density_offset = densityOffset; m.background = g.background; m.majorant_scale = majorantScale;
+        m.maj_res[0] = m.maj_res[1] = m.maj_res[2] = 64;
+        // worldToIndexF on a Vec3R (media.cpp:629-632): Map::applyInverseMapF subtracts the float translation in double, and
+        // matMult(const float*, Vec3T) (NanoVDB.h:1408-1414) hands the doubles to fmaf(float, float, float)
+        auto worldToIndexF = [&](const float w[3], double out[3]) {
+            double d[3] = {(double)w[0] - (double)g.vec_f[0], (double)w[1] - (double)g.vec_f[1], (double)w[2] - (double)g.vec_f[2]};
+            for (int r = 0; r < 3; r++) {
+                const float *mt = g.inv_mat_f + 3 * r;
+                out[r] = (double)fmaf((float)d[0], mt[0], fmaf((float)d[1], mt[1], (float)(d[2] * (double)mt[2])));
+            }
+        };
+        auto value = [&](int i, int j, int k) { return g.dense[((size_t)(k - g.bbox_min[2]) * g.ny + (j - g.bbox_min[1])) * g.nx + (i - g.bbox_min[0])]; };
+        auto lerp = [](float t, float a, float b) { return (1 - t) * a + t * b; };   // util/math.h:210, Bounds3::Lerp
+        std::vector<float> maj((size_t)64 * 64 * 64);
+        for (int z = 0; z < 64; z++)
+            for (int y = 0; y < 64; y++)
+                for (int x = 0; x < 64; x++) {
+                    const int c[3] = {x, y, z};
+                    float lo[3], hi[3];
+                    for (int a = 0; a < 3; a++) {
+                        lo[a] = lerp(float(c[a]) / 64, m.bounds_min[a], m.bounds_max[a]);
+                        hi[a] = lerp(float(c[a] + 1) / 64, m.bounds_min[a], m.bounds_max[a]);
+                    }
+                    double i0[3], i1[3];
+                    worldToIndexF(lo, i0); worldToIndexF(hi, i1);
+                    const float delta = 1.f;   // filter slop
+                    int n0[3], n1[3];
+                    for (int a = 0; a < 3; a++) {
+                        n0[a] = std::max(int(i0[a] - delta), g.bbox_min[a]);
+                        n1[a] = std::min(int(i1[a] + delta), g.bbox_max[a]);
+                    }
+                    float maxValue = 0;
+                    for (int nz = n0[2]; nz <= n1[2]; ++nz)
+                        for (int ny = n0[1]; ny <= n1[1]; ++ny)
+                            for (int nx = n0[0]; nx <= n1[0]; ++nx) maxValue = std::max(maxValue, value(nx, ny, nz));
+                    maj[x + 64 * (y + 64 * (size_t)z)] = (maxValue + densityOffset) * majorantScale;
+                }
+        m.density = own(std::move(g.dense));
+        m.majorant = own(std::move(maj));
     }
 
     int make_material(const std::string &type, const Params &ps, Lexer &lx) {

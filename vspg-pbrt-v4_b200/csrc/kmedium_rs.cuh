@@ -241,7 +241,7 @@ __global__ void __launch_bounds__(kBlock, MINB) k_medium_rs(const DScene sc, con
                 if (GRAY) {
                     const DMedium &med = sc.media[s.medium];
                     T_maj = pT_maj; sigma_maj = pSigma; p = pP;
-                    float d = density_fetch_value(pf);
+                    float d = medium_density_value(med, pf);
                     mp.g = med.g; mp.sigma_a = ld3(med.sigma_a) * d; mp.sigma_s = ld3(med.sigma_s) * d;   // sample_point, GRID branch
                     pend = false;
                 } else {
@@ -279,7 +279,7 @@ __global__ void __launch_bounds__(kBlock, MINB) k_medium_rs(const DScene sc, con
                 pT_maj = s.T_maj * fast_exp3(-(t - s.tMin) * s.segSigma);
                 pP = s.ray.at(t);
                 pSigma = s.segSigma;
-                pf = density_fetch_issue(med, bounds_offset(med, apply_inverse_point(med, pP)));
+                pf = medium_density_issue(med, pP);
                 s.T_maj = to_spec<GRAY>(splat(1.f));
                 s.tMin = t;
                 pend = true;

@@ -223,10 +223,17 @@ int vspg_set_scene(vspg_ctx *ctx, const vspg_scene_desc *s) {
         d.sigma_scale = m.sigma_scale; d.g = m.g; d.nx = m.nx; d.ny = m.ny; d.nz = m.nz;
         d.layout = GRID_LINEAR;
         if (m.type == VSPG_MEDIUM_HOMOGENEOUS) continue;
-        if (m.type != VSPG_MEDIUM_GRID && m.type != VSPG_MEDIUM_RGBGRID) return fail(ctx, VSPG_ERR_UNSUPPORTED, "set_scene: medium %d has unsupported type %d", i, m.type);
+        const bool scalarGrid = m.type == VSPG_MEDIUM_GRID || m.type == VSPG_MEDIUM_NANOVDB;
+        if (m.type == VSPG_MEDIUM_NANOVDB) {
+            if (!m.majorant) return fail(ctx, VSPG_ERR_INVALID, "set_scene: medium %d (nanovdb) comes without its majorant grid", i);
+            for (int a = 0; a < 3; a++) { d.imin[a] = m.index_min[a]; d.nvVec[a] = m.index_origin[a]; }
+            for (int a = 0; a < 9; a++) d.nvInv[a] = m.index_from_medium[a];
+            d.densityOffset = m.density_offset; d.bg = m.background;
+        }
+        if (!scalarGrid && m.type != VSPG_MEDIUM_RGBGRID) return fail(ctx, VSPG_ERR_UNSUPPORTED, "set_scene: medium %d has unsupported type %d", i, m.type);
         size_t nvox = (size_t)m.nx * m.ny * m.nz;
         if (nvox == 0 || m.maj_res[0] <= 0 || m.maj_res[1] <= 0 || m.maj_res[2] <= 0) return fail(ctx, VSPG_ERR_INVALID, "set_scene: medium %d has empty grid", i);
-        if (m.type == VSPG_MEDIUM_GRID) {
+        if (scalarGrid) {
             if (!m.density) return fail(ctx, VSPG_ERR_INVALID, "set_scene: medium %d has no density grid", i);
             CK(upload(ctx, ctx->scene_allocs, m.density, nvox, &d.density));
         } else {
@@ -240,12 +247,12 @@ int vspg_set_scene(vspg_ctx *ctx, const vspg_scene_desc *s) {
             build_majorant_grid(&m, maj.data());
             CK(upload(ctx, ctx->scene_allocs, maj.data(), nmaj, &d.majorant));
         }
-        if (m.type == VSPG_MEDIUM_GRID && ctx->grid_layout == GRID_CELL8) {
+        if (scalarGrid && ctx->grid_layout == GRID_CELL8) {
             size_t ncell = (size_t)(m.nx + 1) * (m.ny + 1) * (m.nz + 1);
             void *cells = nullptr;
             CK(dev_alloc(ctx, ctx->scene_allocs, &cells, ncell * 32));
             int blocks = (int)std::min<size_t>((ncell + 255) / 256, 148 * 32);
-            k_build_cells<<<blocks, 256>>>(d.density, m.nx, m.ny, m.nz, (float4 *)cells);
+            k_build_cells<<<blocks, 256>>>(d.density, m.nx, m.ny, m.nz, d.bg, (float4 *)cells);
             CK(cudaGetLastError());
             d.cells = (const float4 *)cells; d.layout = GRID_CELL8;
             if (!ctx->cells_ptr) { ctx->cells_ptr = cells; ctx->cells_bytes = ncell * 32; }

@@ -13,7 +13,7 @@ VSPG_OK = 0
 ERR_INVALID, ERR_CUDA, ERR_IO, ERR_UNSUPPORTED, ERR_STATE = -1, -2, -3, -4, -5
 ERR_NAMES = {0: "OK", -1: "INVALID", -2: "CUDA", -3: "IO", -4: "UNSUPPORTED", -5: "STATE"}
 
-MEDIUM_HOMOGENEOUS, MEDIUM_GRID, MEDIUM_RGBGRID = 0, 1, 2
+MEDIUM_HOMOGENEOUS, MEDIUM_GRID, MEDIUM_RGBGRID, MEDIUM_NANOVDB = 0, 1, 2, 3
 LIGHT_DIFFUSE_AREA, LIGHT_POINT, LIGHT_DISTANT, LIGHT_UNIFORM_INFINITE = 0, 1, 2, 3
 LIGHTSAMPLER_UNIFORM, LIGHTSAMPLER_POWER, LIGHTSAMPLER_BVH = 0, 1, 2
 MAX_LOBES = 32
@@ -36,7 +36,9 @@ class Camera(C.Structure):
 class Medium(C.Structure):
     _fields_ = [("type", i32), ("bounds_min", F3), ("bounds_max", F3), ("render_from_medium", Transform),
                 ("sigma_a", F3), ("sigma_s", F3), ("sigma_scale", f32), ("g", f32), ("nx", i32), ("ny", i32), ("nz", i32),
-                ("density", PF), ("sigma_a_rgb", PF), ("sigma_s_rgb", PF), ("maj_res", i32 * 3), ("majorant", PF)]
+                ("density", PF), ("sigma_a_rgb", PF), ("sigma_s_rgb", PF), ("maj_res", i32 * 3), ("majorant", PF),
+                ("index_min", i32 * 3), ("index_from_medium", f32 * 9), ("index_origin", F3), ("density_offset", f32), ("background", f32),
+                ("majorant_scale", f32)]
 
 
 class Quad(C.Structure):

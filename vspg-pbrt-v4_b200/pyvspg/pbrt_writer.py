@@ -83,6 +83,10 @@ def scene_text(cfg, out_dir=None, outfile="out.exr", seed=0, integrator_name="gu
                     L.append(head + f' "string densityfile" "{fn}"')
                 else:
                     L.append(head + ' "float density" [' + " ".join(repr(float(x)) for x in d.reshape(-1)) + "]")
+            elif e["type"] == "nanovdb":
+                fn = e["filename"] if placeholder_grids else (e.get("written_name") or e["filename"])
+                L.append(head + f' "rgb sigma_a" [{_v(e["sigma_a"])}] "rgb sigma_s" [{_v(e["sigma_s"])}] "string filename" "{fn}" "string gridname" "{e["gridname"]}"'
+                         f' "float densityoffset" [{_f(e["density_offset"])}] "float majorantscale" [{_f(e["majorant_scale"])}]')
             else:
                 sa, ss = e["sigma_a_rgb"], e["sigma_s_rgb"]
                 if placeholder_grids:

@@ -146,6 +146,18 @@ class Scene:
         self.n_media += 1
         return self.n_media - 1
 
+    def add_nanovdb_medium(self, filename, sigma_a, sigma_s, scale_=1.0, g=0.0, gridname="density", density_offset=0.0, majorant_scale=1.0,
+                           world_from_medium=None, written_name=None):
+        """nanovdb (media.cpp:683-734): float grid `gridname` of a .nvdb file; the front end reads and flattens it.
+        `written_name` is the file name a written .pbrt scene refers to (default: `filename`)."""
+        import os
+        self.log.append(("medium", dict(type="nanovdb", filename=os.path.abspath(filename), written_name=written_name, gridname=gridname,
+                                        sigma_a=[float(x) for x in sigma_a], sigma_s=[float(x) for x in sigma_s], scale=float(scale_), g=float(g),
+                                        density_offset=float(density_offset), majorant_scale=float(majorant_scale),
+                                        world_from_medium=world_from_medium, index=self.n_media)))
+        self.n_media += 1
+        return self.n_media - 1
+
     def finalize(self):
         """Closes the scene description.  The POD desc is built on first use (`.desc`): writing the scene as files for
         the reference renderer needs only the world-space log, not the CUDA library."""
@@ -167,7 +179,7 @@ class Scene:
         assert (d.n_quads, d.n_triangles, d.n_spheres, d.n_materials, d.n_lights, d.n_media) == \
                (self.n_quads, self.n_triangles, self.n_spheres, self.n_materials, self.n_lights, self.n_media)
         for kind, e in self.log:
-            if kind != "medium" or e["type"] == "homogeneous":
+            if kind != "medium" or e["type"] in ("homogeneous", "nanovdb"):   # nanovdb grids are read by the front end itself
                 continue
             m = d.media[e["index"]]
             if e["type"] == "uniformgrid":
