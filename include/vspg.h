@@ -342,6 +342,20 @@ typedef struct vspg_segment {
 int vspg_debug_majorant_segments(vspg_ctx *ctx, int medium, int n, const float *rays7,
                                  int max_segments, vspg_segment *out, int *out_count);
 
+/* The same hook for callers that cannot allocate device memory (code under CUDA graph capture, tight serving loops,
+ * harnesses that forbid cudaMalloc).  It has no counterpart in the reference.
+ * Rays, segments and counts are staged in ONE file-scope device array of fixed size
+ * (csrc/vspg_ctx_noalloc.inl, ~5.7 MiB, held by every GPU that loads the library until the process exits) instead of
+ * cudaMalloc'd blocks: the call makes no cudaMalloc / cudaFree / allocating library call.  Limits: n <= VSPG_NOALLOC_MAX_RAYS
+ * and n * max_segments <= VSPG_NOALLOC_MAX_SEGMENTS, else VSPG_ERR_INVALID with a message.  All calls share the
+ * array and it keeps the previous call's contents; the part a call uses is cleared first.  Calls that overlap on one
+ * GPU (other threads, other contexts of the same device) race on it: serialise them.  Results are identical to
+ * vspg_debug_majorant_segments. */
+#define VSPG_NOALLOC_MAX_RAYS 16384
+#define VSPG_NOALLOC_MAX_SEGMENTS 262144
+int vspg_debug_majorant_segments_noalloc(vspg_ctx *ctx, int medium, int n, const float *rays7,
+                                         int max_segments, vspg_segment *out, int *out_count);
+
 /* Medium::SamplePoint (media.h:256-261, 316-348, 417-441) at n render-space points:
  * out7[i] = sigma_a RGB, sigma_s RGB, g. */
 int vspg_debug_density(vspg_ctx *ctx, int medium, int n, const float *pos3, float *out7);

@@ -9,6 +9,7 @@
 #include <map>
 #include <string>
 #include <unordered_map>
+#include <mutex>
 #include <vector>
 
 #include "host_util.h"
@@ -402,3 +403,4 @@ int vspg_set_scene(vspg_ctx *ctx, const vspg_scene_desc *s) {
 #include "vspg_ctx_guiding.inl"
 #include "vspg_ctx_render.inl"
 #include "vspg_ctx_debug.inl"
+#include "vspg_ctx_noalloc.inl"

@@ -13,6 +13,7 @@ VSPG_OK = 0
 ERR_INVALID, ERR_CUDA, ERR_IO, ERR_UNSUPPORTED, ERR_STATE = -1, -2, -3, -4, -5
 ERR_NAMES = {0: "OK", -1: "INVALID", -2: "CUDA", -3: "IO", -4: "UNSUPPORTED", -5: "STATE"}
 
+NOALLOC_MAX_RAYS, NOALLOC_MAX_SEGMENTS = 16384, 262144
 MEDIUM_HOMOGENEOUS, MEDIUM_GRID, MEDIUM_RGBGRID, MEDIUM_NANOVDB = 0, 1, 2, 3
 LIGHT_DIFFUSE_AREA, LIGHT_POINT, LIGHT_DISTANT, LIGHT_UNIFORM_INFINITE = 0, 1, 2, 3
 LIGHTSAMPLER_UNIFORM, LIGHTSAMPLER_POWER, LIGHTSAMPLER_BVH = 0, 1, 2
@@ -193,6 +194,7 @@ SYMBOLS = {
     "vspg_free": (None, [P]),
     "vspg_build_majorant_grid": (i32, [C.POINTER(Medium), PF]),
     "vspg_debug_majorant_segments": (i32, [P, i32, i32, PF, i32, C.POINTER(Segment), C.POINTER(i32)]),
+    "vspg_debug_majorant_segments_noalloc": (i32, [P, i32, i32, PF, i32, C.POINTER(Segment), C.POINTER(i32)]),
     "vspg_debug_density": (i32, [P, i32, i32, PF, PF]),
     "vspg_debug_sample_distance": (i32, [P, i32, C.POINTER(SdInput), C.POINTER(SdOutput)]),
     "vspg_debug_cache_lookup": (i32, [P, i32, i32, PF, PF, C.POINTER(i32), C.POINTER(i32), PF]),

@@ -144,6 +144,16 @@ class Context:
         arr = np.frombuffer(seg, dtype=np.float32).reshape(n, max_segments, 5).copy()
         return arr, cnt
 
+    def debug_majorant_segments_noalloc(self, medium, rays7, max_segments=64):
+        """vspg_debug_majorant_segments_noalloc: same results, staged in the library's fixed device scratch (no cudaMalloc)."""
+        rays7 = np.ascontiguousarray(rays7, dtype=np.float32).reshape(-1, 7)
+        n = rays7.shape[0]
+        seg = (A.Segment * max(1, n * max_segments))()
+        cnt = np.zeros(n, dtype=np.int32)
+        self._ck(lib().vspg_debug_majorant_segments_noalloc(self._h, medium, n, _fp(rays7), max_segments, seg, cnt.ctypes.data_as(C.POINTER(A.i32))))
+        arr = np.frombuffer(seg, dtype=np.float32)[:n * max_segments * 5].reshape(n, max_segments, 5).copy()
+        return arr, cnt
+
     def debug_density(self, medium, pos3):
         pos3 = np.ascontiguousarray(pos3, dtype=np.float32).reshape(-1, 3)
         out = np.zeros((pos3.shape[0], 7), dtype=np.float32)
