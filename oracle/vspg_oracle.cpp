@@ -70,7 +70,7 @@ int orc_build_majorant_grid(const vspg_medium *m, float *out) {
     return 0;
 }
 float orc_density_lookup(const vspg_medium *m, const float *p) {
-    Medium med; med.init(m, false);
+    Medium med; med.m = m; med.bounds.pMin = V3(m->bounds_min); med.bounds.pMax = V3(m->bounds_max);   // (no majorant grid needed)
     MediumProps mp = med.SamplePoint(V3(p));
     return mp.sigma_a[0] + mp.sigma_s[0];
 }

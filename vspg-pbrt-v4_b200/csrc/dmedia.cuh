@@ -143,11 +143,13 @@ VD float nvdb_fetch_value(const DMedium &m, const DensityFetch &f) {
 // The density at render-space point p of a uniformgrid or nanovdb medium, split in two so that a caller can put
 // independent work between the load and its first use (k_medium_rs issues the fetch for collision k, searches for
 // collision k+1, then consumes k).
-VD DensityFetch medium_density_issue(const DMedium &m, V3 pRender) {
+template <bool NVDB = true> VD DensityFetch medium_density_issue(const DMedium &m, V3 pRender) {
     V3 p = apply_inverse_point(m, pRender);
-    return m.type == VSPG_MEDIUM_NANOVDB ? nvdb_fetch_issue(m, p) : density_fetch_issue(m, bounds_offset(m, p));
+    return NVDB && m.type == VSPG_MEDIUM_NANOVDB ? nvdb_fetch_issue(m, p) : density_fetch_issue(m, bounds_offset(m, p));
 }
-VD float medium_density_value(const DMedium &m, const DensityFetch &f) { return m.type == VSPG_MEDIUM_NANOVDB ? nvdb_fetch_value(m, f) : density_fetch_value(f); }
+template <bool NVDB = true> VD float medium_density_value(const DMedium &m, const DensityFetch &f) {
+    return NVDB && m.type == VSPG_MEDIUM_NANOVDB ? nvdb_fetch_value(m, f) : density_fetch_value(f);
+}
 
 VD V3 rgb_at(const DMedium &m, const float *g, int x, int y, int z) {
     if (x < 0 || y < 0 || z < 0 || x >= m.nx || y >= m.ny || z >= m.nz) return V3();

@@ -99,6 +99,7 @@ struct DScene {
     double *tr_acc;      // storeTrBuffer accumulators {sumR, sumG, sumB, count} per pixel, or null (vspg_tr_store_begin)
     // PixelFilter "gaussian" sampling table (host_util.h build_gaussian_filter); filt_nx == 0 for the box filter
     int filt_nx, filt_ny; const float *filt_f, *filt_cond_cdf, *filt_cond_int, *filt_marg_cdf; float filt_marg_int;
+    float bin_lo[3], bin_scale[3];   // kbin.cuh: render-space box the stage queues are binned over, cells per unit length
     vspg_integrator_params ip;
 };
 

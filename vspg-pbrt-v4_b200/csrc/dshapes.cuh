@@ -146,6 +146,11 @@ VD bool intersect_triangle(V3 ro, V3 rd, float tMax, V3 p0, V3 p1, V3 p2, float 
 // Closest hit: stackless walk over the DFS-ordered threaded BVH.  Box test is the conservative slab test of
 // util/vecmath.h:1574 (tFar widened by 1+2*gamma(3)) so no hit of the brute-force reference order is lost;
 // ties in t go to the lower primitive index (= first primitive in scene order, as a linear scan would keep).
+// KINDS: primitive kinds the scene holds (bit 0 quads, bit 1 triangles, bit 2 spheres; host: vspg_ctx::prim_kinds).  The
+// BASELINE configs are quad-only; compiling the triangle / sphere branches out of their kernels took a third off the
+// tracking kernels' code, whose top stall was instruction fetch (profiles/r02n).
+constexpr int kKindsAll = 7, kKindsQuads = 1;
+template <int KINDS = kKindsAll>
 VD Hit scene_intersect(const DScene &sc, V3 ro, V3 rd, float tMax, unsigned &nodesVisited) {
     Hit h; h.t = tMax; h.prim = -1; h.u = h.v = 0;
     const float rayTMax = tMax;
@@ -183,14 +188,14 @@ VD Hit scene_intersect(const DScene &sc, V3 ro, V3 rd, float tMax, unsigned &nod
                 int q = __ldg(&sc.prim_ids[primBegin + i]);
                 const DQuad &Q = sc.quads[q];
                 float u, v, t, b2;
-                if (Q.kind == PRIM_SPHERE) {   // tested against the ray's own tMax like triangles (both roots are compared with it)
+                if ((KINDS & 4) && Q.kind == PRIM_SPHERE) {   // tested against the ray's own tMax like triangles (both roots are compared with it)
                     V3 pObj;
                     if (intersect_sphere(ro, rd, rayTMax, ld3(Q.p00), Q.p10[0], &t, &pObj) && (t < h.t || (t == h.t && h.prim >= 0 && q < h.prim))) {
                         h.t = t; h.u = 0; h.v = 0; h.prim = q;
                     }
                     continue;
                 }
-                bool got = Q.kind == PRIM_TRIANGLE ? intersect_triangle(ro, rd, rayTMax, ld3(Q.p00), ld3(Q.p10), ld3(Q.p01), &u, &v, &b2, &t)
+                bool got = (KINDS & 2) && Q.kind == PRIM_TRIANGLE ? intersect_triangle(ro, rd, rayTMax, ld3(Q.p00), ld3(Q.p10), ld3(Q.p01), &u, &v, &b2, &t)
                                                    : intersect_bilinear_patch(ro, rd, ld3(Q.p00), ld3(Q.p10), ld3(Q.p01), ld3(Q.p11), &u, &v, &t);
                 if (got && (t < h.t || (t == h.t && h.prim >= 0 && q < h.prim))) { h.t = t; h.u = u; h.v = v; h.prim = q; }
             }
@@ -203,11 +208,12 @@ VD Hit scene_intersect(const DScene &sc, V3 ro, V3 rd, float tMax, unsigned &nod
 // shapes.h:1398-1500 BilinearPatch::InteractionFromIntersection (no mesh uv / normals) + interaction.h:218-229
 // Triangles: shapes.h:884-945 Triangle::InteractionFromIntersection with the default (0,0),(1,0),(1,1) uvs and no
 // mesh normals; the barycentrics are recomputed from the ray (the hit record carries t, b0, b1 only).
+template <int KINDS = kKindsAll>
 VD SurfaceIntr make_intr(const DScene &sc, const Hit &h, V3 rayO, V3 rayD, int rayMedium) {
     SurfaceIntr s;
     const DQuad &q = sc.quads[h.prim];
     V3 p00 = ld3(q.p00), p10 = ld3(q.p10), p01 = ld3(q.p01), p11 = ld3(q.p11);
-    if (q.kind == PRIM_SPHERE) {   // the hit record carries t only: the quadric hit point is recomputed from the ray
+    if ((KINDS & 4) && q.kind == PRIM_SPHERE) {   // the hit record carries t only: the quadric hit point is recomputed from the ray
         float t; V3 pObj;
         intersect_sphere(rayO, rayD, inff(), p00, p10.x, &t, &pObj);
         sphere_interaction(pObj, p00, p10.x, q.flip_normal != 0, &s.p, &s.pError, &s.n, &s.dpdu);
@@ -219,7 +225,7 @@ VD SurfaceIntr make_intr(const DScene &sc, const Hit &h, V3 rayO, V3 rayD, int r
         s.mediumInside = q.medium_inside; s.mediumOutside = q.medium_outside; s.rayMedium = rayMedium;
         return s;
     }
-    if (q.kind == PRIM_TRIANGLE) {
+    if ((KINDS & 2) && q.kind == PRIM_TRIANGLE) {
         V3 p0 = p00, p1 = p10, p2 = p01;
         float b0 = h.u, b1 = h.v, b2 = 0, t;
         intersect_triangle(rayO, rayD, inff(), p0, p1, p2, &b0, &b1, &b2, &t);

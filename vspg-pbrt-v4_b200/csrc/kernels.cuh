@@ -39,6 +39,7 @@ __global__ void __launch_bounds__(kBlock) k_generate(const DScene sc, const Wave
 }
 
 // ------------------------------------------------------------------ closest hit (vspg.cpp:314)
+template <int KINDS = kKindsAll>
 __global__ void __launch_bounds__(kBlock) k_intersect(const DScene sc, const Wavefront W) {
     const int n = *W.active.count;
     unsigned nodes = 0, preSteps = 0;
@@ -47,7 +48,7 @@ __global__ void __launch_bounds__(kBlock) k_intersect(const DScene sc, const Wav
         float4 a = W.P.o_dx[slot], b = W.P.d_med[slot];
         V3 o(a.x, a.y, a.z), d(a.w, b.x, b.y);
         int medium = __float_as_int(b.z);
-        Hit h = scene_intersect(sc, o, d, inff(), nodes);
+        Hit h = scene_intersect<KINDS>(sc, o, d, inff(), nodes);
         W.P.hit[slot] = make_float4(h.t, h.u, h.v, __int_as_float(h.prim));
         bool toMedium = medium >= 0 && h.prim >= 0;  // vspg.cpp:318: rays escaping to infinity skip the medium
         // vspg.cpp:679 use_resampling: the persistent-lane kernel takes those, the generic kernel the rest

@@ -12,6 +12,7 @@ namespace vspg {
 // Streams are touched per branch (profiles/r02n: a whole-record load/store moved 2.9 GB per launch for a kernel that
 // mostly re-spawns rays at interfaces): the hit, the ray and the flags always; throughput / MIS weights / radiance only
 // where light is picked up.
+template <int KINDS = kKindsAll>
 __global__ void __launch_bounds__(kBlock, VSPG_SURFACE_MINB) k_surface(const DScene sc, const Wavefront W) {
     const int n = *W.surface.count;
     const vspg_integrator_params &ip = sc.ip;
@@ -51,7 +52,7 @@ __global__ void __launch_bounds__(kBlock, VSPG_SURFACE_MINB) k_surface(const DSc
         } else {
             const float4 a = W.P.o_dx[slot];
             const V3 ro(a.x, a.y, a.z), rd(a.w, b.x, b.y);
-            SurfaceIntr isect = make_intr(sc, h, ro, rd, __float_as_int(b.z));
+            SurfaceIntr isect = make_intr<KINDS>(sc, h, ro, rd, __float_as_int(b.z));
             if (isect.areaLight >= 0) {
                 V3 Le = area_L(sc.lights[isect.areaLight], isect.n, -rd);
                 if (nonzero(Le))
@@ -236,7 +237,7 @@ __global__ void __launch_bounds__(G > 0 ? 256 : kBlock, G > 0 ? VSPG_SHADE_MINB 
 // One shadow ray: the chain of segments through interface surfaces towards the light point with ratio tracking + Russian
 // roulette in every medium segment.  Returns false when the ray is blocked / its transmittance was terminated; else *Ld is
 // beta * (f_hat * T_ray * L / avg(MIS weights)).
-template <bool GRAY>
+template <bool GRAY, int KINDS = kKindsAll>
 VD bool shadow_trace(const DScene &sc, const ShadowRec &sr, TrackCounters &tc, unsigned &nodes, V3 *Ld) {
     typedef typename SpecT<GRAY>::type Sp;
     const int ch = sr.channel;
@@ -244,7 +245,7 @@ VD bool shadow_trace(const DScene &sc, const ShadowRec &sr, TrackCounters &tc, u
     Sp T_ray = to_spec<GRAY>(splat(1.f)), r_l = T_ray, r_u = T_ray;
     Rng rng; rng.set_sequence(hash_v3(lightRay.o), hash_v3(lightRay.d));
     while (!(lightRay.d == V3(0, 0, 0))) {
-        Hit h = scene_intersect(sc, lightRay.o, lightRay.d, 1 - kShadowEpsilon, nodes);
+        Hit h = scene_intersect<KINDS>(sc, lightRay.o, lightRay.d, 1 - kShadowEpsilon, nodes);
         if (h.prim >= 0 && sc.quads[h.prim].material >= 0) return false;
         if (lightRay.medium >= 0) {
             float tMax = h.prim >= 0 ? h.t : (1 - kShadowEpsilon);
@@ -273,7 +274,7 @@ VD bool shadow_trace(const DScene &sc, const ShadowRec &sr, TrackCounters &tc, u
         }
         if (!nonzero(T_ray)) return false;
         if (h.prim < 0) break;
-        SurfaceIntr hs = make_intr(sc, h, lightRay.o, lightRay.d, lightRay.medium);
+        SurfaceIntr hs = make_intr<KINDS>(sc, h, lightRay.o, lightRay.d, lightRay.medium);
         spawn_ray_to(hs.p, hs.pError, hs.n, sr.pLight, sr.pLightErr, sr.nLight, &lightRay.o, &lightRay.d);
         lightRay.medium = hs.get_medium(lightRay.d);
     }
@@ -285,7 +286,7 @@ VD bool shadow_trace(const DScene &sc, const ShadowRec &sr, TrackCounters &tc, u
     return true;
 }
 
-template <bool GRAY>
+template <bool GRAY, int KINDS = kKindsAll>
 __global__ void __launch_bounds__(kBlock, VSPG_SHADOW_MINB) k_shadow(const DScene sc, const Wavefront W) {
     const int n = *W.shadow.count;
     TrackCounters tc; tc.queries = 0; tc.dda = 0;
@@ -294,7 +295,7 @@ __global__ void __launch_bounds__(kBlock, VSPG_SHADOW_MINB) k_shadow(const DScen
         int slot = W.shadow.items[i];
         ShadowRec sr; shadow_load(W.P, slot, sr);
         V3 Ld;
-        if (shadow_trace<GRAY>(sc, sr, tc, nodes, &Ld)) {
+        if (shadow_trace<GRAY, KINDS>(sc, sr, tc, nodes, &Ld)) {
             float4 e = W.P.rl_L[slot];
             e.y += Ld.x; e.z += Ld.y; e.w += Ld.z;
             W.P.rl_L[slot] = e;

@@ -188,7 +188,8 @@ VD void rs_search_step(RsLane<GRAY> &s, float &t, bool &hit) {
 // Per trip: up to kRsSearchMax search steps, leaving early as soon as at least half of the lanes still walking have a
 // collision ready; then the collision body, predicated on `hit`.  Bounding the search keeps both halves of the trip
 // above ~60 % lane utilisation (an unbounded search ran at 7 lanes of 32, profiles/r01c).
-template <bool GRAY, int MINB>
+// NVDB: some medium of the scene is a NanoVDB grid (its sampler is compiled in only then)
+template <bool GRAY, int MINB, bool NVDB = false>
 __global__ void __launch_bounds__(kBlock, MINB) k_medium_rs(const DScene sc, const Wavefront W, int *cursor, const int kRsRefillIdle) {
     typedef typename SpecT<GRAY>::type Sp;
     const int n = *W.medium_rs.count;
@@ -241,7 +242,7 @@ __global__ void __launch_bounds__(kBlock, MINB) k_medium_rs(const DScene sc, con
                 if (GRAY) {
                     const DMedium &med = sc.media[s.medium];
                     T_maj = pT_maj; sigma_maj = pSigma; p = pP;
-                    float d = medium_density_value(med, pf);
+                    float d = medium_density_value<NVDB>(med, pf);
                     mp.g = med.g; mp.sigma_a = ld3(med.sigma_a) * d; mp.sigma_s = ld3(med.sigma_s) * d;   // sample_point, GRID branch
                     pend = false;
                 } else {
@@ -279,7 +280,7 @@ __global__ void __launch_bounds__(kBlock, MINB) k_medium_rs(const DScene sc, con
                 pT_maj = s.T_maj * fast_exp3(-(t - s.tMin) * s.segSigma);
                 pP = s.ray.at(t);
                 pSigma = s.segSigma;
-                pf = medium_density_issue(med, pP);
+                pf = medium_density_issue<NVDB>(med, pP);
                 s.T_maj = to_spec<GRAY>(splat(1.f));
                 s.tMin = t;
                 pend = true;

@@ -16,6 +16,7 @@
 #include "host_lightbvh.h"
 #include "host_lightpower.h"
 #include "kernels2.cuh"
+#include "kbin.cuh"
 #include "debug_kernels.cuh"
 
 using namespace vspg;
@@ -57,9 +58,14 @@ struct vspg_ctx {
     int grid_layout = GRID_CELL8;
     int scatter_block = 256;   // VSPG_SCATTER_BLOCK overrides (A/B runs)
     int volscatter_ctas = 2, shade_ctas = 2, scatter_ctas_block = 0;   // resident CTAs/SM of the scatter kernels (occupancy API, per scatter_block)
+    int sort_mode = 0;          // coherence pass (kbin.cuh): bit 0 = medium queue, bit 1 = shadow queue (VSPG_SORT)
+    bool bin_ok = false;        // the scene has a grid medium to bin over
+    int *bin_keys = nullptr, *bin_hist = nullptr, *bin_offsets = nullptr, *sorted_medium = nullptr, *sorted_shadow = nullptr;
+    int prim_kinds = 7;         // primitive kinds of the scene (dshapes.cuh KINDS): 1 = quads only
+    bool any_nvdb = false;      // some medium is a NanoVDB grid: the resampling kernel with the NanoVDB sampler compiled in
     bool grids_ready = false;   // one-wave grids of the grid-stride kernels (occupancy API, vspg_ctx_render.inl)
     int g_generate = 0, g_intersect = 0, g_medium = 0, g_lookup0 = 0, g_lookup1 = 0, g_surface = 0, g_volscatter0 = 0, g_shade0 = 0, g_finish = 0,
-        g_shadow_gray = 0, g_shadow_rgb = 0;
+        g_bin = 148, g_shadow_gray = 0, g_shadow_rgb = 0;
     int rs_occ = 5;               // CTAs/SM the gray resampling kernel is compiled for (VSPG_RS_OCC=4|5, A/B runs)
     int rs_refill = kRsRefillIdleDefault;   // VSPG_RS_REFILL overrides (A/B runs)
     bool all_gray = false;        // every medium has sigma_a / sigma_s equal across RGB => scalar tracking kernels (kmedium_rs.cuh)
@@ -166,6 +172,7 @@ int vspg_create(vspg_ctx **out, int device_ordinal) {
     }
     if (const char *rr = getenv("VSPG_RS_REFILL")) { int v = atoi(rr); if (v >= 1 && v <= 32) ctx->rs_refill = v; }
     if (const char *g = getenv("VSPG_GRAPH")) ctx->use_graph = atoi(g) != 0;
+    if (const char *g = getenv("VSPG_SORT")) ctx->sort_mode = atoi(g) & 3;
     if (const char *ro = getenv("VSPG_RS_OCC")) { int v = atoi(ro); if (v == 4 || v == 5) ctx->rs_occ = v; }
     const char *lay = getenv("VSPG_GRID_LAYOUT");
     if (lay && std::string(lay) == "linear") ctx->grid_layout = GRID_LINEAR;
@@ -262,6 +269,24 @@ int vspg_set_scene(vspg_ctx *ctx, const vspg_scene_desc *s) {
     CK(upload(ctx, ctx->scene_allocs, media.data(), media.size(), &sc.media));
     sc.n_media = s->n_media;
     ctx->all_gray = !getenv("VSPG_NO_GRAY");
+    ctx->any_nvdb = false;
+    ctx->bin_ok = false;
+    for (int i = 0; i < s->n_media && !ctx->bin_ok; i++) {   // binning box = render-space bounds of the first grid medium
+        const vspg_medium &m = s->media[i];
+        if (m.type == VSPG_MEDIUM_HOMOGENEOUS) continue;
+        float lo[3] = {INFINITY, INFINITY, INFINITY}, hi[3] = {-INFINITY, -INFINITY, -INFINITY};
+        for (int c = 0; c < 8; c++) {
+            const float p[3] = {c & 1 ? m.bounds_max[0] : m.bounds_min[0], c & 2 ? m.bounds_max[1] : m.bounds_min[1], c & 4 ? m.bounds_max[2] : m.bounds_min[2]};
+            const float(*M)[4] = m.render_from_medium.m;
+            for (int a = 0; a < 3; a++) {
+                float v = M[a][0] * p[0] + M[a][1] * p[1] + M[a][2] * p[2] + M[a][3];
+                lo[a] = std::min(lo[a], v); hi[a] = std::max(hi[a], v);
+            }
+        }
+        for (int a = 0; a < 3; a++) { sc.bin_lo[a] = lo[a]; sc.bin_scale[a] = hi[a] > lo[a] ? kBinCells / (hi[a] - lo[a]) : 0.f; }
+        ctx->bin_ok = true;
+    }
+    for (const DMedium &d : media) ctx->any_nvdb |= d.type == VSPG_MEDIUM_NANOVDB;
     for (const DMedium &d : media)
         if (d.type == VSPG_MEDIUM_RGBGRID || d.sigma_a[0] != d.sigma_a[1] || d.sigma_a[0] != d.sigma_a[2] || d.sigma_s[0] != d.sigma_s[1] || d.sigma_s[0] != d.sigma_s[2])
             ctx->all_gray = false;
@@ -269,6 +294,7 @@ int vspg_set_scene(vspg_ctx *ctx, const vspg_scene_desc *s) {
     // prims = quads, then triangles stored in the same record (p0,p1,p2 in p00,p10,p01; kind = PRIM_TRIANGLE), then full
     // spheres (kind = PRIM_SPHERE; the host-side record holds the corners of Sphere::Bounds for the BVH build)
     const int nPrims = s->n_quads + s->n_triangles + s->n_spheres;
+    ctx->prim_kinds = (s->n_triangles == 0 && s->n_spheres == 0 && !getenv("VSPG_ALL_KINDS")) ? kKindsQuads : kKindsAll;
     std::vector<vspg_quad> hostPrims(nPrims);
     std::vector<DQuad> quads(nPrims);
     for (int i = 0; i < s->n_triangles; i++) {

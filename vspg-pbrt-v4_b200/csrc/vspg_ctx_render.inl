@@ -5,7 +5,7 @@ enum { Q_A = 0, Q_B = 1, Q_MEDIUM = 2, Q_SURFACE = 3, Q_SHADE = 4, Q_VOLSCATTER 
        Q_CURSORS = 4, Q_INTS = Q_COUNT + Q_CURSORS };  // + per-kernel dynamic work cursors
 
 // Everything the captured wave graph depends on; compared bytewise against the current values before each replay.
-struct WaveGraphKey { DScene sc; Wavefront W; int vgrid, sgrid, sblock, rs_refill, rs_occ, nGridWin; cudaAccessPolicyWindow win; };
+struct WaveGraphKey { DScene sc; Wavefront W; int vgrid, sgrid, sblock, rs_refill, rs_occ, nGridWin, all_gray, any_nvdb, sort_mode, prim_kinds; cudaAccessPolicyWindow win; };
 
 static int ensure_wavefront(vspg_ctx *ctx, unsigned long long total) {
     // Default: up to 16.8 M paths in flight (5.7 GB of the 180 GB).  Measured on C2 (profiles/r01z_summary.md, r02b/c): 2 M ->
@@ -38,6 +38,12 @@ static int ensure_wavefront(vspg_ctx *ctx, unsigned long long total) {
     for (int i = 0; i < Q_COUNT; i++) { qs[i]->items = items + (size_t)i * n; qs[i]->count = ctx->qcounts + i; }
     ctx->phys_q[0] = ctx->W.active; ctx->phys_q[1] = ctx->W.next;
     CK(alloc((void **)&ctx->W.next_sample, sizeof(unsigned long long)));
+    CK(alloc((void **)&ctx->bin_keys, n * sizeof(int)));
+    CK(alloc((void **)&ctx->sorted_medium, n * sizeof(int)));
+    CK(alloc((void **)&ctx->sorted_shadow, n * sizeof(int)));
+    CK(alloc((void **)&ctx->bin_hist, kBins * sizeof(int)));
+    CK(alloc((void **)&ctx->bin_offsets, kBins * sizeof(int)));
+    CK(cudaMemset(ctx->bin_hist, 0, kBins * sizeof(int)));
     CK(alloc((void **)&ctx->d_rv, sizeof(RenderVars)));
     CK(alloc((void **)&ctx->d_iters, sizeof(int)));
     ctx->W.rv = ctx->d_rv;
@@ -113,9 +119,10 @@ int vspg_render(vspg_ctx *ctx, int spp_begin, int spp_end, int spp_stride, int x
             int o = 0; cudaError_t e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&o, kernel, kBlock, 0);
             *out = ctx->sm_count * std::max(1, o); return e;
         };
-        CK(occ(k_generate, &ctx->g_generate)); CK(occ(k_intersect, &ctx->g_intersect)); CK(occ(k_medium, &ctx->g_medium));
-        CK(occ(k_lookup<false>, &ctx->g_lookup0)); CK(occ(k_lookup<true>, &ctx->g_lookup1)); CK(occ(k_surface, &ctx->g_surface));
+        CK(occ(k_generate, &ctx->g_generate)); CK(occ(k_intersect<kKindsAll>, &ctx->g_intersect)); CK(occ(k_medium, &ctx->g_medium));
+        CK(occ(k_lookup<false>, &ctx->g_lookup0)); CK(occ(k_lookup<true>, &ctx->g_lookup1)); CK(occ(k_surface<kKindsAll>, &ctx->g_surface));
         CK(occ(k_volscatter<0>, &ctx->g_volscatter0)); CK(occ(k_shade<0>, &ctx->g_shade0)); CK(occ(k_finish, &ctx->g_finish));
+        CK(occ(k_bin_count, &ctx->g_bin));
         CK(occ(k_shadow<true>, &ctx->g_shadow_gray)); CK(occ(k_shadow<false>, &ctx->g_shadow_rgb));
         ctx->g_surface = ctx->sm_count * 8;   // memory-latency bound with very uneven items: measured better oversubscribed (16.8 vs 18.8 ms)
         ctx->grids_ready = true;
@@ -142,8 +149,9 @@ int vspg_render(vspg_ctx *ctx, int spp_begin, int spp_end, int spp_stride, int x
     }
     // One wave iteration = the stage kernels below, in stream order, over the queues of `Wh`; afterwards every counter but
     // the new active queue's (`keep`) is cleared.  `timed` brackets each stage with events (stage-split measurements only).
-    const int perIter = 9 + (guidedVol ? 3 : 0) + (guidedSurf ? 3 : 0);
-    auto enqueue_iteration = [&](const Wavefront &Wh, int keep, cudaStream_t s, bool timed) -> int {
+    const int sortPasses = ctx->bin_ok ? (ctx->sort_mode & 1) + ((ctx->sort_mode >> 1) & 1) : 0;
+    const int perIter = 9 + (guidedVol ? 3 : 0) + (guidedSurf ? 3 : 0) + 3 * sortPasses;
+    auto enqueue_iteration = [&](const Wavefront &Wh0, int keep, cudaStream_t s, bool timed) -> int {
         auto launch_tracking = [&](auto kernel, int nblocks, auto... args) {
             cudaLaunchConfig_t cfg = {};
             cfg.gridDim = dim3(nblocks); cfg.blockDim = dim3(kBlock); cfg.dynamicSmemBytes = 0; cfg.stream = s;
@@ -152,8 +160,19 @@ int vspg_render(vspg_ctx *ctx, int spp_begin, int spp_end, int spp_stride, int x
         };
 #define VSPG_STAGE(K, launch) do { launch; if (timed) { ctx->launches_kernel[K]++; CK(cudaEventRecord(ctx->ev[K], s)); } } while (0)
         if (timed) CK(cudaEventRecord(ctx->ev[0], s));
-        VSPG_STAGE(VSPG_K_INTERSECT, (k_intersect<<<ctx->g_intersect, kBlock, 0, s>>>(sc, Wh)));
-        if (ctx->all_gray && ctx->rs_occ == 5) CK(launch_tracking(k_medium_rs<true, VSPG_RS_MINB>, ctx->sm_count * VSPG_RS_MINB, sc, Wh, ctx->qcounts + Q_COUNT, ctx->rs_refill));
+        const bool quadsOnly = ctx->prim_kinds == kKindsQuads;   // kernels without the triangle / sphere branches (dshapes.cuh KINDS)
+        if (quadsOnly) VSPG_STAGE(VSPG_K_INTERSECT, (k_intersect<kKindsQuads><<<ctx->g_intersect, kBlock, 0, s>>>(sc, Wh0)));
+        else VSPG_STAGE(VSPG_K_INTERSECT, (k_intersect<kKindsAll><<<ctx->g_intersect, kBlock, 0, s>>>(sc, Wh0)));
+        const int sortMode = ctx->bin_ok ? ctx->sort_mode : 0;
+        auto sort_queue = [&](const Queue &q, int which, int *sorted) {
+            k_bin_count<<<ctx->g_bin, kBlock, 0, s>>>(sc, Wh0, q, which, ctx->bin_keys, ctx->bin_hist);
+            k_bin_scan<<<1, 1024, 0, s>>>(ctx->bin_hist, ctx->bin_offsets);
+            k_bin_scatter<<<ctx->g_bin, kBlock, 0, s>>>(q, ctx->bin_keys, ctx->bin_offsets, sorted);
+        };
+        Wavefront Wh = Wh0;
+        if (sortMode & 1) { sort_queue(Wh0.medium_rs, 0, ctx->sorted_medium); Wh.medium_rs.items = ctx->sorted_medium; }
+        if (ctx->all_gray && ctx->any_nvdb) CK(launch_tracking(k_medium_rs<true, 4, true>, ctx->sm_count * 4, sc, Wh, ctx->qcounts + Q_COUNT, ctx->rs_refill));
+        else if (ctx->all_gray && ctx->rs_occ == 5) CK(launch_tracking(k_medium_rs<true, VSPG_RS_MINB>, ctx->sm_count * VSPG_RS_MINB, sc, Wh, ctx->qcounts + Q_COUNT, ctx->rs_refill));
         else if (ctx->all_gray) CK(launch_tracking(k_medium_rs<true, 4>, ctx->sm_count * 4, sc, Wh, ctx->qcounts + Q_COUNT, ctx->rs_refill));
         else CK(launch_tracking(k_medium_rs<false, 4>, ctx->sm_count * 4, sc, Wh, ctx->qcounts + Q_COUNT, ctx->rs_refill));
         VSPG_STAGE(VSPG_K_MEDIUM, (k_medium<<<ctx->g_medium, kBlock, 0, s>>>(sc, Wh)));
@@ -163,15 +182,19 @@ int vspg_render(vspg_ctx *ctx, int spp_begin, int spp_end, int spp_stride, int x
             k_volscatter<16><<<vgrid, sblock, 0, s>>>(sc, Wh, Wh.vol16);
             VSPG_STAGE(VSPG_K_VOLSCATTER, (k_volscatter<32><<<vgrid, sblock, 0, s>>>(sc, Wh, Wh.vol32)));
         } else VSPG_STAGE(VSPG_K_VOLSCATTER, (k_volscatter<0><<<ctx->g_volscatter0, kBlock, 0, s>>>(sc, Wh, Wh.volscatter)));
-        VSPG_STAGE(VSPG_K_SURFACE, (k_surface<<<ctx->g_surface, kBlock, 0, s>>>(sc, Wh)));
+        if (quadsOnly) VSPG_STAGE(VSPG_K_SURFACE, (k_surface<kKindsQuads><<<ctx->g_surface, kBlock, 0, s>>>(sc, Wh)));
+        else VSPG_STAGE(VSPG_K_SURFACE, (k_surface<kKindsAll><<<ctx->g_surface, kBlock, 0, s>>>(sc, Wh)));
         if (guidedSurf) {
             k_lookup<true><<<ctx->g_lookup1, kBlock, 0, s>>>(sc, Wh, Wh.shade, Wh.sh8, Wh.sh16, Wh.sh32);
             k_shade<8><<<sgrid, sblock, 0, s>>>(sc, Wh, Wh.sh8);
             k_shade<16><<<sgrid, sblock, 0, s>>>(sc, Wh, Wh.sh16);
             VSPG_STAGE(VSPG_K_SHADE, (k_shade<32><<<sgrid, sblock, 0, s>>>(sc, Wh, Wh.sh32)));
         } else VSPG_STAGE(VSPG_K_SHADE, (k_shade<0><<<ctx->g_shade0, kBlock, 0, s>>>(sc, Wh, Wh.shade)));
-        if (ctx->all_gray) VSPG_STAGE(VSPG_K_SHADOW, CK(launch_tracking(k_shadow<true>, ctx->g_shadow_gray, sc, Wh)));
-        else VSPG_STAGE(VSPG_K_SHADOW, CK(launch_tracking(k_shadow<false>, ctx->g_shadow_rgb, sc, Wh)));
+        if (sortMode & 2) { sort_queue(Wh0.shadow, 1, ctx->sorted_shadow); Wh.shadow.items = ctx->sorted_shadow; }
+        if (ctx->all_gray && quadsOnly) VSPG_STAGE(VSPG_K_SHADOW, CK(launch_tracking(k_shadow<true, kKindsQuads>, ctx->g_shadow_gray, sc, Wh)));
+        else if (ctx->all_gray) VSPG_STAGE(VSPG_K_SHADOW, CK(launch_tracking(k_shadow<true, kKindsAll>, ctx->g_shadow_gray, sc, Wh)));
+        else if (quadsOnly) VSPG_STAGE(VSPG_K_SHADOW, CK(launch_tracking(k_shadow<false, kKindsQuads>, ctx->g_shadow_rgb, sc, Wh)));
+        else VSPG_STAGE(VSPG_K_SHADOW, CK(launch_tracking(k_shadow<false, kKindsAll>, ctx->g_shadow_rgb, sc, Wh)));
         VSPG_STAGE(VSPG_K_FINISH, (k_finish<<<ctx->g_finish, kBlock, 0, s>>>(sc, Wh)));
         k_reset_counts<<<1, 32, 0, s>>>(ctx->qcounts, Q_INTS, keep);
 #undef VSPG_STAGE
@@ -201,7 +224,7 @@ int vspg_render(vspg_ctx *ctx, int spp_begin, int spp_end, int spp_stride, int x
         // all of which are compared below; it is rebuilt when any of them changed.
         WaveGraphKey key;
         memset(&key, 0, sizeof key);
-        key.sc = sc; key.W = Wab; key.vgrid = vgrid; key.sgrid = sgrid; key.sblock = sblock; key.rs_refill = ctx->rs_refill; key.rs_occ = ctx->rs_occ;
+        key.sc = sc; key.W = Wab; key.vgrid = vgrid; key.sgrid = sgrid; key.sblock = sblock; key.rs_refill = ctx->rs_refill; key.rs_occ = ctx->rs_occ; key.all_gray = ctx->all_gray; key.prim_kinds = ctx->prim_kinds; key.sort_mode = ctx->bin_ok ? ctx->sort_mode : 0; key.any_nvdb = ctx->any_nvdb;
         key.nGridWin = nGridWin; if (nGridWin) key.win = gridWin[0].val.accessPolicyWindow;
         if (!ctx->wave_exec || memcmp(&key, ctx->wave_key, sizeof key) != 0) {
             if (ctx->wave_exec) { cudaGraphExecDestroy(ctx->wave_exec); ctx->wave_exec = nullptr; }
