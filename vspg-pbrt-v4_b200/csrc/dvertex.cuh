@@ -242,6 +242,7 @@ VD float sphere_light_pdf(const DQuad &q, V3 ctxP, V3 wi, V3 hitP, V3 hitN) {
 
 // lights.cpp:796-818 DiffuseAreaLight::SampleLi -> shapes.cpp:1155-1214, 1254-1280 (area-sampling branch);
 // lights.h:243-250 (point), 316-323 (distant); uniform infinite: allowIncompletePDF (lights.cpp:1022-1023)
+template <int KINDS = kKindsAll>
 VD LiSample sample_li(const DScene &sc, int light, V3 ctxP, V3 ctxNs, float u0, float u1) {
     LiSample ls; ls.valid = false; ls.delta = false; ls.pdf = 0;
     const DLight &l = sc.lights[light];
@@ -260,7 +261,7 @@ VD LiSample sample_li(const DScene &sc, int light, V3 ctxP, V3 ctxNs, float u0, 
     }
     if (l.type == VSPG_LIGHT_UNIFORM_INFINITE) return ls;
     const DQuad &q = sc.quads[l.shape_index];   // global primitive id
-    if (q.kind != PRIM_QUAD) {
+    if ((KINDS & 6) && q.kind != PRIM_QUAD) {
         V3 p, pErr, n; float pdf = 0;
         bool ok = q.kind == PRIM_TRIANGLE ? sample_triangle_light(q, ctxP, ctxNs, u0, u1, &p, &pErr, &n, &pdf)
                                           : sample_sphere_light(q, ctxP, u0, u1, &p, &pErr, &n, &pdf);
@@ -330,6 +331,7 @@ VD LiSample sample_li(const DScene &sc, int light, V3 ctxP, V3 ctxNs, float u0, 
 // (shapes.cpp:1337-1341, shapes.h:1133-1137, 366-370) -- not the path's own hit, whose ray may have been re-spawned at
 // interfaces on the way.  `spawnO` is that ray's origin: OffsetRayOrigin(ctx.pi, ctx.n, wi), i.e. where the path left
 // its previous vertex (ctxP itself for a medium vertex).
+template <int KINDS = kKindsAll>
 VD float area_pdf_li(const DScene &sc, int light, V3 ctxP, V3 ctxNs, V3 wi, V3 spawnO) {
     const int prim = sc.lights[light].shape_index;
     const DQuad &q = sc.quads[prim];
@@ -337,15 +339,15 @@ VD float area_pdf_li(const DScene &sc, int light, V3 ctxP, V3 ctxNs, V3 wi, V3 s
     {
         float t, u = 0, v = 0, b2;
         bool ok;
-        if (q.kind == PRIM_SPHERE) { V3 pObj; ok = intersect_sphere(spawnO, wi, inff(), ld3(q.p00), q.p10[0], &t, &pObj); }
-        else if (q.kind == PRIM_TRIANGLE) ok = intersect_triangle(spawnO, wi, inff(), ld3(q.p00), ld3(q.p10), ld3(q.p01), &u, &v, &b2, &t);
+        if ((KINDS & 4) && q.kind == PRIM_SPHERE) { V3 pObj; ok = intersect_sphere(spawnO, wi, inff(), ld3(q.p00), q.p10[0], &t, &pObj); }
+        else if ((KINDS & 2) && q.kind == PRIM_TRIANGLE) ok = intersect_triangle(spawnO, wi, inff(), ld3(q.p00), ld3(q.p10), ld3(q.p01), &u, &v, &b2, &t);
         else ok = intersect_bilinear_patch(spawnO, wi, ld3(q.p00), ld3(q.p10), ld3(q.p01), ld3(q.p11), &u, &v, &t);
         if (!ok) return 0;
         sh.t = t; sh.u = u; sh.v = v; sh.prim = prim;
     }
-    const SurfaceIntr hit = make_intr(sc, sh, spawnO, wi, -1);
-    if (q.kind == PRIM_TRIANGLE) return triangle_light_pdf(q, ctxP, ctxNs, wi, hit.p, hit.n);
-    if (q.kind == PRIM_SPHERE) return sphere_light_pdf(q, ctxP, wi, hit.p, hit.n);
+    const SurfaceIntr hit = make_intr<KINDS>(sc, sh, spawnO, wi, -1);
+    if ((KINDS & 2) && q.kind == PRIM_TRIANGLE) return triangle_light_pdf(q, ctxP, ctxNs, wi, hit.p, hit.n);
+    if ((KINDS & 4) && q.kind == PRIM_SPHERE) return sphere_light_pdf(q, ctxP, wi, hit.p, hit.n);
     V3 p00 = ld3(q.p00), p10 = ld3(q.p10), p01 = ld3(q.p01), p11 = ld3(q.p11);
     float pdf = 1;
     if (q.is_rect) {   // shapes.cpp:1352-1368 PDF for a sample in the spherical rectangle

@@ -121,6 +121,7 @@ VD void shadow_store(const PathSoA &P, int s, const ShadowRec &r) {
 // streams; the G-lane kernels then only skip the three sampler dimensions and read the record back.  Same
 // arithmetic, same stream positions: bit-identical to sampling inside the scatter kernel.
 struct NeePre { bool valid, delta; V3 L, wi, pLight, pLightErr, nLight; float p_l; };
+template <int KINDS = kKindsAll>
 VD NeePre nee_presample(const DScene &sc, Rng rng, V3 ctxP, V3 ctxNs) {
     NeePre np; np.valid = false; np.delta = false; np.p_l = 0;
     float u = rng.uniform();
@@ -128,7 +129,7 @@ VD NeePre nee_presample(const DScene &sc, Rng rng, V3 ctxP, V3 ctxNs) {
     int light = sample_light(sc, u, &pmf, ctxP, ctxNs);
     float ul0 = rng.uniform(), ul1 = rng.uniform();
     if (light < 0) return np;
-    LiSample ls = sample_li(sc, light, ctxP, ctxNs, ul0, ul1);
+    LiSample ls = sample_li<KINDS>(sc, light, ctxP, ctxNs, ul0, ul1);
     if (!(ls.valid && nonzero(ls.L) && ls.pdf != 0)) return np;
     np.valid = true; np.delta = ls.delta; np.L = ls.L; np.wi = ls.wi; np.pLight = ls.pLight; np.pLightErr = ls.pLightErr; np.nLight = ls.nLight;
     np.p_l = pmf * ls.pdf;
@@ -205,7 +206,7 @@ template <int G> VD void scatter_phase_sync() {
 // (field/Field.h:114-150; guiding.h:83-109 / 383-398 front half).  One THREAD per vertex: draws the sampler's `v`,
 // walks the KD tree, picks the stochastic neighbour, and sorts the vertex into the queue of the lane-group width its
 // mixture needs (<= 8 lobes -> G8, <= 16 -> G16, else G32; vertices without a usable region go to G8).
-template <bool SURFACE>
+template <bool SURFACE, int KINDS = kKindsAll>
 __global__ void __launch_bounds__(kBlock) k_lookup(const DScene sc, const Wavefront W, const Queue in, const Queue q8, const Queue q16, const Queue q32) {
     const int n = *in.count;
     unsigned lookups = 0;
@@ -237,10 +238,10 @@ __global__ void __launch_bounds__(kBlock) k_lookup(const DScene sc, const Wavefr
                     float4 a = W.P.o_dx[slot], b = W.P.d_med[slot], hr = W.P.hit[slot];
                     Hit h; h.t = hr.x; h.u = hr.y; h.v = hr.z; h.prim = __float_as_int(hr.w);
                     V3 ro(a.x, a.y, a.z), rd(a.w, b.x, b.y);
-                    SurfaceIntr isect = make_intr(sc, h, ro, rd, __float_as_int(b.z));
-                    nee_store(W.P, slot, nee_presample(sc, rng, offset_ray_origin(isect.p, isect.pError, isect.n, isect.wo), isect.ns));
+                    SurfaceIntr isect = make_intr<KINDS>(sc, h, ro, rd, __float_as_int(b.z));
+                    nee_store(W.P, slot, nee_presample<KINDS>(sc, rng, offset_ray_origin(isect.p, isect.pError, isect.n, isect.wo), isect.ns));
                 }
-            } else nee_store(W.P, slot, nee_presample(sc, rng, p, V3()));
+            } else nee_store(W.P, slot, nee_presample<KINDS>(sc, rng, p, V3()));
         }
         queue_push(q8, nl <= 8, slot);
         queue_push(q16, nl > 8 && nl <= 16, slot);

@@ -59,7 +59,7 @@ __global__ void __launch_bounds__(kBlock, VSPG_SURFACE_MINB) k_surface(const DSc
                     add_emission(Le, [&](V3 prevP, V3 prevNs) {
                         V3 spawnO = prevP;   // medium vertex: ctx.pi is exact and n = 0, SpawnRay starts at p
                         if (nonzero(prevNs)) { float4 po = W.P.prev_o[slot]; spawnO = V3(po.x, po.y, po.z); }
-                        return light_pmf(sc, isect.areaLight, prevP, prevNs) * area_pdf_li(sc, isect.areaLight, prevP, prevNs, rd, spawnO);
+                        return light_pmf(sc, isect.areaLight, prevP, prevNs) * area_pdf_li<KINDS>(sc, isect.areaLight, prevP, prevNs, rd, spawnO);
                     });
             }
             if (isect.material < 0) {  // interface material: SkipIntersection (interaction.cpp:91-97)
@@ -89,7 +89,7 @@ struct ShadeKeep { float p[3], pe[3], n[3], ns[3]; int mIn, mOut, rayMed, hasIf;
 #ifndef VSPG_SHADE_MINB
 #define VSPG_SHADE_MINB 3
 #endif
-template <int G>
+template <int G, int KINDS = kKindsAll>
 __global__ void __launch_bounds__(G > 0 ? 256 : kBlock, G > 0 ? VSPG_SHADE_MINB : 1) k_shade(const DScene sc, const Wavefront W, const Queue in) {
     __shared__ ShadeKeep keep_s[G > 0 ? 256 / G : kBlock];
     ShadeKeep &K = keep_s[G > 0 ? threadIdx.x / (G > 0 ? G : 1) : threadIdx.x];
@@ -113,7 +113,7 @@ __global__ void __launch_bounds__(G > 0 ? 256 : kBlock, G > 0 ? VSPG_SHADE_MINB 
             Hit h; h.t = hr.x; h.u = hr.y; h.v = hr.z; h.prim = __float_as_int(hr.w);
             V3 ro(a.x, a.y, a.z);
             rd = V3(a.w, b.x, b.y);
-            SurfaceIntr isect = make_intr(sc, h, ro, rd, __float_as_int(b.z));
+            SurfaceIntr isect = make_intr<KINDS>(sc, h, ro, rd, __float_as_int(b.z));
             woN = isect.wo;
             if (leader) {
                 K.p[0] = isect.p.x; K.p[1] = isect.p.y; K.p[2] = isect.p.z;
@@ -137,7 +137,7 @@ __global__ void __launch_bounds__(G > 0 ? 256 : kBlock, G > 0 ? VSPG_SHADE_MINB 
                 valid = __float_as_int(r.w) & 1; wi = V3(r.x, r.y, r.z);
             } else {
                 V3 ctxP = offset_ray_origin(ld3(K.p), ld3(K.pe), ld3(K.n), woN);  // reflective-only BSDF (vspg.cpp:1147-1149)
-                NeePre ls = nee_presample(sc, rng, ctxP, ld3(K.ns));
+                NeePre ls = nee_presample<KINDS>(sc, rng, ctxP, ld3(K.ns));
                 rng.uniform(); rng.uniform(); rng.uniform();
                 nee_store(W.P, slot, ls);
                 valid = ls.valid; wi = ls.wi;

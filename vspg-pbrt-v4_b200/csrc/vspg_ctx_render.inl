@@ -99,7 +99,7 @@ int vspg_render(vspg_ctx *ctx, int spp_begin, int spp_end, int spp_stride, int x
     if (ctx->scatter_ctas_block != sblock) {
         int ov = 0, os = 0;
         CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&ov, k_volscatter<8>, sblock, 0));
-        CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&os, k_shade<8>, sblock, 0));
+        CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&os, k_shade<8, kKindsAll>, sblock, 0));
         ctx->volscatter_ctas = std::max(1, ov); ctx->shade_ctas = std::max(1, os); ctx->scatter_ctas_block = sblock;
         if (const char *e = getenv("VSPG_SCATTER_CTAS")) { int v = atoi(e); if (v >= 1 && v <= 32) ctx->volscatter_ctas = ctx->shade_ctas = v; }
     }
@@ -120,8 +120,8 @@ int vspg_render(vspg_ctx *ctx, int spp_begin, int spp_end, int spp_stride, int x
             *out = ctx->sm_count * std::max(1, o); return e;
         };
         CK(occ(k_generate, &ctx->g_generate)); CK(occ(k_intersect<kKindsAll>, &ctx->g_intersect)); CK(occ(k_medium, &ctx->g_medium));
-        CK(occ(k_lookup<false>, &ctx->g_lookup0)); CK(occ(k_lookup<true>, &ctx->g_lookup1)); CK(occ(k_surface<kKindsAll>, &ctx->g_surface));
-        CK(occ(k_volscatter<0>, &ctx->g_volscatter0)); CK(occ(k_shade<0>, &ctx->g_shade0)); CK(occ(k_finish, &ctx->g_finish));
+        CK(occ(k_lookup<false, kKindsAll>, &ctx->g_lookup0)); CK(occ(k_lookup<true, kKindsAll>, &ctx->g_lookup1)); CK(occ(k_surface<kKindsAll>, &ctx->g_surface));
+        CK(occ(k_volscatter<0>, &ctx->g_volscatter0)); CK(occ(k_shade<0, kKindsAll>, &ctx->g_shade0)); CK(occ(k_finish, &ctx->g_finish));
         CK(occ(k_bin_count, &ctx->g_bin));
         CK(occ(k_shadow<true>, &ctx->g_shadow_gray)); CK(occ(k_shadow<false>, &ctx->g_shadow_rgb));
         ctx->g_surface = ctx->sm_count * 8;   // memory-latency bound with very uneven items: measured better oversubscribed (16.8 vs 18.8 ms)
@@ -177,7 +177,8 @@ int vspg_render(vspg_ctx *ctx, int spp_begin, int spp_end, int spp_stride, int x
         else CK(launch_tracking(k_medium_rs<false, 4>, ctx->sm_count * 4, sc, Wh, ctx->qcounts + Q_COUNT, ctx->rs_refill));
         VSPG_STAGE(VSPG_K_MEDIUM, (k_medium<<<ctx->g_medium, kBlock, 0, s>>>(sc, Wh)));
         if (guidedVol) {
-            k_lookup<false><<<ctx->g_lookup0, kBlock, 0, s>>>(sc, Wh, Wh.volscatter, Wh.vol8, Wh.vol16, Wh.vol32);
+            if (quadsOnly) k_lookup<false, kKindsQuads><<<ctx->g_lookup0, kBlock, 0, s>>>(sc, Wh, Wh.volscatter, Wh.vol8, Wh.vol16, Wh.vol32);
+            else k_lookup<false, kKindsAll><<<ctx->g_lookup0, kBlock, 0, s>>>(sc, Wh, Wh.volscatter, Wh.vol8, Wh.vol16, Wh.vol32);
             k_volscatter<8><<<vgrid, sblock, 0, s>>>(sc, Wh, Wh.vol8);
             k_volscatter<16><<<vgrid, sblock, 0, s>>>(sc, Wh, Wh.vol16);
             VSPG_STAGE(VSPG_K_VOLSCATTER, (k_volscatter<32><<<vgrid, sblock, 0, s>>>(sc, Wh, Wh.vol32)));
@@ -185,10 +186,17 @@ int vspg_render(vspg_ctx *ctx, int spp_begin, int spp_end, int spp_stride, int x
         if (quadsOnly) VSPG_STAGE(VSPG_K_SURFACE, (k_surface<kKindsQuads><<<ctx->g_surface, kBlock, 0, s>>>(sc, Wh)));
         else VSPG_STAGE(VSPG_K_SURFACE, (k_surface<kKindsAll><<<ctx->g_surface, kBlock, 0, s>>>(sc, Wh)));
         if (guidedSurf) {
-            k_lookup<true><<<ctx->g_lookup1, kBlock, 0, s>>>(sc, Wh, Wh.shade, Wh.sh8, Wh.sh16, Wh.sh32);
-            k_shade<8><<<sgrid, sblock, 0, s>>>(sc, Wh, Wh.sh8);
-            k_shade<16><<<sgrid, sblock, 0, s>>>(sc, Wh, Wh.sh16);
-            VSPG_STAGE(VSPG_K_SHADE, (k_shade<32><<<sgrid, sblock, 0, s>>>(sc, Wh, Wh.sh32)));
+            if (quadsOnly) {
+                k_lookup<true, kKindsQuads><<<ctx->g_lookup1, kBlock, 0, s>>>(sc, Wh, Wh.shade, Wh.sh8, Wh.sh16, Wh.sh32);
+                k_shade<8, kKindsQuads><<<sgrid, sblock, 0, s>>>(sc, Wh, Wh.sh8);
+                k_shade<16, kKindsQuads><<<sgrid, sblock, 0, s>>>(sc, Wh, Wh.sh16);
+                VSPG_STAGE(VSPG_K_SHADE, (k_shade<32, kKindsQuads><<<sgrid, sblock, 0, s>>>(sc, Wh, Wh.sh32)));
+            } else {
+                k_lookup<true, kKindsAll><<<ctx->g_lookup1, kBlock, 0, s>>>(sc, Wh, Wh.shade, Wh.sh8, Wh.sh16, Wh.sh32);
+                k_shade<8, kKindsAll><<<sgrid, sblock, 0, s>>>(sc, Wh, Wh.sh8);
+                k_shade<16, kKindsAll><<<sgrid, sblock, 0, s>>>(sc, Wh, Wh.sh16);
+                VSPG_STAGE(VSPG_K_SHADE, (k_shade<32, kKindsAll><<<sgrid, sblock, 0, s>>>(sc, Wh, Wh.sh32)));
+            }
         } else VSPG_STAGE(VSPG_K_SHADE, (k_shade<0><<<ctx->g_shade0, kBlock, 0, s>>>(sc, Wh, Wh.shade)));
         if (sortMode & 2) { sort_queue(Wh0.shadow, 1, ctx->sorted_shadow); Wh.shadow.items = ctx->sorted_shadow; }
         if (ctx->all_gray && quadsOnly) VSPG_STAGE(VSPG_K_SHADOW, CK(launch_tracking(k_shadow<true, kKindsQuads>, ctx->g_shadow_gray, sc, Wh)));
