@@ -17,7 +17,7 @@ def main(path, out, note):
     ix = {k: i for i, k in enumerate(rows[h])}
     per = {}
     for r in rows[h + 1:]:
-        if len(r) <= ix["Metric Value"] or r[ix["Metric Name"]] not in METRICS or "vspg::" not in r[ix["Kernel Name"]]:
+        if len(r) <= ix["Metric Value"] or r[ix["Metric Name"]] not in METRICS or not re.match(r"^(void )?(vspg::)?k_", r[ix["Kernel Name"]]):
             continue   # (workload builders may run torch kernels of their own: not part of the render)
         name = re.sub(r"^void ", "", r[ix["Kernel Name"]]).replace("vspg::", "")
         name = name.split("(vspg")[0].split("(DScene")[0].strip()
