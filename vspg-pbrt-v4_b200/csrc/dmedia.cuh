@@ -15,6 +15,7 @@ VD V3 ld3(const float *p) { return V3(p[0], p[1], p[2]); }
 // util/vecmath.h Bounds3::Offset
 VD V3 bounds_offset(const DMedium &m, V3 p) {
     V3 o(p.x - m.bmin[0], p.y - m.bmin[1], p.z - m.bmin[2]);
+    if (m.extPow2 == 7) return V3(o.x * m.invExt[0], o.y * m.invExt[1], o.z * m.invExt[2]);   // extents 2^k: the product is the quotient, exactly
     if (m.bmax[0] > m.bmin[0]) o.x /= m.bmax[0] - m.bmin[0];
     if (m.bmax[1] > m.bmin[1]) o.y /= m.bmax[1] - m.bmin[1];
     if (m.bmax[2] > m.bmin[2]) o.z /= m.bmax[2] - m.bmin[2];
@@ -70,6 +71,9 @@ VD void apply_inverse_ray(const DMedium &m, V3 ro, V3 rd, float *tMax, V3 *oOut,
     *oOut = om; *dOut = d;
 }
 VD V3 apply_inverse_point(const DMedium &m, V3 p) {  // util/transform.h Transform::ApplyInverse(Point3)
+    // pure translation: (1 * p.x + 0 * p.y) + (0 * p.z + t) is p.x + t in value (the zero products only ever decide the
+    // sign of a zero result, which no consumer of the point distinguishes), and wp == 1
+    if (m.xlateOnly) return V3(p.x + m.mInv[0][3], p.y + m.mInv[1][3], p.z + m.mInv[2][3]);
     float xp = (m.mInv[0][0] * p.x + m.mInv[0][1] * p.y) + (m.mInv[0][2] * p.z + m.mInv[0][3]);
     float yp = (m.mInv[1][0] * p.x + m.mInv[1][1] * p.y) + (m.mInv[1][2] * p.z + m.mInv[1][3]);
     float zp = (m.mInv[2][0] * p.x + m.mInv[2][1] * p.y) + (m.mInv[2][2] * p.z + m.mInv[2][3]);

@@ -31,6 +31,10 @@ struct DMedium {
     int imin[3];
     float nvInv[9], nvVec[3];
     float densityOffset, bg;       // bg = 0 for pbrt's own grids (SampledGrid::Lookup outside the grid)
+    // exact shortcuts, set by set_scene when they are bit-neutral (dmedia.cuh): mInv is a pure translation; the bounds'
+    // extent along an axis is a power of two, so that x / extent == x * (1 / extent) for every x
+    int xlateOnly, extPow2;        // extPow2: bit a set = axis a
+    float invExt[3];
 };
 
 // One surface primitive: a bilinear patch (p00,p10,p01,p11) or a triangle (p0,p1,p2 in p00,p10,p01; p11 unused).

@@ -230,6 +230,23 @@ int vspg_set_scene(vspg_ctx *ctx, const vspg_scene_desc *s) {
         memcpy(d.mInv, m.render_from_medium.mInv, sizeof d.mInv);
         d.sigma_scale = m.sigma_scale; d.g = m.g; d.nx = m.nx; d.ny = m.ny; d.nz = m.nz;
         d.layout = GRID_LINEAR;
+        {   // exact shortcuts (dscene.cuh DMedium::xlateOnly / extPow2)
+            const float(*I)[4] = m.render_from_medium.mInv;
+            bool x = true;
+            for (int r = 0; r < 4; r++)
+                for (int c = 0; c < 4; c++) {
+                    if (r < 3 && c == 3) { if (!std::isfinite(I[r][c])) x = false; continue; }
+                    if (I[r][c] != (r == c ? 1.f : 0.f)) x = false;
+                }
+            d.xlateOnly = x && !getenv("VSPG_NO_SHORTCUTS");
+            d.extPow2 = 0;
+            for (int a = 0; a < 3; a++) {
+                float e = m.bounds_max[a] - m.bounds_min[a];
+                int ex; float mant = std::frexp(e, &ex);
+                d.invExt[a] = 1.f / e;
+                if (e > 0 && mant == 0.5f && ex > -100 && ex < 100 && !getenv("VSPG_NO_SHORTCUTS")) d.extPow2 |= 1 << a;
+            }
+        }
         if (m.type == VSPG_MEDIUM_HOMOGENEOUS) continue;
         const bool scalarGrid = m.type == VSPG_MEDIUM_GRID || m.type == VSPG_MEDIUM_NANOVDB;
         if (m.type == VSPG_MEDIUM_NANOVDB) {
