@@ -19,6 +19,42 @@ __global__ void k_build_cells(const float *density, int nx, int ny, int nz, floa
     }
 }
 
+// Majorant grid of a uniformgrid / rgbgrid medium (media.cpp:256-269, 393-408 with util/containers.h:838-855 MaxValue):
+// one CTA per majorant cell takes the maximum over the voxel box MaxValue visits.  A maximum of floats does not depend
+// on the order, so this equals the host loop (host_util.h build_majorant_grid) bit for bit.  comps = 1: density grid;
+// comps = 3: per-voxel max of the three channels of `a` and of `b` (either may be null => 1), out = scale * (maxA + maxB).
+__global__ void __launch_bounds__(256) k_build_majorant(const float *a, const float *b, int comps, float scale, int nx, int ny, int nz, int rx, int ry, int rz, float *out) {
+    __shared__ float red[2][256];
+    const int cell = blockIdx.x, x = cell % rx, y = (cell / rx) % ry, z = cell / (rx * ry);
+    const float p0[3] = {float(x) / rx, float(y) / ry, float(z) / rz}, p1[3] = {float(x + 1) / rx, float(y + 1) / ry, float(z + 1) / rz};
+    const int n[3] = {nx, ny, nz};
+    int lo[3], hi[3];
+    for (int k = 0; k < 3; k++) {
+        lo[k] = max((int)floorf(p0[k] * n[k] - .5f), 0);
+        hi[k] = min((int)floorf(p1[k] * n[k] - .5f) + 1, n[k] - 1);
+    }
+    auto at = [&](const float *g, int vx, int vy, int vz) -> float {
+        if (vx < 0 || vy < 0 || vz < 0 || vx >= nx || vy >= ny || vz >= nz) return 0.f;   // (MaxValue starts from Lookup(lo), which may lie outside)
+        const float *q = g + (size_t)comps * ((size_t)(vz * ny + vy) * nx + vx);
+        return comps == 1 ? q[0] : fmaxf(q[0], fmaxf(q[1], q[2]));
+    };
+    float ma = a ? at(a, lo[0], lo[1], lo[2]) : 1.f, mb = b ? at(b, lo[0], lo[1], lo[2]) : 1.f;
+    const int ex = hi[0] - lo[0] + 1, ey = hi[1] - lo[1] + 1, ez = hi[2] - lo[2] + 1;
+    const long long total = (ex > 0 && ey > 0 && ez > 0) ? (long long)ex * ey * ez : 0;
+    for (long long i = threadIdx.x; i < total; i += blockDim.x) {
+        int vx = lo[0] + (int)(i % ex), vy = lo[1] + (int)((i / ex) % ey), vz = lo[2] + (int)(i / ((long long)ex * ey));
+        if (a) ma = fmaxf(ma, at(a, vx, vy, vz));
+        if (b) mb = fmaxf(mb, at(b, vx, vy, vz));
+    }
+    red[0][threadIdx.x] = ma; red[1][threadIdx.x] = mb;
+    __syncthreads();
+    for (int s = 128; s > 0; s >>= 1) {
+        if (threadIdx.x < s) { red[0][threadIdx.x] = fmaxf(red[0][threadIdx.x], red[0][threadIdx.x + s]); red[1][threadIdx.x] = fmaxf(red[1][threadIdx.x], red[1][threadIdx.x + s]); }
+        __syncthreads();
+    }
+    if (threadIdx.x == 0) out[cell] = comps == 1 ? red[0][0] : scale * (red[0][0] + red[1][0]);
+}
+
 // DDAMajorantIterator segments for explicit rays (already normalised d, tMax given)
 __global__ void k_debug_segments(const DScene sc, int medium, int n, const float *rays7, int maxSeg, vspg_segment *out, int *outCount) {
     for (int i = gtid(); i < n; i += gstride()) {

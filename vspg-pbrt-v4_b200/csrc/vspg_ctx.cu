@@ -267,10 +267,17 @@ int vspg_set_scene(vspg_ctx *ctx, const vspg_scene_desc *s) {
         }
         size_t nmaj = (size_t)m.maj_res[0] * m.maj_res[1] * m.maj_res[2];
         if (m.majorant) CK(upload(ctx, ctx->scene_allocs, m.majorant, nmaj, &d.majorant));
-        else {
+        else if (getenv("VSPG_HOST_MAJORANT")) {
             std::vector<float> maj(nmaj);
             build_majorant_grid(&m, maj.data());
             CK(upload(ctx, ctx->scene_allocs, maj.data(), nmaj, &d.majorant));
+        } else {   // on the device, from the grids just uploaded (exact: a maximum has no rounding)
+            void *dm = nullptr;
+            CK(dev_alloc(ctx, ctx->scene_allocs, &dm, nmaj * sizeof(float)));
+            if (m.type == VSPG_MEDIUM_GRID) k_build_majorant<<<(int)nmaj, 256>>>(d.density, nullptr, 1, 1.f, m.nx, m.ny, m.nz, m.maj_res[0], m.maj_res[1], m.maj_res[2], (float *)dm);
+            else k_build_majorant<<<(int)nmaj, 256>>>(d.sa_rgb, d.ss_rgb, 3, m.sigma_scale, m.nx, m.ny, m.nz, m.maj_res[0], m.maj_res[1], m.maj_res[2], (float *)dm);
+            CK(cudaGetLastError());
+            d.majorant = (const float *)dm;
         }
         if (scalarGrid && ctx->grid_layout == GRID_CELL8) {
             size_t ncell = (size_t)(m.nx + 1) * (m.ny + 1) * (m.nz + 1);
