@@ -165,7 +165,7 @@ struct PathFlags {
 struct Queue { int *items; int *count; };
 
 // Per-render arguments of vspg_render (window, sample-index range, sampler seed), uploaded before each render.
-struct RenderVars { unsigned long long total_samples; int x0, y0, x1, y1, spp_begin, spp_stride, n_spp, seed; };
+struct RenderVars { unsigned long long total_samples; int x0, y0, x1, y1, spp_begin, spp_stride, n_spp, seed, band_rows; };
 
 struct Wavefront {
     PathSoA P;

@@ -23,7 +23,17 @@ VD bool regenerate(const DScene &sc, const Wavefront &W, int slot, PathRegs &r) 
     const RenderVars rv = *W.rv;
     if (id >= rv.total_samples) return false;
     const int w = rv.x1 - rv.x0, npix = w * (rv.y1 - rv.y0);
-    int s = (int)(id / (unsigned long long)npix), pix = (int)(id % (unsigned long long)npix);
+    int s, pix;
+    if (rv.band_rows > 0) {
+        // band-major order: all sample passes of a band of rows before the next band, so that the paths in flight stay in
+        // one slab of the scene (a DRAM-resident grid is then read through L2; measured on C4, profiles/r02_summary.md)
+        const unsigned long long perBand = (unsigned long long)w * rv.band_rows * rv.n_spp;
+        const int band = (int)(id / perBand);
+        const unsigned long long r = id % perBand;
+        const int yb = band * rv.band_rows, rows = min(rv.band_rows, (rv.y1 - rv.y0) - yb), bandPix = w * rows;
+        s = (int)(r / (unsigned long long)bandPix);
+        pix = yb * w + (int)(r % (unsigned long long)bandPix);
+    } else { s = (int)(id / (unsigned long long)npix); pix = (int)(id % (unsigned long long)npix); }
     int px = rv.x0 + pix % w, py = rv.y0 + pix / w;
     generate_camera_path(sc, rv.seed, px, py, rv.spp_begin + s * rv.spp_stride, r);
     path_store(W.P, slot, r);

@@ -90,6 +90,12 @@ int vspg_render(vspg_ctx *ctx, int spp_begin, int spp_end, int spp_stride, int x
         RenderVars *hv = reinterpret_cast<RenderVars *>(ctx->h_pinned + 4);
         hv->total_samples = total; hv->x0 = x0; hv->y0 = y0; hv->x1 = x1; hv->y1 = y1;
         hv->spp_begin = spp_begin; hv->spp_stride = spp_stride; hv->n_spp = nspp; hv->seed = seed;
+        // band-major sample order when the render is larger than the wavefront: bands of ~1/4 of the paths in flight
+        hv->band_rows = 0;
+        if (ctx->band_mode != 0 && total > (unsigned long long)ctx->capacity) {
+            long long rows = ctx->band_mode > 0 ? ctx->band_mode : (long long)(ctx->capacity / 4) / ((long long)(x1 - x0) * nspp);
+            hv->band_rows = (int)std::max<long long>(1, std::min<long long>(rows, y1 - y0));
+        }
         CK(cudaMemcpyAsync(ctx->d_rv, hv, sizeof(RenderVars), cudaMemcpyHostToDevice, st));
     }
     CK(cudaMemsetAsync(ctx->qcounts, 0, Q_INTS * sizeof(int), st));
