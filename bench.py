@@ -465,20 +465,23 @@ def run_b200(args):
         # ---- what only a profiler can count: DRAM bytes and issued instructions, from the committed ncu metric pass of this
         # workload (tools/ncu_metrics_summary.py -> profiles/); the durations they are divided by are this run's own
         prof_path = os.path.join(ROOT, "profiles", f"r02_ncu_metrics_{args.workload}.json")
-        if os.path.exists(prof_path) and not args.spp and args.res_scale == 1.0:
+        if os.path.exists(prof_path) and args.res_scale == 1.0:
             prof = json.load(open(prof_path))
+            # the profiled render may have fewer spp than this run (ncu replays every launch): instruction counts scale
+            # with the number of paths, per-launch DRAM bytes are quoted for the profiled wave size
+            inst_scale = (cfg.spp / prof["spp"]) if prof.get("spp") else 1.0
             dk = max((k for k in prof["kernels"] if k.startswith("k_" + tracked)), key=lambda k: prof["kernels"][k]["ms"], default=None)
             if dk:
                 roofline["traffic"] = prof["kernels"][dk]["dram_bytes_per_launch"]
                 roofline["traffic_kernel"] = dk
-                roofline["traffic_source"] = os.path.relpath(prof_path, ROOT)
+                roofline["traffic_source"] = os.path.relpath(prof_path, ROOT) + (f" (profiled at {prof['spp']} spp)" if prof.get("spp") else "")
             big = max(names, key=lambda k: ks[k]["ms"])
             if big in prof["stages"]:
                 ps_ = prof["stages"][big]
                 sm_mhz = (clk or {}).get("sm_mhz") or 1965.0
                 issue_peak = 148 * 4 * sm_mhz * 1e6          # warp instructions / s: 148 SMs x 4 schedulers x SM clock under load
-                ach = ps_["warp_inst"] / max(1e-12, ks[big]["ms"] / stat_steps * 1e-3)
-                roofline["issue"] = {"stage": big, "warp_inst_per_step": ps_["warp_inst"], "lanes_per_inst": ps_["lanes_per_inst"],
+                ach = ps_["warp_inst"] * inst_scale / max(1e-12, ks[big]["ms"] / stat_steps * 1e-3)
+                roofline["issue"] = {"stage": big, "warp_inst_per_step": ps_["warp_inst"] * inst_scale, "lanes_per_inst": ps_["lanes_per_inst"],
                                      "stage_ms_per_step": ks[big]["ms"] / stat_steps, "achieved": ach / 1e9, "peak": issue_peak / 1e9, "unit": "Gwarp-inst/s",
                                      "frac": ach / issue_peak, "useful_lane_frac": ach / issue_peak * ps_["lanes_per_inst"] / 32.0,
                                      "source": os.path.relpath(prof_path, ROOT)}

@@ -12,6 +12,7 @@ kw = {}
 if len(sys.argv) > 3: kw["spp"] = int(sys.argv[3])
 cfg = configs.BUILDERS[name](**kw)
 ctx = api.Context(0)
+if os.environ.get("VSPG_AB_CAPACITY"): ctx.set_capacity(int(os.environ["VSPG_AB_CAPACITY"]))
 ctx.set_scene(cfg.scene); ctx.set_guiding(cfg.guiding); ctx.set_integrator(cfg.ip)
 ctx.film_clear(); ctx.render(0, cfg.spp, seed=0)           # warm-up
 ctx.kernel_stats(True)                                     # switch stage timing on

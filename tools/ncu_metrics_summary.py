@@ -1,17 +1,17 @@
 """Summarises an `ncu --metrics ... --csv` launch list (long format, one row per metric per launch) into per-kernel and
 per-stage totals: launches, time, warp / thread instructions, DRAM bytes.  Written as JSON for profiles/ and read back
 by bench.py (roofline.traffic, roofline.issue).
-    python tools/ncu_metrics_summary.py gpurun_out/x.csv profiles/r02_ncu_metrics_C2.json "C2 1 render, spp 64" """
+    python tools/ncu_metrics_summary.py gpurun_out/x.csv profiles/r02_ncu_metrics_C2.json "C2 1 render, spp 64" [spp of the profiled render] """
 import csv, json, re, sys
 
-STAGE = [("k_generate", "generate"), ("k_intersect", "intersect"), ("k_medium", "medium"), ("k_lookup<0>", "volscatter"), ("k_volscatter", "volscatter"),
-         ("k_surface", "surface"), ("k_lookup<1>", "shade"), ("k_shade", "shade"), ("k_shadow", "shadow"), ("k_finish", "finish")]
+STAGE = [("k_generate", "generate"), ("k_intersect", "intersect"), ("k_medium", "medium"), ("k_lookup<0", "volscatter"), ("k_volscatter", "volscatter"),
+         ("k_surface", "surface"), ("k_lookup<1", "shade"), ("k_shade", "shade"), ("k_shadow", "shadow"), ("k_finish", "finish")]
 METRICS = {"gpu__time_duration.sum": "ns", "smsp__inst_executed.sum": "warp_inst", "smsp__thread_inst_executed.sum": "thread_inst",
            "dram__bytes_read.sum": "dram_read", "dram__bytes_write.sum": "dram_write"}
 UNIT = {"byte": 1.0, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9, "ns": 1.0, "us": 1e3, "ms": 1e6, "inst": 1.0, "": 1.0, "nsecond": 1.0, "usecond": 1e3, "msecond": 1e6}
 
 
-def main(path, out, note):
+def main(path, out, note, spp=0):
     rows = list(csv.reader(open(path, newline="")))
     h = next(i for i, r in enumerate(rows) if r and r[0] == "ID")
     ix = {k: i for i, k in enumerate(rows[h])}
@@ -38,7 +38,7 @@ def main(path, out, note):
     for a in stages.values():
         a["lanes_per_inst"] = a["thread_inst"] / max(1.0, a["warp_inst"])
     tot = sum(a["ms"] for a in stages.values())
-    doc = {"source": path, "note": note, "what": "ncu --metrics gpu__time_duration.sum,smsp__inst_executed.sum,smsp__thread_inst_executed.sum,dram__bytes_read.sum,dram__bytes_write.sum --clock-control none (per-launch, serialised, cold cache: shares and counts are meaningful, absolute times are not bench values)",
+    doc = {"source": path, "note": note, "spp": spp, "what": "ncu --metrics gpu__time_duration.sum,smsp__inst_executed.sum,smsp__thread_inst_executed.sum,dram__bytes_read.sum,dram__bytes_write.sum --clock-control none (per-launch, serialised, cold cache: shares and counts are meaningful, absolute times are not bench values)",
            "total_ms_under_ncu": tot, "stages": stages, "kernels": kernels}
     json.dump(doc, open(out, "w"), indent=1)
     print(f"{'stage':12s} {'ms':>9s} {'share':>6s} {'Gwarp-inst':>11s} {'lanes':>6s} {'DRAM GB':>8s}")
@@ -47,4 +47,4 @@ def main(path, out, note):
 
 
 if __name__ == "__main__":
-    main(sys.argv[1], sys.argv[2], sys.argv[3] if len(sys.argv) > 3 else "")
+    main(sys.argv[1], sys.argv[2], sys.argv[3] if len(sys.argv) > 3 else "", int(sys.argv[4]) if len(sys.argv) > 4 else 0)

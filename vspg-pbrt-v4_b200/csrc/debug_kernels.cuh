@@ -19,6 +19,27 @@ __global__ void k_build_cells(const float *density, int nx, int ny, int nz, floa
     }
 }
 
+// RGB cell records (dmedia.cuh rgb_cell_lerp): one thread per (cell, grid)
+__global__ void k_build_cells_rgb(const float *sa, const float *ss, int nx, int ny, int nz, float4 *cells) {
+    size_t ncell = (size_t)(nx + 1) * (ny + 1) * (nz + 1);
+    for (size_t t = (size_t)blockIdx.x * blockDim.x + threadIdx.x; t < 2 * ncell; t += (size_t)gridDim.x * blockDim.x) {
+        const size_t c = t >> 1;
+        const float *g = (t & 1) ? ss : sa;
+        int cx = (int)(c % (nx + 1)), cy = (int)((c / (nx + 1)) % (ny + 1)), cz = (int)(c / ((size_t)(nx + 1) * (ny + 1)));
+        float v[24];
+#pragma unroll
+        for (int k = 0; k < 8; k++) {
+            int x = cx - 1 + (k & 1), y = cy - 1 + ((k >> 1) & 1), z = cz - 1 + (k >> 2);
+            bool in = !(x < 0 || y < 0 || z < 0 || x >= nx || y >= ny || z >= nz);
+            const float *q = g + 3 * ((size_t)(z * ny + y) * nx + x);
+            v[3 * k] = in ? q[0] : 0.f; v[3 * k + 1] = in ? q[1] : 0.f; v[3 * k + 2] = in ? q[2] : 0.f;
+        }
+        float4 *o = cells + 12 * c + 6 * (t & 1);
+#pragma unroll
+        for (int k = 0; k < 6; k++) o[k] = make_float4(v[4 * k], v[4 * k + 1], v[4 * k + 2], v[4 * k + 3]);
+    }
+}
+
 // Majorant grid of a uniformgrid / rgbgrid medium (media.cpp:256-269, 393-408 with util/containers.h:838-855 MaxValue):
 // one CTA per majorant cell takes the maximum over the voxel box MaxValue visits.  A maximum of floats does not depend
 // on the order, so this equals the host loop (host_util.h build_majorant_grid) bit for bit.  comps = 1: density grid;

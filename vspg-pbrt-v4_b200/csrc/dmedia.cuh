@@ -170,6 +170,16 @@ VD V3 rgb_lookup(const DMedium &m, const float *g, V3 p) {  // util/containers.h
     V3 d11 = lerpv(dx, rgb_at(m, g, ix, iy + 1, iz + 1), rgb_at(m, g, ix + 1, iy + 1, iz + 1));
     return lerpv(dz, lerpv(dy, d00, d10), lerpv(dy, d01, d11));
 }
+// One grid's half of an RGB cell record: 6 x float4 = corners c000, c100, c010, c110, c001, c101, c011, c111, rgb each;
+// the interpolation is rgb_lookup's, term for term.
+VD V3 rgb_cell_lerp(const float4 *c, bool inside, float dx, float dy, float dz) {
+    float4 q0 = make_float4(0, 0, 0, 0), q1 = q0, q2 = q0, q3 = q0, q4 = q0, q5 = q0;
+    if (inside) { q0 = __ldg(c); q1 = __ldg(c + 1); q2 = __ldg(c + 2); q3 = __ldg(c + 3); q4 = __ldg(c + 4); q5 = __ldg(c + 5); }
+    V3 c000(q0.x, q0.y, q0.z), c100(q0.w, q1.x, q1.y), c010(q1.z, q1.w, q2.x), c110(q2.y, q2.z, q2.w);
+    V3 c001(q3.x, q3.y, q3.z), c101(q3.w, q4.x, q4.y), c011(q4.z, q4.w, q5.x), c111(q5.y, q5.z, q5.w);
+    V3 d00 = lerpv(dx, c000, c100), d10 = lerpv(dx, c010, c110), d01 = lerpv(dx, c001, c101), d11 = lerpv(dx, c011, c111);
+    return lerpv(dz, lerpv(dy, d00, d10), lerpv(dy, d01, d11));
+}
 // media.h:256-261, 316-348, 417-441  Medium::SamplePoint (emission-free media)
 VD MediumProps sample_point(const DMedium &m, V3 p) {
     MediumProps mp; mp.g = m.g;
@@ -185,6 +195,16 @@ VD MediumProps sample_point(const DMedium &m, V3 p) {
         float d = density_lookup(m, p);
         mp.sigma_a = ld3(m.sigma_a) * d; mp.sigma_s = ld3(m.sigma_s) * d;
     } else {
+        if (m.cells_rgb) {   // both grids from one 192-byte cell record instead of 16 scattered 12-byte reads
+            float psx = p.x * m.nx - .5f, psy = p.y * m.ny - .5f, psz = p.z * m.nz - .5f;
+            int ix = (int)floorf(psx), iy = (int)floorf(psy), iz = (int)floorf(psz);
+            float dx = psx - (float)ix, dy = psy - (float)iy, dz = psz - (float)iz;
+            const bool inside = !(ix < -1 || iy < -1 || iz < -1 || ix >= m.nx || iy >= m.ny || iz >= m.nz);
+            const float4 *c = m.cells_rgb + 12 * (inside ? ((size_t)(iz + 1) * (m.ny + 1) + (iy + 1)) * (m.nx + 1) + (ix + 1) : 0);
+            mp.sigma_a = m.sigma_scale * rgb_cell_lerp(c, inside, dx, dy, dz);
+            mp.sigma_s = m.sigma_scale * rgb_cell_lerp(c + 6, inside, dx, dy, dz);
+            return mp;
+        }
         mp.sigma_a = m.sigma_scale * (m.sa_rgb ? rgb_lookup(m, m.sa_rgb, p) : splat(1.f));
         mp.sigma_s = m.sigma_scale * (m.ss_rgb ? rgb_lookup(m, m.ss_rgb, p) : splat(1.f));
     }

@@ -23,6 +23,7 @@ struct DMedium {
     const float *density;      // LINEAR
     const float4 *cells;       // CELL8: 2 x float4 per cell, (nx+1)*(ny+1)*(nz+1) cells
     const float *sa_rgb, *ss_rgb;
+    const float4 *cells_rgb;   // rgbgrid, both grids present: 12 x float4 per cell = the 8 rgb corners of sigma_a, then of sigma_s (192 B)
     int mres[3];
     const float *majorant;
     int layout;

@@ -281,6 +281,16 @@ int vspg_set_scene(vspg_ctx *ctx, const vspg_scene_desc *s) {
             CK(cudaGetLastError());
             d.majorant = (const float *)dm;
         }
+        if (m.type == VSPG_MEDIUM_RGBGRID && d.sa_rgb && d.ss_rgb && ctx->grid_layout == GRID_CELL8) {
+            size_t ncell = (size_t)(m.nx + 1) * (m.ny + 1) * (m.nz + 1);
+            void *cells = nullptr;
+            CK(dev_alloc(ctx, ctx->scene_allocs, &cells, ncell * 192));
+            int blocks = (int)std::min<size_t>((2 * ncell + 255) / 256, 148 * 32);
+            k_build_cells_rgb<<<blocks, 256>>>(d.sa_rgb, d.ss_rgb, m.nx, m.ny, m.nz, (float4 *)cells);
+            CK(cudaGetLastError());
+            d.cells_rgb = (const float4 *)cells;
+            if (!ctx->cells_ptr) { ctx->cells_ptr = cells; ctx->cells_bytes = ncell * 192; }
+        }
         if (scalarGrid && ctx->grid_layout == GRID_CELL8) {
             size_t ncell = (size_t)(m.nx + 1) * (m.ny + 1) * (m.nz + 1);
             void *cells = nullptr;
