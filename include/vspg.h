@@ -309,6 +309,11 @@ const char *vspg_host_scene_outfile(const vspg_host_scene *s); /* Film "filename
 /* "storeTrBuffer" true: resolved "trBufferFileName" the caller writes after the render (vspg_tr_store_* +
  * vspg_exr_write_channels, as `vspg-pbrt` does); "" otherwise. */
 const char *vspg_host_scene_store_tr_file(const vspg_host_scene *s);
+/* "vspguiding" + "vspprimaryguiding" without a loaded ISG buffer: the reference trains the image-space buffer on the fly
+ * (vspg.cpp:161-178); train_isg tells the driver to render wave by wave through vspg_isg_store_* (see there), store_isg_file is
+ * the "isgBufferFileName" to write afterwards when "storeISGBuffer" is set ("" otherwise). */
+int vspg_host_scene_train_isg(const vspg_host_scene *s);
+const char *vspg_host_scene_store_isg_file(const vspg_host_scene *s);
 
 /* loaders, usable on their own (replace pglFieldLoadFromFile, ISGB/Tr EXR readers) */
 typedef struct vspg_host_field vspg_host_field;
@@ -404,6 +409,26 @@ int vspg_debug_light_sample(vspg_ctx *ctx, int n, const float *pos3, const float
 int vspg_tr_store_begin(vspg_ctx *ctx);
 int vspg_tr_store_download(vspg_ctx *ctx, float *out_rgb, int *out_count);
 int vspg_tr_store_end(vspg_ctx *ctx);
+
+/* storeISGBuffer (cpu/guidedvolpathvspgintegrator.cpp:161-178 config, :230-258 PostProcessWave, :613-622 AddSample;
+ * openpgl/imagespace/ImageSpaceGuidingBuffer.h:632-797 update / addSample): the image-space VSP buffer trained on
+ * the fly, which is what the reference does when vspguiding + vspprimaryguiding are on and no ISG buffer was loaded.
+ *   begin    per-pixel records {surfSpp, volSpp, surfContrib rgb, volContrib rgb} cleared; primary rays read vsp = 0.5
+ *            until the first update (the criterion -- contribution or variance -- is the integrator's at this moment:
+ *            call after vspg_set_guiding / vspg_set_integrator)
+ *   render   ONE sample index per vspg_render call while the store is active (the reference's waves are 1 spp): every
+ *            finished path updates its pixel's float running mean exactly as ImageSpaceGuidingBuffer::AddSample does
+ *   update   ImageSpaceGuidingBuffer::Update with the denoiser as the identity: VSP per pixel from the records; from
+ *            then on primary rays read it.  The reference updates after waves 1, 2, 4, 8, ... and once at the end.
+ *   download out_vsp [H*W] (the layer "VSP.Y" of the stored file) and / or out_records8 [H*W*8]
+ *   end      back to the loaded ISG buffer (if any)
+ * NOT the reference's result where it differs by design: the reference denoises pVol and both contribution buffers
+ * with OIDN before forming the ratio; this is the un-denoised estimate (identical to a reference build whose OIDN is the
+ * identity, which is what tests/golden pins it against). */
+int vspg_isg_store_begin(vspg_ctx *ctx);
+int vspg_isg_store_update(vspg_ctx *ctx);
+int vspg_isg_store_download(vspg_ctx *ctx, float *out_vsp, float *out_records8);
+int vspg_isg_store_end(vspg_ctx *ctx);
 
 /* Integrator::Intersect (cpu/integrators.cpp:341-349 -> BVHAggregate::Intersect, cpu/aggregates.cpp:529-579) at n rays
  * (rays7 = o, d, tMax) followed by the shape's InteractionFromIntersection: out_prim[i] = primitive id counted over

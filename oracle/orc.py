@@ -176,6 +176,17 @@ def render(scene, guiding, ip, spp_begin, spp_end, spp_stride=1, window=None, se
     return film, dict(paths=cnt[0], density_queries=cnt[1], dda_steps=cnt[2], cache_lookups=cnt[3], shadow_rays=cnt[4])
 
 
+def render_isg(scene, guiding, ip, spp, seed=0, nthreads=1):
+    """The wave loop with the ISG buffer trained on the fly -> film, vsp [h, w], records [h, w, 8]."""
+    cam = scene.desc.camera
+    film = np.zeros((cam.height, cam.width, 4), dtype=np.float64)
+    vsp = np.zeros((cam.height, cam.width), dtype=np.float32)
+    rec = np.zeros((cam.height, cam.width, 8), dtype=np.float32)
+    rc = lib().orc_render_isg(C.byref(scene.desc), _gp(guiding), C.byref(ip), int(spp), int(seed), int(nthreads), film.ctypes.data_as(P), _fp(vsp), _fp(rec))
+    assert rc == 0, rc
+    return film, vsp, rec
+
+
 def render_tr(scene, guiding, ip, spp_begin, spp_end, seed=0, nthreads=1):
     """Render with the storeTrBuffer pre-pass on: returns film, counters, tr_rgb [h, w, 3] float32, tr_spp [h, w] int32."""
     cam = scene.desc.camera

@@ -698,6 +698,37 @@ struct Integrator {
     Counters cnt;
     // storeTrBuffer (vspg.cpp:190-193, 727-728; cpu/trbuffer.h:40-45): per-pixel running mean of the depth-0 ratio-tracking
     // transmittance estimate.  Shared by the worker threads (each pixel is rendered by one thread, samples in order).
+    // storeISGBuffer: records of 8 floats per pixel {surfSpp, volSpp, surfContrib rgb, volContrib rgb}
+    // (openpgl/imagespace/ImageSpaceGuidingBuffer.h:744-797 addSample with VSP_USE_PVOL_EST), the estimate of the last
+    // Update() (null until the first one), and the event type of the path being traced
+    float *isgRec = nullptr; const float *isgTrained = nullptr; bool isgVariance = false, firstVolume = false;
+    void IsgAddSample(int px, int py, S3 L) {
+        float *r = isgRec + 8 * ((size_t)py * sc->d->camera.width + px);
+        float *spp = r + (firstVolume ? 1 : 0), *c = r + (firstVolume ? 5 : 2);
+        *spp += 1;
+        float alpha = 1.f / *spp;
+        for (int k = 0; k < 3; k++) {
+            float q = isgVariance ? L[k] * L[k] : L[k];
+            c[k] = (1.f - alpha) * c[k] + alpha * q;
+        }
+    }
+    // :632-742 update(), denoiser = identity
+    static void IsgUpdate(const float *rec, size_t npix, bool variance, float *vsp) {
+        for (size_t i = 0; i < npix; i++) {
+            const float *r = rec + 8 * i;
+            float pVol = r[1] / (r[0] + r[1]);
+            pVol = std::max(0.f, std::min(1.f, pVol));
+            float sv[3], vv[3];
+            for (int k = 0; k < 3; k++) {
+                float sm = r[2 + k], vm = r[5 + k];
+                if (variance) { sv[k] = sm > 0.f ? (1.f - pVol) * std::sqrt(sm) : 0.f; vv[k] = vm > 0.f ? pVol * std::sqrt(vm) : 0.f; }
+                else { sv[k] = (1.f - pVol) * sm; vv[k] = pVol * vm; }
+            }
+            float c[3] = {sv[0] + vv[0], sv[1] + vv[1], sv[2] + vv[2]};
+            float cs = std::max(c[0], std::max(c[1], c[2])), vs = std::max(vv[0], std::max(vv[1], vv[2]));
+            vsp[i] = cs > 0.f ? vs / cs : -1.f;
+        }
+    }
     float *trBuf = nullptr; int *trSpp = nullptr;
     void TrAddSample(int px, int py, S3 tr) {
         int pixIdx = py * sc->d->camera.width + px;
@@ -1113,7 +1144,8 @@ struct Integrator {
         auto validate = [&](float v) { guideScatterDecision = !(std::isnan(v) || v < 0.f || v > 1.f); return v; };
         if (ps.depth == 0) {
             if (ip.vsp_guiding && ip.vsp_primary_guiding) {  // vspg.cpp:1098-1112
-                if (sc->g && sc->g->isg_vsp) vsp = sc->g->isg_vsp[(size_t)py * sc->g->isg_width + px];
+                if (isgRec) vsp = isgTrained ? isgTrained[(size_t)py * sc->d->camera.width + px] : 0.5f;   // trained on the fly: 0.5 until IsReady()
+                else if (sc->g && sc->g->isg_vsp) vsp = sc->g->isg_vsp[(size_t)py * sc->g->isg_width + px];
                 else vsp = 0.5f;
                 validate(vsp);
             }
@@ -1173,6 +1205,7 @@ struct Integrator {
                 ps.r_u *= sel.den;
                 if (ps.beta.HasNaNs() || ps.r_u.HasNaNs() || YIsInf(ps.beta) || YIsInf(ps.r_u)) { terminated = true; return; }
             } else {
+                if (ps.depth == 0) firstVolume = true;   // vspg.cpp:776-783 isgbSample.SetSurfaceEvent(false)
                 if (ps.depth++ >= ip.max_depth) { terminated = true; return; }
                 ps.beta *= sel.num * rf;
                 ps.r_u *= sel.den;
@@ -1211,6 +1244,7 @@ struct Integrator {
                         mode = offset;
                     }
                     if (mode == 0) {
+                        if (ps.depth == 0) firstVolume = true;   // vspg.cpp:950-957
                         if (ps.depth++ >= ip.max_depth) { terminated = true; return false; }
                         float pdf = T_maj[ch] * sigma_t[ch];
                         ps.beta *= T_maj * mp.sigma_s / pdf;
@@ -1392,7 +1426,9 @@ struct Integrator {
         sampler.StartPixelSample(px, py, sc->seed, sampleIndex);
         Ray ray; int ch; float fw;
         CameraRay(px, py, sampler, &ray, &ch, &fw);
+        firstVolume = false;
         S3 L = Li(px, py, ray, sampler, ch);
+        if (isgRec) IsgAddSample(px, py, L);   // vspg.cpp:613-622, inside Li: before the film's NaN guard
         if (L.HasNaNs() || YIsInf(L)) L = S3(0.f);
         cnt.paths++;
         // film.h:251-267 RGBFilm::AddSample

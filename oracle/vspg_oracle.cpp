@@ -350,6 +350,43 @@ int orc_render_ex(const vspg_scene_desc *scene, const vspg_guiding_desc *g, cons
     return 0;
 }
 
+// The reference's wave loop with the ISG buffer trained on the fly (cpu/integrators.cpp:123-239 with nextWaveSize = 1;
+// vspg.cpp:230-258 PostProcessWave: Update() after waves 1, 2, 4, 8, ...).  out_vsp [h*w] = the estimate of the last
+// update, out_rec8 [h*w*8] the records after the last wave.
+int orc_render_isg(const vspg_scene_desc *scene, const vspg_guiding_desc *g, const vspg_integrator_params *ip, int spp, int seed, int nthreads,
+                   double *film_rgbw, float *out_vsp, float *out_rec8) {
+    if ((ip->volume_guiding || ip->vsp_secondary_guiding) && g && g->volume && !g_hg_table_set) return -2;
+    Scene sc; sc.init(scene, g, ip, true); sc.seed = seed;
+    if (nthreads < 1) nthreads = 1;
+    const int w = scene->camera.width, h = scene->camera.height;
+    std::vector<float> rec((size_t)w * h * 8, 0.f), trained((size_t)w * h, 0.f);
+    bool ready = false;
+    int nextUpdate = 1;
+    for (int wave = 1; wave <= spp; wave++) {
+        std::atomic<int> nextRow(0);
+        auto worker = [&]() {
+            Integrator integ; integ.sc = &sc;
+            integ.isgRec = rec.data(); integ.isgTrained = ready ? trained.data() : nullptr; integ.isgVariance = ip->vsp_criterion_variance != 0;
+            while (true) {
+                int y = nextRow.fetch_add(1);
+                if (y >= h) break;
+                for (int x = 0; x < w; x++) integ.RenderPixelSample(x, y, wave - 1, film_rgbw);
+            }
+        };
+        std::vector<std::thread> th;
+        for (int i = 0; i < nthreads; i++) th.emplace_back(worker);
+        for (auto &t : th) t.join();
+        if (wave == nextUpdate) {
+            Integrator::IsgUpdate(rec.data(), (size_t)w * h, ip->vsp_criterion_variance != 0, trained.data());
+            ready = true;
+            nextUpdate *= 2;
+        }
+    }
+    if (out_vsp) std::memcpy(out_vsp, trained.data(), trained.size() * sizeof(float));
+    if (out_rec8) std::memcpy(out_rec8, rec.data(), rec.size() * sizeof(float));
+    return 0;
+}
+
 // One path with a trace of the radiance, for debugging single pixels
 int orc_render_pixel_sample(const vspg_scene_desc *scene, const vspg_guiding_desc *g, const vspg_integrator_params *ip, int px, int py,
                             int sampleIndex, int seed, float *L3) {

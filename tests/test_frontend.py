@@ -249,7 +249,8 @@ def test_errors_mirror_the_reference_error_exits(body, code, needle):
     ('Integrator "guidedvolpath"', A.ERR_UNSUPPORTED, "loadGuidingCache"),                       # guiding on, nothing to load: no training here
     ('Integrator "guidedvolpath" "bool loadGuidingCache" true "string guidingCacheFileName" "missing.pgl"', A.ERR_IO, "missing.pgl"),
     ('Integrator "guidedvolpath" "string vspsamplingmethod" "magic"', A.ERR_INVALID, "vspsamplingmethod"),
-    ('Integrator "guidedvolpath" "bool surfaceguiding" false "bool volumeguiding" false "bool vspsecondaryguiding" false', A.ERR_UNSUPPORTED, "loadISGBuffer"),
+    ('Integrator "guidedvolpath" "bool storeISGBuffer" true "bool vspguiding" false "string isgBufferFileName" "x.exr"', A.ERR_UNSUPPORTED, "stores no VSP layer"),
+    ('Integrator "guidedvolpath" "bool storeISGBuffer" true', A.ERR_INVALID, "without isgBufferFileName"),
 ])
 def test_integrator_parameter_errors(integrator, code, needle):
     text = HEAD.replace(HEAD.splitlines()[5], integrator) + "WorldBegin\n"

@@ -108,7 +108,7 @@ VD void generate_camera_path(const DScene &sc, int seed, int px, int py, int sam
                  rm[2][0] * d.x + rm[2][1] * d.y + rm[2][2] * d.z);
     r.ray.medium = c.medium;
     r.beta = r.r_u = r.r_l = splat(1.f); r.L = V3();
-    r.fl.depth = 0; r.fl.channel = ch; r.fl.specular = false; r.fl.anyNonSpecular = false; r.fl.lastVertexVolume = false;
+    r.fl.depth = 0; r.fl.channel = ch; r.fl.specular = false; r.fl.anyNonSpecular = false; r.fl.lastVertexVolume = false; r.fl.firstVolume = false;
     r.rr_correction = 1.f; r.vsp_next = -1.f; r.prevP = V3();
     r.pixel = py * c.width + px; r.sampleIndex = sampleIndex;
 }

@@ -91,6 +91,7 @@ VD void sample_distance(const DScene &sc, PathRegs &ps, float tHit, TrackCounter
             ps.r_u = ps.r_u * selDen;
             if (has_nan(ps.beta) || has_nan(ps.r_u) || y_is_inf(ps.beta) || y_is_inf(ps.r_u)) { res.terminated = true; return; }
         } else {
+            if (ps.fl.depth == 0) ps.fl.firstVolume = true;
             if (ps.fl.depth++ >= ip.max_depth) { res.terminated = true; return; }
             ps.beta = ps.beta * (selNum * rf);
             ps.r_u = ps.r_u * selDen;
@@ -124,6 +125,7 @@ VD void sample_distance(const DScene &sc, PathRegs &ps, float tHit, TrackCounter
                     mode = (0.f + pScatter <= up) ? 1 : 0;
                 }
                 if (mode == 0) {
+                    if (ps.fl.depth == 0) ps.fl.firstVolume = true;
                     if (ps.fl.depth++ >= ip.max_depth) { res.terminated = true; return false; }
                     float pdf = T_maj[ch] * sigma_t[ch];
                     ps.beta = ps.beta * (T_maj * mp.sigma_s / pdf);

@@ -101,6 +101,9 @@ struct DScene {
     const DHGRow *hg_table;   // 128 rows
     const float *isg_vsp; int isg_w, isg_h;
     const float *tr_rgb; int tr_w, tr_h;
+    // storeISGBuffer (vspg_isg_store_*): per pixel {surfSpp, volSpp, surfContrib rgb, volContrib rgb} as the reference's
+    // ImageSpaceGuidingBuffer keeps them (float running means), or null; isg_variance = its vspType is EVariance
+    float *isg_rec; int isg_variance;
     double *tr_acc;      // storeTrBuffer accumulators {sumR, sumG, sumB, count} per pixel, or null (vspg_tr_store_begin)
     // PixelFilter "gaussian" sampling table (host_util.h build_gaussian_filter); filt_nx == 0 for the box filter
     int filt_nx, filt_ny; const float *filt_f, *filt_cond_cdf, *filt_cond_int, *filt_marg_cdf; float filt_marg_int;
@@ -156,10 +159,11 @@ struct PathSoA {
 // packed flags in d_med.w : bits 0-7 depth, 8-9 channel, 10 specularBounce, 11 anyNonSpecular, 12 lastVertexVolume
 struct PathFlags {
     int depth, channel; bool specular, anyNonSpecular, lastVertexVolume;
-    VD int pack() const { return (depth & 0xff) | (channel << 8) | (specular << 10) | (anyNonSpecular << 11) | (lastVertexVolume << 12); }
+    bool firstVolume;   // the path's first scattering event was inside a medium (isgbSample.SetSurfaceEvent(false), vspg.cpp:776-783, 950-957)
+    VD int pack() const { return (depth & 0xff) | (channel << 8) | (specular << 10) | (anyNonSpecular << 11) | (lastVertexVolume << 12) | (firstVolume << 13); }
     VD static PathFlags unpack(int v) {
         PathFlags f; f.depth = v & 0xff; f.channel = (v >> 8) & 3; f.specular = (v >> 10) & 1; f.anyNonSpecular = (v >> 11) & 1;
-        f.lastVertexVolume = (v >> 12) & 1; return f;
+        f.lastVertexVolume = (v >> 12) & 1; f.firstVolume = (v >> 13) & 1; return f;
     }
 };
 

@@ -267,8 +267,8 @@ struct vspg_host_scene {
     float fov = 90, lens_radius = 0, focal_distance = 1e6f, frame_aspect = -1; std::vector<double> screen_window;
     int xres = 1280, yres = 720; float iso = 100, exposure = 1, max_comp = INFINITY;
     int filter_type = 1; float filter_r[2] = {1.5f, 1.5f}, filter_sigma = 0.5f;   // pbrt's default filter is "gaussian"
-    std::string guiding_cache_file, isg_file, tr_file; bool load_cache = false, load_isg = false, load_tr = false, store_tr = false;
-    std::string store_tr_path;
+    std::string guiding_cache_file, isg_file, tr_file; bool load_cache = false, load_isg = false, load_tr = false, store_tr = false, store_isg = false, train_isg = false;
+    std::string store_tr_path, store_isg_path;
     ~vspg_host_scene() { if (field) vspg_host_field_free(field); if (isg) vspg_free(isg); if (tr) vspg_free(tr); }
 };
 
@@ -376,7 +376,7 @@ struct Builder {
         else if (meth == "NDS" || meth == "nds") ip.vsp_sampling_nds = 1;
         else lx.fail("Integrator: vspsamplingmethod must be \"resampling\" or \"nds\"");
         ip.collision_probability_bias = ps.one_bool("collisionProbabilityBias", false);
-        bool store_isg = ps.one_bool("storeISGBuffer", false);
+        S.store_isg = ps.one_bool("storeISGBuffer", false);
         S.load_isg = ps.one_bool("loadISGBuffer", false);
         S.isg_file = ps.one_string("isgBufferFileName", "");
         S.store_tr = ps.one_bool("storeTrBuffer", false);
@@ -391,9 +391,15 @@ struct Builder {
         else lx.fail("Integrator: lightsampler \"" + ls + "\" unknown");
         ip.regularize = ps.one_bool("regularize", false);
         ps.report_unused();
-        if (store_cache || store_isg)
-            lx.fail("Integrator: storeGuidingCache / storeISGBuffer request a training pass; this library renders with frozen, "
-                    "loaded inputs only (guiding-cache training is out of scope; storeTrBuffer is supported)", VSPG_ERR_UNSUPPORTED);
+        if (store_cache)
+            lx.fail("Integrator: storeGuidingCache requests a training pass of the guiding cache, which is out of scope (the cache is a "
+                    "loaded input; storeTrBuffer and storeISGBuffer are supported)", VSPG_ERR_UNSUPPORTED);
+        if (S.store_isg) {   // vspg.cpp:161-178, 215-217: the buffer is trained by the render itself and stored afterwards
+            if (S.isg_file.empty()) lx.fail("Integrator: storeISGBuffer without isgBufferFileName");
+            if (S.load_isg) lx.fail("Integrator: storeISGBuffer together with loadISGBuffer (the reference would only re-write the loaded file)", VSPG_ERR_UNSUPPORTED);
+            if (!(ip.vsp_guiding && ip.vsp_primary_guiding))
+                lx.fail("Integrator: storeISGBuffer without vspguiding + vspprimaryguiding stores no VSP layer (vspg.cpp:169-176)", VSPG_ERR_UNSUPPORTED);
+        }
         if (S.store_tr) {   // vspg.cpp:190-193, 219-221: the Tr buffer is accumulated by the render itself and written afterwards
             if (S.tr_file.empty()) lx.fail("Integrator: storeTrBuffer without trBufferFileName");
             if (S.load_tr) lx.fail("Integrator: storeTrBuffer together with loadTrBuffer (the reference would only re-write the loaded file)", VSPG_ERR_UNSUPPORTED);
@@ -940,14 +946,19 @@ void finish(vspg_host_scene &S) {
         S.has_guiding = true;
     }
     if (ip.vsp_guiding && ip.vsp_primary_guiding) {
-        if (!S.load_isg || S.isg_file.empty())
-            throw ParseError(VSPG_ERR_UNSUPPORTED, "Integrator: vspprimaryguiding needs \"bool loadISGBuffer\" true + \"string isgBufferFileName\" (no buffer-training pass here)");
-        std::string p = S.isg_file[0] == '/' ? S.isg_file : S.base_dir + "/" + S.isg_file;
+        std::string p = S.isg_file.empty() ? "" : (S.isg_file[0] == '/' ? S.isg_file : S.base_dir + "/" + S.isg_file);
+        if (!S.load_isg || S.isg_file.empty()) {
+            // vspg.cpp:161-178: no loaded buffer -> the image-space buffer is trained on the fly by the render's waves
+            // (vspg_isg_store_*; the driver renders one sample index per wave, see vspg_pbrt_main.cpp / Context.render_training_isg)
+            S.train_isg = true;
+            if (S.store_isg) S.store_isg_path = p;
+        } else {
         int w = 0, h = 0;
         int rc = vspg_exr_read_channel(p.c_str(), "VSP.Y", &S.isg, &w, &h, err, sizeof err);
         if (rc != VSPG_OK) throw ParseError(rc, std::string("loadISGBuffer: ") + err);
         S.guiding.isg_vsp = S.isg; S.guiding.isg_width = w; S.guiding.isg_height = h;
         S.has_guiding = true;
+        }
     }
     if (S.store_tr) S.store_tr_path = S.tr_file[0] == '/' ? S.tr_file : S.base_dir + "/" + S.tr_file;
     if (S.load_tr) {
@@ -1016,5 +1027,7 @@ int vspg_host_scene_spp(const vspg_host_scene *s) { return s ? s->spp : 0; }
 int vspg_host_scene_seed(const vspg_host_scene *s) { return s ? s->seed : 0; }
 const char *vspg_host_scene_outfile(const vspg_host_scene *s) { return s ? s->outfile.c_str() : ""; }
 const char *vspg_host_scene_store_tr_file(const vspg_host_scene *s) { return s ? s->store_tr_path.c_str() : ""; }
+const char *vspg_host_scene_store_isg_file(const vspg_host_scene *s) { return s ? s->store_isg_path.c_str() : ""; }
+int vspg_host_scene_train_isg(const vspg_host_scene *s) { return s && s->train_isg ? 1 : 0; }
 
 }  // extern "C"

@@ -306,6 +306,42 @@ __global__ void __launch_bounds__(kBlock, VSPG_SHADOW_MINB) k_shadow(const DScen
     counter_add(W.counters, CNT_BVH, nodes);
 }
 
+// ------------------------------------------------------------------ storeISGBuffer (vspg.cpp:613-622)
+// openpgl/imagespace/ImageSpaceGuidingBuffer.h:744-797 addSample with VSP_USE_PVOL_EST: the running mean of the path
+// contributions (squared for the variance criterion) per first-event type.  The reference adds one sample per pixel
+// and wave, in wave order; vspg_render enforces the same (one sample index per render while the store is active), so the
+// record is owned by one thread and the float arithmetic is the reference's.
+VD void isg_add_sample(const DScene &sc, int pixel, V3 L, bool volumeEvent) {
+    float *r = sc.isg_rec + 8 * (size_t)pixel;
+    float *spp = r + (volumeEvent ? 1 : 0), *c = r + (volumeEvent ? 5 : 2);
+    *spp += 1;
+    float alpha = 1.f / *spp;
+    V3 q = sc.isg_variance ? L * L : L;
+    c[0] = (1.f - alpha) * c[0] + alpha * q.x;
+    c[1] = (1.f - alpha) * c[1] + alpha * q.y;
+    c[2] = (1.f - alpha) * c[2] + alpha * q.z;
+}
+// :632-742 update() with the denoiser taken as the identity (un-denoised estimate; the reference filters pVol and the two
+// contribution buffers with OIDN first): VSP = max(volume term) / max(surface term + volume term), -1 where both vanish
+__global__ void k_isg_update(const float *rec, int npix, int variance, float *vsp) {
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < npix; i += gridDim.x * blockDim.x) {
+        const float *r = rec + 8 * (size_t)i;
+        float pVol = r[1] / (r[0] + r[1]);
+        pVol = pVol < 1.f ? pVol : 1.f;       // std::min(1.f, pVol): NaN -> 1
+        pVol = 0.f < pVol ? pVol : 0.f;       // std::max(0.f, .)
+        float sv[3], vv[3];
+        for (int k = 0; k < 3; k++) {
+            float s = r[2 + k], v = r[5 + k];
+            if (variance) { sv[k] = s > 0.f ? (1.f - pVol) * sqrtf(s) : 0.f; vv[k] = v > 0.f ? pVol * sqrtf(v) : 0.f; }
+            else { sv[k] = (1.f - pVol) * s; vv[k] = pVol * v; }
+        }
+        auto mx = [](float a, float b) { return a < b ? b : a; };   // std::max
+        float c0 = sv[0] + vv[0], c1 = sv[1] + vv[1], c2 = sv[2] + vv[2];
+        float cs = mx(c0, mx(c1, c2)), vs = mx(vv[0], mx(vv[1], vv[2]));
+        vsp[i] = cs > 0.f ? vs / cs : -1.f;
+    }
+}
+
 // ------------------------------------------------------------------ film + regeneration (integrators.cpp:308-334)
 __global__ void __launch_bounds__(kBlock) k_finish(const DScene sc, const Wavefront W) {
     const int n = *W.done.count;
@@ -315,6 +351,7 @@ __global__ void __launch_bounds__(kBlock) k_finish(const DScene sc, const Wavefr
         float4 e = W.P.rl_L[slot];
         float4 m2 = W.P.misc2[slot];
         film_add(sc, W.film, __float_as_int(m2.y), V3(e.y, e.z, e.w), m2.w);
+        if (sc.isg_rec) isg_add_sample(sc, __float_as_int(m2.y), V3(e.y, e.z, e.w), PathFlags::unpack(__float_as_int(W.P.d_med[slot].w)).firstVolume);
         paths++;
         PathRegs r;
         bool ok = regenerate(sc, W, slot, r);

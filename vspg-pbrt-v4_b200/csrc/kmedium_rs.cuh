@@ -124,6 +124,7 @@ VD void rs_finalize(const DScene &sc, const Wavefront &W, RsLane<GRAY> &s) {
         if (!selectSurface) {
             float4 b = W.P.d_med[slot];
             PathFlags fl = PathFlags::unpack(__float_as_int(b.w));
+            if (fl.depth == 0) fl.firstVolume = true;
             if (fl.depth++ >= ip.max_depth) terminated = true;
             else { b.w = __int_as_float(fl.pack()); W.P.d_med[slot] = b; }
         }

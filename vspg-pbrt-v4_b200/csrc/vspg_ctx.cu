@@ -51,6 +51,8 @@ struct vspg_ctx {
     const void *cells_ptr = nullptr; size_t cells_bytes = 0;      // cell-record grid of the (first) uniformgrid medium
     size_t l2_persist_bytes = 0, l2_window_max = 0;               // persisting-L2 carve-out granted by the device (0 = off)
     double *film = nullptr;
+    float *isg_rec = nullptr, *isg_trained = nullptr; size_t isg_pixels = 0; bool isg_active = false;   // storeISGBuffer (vspg_isg_store_*)
+    const float *isg_saved_vsp = nullptr; int isg_saved_w = 0, isg_saved_h = 0;
     double *tr_acc = nullptr; size_t tr_acc_pixels = 0;   // storeTrBuffer accumulators (vspg_tr_store_*)
     unsigned long long *counters = nullptr;
     unsigned long long launches = 0, iterations = 0;
@@ -193,6 +195,8 @@ void vspg_destroy(vspg_ctx *ctx) {
     if (ctx->h_pinned) cudaFreeHost(ctx->h_pinned);
     if (ctx->film) cudaFree(ctx->film);
     if (ctx->tr_acc) cudaFree(ctx->tr_acc);
+    if (ctx->isg_rec) cudaFree(ctx->isg_rec);
+    if (ctx->isg_trained) cudaFree(ctx->isg_trained);
     if (ctx->counters) cudaFree(ctx->counters);
     for (auto e : ctx->ev) if (e) cudaEventDestroy(e);
     delete ctx;
@@ -217,6 +221,7 @@ int vspg_set_scene(vspg_ctx *ctx, const vspg_scene_desc *s) {
     dev_release(ctx, ctx->scene_allocs);
     ctx->have_scene = false;
     ctx->cells_ptr = nullptr; ctx->cells_bytes = 0;
+    vspg_isg_store_end(ctx);    // so does an ISG store
     ctx->sc.tr_acc = nullptr;   // a Tr store belongs to one scene (resolution): vspg_tr_store_begin again after set_scene
     struct Trim { vspg_ctx *c; ~Trim() { dev_trim(c); } } trimOnExit{ctx};   // every return path drops the blocks this call did not reuse
     DScene &sc = ctx->sc;

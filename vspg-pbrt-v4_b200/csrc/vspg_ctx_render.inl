@@ -76,6 +76,8 @@ int vspg_render(vspg_ctx *ctx, int spp_begin, int spp_end, int spp_stride, int x
     int nspp = (spp_end - spp_begin + spp_stride - 1) / spp_stride;
     unsigned long long npix = (unsigned long long)(x1 - x0) * (y1 - y0);
     unsigned long long total = npix * (unsigned long long)nspp;
+    if (ctx->isg_active && nspp != 1)   // the ISG records are float running means in wave order: one sample per pixel and render
+        return fail(ctx, VSPG_ERR_STATE, "render: while the ISG store is active render one sample index per call (got %d); see vspg_isg_store_begin", nspp);
     if (total == 0) return VSPG_OK;
     int rc = ensure_wavefront(ctx, total);
     if (rc != VSPG_OK) return rc;
@@ -328,6 +330,60 @@ int vspg_tr_store_download(vspg_ctx *ctx, float *out_rgb, int *out_count) {
 int vspg_tr_store_end(vspg_ctx *ctx) {
     if (!ctx) return VSPG_ERR_INVALID;
     ctx->sc.tr_acc = nullptr;
+    return VSPG_OK;
+}
+// ---- storeISGBuffer: the image-space VSP buffer trained on the fly, as the reference does when vspguiding and
+// vspprimaryguiding are on and no ISG buffer was loaded (vspg.cpp:161-178, 230-258, 613-622)
+int vspg_isg_store_begin(vspg_ctx *ctx) {
+    if (!ctx) return VSPG_ERR_INVALID;
+    CK_STATE(ctx->have_scene && ctx->film, "isg_store_begin: set_scene has not been called");
+    CK(cudaSetDevice(ctx->device));
+    const size_t npix = (size_t)ctx->film_w * ctx->film_h;
+    if (!ctx->isg_rec || ctx->isg_pixels != npix) {
+        if (ctx->isg_rec) cudaFree(ctx->isg_rec);
+        if (ctx->isg_trained) cudaFree(ctx->isg_trained);
+        ctx->isg_rec = nullptr; ctx->isg_trained = nullptr;
+        CK(cudaMalloc((void **)&ctx->isg_rec, npix * 8 * sizeof(float)));
+        CK(cudaMalloc((void **)&ctx->isg_trained, npix * sizeof(float)));
+        ctx->isg_pixels = npix;
+    }
+    CK(cudaMemset(ctx->isg_rec, 0, npix * 8 * sizeof(float)));
+    ctx->isg_saved_vsp = ctx->sc.isg_vsp; ctx->isg_saved_w = ctx->sc.isg_w; ctx->isg_saved_h = ctx->sc.isg_h;
+    ctx->sc.isg_vsp = nullptr;          // not ready: primary rays use vsp = 0.5 (vspg.cpp:1100-1105) until the first update
+    ctx->sc.isg_w = ctx->film_w; ctx->sc.isg_h = ctx->film_h;
+    ctx->sc.isg_rec = ctx->isg_rec;
+    ctx->sc.isg_variance = ctx->sc.ip.vsp_criterion_variance ? 1 : 0;
+    ctx->isg_active = true;
+    return VSPG_OK;
+}
+int vspg_isg_store_update(vspg_ctx *ctx) {
+    if (!ctx) return VSPG_ERR_INVALID;
+    CK_STATE(ctx->isg_active, "isg_store_update: isg_store_begin has not been called");
+    CK(cudaSetDevice(ctx->device));
+    k_isg_update<<<ctx->sm_count * 4, 256>>>(ctx->isg_rec, (int)ctx->isg_pixels, ctx->sc.isg_variance, ctx->isg_trained);
+    ctx->launches++;
+    CK(cudaGetLastError());
+    CK(cudaDeviceSynchronize());
+    ctx->sc.isg_vsp = ctx->isg_trained;   // ready: the following waves read the estimate
+    return VSPG_OK;
+}
+int vspg_isg_store_download(vspg_ctx *ctx, float *out_vsp, float *out_records8) {
+    if (!ctx) return VSPG_ERR_INVALID;
+    CK_STATE(ctx->isg_active, "isg_store_download: isg_store_begin has not been called");
+    CK(cudaSetDevice(ctx->device));
+    if (out_vsp) {
+        CK_STATE(ctx->sc.isg_vsp == ctx->isg_trained, "isg_store_download: no isg_store_update yet");
+        CK(cudaMemcpy(out_vsp, ctx->isg_trained, ctx->isg_pixels * sizeof(float), cudaMemcpyDeviceToHost));
+    }
+    if (out_records8) CK(cudaMemcpy(out_records8, ctx->isg_rec, ctx->isg_pixels * 8 * sizeof(float), cudaMemcpyDeviceToHost));
+    return VSPG_OK;
+}
+int vspg_isg_store_end(vspg_ctx *ctx) {
+    if (!ctx) return VSPG_ERR_INVALID;
+    if (!ctx->isg_active) return VSPG_OK;
+    ctx->sc.isg_rec = nullptr;
+    ctx->sc.isg_vsp = ctx->isg_saved_vsp; ctx->sc.isg_w = ctx->isg_saved_w; ctx->sc.isg_h = ctx->isg_saved_h;
+    ctx->isg_active = false;
     return VSPG_OK;
 }
 int vspg_film_device_ptr(vspg_ctx *ctx, double **rgbw, size_t *n_doubles) {

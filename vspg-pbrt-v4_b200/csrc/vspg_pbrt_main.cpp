@@ -59,7 +59,15 @@ int main(int argc, char **argv) {
     const std::string trStore = vspg_host_scene_store_tr_file(hs);   // "storeTrBuffer" (vspg.cpp:190-193, 219-221)
     if (!trStore.empty()) ck(vspg_tr_store_begin(ctx), "tr_store_begin");
     auto t0 = std::chrono::steady_clock::now();
-    ck(vspg_render(ctx, 0, spp, 1, 0, 0, W, H, seed, nullptr), "render");
+    const bool trainIsg = vspg_host_scene_train_isg(hs) != 0;      // no loaded ISG buffer: trained on the fly (vspg.cpp:161-178)
+    const std::string isgStore = vspg_host_scene_store_isg_file(hs);   // "storeISGBuffer"
+    if (trainIsg) {   // the reference's wave loop: waves of one sample index, Update() after waves 1, 2, 4, 8, ... (vspg.cpp:230-258)
+        ck(vspg_isg_store_begin(ctx), "isg_store_begin");
+        for (int wave = 1, nextUpdate = 1; wave <= spp; wave++) {
+            ck(vspg_render(ctx, wave - 1, wave, 1, 0, 0, W, H, seed, nullptr), "render");
+            if (wave == nextUpdate) { ck(vspg_isg_store_update(ctx), "isg_store_update"); nextUpdate *= 2; }
+        }
+    } else ck(vspg_render(ctx, 0, spp, 1, 0, 0, W, H, seed, nullptr), "render");
     std::vector<float> rgb((size_t)W * H * 3);
     ck(vspg_film_resolve(ctx, rgb.data()), "film_resolve");
     double sec = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
@@ -72,6 +80,19 @@ int main(int argc, char **argv) {
         const float *pp[3] = {planes[0].data(), planes[1].data(), planes[2].data()};
         if (vspg_exr_write_channels(trStore.c_str(), W, H, 3, names, pp) != VSPG_OK) { fprintf(stderr, "vspg-pbrt: cannot write %s\n", trStore.c_str()); return 1; }
         if (!quiet) printf("vspg-pbrt: transmittance buffer -> %s\n", trStore.c_str());
+    }
+    if (trainIsg && !isgStore.empty()) {   // ImageSpaceGuidingBuffer::Store: the layers this path's own loader and the reference's read
+        const size_t n = (size_t)W * H;
+        std::vector<float> vsp(n), rec(8 * n), pl[8];
+        ck(vspg_isg_store_download(ctx, vsp.data(), rec.data()), "isg_store_download");
+        for (int k = 0; k < 8; k++) { pl[k].resize(n); for (size_t i = 0; i < n; i++) pl[k][i] = rec[8 * i + k]; }
+        const bool var = vspg_host_scene_integrator(hs)->vsp_criterion_variance != 0;
+        const std::string sc_ = var ? "surfContrib2nd" : "surfContrib", vc_ = var ? "volContrib2nd" : "volContrib";
+        std::vector<std::string> nm = {"VSP.Y", "surfSpp.Y", "volSpp.Y", sc_ + ".R", sc_ + ".G", sc_ + ".B", vc_ + ".R", vc_ + ".G", vc_ + ".B"};
+        const char *names[9]; const float *pp[9] = {vsp.data(), pl[0].data(), pl[1].data(), pl[2].data(), pl[3].data(), pl[4].data(), pl[5].data(), pl[6].data(), pl[7].data()};
+        for (int k = 0; k < 9; k++) names[k] = nm[k].c_str();
+        if (vspg_exr_write_channels(isgStore.c_str(), W, H, 9, names, pp) != VSPG_OK) { fprintf(stderr, "vspg-pbrt: cannot write %s\n", isgStore.c_str()); return 1; }
+        if (!quiet) printf("vspg-pbrt: image-space guiding buffer (un-denoised) -> %s\n", isgStore.c_str());
     }
     if (!quiet) {
         vspg_counters c;

@@ -199,9 +199,15 @@ SYMBOLS = {
     "vspg_debug_sample_distance": (i32, [P, i32, C.POINTER(SdInput), C.POINTER(SdOutput)]),
     "vspg_debug_cache_lookup": (i32, [P, i32, i32, PF, PF, C.POINTER(i32), C.POINTER(i32), PF]),
     "vspg_host_scene_store_tr_file": (C.c_char_p, [P]),
+    "vspg_host_scene_store_isg_file": (C.c_char_p, [P]),
+    "vspg_host_scene_train_isg": (i32, [P]),
     "vspg_tr_store_begin": (i32, [P]),
     "vspg_tr_store_download": (i32, [P, PF, C.POINTER(i32)]),
     "vspg_tr_store_end": (i32, [P]),
+    "vspg_isg_store_begin": (i32, [P]),
+    "vspg_isg_store_update": (i32, [P]),
+    "vspg_isg_store_download": (i32, [P, PF, PF]),
+    "vspg_isg_store_end": (i32, [P]),
     "vspg_exr_write_channels": (i32, [C.c_char_p, i32, i32, i32, C.POINTER(C.c_char_p), C.POINTER(PF)]),
     "vspg_debug_intersect": (i32, [P, i32, PF, C.POINTER(i32), PF]),
     "vspg_debug_sample_li": (i32, [P, i32, PF, C.POINTER(i32), PF, PF]),

@@ -200,6 +200,33 @@ class Context:
     def tr_store_end(self):
         self._ck(lib().vspg_tr_store_end(self._h))
 
+    def isg_store_begin(self):
+        self._ck(lib().vspg_isg_store_begin(self._h))
+
+    def isg_store_update(self):
+        self._ck(lib().vspg_isg_store_update(self._h))
+
+    def isg_store_download(self, width, height):
+        """-> vsp [h, w] float32, records [h, w, 8] float32 (surfSpp, volSpp, surfContrib rgb, volContrib rgb)."""
+        vsp = np.zeros((height, width), dtype=np.float32)
+        rec = np.zeros((height, width, 8), dtype=np.float32)
+        self._ck(lib().vspg_isg_store_download(self._h, _fp(vsp), _fp(rec)))
+        return vsp, rec
+
+    def isg_store_end(self):
+        self._ck(lib().vspg_isg_store_end(self._h))
+
+    def render_training_isg(self, spp, seed=0, stream=None):
+        """The reference's wave loop with the ISG buffer trained on the fly (cpu/integrators.cpp:123-239 with nextWaveSize = 1,
+        vspg.cpp:230-258): waves of one sample index, ImageSpaceGuidingBuffer::Update after waves 1, 2, 4, 8, ..."""
+        self.isg_store_begin()
+        next_update = 1
+        for wave in range(1, spp + 1):
+            self.render(wave - 1, wave, seed=seed, stream=stream)
+            if wave == next_update:
+                self.isg_store_update()
+                next_update *= 2
+
     def debug_intersect(self, rays7):
         rays7 = np.ascontiguousarray(rays7, dtype=np.float32).reshape(-1, 7)
         n = rays7.shape[0]

@@ -25,7 +25,7 @@ def _b(x):
 _LS = {A.LIGHTSAMPLER_UNIFORM: "uniform", A.LIGHTSAMPLER_POWER: "power", A.LIGHTSAMPLER_BVH: "bvh"}
 
 
-def integrator_block(ip, name="guidedvolpathvspg", cache_file=None, isg_file=None, tr_file=None):
+def integrator_block(ip, name="guidedvolpathvspg", cache_file=None, isg_file=None, tr_file=None, store_isg_file=None):
     """guidedvolpathvspgintegrator.cpp:1260-1322 parameter names."""
     p = [f'Integrator "{name}"',
          f'  "integer maxdepth" [{ip.max_depth}] "integer minrrdepth" [{ip.min_rr_depth}] "bool usenee" {_b(ip.use_nee)}',
@@ -41,11 +41,13 @@ def integrator_block(ip, name="guidedvolpathvspg", cache_file=None, isg_file=Non
         p.append(f'  "bool loadISGBuffer" true "string isgBufferFileName" "{isg_file}"')
     if tr_file:
         p.append(f'  "bool loadTrBuffer" true "string trBufferFileName" "{tr_file}"')
+    if store_isg_file:
+        p.append(f'  "bool storeISGBuffer" true "string isgBufferFileName" "{store_isg_file}"')
     return "\n".join(p)
 
 
 def scene_text(cfg, out_dir=None, outfile="out.exr", seed=0, integrator_name="guidedvolpathvspg", cache_file=None, isg_file=None,
-               tr_file=None, raw_density=False, placeholder_grids=False):
+               tr_file=None, raw_density=False, placeholder_grids=False, store_isg_file=None):
     """Returns the .pbrt text of `cfg` (a pyvspg.configs.Config).  With raw_density=True grids are written next to
     the scene as raw little-endian float32 files ("string densityfile", the front end's extension for grids too large
     for text) -- needs out_dir."""
@@ -59,7 +61,7 @@ def scene_text(cfg, out_dir=None, outfile="out.exr", seed=0, integrator_name="gu
          ('PixelFilter "box"' if fc.filter_type == 0 else
           f'PixelFilter "gaussian" "float xradius" [{_f(fc.filter_radius[0])}] "float yradius" [{_f(fc.filter_radius[1])}] '
           f'"float sigma" [{_f(fc.filter_sigma)}]'),
-         integrator_block(cfg.ip, integrator_name, cache_file, isg_file, tr_file),
+         integrator_block(cfg.ip, integrator_name, cache_file, isg_file, tr_file, store_isg_file),
          'WorldBegin']
     for kind, e in sc.log:
         if kind == "medium":
