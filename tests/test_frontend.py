@@ -251,6 +251,7 @@ def test_errors_mirror_the_reference_error_exits(body, code, needle):
     ('Integrator "guidedvolpath" "string vspsamplingmethod" "magic"', A.ERR_INVALID, "vspsamplingmethod"),
     ('Integrator "guidedvolpath" "bool storeISGBuffer" true "bool vspguiding" false "string isgBufferFileName" "x.exr"', A.ERR_UNSUPPORTED, "stores no VSP layer"),
     ('Integrator "guidedvolpath" "bool storeISGBuffer" true', A.ERR_INVALID, "without isgBufferFileName"),
+    ('Integrator "guidedvolpath" "bool rrguiding" true', A.ERR_UNSUPPORTED, "rrguiding"),
 ])
 def test_integrator_parameter_errors(integrator, code, needle):
     text = HEAD.replace(HEAD.splitlines()[5], integrator) + "WorldBegin\n"

@@ -383,7 +383,8 @@ struct Builder {
         S.load_tr = ps.one_bool("loadTrBuffer", false);
         S.tr_file = ps.one_string("trBufferFileName", "");
         // guided RR needs OPENPGL_RADIANCE_CACHES, which the reference builds OFF: the flags are inert.
-        ps.one_bool("rrguiding", false); ps.one_bool("surfacerrguiding", true); ps.one_bool("volumerrguiding", true);
+        const bool rrGuiding = ps.one_bool("rrguiding", false);   // surfacerrguiding / volumerrguiding only matter when it is on (vspg.cpp:279-290)
+        ps.one_bool("surfacerrguiding", true); ps.one_bool("volumerrguiding", true);
         std::string ls = ps.one_string("lightsampler", "bvh");
         if (ls == "uniform") ip.light_sampler = VSPG_LIGHTSAMPLER_UNIFORM;
         else if (ls == "power") ip.light_sampler = VSPG_LIGHTSAMPLER_POWER;
@@ -391,6 +392,9 @@ struct Builder {
         else lx.fail("Integrator: lightsampler \"" + ls + "\" unknown");
         ip.regularize = ps.one_bool("regularize", false);
         ps.report_unused();
+        if (rrGuiding)
+            lx.fail("Integrator: rrguiding (adjoint-driven Russian roulette from the denoised pixel-contribution estimate, vspg.cpp:279-290) is "
+                    "outside the hot-path scope; the throughput-based roulette of the default configuration is built", VSPG_ERR_UNSUPPORTED);
         if (store_cache)
             lx.fail("Integrator: storeGuidingCache requests a training pass of the guiding cache, which is out of scope (the cache is a "
                     "loaded input; storeTrBuffer and storeISGBuffer are supported)", VSPG_ERR_UNSUPPORTED);
