@@ -10,7 +10,7 @@ from pyvspg import _abi as A
 from pyvspg import api, configs, pbrt_writer
 from pyvspg.scenes import Scene, perspective_camera
 
-SCENES = ["c1", "c1t", "c1e", "c1s", "c2", "c2u", "c3", "c3nds", "c3contrib", "c4", "c4r", "c5", "c5u", "ch", "cg", "cn", "cnu"]
+SCENES = ["c1", "c1t", "c1e", "c1s", "c2", "c2u", "c3", "c3nds", "c3contrib", "c4", "c4r", "c5", "c5u", "ch", "cg", "cn", "cnu", "cp"]
 
 
 def write_inputs(golden_dir):
@@ -54,6 +54,11 @@ def _guided(name, kind="grid", filt=None, lights="pa", **ipkw):
     if "t" in lights:
         sc.add_triangles([[-0.6, 0.9, 0.1], [-0.3, 1.0, 0.2], [-0.5, 0.95, 0.5], [-0.2, 1.2, 0.6]], [[0, 1, 2], [1, 3, 2]], material=red,
                          emission=[8.0, 9.0, 12.0], two_sided=True)
+    if "m" in lights:   # Shape "plymesh": tests/golden/mesh_small.ply (4 triangles + 2 quads, binary), emissive, and its ascii twin as a diffuse object
+        gold = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
+        sc.add_plymesh(os.path.join(gold, "mesh_small.ply"), 4, 2, material=red, emission=[14.0, 12.0, 9.0], two_sided=True, translate=[-0.7, 0.7, 0.1],
+                       written_name="../mesh_small.ply")
+        sc.add_plymesh(os.path.join(gold, "mesh_small_ascii.ply"), 4, 2, material=white, translate=[1.25, -0.05, -0.3], written_name="../mesh_small_ascii.ply")
     if "b" in lights:
         sc.add_triangle_box([1.2, -0.05, 0.6], [1.5, 0.4, 0.9], material=red)
     ip = api.integrator_defaults(**ipkw)
@@ -98,6 +103,8 @@ def _config(name):
         return _guided(name, kind="nvdb", light_sampler=B)
     if name == "cnu":    # NanoVDB medium, guiding off
         return _guided(name, kind="nvdb", light_sampler=P, surface_guiding=0, volume_guiding=0, vsp_guiding=0)
+    if name == "cp":     # PLY meshes (triangles + bilinear patches from one file), emissive and diffuse
+        return _guided(name, lights="pm", light_sampler=B)
     if name == "ch":
         return _guided(name, kind="hom", light_sampler=B, vsp_mis_ratio=0.3)
     if name == "cg":

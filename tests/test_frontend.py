@@ -299,3 +299,33 @@ def test_render_through_the_front_end_equals_render_through_the_harness(tmp_path
     assert films[0][..., :3].sum() > 0
     np.testing.assert_allclose(films[0], films[1], rtol=1e-6, atol=1e-9)
     hs.close()
+
+
+def test_plymesh_reader_errors(tmp_path):
+    """Shape "plymesh" (util/mesh.cpp:322-420): the reference's error exits, plus what this path leaves out by name."""
+    def parse(body):
+        return api.HostScene(text=HEAD + "WorldBegin\n" + body, base_dir=str(tmp_path))
+    with pytest.raises(api.VspgError) as e:
+        parse('Shape "plymesh" "string filename" "nope.ply"\n')
+    assert e.value.code == A.ERR_IO and "Couldn't open PLY file" in str(e.value)
+    (tmp_path / "n.ply").write_text("ply\nformat ascii 1.0\nelement vertex 3\nproperty float x\nproperty float y\nproperty float z\nproperty float nx\n"
+                                    "property float ny\nproperty float nz\nelement face 1\nproperty list uchar int vertex_indices\nend_header\n"
+                                    "0 0 0 0 0 1\n1 0 0 0 0 1\n0 1 0 0 0 1\n3 0 1 2\n")
+    with pytest.raises(api.VspgError) as e:
+        parse('Shape "plymesh" "string filename" "n.ply"\n')
+    assert e.value.code == A.ERR_UNSUPPORTED and "per-vertex normals" in str(e.value)
+    (tmp_path / "p.ply").write_text("ply\nformat ascii 1.0\nelement vertex 5\nproperty float x\nproperty float y\nproperty float z\nelement face 1\n"
+                                    "property list uchar int vertex_indices\nend_header\n0 0 0\n1 0 0\n1 1 0\n0 1 0\n.5 .5 1\n5 0 1 2 3 4\n")
+    with pytest.raises(api.VspgError) as e:
+        parse('Shape "plymesh" "string filename" "p.ply"\n')
+    assert "Only triangles and quads" in str(e.value)
+    (tmp_path / "i.ply").write_text("ply\nformat ascii 1.0\nelement vertex 3\nproperty float x\nproperty float y\nproperty float z\nelement face 1\n"
+                                    "property list uchar int vertex_indices\nend_header\n0 0 0\n1 0 0\n0 1 0\n3 0 1 7\n")
+    with pytest.raises(api.VspgError) as e:
+        parse('Shape "plymesh" "string filename" "i.ply"\n')
+    assert "out of bounds" in str(e.value)
+    (tmp_path / "ok.ply").write_text("ply\nformat ascii 1.0\nelement vertex 4\nproperty float x\nproperty float y\nproperty float z\nelement face 2\n"
+                                     "property list uchar int vertex_indices\nend_header\n0 0 0\n1 0 0\n1 1 0\n0 1 0\n3 0 1 2\n4 0 1 2 3\n")
+    hs = parse('Shape "plymesh" "string filename" "ok.ply"\n')
+    assert (hs.desc.n_triangles, hs.desc.n_quads) == (1, 1)
+    hs.close()

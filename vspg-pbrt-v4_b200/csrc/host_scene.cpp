@@ -33,6 +33,7 @@
 
 #include "../../include/vspg.h"
 #include "host_nvdb.h"
+#include "host_ply.h"
 #include "host_xform.h"
 
 namespace {
@@ -663,6 +664,35 @@ void Builder::shape(const std::string &type, const Params &ps, Lexer &lx) {
     XF rfo = render_from_object();
     ShapeAttr a = shape_attr(lx, rfo);
     if (ps.find("alpha", {"texture", "float"})) lx.fail("Shape: alpha textures are not supported", VSPG_ERR_UNSUPPORTED);
+    auto emit_quads = [&](const std::vector<double> &P, size_t nv, const std::vector<double> &idx, const char *what) {
+        for (size_t q = 0; q < idx.size(); q += 4) {
+            vspg_quad d{};
+            float *dst[4] = {d.p00, d.p10, d.p01, d.p11};
+            for (int k = 0; k < 4; k++) {
+                size_t vi = (size_t)idx[q + k];
+                if (idx[q + k] < 0 || vi >= nv) lx.fail(std::string(what) + ": vertex index out of range");
+                to_render(rfo, &P[3 * vi], dst[k]);
+            }
+            d.material = a.material; d.medium_inside = a.mi; d.medium_outside = a.mo; d.has_interface = a.has_interface; d.flip_normal = a.flip;
+            float area = tri_area(d.p00, d.p10, d.p11) + tri_area(d.p00, d.p11, d.p01);   // only used for "power"; exact area is computed by set_scene
+            d.area_light = attach_area_light(0, (int)S.quads.size(), area, lx);
+            S.quads.push_back(d);
+        }
+    };
+    auto emit_tris = [&](const std::vector<double> &P, size_t nv, const std::vector<double> &idx, const char *what) {
+        for (size_t t = 0; t < idx.size(); t += 3) {
+            vspg_triangle d{};
+            float *dst[3] = {d.p0, d.p1, d.p2};
+            for (int k = 0; k < 3; k++) {
+                size_t vi = (size_t)idx[t + k];
+                if (idx[t + k] < 0 || vi >= nv) lx.fail(std::string(what) + ": vertex index out of range");
+                to_render(rfo, &P[3 * vi], dst[k]);
+            }
+            d.material = a.material; d.medium_inside = a.mi; d.medium_outside = a.mo; d.has_interface = a.has_interface; d.flip_normal = a.flip;
+            d.area_light = attach_area_light(1, (int)S.tris.size(), tri_area(d.p0, d.p1, d.p2), lx);
+            S.tris.push_back(d);
+        }
+    };
     if (type == "bilinearmesh") {
         const auto *P = ps.points("P");
         if (!P || P->size() % 3) lx.fail("bilinearmesh: vertex positions \"P\" not provided / malformed");
@@ -675,19 +705,7 @@ void Builder::shape(const std::string &type, const Params &ps, Lexer &lx) {
         if (ps.find("uv", {"point2"}) || ps.find("N", {"normal", "normal3"}) || !ps.one_string("emissionfilename", "").empty())
             lx.fail("bilinearmesh: per-vertex uv / N / emission images are not supported", VSPG_ERR_UNSUPPORTED);
         ps.report_unused();
-        for (size_t q = 0; q < idx.size(); q += 4) {
-            vspg_quad d{};
-            float *dst[4] = {d.p00, d.p10, d.p01, d.p11};
-            for (int k = 0; k < 4; k++) {
-                size_t vi = (size_t)idx[q + k];
-                if (idx[q + k] < 0 || vi >= nv) lx.fail("bilinearmesh: vertex index out of range");
-                to_render(rfo, &(*P)[3 * vi], dst[k]);
-            }
-            d.material = a.material; d.medium_inside = a.mi; d.medium_outside = a.mo; d.has_interface = a.has_interface; d.flip_normal = a.flip;
-            float area = tri_area(d.p00, d.p10, d.p11) + tri_area(d.p00, d.p11, d.p01);   // only used for "power"; exact area is computed by set_scene
-            d.area_light = attach_area_light(0, (int)S.quads.size(), area, lx);
-            S.quads.push_back(d);
-        }
+        emit_quads(*P, nv, idx, "bilinearmesh");
     } else if (type == "trianglemesh") {
         const auto *P = ps.points("P");
         if (!P || P->size() % 3) lx.fail("trianglemesh: vertex positions \"P\" not provided / malformed");
@@ -701,18 +719,21 @@ void Builder::shape(const std::string &type, const Params &ps, Lexer &lx) {
             lx.fail("trianglemesh: shading normals / tangents are not supported (geometric normals only)", VSPG_ERR_UNSUPPORTED);
         ps.find("uv", {"point2"});   // uv only feeds textures, which this path does not have
         ps.report_unused();
-        for (size_t t = 0; t < idx.size(); t += 3) {
-            vspg_triangle d{};
-            float *dst[3] = {d.p0, d.p1, d.p2};
-            for (int k = 0; k < 3; k++) {
-                size_t vi = (size_t)idx[t + k];
-                if (idx[t + k] < 0 || vi >= nv) lx.fail("trianglemesh: vertex index out of range");
-                to_render(rfo, &(*P)[3 * vi], dst[k]);
-            }
-            d.material = a.material; d.medium_inside = a.mi; d.medium_outside = a.mo; d.has_interface = a.has_interface; d.flip_normal = a.flip;
-            d.area_light = attach_area_light(1, (int)S.tris.size(), tri_area(d.p0, d.p1, d.p2), lx);
-            S.tris.push_back(d);
-        }
+        emit_tris(*P, nv, idx, "trianglemesh");
+    } else if (type == "plymesh") {   // shapes.cpp:1415-1472: triangles first, then the quads as bilinear patches
+        std::string filename = ps.one_string("filename", "");
+        if (filename.empty()) lx.fail("plymesh: no \"filename\" given");
+        ps.one_float("edgelength", 1);
+        if (ps.find("displacement", {"texture"})) lx.fail("plymesh: displacement is not supported", VSPG_ERR_UNSUPPORTED);
+        ps.report_unused();
+        vspg_host::PlyMesh mesh;
+        std::string err;
+        if (!vspg_host::read_ply(resolve(filename), &mesh, &err)) lx.fail(err, VSPG_ERR_IO);
+        if (mesh.has_normals) lx.fail("plymesh: \"" + filename + "\" carries per-vertex normals; shading normals are not supported (geometric normals only)", VSPG_ERR_UNSUPPORTED);
+        std::vector<double> P(mesh.p.begin(), mesh.p.end());   // (uv only feeds textures, which this path does not have)
+        const size_t nv = P.size() / 3;
+        emit_tris(P, nv, std::vector<double>(mesh.tri.begin(), mesh.tri.end()), "plymesh");
+        emit_quads(P, nv, std::vector<double>(mesh.quad.begin(), mesh.quad.end()), "plymesh");
     } else if (type == "sphere") {
         double r = ps.one_float("radius", 1);
         double zmin = ps.one_float("zmin", -r), zmax = ps.one_float("zmax", r), phimax = ps.one_float("phimax", 360);
@@ -731,7 +752,7 @@ void Builder::shape(const std::string &type, const Params &ps, Lexer &lx) {
         d.area_light = attach_area_light(2, (int)S.spheres.size(), (float)(4 * M_PI * d.radius * d.radius), lx);
         S.spheres.push_back(d);
     } else
-        lx.fail("Shape \"" + type + "\": supported shapes are bilinearmesh, trianglemesh, sphere (PLY / curves / etc. are SURVEY 8f3)", VSPG_ERR_UNSUPPORTED);
+        lx.fail("Shape \"" + type + "\": supported shapes are bilinearmesh, trianglemesh, plymesh, sphere (curves / cylinders / disks / subdivision surfaces are SURVEY 8f3)", VSPG_ERR_UNSUPPORTED);
 }
 
 double num(Lexer &lx, const char *what) {

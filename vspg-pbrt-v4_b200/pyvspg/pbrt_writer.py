@@ -121,6 +121,16 @@ def scene_text(cfg, out_dir=None, outfile="out.exr", seed=0, integrator_name="gu
             L.append('  Shape "trianglemesh" "point3 P" [' + "  ".join(_v(p) for p in e["points"]) + '] "integer indices" ['
                      + "  ".join(" ".join(str(i) for i in t) for t in e["indices"]) + "]")
             L.append("AttributeEnd")
+        elif kind == "plymesh":
+            L.append("AttributeBegin")
+            if e.get("translate") is not None:
+                L.append(f'  Translate {_v(e["translate"])}')
+            L.append(f'  NamedMaterial "mat{e["material"]}"' if e["material"] >= 0 else '  Material "interface"')
+            if e.get("emission") is not None:
+                L.append(f'  AreaLightSource "diffuse" "rgb L" [{_v(e["emission"])}] "bool twosided" {_b(e["two_sided"])}')
+            fn = e["filename"] if placeholder_grids else (e.get("written_name") or e["filename"])
+            L.append(f'  Shape "plymesh" "string filename" "{fn}"')
+            L.append("AttributeEnd")
         elif kind == "sphere":
             L.append("AttributeBegin")
             if e["has_interface"]:

@@ -84,6 +84,18 @@ class Scene:
             self.n_lights += 1
         return self.n_spheres - 1
 
+    def add_plymesh(self, filename, n_triangles, n_quads, material=-1, emission=None, two_sided=False, translate=None, written_name=None):
+        """Shape "plymesh" (shapes.cpp:1415-1472): the front end reads the file; triangles come first, then the quads as
+        bilinear patches.  The face counts are the caller's (who wrote the file); finalize checks them."""
+        import os
+        self.log.append(("plymesh", dict(filename=os.path.abspath(filename), written_name=written_name, material=material,
+                                         emission=None if emission is None else [float(x) for x in emission], two_sided=bool(two_sided),
+                                         translate=None if translate is None else [float(x) for x in translate])))
+        self.n_triangles += n_triangles
+        self.n_quads += n_quads
+        if emission is not None:
+            self.n_lights += n_triangles + n_quads
+
     def add_triangle_box(self, lo, hi, **kw):
         """Axis-aligned box as 12 outward-facing triangles (n = normalize(cross(p0 - p2, p1 - p2)))."""
         a, b = np.asarray(lo, dtype=np.float64), np.asarray(hi, dtype=np.float64)
