@@ -161,8 +161,10 @@ template <int G> VD void mix_parallax_shift(LiLobe &L, int cnt, V3 s) {
     }
 }
 // :861-880
-// by value + noinline: 17 call sites per scatter kernel; inlining them blew the kernels past the instruction cache
-template <int G> __device__ __noinline__ float mix_pdf(Lobe L, int cnt, V3 d) {
+#ifndef VSPG_MIX_ATTR
+#define VSPG_MIX_ATTR __forceinline__   // r02: once the kernels had shrunk (KINDS, unrolled reductions) inlining won 2 % (was a loss in round 1)
+#endif
+template <int G> __device__ VSPG_MIX_ATTR float mix_pdf(Lobe L, int cnt, V3 d) {
     int i = grp_lane<G>();
     float val = 0.f;
     if (i < 4 * cnt) {
@@ -174,7 +176,7 @@ template <int G> __device__ __noinline__ float mix_pdf(Lobe L, int cnt, V3 d) {
     return mix_reduce<G>(val, cnt);
 }
 // :1237-1258
-template <int G> __device__ __noinline__ float mix_vsp(LiLobe L, int cnt, V3 d) {
+template <int G> __device__ VSPG_MIX_ATTR float mix_vsp(LiLobe L, int cnt, V3 d) {
     int i = grp_lane<G>();
     float e = 0.f, ev = 0.f;
     if (i < 4 * cnt) {
@@ -216,7 +218,10 @@ template <int G> VD float mix_product(Lobe &L, int n, int cnt, float _w, V3 md, 
     return integral;
 }
 // :970-1031 selectComponentSIMD + :1086-1129 sample.  s0 drives cos(theta), s1 picks the lobe and becomes phi.
-template <int G> __device__ __noinline__ V3 mix_sample(Lobe L, int n, float s0, float s1) {
+#ifndef VSPG_MIXS_ATTR
+#define VSPG_MIXS_ATTR __noinline__
+#endif
+template <int G> __device__ VSPG_MIXS_ATTR V3 mix_sample(Lobe L, int n, float s0, float s1) {
     int lane = grp_lane<G>(), l = lane & 3, base = lane & ~3;
     float v0 = gshfl<G>(L.w, base), v1 = gshfl<G>(L.w, base + 1);
     float v2 = gshfl<G>(L.w, base + 2), v3 = gshfl<G>(L.w, base + 3);
