@@ -149,9 +149,15 @@ VD void rs_finalize(const DScene &sc, const Wavefront &W, RsLane<GRAY> &s) {
 #ifndef VSPG_RS_MINB
 #define VSPG_RS_MINB 5                    // resident CTAs/SM of the gray resampling kernel's default build (A/B knob)
 #endif
-constexpr int kRsRefillIdleDefault = 12;    // fetch new rays once this many lanes of the warp are idle (kernel argument: VSPG_RS_REFILL for A/B runs)
-constexpr int kRsTripsPerCheck = 4; // collisions between two refill checks
-constexpr int kRsSearchMax = 4;     // search steps before the collision body runs for the lanes that are ready
+constexpr int kRsRefillIdleDefault = 16;    // fetch new rays once this many lanes of the warp are idle (kernel argument: VSPG_RS_REFILL for A/B runs)
+#ifndef VSPG_RS_TRIPS
+#define VSPG_RS_TRIPS 4
+#endif
+#ifndef VSPG_RS_SEARCH
+#define VSPG_RS_SEARCH 4
+#endif
+constexpr int kRsTripsPerCheck = VSPG_RS_TRIPS; // collisions between two refill checks
+constexpr int kRsSearchMax = VSPG_RS_SEARCH;     // search steps before the collision body runs for the lanes that are ready
 
 // One search step of media_sampleTMaj.h:183-246 for one lane, straight-line: (A) if the lane needs a majorant segment,
 // pull the next one from the DDA; (B) if it is inside a segment, draw the next exponential step.  Returns with `hit`
