@@ -131,19 +131,24 @@ VD void shadow_store(const PathSoA &P, int s, const ShadowRec &r) {
 // streams; the G-lane kernels then only skip the three sampler dimensions and read the record back.  Same
 // arithmetic, same stream positions: bit-identical to sampling inside the scatter kernel.
 struct NeePre { bool valid, delta; V3 L, wi, pLight, pLightErr, nLight; float p_l; };
+// second half of the pre-sample: Light::SampleLi for the picked light
 template <int KINDS = kKindsAll>
-VD NeePre nee_presample(const DScene &sc, Rng rng, V3 ctxP, V3 ctxNs) {
+VD NeePre nee_finish(const DScene &sc, int light, float pmf, V3 ctxP, V3 ctxNs, float ul0, float ul1) {
     NeePre np; np.valid = false; np.delta = false; np.p_l = 0;
-    float u = rng.uniform();
-    float pmf = 0;
-    int light = sample_light(sc, u, &pmf, ctxP, ctxNs);
-    float ul0 = rng.uniform(), ul1 = rng.uniform();
     if (light < 0) return np;
     LiSample ls = sample_li<KINDS>(sc, light, ctxP, ctxNs, ul0, ul1);
     if (!(ls.valid && nonzero(ls.L) && ls.pdf != 0)) return np;
     np.valid = true; np.delta = ls.delta; np.L = ls.L; np.wi = ls.wi; np.pLight = ls.pLight; np.pLightErr = ls.pLightErr; np.nLight = ls.nLight;
     np.p_l = pmf * ls.pdf;
     return np;
+}
+template <int KINDS = kKindsAll>
+VD NeePre nee_presample(const DScene &sc, Rng rng, V3 ctxP, V3 ctxNs) {
+    float u = rng.uniform();
+    float pmf = 0;
+    int light = sample_light(sc, u, &pmf, ctxP, ctxNs);
+    float ul0 = rng.uniform(), ul1 = rng.uniform();
+    return nee_finish<KINDS>(sc, light, pmf, ctxP, ctxNs, ul0, ul1);
 }
 VD void nee_store(const PathSoA &P, int s, const NeePre &n) {
     P.sh_rl[s] = make_float4(n.wi.x, n.wi.y, n.wi.z, __int_as_float((n.valid ? 1 : 0) | (n.delta ? 2 : 0)));
@@ -216,46 +221,73 @@ template <int G> VD void scatter_phase_sync() {
 // (field/Field.h:114-150; guiding.h:83-109 / 383-398 front half).  One THREAD per vertex: draws the sampler's `v`,
 // walks the KD tree, picks the stochastic neighbour, and sorts the vertex into the queue of the lane-group width its
 // mixture needs (<= 8 lobes -> G8, <= 16 -> G16, else G32; vertices without a usable region go to G8).
+// Area-light samples (spherical rectangle / triangle / cone sampling: ~10x the work of a point or distant light) are not
+// taken where they are drawn: the CTA collects them in shared memory and then works the list off with consecutive
+// threads, so that the heavy code runs on full warps instead of on the few lanes per warp that picked such a light
+// (profiles/r02r: 8.5 of 32 lanes).
+struct HeavyNee { int slot, light; float pmf, u0, u1, p[3], ns[3]; };
 template <bool SURFACE, int KINDS = kKindsAll>
 __global__ void __launch_bounds__(kBlock) k_lookup(const DScene sc, const Wavefront W, const Queue in, const Queue q8, const Queue q16, const Queue q32) {
+    __shared__ HeavyNee heavy[kBlock];
+    __shared__ int heavyCount;
     const int n = *in.count;
     unsigned lookups = 0;
-    for (int i = gtid(); i < n; i += gstride()) {
-        int slot = in.items[i];
-        ulonglong2 q = W.P.rng[slot];
-        Rng rng; rng.state = q.x; rng.inc = q.y;
-        float v = rng.uniform();
-        W.P.rng[slot] = make_ulonglong2(rng.state, rng.inc);
-        V3 p; bool want = true;
-        if (SURFACE) {
-            float4 a = W.P.o_dx[slot], b = W.P.d_med[slot], hr = W.P.hit[slot];
-            p = V3(a.x, a.y, a.z) + hr.x * V3(a.w, b.x, b.y);
-            const DQuad &Q = sc.quads[__float_as_int(hr.w)];
-            want = nonzero(ld3(sc.materials[Q.material].reflectance));   // GuidedBSDF::init only looks up for non-specular BSDFs
-        } else { float4 e = W.P.ev[slot]; p = V3(e.x, e.y, e.z); }
-        const DField &f = SURFACE ? sc.surf : sc.vol;
-        int r = -1, nl = 0;
-        if (want) {
-            int leaf;
-            r = field_get_region(f, p, &v, &leaf);
-            if (leaf >= 0) lookups++;
-            if (r >= 0) { if (__ldg(&f.regions[r].valid)) nl = __ldg(&f.regions[r].num_components); else r = -1; }
-        }
-        W.P.lk[slot] = r;
-        if (sc.ip.use_nee) {
+    for (int base = blockIdx.x * blockDim.x; base < n; base += gstride()) {
+        if (threadIdx.x == 0) heavyCount = 0;
+        __syncthreads();
+        const int i = base + threadIdx.x;
+        if (i < n) {
+            int slot = in.items[i];
+            ulonglong2 q = W.P.rng[slot];
+            Rng rng; rng.state = q.x; rng.inc = q.y;
+            float v = rng.uniform();
+            W.P.rng[slot] = make_ulonglong2(rng.state, rng.inc);
+            V3 p; bool want = true;
             if (SURFACE) {
-                if (want) {   // GuidedBSDF::non_specular(): reflective-only BSDF, ctx.pi = intr.OffsetRayOrigin(intr.wo) (vspg.cpp:1147-1149)
+                float4 a = W.P.o_dx[slot], b = W.P.d_med[slot], hr = W.P.hit[slot];
+                p = V3(a.x, a.y, a.z) + hr.x * V3(a.w, b.x, b.y);
+                const DQuad &Q = sc.quads[__float_as_int(hr.w)];
+                want = nonzero(ld3(sc.materials[Q.material].reflectance));   // GuidedBSDF::init only looks up for non-specular BSDFs
+            } else { float4 e = W.P.ev[slot]; p = V3(e.x, e.y, e.z); }
+            const DField &f = SURFACE ? sc.surf : sc.vol;
+            int r = -1, nl = 0;
+            if (want) {
+                int leaf;
+                r = field_get_region(f, p, &v, &leaf);
+                if (leaf >= 0) lookups++;
+                if (r >= 0) { if (__ldg(&f.regions[r].valid)) nl = __ldg(&f.regions[r].num_components); else r = -1; }
+            }
+            W.P.lk[slot] = r;
+            if (sc.ip.use_nee && want) {
+                V3 ctxP = p, ctxNs;
+                if (SURFACE) {   // GuidedBSDF::non_specular(): reflective-only BSDF, ctx.pi = intr.OffsetRayOrigin(intr.wo) (vspg.cpp:1147-1149)
                     float4 a = W.P.o_dx[slot], b = W.P.d_med[slot], hr = W.P.hit[slot];
                     Hit h; h.t = hr.x; h.u = hr.y; h.v = hr.z; h.prim = __float_as_int(hr.w);
                     V3 ro(a.x, a.y, a.z), rd(a.w, b.x, b.y);
                     SurfaceIntr isect = make_intr<KINDS>(sc, h, ro, rd, __float_as_int(b.z));
-                    nee_store(W.P, slot, nee_presample<KINDS>(sc, rng, offset_ray_origin(isect.p, isect.pError, isect.n, isect.wo), isect.ns));
+                    ctxP = offset_ray_origin(isect.p, isect.pError, isect.n, isect.wo); ctxNs = isect.ns;
                 }
-            } else nee_store(W.P, slot, nee_presample<KINDS>(sc, rng, p, V3()));
+                // nee_presample, with SampleLi of area lights deferred (rng is a copy: the path's stream is not advanced here)
+                float u = rng.uniform();
+                float pmf = 0;
+                int light = sample_light(sc, u, &pmf, ctxP, ctxNs);
+                float ul0 = rng.uniform(), ul1 = rng.uniform();
+                if (light >= 0 && sc.lights[light].type == VSPG_LIGHT_DIFFUSE_AREA) {
+                    HeavyNee &hn = heavy[atomicAdd(&heavyCount, 1)];
+                    hn.slot = slot; hn.light = light; hn.pmf = pmf; hn.u0 = ul0; hn.u1 = ul1;
+                    hn.p[0] = ctxP.x; hn.p[1] = ctxP.y; hn.p[2] = ctxP.z; hn.ns[0] = ctxNs.x; hn.ns[1] = ctxNs.y; hn.ns[2] = ctxNs.z;
+                } else nee_store(W.P, slot, nee_finish<KINDS>(sc, light, pmf, ctxP, ctxNs, ul0, ul1));
+            }
+            queue_push(q8, nl <= 8, slot);
+            queue_push(q16, nl > 8 && nl <= 16, slot);
+            queue_push(q32, nl > 16, slot);
         }
-        queue_push(q8, nl <= 8, slot);
-        queue_push(q16, nl > 8 && nl <= 16, slot);
-        queue_push(q32, nl > 16, slot);
+        __syncthreads();
+        for (int k = threadIdx.x; k < heavyCount; k += blockDim.x) {
+            const HeavyNee hn = heavy[k];
+            nee_store(W.P, hn.slot, nee_finish<KINDS>(sc, hn.light, hn.pmf, ld3(hn.p), ld3(hn.ns), hn.u0, hn.u1));
+        }
+        __syncthreads();
     }
     counter_add(W.counters, CNT_LOOKUPS, lookups);
 }
