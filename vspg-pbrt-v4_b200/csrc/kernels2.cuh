@@ -87,7 +87,7 @@ __global__ void __launch_bounds__(kBlock, VSPG_SURFACE_MINB) k_surface(const DSc
 // vertex, and the path record is read and written by the group's leader only, straight from / to the SoA streams.
 struct ShadeKeep { float p[3], pe[3], n[3], ns[3]; int mIn, mOut, rayMed, hasIf; };
 #ifndef VSPG_SHADE_MINB
-#define VSPG_SHADE_MINB 3
+#define VSPG_SHADE_MINB 4   // r02: 4 CTAs of 256 threads (64 registers) beat 3 (80): C2 shade 13.5 -> 12.7 ms, C4 32.4 -> 29.7 ms
 #endif
 template <int G, int KINDS = kKindsAll>
 __global__ void __launch_bounds__(G > 0 ? 256 : kBlock, G > 0 ? VSPG_SHADE_MINB : 1) k_shade(const DScene sc, const Wavefront W, const Queue in) {
