@@ -7,6 +7,13 @@
 namespace vspg {
 
 constexpr int kBlock = 128;
+// resident CTAs per SM the thread-per-item kernels are compiled for (A/B knobs; 1 = let the compiler choose)
+#ifndef VSPG_LOOKUP_MINB
+#define VSPG_LOOKUP_MINB 8   // latency-bound KD walk: 64 registers, 8 CTAs per SM (C2 -0.7 ms)
+#endif
+#ifndef VSPG_INTERSECT_MINB
+#define VSPG_INTERSECT_MINB 1
+#endif
 
 VD int gtid() { return blockIdx.x * blockDim.x + threadIdx.x; }
 VD int gstride() { return gridDim.x * blockDim.x; }
@@ -50,7 +57,7 @@ __global__ void __launch_bounds__(kBlock) k_generate(const DScene sc, const Wave
 
 // ------------------------------------------------------------------ closest hit (vspg.cpp:314)
 template <int KINDS = kKindsAll>
-__global__ void __launch_bounds__(kBlock) k_intersect(const DScene sc, const Wavefront W) {
+__global__ void __launch_bounds__(kBlock, VSPG_INTERSECT_MINB) k_intersect(const DScene sc, const Wavefront W) {
     const int n = *W.active.count;
     unsigned nodes = 0, preSteps = 0;
     for (int i = gtid(); i < n; i += gstride()) {
@@ -227,7 +234,7 @@ template <int G> VD void scatter_phase_sync() {
 // (profiles/r02r: 8.5 of 32 lanes).
 struct HeavyNee { int slot, light; float pmf, u0, u1, p[3], ns[3]; };
 template <bool SURFACE, int KINDS = kKindsAll>
-__global__ void __launch_bounds__(kBlock) k_lookup(const DScene sc, const Wavefront W, const Queue in, const Queue q8, const Queue q16, const Queue q32) {
+__global__ void __launch_bounds__(kBlock, VSPG_LOOKUP_MINB) k_lookup(const DScene sc, const Wavefront W, const Queue in, const Queue q8, const Queue q16, const Queue q32) {
     __shared__ HeavyNee heavy[kBlock];
     __shared__ int heavyCount;
     const int n = *in.count;
