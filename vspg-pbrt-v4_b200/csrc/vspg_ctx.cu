@@ -17,6 +17,7 @@
 #include "host_lightpower.h"
 #include "kernels2.cuh"
 #include "kbin.cuh"
+#include "kshadow_p.cuh"
 #include "debug_kernels.cuh"
 
 using namespace vspg;
@@ -60,6 +61,8 @@ struct vspg_ctx {
     int grid_layout = GRID_CELL8;
     int scatter_block = 256;   // VSPG_SCATTER_BLOCK overrides (A/B runs)
     int volscatter_ctas = 2, shade_ctas = 2, scatter_ctas_block = 0;   // resident CTAs/SM of the scatter kernels (occupancy API, per scatter_block)
+    int shadow_persist = 0;     // VSPG_SHADOW_PERSIST=1: shadow rays through the persistent-lane kernel (kshadow_p.cuh); measured slower than one thread per ray (profiles/r02_summary.md)
+    int shadow_refill = 16;
     int band_mode = -1;         // sample order of a render: 0 = pass-major, -1 = band-major with automatic band height, n > 0 = n rows (VSPG_BAND_ROWS)
     int sort_mode = 0;          // coherence pass (kbin.cuh): bit 0 = medium queue, bit 1 = shadow queue (VSPG_SORT)
     bool bin_ok = false;        // the scene has a grid medium to bin over
@@ -177,6 +180,8 @@ int vspg_create(vspg_ctx **out, int device_ordinal) {
     if (const char *g = getenv("VSPG_GRAPH")) ctx->use_graph = atoi(g) != 0;
     if (const char *g = getenv("VSPG_SORT")) ctx->sort_mode = atoi(g) & 3;
     if (const char *g = getenv("VSPG_BAND_ROWS")) ctx->band_mode = atoi(g);
+    if (const char *g = getenv("VSPG_SHADOW_PERSIST")) ctx->shadow_persist = atoi(g) != 0;
+    if (const char *g = getenv("VSPG_SHADOW_REFILL")) { int v = atoi(g); if (v >= 1 && v <= 32) ctx->shadow_refill = v; }
     if (const char *ro = getenv("VSPG_RS_OCC")) { int v = atoi(ro); if (v == 4 || v == 5) ctx->rs_occ = v; }
     const char *lay = getenv("VSPG_GRID_LAYOUT");
     if (lay && std::string(lay) == "linear") ctx->grid_layout = GRID_LINEAR;

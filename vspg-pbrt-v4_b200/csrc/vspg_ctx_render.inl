@@ -5,7 +5,7 @@ enum { Q_A = 0, Q_B = 1, Q_MEDIUM = 2, Q_SURFACE = 3, Q_SHADE = 4, Q_VOLSCATTER 
        Q_CURSORS = 4, Q_INTS = Q_COUNT + Q_CURSORS };  // + per-kernel dynamic work cursors
 
 // Everything the captured wave graph depends on; compared bytewise against the current values before each replay.
-struct WaveGraphKey { DScene sc; Wavefront W; int vgrid, sgrid, sblock, rs_refill, rs_occ, nGridWin, all_gray, any_nvdb, sort_mode, prim_kinds; cudaAccessPolicyWindow win; };
+struct WaveGraphKey { DScene sc; Wavefront W; int vgrid, sgrid, sblock, rs_refill, rs_occ, nGridWin, all_gray, any_nvdb, sort_mode, prim_kinds, shadow_persist; cudaAccessPolicyWindow win; };
 
 static int ensure_wavefront(vspg_ctx *ctx, unsigned long long total) {
     // Default: up to 16.8 M paths in flight (5.7 GB of the 180 GB).  Measured on C2 (profiles/r01z_summary.md, r02b/c): 2 M ->
@@ -207,6 +207,14 @@ int vspg_render(vspg_ctx *ctx, int spp_begin, int spp_end, int spp_stride, int x
             }
         } else VSPG_STAGE(VSPG_K_SHADE, (k_shade<0><<<ctx->g_shade0, kBlock, 0, s>>>(sc, Wh, Wh.shade)));
         if (sortMode & 2) { sort_queue(Wh0.shadow, 1, ctx->sorted_shadow); Wh.shadow.items = ctx->sorted_shadow; }
+        if (ctx->shadow_persist) {   // persistent lanes; work cursor = the second dynamic cursor (cleared with the queue counters)
+            int *cur = ctx->qcounts + Q_COUNT + 1;
+            const int g = ctx->sm_count * VSPG_SHADOWP_MINB;
+            if (ctx->all_gray && quadsOnly) VSPG_STAGE(VSPG_K_SHADOW, CK(launch_tracking(k_shadow_p<true, kKindsQuads>, g, sc, Wh, cur, ctx->shadow_refill)));
+            else if (ctx->all_gray) VSPG_STAGE(VSPG_K_SHADOW, CK(launch_tracking(k_shadow_p<true, kKindsAll>, g, sc, Wh, cur, ctx->shadow_refill)));
+            else if (quadsOnly) VSPG_STAGE(VSPG_K_SHADOW, CK(launch_tracking(k_shadow_p<false, kKindsQuads>, g, sc, Wh, cur, ctx->shadow_refill)));
+            else VSPG_STAGE(VSPG_K_SHADOW, CK(launch_tracking(k_shadow_p<false, kKindsAll>, g, sc, Wh, cur, ctx->shadow_refill)));
+        } else
         if (ctx->all_gray && quadsOnly) VSPG_STAGE(VSPG_K_SHADOW, CK(launch_tracking(k_shadow<true, kKindsQuads>, ctx->g_shadow_gray, sc, Wh)));
         else if (ctx->all_gray) VSPG_STAGE(VSPG_K_SHADOW, CK(launch_tracking(k_shadow<true, kKindsAll>, ctx->g_shadow_gray, sc, Wh)));
         else if (quadsOnly) VSPG_STAGE(VSPG_K_SHADOW, CK(launch_tracking(k_shadow<false, kKindsQuads>, ctx->g_shadow_rgb, sc, Wh)));
@@ -240,7 +248,7 @@ int vspg_render(vspg_ctx *ctx, int spp_begin, int spp_end, int spp_stride, int x
         // all of which are compared below; it is rebuilt when any of them changed.
         WaveGraphKey key;
         memset(&key, 0, sizeof key);
-        key.sc = sc; key.W = Wab; key.vgrid = vgrid; key.sgrid = sgrid; key.sblock = sblock; key.rs_refill = ctx->rs_refill; key.rs_occ = ctx->rs_occ; key.all_gray = ctx->all_gray; key.prim_kinds = ctx->prim_kinds; key.sort_mode = ctx->bin_ok ? ctx->sort_mode : 0; key.any_nvdb = ctx->any_nvdb;
+        key.sc = sc; key.W = Wab; key.vgrid = vgrid; key.sgrid = sgrid; key.sblock = sblock; key.rs_refill = ctx->rs_refill; key.rs_occ = ctx->rs_occ; key.all_gray = ctx->all_gray; key.shadow_persist = ctx->shadow_persist * 100 + ctx->shadow_refill; key.prim_kinds = ctx->prim_kinds; key.sort_mode = ctx->bin_ok ? ctx->sort_mode : 0; key.any_nvdb = ctx->any_nvdb;
         key.nGridWin = nGridWin; if (nGridWin) key.win = gridWin[0].val.accessPolicyWindow;
         if (!ctx->wave_exec || memcmp(&key, ctx->wave_key, sizeof key) != 0) {
             if (ctx->wave_exec) { cudaGraphExecDestroy(ctx->wave_exec); ctx->wave_exec = nullptr; }
