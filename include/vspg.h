@@ -490,6 +490,12 @@ typedef struct vspg_ld_output {
 } vspg_ld_output;
 int vspg_debug_sample_ld(vspg_ctx *ctx, int n, const vspg_ld_input *in, vspg_ld_output *out);
 
+/* The path's transcendental functions as the kernels compute them (include/vspg_libm.h, include/vspg_rsqrtss.h; they stand
+ * in for the host libm calls of the reference: util/math.h, util/sampling.h, shapes.cpp, embree's rsqrt): out[i] = fn(a[i][, b[i]]),
+ * fn = 0 logf, 1 expf, 2 powf(a,b), 3 sinf, 4 cosf, 5 tanf, 6 asinf, 7 acosf, 8 atanf, 9 atan2f(a,b), 10 embree::rsqrt,
+ * 11 (float)log((double)a).  The tests compare with the same header compiled for the host (oracle/libportm.so): bit-equal. */
+int vspg_debug_libm(vspg_ctx *ctx, int fn, int n, const float *a, const float *b, float *out);
+
 #ifdef __cplusplus
 }
 #endif

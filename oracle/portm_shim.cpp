@@ -5,6 +5,7 @@
 // libm selects for this CPU.  tests/golden/make_golden_pbrt.py produces the golden vectors under this shim.
 // Built by oracle/Makefile with -fno-builtin -ffp-contract=off.
 #include "../include/vspg_libm.h"
+#include "../include/vspg_rsqrtss.h"
 
 extern "C" {
 float logf(float x) { return vspg_logf(x); }
@@ -24,4 +25,5 @@ float coshf(float x) { return vspg_coshf(x); }
 float sinhf(float x) { return vspg_sinhf(x); }
 float tanhf(float x) { return vspg_tanhf(x); }
 int vspg_portm_loaded(void) { return 1; }
+float vspg_portm_embree_rsqrt(float x) { return vspg_embree_rsqrt(x); }   // (host value of include/vspg_rsqrtss.h, for tests/test_libm_device.py)
 }

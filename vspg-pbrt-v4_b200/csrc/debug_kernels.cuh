@@ -296,4 +296,27 @@ __global__ void __launch_bounds__(kBlock) k_debug_sample_ld(const DScene sc, int
     }
 }
 
+// The path's libm on the device (include/vspg_libm.h, include/vspg_rsqrtss.h): out[i] = fn(a[i] [, b[i]]).
+// fn: 0 logf, 1 expf, 2 powf(a, b), 3 sinf, 4 cosf, 5 tanf, 6 asinf, 7 acosf, 8 atanf, 9 atan2f(a, b), 10 embree rsqrt, 11 log (double, a widened)
+__global__ void k_debug_libm(int fn, int n, const float *a, const float *b, float *out) {
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+        float x = a[i], y = b ? b[i] : 0.f, r = 0.f;
+        switch (fn) {
+            case 0: r = vspg_logf(x); break;
+            case 1: r = vspg_expf(x); break;
+            case 2: r = vspg_powf(x, y); break;
+            case 3: r = vspg_sinf(x); break;
+            case 4: r = vspg_cosf(x); break;
+            case 5: r = vspg_tanf(x); break;
+            case 6: r = vspg_asinf(x); break;
+            case 7: r = vspg_acosf(x); break;
+            case 8: r = vspg_atanf(x); break;
+            case 9: r = vspg_atan2f(x, y); break;
+            case 10: r = vspg_embree_rsqrt(x); break;
+            default: r = (float)vspg_log((double)x); break;
+        }
+        out[i] = r;
+    }
+}
+
 }  // namespace vspg

@@ -192,4 +192,19 @@ int vspg_debug_sample_ld(vspg_ctx *ctx, int n, const vspg_ld_input *in, vspg_ld_
     return VSPG_OK;
 }
 
+int vspg_debug_libm(vspg_ctx *ctx, int fn, int n, const float *a, const float *b, float *out) {
+    if (!ctx || n < 0 || !a || !out || fn < 0 || fn > 11) return VSPG_ERR_INVALID;
+    if (n == 0) return VSPG_OK;
+    CK(cudaSetDevice(ctx->device));
+    DevBuf da, db, dout;
+    CK(da.alloc((size_t)n * sizeof(float))); CK(dout.alloc((size_t)n * sizeof(float)));
+    CK(cudaMemcpy(da.p, a, (size_t)n * sizeof(float), cudaMemcpyHostToDevice));
+    if (b) { CK(db.alloc((size_t)n * sizeof(float))); CK(cudaMemcpy(db.p, b, (size_t)n * sizeof(float), cudaMemcpyHostToDevice)); }
+    k_debug_libm<<<ctx->sm_count * 8, 256>>>(fn, n, da.as<float>(), b ? db.as<float>() : nullptr, dout.as<float>());
+    ctx->launches++;
+    CK(cudaGetLastError());
+    CK(cudaMemcpy(out, dout.p, (size_t)n * sizeof(float), cudaMemcpyDeviceToHost));
+    return VSPG_OK;
+}
+
 }  // extern "C"

@@ -214,6 +214,7 @@ SYMBOLS = {
     "vspg_debug_light_sample": (i32, [P, i32, PF, PF, PF, C.POINTER(i32), C.POINTER(i32), PF, PF]),
     "vspg_debug_guided_sample": (i32, [P, i32, i32, C.POINTER(GsInput), C.POINTER(GsOutput)]),
     "vspg_debug_sample_ld": (i32, [P, i32, C.POINTER(LdInput), C.POINTER(LdOutput)]),
+    "vspg_debug_libm": (i32, [P, i32, i32, PF, PF, PF]),
 }
 
 

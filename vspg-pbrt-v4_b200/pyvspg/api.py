@@ -251,6 +251,14 @@ class Context:
         return (np.array([o.status for o in out], dtype=np.int32),
                 np.array([[o.Ld[0], o.Ld[1], o.Ld[2]] for o in out], dtype=np.float32).reshape(n, 3))
 
+    def debug_libm(self, fn, a, b=None):
+        """vspg_debug_libm: the device's value of libm function `fn` at a (and b)."""
+        a = np.ascontiguousarray(a, dtype=np.float32)
+        out = np.zeros_like(a)
+        bb = None if b is None else np.ascontiguousarray(b, dtype=np.float32)
+        self._ck(lib().vspg_debug_libm(self._h, int(fn), a.size, _fp(a), None if bb is None else _fp(bb), _fp(out)))
+        return out
+
     def debug_guided_sample(self, is_surface, inputs):
         n = len(inputs)
         out = (A.GsOutput * n)()
