@@ -220,8 +220,16 @@ template <int G> struct GroupIter {
 #ifndef VSPG_SCATTER_SYNC
 #define VSPG_SCATTER_SYNC 1
 #endif
-template <int G> VD void scatter_phase_sync() {
-    if (G > 0) { if (VSPG_SCATTER_SYNC) __syncthreads(); else __syncwarp(); }
+// bit i = phase boundary i keeps its CTA barrier.  Measured (profiles/r02_summary.md): the volume kernel is best with the loop-top
+// barrier only (C2 volscatter 29.1 -> 28.0 ms), the surface kernel with all four
+#ifndef VSPG_VOL_SYNC_SITES
+#define VSPG_VOL_SYNC_SITES 1
+#endif
+#ifndef VSPG_SHADE_SYNC_SITES
+#define VSPG_SHADE_SYNC_SITES 15
+#endif
+template <int G, int SITE = 0, int SITES = 15> VD void scatter_phase_sync() {
+    if (G > 0) { if (VSPG_SCATTER_SYNC && ((SITES >> SITE) & 1)) __syncthreads(); else __syncwarp(); }
 }
 
 // ------------------------------------------------------------------ Field::getRegion for a whole stage queue
@@ -317,7 +325,7 @@ __global__ void __launch_bounds__(G > 0 ? 256 : kBlock, G > 0 ? VSPG_VOL_MINB : 
         const int i0 = base + gi.warpOff;
         const bool live = i0 + gi.sub < n;
         if (G == 0 && !live) continue;             // one thread per vertex: no group shuffles, no barriers
-        scatter_phase_sync<G>();
+        scatter_phase_sync<G, 0, VSPG_VOL_SYNC_SITES>();
         const int slot = in.items[live ? i0 + gi.sub : base];
         V3 p, rd; float g_; int flw;
         {
@@ -330,7 +338,7 @@ __global__ void __launch_bounds__(G > 0 ? 256 : kBlock, G > 0 ? VSPG_VOL_MINB : 
         gphase.enableGuiding = ip.volume_guiding; gphase.enableScatterGuiding = ip.vsp_secondary_guiding; gphase.ris = ip.volume_guiding_ris;
         if (G > 0) gphase.init_region(sc, g_, p, rd, W.P.lk[slot]);   // `v` was drawn by k_lookup
         else { float v = rng.uniform(); gphase.init(sc, g_, p, rd, v, lookups); }
-        scatter_phase_sync<G>();
+        scatter_phase_sync<G, 1, VSPG_VOL_SYNC_SITES>();
         float survivalProb = 1.0f;
         if (depth > ip.min_rr_depth) {
             float4 c = W.P.beta_ru[slot], d = W.P.ru_rl[slot];
@@ -359,7 +367,7 @@ __global__ void __launch_bounds__(G > 0 ? 256 : kBlock, G > 0 ? VSPG_VOL_MINB : 
                 emitShadow = nee_ph != 0;
             }
         }
-        scatter_phase_sync<G>();
+        scatter_phase_sync<G, 2, VSPG_VOL_SYNC_SITES>();
         bool alive = true, rr = false;
         if (survivalProb < 1 && depth > ip.min_rr_depth) {
             float q = fmaxf(0.f, 1 - survivalProb);
@@ -376,7 +384,7 @@ __global__ void __launch_bounds__(G > 0 ? 256 : kBlock, G > 0 ? VSPG_VOL_MINB : 
                 vspNext = gphase.vsp(s.wi);
             }
         }
-        scatter_phase_sync<G>();
+        scatter_phase_sync<G, 3, VSPG_VOL_SYNC_SITES>();
         const bool w = leader && live;
         if (w && (emitShadow || alive)) {
             float4 c = W.P.beta_ru[slot], d = W.P.ru_rl[slot];

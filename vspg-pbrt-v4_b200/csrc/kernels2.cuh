@@ -102,7 +102,7 @@ __global__ void __launch_bounds__(G > 0 ? 256 : kBlock, G > 0 ? VSPG_SHADE_MINB 
         const int i0 = base + gi.warpOff;
         const bool live = i0 + gi.sub < n;
         if (G == 0 && !live) continue;             // one thread per vertex: no group shuffles, no barriers
-        scatter_phase_sync<G>();                   // also: the previous trip's epilogue is done with K
+        if (G > 0) __syncthreads();                // phase boundary 0; also: the previous trip's epilogue is done with K (always a CTA barrier)
         const int slot = in.items[live ? i0 + gi.sub : base];
         Rng rng; { ulonglong2 q = W.P.rng[slot]; rng.state = q.x; rng.inc = q.y; }
         GuidedBSDF<G> gbsdf;
@@ -126,7 +126,7 @@ __global__ void __launch_bounds__(G > 0 ? 256 : kBlock, G > 0 ? VSPG_SHADE_MINB 
             if (G > 0) gbsdf.init_region(sc, ro + h.t * rd, rd, isect.ns, W.P.lk[slot]);   // `v` was drawn by k_lookup
             else { float v = rng.uniform(); gbsdf.init(sc, ro + h.t * rd, rd, isect.ns, v, lookups); }
         }
-        scatter_phase_sync<G>();
+        scatter_phase_sync<G, 1, VSPG_SHADE_SYNC_SITES>();
         bool emitShadow = false;
         V3 nee_f; float nee_pdf = 0;
         if (ip.use_nee && gbsdf.non_specular()) {
@@ -148,7 +148,7 @@ __global__ void __launch_bounds__(G > 0 ? 256 : kBlock, G > 0 ? VSPG_SHADE_MINB 
                 emitShadow = nonzero(nee_f);
             }
         }
-        scatter_phase_sync<G>();
+        scatter_phase_sync<G, 2, VSPG_SHADE_SYNC_SITES>();
         float vspNext = 0;
         ScatterSample bs;
         {
@@ -157,7 +157,7 @@ __global__ void __launch_bounds__(G > 0 ? 256 : kBlock, G > 0 ? VSPG_SHADE_MINB 
             bs = gbsdf.sample_f(-rd, u, u0, u1, rng);
             if (bs.valid) vspNext = gbsdf.vsp(bs.wi);
         }
-        scatter_phase_sync<G>();
+        scatter_phase_sync<G, 3, VSPG_SHADE_SYNC_SITES>();
         const bool w = leader && live;
         bool alive = false;
         if (w) {
