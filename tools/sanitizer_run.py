@@ -1,4 +1,5 @@
-"""Small renders of every kernel family for compute-sanitizer (memcheck): guided grid (C2), NDS+ (C3), rgbgrid with all
+"""Small renders of every kernel family (written for compute-sanitizer memcheck, which is closed on this pool; kept as a quick
+all-kernels smoke run): guided grid (C2), NDS+ (C3), rgbgrid with all
 light types (C5), homogeneous (C1), NanoVDB, triangles / spheres; capacity below the sample count so that regeneration
 and band-major ordering run; the queue coherence pass on; the allocation-free hook."""
 import os, sys
