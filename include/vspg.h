@@ -125,7 +125,8 @@ enum {
     VSPG_LIGHT_DIFFUSE_AREA = 0, /* lights.h:458 */
     VSPG_LIGHT_POINT = 1,
     VSPG_LIGHT_DISTANT = 2,
-    VSPG_LIGHT_UNIFORM_INFINITE = 3
+    VSPG_LIGHT_UNIFORM_INFINITE = 3,
+    VSPG_LIGHT_SPOT = 4          /* lights.h:825-880, lights.cpp:1425-1555 */
 };
 typedef struct vspg_light {
     int type;
@@ -137,7 +138,13 @@ typedef struct vspg_light {
     int shape_kind;    /* area: 0 quad, 1 triangle, 2 sphere                             */
     int shape_index;   /* area: index into that shape array                              */
     int two_sided;     /* area                                                           */
-    int medium;        /* point: medium the light sits in; -1 vacuum                     */
+    int medium;        /* point / spot: medium the light sits in; -1 vacuum              */
+    /* spot (all zero otherwise): the light's frame and cone as SpotLight keeps them */
+    float light_from_render[9]; /* rows of the upper 3x3 of renderFromLight's inverse: SampleLi takes the direction
+                                   to the shading point into the light's frame with it (lights.h:857)           */
+    float axis[3];              /* Normalize(renderFromLight(0,0,1)): the cone axis of Bounds() (lights.cpp:1459) */
+    float cos_falloff_start;    /* cos(Radians(coneangle - conedeltaangle)) (lights.cpp:1439)                   */
+    float cos_falloff_end;      /* cos(Radians(coneangle)) (lights.cpp:1438)                                    */
 } vspg_light;
 
 enum { VSPG_LIGHTSAMPLER_UNIFORM = 0, VSPG_LIGHTSAMPLER_POWER = 1, VSPG_LIGHTSAMPLER_BVH = 2 };

@@ -338,6 +338,7 @@ struct Scene {
         switch (l.type) {
         case VSPG_LIGHT_DIFFUSE_AREA: return Pi * (l.two_sided ? 2 : 1) * ShapeArea(l) * (L * l.scale);
         case VSPG_LIGHT_POINT: return 4 * Pi * l.scale * L;
+        case VSPG_LIGHT_SPOT: return l.scale * L * 2 * Pi * ((1 - l.cos_falloff_start) + (l.cos_falloff_start - l.cos_falloff_end) / 2);   // lights.cpp:1452-1455
         case VSPG_LIGHT_DISTANT: return l.scale * L * Pi * Sqr(sceneRadius);
         default: return 4 * Pi * Pi * Sqr(sceneRadius) * l.scale * L;
         }
@@ -859,6 +860,24 @@ struct Integrator {
             ls.wi = Normalize(p - ctx.p);
             ls.L = Scene::LightL(l) / DistanceSquared(p, ctx.p);
             ls.pdf = 1; ls.pLight = p; ls.delta = true; ls.valid = true;
+            return ls;
+        }
+        if (l.type == VSPG_LIGHT_SPOT) {  // lights.h:852-866; I(): lights.cpp:1448-1451; SmoothStep: util/math.h:268-274
+            V3 p(l.pos);
+            V3 wi = Normalize(p - ctx.p);
+            V3 v = -wi;
+            const float *m = l.light_from_render;   // Transform::ApplyInverse(Vector3f), util/transform.h:401-406
+            V3 wLight = Normalize(V3(m[0] * v.x + m[1] * v.y + m[2] * v.z, m[3] * v.x + m[4] * v.y + m[5] * v.z, m[6] * v.x + m[7] * v.y + m[8] * v.z));
+            float a = l.cos_falloff_end, b = l.cos_falloff_start, x = wLight.z, ss;
+            if (a == b) ss = x < a ? 0.f : 1.f;
+            else {
+                float t = (x - a) / (b - a);
+                t = t < 0 ? 0.f : t > 1 ? 1.f : t;
+                ss = t * t * (3 - 2 * t);
+            }
+            S3 Li = ss * l.scale * S3(l.L) / DistanceSquared(p, ctx.p);
+            if (!Li) return ls;
+            ls.wi = wi; ls.L = Li; ls.pdf = 1; ls.pLight = p; ls.delta = true; ls.valid = true;
             return ls;
         }
         if (l.type == VSPG_LIGHT_DISTANT) {  // lights.h:316-323

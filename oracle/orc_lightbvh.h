@@ -207,6 +207,12 @@ struct BVHLightSampler {
             if (l.type == VSPG_LIGHT_POINT) {   // lights.cpp:200-205
                 lb.bounds.pMin = lb.bounds.pMax = V3(l.pos);
                 lb.w = V3(0, 0, 1); lb.phi = 4 * Pi * l.scale * maxL; lb.cosTheta_o = vspg_cosf(Pi); lb.cosTheta_e = vspg_cosf(Pi / 2); lb.twoSided = false;
+            } else if (l.type == VSPG_LIGHT_SPOT) {   // lights.cpp:1457-1468 SpotLight::Bounds
+                lb.bounds.pMin = lb.bounds.pMax = V3(l.pos);
+                lb.w = V3(l.axis); lb.phi = l.scale * maxL * 4 * Pi; lb.cosTheta_o = l.cos_falloff_start;
+                lb.cosTheta_e = vspg_cosf(vspg_acosf(l.cos_falloff_end) - vspg_acosf(l.cos_falloff_start));
+                if (lb.cosTheta_e == 1 && l.cos_falloff_end != l.cos_falloff_start) lb.cosTheta_e = 0.999f;
+                lb.twoSided = false;
             } else if (l.type == VSPG_LIGHT_DIFFUSE_AREA && l.shape_kind == 1) {   // Triangle::Bounds / NormalBounds
                 const vspg_triangle &q = tris[l.shape_index];
                 V3 p0(q.p0), p1(q.p1), p2(q.p2);

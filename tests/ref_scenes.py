@@ -10,7 +10,7 @@ from pyvspg import _abi as A
 from pyvspg import api, configs, pbrt_writer
 from pyvspg.scenes import Scene, perspective_camera
 
-SCENES = ["c1", "c1t", "c1e", "c1s", "c2", "c2u", "c3", "c3nds", "c3contrib", "c4", "c4r", "c5", "c5u", "ch", "cg", "cn", "cnu", "cp"]
+SCENES = ["c1", "c1t", "c1e", "c1s", "c2", "c2u", "c3", "c3nds", "c3contrib", "c4", "c4r", "c5", "c5u", "ch", "cg", "cn", "cnu", "cp", "cs", "csp"]
 
 
 def write_inputs(golden_dir):
@@ -47,6 +47,9 @@ def _guided(name, kind="grid", filt=None, lights="pa", **ipkw):
         sc.add_point_light([0.2, 1.8, -0.4], [9.0, 8.0, 7.0])
     if "a" in lights:
         sc.add_quad([1.4, 1.5, 0.2], [0.4, 0, 0], [0, 0, 0.4], material=white, emission=[40.0, 36.0, 30.0])
+    if "s" in lights:   # LightSource "spot": one with the default smooth-step falloff, one with conedeltaangle 0 (hard edge)
+        sc.add_spot_light([0.3, 1.9, -0.5], [0.5, 0.4, 0.5], [30.0, 26.0, 22.0], coneangle=25.0, conedeltaangle=8.0)
+        sc.add_spot_light([1.6, 1.2, 0.3], [0.6, 0.2, 0.6], [20.0, 25.0, 30.0], coneangle=18.0, conedeltaangle=0.0)
     if "d" in lights:
         sc.add_distant_light([0.4, 1.0, -0.3], [3.0, 2.5, 2.0])
     if "i" in lights:
@@ -105,6 +108,10 @@ def _config(name):
         return _guided(name, kind="nvdb", light_sampler=P, surface_guiding=0, volume_guiding=0, vsp_guiding=0)
     if name == "cp":     # PLY meshes (triangles + bilinear patches from one file), emissive and diffuse
         return _guided(name, lights="pm", light_sampler=B)
+    if name == "cs":     # spot lights, light BVH
+        return _guided(name, lights="sa", light_sampler=B)
+    if name == "csp":    # spot lights, power light sampler, guiding off
+        return _guided(name, lights="sat", light_sampler=P, surface_guiding=0, volume_guiding=0, vsp_guiding=0)
     if name == "ch":
         return _guided(name, kind="hom", light_sampler=B, vsp_mis_ratio=0.3)
     if name == "cg":

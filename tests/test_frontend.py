@@ -219,7 +219,41 @@ LightSource "infinite"
     hs.close()
 
 
+def test_spot_light_frame_cone_and_power():
+    """LightSource "spot" (lights.cpp:1505-1545): position and axis through the CTM, the render -> light rotation the inverse of the
+    light -> render one, cosines of coneangle / coneangle - conedeltaangle, and "power" turned into a scale by
+    2 Pi ((1 - cosStart) + (cosStart - cosEnd) / 2).  (Bit-level agreement with the reference: golden scenes cs / csp.)"""
+    text = HEAD + """WorldBegin
+AttributeBegin
+  Translate 1 0 0
+  Rotate 90 0 1 0
+  LightSource "spot" "point3 from" [0 2 0] "point3 to" [0 1 1] "rgb I" [1 2 3] "float coneangle" 40 "float conedeltaangle" 10 "float power" 50 "float scale" 2
+AttributeEnd
+LightSource "spot"
+"""
+    hs = api.HostScene(text=text)
+    d = hs.desc
+    eye = np.array([0, 0, -3.0])
+    l = d.lights[0]
+    assert l.type == A.LIGHT_SPOT and list(l.L) == [1, 2, 3] and l.medium == -1
+    assert np.allclose(l.pos, np.array([1, 2, 0]) - eye, atol=1e-6)            # Rotate 90 about y leaves (0, 2, 0) in place; then the translation
+    ax = np.array([0, -1, 1]) / np.sqrt(2)
+    assert np.allclose(l.axis, [ax[2], ax[1], -ax[0]], atol=1e-6)              # the rotation takes +z to +x
+    R = np.array(l.light_from_render, np.float64).reshape(3, 3)
+    assert np.allclose(R @ R.T, np.eye(3), atol=1e-6) and np.allclose(R @ np.array(l.axis), [0, 0, 1], atol=1e-6)
+    cs, ce = np.cos(np.radians(30.0)), np.cos(np.radians(40.0))
+    assert np.isclose(l.cos_falloff_start, cs, rtol=1e-6) and np.isclose(l.cos_falloff_end, ce, rtol=1e-6)
+    assert np.isclose(l.scale, 2 * 50 / (2 * np.pi * ((1 - cs) + (cs - ce) / 2)), rtol=1e-5)
+    m = d.lights[1]                                                             # defaults: at the origin, along +z, 30 / 5 degrees
+    assert np.allclose(m.pos, -eye) and np.allclose(m.axis, [0, 0, 1]) and m.scale == 1 and list(m.L) == [1, 1, 1]
+    assert np.isclose(m.cos_falloff_end, np.cos(np.radians(30.0)), rtol=1e-6) and np.isclose(m.cos_falloff_start, np.cos(np.radians(25.0)), rtol=1e-6)
+    hs.close()
+
+
 @pytest.mark.parametrize("body,code,needle", [
+    ("WorldBegin\nLightSource \"spot\" \"point3 from\" [1 1 1] \"point3 to\" [1 1 1]\n", A.ERR_INVALID, "from == to"),
+    ("WorldBegin\nLightSource \"spot\" \"float conedeltaangle\" -1\n", A.ERR_INVALID, "conedeltaangle"),
+    ("WorldBegin\nLightSource \"goniometric\"\n", A.ERR_UNSUPPORTED, "goniometric"),
     ("WorldBegin\nShape \"sphere\" \"float radious\" 1\n", A.ERR_INVALID, "unused"),                       # paramdict.cpp:642-664
     ("WorldBegin\nShape \"cylinder\"\n", A.ERR_UNSUPPORTED, "cylinder"),
     ("WorldBegin\nMaterial \"dielectric\"\n", A.ERR_UNSUPPORTED, "dielectric"),

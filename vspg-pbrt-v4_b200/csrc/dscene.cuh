@@ -64,6 +64,9 @@ struct DLight {
     int shape_index, two_sided, medium;
     float pmf;            // PowerLightSampler: AliasTable bins[i].p
     float q; int alias;   //                    bins[i].q, bins[i].alias (util/sampling.cpp:563-618)
+    // spot lights (lights.h:852-866): unscaled intensity and scale apart (I() multiplies SmoothStep * scale first), the
+    // rows of the render -> light rotation, the cone
+    float I[3], scale, toLight[9], cosStart, cosEnd;
 };
 
 // Light-BVH node (lightsamplers.h LightBVHNode), stored decoded -- see host_lightbvh.h.

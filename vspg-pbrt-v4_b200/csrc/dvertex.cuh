@@ -241,7 +241,7 @@ VD float sphere_light_pdf(const DQuad &q, V3 ctxP, V3 wi, V3 hitP, V3 hitN) {
 }
 
 // lights.cpp:796-818 DiffuseAreaLight::SampleLi -> shapes.cpp:1155-1214, 1254-1280 (area-sampling branch);
-// lights.h:243-250 (point), 316-323 (distant); uniform infinite: allowIncompletePDF (lights.cpp:1022-1023)
+// lights.h:243-250 (point), 852-866 (spot), 316-323 (distant); uniform infinite: allowIncompletePDF (lights.cpp:1022-1023)
 template <int KINDS = kKindsAll>
 VD LiSample sample_li(const DScene &sc, int light, V3 ctxP, V3 ctxNs, float u0, float u1) {
     LiSample ls; ls.valid = false; ls.delta = false; ls.pdf = 0;
@@ -251,6 +251,24 @@ VD LiSample sample_li(const DScene &sc, int light, V3 ctxP, V3 ctxNs, float u0, 
         ls.wi = normalize(p - ctxP);
         ls.L = ld3(l.L) / dist_sq(p, ctxP);
         ls.pdf = 1; ls.pLight = p; ls.delta = true; ls.valid = true;
+        return ls;
+    }
+    if (l.type == VSPG_LIGHT_SPOT) {   // lights.h:852-866, lights.cpp:1448-1451 (I), util/math.h:268-274 (SmoothStep)
+        V3 p = ld3(l.pos);
+        V3 wi = normalize(p - ctxP);
+        V3 v = -wi;
+        const float *m = l.toLight;
+        V3 wl = normalize(V3(m[0] * v.x + m[1] * v.y + m[2] * v.z, m[3] * v.x + m[4] * v.y + m[5] * v.z, m[6] * v.x + m[7] * v.y + m[8] * v.z));
+        float ss;
+        if (l.cosEnd == l.cosStart) ss = wl.z < l.cosEnd ? 0.f : 1.f;
+        else {
+            float t = fminf(fmaxf((wl.z - l.cosEnd) / (l.cosStart - l.cosEnd), 0.f), 1.f);
+            ss = t * t * (3 - 2 * t);
+        }
+        float k = ss * l.scale;
+        V3 Li = V3(k * l.I[0], k * l.I[1], k * l.I[2]) / dist_sq(p, ctxP);
+        if (!nonzero(Li)) return ls;
+        ls.wi = wi; ls.L = Li; ls.pdf = 1; ls.pLight = p; ls.delta = true; ls.valid = true;
         return ls;
     }
     if (l.type == VSPG_LIGHT_DISTANT) {

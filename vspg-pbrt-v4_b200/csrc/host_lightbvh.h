@@ -225,6 +225,12 @@ inline HostLightBvh build_light_bvh(const vspg_scene_desc *scene, const float *p
         if (l.type == VSPG_LIGHT_POINT) {   // lights.cpp:200-205
             for (int k = 0; k < 3; k++) lb.bmin[k] = lb.bmax[k] = l.pos[k];
             lb.w = H3(0, 0, 1); lb.phi = 4 * kPi * l.scale * maxL; lb.cosTheta_o = vspg_cosf(kPi); lb.cosTheta_e = cosHalfPi; lb.twoSided = false;
+        } else if (l.type == VSPG_LIGHT_SPOT) {   // lights.cpp:1457-1468
+            for (int k = 0; k < 3; k++) lb.bmin[k] = lb.bmax[k] = l.pos[k];
+            lb.w = H3(l.axis); lb.phi = l.scale * maxL * 4 * kPi; lb.cosTheta_o = l.cos_falloff_start;
+            lb.cosTheta_e = vspg_cosf(vspg_acosf(l.cos_falloff_end) - vspg_acosf(l.cos_falloff_start));
+            if (lb.cosTheta_e == 1 && l.cos_falloff_end != l.cos_falloff_start) lb.cosTheta_e = 0.999f;
+            lb.twoSided = false;
         } else if (l.type == VSPG_LIGHT_DIFFUSE_AREA && l.shape_kind == 1) {   // shapes.cpp:290-314 Triangle::Bounds / NormalBounds
             const vspg_triangle &q = scene->triangles[l.shape_index];
             H3 p0(q.p0), p1(q.p1), p2(q.p2);

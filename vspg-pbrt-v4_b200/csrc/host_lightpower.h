@@ -32,6 +32,8 @@ inline HostPowerSampler build_power_sampler(const vspg_light *lights, int n, con
             switch (l.type) {   // lights.cpp:196-198, 251-253, 826-842, 1038-1040 with the products in the reference's order
             case VSPG_LIGHT_DIFFUSE_AREA: phi[c] = Pi * (l.two_sided ? 2 : 1) * area[i] * (l.L[c] * l.scale); break;
             case VSPG_LIGHT_POINT: phi[c] = 4 * Pi * l.scale * l.L[c]; break;
+            case VSPG_LIGHT_SPOT:    // lights.cpp:1452-1455
+                phi[c] = l.scale * l.L[c] * 2 * Pi * ((1 - l.cos_falloff_start) + (l.cos_falloff_start - l.cos_falloff_end) / 2); break;
             case VSPG_LIGHT_DISTANT: phi[c] = l.scale * l.L[c] * Pi * (sceneRadius * sceneRadius); break;
             default: phi[c] = 4 * Pi * Pi * (sceneRadius * sceneRadius) * l.scale * l.L[c]; break;
             }

@@ -575,6 +575,39 @@ struct Builder {
             const double origin[3] = {0, 0, 0};
             to_render(rfl * xf::translate((float)from[0], (float)from[1], (float)from[2]), origin, l.pos);
             l.medium = medium_id(S.gs.outside, lx);
+        } else if (type == "spot") {
+            l.type = VSPG_LIGHT_SPOT;
+            ps.rgb("I", L);
+            float coneangle = (float)ps.one_float("coneangle", 30), conedelta = (float)ps.one_float("conedeltaangle", 5);
+            double from[3] = {0, 0, 0}, to[3] = {0, 0, 1};
+            ps.point3("from", from); ps.point3("to", to);
+            if (conedelta < 0) lx.fail("spot light: conedeltaangle must not be negative");   // CHECK_LE(falloffStart, totalWidth), lights.cpp:1440
+            // lights.cpp:1518-1520: dirToZ = Transform(Frame::FromZ(Normalize(to - from))), whose inverse comes from the
+            // numeric matrix inversion of Transform(SquareMatrix); t = Translate(from) * Inverse(dirToZ)
+            float w[3] = {(float)to[0] - (float)from[0], (float)to[1] - (float)from[1], (float)to[2] - (float)from[2]};
+            if (xf::length3(w[0], w[1], w[2]) == 0) lx.fail("spot light: from == to");
+            xf::normalize3(w);
+            float sign = std::copysign(1.f, w[2]), ca = -1 / (sign + w[2]), cb = w[0] * w[1] * ca;   // CoordinateSystem (util/vecmath.h:1007-1013)
+            float v1[3] = {1 + sign * (w[0] * w[0]) * ca, sign * cb, -sign * w[0]}, v2[3] = {cb, sign + (w[1] * w[1]) * ca, -w[1]};
+            M4f fm = M4f::identity();
+            for (int i = 0; i < 3; i++) { fm.m[0][i] = v1[i]; fm.m[1][i] = v2[i]; fm.m[2][i] = w[i]; }
+            XF fin = rfl * (xf::translate((float)from[0], (float)from[1], (float)from[2]) * xf::inverse(XF(fm)));
+            l.cos_falloff_end = vspg_cosf(xf::radians(coneangle));
+            l.cos_falloff_start = vspg_cosf(xf::radians(coneangle - conedelta));
+            float pw = (float)ps.one_float("power", -1);
+            if (pw > 0) {   // lights.cpp:1524-1531 (photometric == 1)
+                float k_e = 2 * 3.14159265358979323846f * ((1 - l.cos_falloff_start) + (l.cos_falloff_start - l.cos_falloff_end) / 2);
+                sc *= pw / k_e;
+            }
+            const double origin[3] = {0, 0, 0};
+            to_render(fin, origin, l.pos);
+            for (int i = 0; i < 3; i++) for (int j = 0; j < 3; j++) l.light_from_render[3 * i + j] = fin.inv.m[i][j];
+            const float z[3] = {0, 0, 1};
+            float ax[3];
+            xf::apply_vector(fin.m, z, ax);
+            xf::normalize3(ax);
+            for (int i = 0; i < 3; i++) l.axis[i] = ax[i];
+            l.medium = medium_id(S.gs.outside, lx);
         } else if (type == "distant") {
             l.type = VSPG_LIGHT_DISTANT;
             ps.rgb("L", L);
@@ -604,7 +637,7 @@ struct Builder {
                 lx.fail("image / portal infinite lights are outside the hot-path scope (SURVEY 8f3)", VSPG_ERR_UNSUPPORTED);
             float ev = (float)ps.one_float("illuminance", -1);
             if (ev > 0) sc *= ev / 3.14159265358979323846f;
-        } else lx.fail("LightSource \"" + type + "\": supported types are point, distant, infinite (uniform)", VSPG_ERR_UNSUPPORTED);
+        } else lx.fail("LightSource \"" + type + "\": supported types are point, spot, distant, infinite (uniform)", VSPG_ERR_UNSUPPORTED);
         ps.report_unused();
         for (int i = 0; i < 3; i++) l.L[i] = L[i];
         l.scale = sc;

@@ -424,6 +424,10 @@ int vspg_set_scene(vspg_ctx *ctx, const vspg_scene_desc *s) {
             break;
         }
         case VSPG_LIGHT_POINT: break;
+        case VSPG_LIGHT_SPOT:
+            if (!(l.cos_falloff_end <= l.cos_falloff_start)) return fail(ctx, VSPG_ERR_INVALID, "set_scene: light %d: spot light with cos_falloff_end %g > cos_falloff_start %g", i, l.cos_falloff_end, l.cos_falloff_start);
+            memcpy(d.I, l.L, 12); d.scale = l.scale; memcpy(d.toLight, l.light_from_render, 36); d.cosStart = l.cos_falloff_start; d.cosEnd = l.cos_falloff_end;
+            break;
         case VSPG_LIGHT_DISTANT: case VSPG_LIGHT_UNIFORM_INFINITE: inf.push_back(i); break;   // Integrator::infiniteLights (cpu/integrators.h:77-81)
         default: return fail(ctx, VSPG_ERR_UNSUPPORTED, "set_scene: light %d has unsupported type %d", i, l.type);
         }

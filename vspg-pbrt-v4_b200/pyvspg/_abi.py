@@ -15,7 +15,7 @@ ERR_NAMES = {0: "OK", -1: "INVALID", -2: "CUDA", -3: "IO", -4: "UNSUPPORTED", -5
 
 NOALLOC_MAX_RAYS, NOALLOC_MAX_SEGMENTS = 16384, 262144
 MEDIUM_HOMOGENEOUS, MEDIUM_GRID, MEDIUM_RGBGRID, MEDIUM_NANOVDB = 0, 1, 2, 3
-LIGHT_DIFFUSE_AREA, LIGHT_POINT, LIGHT_DISTANT, LIGHT_UNIFORM_INFINITE = 0, 1, 2, 3
+LIGHT_DIFFUSE_AREA, LIGHT_POINT, LIGHT_DISTANT, LIGHT_UNIFORM_INFINITE, LIGHT_SPOT = 0, 1, 2, 3, 4
 LIGHTSAMPLER_UNIFORM, LIGHTSAMPLER_POWER, LIGHTSAMPLER_BVH = 0, 1, 2
 MAX_LOBES = 32
 
@@ -63,7 +63,8 @@ class Material(C.Structure):
 
 class Light(C.Structure):
     _fields_ = [("type", i32), ("L", F3), ("scale", C.c_float), ("pos", F3), ("shape_kind", i32), ("shape_index", i32), ("two_sided", i32),
-                ("medium", i32)]
+                ("medium", i32), ("light_from_render", C.c_float * 9), ("axis", F3), ("cos_falloff_start", C.c_float),
+                ("cos_falloff_end", C.c_float)]
 
 
 class SceneDesc(C.Structure):

@@ -144,6 +144,9 @@ def scene_text(cfg, out_dir=None, outfile="out.exr", seed=0, integrator_name="gu
             L.append("AttributeEnd")
         elif kind == "point":
             L.append(f'LightSource "point" "rgb I" [{_v(e["I"])}] "point3 from" [{_v(e["pos"])}]')
+        elif kind == "spot":
+            L.append(f'LightSource "spot" "rgb I" [{_v(e["I"])}] "point3 from" [{_v(e["pos"])}] "point3 to" [{_v(e["to"])}] '
+                     f'"float coneangle" [{_f(e["coneangle"])}] "float conedeltaangle" [{_f(e["conedeltaangle"])}]')
         elif kind == "distant":
             L.append(f'LightSource "distant" "rgb L" [{_v(e["L"])}] "point3 from" [{_v(e["to_light"])}] "point3 to" [0 0 0]')
         elif kind == "infinite":

@@ -124,6 +124,13 @@ class Scene:
         self.log.append(("point", dict(pos=[float(x) for x in pos], I=[float(x) for x in intensity], medium=medium)))
         self.n_lights += 1
 
+    def add_spot_light(self, pos, to, intensity, coneangle=30.0, conedeltaangle=5.0, medium=-1):
+        """LightSource "spot" (lights.cpp:1505-1545): at `pos`, looking at `to`, full intensity inside
+        coneangle - conedeltaangle degrees of the axis and a smooth-step falloff to zero at coneangle."""
+        self.log.append(("spot", dict(pos=[float(x) for x in pos], to=[float(x) for x in to], I=[float(x) for x in intensity],
+                                      coneangle=float(coneangle), conedeltaangle=float(conedeltaangle), medium=medium)))
+        self.n_lights += 1
+
     def add_distant_light(self, to_light, radiance):
         self.log.append(("distant", dict(to_light=[float(x) for x in to_light], L=[float(x) for x in radiance])))
         self.n_lights += 1
