@@ -89,6 +89,15 @@ typedef struct vspg_medium {
     float density_offset;
     float background;
     float majorant_scale;      /* "majorantscale" the given majorant grid was built with (informational) */
+    /* emission, homogeneous and uniformgrid media (media.h:243-260, 329-345; media.cpp:188-194, 304-329).  Le is the "Le"
+     * rgb -- homogeneous: already times "Lescale".  uniformgrid: the emitted radiance at p is s * Le where
+     * s = trilinear lookup of le_scale (le_nx * le_ny * le_nz floats, x fastest, same lookup as the density) is positive;
+     * le_scale NULL with Le != 0 stands for the reference's 1 x 1 x 1 grid holding 1 when no "Lescale" array is given.
+     * The medium is emissive when max(Le) > 0.  Only the delta-tracking branch of SampleDistance adds medium emission
+     * (guidedvolpathvspgintegrator.cpp:895-906); the resampling branch ignores it, as the reference does. */
+    float Le[3];
+    const float *le_scale;
+    int le_nx, le_ny, le_nz;
 } vspg_medium;
 
 /* One bilinear patch (shapes.h:1350) in render space; vertex order p00,p10,p01,p11. */

@@ -1240,6 +1240,12 @@ struct Integrator {
                 med, ps.ray, tMax, sampler.Get1D(), rng, ch, guideScatterDecision, vsp, ip.vsp_mis_ratio, ip.vsp_sampling_nds != 0,
                 beta_factor, r_u_factor, &st, [&](V3 p, const MediumProps &mp, S3 sigma_maj, S3 T_maj, bool activateNDS) {
                     if (!ps.beta) { terminated = true; return false; }
+                    if (ps.depth < ip.max_depth && mp.Le) {   // :895-906 emission from the medium at the tentative collision
+                        float pdf = sigma_maj[ch] * T_maj[ch];
+                        S3 betap = ps.beta * T_maj / pdf;
+                        S3 r_e = ps.r_u * sigma_maj * T_maj / pdf;
+                        if (r_e) ps.L += betap * mp.sigma_a * mp.Le / r_e.Average();
+                    }
                     S3 sigma_t = mp.sigma_s + mp.sigma_a;
                     float pScatter = sigma_t[ch] / sigma_maj[ch];
                     bool NDS_plus = false;

@@ -111,7 +111,7 @@ inline V3 ApplyInversePoint(const vspg_transform &T, V3 p) {  // util/transform.
     return V3(xp, yp, zp) / wp;
 }
 
-struct MediumProps { S3 sigma_a, sigma_s; float g; };
+struct MediumProps { S3 sigma_a, sigma_s; float g; S3 Le = S3(0.f); };
 struct Segment { float tMin, tMax; S3 sigma_maj; };
 
 struct Medium {
@@ -180,10 +180,29 @@ struct Medium {
         vx1 = lerp(vy, vy1, xyz[1]);
         return lerp(vx, vx1, xyz[0]);
     }
-    // media.h:256-261, 316-348, 417-441, 692-705 SamplePoint (emission branches out of scope: configs have none)
+    bool IsEmissive() const { return std::max({m->Le[0], m->Le[1], m->Le[2]}) > 0; }   // media.h:250, media.cpp:261
+    // util/containers.h:804-831 Lookup on the "Lescale" grid (a 1x1x1 grid of 1 when le_scale is NULL, media.cpp:319-320)
+    float leScaleLookup(V3 p) const {
+        static const float one = 1.f;
+        const float *g = m->le_scale ? m->le_scale : &one;
+        const int nx = m->le_scale ? m->le_nx : 1, ny = m->le_scale ? m->le_ny : 1, nz = m->le_scale ? m->le_nz : 1;
+        auto at = [&](int x, int y, int z) {
+            if (x < 0 || y < 0 || z < 0 || x >= nx || y >= ny || z >= nz) return 0.f;
+            return g[(size_t)(z * ny + y) * nx + x];
+        };
+        V3 ps(p.x * nx - .5f, p.y * ny - .5f, p.z * nz - .5f);
+        int ix = (int)std::floor(ps.x), iy = (int)std::floor(ps.y), iz = (int)std::floor(ps.z);
+        V3 d(ps.x - (float)ix, ps.y - (float)iy, ps.z - (float)iz);
+        float d00 = Lerp(d.x, at(ix, iy, iz), at(ix + 1, iy, iz));
+        float d10 = Lerp(d.x, at(ix, iy + 1, iz), at(ix + 1, iy + 1, iz));
+        float d01 = Lerp(d.x, at(ix, iy, iz + 1), at(ix + 1, iy, iz + 1));
+        float d11 = Lerp(d.x, at(ix, iy + 1, iz + 1), at(ix + 1, iy + 1, iz + 1));
+        return Lerp(d.z, Lerp(d.y, d00, d10), Lerp(d.y, d01, d11));
+    }
+    // media.h:256-261, 316-348, 417-441, 692-705 SamplePoint (emission: homogeneous and uniformgrid "Le" / "Lescale")
     MediumProps SamplePoint(V3 p) const {
         MediumProps mp; mp.g = m->g;
-        if (m->type == VSPG_MEDIUM_HOMOGENEOUS) { mp.sigma_a = S3(m->sigma_a); mp.sigma_s = S3(m->sigma_s); return mp; }
+        if (m->type == VSPG_MEDIUM_HOMOGENEOUS) { mp.sigma_a = S3(m->sigma_a); mp.sigma_s = S3(m->sigma_s); mp.Le = S3(m->Le); return mp; }
         p = ApplyInversePoint(m->render_from_medium, p);
         if (m->type == VSPG_MEDIUM_NANOVDB) {
             float d = nvdbLookup(p);
@@ -195,6 +214,10 @@ struct Medium {
         if (m->type == VSPG_MEDIUM_GRID) {
             float d = densityLookup(p);
             mp.sigma_a = S3(m->sigma_a) * d; mp.sigma_s = S3(m->sigma_s) * d;
+            if (IsEmissive()) {   // media.h:329-345
+                float scale = leScaleLookup(p);
+                if (scale > 0) mp.Le = scale * S3(m->Le);
+            }
         } else {
             mp.sigma_a = m->sigma_scale * (m->sigma_a_rgb ? rgbLookup(m->sigma_a_rgb, p) : S3(1.f));
             mp.sigma_s = m->sigma_scale * (m->sigma_s_rgb ? rgbLookup(m->sigma_s_rgb, p) : S3(1.f));

@@ -10,7 +10,7 @@ from pyvspg import _abi as A
 from pyvspg import api, configs, pbrt_writer
 from pyvspg.scenes import Scene, perspective_camera
 
-SCENES = ["c1", "c1t", "c1e", "c1s", "c2", "c2u", "c3", "c3nds", "c3contrib", "c4", "c4r", "c5", "c5u", "ch", "cg", "cn", "cnu", "cp", "cs", "csp"]
+SCENES = ["c1", "c1t", "c1e", "c1s", "c2", "c2u", "c3", "c3nds", "c3contrib", "c4", "c4r", "c5", "c5u", "ch", "cg", "cn", "cnu", "cp", "cs", "csp", "ce", "ceg", "cet"]
 
 
 def write_inputs(golden_dir):
@@ -23,14 +23,21 @@ def write_inputs(golden_dir):
     api.exr_write_channels(os.path.join(golden_dir, "tr_small.exr"), {"Transmittance.R": tr[..., 0], "Transmittance.G": tr[..., 1], "Transmittance.B": tr[..., 2]})
 
 
-def _guided(name, kind="grid", filt=None, lights="pa", **ipkw):
+def _guided(name, kind="grid", filt=None, lights="pa", emit=None, **ipkw):
     cam, eye = perspective_camera([0.5, 0.6, -2.2], [0.5, 0.45, 0.5], [0, 1, 0], 40.0, 40, 24)
     sc = Scene(cam, eye)
     white, red = sc.add_material([.6, .6, .6]), sc.add_material([.7, .2, .1])
     sc.add_quad([-2, -0.05, -2], [5, 0, 0], [0, 0, 5], material=white)
     rng = np.random.default_rng(5)
     if kind == "grid":
-        med = sc.add_grid_medium(rng.random((6, 5, 4), dtype=np.float32), (0, 0, 0), (1, 1, 1), [0.1, 0.1, 0.1], [6.0, 6.0, 6.0], 8.0, 0.6)
+        dens = rng.random((6, 5, 4), dtype=np.float32)
+        ekw = {}
+        if emit == "grid":     # "Le" scaled by a "Lescale" grid with some zero voxels (media.cpp:317-329)
+            les = np.random.default_rng(9).random((6, 5, 4), dtype=np.float32)
+            ekw = dict(Le=[1.5, 0.9, 0.4], Le_scale=np.where(les > 0.3, les * 2, 0).astype(np.float32))
+        elif emit == "tent":   # "Le" alone: the reference's 1x1x1 scale grid
+            ekw = dict(Le=[0.8, 1.1, 1.6])
+        med = sc.add_grid_medium(dens, (0, 0, 0), (1, 1, 1), [0.1, 0.1, 0.1], [6.0, 6.0, 6.0], 8.0, 0.6, **ekw)
     elif kind == "rgb":
         sa = rng.random((6, 5, 4, 3), dtype=np.float32) * np.float32([0.02, 0.05, 0.2])
         ss = rng.random((6, 5, 4, 3), dtype=np.float32) * np.float32([4, 3, 2])
@@ -41,7 +48,7 @@ def _guided(name, kind="grid", filt=None, lights="pa", **ipkw):
         med = sc.add_nanovdb_medium(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "nvdb_small.nvdb"), [0.1, 0.1, 0.1], [3.0, 3.0, 3.0],
                                     4.0, 0.5, density_offset=0.02, majorant_scale=1.25, written_name="../nvdb_small.nvdb")
     else:
-        med = sc.add_homogeneous_medium([0.2, 0.3, 0.5], [3.0, 2.0, 1.5], 1.5, 0.3)
+        med = sc.add_homogeneous_medium([0.2, 0.3, 0.5], [3.0, 2.0, 1.5], 1.5, 0.3, **(dict(Le=[0.6, 0.5, 0.9], Le_scale=1.5) if emit else {}))
     sc.add_box([0, 0, 0], [1, 1, 1], material=-1, medium_inside=med, medium_outside=-1, has_interface=True)
     if "p" in lights:
         sc.add_point_light([0.2, 1.8, -0.4], [9.0, 8.0, 7.0])
@@ -108,6 +115,12 @@ def _config(name):
         return _guided(name, kind="nvdb", light_sampler=P, surface_guiding=0, volume_guiding=0, vsp_guiding=0)
     if name == "cp":     # PLY meshes (triangles + bilinear patches from one file), emissive and diffuse
         return _guided(name, lights="pm", light_sampler=B)
+    if name == "ce":     # emissive homogeneous medium, guided
+        return _guided(name, kind="hom", emit="hom", light_sampler=B)
+    if name == "ceg":    # emissive grid medium with a "Lescale" grid, NDS distance sampling (the delta-tracking branch adds the emission)
+        return _guided(name, emit="grid", light_sampler=P, vsp_sampling_nds=1)
+    if name == "cet":    # emissive grid medium without "Lescale", unguided NDS
+        return _guided(name, emit="tent", light_sampler=U, vsp_sampling_nds=1, surface_guiding=0, volume_guiding=0, vsp_guiding=0)
     if name == "cs":     # spot lights, light BVH
         return _guided(name, lights="sa", light_sampler=B)
     if name == "csp":    # spot lights, power light sampler, guiding off

@@ -250,7 +250,27 @@ LightSource "spot"
     hs.close()
 
 
+def test_medium_emission_parameters():
+    """"Le" / "Lescale" (media.cpp:188-194, 304-329): homogeneous media fold the float "Lescale" into Le; uniformgrid media keep Le
+    and take "Lescale" as a grid (without one: the reference's 1x1x1 grid of 1); an all-zero Le is no emission."""
+    text = HEAD + """WorldBegin
+MakeNamedMedium "a" "string type" "homogeneous" "rgb Le" [1 2 3] "float Lescale" 0.5
+MakeNamedMedium "b" "string type" "uniformgrid" "float density" [1 2 3 4] "integer nx" 2 "integer ny" 2 "rgb Le" [4 5 6] "float Lescale" [0 1 2 3]
+MakeNamedMedium "c" "string type" "uniformgrid" "float density" [1 2] "integer nx" 2 "rgb Le" [7 8 9]
+MakeNamedMedium "d" "string type" "homogeneous" "rgb Le" [0 0 0] "float Lescale" 5
+"""
+    hs = api.HostScene(text=text)
+    a, b, c, d = (hs.desc.media[i] for i in range(4))
+    assert list(a.Le) == [0.5, 1.0, 1.5] and not a.le_scale
+    assert list(b.Le) == [4, 5, 6] and (b.le_nx, b.le_ny, b.le_nz) == (2, 2, 1) and [b.le_scale[i] for i in range(4)] == [0, 1, 2, 3]
+    assert list(c.Le) == [7, 8, 9] and (c.le_nx, c.le_ny, c.le_nz) == (1, 1, 1) and c.le_scale[0] == 1
+    assert list(d.Le) == [0, 0, 0] and not d.le_scale
+    hs.close()
+
+
 @pytest.mark.parametrize("body,code,needle", [
+    ("WorldBegin\nMakeNamedMedium \"m\" \"string type\" \"uniformgrid\" \"float density\" [1 2] \"integer nx\" 2 \"rgb Le\" [1 1 1] \"float Lescale\" [1 2 3]\n", A.ERR_INVALID, "values for \"Lescale\""),
+    ("WorldBegin\nMakeNamedMedium \"m\" \"string type\" \"rgbgrid\" \"rgb sigma_a\" [1 1 1] \"rgb Le\" [1 1 1]\n", A.ERR_UNSUPPORTED, "homogeneous and uniformgrid"),
     ("WorldBegin\nLightSource \"spot\" \"point3 from\" [1 1 1] \"point3 to\" [1 1 1]\n", A.ERR_INVALID, "from == to"),
     ("WorldBegin\nLightSource \"spot\" \"float conedeltaangle\" -1\n", A.ERR_INVALID, "conedeltaangle"),
     ("WorldBegin\nLightSource \"goniometric\"\n", A.ERR_UNSUPPORTED, "goniometric"),

@@ -1,5 +1,7 @@
 """A/B timing driver: renders a workload N times through the C ABI and prints ms per render (CUDA events inside the
-library) plus the per-stage split, and a checksum of the film so that variants can be compared for identity.
+library) plus the per-stage split, and a checksum of the film.  The film is summed with fp64 atomics in completion order, so
+the checksum of a full-size render can differ between two runs of the SAME build in a few last-bit roundings (C3: a handful of
+distinct values); identity of variants is what the pixel tests against the oracle establish, not this hash.
     VSPG_LIB=/path/to/libvspg_variant.so python tools/ab_run.py C2 3"""
 import hashlib, os, sys
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))

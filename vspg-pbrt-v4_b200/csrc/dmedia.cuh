@@ -211,6 +211,28 @@ VD MediumProps sample_point(const DMedium &m, V3 p) {
     return mp;
 }
 
+// MediumProperties::Le (media.h:259, 329-345): homogeneous media emit Le; grid media s * Le where the trilinear lookup s
+// of the "Lescale" grid (util/containers.h:804-831, zero outside the grid) is positive.  p in render space.
+VD V3 medium_emission(const DMedium &m, V3 p) {
+    if (m.type == VSPG_MEDIUM_HOMOGENEOUS) return ld3(m.Le);
+    p = apply_inverse_point(m, p);
+    p = bounds_offset(m, p);
+    const int nx = m.leN[0], ny = m.leN[1], nz = m.leN[2];
+    float psx = p.x * nx - .5f, psy = p.y * ny - .5f, psz = p.z * nz - .5f;
+    int ix = (int)floorf(psx), iy = (int)floorf(psy), iz = (int)floorf(psz);
+    float dx = psx - (float)ix, dy = psy - (float)iy, dz = psz - (float)iz;
+    auto at = [&](int x, int y, int z) {
+        if (x < 0 || y < 0 || z < 0 || x >= nx || y >= ny || z >= nz) return 0.f;
+        return __ldg(&m.leScale[(size_t)(z * ny + y) * nx + x]);
+    };
+    float d00 = lerpf(dx, at(ix, iy, iz), at(ix + 1, iy, iz));
+    float d10 = lerpf(dx, at(ix, iy + 1, iz), at(ix + 1, iy + 1, iz));
+    float d01 = lerpf(dx, at(ix, iy, iz + 1), at(ix + 1, iy, iz + 1));
+    float d11 = lerpf(dx, at(ix, iy + 1, iz + 1), at(ix + 1, iy + 1, iz + 1));
+    float s = lerpf(dz, lerpf(dy, d00, d10), lerpf(dy, d01, d11));
+    return s > 0 ? s * ld3(m.Le) : V3();
+}
+
 // ------------------------------------------------------------------ majorant iterators (media.h:76-107, 140-218)
 struct MajorantIterator {
     bool homogeneous, called;

@@ -36,6 +36,11 @@ struct DMedium {
     // extent along an axis is a power of two, so that x / extent == x * (1 / extent) for every x
     int xlateOnly, extPow2;        // extPow2: bit a set = axis a
     float invExt[3];
+    // emission (media.h:243-260, 329-345): Le rgb; grid media scale it by a trilinear lookup of leScale (leN voxels)
+    int emissive;
+    float Le[3];
+    const float *leScale;
+    int leN[3];
 };
 
 // One surface primitive: a bilinear patch (p00,p10,p01,p11) or a triangle (p0,p1,p2 in p00,p10,p01; p11 unused).

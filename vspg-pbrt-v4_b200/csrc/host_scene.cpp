@@ -422,9 +422,14 @@ struct Builder {
         m.sigma_scale = 1;
         float scale_ = (float)ps.one_float("scale", 1);
         m.g = (float)ps.one_float("g", 0);
-        float Le[3];
-        if (ps.rgb("Le", Le) && (Le[0] != 0 || Le[1] != 0 || Le[2] != 0)) lx.fail("medium emission is outside the hot-path scope (SURVEY 8f3)", VSPG_ERR_UNSUPPORTED);
-        ps.one_float("Lescale", 1);
+        float Le[3] = {0, 0, 0};
+        const bool emits = ps.rgb("Le", Le) && std::max(std::max(Le[0], Le[1]), Le[2]) != 0;   // media.cpp:191, 311: "Le" absent or MaxValue() == 0 -> no emission
+        if (emits && type != "homogeneous" && type != "uniformgrid")
+            lx.fail("medium emission is built for homogeneous and uniformgrid media only (SURVEY 8f3)", VSPG_ERR_UNSUPPORTED);
+        if (type != "uniformgrid" && type != "nanovdb") {
+            float LeScale = (float)ps.one_float("Lescale", 1);
+            if (emits) for (int i = 0; i < 3; i++) m.Le[i] = Le[i] * LeScale;   // media.h:243 Le_spec.Scale(LeScale) (photometric == 1)
+        }
         auto grid_dims = [&](size_t n) {
             m.nx = ps.one_int("nx", 1); m.ny = ps.one_int("ny", 1); m.nz = ps.one_int("nz", 1);
             if ((size_t)m.nx * m.ny * m.nz != n)
@@ -451,6 +456,17 @@ struct Builder {
             } else lx.fail("No \"density\" value provided for grid medium.");
             if (ps.floats("temperature")) lx.fail("grid medium \"temperature\" (emission) is outside the hot-path scope", VSPG_ERR_UNSUPPORTED);
             grid_dims(d.size());
+            {   // media.cpp:304-329: "Lescale" is a grid here (nx*ny*nz values); without one, a 1x1x1 grid holding LeNorm = 1
+                const auto *ls = ps.floats("Lescale");
+                if (ls && !ls->empty() && ls->size() != d.size())
+                    lx.fail("Expected " + std::to_string(m.nx) + " x " + std::to_string(m.ny) + " " + std::to_string(m.nz) + " = " + std::to_string(d.size()) +
+                            " values for \"Lescale\" but were given " + std::to_string(ls->size()) + ".");
+                if (emits) {
+                    for (int i = 0; i < 3; i++) m.Le[i] = Le[i];
+                    if (ls && !ls->empty()) { m.le_scale = own(std::vector<float>(ls->begin(), ls->end())); m.le_nx = m.nx; m.le_ny = m.ny; m.le_nz = m.nz; }
+                    else { m.le_scale = own(std::vector<float>(1, 1.f)); m.le_nx = m.le_ny = m.le_nz = 1; }
+                }
+            }
             float sa[3] = {1, 1, 1}, ss[3] = {1, 1, 1};
             ps.rgb("sigma_a", sa); ps.rgb("sigma_s", ss);
             for (int i = 0; i < 3; i++) { m.sigma_a[i] = sa[i] * scale_; m.sigma_s[i] = ss[i] * scale_; }   // media.cpp:249-250

@@ -117,6 +117,28 @@ __global__ void __launch_bounds__(kBlock) k_medium(const DScene sc, const Wavefr
     counter_add(W.counters, CNT_DDA, tc.dda);
 }
 
+// the same with the emission term compiled in (some medium of the scene emits; chosen per scene by set_scene)
+__global__ void __launch_bounds__(kBlock) k_medium_emit(const DScene sc, const Wavefront W) {
+    const int n = *W.medium.count;
+    TrackCounters tc; tc.queries = 0; tc.dda = 0;
+    for (int i = gtid(); i < n; i += gstride()) {
+        int slot = W.medium.items[i];
+        PathRegs ps; path_load(W.P, slot, ps);
+        float tHit = W.P.hit[slot].x;
+        DistanceResult res;
+        sample_distance_emit(sc, ps, tHit, tc, res);
+        path_store(W.P, slot, ps);
+        bool dead = res.terminated || !nonzero(ps.beta) || !nonzero(ps.r_u);
+        bool scat = !dead && res.scattered;
+        if (scat) W.P.ev[slot] = make_float4(res.p.x, res.p.y, res.p.z, res.mp.g);
+        queue_push(W.done, dead, slot);
+        queue_push(W.volscatter, scat, slot);
+        queue_push(W.surface, !dead && !scat, slot);
+    }
+    counter_add(W.counters, CNT_QUERIES, tc.queries);
+    counter_add(W.counters, CNT_DDA, tc.dda);
+}
+
 // ------------------------------------------------------------------ shadow-ray record (SampleLd front half, vspg.cpp:1136-1192)
 // f_hat, L and beta travel apart: the reference forms ((f_hat * T_ray) * L) / w first and multiplies by beta last
 // (vspg.cpp:1247-1250, :479 / :833), and float products do not re-associate

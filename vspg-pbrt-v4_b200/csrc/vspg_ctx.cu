@@ -68,6 +68,7 @@ struct vspg_ctx {
     bool bin_ok = false;        // the scene has a grid medium to bin over
     int *bin_keys = nullptr, *bin_hist = nullptr, *bin_offsets = nullptr, *sorted_medium = nullptr, *sorted_shadow = nullptr;
     int prim_kinds = 7;         // primitive kinds of the scene (dshapes.cuh KINDS): 1 = quads only
+    bool any_emissive = false;  // some medium emits: the delta-tracking kernel with the emission term compiled in
     bool any_nvdb = false;      // some medium is a NanoVDB grid: the resampling kernel with the NanoVDB sampler compiled in
     bool grids_ready = false;   // one-wave grids of the grid-stride kernels (occupancy API, vspg_ctx_render.inl)
     int g_generate = 0, g_intersect = 0, g_medium = 0, g_lookup0 = 0, g_lookup1 = 0, g_surface = 0, g_volscatter0 = 0, g_shade0 = 0, g_finish = 0,
@@ -233,6 +234,7 @@ int vspg_set_scene(vspg_ctx *ctx, const vspg_scene_desc *s) {
     sc.cam = s->camera;
     // ---- media
     std::vector<DMedium> media(s->n_media);
+    ctx->any_emissive = false;
     for (int i = 0; i < s->n_media; i++) {
         const vspg_medium &m = s->media[i];
         DMedium &d = media[i];
@@ -257,6 +259,19 @@ int vspg_set_scene(vspg_ctx *ctx, const vspg_scene_desc *s) {
                 int ex; float mant = std::frexp(e, &ex);
                 d.invExt[a] = 1.f / e;
                 if (e > 0 && mant == 0.5f && ex > -100 && ex < 100 && !getenv("VSPG_NO_SHORTCUTS")) d.extPow2 |= 1 << a;
+            }
+        }
+        if (std::max({m.Le[0], m.Le[1], m.Le[2]}) > 0) {   // IsEmissive(): Le_spec.MaxValue() > 0 (media.h:250, media.cpp:261)
+            if (m.type != VSPG_MEDIUM_HOMOGENEOUS && m.type != VSPG_MEDIUM_GRID)
+                return fail(ctx, VSPG_ERR_UNSUPPORTED, "set_scene: medium %d: emission is built for homogeneous and uniformgrid media only", i);
+            d.emissive = 1; memcpy(d.Le, m.Le, 12);
+            ctx->any_emissive = true;
+            if (m.type == VSPG_MEDIUM_GRID) {
+                static const float one = 1.f;
+                const bool given = m.le_scale != nullptr;
+                if (given && (m.le_nx <= 0 || m.le_ny <= 0 || m.le_nz <= 0)) return fail(ctx, VSPG_ERR_INVALID, "set_scene: medium %d: le_scale grid without dimensions", i);
+                d.leN[0] = given ? m.le_nx : 1; d.leN[1] = given ? m.le_ny : 1; d.leN[2] = given ? m.le_nz : 1;
+                CK(upload(ctx, ctx->scene_allocs, given ? m.le_scale : &one, (size_t)d.leN[0] * d.leN[1] * d.leN[2], &d.leScale));
             }
         }
         if (m.type == VSPG_MEDIUM_HOMOGENEOUS) continue;

@@ -39,7 +39,7 @@ class Medium(C.Structure):
                 ("sigma_a", F3), ("sigma_s", F3), ("sigma_scale", f32), ("g", f32), ("nx", i32), ("ny", i32), ("nz", i32),
                 ("density", PF), ("sigma_a_rgb", PF), ("sigma_s_rgb", PF), ("maj_res", i32 * 3), ("majorant", PF),
                 ("index_min", i32 * 3), ("index_from_medium", f32 * 9), ("index_origin", F3), ("density_offset", f32), ("background", f32),
-                ("majorant_scale", f32)]
+                ("majorant_scale", f32), ("Le", F3), ("le_scale", PF), ("le_nx", i32), ("le_ny", i32), ("le_nz", i32)]
 
 
 class Quad(C.Structure):

@@ -72,6 +72,13 @@ def scene_text(cfg, out_dir=None, outfile="out.exr", seed=0, integrator_name="gu
                 pre.append("AttributeBegin\nTransform [" + _v(m.T.reshape(-1)) + "]")   # column-major, as pbrt files give matrices
                 post.append("AttributeEnd")
             L += pre
+            if e.get("Le") is not None:
+                head += f' "rgb Le" [{_v(e["Le"])}]'
+                if e["type"] == "homogeneous":
+                    head += f' "float Lescale" [{_f(e["Le_scale"])}]'
+                elif e.get("Le_scale") is not None:
+                    ls = e["Le_scale"][:1, :1, :1] if placeholder_grids else e["Le_scale"]
+                    head += ' "float Lescale" [' + " ".join(repr(float(x)) for x in ls.reshape(-1)) + "]"
             if e["type"] == "homogeneous":
                 L.append(head + f' "rgb sigma_a" [{_v(e["sigma_a"])}] "rgb sigma_s" [{_v(e["sigma_s"])}]')
             elif e["type"] == "uniformgrid":

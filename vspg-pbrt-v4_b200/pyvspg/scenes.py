@@ -139,19 +139,28 @@ class Scene:
         self.log.append(("infinite", dict(L=[float(x) for x in radiance])))
         self.n_lights += 1
 
-    def add_homogeneous_medium(self, sigma_a, sigma_s, scale_=1.0, g=0.0):
+    def add_homogeneous_medium(self, sigma_a, sigma_s, scale_=1.0, g=0.0, Le=None, Le_scale=1.0):
+        """homogeneous (media.cpp:164-206); Le (rgb) x Le_scale = emitted radiance (media.h:243, 259)."""
         self.log.append(("medium", dict(type="homogeneous", sigma_a=[float(x) for x in sigma_a], sigma_s=[float(x) for x in sigma_s],
-                                        scale=float(scale_), g=float(g), index=self.n_media)))
+                                        scale=float(scale_), g=float(g), index=self.n_media,
+                                        Le=None if Le is None else [float(x) for x in Le], Le_scale=float(Le_scale))))
         self.n_media += 1
         return self.n_media - 1
 
-    def add_grid_medium(self, density, lo, hi, sigma_a, sigma_s, scale_=1.0, g=0.0, world_from_medium=None):
-        """uniformgrid (media.cpp:272-361): density[nz][ny][nx] float32, medium-space bounds lo..hi."""
+    def add_grid_medium(self, density, lo, hi, sigma_a, sigma_s, scale_=1.0, g=0.0, world_from_medium=None, Le=None, Le_scale=None):
+        """uniformgrid (media.cpp:272-361): density[nz][ny][nx] float32, medium-space bounds lo..hi.  Le (rgb): emission
+        spectrum; Le_scale: optional [nz][ny][nx] float32 grid scaling it (without one the reference uses a 1x1x1 grid of 1,
+        i.e. a trilinear tent around the centre of the box)."""
         d = np.ascontiguousarray(density, dtype=np.float32)
         self._keep.append(d)
+        if Le_scale is not None:
+            Le_scale = np.ascontiguousarray(Le_scale, dtype=np.float32)
+            assert Le is not None and Le_scale.shape == d.shape
+            self._keep.append(Le_scale)
         self.log.append(("medium", dict(type="uniformgrid", density=d, lo=[float(x) for x in lo], hi=[float(x) for x in hi],
                                         sigma_a=[float(x) for x in sigma_a], sigma_s=[float(x) for x in sigma_s], scale=float(scale_), g=float(g),
-                                        world_from_medium=world_from_medium, index=self.n_media)))
+                                        world_from_medium=world_from_medium, index=self.n_media,
+                                        Le=None if Le is None else [float(x) for x in Le], Le_scale=Le_scale)))
         self.n_media += 1
         return self.n_media - 1
 
@@ -204,6 +213,9 @@ class Scene:
             if e["type"] == "uniformgrid":
                 m.nz, m.ny, m.nx = e["density"].shape
                 m.density = e["density"].ctypes.data_as(A.PF)
+                if e.get("Le_scale") is not None:
+                    m.le_nz, m.le_ny, m.le_nx = e["Le_scale"].shape
+                    m.le_scale = e["Le_scale"].ctypes.data_as(A.PF)
             else:
                 m.nz, m.ny, m.nx = e["sigma_a_rgb"].shape[:3]
                 m.sigma_a_rgb = e["sigma_a_rgb"].ctypes.data_as(A.PF)
