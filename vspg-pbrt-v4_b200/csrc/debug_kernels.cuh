@@ -164,7 +164,7 @@ __global__ void k_debug_sample_distance(const DScene sc, int n, const vspg_sd_in
         ps.pixel = I.pixel_y * sc.cam.width + I.pixel_x; ps.sampleIndex = 0;
         TrackCounters tc; tc.queries = 0; tc.dda = 0;
         DistanceResult res; res.p = V3(); res.mp.sigma_a = V3(); res.mp.sigma_s = V3(); res.mp.g = 0;
-        sample_distance_emit(sc, ps, I.t_max, tc, res);
+        sample_distance_full(sc, ps, I.t_max, tc, res);
         O.scattered = res.scattered; O.terminated = res.terminated; O.depth = ps.fl.depth;
         V3 p = res.scattered ? res.p : V3();
         O.p[0] = p.x; O.p[1] = p.y; O.p[2] = p.z;

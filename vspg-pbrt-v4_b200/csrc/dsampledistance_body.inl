@@ -1,4 +1,5 @@
-// Body of sample_distance() / sample_distance_emit(): included twice by dsampledistance.cuh with VSPG_SD_NAME / VSPG_SD_EMIT set.
+// Body of sample_distance() / sample_distance_emit() / sample_distance_full(): included by dsampledistance.cuh with VSPG_SD_NAME,
+// VSPG_SD_EMIT and VSPG_SD_RESAMPLING set.
 // Two plain functions instead of one template: as a template <bool EMIT> the same source compiled to a k_medium with a
 // 1392-byte stack frame instead of 344 bytes (C3 medium stage 62 -> 71 ms), also for EMIT = false.
 VD void VSPG_SD_NAME(const DScene &sc, PathRegs &ps, float tHit, TrackCounters &tc, DistanceResult &res) {
@@ -31,7 +32,7 @@ VD void VSPG_SD_NAME(const DScene &sc, PathRegs &ps, float tHit, TrackCounters &
     ray.d = normalize(ray.d);
     float uT = ps.rng.uniform();
 
-    const bool use_resampling = !ip.vsp_sampling_nds && med.type != VSPG_MEDIUM_HOMOGENEOUS;
+    const bool use_resampling = VSPG_SD_RESAMPLING && !ip.vsp_sampling_nds && med.type != VSPG_MEDIUM_HOMOGENEOUS;
     if (use_resampling) {
         float volumeRatioCompensated = 0, majorantScale = 1;
         float weightSum = 0;

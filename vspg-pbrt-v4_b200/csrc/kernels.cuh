@@ -96,48 +96,41 @@ __global__ void __launch_bounds__(kBlock, VSPG_INTERSECT_MINB) k_intersect(const
 }
 
 // ------------------------------------------------------------------ SampleDistance (vspg.cpp:318-351, 637-1096)
-__global__ void __launch_bounds__(kBlock) k_medium(const DScene sc, const Wavefront W) {
-    const int n = *W.medium.count;
-    TrackCounters tc; tc.queries = 0; tc.dda = 0;
-    for (int i = gtid(); i < n; i += gstride()) {
-        int slot = W.medium.items[i];
-        PathRegs ps; path_load(W.P, slot, ps);
-        float tHit = W.P.hit[slot].x;
-        DistanceResult res;
-        sample_distance(sc, ps, tHit, tc, res);
-        path_store(W.P, slot, ps);
-        bool dead = res.terminated || !nonzero(ps.beta) || !nonzero(ps.r_u);
-        bool scat = !dead && res.scattered;
-        if (scat) W.P.ev[slot] = make_float4(res.p.x, res.p.y, res.p.z, res.mp.g);
-        queue_push(W.done, dead, slot);
-        queue_push(W.volscatter, scat, slot);
-        queue_push(W.surface, !dead && !scat, slot);
+// One thread per ray, start to end of the delta-tracking walk.  The walk is a chain of dependent gathers (majorant cell,
+// density cell) and the kernel is bound by their latency, not by registers: on C3 (NDS sampling over a 128^3 grid) the medium
+// stage went 63.6 -> 59.9 -> 55.3 -> 50.6 -> 47.1 -> 43.5 ms at 3 (ptxas' own choice: 168 registers) / 4 / 6 / 8 / 12 / 16
+// CTAs per SM -- 32 registers and 4.6 KB of spill traffic per thread at full occupancy still win (profiles/r02_summary.md
+// section 7).  Scenes whose media are all homogeneous have no gathers to hide and keep the unconstrained build (C1: 0.36 vs
+// 0.47 ms).  Three plain kernels from one macro (emissive scenes always take the
+// full-occupancy one): as templates the same source compiled to
+// a 1392-byte stack frame (dsampledistance_body.inl).
+#ifndef VSPG_MEDIUM_MINB
+#define VSPG_MEDIUM_MINB 16
+#endif
+#define VSPG_DEFINE_K_MEDIUM(NAME, BOUNDS, SAMPLE_DISTANCE)                                               \
+    __global__ void BOUNDS NAME(const DScene sc, const Wavefront W) {                                     \
+        const int n = *W.medium.count;                                                                    \
+        TrackCounters tc; tc.queries = 0; tc.dda = 0;                                                     \
+        for (int i = gtid(); i < n; i += gstride()) {                                                     \
+            int slot = W.medium.items[i];                                                                 \
+            PathRegs ps; path_load(W.P, slot, ps);                                                        \
+            float tHit = W.P.hit[slot].x;                                                                 \
+            DistanceResult res;                                                                           \
+            SAMPLE_DISTANCE(sc, ps, tHit, tc, res);                                                       \
+            path_store(W.P, slot, ps);                                                                    \
+            bool dead = res.terminated || !nonzero(ps.beta) || !nonzero(ps.r_u);                          \
+            bool scat = !dead && res.scattered;                                                           \
+            if (scat) W.P.ev[slot] = make_float4(res.p.x, res.p.y, res.p.z, res.mp.g);                    \
+            queue_push(W.done, dead, slot);                                                               \
+            queue_push(W.volscatter, scat, slot);                                                         \
+            queue_push(W.surface, !dead && !scat, slot);                                                  \
+        }                                                                                                 \
+        counter_add(W.counters, CNT_QUERIES, tc.queries);                                                 \
+        counter_add(W.counters, CNT_DDA, tc.dda);                                                         \
     }
-    counter_add(W.counters, CNT_QUERIES, tc.queries);
-    counter_add(W.counters, CNT_DDA, tc.dda);
-}
-
-// the same with the emission term compiled in (some medium of the scene emits; chosen per scene by set_scene)
-__global__ void __launch_bounds__(kBlock) k_medium_emit(const DScene sc, const Wavefront W) {
-    const int n = *W.medium.count;
-    TrackCounters tc; tc.queries = 0; tc.dda = 0;
-    for (int i = gtid(); i < n; i += gstride()) {
-        int slot = W.medium.items[i];
-        PathRegs ps; path_load(W.P, slot, ps);
-        float tHit = W.P.hit[slot].x;
-        DistanceResult res;
-        sample_distance_emit(sc, ps, tHit, tc, res);
-        path_store(W.P, slot, ps);
-        bool dead = res.terminated || !nonzero(ps.beta) || !nonzero(ps.r_u);
-        bool scat = !dead && res.scattered;
-        if (scat) W.P.ev[slot] = make_float4(res.p.x, res.p.y, res.p.z, res.mp.g);
-        queue_push(W.done, dead, slot);
-        queue_push(W.volscatter, scat, slot);
-        queue_push(W.surface, !dead && !scat, slot);
-    }
-    counter_add(W.counters, CNT_QUERIES, tc.queries);
-    counter_add(W.counters, CNT_DDA, tc.dda);
-}
+VSPG_DEFINE_K_MEDIUM(k_medium, __launch_bounds__(kBlock, VSPG_MEDIUM_MINB), sample_distance)             // some grid medium in the scene
+VSPG_DEFINE_K_MEDIUM(k_medium_emit, __launch_bounds__(kBlock, VSPG_MEDIUM_MINB), sample_distance_emit)   // some medium emits (homogeneous or grid)
+VSPG_DEFINE_K_MEDIUM(k_medium_hom, __launch_bounds__(kBlock), sample_distance)                           // homogeneous media only
 
 // ------------------------------------------------------------------ shadow-ray record (SampleLd front half, vspg.cpp:1136-1192)
 // f_hat, L and beta travel apart: the reference forms ((f_hat * T_ray) * L) / w first and multiplies by beta last

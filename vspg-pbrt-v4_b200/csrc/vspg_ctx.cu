@@ -68,10 +68,11 @@ struct vspg_ctx {
     bool bin_ok = false;        // the scene has a grid medium to bin over
     int *bin_keys = nullptr, *bin_hist = nullptr, *bin_offsets = nullptr, *sorted_medium = nullptr, *sorted_shadow = nullptr;
     int prim_kinds = 7;         // primitive kinds of the scene (dshapes.cuh KINDS): 1 = quads only
+    bool any_grid_medium = false;   // some medium is not homogeneous: k_medium at full occupancy (kernels.cuh)
     bool any_emissive = false;  // some medium emits: the delta-tracking kernel with the emission term compiled in
     bool any_nvdb = false;      // some medium is a NanoVDB grid: the resampling kernel with the NanoVDB sampler compiled in
     bool grids_ready = false;   // one-wave grids of the grid-stride kernels (occupancy API, vspg_ctx_render.inl)
-    int g_generate = 0, g_intersect = 0, g_medium = 0, g_lookup0 = 0, g_lookup1 = 0, g_surface = 0, g_volscatter0 = 0, g_shade0 = 0, g_finish = 0,
+    int g_generate = 0, g_intersect = 0, g_medium = 0, g_medium_hom = 0, g_lookup0 = 0, g_lookup1 = 0, g_surface = 0, g_volscatter0 = 0, g_shade0 = 0, g_finish = 0,
         g_bin = 148, g_shadow_gray = 0, g_shadow_rgb = 0;
     int rs_occ = 5;               // CTAs/SM the gray resampling kernel is compiled for (VSPG_RS_OCC=4|5, A/B runs)
     int rs_refill = kRsRefillIdleDefault;   // VSPG_RS_REFILL overrides (A/B runs)
@@ -234,7 +235,7 @@ int vspg_set_scene(vspg_ctx *ctx, const vspg_scene_desc *s) {
     sc.cam = s->camera;
     // ---- media
     std::vector<DMedium> media(s->n_media);
-    ctx->any_emissive = false;
+    ctx->any_emissive = false; ctx->any_grid_medium = false;
     for (int i = 0; i < s->n_media; i++) {
         const vspg_medium &m = s->media[i];
         DMedium &d = media[i];
@@ -275,6 +276,7 @@ int vspg_set_scene(vspg_ctx *ctx, const vspg_scene_desc *s) {
             }
         }
         if (m.type == VSPG_MEDIUM_HOMOGENEOUS) continue;
+        ctx->any_grid_medium = true;
         const bool scalarGrid = m.type == VSPG_MEDIUM_GRID || m.type == VSPG_MEDIUM_NANOVDB;
         if (m.type == VSPG_MEDIUM_NANOVDB) {
             if (!m.majorant) return fail(ctx, VSPG_ERR_INVALID, "set_scene: medium %d (nanovdb) comes without its majorant grid", i);

@@ -5,7 +5,7 @@ enum { Q_A = 0, Q_B = 1, Q_MEDIUM = 2, Q_SURFACE = 3, Q_SHADE = 4, Q_VOLSCATTER 
        Q_CURSORS = 4, Q_INTS = Q_COUNT + Q_CURSORS };  // + per-kernel dynamic work cursors
 
 // Everything the captured wave graph depends on; compared bytewise against the current values before each replay.
-struct WaveGraphKey { DScene sc; Wavefront W; int vgrid, sgrid, sblock, rs_refill, rs_occ, nGridWin, all_gray, any_nvdb, any_emissive, sort_mode, prim_kinds, shadow_persist; cudaAccessPolicyWindow win; };
+struct WaveGraphKey { DScene sc; Wavefront W; int vgrid, sgrid, sblock, rs_refill, rs_occ, nGridWin, all_gray, any_nvdb, any_emissive, any_grid_medium, sort_mode, prim_kinds, shadow_persist; cudaAccessPolicyWindow win; };
 
 static int ensure_wavefront(vspg_ctx *ctx, unsigned long long total) {
     // Default: up to 16.8 M paths in flight (5.7 GB of the 180 GB).  Measured on C2 (profiles/r01z_summary.md, r02b/c): 2 M ->
@@ -127,7 +127,7 @@ int vspg_render(vspg_ctx *ctx, int spp_begin, int spp_end, int spp_stride, int x
             int o = 0; cudaError_t e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&o, kernel, kBlock, 0);
             *out = ctx->sm_count * std::max(1, o); return e;
         };
-        CK(occ(k_generate, &ctx->g_generate)); CK(occ(k_intersect<kKindsAll>, &ctx->g_intersect)); CK(occ(k_medium, &ctx->g_medium));
+        CK(occ(k_generate, &ctx->g_generate)); CK(occ(k_intersect<kKindsAll>, &ctx->g_intersect)); CK(occ(k_medium, &ctx->g_medium)); CK(occ(k_medium_hom, &ctx->g_medium_hom));
         CK(occ(k_lookup<false, kKindsAll>, &ctx->g_lookup0)); CK(occ(k_lookup<true, kKindsAll>, &ctx->g_lookup1)); CK(occ(k_surface<kKindsAll>, &ctx->g_surface));
         CK(occ(k_volscatter<0>, &ctx->g_volscatter0)); CK(occ(k_shade<0, kKindsAll>, &ctx->g_shade0)); CK(occ(k_finish, &ctx->g_finish));
         CK(occ(k_bin_count, &ctx->g_bin));
@@ -183,8 +183,10 @@ int vspg_render(vspg_ctx *ctx, int spp_begin, int spp_end, int spp_stride, int x
         else if (ctx->all_gray && ctx->rs_occ == 5) CK(launch_tracking(k_medium_rs<true, VSPG_RS_MINB>, ctx->sm_count * VSPG_RS_MINB, sc, Wh, ctx->qcounts + Q_COUNT, ctx->rs_refill));
         else if (ctx->all_gray) CK(launch_tracking(k_medium_rs<true, 4>, ctx->sm_count * 4, sc, Wh, ctx->qcounts + Q_COUNT, ctx->rs_refill));
         else CK(launch_tracking(k_medium_rs<false, 4>, ctx->sm_count * 4, sc, Wh, ctx->qcounts + Q_COUNT, ctx->rs_refill));
+        // full-occupancy builds hide the gathers of the walk over a grid; homogeneous-only scenes have none (kernels.cuh)
         if (ctx->any_emissive) { VSPG_STAGE(VSPG_K_MEDIUM, (k_medium_emit<<<ctx->g_medium, kBlock, 0, s>>>(sc, Wh))); }
-        else { VSPG_STAGE(VSPG_K_MEDIUM, (k_medium<<<ctx->g_medium, kBlock, 0, s>>>(sc, Wh))); }
+        else if (ctx->any_grid_medium) { VSPG_STAGE(VSPG_K_MEDIUM, (k_medium<<<ctx->g_medium, kBlock, 0, s>>>(sc, Wh))); }
+        else { VSPG_STAGE(VSPG_K_MEDIUM, (k_medium_hom<<<ctx->g_medium_hom, kBlock, 0, s>>>(sc, Wh))); }
         if (guidedVol) {
             if (quadsOnly) k_lookup<false, kKindsQuads><<<ctx->g_lookup0, kBlock, 0, s>>>(sc, Wh, Wh.volscatter, Wh.vol8, Wh.vol16, Wh.vol32);
             else k_lookup<false, kKindsAll><<<ctx->g_lookup0, kBlock, 0, s>>>(sc, Wh, Wh.volscatter, Wh.vol8, Wh.vol16, Wh.vol32);
@@ -249,7 +251,7 @@ int vspg_render(vspg_ctx *ctx, int spp_begin, int spp_end, int spp_stride, int x
         // all of which are compared below; it is rebuilt when any of them changed.
         WaveGraphKey key;
         memset(&key, 0, sizeof key);
-        key.sc = sc; key.W = Wab; key.vgrid = vgrid; key.sgrid = sgrid; key.sblock = sblock; key.rs_refill = ctx->rs_refill; key.rs_occ = ctx->rs_occ; key.all_gray = ctx->all_gray; key.any_emissive = ctx->any_emissive; key.shadow_persist = ctx->shadow_persist * 100 + ctx->shadow_refill; key.prim_kinds = ctx->prim_kinds; key.sort_mode = ctx->bin_ok ? ctx->sort_mode : 0; key.any_nvdb = ctx->any_nvdb;
+        key.sc = sc; key.W = Wab; key.vgrid = vgrid; key.sgrid = sgrid; key.sblock = sblock; key.rs_refill = ctx->rs_refill; key.rs_occ = ctx->rs_occ; key.all_gray = ctx->all_gray; key.any_emissive = ctx->any_emissive; key.any_grid_medium = ctx->any_grid_medium; key.shadow_persist = ctx->shadow_persist * 100 + ctx->shadow_refill; key.prim_kinds = ctx->prim_kinds; key.sort_mode = ctx->bin_ok ? ctx->sort_mode : 0; key.any_nvdb = ctx->any_nvdb;
         key.nGridWin = nGridWin; if (nGridWin) key.win = gridWin[0].val.accessPolicyWindow;
         if (!ctx->wave_exec || memcmp(&key, ctx->wave_key, sizeof key) != 0) {
             if (ctx->wave_exec) { cudaGraphExecDestroy(ctx->wave_exec); ctx->wave_exec = nullptr; }
