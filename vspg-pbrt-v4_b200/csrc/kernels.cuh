@@ -14,6 +14,9 @@ constexpr int kBlock = 128;
 #ifndef VSPG_INTERSECT_MINB
 #define VSPG_INTERSECT_MINB 1
 #endif
+#ifndef VSPG_SCATTER0_MINB
+#define VSPG_SCATTER0_MINB 4   // CTAs / SM of the one-thread-per-vertex scatter kernels (k_volscatter<0>, k_shade<0>: unguided configurations; C1 shade 1.77 -> 1.67 ms, 6 / 8 the same, 16 none)
+#endif
 
 VD int gtid() { return blockIdx.x * blockDim.x + threadIdx.x; }
 VD int gstride() { return gridDim.x * blockDim.x; }
@@ -330,7 +333,7 @@ __global__ void __launch_bounds__(kBlock, VSPG_LOOKUP_MINB) k_lookup(const DScen
 // pre-drawn light sample, and the group's leader assembles the shadow-ray record and the outgoing path record in a
 // scalar epilogue, straight from the SoA streams, once the mixture is dead.
 template <int G>
-__global__ void __launch_bounds__(G > 0 ? 256 : kBlock, G > 0 ? VSPG_VOL_MINB : 1) k_volscatter(const DScene sc, const Wavefront W, const Queue in) {
+__global__ void __launch_bounds__(G > 0 ? 256 : kBlock, G > 0 ? VSPG_VOL_MINB : VSPG_SCATTER0_MINB) k_volscatter(const DScene sc, const Wavefront W, const Queue in) {
     const int n = *in.count;
     const GroupIter<G> gi;
     const bool leader = gi.leader;

@@ -90,7 +90,7 @@ struct ShadeKeep { float p[3], pe[3], n[3], ns[3]; int mIn, mOut, rayMed, hasIf;
 #define VSPG_SHADE_MINB 4   // r02: 4 CTAs of 256 threads (64 registers) beat 3 (80): C2 shade 13.5 -> 12.7 ms, C4 32.4 -> 29.7 ms
 #endif
 template <int G, int KINDS = kKindsAll>
-__global__ void __launch_bounds__(G > 0 ? 256 : kBlock, G > 0 ? VSPG_SHADE_MINB : 1) k_shade(const DScene sc, const Wavefront W, const Queue in) {
+__global__ void __launch_bounds__(G > 0 ? 256 : kBlock, G > 0 ? VSPG_SHADE_MINB : VSPG_SCATTER0_MINB) k_shade(const DScene sc, const Wavefront W, const Queue in) {
     __shared__ ShadeKeep keep_s[G > 0 ? 256 / G : kBlock];
     ShadeKeep &K = keep_s[G > 0 ? threadIdx.x / (G > 0 ? G : 1) : threadIdx.x];
     const int n = *in.count;
